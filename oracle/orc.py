@@ -1,0 +1,306 @@
+"""TEST INFRASTRUCTURE — ctypes front-end to the CPU oracle (oracle/_build/liborc.so).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module; the product package gpirt_b200 never does. All matrices are column-major float64,
+exactly as the reference's Armadillo containers lay them out (y: n x m with NaN = missing).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = os.path.join(_HERE, "_build", "liborc.so")
+NGRID = 1001
+BLOCKS = {"f": 0, "fstar": 1, "theta": 2, "beta": 3, "thr": 4}
+
+
+def build(force=False):
+    """Compile liborc.so (and oracle/_ref when /root/reference is present)."""
+    if force or not os.path.exists(_LIB):
+        subprocess.run(["make", "-C", _HERE, "_build/liborc.so"], check=True, capture_output=True)
+    return _LIB
+
+
+class Src(C.Structure):
+    _fields_ = [("mode", C.c_int32), ("z", C.c_void_p), ("zstride", C.c_uint64), ("u", C.c_void_p),
+                ("ustride", C.c_uint64), ("seed", C.c_uint64), ("chain", C.c_uint32), ("iter", C.c_uint32)]
+
+
+_lib = None
+_dp = C.POINTER(C.c_double)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        L = C.CDLL(_LIB)
+        L.orc_pnorm.restype = C.c_double
+        L.orc_pnorm.argtypes = [C.c_double]
+        L.orc_ll_bar_sparse.restype = C.c_double
+        L.orc_grid_value.restype = C.c_double
+        L.orc_grid_value.argtypes = [C.c_int]
+        L.orc_grid_index.argtypes = [C.c_double]
+        L.orc_total_ll.restype = C.c_double
+        L.orc_last_ll.restype = C.c_double
+        L.orc_create.restype = C.c_void_p
+        for name in ("orc_destroy", "orc_set_state", "orc_get_state", "orc_get_L", "orc_set_L", "orc_get_mu",
+                     "orc_compute_mu", "orc_update_cholesky", "orc_mt_seed_all", "orc_num_threads", "orc_draw_f",
+                     "orc_draw_fstar", "orc_draw_theta", "orc_gather_f", "orc_draw_beta", "orc_draw_threshold",
+                     "orc_total_ll", "orc_item_ll", "orc_sweep", "orc_last_ll", "orc_get_diag", "orc_run_mt",
+                     "orc_set_opts"):
+            getattr(L, name).argtypes = None
+        _lib = L
+    return _lib
+
+
+def _f64(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _F(a):
+    """column-major float64 copy"""
+    return np.asfortranarray(np.asarray(a, dtype=np.float64))
+
+
+# ---- leaves ------------------------------------------------------------------------------------
+def pnorm(x):
+    x = _f64(x).ravel()
+    out = np.empty_like(x)
+    lib().orc_pnorm_vec(_p(x), C.c_uint64(x.size), _p(out))
+    return out
+
+
+def K(x1, x2, sds):
+    x1, x2, sds = _f64(x1), _f64(x2), _f64(sds)
+    out = np.empty((x1.size, x2.size), order="F")
+    lib().orc_K(_p(x1), C.c_uint64(x1.size), _p(x2), C.c_uint64(x2.size), _p(sds), _p(out))
+    return out
+
+
+def K_time(x1, x2, os_, ls, tsds, kernel="Matern"):
+    x1, x2, tsds = _f64(x1), _f64(x2), _f64(tsds)
+    out = np.zeros((x1.size, x2.size), order="F")
+    k = {"Matern": 0, "RBF": 1}.get(kernel, 2)
+    lib().orc_K_time(_p(x1), C.c_uint64(x1.size), _p(x2), C.c_uint64(x2.size), C.c_double(os_), C.c_double(ls),
+                     _p(tsds), C.c_int(k), _p(out))
+    return out
+
+
+def chol(A, long_double=False):
+    A = _F(A).copy(order="F")
+    fn = lib().orc_chol_ld if long_double else lib().orc_chol
+    info = fn(_p(A), C.c_uint64(A.shape[0]))
+    return A, info
+
+
+def double_solve(L, x):
+    L = _F(L)
+    x = _f64(x).copy()
+    lib().orc_double_solve(_p(L), C.c_uint64(L.shape[0]), _p(x))
+    return x
+
+
+def trsv_lower(L, x):
+    L = _F(L)
+    x = _f64(x).copy()
+    lib().orc_trsv_lower(_p(L), C.c_uint64(L.shape[0]), _p(x))
+    return x
+
+
+def ll_bar_sparse(f, y, mu, thr):
+    f, y, mu, thr = _f64(f), _f64(y), _f64(mu), _f64(thr)
+    return lib().orc_ll_bar_sparse(_p(f), _p(y), _p(mu), _p(thr), C.c_uint64(f.size))
+
+
+def delta_to_threshold(d):
+    d = _f64(d)
+    Cc = d.size + 1
+    out = np.empty(Cc + 1)
+    lib().orc_delta_to_threshold(_p(d), C.c_uint64(Cc), _p(out))
+    return out
+
+
+def threshold_to_delta(t):
+    t = _f64(t)
+    Cc = t.size - 1
+    out = np.empty(Cc - 1)
+    lib().orc_threshold_to_delta(_p(t), C.c_uint64(Cc), _p(out))
+    return out
+
+
+def grid_index(theta):
+    return lib().orc_grid_index(C.c_double(theta))
+
+
+def grid_value(idx):
+    return lib().orc_grid_value(C.c_int(idx))
+
+
+def philox_uniform(seed, chain, it, stream, unit, count):
+    out = np.empty(count)
+    lib().orc_philox_uniform(C.c_uint64(seed), C.c_uint32(chain), C.c_uint32(it), C.c_uint32(stream),
+                             C.c_uint32(unit), C.c_uint64(count), _p(out))
+    return out
+
+
+def philox_normal(seed, chain, it, stream, unit, count):
+    out = np.empty(count)
+    lib().orc_philox_normal(C.c_uint64(seed), C.c_uint32(chain), C.c_uint32(it), C.c_uint32(stream),
+                            C.c_uint32(unit), C.c_uint64(count), _p(out))
+    return out
+
+
+def philox_raw(ctr, key):
+    out = np.empty(4, dtype=np.uint32)
+    lib().orc_philox_raw(*(C.c_uint32(int(c)) for c in ctr), C.c_uint32(int(key[0])), C.c_uint32(int(key[1])), _p(out))
+    return out
+
+
+# ---- sampler -----------------------------------------------------------------------------------
+def supplied(z=None, u=None):
+    """Src for caller-supplied streams: z is (nz, units) column-major, u is (ustride, units)."""
+    s = Src()
+    s.mode = 0
+    s._keep = []
+    if z is not None:
+        z = _F(z)
+        s.z, s.zstride = z.ctypes.data, z.shape[0]
+        s._keep.append(z)
+    if u is not None:
+        u = _F(u)
+        s.u, s.ustride = u.ctypes.data, u.shape[0]
+        s._keep.append(u)
+    return s
+
+
+def philox(seed, chain, it):
+    s = Src()
+    s.mode, s.seed, s.chain, s.iter = 1, seed, chain, it
+    return s
+
+
+def mt():
+    s = Src()
+    s.mode = 2
+    return s
+
+
+class Sampler:
+    """CPU oracle of the reference sweep at horizon 1, constant_IRF 0 (src/gpirtMCMC.cpp:261-331)."""
+
+    def __init__(self, y, C_, beta_prior_sds, theta_prior_sds=None, faithful=0, p_beta=3, theta_regime=0, theta_os=1.0):
+        y = _F(y)
+        self.n, self.m = y.shape
+        self.C = int(C_)
+        sds = _F(beta_prior_sds)
+        assert sds.shape == (3, self.m)
+        tps = _F(np.zeros((2, self.n)) if theta_prior_sds is None else theta_prior_sds)
+        self._h = C.c_void_p(lib().orc_create(C.c_uint64(self.n), C.c_uint64(self.m), C.c_uint64(self.C), _p(y), _p(sds), _p(tps)))
+        lib().orc_set_opts(self._h, C.c_int(faithful), C.c_int(p_beta), C.c_int(theta_regime), C.c_double(theta_os))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().orc_destroy(self._h)
+            self._h = None
+
+    def set_state(self, theta=None, beta=None, f=None, thr=None, fstar=None):
+        a = [None if x is None else _F(x) for x in (theta, beta, f, thr, fstar)]
+        if a[1] is not None and a[1].shape[0] == 2:  # recover_fstar's 2-row beta
+            a[1] = _F(np.vstack([a[1], np.zeros((1, self.m))]))
+        lib().orc_set_state(self._h, *[_p(x) for x in a])
+
+    def state(self):
+        th = np.empty(self.n)
+        be = np.empty((3, self.m), order="F")
+        f = np.empty((self.n, self.m), order="F")
+        thr = np.empty((self.m, self.C + 1), order="F")
+        fs = np.empty((NGRID, self.m), order="F")
+        lib().orc_get_state(self._h, _p(th), _p(be), _p(f), _p(thr), _p(fs))
+        return dict(theta=th, beta=be, f=f, thr=thr, fstar=fs)
+
+    def L(self):
+        out = np.empty((self.n, self.n), order="F")
+        lib().orc_get_L(self._h, _p(out))
+        return out
+
+    def set_L(self, L):
+        L = _F(L)
+        lib().orc_set_L(self._h, _p(L))
+
+    def mu(self):
+        mu = np.empty((self.n, self.m), order="F")
+        ms = np.empty((NGRID, self.m), order="F")
+        lib().orc_get_mu(self._h, _p(mu), _p(ms))
+        return mu, ms
+
+    def compute_mu(self):
+        lib().orc_compute_mu(self._h)
+
+    def update_cholesky(self):
+        return lib().orc_update_cholesky(self._h)
+
+    def mt_seed_all(self, base):
+        lib().orc_mt_seed_all(self._h, C.c_uint32(base))
+
+    def num_threads(self):
+        return lib().orc_num_threads(self._h)
+
+    def draw_f(self, src, nu=None):
+        nu = None if nu is None else _F(nu)
+        lib().orc_draw_f(self._h, C.byref(src), _p(nu))
+
+    def draw_fstar(self, src):
+        return lib().orc_draw_fstar(self._h, C.byref(src))
+
+    def draw_theta(self, src):
+        lib().orc_draw_theta(self._h, C.byref(src))
+
+    def gather_f(self):
+        lib().orc_gather_f(self._h)
+
+    def draw_beta(self, src):
+        lib().orc_draw_beta(self._h, C.byref(src))
+
+    def draw_threshold(self, src):
+        lib().orc_draw_threshold(self._h, C.byref(src))
+
+    def total_ll(self):
+        return lib().orc_total_ll(self._h)
+
+    def item_ll(self):
+        out = np.empty(self.m)
+        lib().orc_item_ll(self._h, _p(out))
+        return out
+
+    def sweep(self, srcs):
+        arr = (Src * 5)()
+        keep = []
+        for k, name in enumerate(("f", "fstar", "theta", "beta", "thr")):
+            s = srcs[name] if isinstance(srcs, dict) else srcs
+            for fld, _ in Src._fields_:
+                setattr(arr[k], fld, getattr(s, fld))
+            keep.append(s)
+        return lib().orc_sweep(self._h, arr)
+
+    def last_ll(self):
+        return lib().orc_last_ll(self._h)
+
+    def diag(self, block):
+        units = self.n if block == "theta" else self.m
+        ev = np.empty(units, dtype=np.int32)
+        mg = np.empty(units)
+        over = lib().orc_get_diag(self._h, C.c_int(BLOCKS[block]), _p(ev), _p(mg))
+        return ev, mg, bool(over)
+
+    def run_mt(self, iter0, iters, store=True):
+        th = np.empty((self.n, iters), order="F") if store else None
+        ll = np.empty(iters) if store else None
+        info = lib().orc_run_mt(self._h, C.c_int(iter0), C.c_int(iters), _p(th), _p(ll))
+        return info, th, ll

@@ -1,0 +1,86 @@
+// TEST INFRASTRUCTURE — CPU oracle: the per-block samplers and the sweep (see orc_math.h header).
+// Restated from (citations relative to /root/reference):
+//   ESS skeleton              src/draw-f.cpp:5-45 (identical in draw-theta.cpp:26-84, draw-beta.cpp:4-49,
+//                             draw_threshold.cpp:99-169)
+//   draw_f                    src/draw-f.cpp:47-83           (constant_IRF == 0, horizon == 1)
+//   draw_fstar                src/draw-fstar.cpp:18-57
+//   draw_theta                src/draw-theta.cpp:4-24,112-170 (+ the L_i of :171-236 at horizon 1)
+//   f <- f* gather            src/gpirtMCMC.cpp:291-298
+//   draw_beta                 src/draw-beta.cpp:51-101
+//   draw_threshold            src/draw_threshold.cpp:206-228
+//   sweep order / total ll    src/gpirtMCMC.cpp:261-331
+// Scope: horizon == 1, constant_IRF == 0 (every BASELINE.json config). Parity of this file itself
+// is pinned against the reference's own translation units compiled under oracle/_ref (see
+// oracle/Makefile and tests/test_oracle_vs_ref.py).
+#pragma once
+#include <algorithm>
+#include <cstring>
+#include <vector>
+
+#include "orc_math.h"
+#include "orc_rng.h"
+
+namespace orc {
+
+static const double TWO_PI = 6.283185307179586476925286766559;  // Rmath M_2PI
+static const size_t NGRID = 1001;                               // regspace(-5, 0.01, 5)
+
+inline double grid_value(int idx) { return -5.0 + double(idx) * 0.01; }
+inline int grid_index(double theta) {
+    int idx = static_cast<int>(std::round((theta + 5.0) / 0.01));
+    return std::max(0, std::min(idx, int(NGRID) - 1));
+}
+
+enum Block { B_F = 0, B_FSTAR = 1, B_THETA = 2, B_BETA = 3, B_THR = 4, N_BLOCKS = 5 };
+
+// Where random numbers come from for one call of a block sampler.
+struct Src {
+    int mode = 0;  // 0 supplied, 1 philox, 2 reference ThreadRNG (mt19937)
+    // supplied: z[unit*zstride + i], u[unit*ustride + k]
+    const double* z = nullptr; size_t zstride = 0;
+    const double* u = nullptr; size_t ustride = 0;
+    // philox
+    uint64_t seed = 0; uint32_t chain = 0, iter = 0, zs = 0, us = 0;
+    // mt: one generator per worker thread
+    std::vector<MtRng>* mts = nullptr;
+};
+
+struct Diag {  // per-unit diagnostics of one block call
+    std::vector<int32_t> evals;    // likelihood evaluations (1 + proposals)
+    std::vector<double> margin;    // min |ll' - log_y| over the unit's proposals
+    bool overrun = false;          // a supplied stream ran dry
+    void reset(size_t n) { evals.assign(n, 0); margin.assign(n, std::numeric_limits<double>::infinity()); overrun = false; }
+};
+
+struct Sampler {
+    size_t n = 0, m = 0, C = 0;
+    int p_beta = 3;            // rows of beta: 3 in gpirtMCMC, 2 in recover_fstar (src/recover_fstar.cpp:58-60)
+    int faithful = 0;          // 1: keep the reference's redundant work (second chol, table copies)
+    int theta_regime = 0;      // 0 CST / RDM: L_i = sqrt(1+sd0_i^2); 1 GP-over-time at H=1: sqrt(os^2+1e-6)
+    double theta_os = 1.0;
+    std::vector<double> y;                 // n x m, NaN missing
+    std::vector<std::vector<uint64_t>> obs_persons, obs_items;
+    std::vector<double> sds;               // beta_prior_sds 3 x m
+    std::vector<double> theta_prior_sds;   // 2 x n
+    // state
+    std::vector<double> theta, beta, f, thr, fstar, L;
+    double ll = 0.0;
+    // scratch
+    std::vector<double> f_new, mu, mu_star, Lpost, W;
+    std::vector<MtRng> mts;
+    Diag diag[N_BLOCKS];
+
+    void init(size_t n_, size_t m_, size_t C_, const double* y_, const double* sds_, const double* tps_);
+    void compute_mu();        // mu = X beta, mu_star = X* beta (src/gpirtMCMC.cpp:308-311)
+    int update_cholesky();    // src/cholesky-cache.cpp:20-24
+    void draw_f(const Src& s, const double* nu_supplied);
+    int draw_fstar(const Src& s);
+    void draw_theta(const Src& s);
+    void gather_f();
+    void draw_beta(const Src& s);
+    void draw_threshold(const Src& s);
+    double total_ll();
+    int sweep(const Src srcs[N_BLOCKS]);
+};
+
+}  // namespace orc
