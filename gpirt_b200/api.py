@@ -1,0 +1,159 @@
+"""The reference's two entry points and its numerical leaves, over the C-ABI.
+
+gpirtMCMC()/recover_fstar() take the arguments of R/gpirtMCMC.R:98-109 and R/recover_fstar.R:36-39 and
+return what the Rcpp functions return (src/gpirtMCMC.cpp:396-403, src/recover_fstar.cpp:92): a list with
+one dict per chain holding theta (n_samples, n, 1), f, beta, fstar, threshold (lists) and ll.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import NGRID, GpirtError, McmcArgs, RecoverArgs, check
+from .sampler import _F, _p, default_thresholds
+
+
+def _as_cube(data):
+    y = np.asarray(data, dtype=np.float64)
+    if y.ndim == 2:
+        y = y[:, :, None]
+    if y.ndim != 3:
+        raise GpirtError(_lib.ERR_SHAPE, "data must be an n x m x horizon array of codes 1..C (NA = missing)")
+    return np.asfortranarray(y)
+
+
+def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_codes=None, beta_prior_means=None,
+              beta_prior_sds=None, theta_prior_means=None, theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern",
+              theta_init=None, thresholds=None, SEED=1, constant_IRF=0, store_f=False, store_fstar=False, beta_init=None,
+              f_init=None, device=0, progress=None):
+    """Drop-in for gpirtMCMC() (R/gpirtMCMC.R:98-167). `vote_codes` must stay None: the reference's recoding
+    path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing."""
+    if vote_codes is not None:
+        raise GpirtError(_lib.ERR_UNSUPPORTED, "vote_codes recoding is not part of the sampler path; pass codes 1..C")
+    y = _as_cube(data)
+    n, m, H = y.shape
+    bpm = _F(np.zeros((3, m)) if beta_prior_means is None else beta_prior_means)
+    bps = _F(np.full((3, m), 3.0) if beta_prior_sds is None else beta_prior_sds)
+    tpm = _F(np.zeros((2, n)) if theta_prior_means is None else theta_prior_means)
+    tps = _F(np.zeros((2, n)) if theta_prior_sds is None else theta_prior_sds)
+    for name, a, shp in (("beta_prior_means", bpm, (3, m)), ("beta_prior_sds", bps, (3, m)), ("theta_prior_means", tpm, (2, n)),
+                         ("theta_prior_sds", tps, (2, n))):
+        if a.shape != shp:
+            raise GpirtError(_lib.ERR_SHAPE, f"{name} has shape {a.shape}, expected {shp}")
+    if thresholds is None:
+        codes = np.unique(y[np.isfinite(y)])
+        Ccat = len(codes)  # R/gpirtMCMC.R:145
+        thr = default_thresholds(m, Ccat)[:, :, None].repeat(H, axis=2)
+    else:
+        thr = np.asarray(thresholds, dtype=np.float64)
+        if thr.ndim == 2:
+            thr = thr[:, :, None]
+        Ccat = thr.shape[1] - 1
+    thr = np.asfortranarray(thr)
+    n_samples = int(sample_iterations / THIN)
+    result = []
+    for chain in range(CHAIN):
+        rng = np.random.default_rng(SEED + chain)  # stands in for set.seed(SEED+chain-1) (R/gpirtMCMC.R:114)
+        if theta_init is None:
+            th0 = np.empty((n, H), order="F")
+            th0[:, 0] = tpm[0] + tps[0] * rng.standard_normal(n)  # rnorm(1, mean, sd) per respondent (:124-126)
+            th0[:, 1:] = th0[:, :1]
+        else:
+            th0 = _F(np.asarray(theta_init, dtype=np.float64).reshape(n, H))
+        out = dict(theta=np.zeros((n_samples, n, H), order="F"), beta=np.zeros((3, m, H, n_samples), order="F"),
+                   threshold=np.zeros((m, Ccat + 1, H, n_samples), order="F"), ll=np.zeros(n_samples),
+                   f=np.zeros((n, m, H, n_samples), order="F") if store_f else None,
+                   fstar=np.zeros((NGRID, m, H, n_samples), order="F") if store_fstar else None)
+        a = McmcArgs()
+        b0, f0 = _F(beta_init), _F(f_init)
+        a.y, a.n, a.m, a.horizon = y.ctypes.data, n, m, H
+        a.theta = th0.ctypes.data
+        a.sample_iterations, a.burn_iterations, a.THIN = int(sample_iterations), int(burn_iterations), int(THIN)
+        a.beta_prior_means, a.beta_prior_sds = bpm.ctypes.data, bps.ctypes.data
+        a.theta_prior_means, a.theta_prior_sds = tpm.ctypes.data, tps.ctypes.data
+        a.theta_os, a.theta_ls, a.KERNEL = float(theta_os), float(theta_ls), KERNEL.encode()
+        a.thresholds, a.C = thr.ctypes.data, Ccat
+        a.constant_IRF, a.store_f, a.store_fstar = int(constant_IRF), int(store_f), int(store_fstar)
+        a.beta_init = b0.ctypes.data if b0 is not None else None
+        a.f_init = f0.ctypes.data if f0 is not None else None
+        a.seed, a.chain, a.device = int(SEED), chain, int(device)
+        a.theta_draws, a.beta_draws = out["theta"].ctypes.data, out["beta"].ctypes.data
+        a.threshold_draws, a.ll_draws = out["threshold"].ctypes.data, out["ll"].ctypes.data
+        a.f_draws = out["f"].ctypes.data if store_f else None
+        a.fstar_draws = out["fstar"].ctypes.data if store_fstar else None
+        cb = _lib.PROGRESS_FN(progress) if progress is not None else _lib.PROGRESS_FN()
+        a.progress = cb
+        check(_lib.lib().gpirt_mcmc(C.byref(a)))
+        result.append(dict(theta=out["theta"],
+                           f=[out["f"][..., s] for s in range(n_samples)] if store_f else None,
+                           beta=[out["beta"][..., s] for s in range(n_samples)],
+                           fstar=[out["fstar"][..., s] for s in range(n_samples)] if store_fstar else None,
+                           threshold=[out["threshold"][..., s] for s in range(n_samples)], ll=out["ll"]))
+    return result
+
+
+def recover_fstar(seed, f, y, theta, beta, thresholds, beta_prior_means=None, beta_prior_sds=None, constant_IRF=0, device=0):
+    """Drop-in for recover_fstar() (R/recover_fstar.R:36-46): one draw_f + draw_fstar from a stored f and a seed."""
+    yy = _as_cube(y)
+    n, m, H = yy.shape
+    ff = np.asfortranarray(np.asarray(f, dtype=np.float64).reshape(n, m, H))
+    th = _F(np.asarray(theta, dtype=np.float64).reshape(n, H))
+    be = np.asfortranarray(np.asarray(beta, dtype=np.float64).reshape(2, m, H))
+    thr = np.asarray(thresholds, dtype=np.float64)
+    thr = np.asfortranarray(thr[:, :, None] if thr.ndim == 2 else thr)
+    bpm = _F(np.zeros((2, m)) if beta_prior_means is None else beta_prior_means)
+    bps = _F(np.full((2, m), 0.5) if beta_prior_sds is None else beta_prior_sds)
+    out = np.zeros((NGRID, m, H), order="F")
+    a = RecoverArgs()
+    a.seed, a.f, a.y, a.n, a.m, a.horizon = int(seed), ff.ctypes.data, yy.ctypes.data, n, m, H
+    a.theta, a.beta, a.thresholds, a.C = th.ctypes.data, be.ctypes.data, thr.ctypes.data, thr.shape[1] - 1
+    a.beta_prior_means, a.beta_prior_sds = bpm.ctypes.data, bps.ctypes.data
+    a.constant_IRF, a.device, a.fstar = int(constant_IRF), int(device), out.ctypes.data
+    check(_lib.lib().gpirt_recover_fstar(C.byref(a)))
+    return dict(fstar=out)
+
+
+# ---- numerical leaves (src/gpirt.h:262-290) ----
+def K(x1, x2, beta_prior_sds, device=0):
+    x1, x2, s = _F(x1).ravel(), _F(x2).ravel(), _F(beta_prior_sds).ravel()
+    out = np.empty((x1.size, x2.size), order="F")
+    check(_lib.lib().gpirt_K(device, _p(x1), C.c_int64(x1.size), _p(x2), C.c_int64(x2.size), _p(s), _p(out)))
+    return out
+
+
+def K_time(x1, x2, os, ls, theta_prior_sds, KERNEL, device=0):
+    x1, x2, s = _F(x1).ravel(), _F(x2).ravel(), _F(theta_prior_sds).ravel()
+    out = np.empty((x1.size, x2.size), order="F")
+    kern = {"Matern": 0, "RBF": 1}.get(KERNEL, 2)
+    check(_lib.lib().gpirt_K_time(device, _p(x1), C.c_int64(x1.size), _p(x2), C.c_int64(x2.size), C.c_double(os), C.c_double(ls),
+                                  _p(s), kern, _p(out)))
+    return out
+
+
+def chol(A, device=0):
+    A = _F(A)
+    out = np.empty_like(A, order="F")
+    check(_lib.lib().gpirt_chol(device, _p(A), C.c_int64(A.shape[0]), _p(out)))
+    return out
+
+
+def double_solve(L, X, device=0):
+    L = _F(L)
+    X = _F(np.asarray(X, dtype=np.float64).reshape(L.shape[0], -1))
+    out = np.empty_like(X, order="F")
+    check(_lib.lib().gpirt_double_solve(device, _p(L), C.c_int64(L.shape[0]), _p(X), C.c_int64(X.shape[1]), _p(out)))
+    return out
+
+
+def delta_to_threshold(deltas):
+    d = _F(deltas).ravel()
+    out = np.empty(d.size + 2)
+    check(_lib.lib().gpirt_delta_to_threshold(_p(d), d.size + 1, _p(out)))
+    return out
+
+
+def threshold_to_delta(thresholds):
+    t = _F(thresholds).ravel()
+    out = np.empty(t.size - 2)
+    check(_lib.lib().gpirt_threshold_to_delta(_p(t), t.size - 1, _p(out)))
+    return out

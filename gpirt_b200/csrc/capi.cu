@@ -1,0 +1,731 @@
+// C-ABI of the B200-native gpirt sweep: lifetime, data/state marshalling and the subsystem entry points
+// declared in include/gpirt_b200.h (each declaration there cites the reference interface it replaces).
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include "probit.cuh"
+#include "sampler_state.cuh"
+
+using namespace gpirt;
+
+static thread_local char g_err[512] = "";
+static int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+#define CU(x)                                                                                           \
+    do {                                                                                                \
+        cudaError_t e_ = (x);                                                                           \
+        if (e_ != cudaSuccess) return fail(GPIRT_ERR_CUDA, "%s: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+#define CHECK_H(h) \
+    if (!(h)) return fail(GPIRT_ERR_INVALID, "NULL sampler handle")
+
+static int select_device(int device) {
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(GPIRT_ERR_NO_DEVICE, "no CUDA device (%s); gpirt_b200 has no CPU path", e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail(GPIRT_ERR_INVALID, "device %d out of range (0..%d)", device, count - 1);
+    CU(cudaSetDevice(device));
+    return GPIRT_OK;
+}
+
+template <class T>
+static int dalloc(T** p, size_t count) {
+    *p = nullptr;
+    if (count == 0) count = 1;
+    CU(cudaMalloc((void**)p, count * sizeof(T)));
+    CU(cudaMemset(*p, 0, count * sizeof(T)));
+    return GPIRT_OK;
+}
+#define TRY(x)                   \
+    do {                         \
+        int rc_ = (x);           \
+        if (rc_ != GPIRT_OK) return rc_; \
+    } while (0)
+
+__global__ void k_add_diag(double* A, int ld, int n, double v) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) A[(size_t)i * ld + i] = __dadd_rn(A[(size_t)i * ld + i], v);
+}
+__global__ void k_fill_grid(double* t) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < NGRID) t[i] = grid_value(i);
+}
+// beta0[q,J] = mean + sd * z  (R::rnorm(mean, sd), src/gpirtMCMC.cpp:153)
+__global__ void k_init_beta(double* beta, const double* means, const double* sds, int m_total, RngKey key) {
+    int J = blockIdx.x * blockDim.x + threadIdx.x;
+    if (J >= m_total) return;
+    for (int q = 0; q < 3; ++q) beta[3 * (size_t)J + q] = means[3 * (size_t)J + q] + sds[3 * (size_t)J + q] * philox_normal(key, ST_INIT_BETA, J, q);
+}
+
+extern "C" {
+
+const char* gpirt_last_error(void) { return g_err; }
+
+int gpirt_device_count(void) {
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) return 0;
+    return count;
+}
+
+int gpirt_delta_to_threshold(const double* d, int C, double* thr) {  // src/log-likelihood.cpp:66-76
+    if (!d || !thr || C < 2) return fail(GPIRT_ERR_INVALID, "delta_to_threshold: bad arguments");
+    for (int i = 0; i <= C; ++i) thr[i] = 0.0;
+    thr[0] = -std::numeric_limits<double>::infinity();
+    thr[1] = d[0];
+    thr[C] = std::numeric_limits<double>::infinity();
+    for (int i = 1; i < C - 1; ++i) thr[i + 1] = thr[i] + std::exp(d[i]);
+    return GPIRT_OK;
+}
+int gpirt_threshold_to_delta(const double* thr, int C, double* d) {  // src/log-likelihood.cpp:78-88
+    if (!d || !thr || C < 2) return fail(GPIRT_ERR_INVALID, "threshold_to_delta: bad arguments");
+    for (int i = 0; i < C - 1; ++i) d[i] = 0.0;
+    d[0] = thr[1];
+    for (int i = 1; i < C - 1; ++i) d[i] = std::log(thr[i + 1] - thr[i]);
+    return GPIRT_OK;
+}
+
+int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
+    if (!cfg || !out) return fail(GPIRT_ERR_INVALID, "gpirt_create: NULL argument");
+    *out = nullptr;
+    if (cfg->horizon != 1) return fail(GPIRT_ERR_UNSUPPORTED, "horizon %d: only horizon == 1 is built", cfg->horizon);
+    if (cfg->constant_IRF != 0) return fail(GPIRT_ERR_UNSUPPORTED, "constant_IRF %d: only 0 is built", cfg->constant_IRF);
+    if (cfg->C < 2 || cfg->C > GPIRT_MAX_C) return fail(GPIRT_ERR_CATEGORIES, "C = %d outside 2..%d", cfg->C, GPIRT_MAX_C);
+    if (cfg->n < 1 || cfg->m_total < 1) return fail(GPIRT_ERR_SHAPE, "n = %d, m = %d", cfg->n, cfg->m_total);
+    if (cfg->p_beta != 2 && cfg->p_beta != 3) return fail(GPIRT_ERR_SHAPE, "p_beta = %d (2 or 3)", cfg->p_beta);
+    if (cfg->world < 1 || cfg->rank < 0 || cfg->rank >= cfg->world) return fail(GPIRT_ERR_INVALID, "rank %d of %d", cfg->rank, cfg->world);
+    if (cfg->m_total < cfg->world || cfg->n < cfg->world) return fail(GPIRT_ERR_SHAPE, "fewer items/respondents than ranks");
+    if (cfg->kernel != 0 && cfg->kernel != 1) return fail(GPIRT_ERR_INVALID, "KERNEL must be Matern (0) or RBF (1)");
+    TRY(select_device(cfg->device));
+
+    gpirt_sampler* h = new gpirt_sampler();
+    h->cfg = *cfg;
+    h->n = cfg->n; h->m_total = cfg->m_total; h->C = cfg->C; h->world = cfg->world; h->rank = cfg->rank;
+    h->m_chunk = (h->m_total + h->world - 1) / h->world;
+    h->item0 = h->rank * h->m_chunk;
+    h->m_local = std::max(0, std::min(h->m_chunk, h->m_total - h->item0));
+    h->n_chunk = (h->n + h->world - 1) / h->world;
+    h->resp0 = h->rank * h->n_chunk;
+    h->n_local = std::max(0, std::min(h->n_chunk, h->n - h->resp0));
+    h->ldn = pad_ld(h->n); h->ldN = pad_ld(NGRID); h->ldy = pad_ld(h->n);
+    h->ld_chunk = pad_ld(h->m_chunk); h->ldz = std::max(h->ldn, h->ldN);
+    h->ldm = pad_ld((long long)h->world * h->m_chunk);
+    // regime switch of src/draw-theta.cpp:112,171,206 at horizon 1: CST and RDM share L_i = sqrt(1 + sd^2)
+    const double ls = cfg->theta_ls;
+    h->theta_regime = (ls >= 3.0 || ls <= 0.1) ? 0 : 1;
+    *out = h;  // from here on the caller can destroy a half-built handle
+
+    CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    h->own_stream = true;
+    const size_t mt = (size_t)h->world * h->m_chunk;
+    TRY(dalloc(&h->y_im, (size_t)h->ldy * std::max(h->m_local, 1)));
+    TRY(dalloc(&h->y_rm, (size_t)h->ldm * std::max(h->n_local, 1)));
+    TRY(dalloc(&h->theta, (size_t)h->world * h->n_chunk));
+    TRY(dalloc(&h->theta_x, (size_t)h->world * h->n_chunk));
+    TRY(dalloc(&h->beta, 3 * mt));
+    TRY(dalloc(&h->thr, (size_t)(h->C + 1) * mt));
+    TRY(dalloc(&h->f, (size_t)h->ldn * h->m_local));
+    TRY(dalloc(&h->nu, (size_t)h->ldn * h->m_local));
+    TRY(dalloc(&h->zbuf, (size_t)h->ldz * h->m_local));
+    TRY(dalloc(&h->fstar, (size_t)h->world * NGRID * h->ld_chunk));
+    TRY(dalloc(&h->L, (size_t)h->ldn * h->n));
+    TRY(dalloc(&h->W, (size_t)h->ldn * NGRID));
+    TRY(dalloc(&h->Kpost, (size_t)h->ldN * NGRID));
+    TRY(dalloc(&h->tstar, (size_t)h->ldN));
+    TRY(dalloc(&h->sds, 3 * mt));
+    TRY(dalloc(&h->tps, 2 * (size_t)h->n));
+    TRY(dalloc(&h->item_ll, mt));
+    TRY(dalloc(&h->total_ll, 1));
+    TRY(dalloc(&h->flags, 1));
+    for (int b = 0; b < 5; ++b) {
+        size_t units = (b == GPIRT_BLOCK_THETA) ? (size_t)h->world * h->n_chunk : mt;
+        TRY(dalloc(&h->evals[b], units));
+        TRY(dalloc(&h->margin[b], units));
+    }
+    k_fill_grid<<<(NGRID + 255) / 256, 256, 0, h->stream>>>(h->tstar);
+    CU(cudaGetLastError());
+    CU(cudaDeviceSynchronize());  // the zero-fills above ran on the legacy stream
+    return GPIRT_OK;
+}
+
+int gpirt_destroy(gpirt_sampler* h) {
+    if (!h) return GPIRT_OK;
+    cudaSetDevice(h->cfg.device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
+                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u};
+    for (void* p : ptrs)
+        if (p) cudaFree(p);
+    for (int b = 0; b < 5; ++b) {
+        if (h->evals[b]) cudaFree(h->evals[b]);
+        if (h->margin[b]) cudaFree(h->margin[b]);
+    }
+    if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return GPIRT_OK;
+}
+
+int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    if (h->own_stream) { cudaStreamDestroy(h->stream); h->own_stream = false; }
+    h->stream = (cudaStream_t)cuda_stream;
+    return GPIRT_OK;
+}
+
+int gpirt_set_iter(gpirt_sampler* h, uint32_t iter) {
+    CHECK_H(h);
+    h->iter = iter;
+    return GPIRT_OK;
+}
+
+}  // extern "C"
+
+// ---- deferred error flags ------------------------------------------------------------------------
+static int check_flags(gpirt_sampler* h) {
+    DevFlags fl;
+    CU(cudaMemcpyAsync(&fl, h->flags, sizeof(fl), cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    if (fl.chol_info || fl.chol_post_info || fl.overrun || fl.stalled || fl.bad_code) {
+        CU(cudaMemsetAsync(h->flags, 0, sizeof(fl), h->stream));
+        if (fl.bad_code) return fail(GPIRT_ERR_CATEGORIES, "response code outside 1..%d", h->C);
+        if (fl.chol_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K(theta,theta) + 1e-6 I not positive definite at leading minor %d", fl.chol_info);
+        if (fl.chol_post_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K_post not positive definite at leading minor %d", fl.chol_post_info);
+        if (fl.overrun) return fail(GPIRT_ERR_STREAM_OVERRUN, "a supplied uniform stream ran dry before its ESS loop accepted");
+        return fail(GPIRT_ERR_ESS_STALLED, "an ESS loop made %d proposals without accepting (NaN likelihood?)", ESS_MAX_PROPOSALS);
+    }
+    return GPIRT_OK;
+}
+
+static int upload(gpirt_sampler* h, double** buf, size_t* cap, const double* host, size_t count) {
+    if (count > *cap) {
+        if (*buf) CU(cudaFree(*buf));
+        *buf = nullptr;
+        CU(cudaMalloc((void**)buf, count * sizeof(double)));
+        *cap = count;
+    }
+    CU(cudaMemcpyAsync(*buf, host, count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    return GPIRT_OK;
+}
+
+static int build_layouts(gpirt_sampler* h, const int8_t* d_full) {
+    CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
+    CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
+    CU(launch_y_layouts(h->stream, d_full, h->n, h->m_total, h->item0, h->m_local, h->y_im, h->ldy, h->resp0, h->n_local, h->y_rm, h->ldm));
+    h->have_data = true;
+    return GPIRT_OK;
+}
+
+extern "C" {
+
+int gpirt_sync(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    return check_flags(h);
+}
+
+int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
+    CHECK_H(h);
+    if (!y) return fail(GPIRT_ERR_INVALID, "set_data: NULL y");
+    CU(cudaSetDevice(h->cfg.device));
+    const long long count = (long long)h->n * h->m_total;
+    double* d_y = nullptr;
+    int8_t* d_full = nullptr;
+    // staged in column slabs so the fp64 copy of y never needs more than 256 MB of device memory
+    const long long slab_cols = std::max(1LL, (256LL << 20) / (8LL * h->n));
+    CU(cudaMalloc((void**)&d_full, (size_t)count));
+    CU(cudaMalloc((void**)&d_y, (size_t)std::min<long long>(slab_cols, h->m_total) * h->n * 8));
+    for (long long c0 = 0; c0 < h->m_total; c0 += slab_cols) {
+        const long long cols = std::min<long long>(slab_cols, h->m_total - c0);
+        CU(cudaMemcpyAsync(d_y, y + c0 * h->n, (size_t)cols * h->n * 8, cudaMemcpyHostToDevice, h->stream));
+        CU(launch_y_to_i8(h->stream, d_y, cols * h->n, h->C, d_full + c0 * h->n, h->flags));
+    }
+    int rc = build_layouts(h, d_full);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(d_y);
+    cudaFree(d_full);
+    if (rc != GPIRT_OK) return rc;
+    return check_flags(h);
+}
+
+int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y) {
+    CHECK_H(h);
+    if (!y) return fail(GPIRT_ERR_INVALID, "set_data: NULL y");
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t count = (size_t)h->n * h->m_total;
+    for (size_t e = 0; e < count; ++e)
+        if (y[e] < 0 || y[e] > h->C) return fail(GPIRT_ERR_CATEGORIES, "response code %d outside 0..%d at element %zu", (int)y[e], h->C, e);
+    int8_t* d_full = nullptr;
+    CU(cudaMalloc((void**)&d_full, count));
+    CU(cudaMemcpyAsync(d_full, y, count, cudaMemcpyHostToDevice, h->stream));
+    int rc = build_layouts(h, d_full);
+    cudaStreamSynchronize(h->stream);
+    cudaFree(d_full);
+    return rc;
+}
+
+int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds, const double* theta_prior_sds) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    if (beta_prior_sds) {
+        CU(cudaMemcpyAsync(h->sds, beta_prior_sds, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, h->stream));
+        for (int q = 0; q < 3; ++q) h->sds0[q] = beta_prior_sds[q];  // column 0 feeds every K() call
+        h->chol_valid = false;
+    }
+    if (theta_prior_sds) CU(cudaMemcpyAsync(h->tps, theta_prior_sds, 2 * (size_t)h->n * 8, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return GPIRT_OK;
+}
+
+int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, const double* f, const double* thresholds,
+                    const double* fstar) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    cudaStream_t st = h->stream;
+    if (theta) {
+        CU(cudaMemcpyAsync(h->theta, theta, (size_t)h->n * 8, cudaMemcpyHostToDevice, st));
+        CU(launch_clamp_theta(st, h->theta, h->n));
+        h->chol_valid = false;
+    }
+    if (beta) {  // p_beta x m_total -> 3 x m_total (third row zero when p_beta == 2)
+        std::vector<double> b3(3 * (size_t)h->m_total, 0.0);
+        for (int J = 0; J < h->m_total; ++J)
+            for (int q = 0; q < h->cfg.p_beta; ++q) b3[3 * (size_t)J + q] = beta[(size_t)h->cfg.p_beta * J + q];
+        CU(cudaMemcpyAsync(h->beta, b3.data(), b3.size() * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (thresholds) {  // m_total x (C+1) column-major -> item-major (C+1) x m_total
+        const int C1 = h->C + 1;
+        std::vector<double> t((size_t)C1 * h->m_total);
+        for (int J = 0; J < h->m_total; ++J)
+            for (int c = 0; c < C1; ++c) t[(size_t)J * C1 + c] = thresholds[(size_t)c * h->m_total + J];
+        CU(cudaMemcpyAsync(h->thr, t.data(), t.size() * 8, cudaMemcpyHostToDevice, st));
+        CU(cudaStreamSynchronize(st));
+    }
+    if (f && h->m_local > 0)
+        CU(cudaMemcpy2DAsync(h->f, (size_t)h->ldn * 8, f + (size_t)h->item0 * h->n, (size_t)h->n * 8, (size_t)h->n * 8, h->m_local,
+                             cudaMemcpyHostToDevice, st));
+    if (fstar) {  // NGRID x m_total column-major -> every chunk of the grid-row-major table
+        double* tmp = nullptr;
+        CU(cudaMalloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        CU(cudaMemcpyAsync(tmp, fstar, (size_t)NGRID * h->m_total * 8, cudaMemcpyHostToDevice, st));
+        for (int r = 0; r < h->world; ++r) {
+            const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
+            if (cols > 0) CU(launch_transpose(st, tmp + (size_t)j0 * NGRID, NGRID, NGRID, cols, h->fstar + (size_t)r * NGRID * h->ld_chunk, h->ld_chunk));
+        }
+        CU(cudaStreamSynchronize(st));
+        cudaFree(tmp);
+    }
+    CU(cudaStreamSynchronize(st));
+    return GPIRT_OK;
+}
+
+int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, double* thresholds, double* fstar) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(check_flags(h));
+    cudaStream_t st = h->stream;
+    if (theta) CU(cudaMemcpyAsync(theta, h->theta, (size_t)h->n * 8, cudaMemcpyDeviceToHost, st));
+    if (beta) {
+        std::vector<double> b3(3 * (size_t)h->m_total);
+        CU(cudaMemcpyAsync(b3.data(), h->beta, b3.size() * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        for (int J = 0; J < h->m_total; ++J)
+            for (int q = 0; q < h->cfg.p_beta; ++q) beta[(size_t)h->cfg.p_beta * J + q] = b3[3 * (size_t)J + q];
+    }
+    if (thresholds) {
+        const int C1 = h->C + 1;
+        std::vector<double> t((size_t)C1 * h->m_total);
+        CU(cudaMemcpyAsync(t.data(), h->thr, t.size() * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        for (int J = 0; J < h->m_total; ++J)
+            for (int c = 0; c < C1; ++c) thresholds[(size_t)c * h->m_total + J] = t[(size_t)J * C1 + c];
+    }
+    if (f && h->m_local > 0)  // only the local items' columns are written (world > 1: the caller gathers)
+        CU(cudaMemcpy2DAsync(f + (size_t)h->item0 * h->n, (size_t)h->n * 8, h->f, (size_t)h->ldn * 8, (size_t)h->n * 8, h->m_local,
+                             cudaMemcpyDeviceToHost, st));
+    if (fstar) {
+        double* tmp = nullptr;
+        CU(cudaMalloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        for (int r = 0; r < h->world; ++r) {
+            const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
+            // chunk is cols x NGRID (ld_chunk) column-major in (j, idx); transpose back to NGRID x cols
+            if (cols > 0) CU(launch_transpose(st, h->fstar + (size_t)r * NGRID * h->ld_chunk, h->ld_chunk, cols, NGRID, tmp + (size_t)j0 * NGRID, NGRID));
+        }
+        CU(cudaMemcpyAsync(fstar, tmp, (size_t)NGRID * h->m_total * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        cudaFree(tmp);
+    }
+    CU(cudaStreamSynchronize(st));
+    return GPIRT_OK;
+}
+
+int gpirt_get_L(gpirt_sampler* h, double* L) {
+    CHECK_H(h);
+    if (!L) return fail(GPIRT_ERR_INVALID, "get_L: NULL output");
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(check_flags(h));
+    CU(cudaMemcpy2DAsync(L, (size_t)h->n * 8, h->L, (size_t)h->ldn * 8, (size_t)h->n * 8, h->n, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return GPIRT_OK;
+}
+
+int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin) {
+    CHECK_H(h);
+    if (block < 0 || block > 4) return fail(GPIRT_ERR_INVALID, "get_diag: block %d", block);
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t units = (block == GPIRT_BLOCK_THETA) ? h->n : h->m_total;
+    if (evals) CU(cudaMemcpyAsync(evals, h->evals[block], units * 4, cudaMemcpyDeviceToHost, h->stream));
+    if (margin) CU(cudaMemcpyAsync(margin, h->margin[block], units * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    return GPIRT_OK;
+}
+
+}  // extern "C"
+
+// ---- subsystem internals -------------------------------------------------------------------------
+static ItemView item_view(gpirt_sampler* h) {
+    ItemView v{};
+    v.n = h->n; v.ldn = h->ldn; v.m_local = h->m_local; v.item0 = h->item0; v.m_total = h->m_total; v.C = h->C; v.p_beta = h->cfg.p_beta;
+    v.y_im = h->y_im; v.ldy = h->ldy; v.theta = h->theta; v.beta = h->beta; v.thr = h->thr; v.f = h->f; v.nu = h->nu; v.sds = h->sds;
+    v.z = nullptr; v.z_stride = 0; v.us.u = nullptr; v.us.stride = 0; v.key = h->key();
+    v.item_ll = h->item_ll; v.flags = h->flags;
+    return v;
+}
+
+// uploads the supplied streams of one block call; returns device pointers (or NULL for Philox)
+static int stage_streams(gpirt_sampler* h, const gpirt_streams* s, size_t units, size_t nz, const double** dz, long long* zs,
+                         UniformSrc* us) {
+    *dz = nullptr; *zs = 0; us->u = nullptr; us->stride = 0;
+    if (!s) return GPIRT_OK;
+    if (s->z && nz > 0) {
+        if (s->z_stride < (long long)nz) return fail(GPIRT_ERR_SHAPE, "z_stride %lld < %zu normals per unit", (long long)s->z_stride, nz);
+        TRY(upload(h, &h->d_z, &h->d_z_cap, s->z, units * (size_t)s->z_stride));
+        *dz = h->d_z; *zs = s->z_stride;
+    }
+    if (s->u) {
+        if (s->u_stride < 2) return fail(GPIRT_ERR_SHAPE, "u_stride %lld < 2", (long long)s->u_stride);
+        TRY(upload(h, &h->d_u, &h->d_u_cap, s->u, units * (size_t)s->u_stride));
+        us->u = h->d_u; us->stride = s->u_stride;
+    }
+    return GPIRT_OK;
+}
+
+static int need_data(gpirt_sampler* h) {
+    if (!h->have_data) return fail(GPIRT_ERR_INVALID, "no response data: call gpirt_set_data_* first");
+    return GPIRT_OK;
+}
+
+static int do_update_cholesky(gpirt_sampler* h) {  // src/cholesky-cache.cpp:20-24
+    CU(build_K(h->stream, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6));
+    CU(chol_lower_blocked(h->stream, h->L, h->ldn, h->n, &h->flags->chol_info));
+    h->chol_valid = true;
+    return GPIRT_OK;
+}
+
+static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
+    if (!h->chol_valid) TRY(do_update_cholesky(h));  // the reference refactorises here (src/draw-f.cpp:59); same theta, same L
+    cudaStream_t st = h->stream;
+    ItemView v = item_view(h);
+    const double* dz; long long zs;
+    gpirt_streams s_u{};  // only the uniforms go through stage_streams; z / nu are matrices handled below
+    if (s) { s_u.u = s->u; s_u.u_stride = s->u_stride; }
+    TRY(stage_streams(h, &s_u, h->m_total, 0, &dz, &zs, &v.us));
+    if (h->m_local > 0) {
+        if (s && s->nu) {
+            CU(cudaMemcpy2DAsync(h->nu, (size_t)h->ldn * 8, s->nu + (size_t)h->item0 * h->n, (size_t)h->n * 8, (size_t)h->n * 8, h->m_local,
+                                 cudaMemcpyHostToDevice, st));
+        } else {
+            if (s && s->z) {
+                if (s->z_stride < h->n) return fail(GPIRT_ERR_SHAPE, "draw_f: z_stride %lld < n", (long long)s->z_stride);
+                CU(cudaMemcpy2DAsync(h->zbuf, (size_t)h->ldz * 8, s->z + (size_t)h->item0 * s->z_stride, (size_t)s->z_stride * 8,
+                                     (size_t)h->n * 8, h->m_local, cudaMemcpyHostToDevice, st));
+            } else {
+                CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_F_Z, h->item0));
+            }
+            // nu = L * Z for every local item at once (rmvnorm_threadsafe per item, src/mvnormal.h:17-24)
+            GemmArgs g{};
+            g.M = h->n; g.N = h->m_local; g.K = h->n;
+            g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->nu; g.ldc = h->ldn;
+            g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
+            CU(gemm_f64(st, false, false, g));
+        }
+    }
+    v.evals = h->evals[GPIRT_BLOCK_F]; v.margin = h->margin[GPIRT_BLOCK_F];
+    CU(launch_ess_items(st, IB_F, v));
+    return GPIRT_OK;
+}
+
+static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/draw-fstar.cpp:18-57
+    if (!h->chol_valid) TRY(do_update_cholesky(h));
+    cudaStream_t st = h->stream;
+    const int n = h->n, N = NGRID;
+    // shared over items: k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I, L_post = chol(K_post)
+    CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0));
+    CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N));
+    CU(build_K(st, h->tstar, N, h->tstar, N, h->sds0, h->Kpost, h->ldN, 0.0));
+    {
+        GemmArgs g{};
+        g.M = N; g.N = N; g.K = n; g.A = h->W; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->Kpost; g.ldc = h->ldN;
+        g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
+        CU(gemm_f64(st, true, false, g));
+    }
+    k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
+    CU(cudaGetLastError());
+    CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info));
+    // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
+    CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N));
+    if (h->m_local == 0) return GPIRT_OK;
+    double* chunk = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk;
+    {
+        GemmArgs g{};
+        g.M = h->m_local; g.N = N; g.K = n; g.A = h->f; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = chunk; g.ldc = h->ld_chunk;
+        g.alpha = 1.0; g.beta = 0.0;
+        CU(gemm_f64(st, true, false, g));
+    }
+    if (s && s->z) {
+        if (s->z_stride < N) return fail(GPIRT_ERR_SHAPE, "draw_fstar: z_stride %lld < %d", (long long)s->z_stride, N);
+        CU(cudaMemcpy2DAsync(h->zbuf, (size_t)h->ldz * 8, s->z + (size_t)h->item0 * s->z_stride, (size_t)s->z_stride * 8, (size_t)N * 8,
+                             h->m_local, cudaMemcpyHostToDevice, st));
+    } else {
+        CU(launch_gen_normals(st, h->zbuf, h->ldz, N, h->m_local, h->key(), ST_FSTAR_Z, h->item0));
+    }
+    {   // + (L_post Z*)^T : op(A) = Z*^T, op(B) = L_post^T (upper triangular)
+        GemmArgs g{};
+        g.M = h->m_local; g.N = N; g.K = N; g.A = h->zbuf; g.lda = h->ldz; g.B = h->Kpost; g.ldb = h->ldN; g.C = chunk; g.ldc = h->ld_chunk;
+        g.alpha = 1.0; g.beta = 1.0; g.b_upper = 1;
+        CU(gemm_f64(st, true, true, g));
+    }
+    CU(launch_add_mustar(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta));
+    return GPIRT_OK;
+}
+
+static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
+    ThetaView v{};
+    v.n = h->n; v.resp0 = h->resp0; v.n_local = h->n_local; v.m_total = h->m_total; v.m_chunk = h->m_chunk; v.ld_chunk = h->ld_chunk;
+    v.world = h->world; v.C = h->C; v.y_rm = h->y_rm; v.ldm = h->ldm; v.theta = h->theta; v.theta_new = h->theta_x;
+    v.fstar_all = h->fstar; v.chunk_elems = (long long)NGRID * h->ld_chunk; v.beta = h->beta; v.thr = h->thr; v.theta_prior_sds = h->tps;
+    v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os; v.key = h->key();
+    v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
+    TRY(stage_streams(h, s, h->n, 1, &v.z, &v.z_stride, &v.us));
+    CU(launch_ess_theta(h->stream, v));
+    return GPIRT_OK;
+}
+
+static int commit_theta(gpirt_sampler* h) {  // theta.swap(theta_new), src/gpirtMCMC.cpp:284
+    CU(cudaMemcpyAsync(h->theta, h->theta_x, (size_t)h->n * 8, cudaMemcpyDeviceToDevice, h->stream));
+    h->chol_valid = false;
+    return GPIRT_OK;
+}
+
+static int do_gather_f(gpirt_sampler* h) {
+    if (h->m_local == 0) return GPIRT_OK;
+    CU(launch_gather_f(h->stream, h->theta, h->n, h->fstar + (size_t)h->rank * NGRID * h->ld_chunk, h->ld_chunk, h->m_local, h->f, h->ldn));
+    return GPIRT_OK;
+}
+
+static int do_small_ess(gpirt_sampler* h, int which, const gpirt_streams* s) {
+    ItemView v = item_view(h);
+    const int blk = which == IB_BETA ? GPIRT_BLOCK_BETA : GPIRT_BLOCK_THR;
+    const size_t nz = which == IB_BETA ? 3 : (size_t)(h->C - 1);
+    TRY(stage_streams(h, s, h->m_total, nz, &v.z, &v.z_stride, &v.us));
+    v.evals = h->evals[blk]; v.margin = h->margin[blk];
+    CU(launch_ess_items(h->stream, which, v));
+    return GPIRT_OK;
+}
+
+static int do_item_ll(gpirt_sampler* h) {
+    ItemView v = item_view(h);
+    CU(launch_item_ll(h->stream, v));
+    return GPIRT_OK;
+}
+
+extern "C" {
+
+#define ENTER(h)                         \
+    CHECK_H(h);                          \
+    CU(cudaSetDevice((h)->cfg.device));  \
+    TRY(need_data(h))
+
+int gpirt_update_cholesky_cache(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    return do_update_cholesky(h);
+}
+int gpirt_draw_f(gpirt_sampler* h, const gpirt_streams* s) { ENTER(h); return do_draw_f(h, s); }
+int gpirt_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) { ENTER(h); return do_draw_fstar(h, s); }
+int gpirt_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
+    ENTER(h);
+    TRY(do_draw_theta(h, s));
+    if (h->world == 1) return commit_theta(h);  // world > 1: the caller all-gathers XCHG_THETA, then gpirt_sweep_phase_close commits
+    return GPIRT_OK;
+}
+int gpirt_gather_f(gpirt_sampler* h) { ENTER(h); return do_gather_f(h); }
+int gpirt_draw_beta(gpirt_sampler* h, const gpirt_streams* s) {
+    ENTER(h);
+    if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "draw_beta needs 3 mean coefficients per item (X is n x 3, src/gpirtMCMC.cpp:138-141)");
+    return do_small_ess(h, IB_BETA, s);
+}
+int gpirt_draw_threshold(gpirt_sampler* h, const gpirt_streams* s) { ENTER(h); return do_small_ess(h, IB_THR, s); }
+
+int gpirt_total_ll(gpirt_sampler* h, double* total) {
+    CHECK_H(h);
+    if (!total) return fail(GPIRT_ERR_INVALID, "total_ll: NULL output");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(launch_ordered_sum(h->stream, h->item_ll, h->m_total, h->total_ll));
+    CU(cudaMemcpyAsync(total, h->total_ll, 8, cudaMemcpyDeviceToHost, h->stream));
+    return check_flags(h);
+}
+
+int gpirt_ll_bar(gpirt_sampler* h, double* per_item, double* total) {
+    ENTER(h);
+    TRY(do_item_ll(h));
+    if (per_item) CU(cudaMemcpyAsync(per_item, h->item_ll, (size_t)h->m_total * 8, cudaMemcpyDeviceToHost, h->stream));
+    if (total) return gpirt_total_ll(h, total);  // world > 1: only meaningful after the ITEM_LL exchange
+    return check_flags(h);
+}
+
+// ---- sweep (src/gpirtMCMC.cpp:267-331) ----
+int gpirt_sweep_phase_items(gpirt_sampler* h) {
+    ENTER(h);
+    TRY(do_draw_f(h, nullptr));
+    return do_draw_fstar(h, nullptr);
+}
+int gpirt_sweep_phase_theta(gpirt_sampler* h) { ENTER(h); return do_draw_theta(h, nullptr); }
+int gpirt_sweep_phase_close(gpirt_sampler* h) {
+    ENTER(h);
+    TRY(commit_theta(h));
+    TRY(do_gather_f(h));
+    TRY(do_small_ess(h, IB_BETA, nullptr));
+    TRY(do_update_cholesky(h));
+    TRY(do_small_ess(h, IB_THR, nullptr));
+    TRY(do_item_ll(h));
+    h->iter += 1;
+    return GPIRT_OK;
+}
+int gpirt_sweep(gpirt_sampler* h, int n_sweeps) {
+    ENTER(h);
+    if (h->world != 1) return fail(GPIRT_ERR_INVALID, "gpirt_sweep on an item shard: drive the three phases and the exchanges instead");
+    if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "a sweep needs 3 mean coefficients per item");
+    for (int k = 0; k < n_sweeps; ++k) {
+        TRY(gpirt_sweep_phase_items(h));
+        TRY(gpirt_sweep_phase_theta(h));
+        TRY(gpirt_sweep_phase_close(h));
+    }
+    return GPIRT_OK;
+}
+
+int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes) {
+    CHECK_H(h);
+    if (!dev_ptr || !chunk_bytes) return fail(GPIRT_ERR_INVALID, "exchange_buffer: NULL output");
+    switch (which) {
+        case GPIRT_XCHG_FSTAR: *dev_ptr = h->fstar; *chunk_bytes = (int64_t)NGRID * h->ld_chunk * 8; break;
+        case GPIRT_XCHG_BETA: *dev_ptr = h->beta; *chunk_bytes = (int64_t)3 * h->m_chunk * 8; break;
+        case GPIRT_XCHG_THR: *dev_ptr = h->thr; *chunk_bytes = (int64_t)(h->C + 1) * h->m_chunk * 8; break;
+        case GPIRT_XCHG_THETA: *dev_ptr = h->theta_x; *chunk_bytes = (int64_t)h->n_chunk * 8; break;
+        case GPIRT_XCHG_ITEM_LL: *dev_ptr = h->item_ll; *chunk_bytes = (int64_t)h->m_chunk * 8; break;
+        default: return fail(GPIRT_ERR_INVALID, "exchange_buffer: unknown buffer %d", which);
+    }
+    return GPIRT_OK;
+}
+
+// ---- stateless leaves ----
+int gpirt_K(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, const double* sds3, double* out) {
+    if (!x1 || !x2 || !sds3 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K: bad arguments");
+    TRY(select_device(device));
+    double *d1, *d2, *dK;
+    CU(cudaMalloc((void**)&d1, n1 * 8)); CU(cudaMalloc((void**)&d2, n2 * 8)); CU(cudaMalloc((void**)&dK, n1 * n2 * 8));
+    CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
+    CU(build_K(0, d1, (int)n1, d2, (int)n2, sds3, dK, (int)n1, 0.0));
+    CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d1); cudaFree(d2); cudaFree(dK);
+    return GPIRT_OK;
+}
+int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, double os, double ls, const double* tsds2,
+                 int kernel, double* out) {
+    if (!x1 || !x2 || !tsds2 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K_time: bad arguments");
+    TRY(select_device(device));
+    double *d1, *d2, *dK;
+    CU(cudaMalloc((void**)&d1, n1 * 8)); CU(cudaMalloc((void**)&d2, n2 * 8)); CU(cudaMalloc((void**)&dK, n1 * n2 * 8));
+    CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemset(dK, 0, n1 * n2 * 8));  // an unknown KERNEL string leaves the matrix untouched in the reference; here zeros
+    CU(build_K_time(0, d1, (int)n1, d2, (int)n2, os, ls, tsds2[0], tsds2[1], kernel, dK, (int)n1));
+    CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d1); cudaFree(d2); cudaFree(dK);
+    return GPIRT_OK;
+}
+int gpirt_chol(int device, const double* A, int64_t n, double* L) {
+    if (!A || !L || n < 1) return fail(GPIRT_ERR_INVALID, "gpirt_chol: bad arguments");
+    TRY(select_device(device));
+    const int ld = pad_ld(n);
+    double* dA; int* info; int hinfo = 0;
+    CU(cudaMalloc((void**)&dA, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&info, 4));
+    CU(cudaMemset(dA, 0, (size_t)ld * n * 8)); CU(cudaMemset(info, 0, 4));
+    CU(cudaMemcpy2D(dA, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
+    CU(chol_lower_blocked(0, dA, ld, (int)n, info));
+    CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(&hinfo, info, 4, cudaMemcpyDeviceToHost));
+    cudaFree(dA); cudaFree(info);
+    if (hinfo) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed at leading minor %d", hinfo);
+    return GPIRT_OK;
+}
+int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, int64_t nrhs, double* out) {
+    if (!L || !X || !out || n < 1 || nrhs < 1) return fail(GPIRT_ERR_INVALID, "gpirt_double_solve: bad arguments");
+    TRY(select_device(device));
+    const int ld = pad_ld(n);
+    double *dL, *dX;
+    CU(cudaMalloc((void**)&dL, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&dX, (size_t)ld * nrhs * 8));
+    CU(cudaMemset(dL, 0, (size_t)ld * n * 8)); CU(cudaMemset(dX, 0, (size_t)ld * nrhs * 8));
+    CU(cudaMemcpy2D(dL, (size_t)ld * 8, L, n * 8, n * 8, n, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy2D(dX, (size_t)ld * 8, X, n * 8, n * 8, nrhs, cudaMemcpyHostToDevice));
+    CU(trsm_left_lower(0, dL, ld, (int)n, dX, ld, (int)nrhs));
+    CU(trsm_left_lower_t(0, dL, ld, (int)n, dX, ld, (int)nrhs));
+    CU(cudaMemcpy2D(out, n * 8, dX, (size_t)ld * 8, n * 8, nrhs, cudaMemcpyDeviceToHost));
+    cudaFree(dL); cudaFree(dX);
+    return GPIRT_OK;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// Initial values the reference draws with R's RNG inside gpirtMCMC (src/gpirtMCMC.cpp:149-163):
+// beta0 ~ N(prior mean, prior sd) per coefficient, f0_j = L z_j. Here from the Philox INIT streams.
+int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_beta, int draw_f) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    cudaStream_t st = h->stream;
+    if (draw_beta) {
+        if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "init_draw: beta has 3 rows in gpirtMCMC");
+        double* d_means = nullptr;
+        CU(cudaMalloc((void**)&d_means, 3 * (size_t)h->m_total * 8));
+        if (beta_prior_means) CU(cudaMemcpyAsync(d_means, beta_prior_means, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, st));
+        else CU(cudaMemsetAsync(d_means, 0, 3 * (size_t)h->m_total * 8, st));
+        k_init_beta<<<(h->m_total + 127) / 128, 128, 0, st>>>(h->beta, d_means, h->sds, h->m_total, h->key());
+        CU(cudaGetLastError());
+        CU(cudaStreamSynchronize(st));
+        cudaFree(d_means);
+    }
+    if (draw_f && h->m_local > 0) {
+        if (!h->chol_valid) TRY(do_update_cholesky(h));
+        CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_INIT_F, h->item0));
+        GemmArgs g{};
+        g.M = h->n; g.N = h->m_local; g.K = h->n;
+        g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->f; g.ldc = h->ldn;
+        g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
+        CU(gemm_f64(st, false, false, g));
+    }
+    return GPIRT_OK;
+}
+
+}  // extern "C"

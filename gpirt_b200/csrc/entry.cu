@@ -1,0 +1,91 @@
+// The two Rcpp entry points of the reference as C-ABI calls with host buffers:
+//   gpirt_mcmc            <- gpirtMCMC()      src/gpirtMCMC.cpp:25-406
+//   gpirt_recover_fstar   <- recover_fstar()  src/recover_fstar.cpp:8-93
+// Host side only: sample storage, thinning and the progress/interrupt poll; all arithmetic runs in the
+// kernels behind the subsystem calls.
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gpirt_b200.h"
+
+extern "C" int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_beta, int draw_f);
+
+namespace {
+struct Guard {
+    gpirt_sampler* h = nullptr;
+    ~Guard() { if (h) gpirt_destroy(h); }
+};
+}  // namespace
+
+#define TRYC(x)                 \
+    do {                        \
+        int rc_ = (x);          \
+        if (rc_ != GPIRT_OK) return rc_; \
+    } while (0)
+
+extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
+    if (!a || !a->y || !a->theta || !a->beta_prior_sds || !a->theta_prior_sds || !a->thresholds || !a->theta_draws || !a->beta_draws ||
+        !a->threshold_draws || !a->ll_draws)
+        return GPIRT_ERR_INVALID;
+    if (a->THIN < 1 || a->sample_iterations < 0 || a->burn_iterations < 0) return GPIRT_ERR_INVALID;
+    gpirt_config cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.n = a->n; cfg.m_total = a->m; cfg.horizon = a->horizon; cfg.C = a->C; cfg.constant_IRF = a->constant_IRF; cfg.p_beta = 3;
+    cfg.theta_os = a->theta_os; cfg.theta_ls = a->theta_ls;
+    const std::string kern = a->KERNEL ? a->KERNEL : "Matern";
+    cfg.kernel = kern == "RBF" ? 1 : 0;
+    cfg.device = a->device; cfg.seed = a->seed; cfg.chain = a->chain; cfg.rank = 0; cfg.world = 1;
+    Guard g;
+    TRYC(gpirt_create(&cfg, &g.h));
+    gpirt_sampler* h = g.h;
+    TRYC(gpirt_set_data_f64(h, a->y));
+    TRYC(gpirt_set_priors(h, a->beta_prior_sds, a->theta_prior_sds));
+    TRYC(gpirt_set_state(h, a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
+    TRYC(gpirt_set_iter(h, 0xFFFFFFFFu));  // initial draws use a sweep id no sweep reaches
+    TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr));
+    TRYC(gpirt_set_iter(h, 0));
+
+    const int total = a->sample_iterations + a->burn_iterations;
+    const int n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
+    const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1;
+    std::vector<double> theta(n);
+    for (int iter = 0; iter < total; ++iter) {
+        if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;  // user interrupt
+        TRYC(gpirt_sweep(h, 1));
+        if (iter >= a->burn_iterations && iter % a->THIN == 0) {  // src/gpirtMCMC.cpp:334-335
+            const int s = (iter - a->burn_iterations) / a->THIN;
+            if (s >= n_samples) continue;  // the reference would write past theta_draws here
+            TRYC(gpirt_get_state(h, theta.data(), a->beta_draws + (size_t)s * 3 * m, a->f_draws ? a->f_draws + (size_t)s * n * m : nullptr,
+                                 a->threshold_draws + (size_t)s * m * C1, a->fstar_draws ? a->fstar_draws + (size_t)s * GPIRT_NGRID * m : nullptr));
+            for (size_t i = 0; i < n; ++i) a->theta_draws[(size_t)s + i * n_samples] = theta[i];  // cube n_samples x n x 1
+            TRYC(gpirt_total_ll(h, &a->ll_draws[s]));
+        }
+    }
+    return gpirt_sync(h);
+}
+
+extern "C" int gpirt_recover_fstar(const gpirt_recover_fstar_args* a) {
+    if (!a || !a->f || !a->y || !a->theta || !a->beta || !a->thresholds || !a->beta_prior_sds || !a->fstar) return GPIRT_ERR_INVALID;
+    gpirt_config cfg;
+    std::memset(&cfg, 0, sizeof(cfg));
+    cfg.n = a->n; cfg.m_total = a->m; cfg.horizon = a->horizon; cfg.C = a->C; cfg.constant_IRF = a->constant_IRF; cfg.p_beta = 2;
+    cfg.theta_os = 1.0; cfg.theta_ls = 10.0; cfg.kernel = 0; cfg.device = a->device;
+    cfg.seed = (uint64_t)(uint32_t)a->seed;  // ws_pool.seed_all(seed), src/recover_fstar.cpp:80
+    cfg.chain = 0; cfg.rank = 0; cfg.world = 1;
+    Guard g;
+    TRYC(gpirt_create(&cfg, &g.h));
+    gpirt_sampler* h = g.h;
+    TRYC(gpirt_set_data_f64(h, a->y));
+    // recover_fstar passes a 2 x m beta_prior_sds (R/recover_fstar.R:37-38); K() reads rows 0..2 of column 0
+    // (src/covariance-function.cpp:12-14) — an out-of-bounds read in the reference. Row 2 is taken as 0 here.
+    std::vector<double> sds3(3 * (size_t)a->m, 0.0);
+    for (int j = 0; j < a->m; ++j) { sds3[3 * (size_t)j] = a->beta_prior_sds[2 * (size_t)j]; sds3[3 * (size_t)j + 1] = a->beta_prior_sds[2 * (size_t)j + 1]; }
+    TRYC(gpirt_set_priors(h, sds3.data(), nullptr));
+    TRYC(gpirt_set_state(h, a->theta, a->beta, a->f, a->thresholds, nullptr));
+    TRYC(gpirt_set_iter(h, 0));
+    TRYC(gpirt_draw_f(h, nullptr));      // src/recover_fstar.cpp:87-88
+    TRYC(gpirt_draw_fstar(h, nullptr));  // :89-90
+    return gpirt_get_state(h, nullptr, nullptr, nullptr, nullptr, a->fstar);
+}

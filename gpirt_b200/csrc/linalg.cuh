@@ -1,0 +1,25 @@
+// Declarations of the dense fp64 building blocks (see linalg.cu).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "gemm.cuh"
+
+namespace gpirt {
+
+constexpr int CHOL_NB = 64;   // panel width of the blocked factorisation / solves
+constexpr int LD_ALIGN = 16;  // leading dimensions are padded to this many doubles
+inline int pad_ld(long long n) { return (int)((n + LD_ALIGN - 1) / LD_ALIGN * LD_ALIGN); }
+
+cudaError_t build_K(cudaStream_t st, const double* x1, int n1, const double* x2, int n2, const double* sds_host3,
+                    double* out, int ld, double diag_add);
+cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double* x2, int n2, double os, double ls,
+                         double t0, double t1, int kernel, double* out, int ld);
+
+// In-place lower Cholesky of the n x n matrix A (lower triangle read, upper triangle zeroed on exit).
+// *info_dev (device int, must be 0 on entry) receives the 1-based index of the first non-positive pivot.
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev);
+// B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
+cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
+cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
+
+}  // namespace gpirt

@@ -1,0 +1,63 @@
+// The sampler handle behind the C-ABI: owns every device buffer of one chain's item shard.
+// Replaces the reference's CholeskyCache + WorkspacePool + the state variables of gpirtMCMC()
+// (src/gpirt.h:49-68,153-195; src/gpirtMCMC.cpp:89-90,138-224).
+//
+// HBM layout (all fp64 matrices column-major, leading dimensions padded to 16 doubles, padding zero):
+//   y_im   int8  [m_local][ldy]            item-major responses of the local items (0 = missing)
+//   y_rm   int8  [n_local][ldm]            respondent-major rows of the local respondents, all items
+//   theta  f64   [n]                       current abilities (always on the theta* grid after sweep 1)
+//   theta_x f64  [world*n_chunk]           all-gather buffer of the theta step (chunk r = respondents of rank r)
+//   beta   f64   [3][world*m_chunk]        all-gather buffer, chunk r = items of rank r
+//   thr    f64   [C+1][world*m_chunk]      item-major thresholds (transposed w.r.t. the reference's m x (C+1))
+//   f, nu  f64   [ldn][m_local]            latent responses and the prior draws L*Z
+//   zbuf   f64   [max(ldn,ldN)][m_local]   normals: Z (n x m) for draw_f, then Z* (N x m) for draw_fstar
+//   fstar  f64   [world][NGRID][ld_chunk]  grid-row-major f* table: the row of one grid point is contiguous
+//   L      f64   [ldn][n]                  chol(K(theta,theta) + 1e-6 I)
+//   W      f64   [ldn][NGRID]              k*, then L^-1 k*, then K^-1 k*
+//   Kpost  f64   [ldN][NGRID]              K** - tmp^T tmp + 1e-6 I, then its Cholesky factor
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+
+#include "../../include/gpirt_b200.h"
+#include "linalg.cuh"
+#include "samplers.cuh"
+
+struct gpirt_sampler {
+    gpirt_config cfg{};
+    int n = 0, m_total = 0, C = 0, world = 1, rank = 0;
+    int m_chunk = 0, m_local = 0, item0 = 0;
+    int n_chunk = 0, n_local = 0, resp0 = 0;
+    int ldn = 0, ldN = 0, ldy = 0, ld_chunk = 0, ldz = 0;
+    long long ldm = 0;
+    int theta_regime = 0;
+
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    uint32_t iter = 0;
+    bool have_data = false, chol_valid = false;
+
+    int8_t *y_im = nullptr, *y_rm = nullptr;
+    double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;
+    double *f = nullptr, *nu = nullptr, *zbuf = nullptr, *fstar = nullptr;
+    double *L = nullptr, *W = nullptr, *Kpost = nullptr, *tstar = nullptr;
+    double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
+    int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    gpirt::DevFlags* flags = nullptr;
+    double sds0[3] = {0, 0, 0};  // beta_prior_sds.col(0): the sds every K() call uses (src/cholesky-cache.cpp:21)
+
+    // staging for supplied streams
+    double *d_z = nullptr, *d_u = nullptr;
+    size_t d_z_cap = 0, d_u_cap = 0;
+
+    gpirt::RngKey key() const {
+        gpirt::RngKey k;
+        k.k0 = (uint32_t)cfg.seed;
+        k.k1 = (uint32_t)(cfg.seed >> 32);
+        k.chain = cfg.chain;
+        k.iter = iter;
+        return k;
+    }
+};

@@ -1,0 +1,437 @@
+// The elliptical-slice samplers of the sweep as sm_100a kernels.
+//   item-parallel (one warp per item, warp-shuffle reductions, int8 responses):
+//     draw_f            src/draw-f.cpp:5-83            ess_sparse_threadsafe per item
+//     draw_beta         src/draw-beta.cpp:4-101
+//     draw_threshold    src/draw_threshold.cpp:99-169,206-228
+//     ll_bar_sparse     src/log-likelihood.cpp:50-64   (per-item totals, src/gpirtMCMC.cpp:324-331)
+//   respondent-parallel (one CTA per respondent over the grid-row-major f* table):
+//     draw_theta        src/draw-theta.cpp:4-84,112-170
+// The shrink-bracket loop runs entirely on chip: the only per-proposal traffic is the re-read of the
+// item's f / nu / y columns, which stay L1/L2 resident between proposals.
+#include "samplers.cuh"
+
+#include "probit.cuh"
+
+namespace gpirt {
+
+#define TWO_PI_R 6.283185307179586476925286766559  // Rmath M_2PI (src/draw-f.cpp:19)
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Z[i + j*ld] = i-th standard normal of unit (unit0 + j) on `stream` (Box-Muller pairs from Philox)
+__global__ void k_gen_normals(double* __restrict__ out, int ld, int rows, int cols, RngKey key, uint32_t stream, uint32_t unit0) {
+    const int pairs = (rows + 1) >> 1;
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    int j = blockIdx.y;
+    if (b >= pairs || j >= cols) return;
+    double z0, z1;
+    philox_normal2(key, stream, unit0 + j, b, z0, z1);
+    double* col = out + (size_t)j * ld;
+    col[2 * b] = z0;
+    if (2 * b + 1 < rows) col[2 * b + 1] = z1;
+}
+
+cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, int cols, RngKey key, uint32_t stream, uint32_t unit0) {
+    if (rows <= 0 || cols <= 0) return cudaSuccess;
+    dim3 grid(((rows + 1) / 2 + 127) / 128, cols);
+    k_gen_normals<<<grid, 128, 0, st>>>(out, ld, rows, cols, key, stream, unit0);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+// One warp per item. MODE selects what the ellipse moves: the item's f column, its 3 mean
+// coefficients, or its C-1 threshold deltas.
+constexpr int ITEM_WARPS = 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
+    __shared__ double s_tau[ITEM_WARPS][MAX_C + 1];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * ITEM_WARPS + warp;
+    if (j >= v.m_local) return;
+    const int J = v.item0 + j;
+    const int C = v.C;
+    double* tau = s_tau[warp];
+    for (int c = lane; c <= C; c += 32) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
+    __syncwarp();
+
+    const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
+    double* __restrict__ fj = v.f + (size_t)j * v.ldn;
+    const double* __restrict__ nuj = (MODE == IB_F) ? v.nu + (size_t)j * v.ldn : nullptr;
+    const double* __restrict__ theta = v.theta;
+    const int n = v.n;
+    double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
+
+    // log-likelihood of the item at the point (ce, se) of the ellipse; ce=1, se=0 is the current state
+    double pb0 = b0, pb1 = b1, pb2 = b2;
+    auto loglik = [&](double ce, double se, bool current) -> double {
+        double acc = 0.0;
+        for (int i = lane; i < n; i += 32) {
+            const int y = yj[i];
+            if (y == 0) continue;
+            double fi = fj[i];
+            if (MODE == IB_F && !current) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
+            const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
+            acc += cell_ll(g, tau[y - 1], tau[y], y == 1, y == C);
+        }
+        return warp_sum(acc);
+    };
+
+    // prior draw for the low-dimensional blocks
+    double nu_small[MAX_C];  // beta: 3 used; thresholds: C-1 used
+    double delta[MAX_C];
+    if (MODE == IB_BETA) {
+        // items without observations keep beta and draw nothing (src/draw-beta.cpp:73,97-99)
+        int any = 0;
+        for (int i = lane; i < n; i += 32) any |= (yj[i] != 0);
+        if (!__any_sync(0xffffffffu, any)) {
+            if (lane == 0) { v.evals[J] = 0; v.margin[J] = CUDART_INF; }
+            return;
+        }
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            double z = v.z ? v.z[(size_t)J * v.z_stride + q] : philox_normal(v.key, ST_BETA_Z, J, q);
+            double sd = v.sds[3 * (size_t)J + q];
+            nu_small[q] = __dmul_rn(sqrt(__dadd_rn(__dmul_rn(sd, sd), 1e-6)), z);  // chol(diag(sd^2+1e-6)) z, :82-86
+        }
+    }
+    if (MODE == IB_THR) {
+        // threshold_to_delta (src/log-likelihood.cpp:78-88), identity prior (src/draw_threshold.cpp:110-114)
+        delta[0] = tau[1];
+        for (int q = 1; q < C - 1; ++q) delta[q] = log(__dsub_rn(tau[q + 1], tau[q]));
+        for (int q = 0; q < C - 1; ++q) nu_small[q] = v.z ? v.z[(size_t)J * v.z_stride + q] : philox_normal(v.key, ST_THR_Z, J, q);
+        // the reference evaluates the current state through delta_to_threshold(delta) (:118)
+        __syncwarp();
+        if (lane == 0) {
+            tau[1] = delta[0];
+            for (int q = 1; q < C - 1; ++q) tau[q + 1] = __dadd_rn(tau[q], exp(delta[q]));
+        }
+        __syncwarp();
+    }
+
+    const uint32_t ustream = MODE == IB_F ? ST_F_U : (MODE == IB_BETA ? ST_BETA_U : ST_THR_U);
+    int overrun = 0;
+    uint32_t k = 0;
+    const double u = v.us.get(v.key, ustream, J, k++, &overrun);
+    const double ll_cur = loglik(1.0, 0.0, true);
+    const double log_y = __dadd_rn(ll_cur, log(u));
+    double eps_min = 0.0, eps_max = TWO_PI_R;
+    double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
+    eps_min = __dsub_rn(eps, TWO_PI_R);
+    int evals = 1;
+    double margin = CUDART_INF;
+    double ce = 1.0, se = 0.0;
+    bool accepted = false;
+    for (int it = 0; it < ESS_MAX_PROPOSALS; ++it) {
+        ce = cos(eps);
+        se = sin(eps);
+        if (MODE == IB_BETA) {
+            pb0 = __dadd_rn(__dmul_rn(b0, ce), __dmul_rn(nu_small[0], se));
+            pb1 = __dadd_rn(__dmul_rn(b1, ce), __dmul_rn(nu_small[1], se));
+            pb2 = __dadd_rn(__dmul_rn(b2, ce), __dmul_rn(nu_small[2], se));
+        }
+        if (MODE == IB_THR) {
+            __syncwarp();
+            if (lane == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
+                tau[1] = __dadd_rn(__dmul_rn(delta[0], ce), __dmul_rn(nu_small[0], se));
+                for (int q = 1; q < C - 1; ++q)
+                    tau[q + 1] = __dadd_rn(tau[q], exp(__dadd_rn(__dmul_rn(delta[q], ce), __dmul_rn(nu_small[q], se))));
+            }
+            __syncwarp();
+        }
+        double llp = loglik(ce, se, false);
+        llp = __shfl_sync(0xffffffffu, llp, 0);
+        ++evals;
+        margin = fmin(margin, fabs(llp - log_y));
+        if (llp > log_y) { accepted = true; break; }
+        if (eps < 0.0) eps_min = eps; else eps_max = eps;
+        eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
+        if (overrun) break;
+    }
+    if (lane == 0) {
+        v.evals[J] = evals;
+        v.margin[J] = margin;
+        if (overrun) atomicExch(&v.flags->overrun, 1);
+        else if (!accepted) atomicExch(&v.flags->stalled, 1);
+    }
+    // commit the last proposal (the reference's `out = f_prime`): on a stall/overrun this is still a
+    // point of the ellipse, and the raised flag turns the call into an error at the next sync
+    if (MODE == IB_F) {
+        for (int i = lane; i < n; i += 32) fj[i] = __dadd_rn(__dmul_rn(fj[i], ce), __dmul_rn(nuj[i], se));
+    } else if (MODE == IB_BETA) {
+        if (lane == 0) {
+            v.beta[3 * (size_t)J] = pb0;
+            v.beta[3 * (size_t)J + 1] = pb1;
+            v.beta[3 * (size_t)J + 2] = pb2;
+        }
+    } else {
+        __syncwarp();
+        for (int c = 1 + lane; c < C; c += 32) v.thr[(size_t)J * (v.C + 1) + c] = tau[c];
+    }
+}
+
+cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v) {
+    if (v.m_local <= 0) return cudaSuccess;
+    dim3 grid((v.m_local + ITEM_WARPS - 1) / ITEM_WARPS);
+    if (block == IB_F) k_ess_items<IB_F><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
+    else if (block == IB_BETA) k_ess_items<IB_BETA><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
+    else k_ess_items<IB_THR><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
+    return cudaGetLastError();
+}
+
+// per-item ll_bar_sparse with the current state
+__global__ void __launch_bounds__(ITEM_WARPS * 32) k_item_ll(ItemView v) {
+    __shared__ double s_tau[ITEM_WARPS][MAX_C + 1];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int j = blockIdx.x * ITEM_WARPS + warp;
+    if (j >= v.m_local) return;
+    const int J = v.item0 + j;
+    double* tau = s_tau[warp];
+    for (int c = lane; c <= v.C; c += 32) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
+    __syncwarp();
+    const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
+    const double* __restrict__ fj = v.f + (size_t)j * v.ldn;
+    const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
+    double acc = 0.0;
+    for (int i = lane; i < v.n; i += 32) {
+        const int y = yj[i];
+        if (y == 0) continue;
+        const double g = __dadd_rn(fj[i], mu_of(v.theta[i], b0, b1, b2));
+        acc += cell_ll(g, tau[y - 1], tau[y], y == 1, y == v.C);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) v.item_ll[J] = acc;
+}
+
+cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v) {
+    if (v.m_local <= 0) return cudaSuccess;
+    k_item_ll<<<(v.m_local + ITEM_WARPS - 1) / ITEM_WARPS, ITEM_WARPS * 32, 0, st>>>(v);
+    return cudaGetLastError();
+}
+
+}  // namespace gpirt
+
+namespace gpirt {
+
+// ------------------------------------------------------------------------------------------------
+// draw_theta: one CTA per respondent. The f* table is grid-row-major, so the row a proposal lands on
+// is one contiguous run of m doubles per shard chunk (the reference gathers it with stride N).
+constexpr int THETA_THREADS = 128;
+
+__global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
+    __shared__ double s_part[THETA_THREADS / 32];
+    const int il = blockIdx.x;
+    if (il >= v.n_local) return;
+    const int i = v.resp0 + il;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int8_t* __restrict__ yrow = v.y_rm + (size_t)il * v.ldm;
+    const int C = v.C, m_total = v.m_total;
+
+    auto loglik = [&](double th) -> double {  // compute_ll_sparse, src/draw-theta.cpp:4-24
+        const int idx = grid_index(th);
+        const double ts = grid_value(idx);
+        double acc = 0.0;
+        for (int J = tid; J < m_total; J += THETA_THREADS) {
+            const int y = yrow[J];
+            if (y == 0) continue;
+            const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
+            const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+            const double mu = mu_of(ts, v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
+            const double g = __dadd_rn(fs, mu);  // f* already holds mu*; the reference adds it again (:17)
+            acc += cell_ll(g, v.thr[(size_t)J * (C + 1) + y - 1], v.thr[(size_t)J * (C + 1) + y], y == 1, y == C);
+        }
+        acc = warp_sum(acc);
+        __syncthreads();
+        if (lane == 0) s_part[warp] = acc;
+        __syncthreads();
+        double tot = 0.0;
+#pragma unroll
+        for (int w = 0; w < THETA_THREADS / 32; ++w) tot += s_part[w];
+        return tot;
+    };
+
+    double Li;
+    if (v.regime == 0) {
+        const double sd = v.theta_prior_sds[2 * (size_t)i];
+        Li = sqrt(__dadd_rn(1.0, __dmul_rn(sd, sd)));  // chol(V + sd^2), src/draw-theta.cpp:158,194
+    } else {
+        Li = sqrt(__dadd_rn(__dmul_rn(v.theta_os, v.theta_os), 1e-6));  // L_time at H = 1, src/cholesky-cache.cpp:29-33
+    }
+    const double z = v.z ? v.z[(size_t)i * v.z_stride] : philox_normal(v.key, ST_THETA_Z, i, 0);
+    const double nu = __dmul_rn(Li, z);
+    const double th0 = v.theta[i];
+    int overrun = 0;
+    uint32_t k = 0;
+    const double u = v.us.get(v.key, ST_THETA_U, i, k++, &overrun);
+    const double log_y = __dadd_rn(log(u), loglik(th0));
+    double eps_min = 0.0, eps_max = TWO_PI_R;
+    double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+    eps_min = __dsub_rn(eps, TWO_PI_R);
+    int evals = 1;
+    double margin = CUDART_INF, raw = th0;
+    bool accepted = false;
+    for (int it = 0; it < ESS_MAX_PROPOSALS; ++it) {
+        raw = __dadd_rn(__dmul_rn(th0, cos(eps)), __dmul_rn(nu, sin(eps)));
+        raw = fmax(-5.0, fmin(5.0, raw));
+        const double llp = loglik(raw);
+        ++evals;
+        margin = fmin(margin, fabs(llp - log_y));
+        if (llp > log_y) { accepted = true; break; }
+        if (eps < 0.0) eps_min = eps; else eps_max = eps;
+        eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+        if (overrun) break;
+    }
+    if (tid == 0) {
+        v.theta_new[i] = grid_value(grid_index(raw));  // snapped to the grid, src/draw-theta.cpp:165-169
+        v.evals[i] = evals;
+        v.margin[i] = margin;
+        if (overrun) atomicExch(&v.flags->overrun, 1);
+        else if (!accepted) atomicExch(&v.flags->stalled, 1);
+    }
+}
+
+cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
+    if (v.n_local <= 0) return cudaSuccess;
+    k_ess_theta<<<v.n_local, THETA_THREADS, 0, st>>>(v);
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void k_gather_f(const double* __restrict__ theta, int n, const double* __restrict__ fstar, int ld_chunk,
+                           int m_local, double* __restrict__ f, int ldn) {
+    __shared__ double t[32][33];
+    const int i0 = blockIdx.x * 32, j0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int r = ty; r < 32; r += 8) {
+        const int i = i0 + r, j = j0 + tx;
+        if (i < n && j < m_local) t[r][tx] = fstar[(size_t)grid_index(theta[i]) * ld_chunk + j];
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int j = j0 + r, i = i0 + tx;
+        if (i < n && j < m_local) f[(size_t)j * ldn + i] = t[tx][r];
+    }
+}
+
+cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const double* fstar_chunk, int ld_chunk, int m_local,
+                            double* f, int ldn) {
+    dim3 grid((n + 31) / 32, (m_local + 31) / 32), blk(32, 8);
+    k_gather_f<<<grid, blk, 0, st>>>(theta, n, fstar_chunk, ld_chunk, m_local, f, ldn);
+    return cudaGetLastError();
+}
+
+__global__ void k_add_mustar(double* __restrict__ fstar, int ld_chunk, int m_local, int item0, const double* __restrict__ beta, int p_beta) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = blockIdx.y;
+    if (j >= m_local) return;
+    const size_t J = (size_t)item0 + j;
+    const double ts = grid_value(idx);
+    const double mu = mu_of(ts, beta[3 * J], beta[3 * J + 1], p_beta == 3 ? beta[3 * J + 2] : 0.0);
+    fstar[(size_t)idx * ld_chunk + j] += mu;
+}
+
+cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta) {
+    dim3 grid((m_local + 127) / 128, NGRID);
+    k_add_mustar<<<grid, 128, 0, st>>>(fstar_chunk, ld_chunk, m_local, item0, beta, p_beta);
+    return cudaGetLastError();
+}
+
+__global__ void k_ordered_sum(const double* __restrict__ x, int n, double* out) {
+    // fixed-shape reduction: 256 strided partial sums, combined in index order by thread 0
+    __shared__ double s[256];
+    double acc = 0.0;
+    for (int i = threadIdx.x; i < n; i += 256) acc += x[i];
+    s[threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 256; ++k) t += s[k];
+        *out = t;
+    }
+}
+cudaError_t launch_ordered_sum(cudaStream_t st, const double* x, int n, double* out) {
+    k_ordered_sum<<<1, 256, 0, st>>>(x, n, out);
+    return cudaGetLastError();
+}
+
+// out[c + r*ld_out] = in[r + c*ld_in]
+__global__ void k_transpose(const double* __restrict__ in, int ld_in, int rows, int cols, double* __restrict__ out, int ld_out) {
+    __shared__ double t[32][33];
+    const int r0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int k = ty; k < 32; k += 8) {
+        const int r = r0 + tx, c = c0 + k;
+        if (r < rows && c < cols) t[k][tx] = in[(size_t)c * ld_in + r];
+    }
+    __syncthreads();
+    for (int k = ty; k < 32; k += 8) {
+        const int c = c0 + tx, r = r0 + k;
+        if (r < rows && c < cols) out[(size_t)r * ld_out + c] = t[tx][k];
+    }
+}
+cudaError_t launch_transpose(cudaStream_t st, const double* in, int ld_in, int rows, int cols, double* out, int ld_out) {
+    dim3 grid((rows + 31) / 32, (cols + 31) / 32), blk(32, 8);
+    k_transpose<<<grid, blk, 0, st>>>(in, ld_in, rows, cols, out, ld_out);
+    return cudaGetLastError();
+}
+
+__global__ void k_clamp_theta(double* theta, int n) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) theta[i] = fmax(-5.0, fmin(5.0, theta[i]));  // theta.clamp(-5,5), src/gpirtMCMC.cpp:133
+}
+cudaError_t launch_clamp_theta(cudaStream_t st, double* theta, int n) {
+    k_clamp_theta<<<(n + 255) / 256, 256, 0, st>>>(theta, n);
+    return cudaGetLastError();
+}
+
+// y (float64, NaN missing, codes 1..C) -> int8 (0 missing). Non-finite == missing (arma::find_finite).
+__global__ void k_y_to_i8(const double* __restrict__ y, long long count, int C, int8_t* __restrict__ out, DevFlags* flags) {
+    long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= count) return;
+    const double v = y[e];
+    int8_t code = 0;
+    if (isfinite(v)) {
+        const int c = (int)v;  // int(y[i]), src/log-likelihood.cpp:57
+        if (c < 1 || c > C) { atomicExch(&flags->bad_code, 1); code = 0; }
+        else code = (int8_t)c;
+    }
+    out[e] = code;
+}
+cudaError_t launch_y_to_i8(cudaStream_t st, const double* y, long long count, int C, int8_t* out, DevFlags* flags) {
+    k_y_to_i8<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(y, count, C, out, flags);
+    return cudaGetLastError();
+}
+
+// From the full n x m_total int8 matrix (column-major) build the two resident layouts:
+//   y_im[j*ldy + i]   item-major columns of the local items (padding zero = missing)
+//   y_rm[il*ldm + J]  respondent-major rows of the local respondents
+__global__ void k_y_layouts(const int8_t* __restrict__ y, int n, int m_total, int item0, int m_local, int8_t* __restrict__ y_im, int ldy,
+                            int resp0, int n_local, int8_t* __restrict__ y_rm, long long ldm) {
+    __shared__ int8_t t[32][33];
+    const int i0 = blockIdx.x * 32, J0 = blockIdx.y * 32;
+    const int tx = threadIdx.x, ty = threadIdx.y;
+    for (int k = ty; k < 32; k += 8) {
+        const int i = i0 + tx, J = J0 + k;
+        int8_t val = (i < n && J < m_total) ? y[(size_t)J * n + i] : 0;
+        t[k][tx] = val;
+        if (i < n && J >= item0 && J < item0 + m_local) y_im[(size_t)(J - item0) * ldy + i] = val;
+    }
+    __syncthreads();
+    for (int k = ty; k < 32; k += 8) {
+        const int J = J0 + tx, i = i0 + k;
+        if (J < m_total && i >= resp0 && i < resp0 + n_local) y_rm[(size_t)(i - resp0) * ldm + J] = t[tx][k];
+    }
+}
+cudaError_t launch_y_layouts(cudaStream_t st, const int8_t* y_full, int n, int m_total, int item0, int m_local, int8_t* y_im, int ldy,
+                             int resp0, int n_local, int8_t* y_rm, long long ldm) {
+    dim3 grid((n + 31) / 32, (m_total + 31) / 32), blk(32, 8);
+    k_y_layouts<<<grid, blk, 0, st>>>(y_full, n, m_total, item0, m_local, y_im, ldy, resp0, n_local, y_rm, ldm);
+    return cudaGetLastError();
+}
+
+}  // namespace gpirt

@@ -1,0 +1,86 @@
+// Device-side views and launchers of the per-block samplers (see samplers.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "rng.cuh"
+
+namespace gpirt {
+
+constexpr int NGRID = 1001;
+constexpr int MAX_C = 21;
+constexpr int ESS_MAX_PROPOSALS = 2000;  // the reference has no cap (src/draw-f.cpp:23); a NaN likelihood would spin forever
+
+// flags raised by kernels, read back at sync points
+struct DevFlags {
+    int chol_info;       // failing leading minor of chol(K)
+    int chol_post_info;  // failing leading minor of chol(K_post)
+    int overrun;         // a supplied uniform stream ran dry
+    int stalled;         // an ESS loop hit ESS_MAX_PROPOSALS
+    int bad_code;        // a y code outside 0..C
+};
+
+// Everything the item-parallel kernels need (one warp per local item).
+struct ItemView {
+    int n, ldn;               // respondents; leading dimension of f / nu
+    int m_local, item0;       // local items and the global index of the first one
+    int m_total, C, p_beta;
+    const int8_t* y_im;       // item-major responses of the local items: y_im[j*ldy + i], 0 = missing
+    int ldy;
+    const double* theta;      // n
+    double* beta;             // 3 x m_total
+    double* thr;              // (C+1) x m_total item-major: thr[J*(C+1) + c]
+    double* f;                // n x m_local
+    const double* nu;         // n x m_local (draw_f)
+    const double* sds;        // 3 x m_total beta_prior_sds
+    const double* z; long long z_stride;   // supplied normals (beta / thresholds) or nullptr
+    UniformSrc us;
+    RngKey key;
+    int32_t* evals;           // per global item
+    double* margin;
+    double* item_ll;          // per global item (k_item_ll)
+    DevFlags* flags;
+};
+
+struct ThetaView {
+    int n, resp0, n_local;    // local respondents [resp0, resp0 + n_local)
+    int m_total, m_chunk, ld_chunk, world, C;
+    const int8_t* y_rm;       // respondent-major rows of the local respondents: y_rm[il*ldm + J]
+    long long ldm;
+    const double* theta;      // n (current)
+    double* theta_new;        // n
+    const double* fstar_all;  // world chunks of NGRID x ld_chunk (grid-row-major: [idx*ld_chunk + jl])
+    long long chunk_elems;
+    const double* beta;       // 3 x m_total
+    const double* thr;        // (C+1) x m_total item-major
+    const double* theta_prior_sds;  // 2 x n
+    int regime;               // 0: L_i = sqrt(1 + sd0_i^2) (CST/RDM), 1: sqrt(os^2 + 1e-6) (GP over time, H = 1)
+    double theta_os;
+    const double* z; long long z_stride;
+    UniformSrc us;
+    RngKey key;
+    int32_t* evals;
+    double* margin;
+    DevFlags* flags;
+};
+
+enum ItemBlock { IB_F = 0, IB_BETA = 1, IB_THR = 2 };
+
+cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, int cols, RngKey key, uint32_t stream, uint32_t unit0);
+cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v);
+cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v);
+cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v);
+// f[i + j*ldn] = fstar_chunk[grid_index(theta_i)*ld_chunk + j]  (src/gpirtMCMC.cpp:291-298)
+cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const double* fstar_chunk, int ld_chunk, int m_local, double* f, int ldn);
+// fstar_chunk[idx*ld_chunk + j] += mu_star(idx, item0 + j)  (src/draw-fstar.cpp:52)
+cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta);
+// sum of per-item values in index order (src/gpirtMCMC.cpp:325-331 accumulates item by item)
+cudaError_t launch_ordered_sum(cudaStream_t st, const double* x, int n, double* out);
+// layout converters between the reference's N x m column-major f* and the grid-row-major device table
+cudaError_t launch_transpose(cudaStream_t st, const double* in, int ld_in, int rows, int cols, double* out, int ld_out);
+cudaError_t launch_clamp_theta(cudaStream_t st, double* theta, int n);
+cudaError_t launch_y_to_i8(cudaStream_t st, const double* y, long long count, int C, int8_t* out, DevFlags* flags);
+cudaError_t launch_y_layouts(cudaStream_t st, const int8_t* y_full, int n, int m_total, int item0, int m_local, int8_t* y_im, int ldy,
+                             int resp0, int n_local, int8_t* y_rm, long long ldm);
+
+}  // namespace gpirt

@@ -1,0 +1,189 @@
+/* gpirt_b200 — C-ABI of the B200-native gpirt sweep (drop-in boundary).
+ *
+ * Every entry point replaces one interface of the reference (paths relative to the reference tree):
+ *   gpirt_K                      <- arma::mat K(x1, x2, sds)                    src/gpirt.h:269, src/covariance-function.cpp:3-18
+ *   gpirt_K_time                 <- arma::mat K_time(...)                       src/gpirt.h:270-272, src/covariance-function.cpp:21-44
+ *   gpirt_delta_to_threshold /
+ *   gpirt_threshold_to_delta     <- src/gpirt.h:285-286, src/log-likelihood.cpp:66-88
+ *   gpirt_update_cholesky_cache  <- update_cholesky_cache()                     src/gpirt.h:262-266, src/cholesky-cache.cpp:11-40
+ *   gpirt_double_solve           <- double_solve(L, X)                          src/gpirt.h:289, src/cholesky-cache.cpp:4-9
+ *   gpirt_ll_bar                 <- ll_bar_sparse() over every item             src/gpirt.h:280-282, src/log-likelihood.cpp:50-64,
+ *                                                                                src/gpirtMCMC.cpp:324-331
+ *   gpirt_draw_f                 <- draw_f()                                    src/gpirt.h:216-222, src/draw-f.cpp:47-83
+ *   gpirt_draw_fstar             <- draw_fstar()                                src/gpirt.h:225-232, src/draw-fstar.cpp:4-57
+ *   gpirt_draw_theta             <- draw_theta()                                src/gpirt.h:235-244, src/draw-theta.cpp:86-237
+ *   gpirt_gather_f               <- f(k,:,h) = f_star(idx,:,h)                  src/gpirtMCMC.cpp:291-298
+ *   gpirt_draw_beta              <- draw_beta()                                 src/gpirt.h:247-252, src/draw-beta.cpp:51-101
+ *   gpirt_draw_threshold         <- draw_threshold()                            src/gpirt.h:255-259, src/draw_threshold.cpp:171-230
+ *   gpirt_sweep                  <- one body of the sweep loop                  src/gpirtMCMC.cpp:261-331
+ *   gpirt_mcmc                   <- Rcpp::List gpirtMCMC(...)                   src/gpirtMCMC.cpp:25-406 (.Call _gpirt_gpirtMCMC,
+ *                                                                                src/RcppExports.cpp:16-39)
+ *   gpirt_recover_fstar          <- Rcpp::List recover_fstar(...)               src/recover_fstar.cpp:8-93 (.Call _gpirt_recover_fstar,
+ *                                                                                src/RcppExports.cpp:42-58)
+ *   gpirt_create/destroy, set/get <- CholeskyCache + WorkspacePool lifetime     src/gpirt.h:49-68,153-195, src/gpirtMCMC.cpp:89-90
+ *
+ * Conventions: every matrix is column-major float64 exactly as Armadillo lays it out (a cube is
+ * `horizon` contiguous slices); y is float64 with NaN = missing and integer codes 1..C otherwise
+ * (gpirt_set_data_i8 takes the compact form: 0 = missing). All pointers in this header are HOST
+ * pointers unless a name says `dev`. No call throws; each returns a gpirt_status and
+ * gpirt_last_error() holds the message (R shim: Rcpp::stop(gpirt_last_error())). There is no CPU
+ * fallback: without a CUDA device every compute call returns GPIRT_ERR_NO_DEVICE.
+ *
+ * Scope of this build: horizon == 1 and constant_IRF == 0 (all BASELINE configs); other values
+ * return GPIRT_ERR_UNSUPPORTED.
+ */
+#ifndef GPIRT_B200_H
+#define GPIRT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPIRT_NGRID 1001     /* theta* = regspace(-5, 0.01, 5), src/gpirtMCMC.cpp:205 */
+#define GPIRT_MAX_C 21       /* Workspace::delta_prime(20), src/gpirt.h:111 */
+
+typedef enum {
+    GPIRT_OK = 0,
+    GPIRT_ERR_INVALID = 1,        /* NULL handle / argument */
+    GPIRT_ERR_SHAPE = 2,          /* inconsistent sizes (Armadillo would throw a shape error) */
+    GPIRT_ERR_CATEGORIES = 3,     /* C < 2 or C > 21, or a y code outside 1..C */
+    GPIRT_ERR_NOT_PD = 4,         /* chol failed (arma::chol throws); gpirt_last_error names the leading minor */
+    GPIRT_ERR_CUDA = 5,
+    GPIRT_ERR_UNSUPPORTED = 6,    /* horizon > 1, constant_IRF != 0 */
+    GPIRT_ERR_STREAM_OVERRUN = 7, /* a supplied uniform stream ran dry before an ESS loop accepted */
+    GPIRT_ERR_NO_DEVICE = 8,
+    GPIRT_ERR_ESS_STALLED = 9     /* an ESS loop hit the proposal cap (reference would spin forever) */
+} gpirt_status;
+
+typedef struct gpirt_sampler gpirt_sampler; /* opaque: owns all device memory, streams and events */
+
+typedef struct {
+    int32_t n;             /* respondents */
+    int32_t m_total;       /* items of the whole problem */
+    int32_t horizon;       /* must be 1 */
+    int32_t C;             /* response categories, 2..21 */
+    int32_t constant_IRF;  /* must be 0 */
+    int32_t p_beta;        /* rows of beta: 3 (gpirtMCMC) or 2 (recover_fstar, src/recover_fstar.cpp:58-60) */
+    double theta_os;       /* gpirtMCMC(theta_os=) */
+    double theta_ls;       /* gpirtMCMC(theta_ls=): regime switch of src/draw-theta.cpp:112,171,206 */
+    int32_t kernel;        /* 0 "Matern", 1 "RBF" (src/covariance-function.cpp:31,36) */
+    int32_t device;        /* CUDA ordinal */
+    uint64_t seed;         /* Philox key for production-mode streams */
+    uint32_t chain;        /* stream id of this chain */
+    /* item shard owned by this handle (single GPU: rank 0 of 1). Items [rank*m_total/world, ...). */
+    int32_t rank, world;
+} gpirt_config;
+
+/* Random streams for one block call. NULL members => on-device Philox4x32-10 keyed by
+ * (seed, chain, iter, block, unit). Supplied members (parity mode) are host arrays:
+ *   z  : z[unit * z_stride + i]   standard normals, in the reference's draw order
+ *   u  : u[unit * u_stride + k]   U(0,1): k=0 slice height, k=1 initial angle, k>=2 one per rejection
+ *   nu : draw_f only — the prior draw nu = L z itself, n x m column-major (skips the L*Z contraction)
+ * `unit` is the GLOBAL item (or respondent) index. */
+typedef struct {
+    const double* z;  int64_t z_stride;
+    const double* u;  int64_t u_stride;
+    const double* nu;
+} gpirt_streams;
+
+typedef enum { GPIRT_BLOCK_F = 0, GPIRT_BLOCK_FSTAR = 1, GPIRT_BLOCK_THETA = 2, GPIRT_BLOCK_BETA = 3, GPIRT_BLOCK_THR = 4 } gpirt_block;
+
+const char* gpirt_last_error(void);
+int gpirt_device_count(void);
+
+/* ---- stateless leaves (host in, host out; run on `device`) ---- */
+int gpirt_K(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, const double* sds3, double* out);
+int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, double os, double ls,
+                 const double* tsds2, int kernel, double* out);
+int gpirt_delta_to_threshold(const double* deltas, int C, double* thresholds);   /* host-only bookkeeping, bit-exact */
+int gpirt_threshold_to_delta(const double* thresholds, int C, double* deltas);
+int gpirt_chol(int device, const double* A, int64_t n, double* L);               /* arma::chol(A,"lower") */
+int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, int64_t nrhs, double* out);
+
+/* ---- lifetime, data, state ---- */
+int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out);
+int gpirt_destroy(gpirt_sampler* h);
+int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream);  /* run on the caller's stream (e.g. torch's current stream) */
+int gpirt_set_data_f64(gpirt_sampler* h, const double* y);  /* n x m_total, NaN missing */
+int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y);   /* n x m_total, 0 missing */
+int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds /*3 x m_total*/, const double* theta_prior_sds /*2 x n*/);
+/* any pointer may be NULL (left unchanged). beta: p_beta x m_total; f: n x m_total; thresholds: m_total x (C+1);
+ * fstar: NGRID x m_total. Setting theta clamps it to [-5,5] (src/gpirtMCMC.cpp:133). */
+int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, const double* f, const double* thresholds,
+                    const double* fstar);
+int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, double* thresholds, double* fstar);
+int gpirt_get_L(gpirt_sampler* h, double* L /* n x n, upper triangle zero */);
+int gpirt_set_iter(gpirt_sampler* h, uint32_t iter);         /* sweep counter used to key the Philox streams */
+int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin); /* per unit: 1+proposals, min |ll'-log_y| */
+int gpirt_sync(gpirt_sampler* h);                            /* wait for queued work; surfaces deferred errors */
+/* initial values the reference draws inside gpirtMCMC (src/gpirtMCMC.cpp:149-163): beta0 ~ N(prior mean, prior sd)
+ * (beta_prior_means 3 x m_total or NULL = 0) and f0_j = L z_j, from the Philox INIT streams */
+int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_beta, int draw_f);
+
+/* ---- subsystems (asynchronous on the handle's stream unless they return host data) ---- */
+int gpirt_update_cholesky_cache(gpirt_sampler* h);
+int gpirt_draw_f(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_draw_fstar(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_draw_theta(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_gather_f(gpirt_sampler* h);
+int gpirt_draw_beta(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_draw_threshold(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_ll_bar(gpirt_sampler* h, double* per_item /* m_total or NULL */, double* total /* or NULL */);
+
+/* ---- sweep ---- */
+int gpirt_sweep(gpirt_sampler* h, int n_sweeps);             /* world == 1: whole sweeps, Philox streams */
+/* item-sharded sweeps (world > 1): the caller performs the exchanges between the phases on the
+ * same stream; gpirt_exchange_buffer exposes the device buffers they operate on. */
+int gpirt_sweep_phase_items(gpirt_sampler* h);               /* draw_f, draw_fstar on the local items */
+int gpirt_sweep_phase_theta(gpirt_sampler* h);               /* theta ESS for the local respondents */
+int gpirt_sweep_phase_close(gpirt_sampler* h);               /* gather, beta, mu, cholesky, thresholds, item ll */
+typedef enum { GPIRT_XCHG_FSTAR = 0, GPIRT_XCHG_BETA = 1, GPIRT_XCHG_THR = 2, GPIRT_XCHG_THETA = 3, GPIRT_XCHG_ITEM_LL = 4 } gpirt_xchg;
+/* device pointer of the all-gather buffer `which`; it holds `world` equal chunks of chunk_bytes, chunk r owned by rank r */
+int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
+int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */
+
+/* ---- the two Rcpp entry points ---- */
+typedef struct {
+    /* inputs mirror gpirtMCMC()'s arguments (src/gpirtMCMC.cpp:25-38) */
+    const double* y; int32_t n, m, horizon;
+    const double* theta;                       /* n x horizon initial values */
+    int32_t sample_iterations, burn_iterations, THIN;
+    const double* beta_prior_means;            /* 3 x m */
+    const double* beta_prior_sds;              /* 3 x m */
+    const double* theta_prior_means;           /* 2 x n (unused by the sampler, as in the reference) */
+    const double* theta_prior_sds;             /* 2 x n */
+    double theta_os, theta_ls; const char* KERNEL;
+    const double* thresholds; int32_t C;       /* m x (C+1) x horizon */
+    int32_t constant_IRF, store_f, store_fstar;
+    /* the reference draws these with R's RNG inside the call (src/gpirtMCMC.cpp:149-163); the R shim draws
+     * them and passes them in; NULL => drawn on the device from the Philox INIT streams */
+    const double* beta_init;                   /* 3 x m or NULL */
+    const double* f_init;                      /* n x m or NULL */
+    uint64_t seed; uint32_t chain; int32_t device;
+    /* outputs, caller-allocated (n_samples = sample_iterations / THIN) */
+    double* theta_draws;                       /* n_samples x n x horizon */
+    double* beta_draws;                        /* n_samples slices of 3 x m x horizon */
+    double* threshold_draws;                   /* n_samples slices of m x (C+1) x horizon */
+    double* f_draws;                           /* n_samples slices of n x m x horizon, or NULL */
+    double* fstar_draws;                       /* n_samples slices of NGRID x m x horizon, or NULL */
+    double* ll_draws;                          /* n_samples */
+    /* progress / interrupt poll, called once per sweep on the calling thread (Rprintf + checkUserInterrupt,
+     * src/gpirtMCMC.cpp:262-264); return non-zero to stop. May be NULL. */
+    int (*progress)(int iter, int total, void* user); void* user;
+} gpirt_mcmc_args;
+int gpirt_mcmc(const gpirt_mcmc_args* a);
+
+typedef struct {
+    int32_t seed; const double* f; const double* y; int32_t n, m, horizon;
+    const double* theta; const double* beta /* 2 x m x horizon */; const double* thresholds; int32_t C;
+    const double* beta_prior_means; const double* beta_prior_sds; int32_t constant_IRF; int32_t device;
+    double* fstar /* NGRID x m x horizon */;
+} gpirt_recover_fstar_args;
+int gpirt_recover_fstar(const gpirt_recover_fstar_args* a);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

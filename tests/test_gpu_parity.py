@@ -1,0 +1,229 @@
+"""GPU parity: every subsystem of the sweep, called through the C-ABI, against the CPU oracle on the same
+seeded inputs with the same supplied nu / z / uniform streams. Tolerances are written at each check."""
+import numpy as np
+import pytest
+
+import gpirt_b200
+from oracle import orc
+from tests.problems import make_problem, uniform_streams
+
+pytestmark = pytest.mark.gpu
+
+
+def _pair(P, seed=1, **kw):
+    S = gpirt_b200.Sampler(P["n"], P["m"], P["C"], seed=seed, **kw)
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    O = orc.Sampler(P["y"], P["C"], P["beta_prior_sds"], P["theta_prior_sds"])
+    return S, O
+
+
+def test_K_matches_reference_formula():
+    rng = np.random.default_rng(0)
+    x1, x2 = rng.standard_normal(257) * 2, rng.standard_normal(130) * 2
+    sds = np.array([3.0, 2.0, 0.5])
+    got, want = gpirt_b200.K(x1, x2, sds), orc.K(x1, x2, sds)
+    assert np.max(np.abs(got - want) / np.abs(want)) < 1e-14  # north_star: 1e-10; only exp() can differ (<= 2 ulp)
+    assert gpirt_b200.K([0.0], [0.0], sds)[0, 0] == 1.0 + 9.0
+
+
+@pytest.mark.parametrize("kernel", ["Matern", "RBF"])
+def test_K_time(kernel):
+    ts = np.arange(6.0)
+    got = gpirt_b200.K_time(ts, ts, 1.3, 2.5, [0.2, 0.7], kernel)
+    want = orc.K_time(ts, ts, 1.3, 2.5, [0.2, 0.7], kernel)
+    assert np.max(np.abs(got - want) / np.abs(want)) < 1e-14
+
+
+@pytest.mark.parametrize("n", [5, 64, 100, 333, 1001])
+def test_chol_well_conditioned_elementwise(n):
+    rng = np.random.default_rng(n)
+    x = np.sort(rng.uniform(-3, 3, n))
+    A = orc.K(x, x, [0.5, 0.3, 0.0]) + np.eye(n) * 0.5  # distinct theta, large jitter: kappa ~ 1e3
+    L = gpirt_b200.chol(A)
+    Lo, info = orc.chol(A)
+    assert info == 0
+    assert np.allclose(np.triu(L, 1), 0.0)
+    assert np.max(np.abs(L - Lo)) / np.max(np.abs(Lo)) < 1e-10  # north_star tolerance on a well-conditioned fixture
+    assert np.max(np.abs(L @ L.T - A)) / np.max(np.abs(A)) < 1e-14
+
+
+def test_chol_not_positive_definite_is_an_error():
+    A = np.eye(70)
+    A[65, 65] = -1.0
+    with pytest.raises(gpirt_b200.GpirtError) as e:
+        gpirt_b200.chol(A)
+    assert e.value.code == 4 and "66" in str(e.value)
+
+
+@pytest.mark.parametrize("n,on_grid", [(100, False), (700, True)])
+def test_cholesky_cache_default_priors(n, on_grid):
+    """K with the reference's default sds=3 is ill-conditioned (kappa ~ 1e10, duplicated theta when on the grid):
+    criterion = backward error <= 1e-14 and norm-wise forward error vs a long-double factor <= 1e-8."""
+    P = make_problem(n, 8, 5, seed=3, on_grid=on_grid)
+    S, O = _pair(P)
+    S.set_state(theta=P["theta0"])
+    S.update_cholesky_cache()
+    L = S.get_L()
+    Kmat = orc.K(P["theta0"], P["theta0"], [3.0, 3.0, 3.0]) + 1e-6 * np.eye(n)
+    assert np.max(np.abs(L @ L.T - Kmat)) / np.max(np.abs(Kmat)) < 1e-14
+    Lld, info = orc.chol(Kmat, long_double=True)
+    assert info == 0
+    assert np.linalg.norm(L - Lld) / np.linalg.norm(Lld) < 1e-8
+
+
+def test_double_solve():
+    rng = np.random.default_rng(5)
+    n = 300
+    x = np.sort(rng.uniform(-3, 3, n))
+    A = orc.K(x, x, [0.5, 0.3, 0.0]) + np.eye(n) * 0.5
+    L, _ = orc.chol(A)
+    X = rng.standard_normal((n, 7))
+    got = gpirt_b200.double_solve(L, X)
+    want = np.stack([orc.double_solve(L, X[:, k]) for k in range(7)], axis=1)
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-10
+
+
+@pytest.mark.parametrize("n,m,C", [(100, 37, 2), (257, 50, 5), (64, 9, 7)])
+def test_ll_bar_matches_oracle(n, m, C):
+    P = make_problem(n, m, C, seed=11)
+    S, O = _pair(P)
+    f0 = np.asfortranarray(P["rng"].standard_normal((n, m)))
+    for X in (S, O):
+        X.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, **({"thresholds": P["thr0"]} if X is S else {"thr": P["thr0"]}))
+    O.compute_mu()
+    per, tot = S.ll_bar()
+    want = O.item_ll()
+    assert np.max(np.abs(per - want) / np.abs(want)) < 1e-10  # north_star tolerance
+    assert abs(tot - O.total_ll()) / abs(tot) < 1e-12
+
+
+def _set_both(S, O, theta, beta, f, thr, fstar=None):
+    S.set_state(theta=theta, beta=beta, f=f, thresholds=thr, fstar=fstar)
+    O.set_state(theta=theta, beta=beta, f=f, thr=thr, fstar=fstar)
+    O.compute_mu()
+
+
+@pytest.mark.parametrize("n,m,C", [(100, 40, 2), (300, 33, 5)])
+def test_draw_f_same_states_given_same_nu_and_uniforms(n, m, C):
+    P = make_problem(n, m, C, seed=21)
+    rng = P["rng"]
+    S, O = _pair(P)
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    _set_both(S, O, P["theta0"], P["beta0"], f0, P["thr0"])
+    nu = np.asfortranarray(rng.standard_normal((n, m)) * 2.0)
+    u = uniform_streams(rng, m)
+    S.draw_f(u=u, nu=nu)
+    O.draw_f(orc.supplied(u=u), nu=nu)
+    ev_o, mg_o, over = O.diag("f")
+    ev_s, mg_s = S.diag("f")
+    assert not over
+    assert np.array_equal(ev_s, ev_o), "ESS accepted after a different number of proposals"
+    assert mg_o.min() > 1e-9  # the decisions were not near-ties
+    got, want = S.get_state()["f"], O.state()["f"]
+    assert np.max(np.abs(got - want)) < 1e-12  # same accepted angle: only cos/sin rounding differs
+
+
+def test_draw_f_with_supplied_z_uses_L():
+    n, m, C = 200, 16, 5
+    P = make_problem(n, m, C, seed=22)
+    rng = P["rng"]
+    S, O = _pair(P)
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    theta = np.sort(rng.uniform(-2, 2, n))
+    sds = np.full((3, m), 0.3, order="F")
+    S.set_priors(sds, None)
+    O = orc.Sampler(P["y"], C, sds, P["theta_prior_sds"])
+    _set_both(S, O, theta, P["beta0"], f0, P["thr0"])
+    z = np.asfortranarray(rng.standard_normal((n, m)))
+    u = uniform_streams(rng, m)
+    S.update_cholesky_cache()
+    assert O.update_cholesky() == 0
+    S.draw_f(z=z, u=u)
+    O.draw_f(orc.supplied(z=z, u=u))
+    assert np.array_equal(S.diag("f")[0], O.diag("f")[0])
+    got, want = S.get_state()["f"], O.state()["f"]
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-8  # nu = L z inherits the kappa-limited error of L
+
+
+@pytest.mark.parametrize("n,m,C", [(150, 30, 2), (120, 45, 5)])
+def test_draw_theta_same_states(n, m, C):
+    P = make_problem(n, m, C, seed=31, on_grid=True)
+    rng = P["rng"]
+    S, O = _pair(P)
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    fstar = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+    _set_both(S, O, P["theta0"], P["beta0"], f0, P["thr0"], fstar)
+    z = np.asfortranarray(rng.standard_normal((1, n)))
+    u = uniform_streams(rng, n)
+    S.draw_theta(z=z, u=u)
+    O.draw_theta(orc.supplied(z=z, u=u))
+    assert np.array_equal(S.diag("theta")[0], O.diag("theta")[0])
+    assert O.diag("theta")[1].min() > 1e-9
+    assert np.array_equal(S.get_state()["theta"], O.state()["theta"])  # grid values: bit-exact
+    S.gather_f()
+    O.gather_f()
+    assert np.array_equal(S.get_state()["f"], O.state()["f"])  # pure indexing: bit-exact
+
+
+@pytest.mark.parametrize("n,m,C", [(150, 30, 2), (120, 45, 5)])
+def test_draw_beta_and_threshold_same_states(n, m, C):
+    P = make_problem(n, m, C, seed=41, on_grid=True)
+    P["y"][:, 3] = np.nan  # an item nobody answered: beta kept, no draws (src/draw-beta.cpp:73,97-99)
+    rng = P["rng"]
+    S, O = _pair(P)
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    _set_both(S, O, P["theta0"], P["beta0"], f0, P["thr0"])
+    z = np.asfortranarray(rng.standard_normal((3, m)))
+    u = uniform_streams(rng, m)
+    S.draw_beta(z=z, u=u)
+    O.draw_beta(orc.supplied(z=z, u=u))
+    ev_s, ev_o = S.diag("beta")[0], O.diag("beta")[0]
+    assert np.array_equal(ev_s, ev_o) and ev_s[3] == 0
+    got, want = S.get_state()["beta"], O.state()["beta"]
+    assert np.array_equal(got[:, 3], P["beta0"][:, 3])
+    assert np.max(np.abs(got - want)) < 1e-12
+    O.compute_mu()
+    z = np.asfortranarray(rng.standard_normal((C - 1, m)))
+    u = uniform_streams(rng, m)
+    S.draw_threshold(z=z, u=u)
+    O.draw_threshold(orc.supplied(z=z, u=u))
+    assert np.array_equal(S.diag("thr")[0], O.diag("thr")[0])
+    got, want = S.get_state()["thresholds"], O.state()["thr"]
+    assert np.all(np.isneginf(got[:, 0])) and np.all(np.isposinf(got[:, C]))  # bookkeeping of the open ends: exact
+    assert np.max(np.abs(got[:, 1:C] - want[:, 1:C])) < 1e-12
+
+
+def test_draw_fstar_against_oracle_well_conditioned():
+    n, m, C = 150, 12, 5
+    P = make_problem(n, m, C, seed=51)
+    rng = P["rng"]
+    sds = np.full((3, m), 0.3, order="F")
+    S = gpirt_b200.Sampler(n, m, C)
+    S.set_data(P["y"])
+    S.set_priors(sds, P["theta_prior_sds"])
+    O = orc.Sampler(P["y"], C, sds, P["theta_prior_sds"])
+    theta = np.sort(rng.uniform(-2.5, 2.5, n))
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    _set_both(S, O, theta, P["beta0"], f0, P["thr0"])
+    S.update_cholesky_cache()
+    assert O.update_cholesky() == 0
+    z = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+    S.draw_fstar(z=z)
+    assert O.draw_fstar(orc.supplied(z=z)) == 0
+    got, want = S.get_state(fstar=True)["fstar"], O.state()["fstar"]
+    # K^-1 f is kappa-limited: two correct fp64 codes agree to ~kappa*eps, not 1e-10
+    assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-6
+
+
+def test_supplied_stream_overrun_is_reported():
+    n, m, C = 64, 8, 2
+    P = make_problem(n, m, C, seed=61)
+    S, _ = _pair(P)
+    S.set_state(theta=P["theta0"], beta=P["beta0"], f=np.zeros((n, m)), thresholds=P["thr0"])
+    u = np.full((2, m), 1e-300, order="F")  # slice height log(1e-300): first proposal is always accepted
+    S.draw_f(u=u, nu=np.zeros((n, m)))
+    u = np.asfortranarray(np.vstack([np.full((1, m), 1.0 - 1e-16), np.full((1, m), 0.5)]))
+    with pytest.raises(gpirt_b200.GpirtError) as e:  # u ~ 1: nothing but the current state is acceptable, stream of 2 runs dry
+        S.draw_f(u=u, nu=np.ones((n, m)))
+    assert e.value.code == 7
