@@ -1,0 +1,288 @@
+#!/usr/bin/env python
+"""bench.py — MCMC sweeps/sec of the gpirt hot path on B200 (BASELINE.json metric), one JSON line on stdout.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            our CUDA path (N>1: launched under torchrun)
+  python bench.py --impl reference [--gpus N] --steps K --warmup W   the reference algorithm on the host cores
+
+A step is one full sweep (draw_f, draw_fstar, draw_theta, f<-f* gather, draw_beta, K+Cholesky, draw_threshold,
+total log-likelihood: src/gpirtMCMC.cpp:267-331 of the reference) over synthetic data of the named shape.
+Workload: BASELINE config C3 — synthetic ordinal n=2000 respondents x 5000 items per GPU, C=5, 5% missing
+(weak scaling over items: N GPUs run n=2000 x m=5000*N, item-sharded; the metric counts C3-sized item blocks,
+i.e. value = N * sweeps/s, which at N=1 is plain sweeps/s of C3).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_RESP, M_PER_GPU, C_CAT = 2000, 5000, 5
+FP64_DMMA_PEAK_TFLOPS = 37.1  # measured on this pool's B200, profiles/r01_microbench_fp64.txt (MEASURED_PEAKS.json has no fp64 entry)
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def synth(n, m, C, seed):
+    from tests.problems import make_problem
+
+    return make_problem(n, m, C, seed=seed, missing=0.05, on_grid=False, dtype="i8")
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def cpu_reference_sweeps(n, m_full, C, seed, steps, warmup, m_sub):
+    """The reference algorithm (oracle port, faithful mode: second Cholesky, per-respondent table copies, per-item
+    gemv/trsv — SURVEY.md A.7) on all host cores, on a BOUNDED sample: the first m_sub items of the workload.
+    The oracle clocks the work shared by all items (Cholesky of K, k* solves, K_post) separately from the per-item /
+    per-respondent work, which is linear in m; the full-size rate is 1/(t_shared + t_items * m_full/m_sub)."""
+    from oracle import orc
+
+    cores = os.cpu_count() or 1
+    P = synth(n, m_sub, C, seed)
+
+    mm = m_sub
+    y = np.where(P["y"][:, :mm] == 0, np.nan, P["y"][:, :mm].astype(np.float64))
+    O = orc.Sampler(y, C, P["beta_prior_sds"][:, :mm], P["theta_prior_sds"], faithful=1)
+    O.set_state(theta=P["theta0"], beta=P["beta0"][:, :mm], thr=P["thr0"][:mm], f=np.zeros((n, mm)))
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.run_mt(0, warmup, store=False)
+    O.times(reset=True)
+    t0 = time.perf_counter()
+    info, _, _ = O.run_mt(warmup, steps, store=False)
+    t1 = (time.perf_counter() - t0) / steps
+    assert info == 0
+    fixed, items = (t / steps for t in O.times())
+    t_full = fixed + items * m_full / m_sub
+    return dict(value=1.0 / t_full, t_step_sample=t1, threads=O.num_threads(), cores=cores,
+                sample=f"first {m_sub} of {m_full} items, all n={n} respondents, {steps} timed sweep(s) of the faithful port on {O.num_threads()} threads: "
+                       f"{t1:.2f} s/sweep = {fixed:.2f} s shared by all items (2x chol(K), k* solves, chol(K_post)) + {items:.2f} s per-item/per-respondent "
+                       f"work, which is linear in m; value = 1/({fixed:.2f} + {items:.2f}*{m_full}/{m_sub}) (extrapolated)")
+
+
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    m_full = M_PER_GPU * args.gpus
+    r = cpu_reference_sweeps(N_RESP, m_full, C_CAT, 20261104 + 3, args.steps, args.warmup, args.ref_items)
+    line = {"impl": "reference", "metric": "mcmc_sweeps_per_sec_c3_blocks", "value": r["value"] * args.gpus, "unit": "sweeps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / r["value"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C3 synthetic ordinal n={N_RESP} x m={m_full} ({M_PER_GPU} items per GPU), C={C_CAT}, 5% missing",
+                       "n": N_RESP, "m": m_full, "C": C_CAT},
+            "cpu_baseline": {"value": r["value"] * args.gpus, "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]},
+            "e2e": {"value": r["value"] * args.gpus, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+def ours(args):
+    import torch
+
+    import gpirt_b200
+    from gpirt_b200 import _lib
+    from gpirt_b200.distributed import ShardedSampler
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched under torch.distributed.run with N ranks")
+    torch.cuda.set_device(local)
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    n, m, C = N_RESP, M_PER_GPU * world, C_CAT
+    P = synth(n, m, C, 20261104 + 3)
+    common = dict(seed=20261104, chain=0)
+    if world == 1:
+        S = gpirt_b200.Sampler(n, m, C, device=local, **common)
+        S.set_stream(torch.cuda.current_stream().cuda_stream)
+        sweep = S.sweep
+    else:
+        S = ShardedSampler(n, m, C, rank=rank, world=world, device=local, **common)
+        sweep = S.sweep
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+    S.init_draw(draw_beta=False, draw_f=True)  # f0_j = L z_j as the reference initialises it (src/gpirtMCMC.cpp:158-162)
+    L = _lib.lib()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    sweep(args.warmup)
+    S.sync()
+    barrier()
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+    launches0 = L.gpirt_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    sweep(args.steps)
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = L.gpirt_launch_count() - launches0
+    clk = clocks.stop() if rank == 0 else None
+    S.sync()
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ll = S.total_ll()
+    ms_per_step = ms / args.steps
+    value = world * 1e3 / ms_per_step  # C3-sized item blocks swept per second
+
+    # ---- per-kernel-group device times (CUDA events inside the library), separate pass ----
+    S.profile(True)
+    S.profile_reset()
+    prof_sweeps = 3
+    sweep(prof_sweeps)
+    sections = S.profile_read()
+    S.profile(False)
+    per_sweep = {k: v[0] / prof_sweeps for k, v in sections.items()}
+    launches_per = {k: v[1] / prof_sweeps for k, v in sections.items()}
+    ev = {b: S.diag(b)[0] for b in ("f", "theta", "beta", "thr")}
+    E = {b: float(np.mean(ev[b][ev[b] > 0])) if np.any(ev[b] > 0) else 0.0 for b in ev}
+    m_loc, N = M_PER_GPU, 1001
+    nm = n * m_loc
+    algo = {  # algorithmic bytes (HBM-bound groups) or flops (FP64-tensor groups) per sweep, SURVEY.md 8(d)
+        "ess_f": ("hbm", 25.0 * nm), "ess_theta": ("hbm", E["theta"] * (n / world) * m * 9.0), "ess_beta": ("hbm", 9.0 * nm),
+        "ess_thr": ("hbm", 9.0 * nm), "item_ll": ("hbm", 9.0 * nm + 8.0 * (n + 3 * m_loc + (C + 1) * m_loc)), "gather_f": ("hbm", 16.0 * nm),
+        "gen_Z": ("hbm", 8.0 * (n + N) * m_loc), "add_mustar": ("hbm", 16.0 * N * m_loc), "K_build": ("hbm", 8.0 * (n * n + n * N + N * N)),
+        "gemm_LZ": ("tensor", 1.0 * n * n * m_loc), "gemm_FtW": ("tensor", 2.0 * N * n * m_loc), "gemm_ZLpost": ("tensor", 1.0 * N * N * m_loc),
+        "gemm_Kpost": ("tensor", 1.0 * n * N * N), "chol_K": ("tensor", n ** 3 / 3.0), "chol_Kpost": ("tensor", N ** 3 / 3.0),
+        "trsm_kstar": ("tensor", 1.0 * n * n * N), "trsm_W": ("tensor", 1.0 * n * n * N),
+    }
+    peaks, peak_src = measured_peaks()
+    kernels = []
+    for k, t in sorted(per_sweep.items(), key=lambda kv: -kv[1]):
+        bound, amount = algo.get(k, ("hbm", 0.0))
+        ach = amount / (t * 1e-3) / (1e9 if bound == "hbm" else 1e12) if t > 0 else 0.0
+        peak = peaks["hbm_gbs"] if bound == "hbm" else FP64_DMMA_PEAK_TFLOPS
+        kernels.append({"group": k, "ms_per_sweep": round(t, 4), "launches_per_sweep": launches_per[k], "bound": bound,
+                        "achieved": round(ach, 2), "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": round(ach / peak, 4)})
+    top = kernels[0]
+    roofline = {"kernel": top["group"], "bound": top["bound"], "achieved": top["achieved"],
+                "peak": peaks["hbm_gbs"] if top["bound"] == "hbm" else FP64_DMMA_PEAK_TFLOPS, "unit": top["unit"], "frac": top["frac"],
+                "traffic": None, "peak_source": f"{peak_src} MEASURED_PEAKS.json hbm_gbs" if top["bound"] == "hbm" else
+                "fp64 DMMA.8x8x4 issue-rate microbenchmark on this pool (profiles/r01_microbench_fp64.txt); MEASURED_PEAKS.json has no fp64 figure",
+                "share_of_sweep": round(top["ms_per_sweep"] / sum(per_sweep.values()), 3),
+                "note": "ESS groups are fp64-ALU bound (2 Phi + 1 log per cell), not HBM bound: algorithmic bytes / time stays far below the copy peak by construction"}
+    # log-likelihood GB/s (BASELINE metric, second half): the full-matrix ll_bar pass timed alone
+    ll_ms = per_sweep.get("item_ll", 0.0)
+    loglik_gbs = algo["item_ll"][1] / (ll_ms * 1e-3) / 1e9 if ll_ms > 0 else None
+
+    line = {"metric": "mcmc_sweeps_per_sec_c3_blocks", "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": f"C3 synthetic ordinal n={n} x m={m} ({M_PER_GPU} items per GPU), C={C}, 5% missing", "n": n, "m": m, "C": C,
+                       "l2": "working set per sweep (f, nu, Z, f*, L, W: >350 MB) exceeds the 126 MB L2; no explicit flush",
+                       "parallelism": f"items sharded over {world} GPU(s), theta step sharded over respondents"},
+            "gpu_launches": int(launches), "ll_after": ll, "mean_evals": E, "kernels": kernels, "roofline": roofline,
+            "loglik_gbs": loglik_gbs}
+    if rank == 0:
+        line["clocks"] = clk
+
+    # ---- e2e: the reference-facing call with HOST buffers (gpirtMCMC -> gpirt_mcmc C-ABI), copies inside the timed region ----
+    if world == 1:
+        S.close()
+        y_pin = torch.empty((m, n), dtype=torch.float64, pin_memory=True)  # column-major n x m in pinned host memory
+        y_host = y_pin.numpy().T
+        y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
+        k = args.steps
+        t0 = time.perf_counter()
+        res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=1, beta_prior_sds=P["beta_prior_sds"],
+                                   theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104,
+                                   beta_init=P["beta0"], device=local)
+        dt = time.perf_counter() - t0
+        assert np.all(np.isfinite(res[0]["ll"]))
+        h2d = (y_host.nbytes + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
+        d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
+        line["e2e"] = {"value": k / dt, "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock incl. handle creation, fp64 y upload from pinned memory, per-sweep D2H of theta/beta/threshold/ll draws"}
+        # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
+        if not args.no_cpu_baseline:
+            r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)
+            line["cpu_baseline"] = {"value": r["value"], "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
+    else:
+        line["e2e"] = None
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--ref-items", type=int, default=40, help="items in the CPU baseline's bounded sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        ours(args)
+
+
+if __name__ == "__main__":
+    main()

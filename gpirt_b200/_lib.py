@@ -66,7 +66,8 @@ SYMBOLS = [
     "gpirt_set_iter", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_exchange_buffer",
-    "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_recover_fstar",
+    "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
+    "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count",
 ]
 
 _lib = None
@@ -81,6 +82,7 @@ def lib():
                               "(gpirt_b200 has no CPU or pure-Python path)")
         L = C.CDLL(LIB_PATH)
         L.gpirt_last_error.restype = C.c_char_p
+        L.gpirt_launch_count.restype = C.c_longlong
         for s in SYMBOLS:
             getattr(L, s)  # AttributeError if the build is stale
         _lib = L

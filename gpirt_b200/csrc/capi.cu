@@ -38,6 +38,23 @@ static int select_device(int device) {
     return GPIRT_OK;
 }
 
+// SEC(h, "name", launch): times `launch` with CUDA events when profiling is on (never in the timed bench pass)
+struct SecScope {
+    gpirt_sampler* h; bool on; gpirt_sampler::Pending p;
+    SecScope(gpirt_sampler* h_, const char* name) : h(h_), on(h_->profiling) {
+        if (!on) return;
+        p.name = name;
+        cudaEventCreate(&p.a); cudaEventCreate(&p.b);
+        cudaEventRecord(p.a, h->stream);
+    }
+    ~SecScope() {
+        if (!on) return;
+        cudaEventRecord(p.b, h->stream);
+        h->pending.push_back(p);
+    }
+};
+#define SEC(h, name, call) do { SecScope sec_(h, name); call; } while (0)
+
 template <class T>
 static int dalloc(T** p, size_t count) {
     *p = nullptr;
@@ -152,6 +169,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         TRY(dalloc(&h->margin[b], units));
     }
     k_fill_grid<<<(NGRID + 255) / 256, 256, 0, h->stream>>>(h->tstar);
+    ++g_kernel_launches;
     CU(cudaGetLastError());
     CU(cudaDeviceSynchronize());  // the zero-fills above ran on the legacy stream
     return GPIRT_OK;
@@ -427,8 +445,8 @@ static int need_data(gpirt_sampler* h) {
 }
 
 static int do_update_cholesky(gpirt_sampler* h) {  // src/cholesky-cache.cpp:20-24
-    CU(build_K(h->stream, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6));
-    CU(chol_lower_blocked(h->stream, h->L, h->ldn, h->n, &h->flags->chol_info));
+    SEC(h, "K_build", CU(build_K(h->stream, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
+    SEC(h, "chol_K", CU(chol_lower_blocked(h->stream, h->L, h->ldn, h->n, &h->flags->chol_info)));
     h->chol_valid = true;
     return GPIRT_OK;
 }
@@ -451,18 +469,18 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
                 CU(cudaMemcpy2DAsync(h->zbuf, (size_t)h->ldz * 8, s->z + (size_t)h->item0 * s->z_stride, (size_t)s->z_stride * 8,
                                      (size_t)h->n * 8, h->m_local, cudaMemcpyHostToDevice, st));
             } else {
-                CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_F_Z, h->item0));
+                SEC(h, "gen_Z", CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_F_Z, h->item0)));
             }
             // nu = L * Z for every local item at once (rmvnorm_threadsafe per item, src/mvnormal.h:17-24)
             GemmArgs g{};
             g.M = h->n; g.N = h->m_local; g.K = h->n;
             g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->nu; g.ldc = h->ldn;
             g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
-            CU(gemm_f64(st, false, false, g));
+            SEC(h, "gemm_LZ", CU(gemm_f64(st, false, false, g)));
         }
     }
     v.evals = h->evals[GPIRT_BLOCK_F]; v.margin = h->margin[GPIRT_BLOCK_F];
-    CU(launch_ess_items(st, IB_F, v));
+    SEC(h, "ess_f", CU(launch_ess_items(st, IB_F, v)));
     return GPIRT_OK;
 }
 
@@ -471,42 +489,43 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     cudaStream_t st = h->stream;
     const int n = h->n, N = NGRID;
     // shared over items: k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I, L_post = chol(K_post)
-    CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0));
-    CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N));
+    SEC(h, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
+    SEC(h, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
     CU(build_K(st, h->tstar, N, h->tstar, N, h->sds0, h->Kpost, h->ldN, 0.0));
     {
         GemmArgs g{};
         g.M = N; g.N = N; g.K = n; g.A = h->W; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->Kpost; g.ldc = h->ldN;
         g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
-        CU(gemm_f64(st, true, false, g));
+        SEC(h, "gemm_Kpost", CU(gemm_f64(st, true, false, g)));
     }
     k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
+    ++g_kernel_launches;
     CU(cudaGetLastError());
-    CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info));
+    SEC(h, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info)));
     // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
-    CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N));
+    SEC(h, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
     if (h->m_local == 0) return GPIRT_OK;
     double* chunk = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk;
     {
         GemmArgs g{};
         g.M = h->m_local; g.N = N; g.K = n; g.A = h->f; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = chunk; g.ldc = h->ld_chunk;
         g.alpha = 1.0; g.beta = 0.0;
-        CU(gemm_f64(st, true, false, g));
+        SEC(h, "gemm_FtW", CU(gemm_f64(st, true, false, g)));
     }
     if (s && s->z) {
         if (s->z_stride < N) return fail(GPIRT_ERR_SHAPE, "draw_fstar: z_stride %lld < %d", (long long)s->z_stride, N);
         CU(cudaMemcpy2DAsync(h->zbuf, (size_t)h->ldz * 8, s->z + (size_t)h->item0 * s->z_stride, (size_t)s->z_stride * 8, (size_t)N * 8,
                              h->m_local, cudaMemcpyHostToDevice, st));
     } else {
-        CU(launch_gen_normals(st, h->zbuf, h->ldz, N, h->m_local, h->key(), ST_FSTAR_Z, h->item0));
+        SEC(h, "gen_Z", CU(launch_gen_normals(st, h->zbuf, h->ldz, N, h->m_local, h->key(), ST_FSTAR_Z, h->item0)));
     }
     {   // + (L_post Z*)^T : op(A) = Z*^T, op(B) = L_post^T (upper triangular)
         GemmArgs g{};
         g.M = h->m_local; g.N = N; g.K = N; g.A = h->zbuf; g.lda = h->ldz; g.B = h->Kpost; g.ldb = h->ldN; g.C = chunk; g.ldc = h->ld_chunk;
         g.alpha = 1.0; g.beta = 1.0; g.b_upper = 1;
-        CU(gemm_f64(st, true, true, g));
+        SEC(h, "gemm_ZLpost", CU(gemm_f64(st, true, true, g)));
     }
-    CU(launch_add_mustar(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta));
+    SEC(h, "add_mustar", CU(launch_add_mustar(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta)));
     return GPIRT_OK;
 }
 
@@ -518,7 +537,7 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
     v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os; v.key = h->key();
     v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
     TRY(stage_streams(h, s, h->n, 1, &v.z, &v.z_stride, &v.us));
-    CU(launch_ess_theta(h->stream, v));
+    SEC(h, "ess_theta", CU(launch_ess_theta(h->stream, v)));
     return GPIRT_OK;
 }
 
@@ -530,7 +549,7 @@ static int commit_theta(gpirt_sampler* h) {  // theta.swap(theta_new), src/gpirt
 
 static int do_gather_f(gpirt_sampler* h) {
     if (h->m_local == 0) return GPIRT_OK;
-    CU(launch_gather_f(h->stream, h->theta, h->n, h->fstar + (size_t)h->rank * NGRID * h->ld_chunk, h->ld_chunk, h->m_local, h->f, h->ldn));
+    SEC(h, "gather_f", CU(launch_gather_f(h->stream, h->theta, h->n, h->fstar + (size_t)h->rank * NGRID * h->ld_chunk, h->ld_chunk, h->m_local, h->f, h->ldn)));
     return GPIRT_OK;
 }
 
@@ -540,13 +559,13 @@ static int do_small_ess(gpirt_sampler* h, int which, const gpirt_streams* s) {
     const size_t nz = which == IB_BETA ? 3 : (size_t)(h->C - 1);
     TRY(stage_streams(h, s, h->m_total, nz, &v.z, &v.z_stride, &v.us));
     v.evals = h->evals[blk]; v.margin = h->margin[blk];
-    CU(launch_ess_items(h->stream, which, v));
+    SEC(h, which == IB_BETA ? "ess_beta" : "ess_thr", CU(launch_ess_items(h->stream, which, v)));
     return GPIRT_OK;
 }
 
 static int do_item_ll(gpirt_sampler* h) {
     ItemView v = item_view(h);
-    CU(launch_item_ll(h->stream, v));
+    SEC(h, "item_ll", CU(launch_item_ll(h->stream, v)));
     return GPIRT_OK;
 }
 
@@ -712,6 +731,7 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
         if (beta_prior_means) CU(cudaMemcpyAsync(d_means, beta_prior_means, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, st));
         else CU(cudaMemsetAsync(d_means, 0, 3 * (size_t)h->m_total * 8, st));
         k_init_beta<<<(h->m_total + 127) / 128, 128, 0, st>>>(h->beta, d_means, h->sds, h->m_total, h->key());
+        ++g_kernel_launches;
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(st));
         cudaFree(d_means);
@@ -729,3 +749,68 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
 }
 
 }  // extern "C"
+
+extern "C" {
+
+// Per-section device timing for bench.py's roofline block: CUDA events around each kernel group.
+int gpirt_profile_enable(gpirt_sampler* h, int on) {
+    CHECK_H(h);
+    h->profiling = on != 0;
+    return GPIRT_OK;
+}
+// Collects finished sections; writes up to `cap` entries "name\0" (32 bytes each) with total ms and launch counts.
+int gpirt_profile_read(gpirt_sampler* h, char* names, double* ms, int64_t* launches, int cap, int* count) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    for (auto& p : h->pending) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, p.a, p.b);
+        auto& s = h->sections[p.name];
+        s.first += t; s.second += 1;
+        cudaEventDestroy(p.a); cudaEventDestroy(p.b);
+    }
+    h->pending.clear();
+    int k = 0;
+    for (auto& kv : h->sections) {
+        if (k >= cap) break;
+        std::snprintf(names + 32 * k, 32, "%s", kv.first.c_str());
+        ms[k] = kv.second.first; launches[k] = kv.second.second;
+        ++k;
+    }
+    *count = k;
+    return GPIRT_OK;
+}
+int gpirt_profile_reset(gpirt_sampler* h) {
+    CHECK_H(h);
+    h->sections.clear();
+    return GPIRT_OK;
+}
+
+// Test hooks: the raw Philox streams the kernels consume, so tests can pin them bit-for-bit against the oracle's restatement.
+int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int count, double* out) {
+    CHECK_H(h);
+    RngKey key = h->key();
+    for (int k = 0; k < count; k += 2) {
+        double a, b;
+        philox_uniform2(key, stream, unit, (uint32_t)(k >> 1), a, b);
+        out[k] = a;
+        if (k + 1 < count) out[k + 1] = b;
+    }
+    return GPIRT_OK;
+}
+int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    double* d = nullptr;
+    CU(cudaMalloc((void**)&d, (size_t)rows * cols * 8));
+    CU(launch_gen_normals(h->stream, d, rows, rows, cols, h->key(), stream, unit0));
+    CU(cudaMemcpyAsync(out, d, (size_t)rows * cols * 8, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    cudaFree(d);
+    return GPIRT_OK;
+}
+
+}  // extern "C"
+
+extern "C" long long gpirt_launch_count(void) { return gpirt::g_kernel_launches; }

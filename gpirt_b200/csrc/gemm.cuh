@@ -19,6 +19,9 @@
 
 namespace gpirt {
 
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+extern long long g_kernel_launches;
+
 struct GemmArgs {
     int M, N, K;
     const double* A; int lda;

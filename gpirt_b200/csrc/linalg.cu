@@ -7,6 +7,8 @@
 
 namespace gpirt {
 
+long long g_kernel_launches = 0;
+
 // ------------------------------------------------------------------------------------------------
 // GEMM dispatch
 template <int BM, int BN, int BK, int WM, int WN, int STAGES, bool TA, bool TB>
@@ -21,6 +23,7 @@ static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
     }
     dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(g);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -63,6 +66,7 @@ cudaError_t build_K(cudaStream_t st, const double* x1, int n1, const double* x2,
                     double* out, int ld, double diag_add) {
     dim3 grid((n1 + 255) / 256, n2);
     k_build_K<<<grid, 256, 0, st>>>(x1, n1, x2, n2, sds_host3[0], sds_host3[1], sds_host3[2], out, ld, diag_add);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -95,6 +99,7 @@ cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double
                          double t0, double t1, int kernel, double* out, int ld) {
     dim3 grid((n1 + 255) / 256, n2);
     k_build_K_time<<<grid, 256, 0, st>>>(x1, n1, x2, n2, os, ls, t0, t1, kernel, out, ld);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -217,10 +222,12 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
         const int kb = (n - k0 < NB) ? n - k0 : NB;
         double* Akk = A + (size_t)k0 * ld + k0;
         k_potf2<<<1, 256, 0, st>>>(Akk, ld, kb, info_dev, k0);
+        ++g_kernel_launches;
         const int rows = n - k0 - kb;
         if (rows > 0) {
             double* A21 = Akk + kb;
             k_trsm_right_lt<<<(rows + 63) / 64, 64, 0, st>>>(A21, ld, rows, Akk);
+            ++g_kernel_launches;
             GemmArgs g{};
             g.M = rows; g.N = rows; g.K = kb;
             g.A = A21; g.lda = ld; g.B = A21; g.ldb = ld;
@@ -232,6 +239,7 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
     }
     dim3 grid((n + 255) / 256, n);
     k_zero_upper<<<grid, 256, 0, st>>>(A, ld, n);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -240,6 +248,7 @@ cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, do
     for (int k0 = 0; k0 < n; k0 += NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
         k_trsm_left<false><<<(nrhs + 63) / 64, 64, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
+        ++g_kernel_launches;
         const int rows = n - k0 - kb;
         if (rows > 0) {
             GemmArgs g{};
@@ -261,6 +270,7 @@ cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, 
     for (int k0 = last; k0 >= 0; k0 -= NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
         k_trsm_left<true><<<(nrhs + 63) / 64, 64, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
+        ++g_kernel_launches;
         if (k0 > 0) {
             // B[0:k0, :] -= L[k0:k0+kb, 0:k0]^T * X_k
             GemmArgs g{};

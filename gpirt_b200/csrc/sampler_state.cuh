@@ -18,7 +18,9 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <map>
 #include <string>
+#include <vector>
 
 #include "../../include/gpirt_b200.h"
 #include "linalg.cuh"
@@ -47,6 +49,12 @@ struct gpirt_sampler {
     double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     gpirt::DevFlags* flags = nullptr;
     double sds0[3] = {0, 0, 0};  // beta_prior_sds.col(0): the sds every K() call uses (src/cholesky-cache.cpp:21)
+
+    // optional per-section device timing (gpirt_profile_*): CUDA events around each kernel group
+    struct Pending { const char* name; cudaEvent_t a, b; };
+    bool profiling = false;
+    std::vector<Pending> pending;
+    std::map<std::string, std::pair<double, long>> sections;  // name -> (total ms, launches)
 
     // staging for supplied streams
     double *d_z = nullptr, *d_u = nullptr;

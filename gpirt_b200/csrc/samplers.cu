@@ -40,6 +40,7 @@ cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, i
     if (rows <= 0 || cols <= 0) return cudaSuccess;
     dim3 grid(((rows + 1) / 2 + 127) / 128, cols);
     k_gen_normals<<<grid, 128, 0, st>>>(out, ld, rows, cols, key, stream, unit0);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -181,6 +182,7 @@ cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v) {
     if (block == IB_F) k_ess_items<IB_F><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
     else if (block == IB_BETA) k_ess_items<IB_BETA><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
     else k_ess_items<IB_THR><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -211,6 +213,7 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_item_ll(ItemView v) {
 cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v) {
     if (v.m_local <= 0) return cudaSuccess;
     k_item_ll<<<(v.m_local + ITEM_WARPS - 1) / ITEM_WARPS, ITEM_WARPS * 32, 0, st>>>(v);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -298,6 +301,7 @@ __global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
 cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     if (v.n_local <= 0) return cudaSuccess;
     k_ess_theta<<<v.n_local, THETA_THREADS, 0, st>>>(v);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -322,6 +326,7 @@ cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const d
                             double* f, int ldn) {
     dim3 grid((n + 31) / 32, (m_local + 31) / 32), blk(32, 8);
     k_gather_f<<<grid, blk, 0, st>>>(theta, n, fstar_chunk, ld_chunk, m_local, f, ldn);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -338,6 +343,7 @@ __global__ void k_add_mustar(double* __restrict__ fstar, int ld_chunk, int m_loc
 cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta) {
     dim3 grid((m_local + 127) / 128, NGRID);
     k_add_mustar<<<grid, 128, 0, st>>>(fstar_chunk, ld_chunk, m_local, item0, beta, p_beta);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -356,6 +362,7 @@ __global__ void k_ordered_sum(const double* __restrict__ x, int n, double* out) 
 }
 cudaError_t launch_ordered_sum(cudaStream_t st, const double* x, int n, double* out) {
     k_ordered_sum<<<1, 256, 0, st>>>(x, n, out);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -377,6 +384,7 @@ __global__ void k_transpose(const double* __restrict__ in, int ld_in, int rows, 
 cudaError_t launch_transpose(cudaStream_t st, const double* in, int ld_in, int rows, int cols, double* out, int ld_out) {
     dim3 grid((rows + 31) / 32, (cols + 31) / 32), blk(32, 8);
     k_transpose<<<grid, blk, 0, st>>>(in, ld_in, rows, cols, out, ld_out);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -386,6 +394,7 @@ __global__ void k_clamp_theta(double* theta, int n) {
 }
 cudaError_t launch_clamp_theta(cudaStream_t st, double* theta, int n) {
     k_clamp_theta<<<(n + 255) / 256, 256, 0, st>>>(theta, n);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -404,6 +413,7 @@ __global__ void k_y_to_i8(const double* __restrict__ y, long long count, int C, 
 }
 cudaError_t launch_y_to_i8(cudaStream_t st, const double* y, long long count, int C, int8_t* out, DevFlags* flags) {
     k_y_to_i8<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(y, count, C, out, flags);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 
@@ -431,6 +441,7 @@ cudaError_t launch_y_layouts(cudaStream_t st, const int8_t* y_full, int n, int m
                              int resp0, int n_local, int8_t* y_rm, long long ldm) {
     dim3 grid((n + 31) / 32, (m_total + 31) / 32), blk(32, 8);
     k_y_layouts<<<grid, blk, 0, st>>>(y_full, n, m_total, item0, m_local, y_im, ldy, resp0, n_local, y_rm, ldm);
+    ++g_kernel_launches;
     return cudaGetLastError();
 }
 

@@ -7,6 +7,8 @@
 
 namespace gpirt {
 
+extern long long g_kernel_launches;  // defined in linalg.cu
+
 constexpr int NGRID = 1001;
 constexpr int MAX_C = 21;
 constexpr int ESS_MAX_PROPOSALS = 2000;  // the reference has no cap (src/draw-f.cpp:23); a NaN likelihood would spin forever

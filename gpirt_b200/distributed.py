@@ -1,0 +1,86 @@
+"""Item-sharded sweeps over several B200s: one process per GPU, torch.distributed (NCCL over NVLink/NVSwitch)
+for the exchanges, every kernel and buffer owned by the rank's gpirt_sampler handle.
+
+Given theta, the items are conditionally independent — the reference's `omp parallel for` over j
+(src/draw-f.cpp:68, src/draw-fstar.cpp:44, src/draw-beta.cpp:64, src/draw_threshold.cpp:210) — so rank r owns the
+contiguous item block [r*m_chunk, (r+1)*m_chunk). The theta step is independent over respondents but needs every
+item (src/draw-theta.cpp:123), so it is sharded by respondents and fed by one all-gather of the f* shards:
+
+    phase_items   draw_f, draw_fstar on the local items                     (no communication)
+    all_gather    f* chunks (8*1001*m bytes in total), beta, thresholds
+    phase_theta   theta ESS for the local respondents over the whole table
+    all_gather    theta (8*n bytes)
+    phase_close   f <- f* gather, draw_beta, K + Cholesky (replicated), draw_threshold, per-item ll
+    all_gather    beta, thresholds, per-item ll  (tiny)
+
+Random streams are keyed by GLOBAL item / respondent index, so a chain is bit-identical for any world size.
+"""
+import numpy as np
+
+from .sampler import Sampler
+
+
+def shard_plan(n, m, world):
+    """Partition used by the C-ABI (gpirt_create): equal ceil-sized chunks, the last one ragged."""
+    m_chunk, n_chunk = (m + world - 1) // world, (n + world - 1) // world
+    plan = []
+    for r in range(world):
+        i0, r0 = r * m_chunk, r * n_chunk
+        plan.append(dict(rank=r, item0=i0, m_local=max(0, min(m_chunk, m - i0)), resp0=r0, n_local=max(0, min(n_chunk, n - r0))))
+    return dict(m_chunk=m_chunk, n_chunk=n_chunk, ranks=plan)
+
+
+def all_gather_chunks(buf, rank, world, group=None):
+    """In-place all-gather of a flat tensor made of `world` equal chunks, chunk r owned by rank r."""
+    import torch.distributed as dist
+
+    chunk = buf.numel() // world
+    assert chunk * world == buf.numel()
+    if world == 1:
+        return
+    mine = buf[rank * chunk:(rank + 1) * chunk]
+    if buf.is_cuda:
+        dist.all_gather_into_tensor(buf, mine, group=group)
+    else:  # gloo (CPU tests of the host logic)
+        parts = [buf[r * chunk:(r + 1) * chunk] for r in range(world)]
+        dist.all_gather(parts, mine.clone(), group=group)
+
+
+class _DevBuf:
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 8,), "typestr": "<f8", "data": (ptr, False), "version": 2}
+
+
+class ShardedSampler:
+    """One rank's shard of a chain. Every rank passes the same full-size y / state arrays; the handle keeps its part."""
+
+    def __init__(self, n, m, Ccat, *, rank, world, device, group=None, **kw):
+        import torch
+
+        self.rank, self.world, self.group = rank, world, group
+        self.S = Sampler(n, m, Ccat, rank=rank, world=world, device=device, **kw)
+        self.S.set_stream(torch.cuda.current_stream(device).cuda_stream)
+        self._bufs = {}
+        for name in ("fstar", "beta", "thr", "theta", "item_ll"):
+            ptr, chunk_bytes = self.S.exchange_buffer(name)
+            self._bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * world), device=f"cuda:{device}")
+
+    def _gather(self, name):
+        all_gather_chunks(self._bufs[name], self.rank, self.world, self.group)
+
+    def sweep(self, k=1):
+        for _ in range(k):
+            self.S.phase_items()
+            self._gather("fstar")
+            self.S.phase_theta()
+            self._gather("theta")
+            self.S.phase_close()
+            self._gather("beta")
+            self._gather("thr")
+            self._gather("item_ll")
+
+    def total_ll(self):
+        return self.S.total_ll()
+
+    def __getattr__(self, name):  # set_data, set_priors, set_state, get_state, sync, ...
+        return getattr(self.S, name)

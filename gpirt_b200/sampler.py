@@ -230,3 +230,30 @@ class Sampler:
         ptr, nbytes = C.c_void_p(), C.c_int64()
         check(self._L.gpirt_exchange_buffer(self._h, _lib.XCHG[which], C.byref(ptr), C.byref(nbytes)))
         return ptr.value, nbytes.value
+
+    # ---- measurement / test hooks ----
+    def profile(self, on=True):
+        check(self._L.gpirt_profile_enable(self._h, int(on)))
+
+    def profile_reset(self):
+        check(self._L.gpirt_profile_reset(self._h))
+
+    def profile_read(self):
+        """{section: (total_ms, launches)} accumulated since the last reset"""
+        cap = 64
+        names = C.create_string_buffer(32 * cap)
+        ms = (C.c_double * cap)()
+        cnt = (C.c_int64 * cap)()
+        k = C.c_int()
+        check(self._L.gpirt_profile_read(self._h, names, ms, cnt, cap, C.byref(k)))
+        return {names.raw[32 * i:32 * i + 32].split(b"\0")[0].decode(): (ms[i], cnt[i]) for i in range(k.value)}
+
+    def debug_uniforms(self, stream, unit, count):
+        out = np.empty(count)
+        check(self._L.gpirt_debug_uniforms(self._h, C.c_uint32(stream), C.c_uint32(unit), int(count), _p(out)))
+        return out
+
+    def debug_normals(self, stream, unit0, rows, cols):
+        out = np.empty((rows, cols), order="F")
+        check(self._L.gpirt_debug_normals(self._h, C.c_uint32(stream), C.c_uint32(unit0), int(rows), int(cols), _p(out)))
+        return out

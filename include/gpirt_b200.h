@@ -144,6 +144,14 @@ typedef enum { GPIRT_XCHG_FSTAR = 0, GPIRT_XCHG_BETA = 1, GPIRT_XCHG_THR = 2, GP
 int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
 int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */
 
+/* ---- measurement and test hooks (no reference counterpart) ---- */
+int gpirt_profile_enable(gpirt_sampler* h, int on);          /* CUDA events around every kernel group of a sweep */
+int gpirt_profile_read(gpirt_sampler* h, char* names /* cap x 32 */, double* ms, int64_t* launches, int cap, int* count);
+int gpirt_profile_reset(gpirt_sampler* h);
+long long gpirt_launch_count(void);                          /* kernels launched by this library so far */
+int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int count, double* out);
+int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
+
 /* ---- the two Rcpp entry points ---- */
 typedef struct {
     /* inputs mirror gpirtMCMC()'s arguments (src/gpirtMCMC.cpp:25-38) */

@@ -289,6 +289,12 @@ class Sampler:
             keep.append(s)
         return lib().orc_sweep(self._h, arr)
 
+    def times(self, reset=True):
+        """(seconds in work shared by all items, seconds in per-item / per-respondent work) since the last reset"""
+        a, b = C.c_double(), C.c_double()
+        lib().orc_get_times(self._h, C.byref(a), C.byref(b), C.c_int(int(reset)))
+        return a.value, b.value
+
     def last_ll(self):
         return lib().orc_last_ll(self._h)
 

@@ -34,6 +34,7 @@ void orc_K_time(const double* x1, uint64_t n1, const double* x2, uint64_t n2, do
     K_time(x1, n1, x2, n2, os, ls, tsds, kernel, out);
 }
 int orc_chol(double* A, uint64_t n) { return chol_lower(A, n); }
+int orc_chol_blocked(double* A, uint64_t n) { return chol_lower_blocked(A, n); }
 int orc_chol_ld(double* A, uint64_t n) {  // long-double factorisation, rounded back to double
     std::vector<long double> B(A, A + n * n);
     int info = chol_lower(B.data(), n);
@@ -136,6 +137,11 @@ int orc_sweep(void* h, const orc_src* c /* N_BLOCKS entries */) {
     Src s[N_BLOCKS];
     for (int b = 0; b < N_BLOCKS; ++b) s[b] = to_src(S, &c[b], b);
     return S->sweep(s);
+}
+void orc_get_times(void* h, double* fixed, double* items, int reset) {
+    Sampler* S = static_cast<Sampler*>(h);
+    *fixed = S->t_fixed; *items = S->t_items;
+    if (reset) S->t_fixed = S->t_items = 0.0;
 }
 double orc_last_ll(void* h) { return static_cast<Sampler*>(h)->ll; }
 int orc_get_diag(void* h, int block, int32_t* evals, double* margin) {

@@ -13,6 +13,7 @@
 //                              error function", the algorithm R documents for pnorm; pinned in
 //                              tests/test_oracle_math.py against mpmath at 40 digits.
 #pragma once
+#include <algorithm>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
@@ -138,6 +139,67 @@ inline int chol_lower(T* A, size_t n) {
         for (size_t i = j + 1; i < n; ++i) cj[i] /= d;
         for (size_t i = 0; i < j; ++i) cj[i] = T(0);
     }
+    return 0;
+}
+
+// Blocked right-looking variant of the same factorisation (64-wide panels, OpenMP over the trailing
+// tiles): what the timed CPU baseline uses so that the O(n^3) part is cache-blocked and threaded, as
+// the LAPACK dpotrf behind arma::chol would be. Same arithmetic up to summation order.
+inline int chol_lower_blocked(double* A, size_t n) {
+    const size_t NB = 64;
+    if (n <= 2 * NB) return chol_lower(A, n);
+    for (size_t k0 = 0; k0 < n; k0 += NB) {
+        const size_t kb = std::min(NB, n - k0);
+        // diagonal block (unblocked, in place inside A)
+        for (size_t j = k0; j < k0 + kb; ++j) {
+            double* cj = A + j * n;
+            for (size_t k = k0; k < j; ++k) {
+                const double* ck = A + k * n;
+                const double ljk = ck[j];
+                for (size_t i = j; i < k0 + kb; ++i) cj[i] -= ck[i] * ljk;
+            }
+            double d = cj[j];
+            if (!(d > 0.0)) return int(j + 1);
+            d = std::sqrt(d);
+            cj[j] = d;
+            for (size_t i = j + 1; i < k0 + kb; ++i) cj[i] /= d;
+        }
+        const size_t r0 = k0 + kb;
+        if (r0 >= n) break;
+        // panel: rows r0.. of columns k0..k0+kb solve X L11^T = A21 (row chunks in parallel)
+#pragma omp parallel for schedule(static)
+        for (size_t rb = r0; rb < n; rb += NB) {
+            const size_t re = std::min(rb + NB, n);
+            for (size_t j = k0; j < k0 + kb; ++j) {
+                double* cj = A + j * n;
+                for (size_t k = k0; k < j; ++k) {
+                    const double* ck = A + k * n;
+                    const double ljk = ck[j];
+                    for (size_t i = rb; i < re; ++i) cj[i] -= ck[i] * ljk;
+                }
+                const double d = cj[j];
+                for (size_t i = rb; i < re; ++i) cj[i] /= d;
+            }
+        }
+        // trailing update A22 -= L21 L21^T, lower tiles only
+        const size_t nt = (n - r0 + NB - 1) / NB;
+#pragma omp parallel for schedule(dynamic)
+        for (size_t t = 0; t < nt * nt; ++t) {
+            const size_t bi = t % nt, bj = t / nt;
+            if (bi < bj) continue;
+            const size_t i0 = r0 + bi * NB, i1 = std::min(i0 + NB, n), j0 = r0 + bj * NB, j1 = std::min(j0 + NB, n);
+            for (size_t j = j0; j < j1; ++j) {
+                double* cj = A + j * n;
+                for (size_t k = k0; k < k0 + kb; ++k) {
+                    const double* ck = A + k * n;
+                    const double ljk = ck[j];
+                    for (size_t i = std::max(i0, j); i < i1; ++i) cj[i] -= ck[i] * ljk;
+                }
+            }
+        }
+    }
+    for (size_t j = 0; j < n; ++j)
+        for (size_t i = 0; i < j; ++i) A[i + j * n] = 0.0;
     return 0;
 }
 

@@ -1,11 +1,15 @@
 // TEST INFRASTRUCTURE — CPU oracle implementation (see orc_sampler.h for the reference citations).
 #include "orc_sampler.h"
 
+#include <chrono>
+
 #ifdef _OPENMP
 #include <omp.h>
 #endif
 
 namespace orc {
+
+static inline double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
 static inline int thread_id() {
 #ifdef _OPENMP
@@ -96,11 +100,13 @@ void Sampler::compute_mu() {
 int Sampler::update_cholesky() {
     K(theta.data(), n, theta.data(), n, sds.data() /* column 0: item 0's sds */, L.data());
     for (size_t i = 0; i < n; ++i) L[i + i * n] += 1e-6;
-    return chol_lower(L.data(), n);
+    return chol_lower_blocked(L.data(), n);
 }
 
 void Sampler::draw_f(const Src& s, const double* nu_supplied) {
+    double t0 = now();
     if (faithful) update_cholesky();  // src/draw-f.cpp:59 refactorises the same K
+    t_fixed += now() - t0; t0 = now();
     diag[B_F].reset(m);
     bool over = false;
 #pragma omp parallel for schedule(dynamic) reduction(|| : over)
@@ -131,10 +137,12 @@ void Sampler::draw_f(const Src& s, const double* nu_supplied) {
     }
     diag[B_F].overrun = over;
     f.swap(f_new);  // src/gpirtMCMC.cpp:274
+    t_items += now() - t0;
 }
 
 int Sampler::draw_fstar(const Src& s) {
     const size_t N = NGRID;
+    double t0 = now();
     std::vector<double> tstar(N);
     for (size_t k = 0; k < N; ++k) tstar[k] = grid_value(int(k));
     std::vector<double> kstar(n * N), tmp;
@@ -155,7 +163,8 @@ int Sampler::draw_fstar(const Src& s) {
         }
     }
     for (size_t k = 0; k < N; ++k) Lpost[k + k * N] += 1e-6;  // :35
-    int info = chol_lower(Lpost.data(), N);                    // :36
+    int info = chol_lower_blocked(Lpost.data(), N);            // :36
+    t_fixed += now() - t0; t0 = now();
     if (info) return info;
     diag[B_FSTAR].reset(m);
     bool over = false;
@@ -176,6 +185,7 @@ int Sampler::draw_fstar(const Src& s) {
         }
     }
     diag[B_FSTAR].overrun = over;
+    t_items += now() - t0;
     return 0;
 }
 
@@ -349,14 +359,18 @@ int Sampler::sweep(const Src srcs[N_BLOCKS]) {
     draw_f(srcs[B_F], nullptr);
     int info = draw_fstar(srcs[B_FSTAR]);
     if (info) return 1000000 + info;
+    double t0 = now();
     draw_theta(srcs[B_THETA]);
     gather_f();
     draw_beta(srcs[B_BETA]);
     compute_mu();
+    t_items += now() - t0; t0 = now();
     info = update_cholesky();
+    t_fixed += now() - t0; t0 = now();
     if (info) return info;
     draw_threshold(srcs[B_THR]);
     ll = total_ll();
+    t_items += now() - t0;
     return 0;
 }
 

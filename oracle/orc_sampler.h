@@ -65,6 +65,9 @@ struct Sampler {
     // state
     std::vector<double> theta, beta, f, thr, fstar, L;
     double ll = 0.0;
+    // wall-clock split of the sweeps run so far: work shared by all items (Cholesky of K, k*, K_post) vs per-item /
+    // per-respondent work, which is linear in m (used by bench.py to extrapolate a bounded sample to the full item count)
+    double t_fixed = 0.0, t_items = 0.0;
     // scratch
     std::vector<double> f_new, mu, mu_star, Lpost, W;
     std::vector<MtRng> mts;
