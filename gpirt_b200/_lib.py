@@ -67,7 +67,7 @@ SYMBOLS = [
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_exchange_buffer",
     "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
-    "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count",
+    "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit",
 ]
 
 _lib = None

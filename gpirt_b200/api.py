@@ -157,3 +157,11 @@ def threshold_to_delta(thresholds):
     out = np.empty(t.size - 2)
     check(_lib.lib().gpirt_threshold_to_delta(_p(t), t.size - 1, _p(out)))
     return out
+
+
+def debug_probit(x, device=0):
+    """(Phi(x), log(x)) as the likelihood kernels evaluate them on the device (test hook)."""
+    x = _F(x).ravel()
+    ph, lg = np.empty_like(x), np.empty_like(x)
+    check(_lib.lib().gpirt_debug_probit(device, _p(x), int(x.size), _p(ph), _p(lg)))
+    return ph, lg

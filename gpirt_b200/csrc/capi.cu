@@ -180,7 +180,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
-                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u};
+                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int b = 0; b < 5; ++b) {
@@ -537,6 +537,16 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
     v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os; v.key = h->key();
     v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
     TRY(stage_streams(h, s, h->n, 1, &v.z, &v.z_stride, &v.us));
+    // Every term the step can ask for is a function of (grid point, item, category) only: when the respondents of this
+    // rank would evaluate more terms than the table holds (about 8 evaluations each), build the table once instead.
+    const double table_cost = (double)NGRID * (1.4 * h->C - 1.0), direct_cost = (double)h->n_local * 8.0 * 2.4;
+    const size_t table_bytes = (size_t)NGRID * h->m_total * h->C * 8;
+    v.table = nullptr;
+    if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {
+        if (!h->theta_tab) CU(cudaMalloc((void**)&h->theta_tab, table_bytes));
+        SEC(h, "theta_table", CU(launch_theta_table(h->stream, v, h->theta_tab)));
+        v.table = h->theta_tab;
+    }
     SEC(h, "ess_theta", CU(launch_ess_theta(h->stream, v)));
     return GPIRT_OK;
 }
@@ -814,3 +824,24 @@ int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int r
 }  // extern "C"
 
 extern "C" long long gpirt_launch_count(void) { return gpirt::g_kernel_launches; }
+
+// Test hook: the device Phi / log the likelihood kernels use, evaluated element-wise (tests pin them against mpmath).
+__global__ void k_debug_probit(const double* x, int n, double* phi_out, double* log_out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    phi_out[i] = phi(x[i]);
+    log_out[i] = x[i] > 0.0 ? log_pos(x[i]) : 0.0;
+}
+extern "C" int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out) {
+    if (!x || !phi_out || !log_out || n < 1) return fail(GPIRT_ERR_INVALID, "debug_probit: bad arguments");
+    TRY(select_device(device));
+    double* d = nullptr;
+    CU(cudaMalloc((void**)&d, (size_t)3 * n * 8));
+    CU(cudaMemcpy(d, x, (size_t)n * 8, cudaMemcpyHostToDevice));
+    k_debug_probit<<<(n + 255) / 256, 256>>>(d, n, d + n, d + 2 * (size_t)n);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(phi_out, d + n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(log_out, d + 2 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return GPIRT_OK;
+}

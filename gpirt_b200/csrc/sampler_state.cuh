@@ -44,6 +44,7 @@ struct gpirt_sampler {
     double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;
     double *f = nullptr, *nu = nullptr, *zbuf = nullptr, *fstar = nullptr;
     double *L = nullptr, *W = nullptr, *Kpost = nullptr, *tstar = nullptr;
+    double* theta_tab = nullptr;  // [NGRID][m_total][C] per-sweep table of theta-step terms (allocated on first use)
     double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -1,5 +1,5 @@
 // The elliptical-slice samplers of the sweep as sm_100a kernels.
-//   item-parallel (one warp per item, warp-shuffle reductions, int8 responses):
+//   item-parallel (one CTA of 1-16 warps per item, warp-shuffle reductions, int8 responses):
 //     draw_f            src/draw-f.cpp:5-83            ess_sparse_threadsafe per item
 //     draw_beta         src/draw-beta.cpp:4-101
 //     draw_threshold    src/draw_threshold.cpp:99-169,206-228
@@ -45,42 +45,63 @@ cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, i
 }
 
 // ------------------------------------------------------------------------------------------------
-// One warp per item. MODE selects what the ellipse moves: the item's f column, its 3 mean
-// coefficients, or its C-1 threshold deltas.
-constexpr int ITEM_WARPS = 4;
+// One CTA of WARPS warps per item. MODE selects what the ellipse moves: the item's f column, its 3 mean
+// coefficients, or its C-1 threshold deltas. The shrink loop is a serial chain of likelihood passes, so the
+// time of the block is (slowest item's proposals) x (latency of one pass): a pass is spread over enough
+// threads that each one owns only a handful of cells, and cells are processed two at a time for ILP.
+// Reductions are fixed-order (lane-strided partials -> xor butterfly -> warp partials summed in warp order).
+template <int WARPS>
+__device__ __forceinline__ double block_sum(double v, double* s_part) {
+    v = warp_sum(v);
+    if (WARPS == 1) return v;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();  // previous readers of s_part are done
+    if (lane == 0) s_part[warp] = v;
+    __syncthreads();
+    double t = 0.0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) t += s_part[w];
+    return t;
+}
 
-template <int MODE>
-__global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
-    __shared__ double s_tau[ITEM_WARPS][MAX_C + 1];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = blockIdx.x * ITEM_WARPS + warp;
-    if (j >= v.m_local) return;
+template <int MODE, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
+    constexpr int T = WARPS * 32;
+    __shared__ double tau[MAX_C + 1];
+    __shared__ double s_part[WARPS];
+    const int tid = threadIdx.x;
+    const int j = blockIdx.x;
     const int J = v.item0 + j;
     const int C = v.C;
-    double* tau = s_tau[warp];
-    for (int c = lane; c <= C; c += 32) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
-    __syncwarp();
+    for (int c = tid; c <= C; c += T) tau[c] = v.thr[(size_t)J * (C + 1) + c];
+    __syncthreads();
 
     const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
     double* __restrict__ fj = v.f + (size_t)j * v.ldn;
     const double* __restrict__ nuj = (MODE == IB_F) ? v.nu + (size_t)j * v.ldn : nullptr;
     const double* __restrict__ theta = v.theta;
     const int n = v.n;
-    double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
-
-    // log-likelihood of the item at the point (ce, se) of the ellipse; ce=1, se=0 is the current state
+    const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
     double pb0 = b0, pb1 = b1, pb2 = b2;
+
+    // one cell's term at the point (ce, se) of the ellipse (current == true: the state itself)
+    auto term = [&](int i, double ce, double se, bool current) -> double {
+        const int y = yj[i];
+        if (y == 0) return 0.0;
+        double fi = fj[i];
+        if (MODE == IB_F && !current) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
+        const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
+        return cell_ll(g, tau[y - 1], tau[y], y == 1, y == C);
+    };
     auto loglik = [&](double ce, double se, bool current) -> double {
-        double acc = 0.0;
-        for (int i = lane; i < n; i += 32) {
-            const int y = yj[i];
-            if (y == 0) continue;
-            double fi = fj[i];
-            if (MODE == IB_F && !current) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
-            const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
-            acc += cell_ll(g, tau[y - 1], tau[y], y == 1, y == C);
+        double acc0 = 0.0, acc1 = 0.0;
+        int i = tid;
+        for (; i + T < n; i += 2 * T) {
+            acc0 += term(i, ce, se, current);
+            acc1 += term(i + T, ce, se, current);
         }
-        return warp_sum(acc);
+        if (i < n) acc0 += term(i, ce, se, current);
+        return block_sum<WARPS>(acc0 + acc1, s_part);
     };
 
     // prior draw for the low-dimensional blocks
@@ -89,15 +110,15 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
     if (MODE == IB_BETA) {
         // items without observations keep beta and draw nothing (src/draw-beta.cpp:73,97-99)
         int any = 0;
-        for (int i = lane; i < n; i += 32) any |= (yj[i] != 0);
-        if (!__any_sync(0xffffffffu, any)) {
-            if (lane == 0) { v.evals[J] = 0; v.margin[J] = CUDART_INF; }
+        for (int i = tid; i < n; i += T) any |= (yj[i] != 0);
+        if (!__syncthreads_or(any)) {
+            if (tid == 0) { v.evals[J] = 0; v.margin[J] = CUDART_INF; }
             return;
         }
 #pragma unroll
         for (int q = 0; q < 3; ++q) {
-            double z = v.z ? v.z[(size_t)J * v.z_stride + q] : philox_normal(v.key, ST_BETA_Z, J, q);
-            double sd = v.sds[3 * (size_t)J + q];
+            const double z = v.z ? v.z[(size_t)J * v.z_stride + q] : philox_normal(v.key, ST_BETA_Z, J, q);
+            const double sd = v.sds[3 * (size_t)J + q];
             nu_small[q] = __dmul_rn(sqrt(__dadd_rn(__dmul_rn(sd, sd), 1e-6)), z);  // chol(diag(sd^2+1e-6)) z, :82-86
         }
     }
@@ -107,12 +128,12 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
         for (int q = 1; q < C - 1; ++q) delta[q] = log(__dsub_rn(tau[q + 1], tau[q]));
         for (int q = 0; q < C - 1; ++q) nu_small[q] = v.z ? v.z[(size_t)J * v.z_stride + q] : philox_normal(v.key, ST_THR_Z, J, q);
         // the reference evaluates the current state through delta_to_threshold(delta) (:118)
-        __syncwarp();
-        if (lane == 0) {
+        __syncthreads();
+        if (tid == 0) {
             tau[1] = delta[0];
             for (int q = 1; q < C - 1; ++q) tau[q + 1] = __dadd_rn(tau[q], exp(delta[q]));
         }
-        __syncwarp();
+        __syncthreads();
     }
 
     const uint32_t ustream = MODE == IB_F ? ST_F_U : (MODE == IB_BETA ? ST_BETA_U : ST_THR_U);
@@ -137,16 +158,15 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
             pb2 = __dadd_rn(__dmul_rn(b2, ce), __dmul_rn(nu_small[2], se));
         }
         if (MODE == IB_THR) {
-            __syncwarp();
-            if (lane == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
+            __syncthreads();
+            if (tid == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
                 tau[1] = __dadd_rn(__dmul_rn(delta[0], ce), __dmul_rn(nu_small[0], se));
                 for (int q = 1; q < C - 1; ++q)
                     tau[q + 1] = __dadd_rn(tau[q], exp(__dadd_rn(__dmul_rn(delta[q], ce), __dmul_rn(nu_small[q], se))));
             }
-            __syncwarp();
+            __syncthreads();
         }
-        double llp = loglik(ce, se, false);
-        llp = __shfl_sync(0xffffffffu, llp, 0);
+        const double llp = loglik(ce, se, false);  // identical on every thread of the CTA
         ++evals;
         margin = fmin(margin, fabs(llp - log_y));
         if (llp > log_y) { accepted = true; break; }
@@ -154,7 +174,7 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
         eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
         if (overrun) break;
     }
-    if (lane == 0) {
+    if (tid == 0) {
         v.evals[J] = evals;
         v.margin[J] = margin;
         if (overrun) atomicExch(&v.flags->overrun, 1);
@@ -163,56 +183,74 @@ __global__ void __launch_bounds__(ITEM_WARPS * 32) k_ess_items(ItemView v) {
     // commit the last proposal (the reference's `out = f_prime`): on a stall/overrun this is still a
     // point of the ellipse, and the raised flag turns the call into an error at the next sync
     if (MODE == IB_F) {
-        for (int i = lane; i < n; i += 32) fj[i] = __dadd_rn(__dmul_rn(fj[i], ce), __dmul_rn(nuj[i], se));
+        for (int i = tid; i < n; i += T) fj[i] = __dadd_rn(__dmul_rn(fj[i], ce), __dmul_rn(nuj[i], se));
     } else if (MODE == IB_BETA) {
-        if (lane == 0) {
+        if (tid == 0) {
             v.beta[3 * (size_t)J] = pb0;
             v.beta[3 * (size_t)J + 1] = pb1;
             v.beta[3 * (size_t)J + 2] = pb2;
         }
     } else {
-        __syncwarp();
-        for (int c = 1 + lane; c < C; c += 32) v.thr[(size_t)J * (v.C + 1) + c] = tau[c];
+        __syncthreads();
+        for (int c = 1 + tid; c < C; c += T) v.thr[(size_t)J * (C + 1) + c] = tau[c];
     }
+}
+
+// warps per item: each thread should own <= ~8 cells of a pass
+static int item_warps(int n) { return n <= 256 ? 1 : (n <= 1024 ? 4 : (n <= 4096 ? 8 : 16)); }
+
+template <int MODE>
+static void launch_ess_mode(cudaStream_t st, const ItemView& v) {
+    switch (item_warps(v.n)) {
+        case 1: k_ess_items<MODE, 1><<<v.m_local, 32, 0, st>>>(v); break;
+        case 4: k_ess_items<MODE, 4><<<v.m_local, 128, 0, st>>>(v); break;
+        case 8: k_ess_items<MODE, 8><<<v.m_local, 256, 0, st>>>(v); break;
+        default: k_ess_items<MODE, 16><<<v.m_local, 512, 0, st>>>(v); break;
+    }
+    ++g_kernel_launches;
 }
 
 cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v) {
     if (v.m_local <= 0) return cudaSuccess;
-    dim3 grid((v.m_local + ITEM_WARPS - 1) / ITEM_WARPS);
-    if (block == IB_F) k_ess_items<IB_F><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
-    else if (block == IB_BETA) k_ess_items<IB_BETA><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
-    else k_ess_items<IB_THR><<<grid, ITEM_WARPS * 32, 0, st>>>(v);
-    ++g_kernel_launches;
+    if (block == IB_F) launch_ess_mode<IB_F>(st, v);
+    else if (block == IB_BETA) launch_ess_mode<IB_BETA>(st, v);
+    else launch_ess_mode<IB_THR>(st, v);
     return cudaGetLastError();
 }
 
 // per-item ll_bar_sparse with the current state
-__global__ void __launch_bounds__(ITEM_WARPS * 32) k_item_ll(ItemView v) {
-    __shared__ double s_tau[ITEM_WARPS][MAX_C + 1];
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int j = blockIdx.x * ITEM_WARPS + warp;
-    if (j >= v.m_local) return;
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) k_item_ll(ItemView v) {
+    constexpr int T = WARPS * 32;
+    __shared__ double tau[MAX_C + 1];
+    __shared__ double s_part[WARPS];
+    const int tid = threadIdx.x;
+    const int j = blockIdx.x;
     const int J = v.item0 + j;
-    double* tau = s_tau[warp];
-    for (int c = lane; c <= v.C; c += 32) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
-    __syncwarp();
+    for (int c = tid; c <= v.C; c += T) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
+    __syncthreads();
     const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
     const double* __restrict__ fj = v.f + (size_t)j * v.ldn;
     const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
     double acc = 0.0;
-    for (int i = lane; i < v.n; i += 32) {
+    for (int i = tid; i < v.n; i += T) {
         const int y = yj[i];
         if (y == 0) continue;
         const double g = __dadd_rn(fj[i], mu_of(v.theta[i], b0, b1, b2));
         acc += cell_ll(g, tau[y - 1], tau[y], y == 1, y == v.C);
     }
-    acc = warp_sum(acc);
-    if (lane == 0) v.item_ll[J] = acc;
+    acc = block_sum<WARPS>(acc, s_part);
+    if (tid == 0) v.item_ll[J] = acc;
 }
 
 cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v) {
     if (v.m_local <= 0) return cudaSuccess;
-    k_item_ll<<<(v.m_local + ITEM_WARPS - 1) / ITEM_WARPS, ITEM_WARPS * 32, 0, st>>>(v);
+    switch (item_warps(v.n)) {
+        case 1: k_item_ll<1><<<v.m_local, 32, 0, st>>>(v); break;
+        case 4: k_item_ll<4><<<v.m_local, 128, 0, st>>>(v); break;
+        case 8: k_item_ll<8><<<v.m_local, 256, 0, st>>>(v); break;
+        default: k_item_ll<16><<<v.m_local, 512, 0, st>>>(v); break;
+    }
     ++g_kernel_launches;
     return cudaGetLastError();
 }
@@ -224,38 +262,67 @@ namespace gpirt {
 // ------------------------------------------------------------------------------------------------
 // draw_theta: one CTA per respondent. The f* table is grid-row-major, so the row a proposal lands on
 // is one contiguous run of m doubles per shard chunk (the reference gathers it with stride N).
-constexpr int THETA_THREADS = 128;
+constexpr int THETA_THREADS = 256;
+
+__global__ void __launch_bounds__(128) k_theta_table(ThetaView v, double* __restrict__ table) {
+    const int J = blockIdx.x * 128 + threadIdx.x;
+    const int idx = blockIdx.y;
+    if (J >= v.m_total) return;
+    const int C = v.C;
+    const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
+    const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+    const double mu = mu_of(grid_value(idx), v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
+    const double g = __dadd_rn(fs, mu);
+    const double* tau = v.thr + (size_t)J * (C + 1);
+    double* out = table + ((size_t)idx * v.m_total + J) * C;
+    double p_lo = 0.0;
+    for (int c = 1; c <= C; ++c) {
+        const double p_hi = (c == C) ? 1.0 : phi(tau[c] - g);
+        out[c - 1] = cell_from_probs(p_lo, p_hi);
+        p_lo = p_hi;
+    }
+}
+
+cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* table) {
+    dim3 grid((v.m_total + 127) / 128, NGRID);
+    k_theta_table<<<grid, 128, 0, st>>>(v, table);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
 
 __global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
     __shared__ double s_part[THETA_THREADS / 32];
     const int il = blockIdx.x;
     if (il >= v.n_local) return;
     const int i = v.resp0 + il;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x;
     const int8_t* __restrict__ yrow = v.y_rm + (size_t)il * v.ldm;
     const int C = v.C, m_total = v.m_total;
+    const double* __restrict__ table = v.table;
 
-    auto loglik = [&](double th) -> double {  // compute_ll_sparse, src/draw-theta.cpp:4-24
+    auto term = [&](int J, int idx, double ts) -> double {  // one item's term of compute_ll_sparse, src/draw-theta.cpp:14-22
+        const int y = yrow[J];
+        if (y == 0) return 0.0;
+        if (table) return table[((size_t)idx * m_total + J) * C + (y - 1)];
+        const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
+        const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+        const double mu = mu_of(ts, v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
+        const double g = __dadd_rn(fs, mu);  // f* already holds mu*; the reference adds it again (:17)
+        return cell_ll(g, v.thr[(size_t)J * (C + 1) + y - 1], v.thr[(size_t)J * (C + 1) + y], y == 1, y == C);
+    };
+    auto loglik = [&](double th) -> double {
         const int idx = grid_index(th);
         const double ts = grid_value(idx);
-        double acc = 0.0;
-        for (int J = tid; J < m_total; J += THETA_THREADS) {
-            const int y = yrow[J];
-            if (y == 0) continue;
-            const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
-            const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
-            const double mu = mu_of(ts, v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
-            const double g = __dadd_rn(fs, mu);  // f* already holds mu*; the reference adds it again (:17)
-            acc += cell_ll(g, v.thr[(size_t)J * (C + 1) + y - 1], v.thr[(size_t)J * (C + 1) + y], y == 1, y == C);
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int J = tid;
+        for (; J + 3 * THETA_THREADS < m_total; J += 4 * THETA_THREADS) {
+            a0 += term(J, idx, ts);
+            a1 += term(J + THETA_THREADS, idx, ts);
+            a2 += term(J + 2 * THETA_THREADS, idx, ts);
+            a3 += term(J + 3 * THETA_THREADS, idx, ts);
         }
-        acc = warp_sum(acc);
-        __syncthreads();
-        if (lane == 0) s_part[warp] = acc;
-        __syncthreads();
-        double tot = 0.0;
-#pragma unroll
-        for (int w = 0; w < THETA_THREADS / 32; ++w) tot += s_part[w];
-        return tot;
+        for (; J < m_total; J += THETA_THREADS) a0 += term(J, idx, ts);
+        return block_sum<THETA_THREADS / 32>((a0 + a1) + (a2 + a3), s_part);
     };
 
     double Li;

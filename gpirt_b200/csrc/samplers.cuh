@@ -55,6 +55,7 @@ struct ThetaView {
     long long chunk_elems;
     const double* beta;       // 3 x m_total
     const double* thr;        // (C+1) x m_total item-major
+    const double* table;      // optional [NGRID][m_total][C] table of cell terms (k_theta_table), or nullptr
     const double* theta_prior_sds;  // 2 x n
     int regime;               // 0: L_i = sqrt(1 + sd0_i^2) (CST/RDM), 1: sqrt(os^2 + 1e-6) (GP over time, H = 1)
     double theta_os;
@@ -72,6 +73,9 @@ cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, i
 cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v);
 cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v);
 cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v);
+// table[(idx*m_total + J)*C + c-1] = log(Phi(tau_c - g) - Phi(tau_{c-1} - g) + 1e-6), g = f*(idx,J) + mu*(idx,J): every term the theta
+// step can ask for, computed once per sweep instead of once per (respondent, proposal)
+cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* table);
 // f[i + j*ldn] = fstar_chunk[grid_index(theta_i)*ld_chunk + j]  (src/gpirtMCMC.cpp:291-298)
 cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const double* fstar_chunk, int ld_chunk, int m_local, double* f, int ldn);
 // fstar_chunk[idx*ld_chunk + j] += mu_star(idx, item0 + j)  (src/draw-fstar.cpp:52)

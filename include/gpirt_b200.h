@@ -150,6 +150,7 @@ int gpirt_profile_read(gpirt_sampler* h, char* names /* cap x 32 */, double* ms,
 int gpirt_profile_reset(gpirt_sampler* h);
 long long gpirt_launch_count(void);                          /* kernels launched by this library so far */
 int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int count, double* out);
+int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out); /* device Phi(x), log(x) */
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
 
 /* ---- the two Rcpp entry points ---- */

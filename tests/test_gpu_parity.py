@@ -18,6 +18,21 @@ def _pair(P, seed=1, **kw):
     return S, O
 
 
+def test_device_phi_and_log_against_mpmath():
+    import mpmath as mp
+    from gpirt_b200.api import debug_probit
+    mp.mp.dps = 40
+    rng = np.random.default_rng(0)
+    x = np.concatenate([np.linspace(-9.5, 9.5, 1501), rng.normal(size=1500) * 2.5, [0.0, -8.6, 8.6, -8.6000001, 8.6000001, np.inf, -np.inf]])
+    ph, _ = debug_probit(x)
+    assert ph[-2] == 1.0 and ph[-1] == 0.0  # Phi(+inf), Phi(-inf): exact, as pnorm
+    err = max(abs(mp.mpf(float(p)) - mp.ncdf(mp.mpf(float(xi)))) for xi, p in zip(x[:-2], ph[:-2]))
+    assert err < 5e-16  # absolute; R's pnorm (Cody) is ~1e-16. The 1e-6 floor inside the log makes absolute error the relevant one
+    z = np.concatenate([10 ** rng.uniform(-6, 0, 2000), 1 + rng.uniform(-1e-6, 1e-6, 200), [1e-6, 1.0, 1.000001, 0.5]])
+    _, lg = debug_probit(z)
+    assert max(abs(mp.mpf(float(l)) - mp.log(mp.mpf(float(zi)))) for zi, l in zip(z, lg)) < 4e-15
+
+
 def test_K_matches_reference_formula():
     rng = np.random.default_rng(0)
     x1, x2 = rng.standard_normal(257) * 2, rng.standard_normal(130) * 2
@@ -146,7 +161,7 @@ def test_draw_f_with_supplied_z_uses_L():
     assert np.max(np.abs(got - want)) / np.max(np.abs(want)) < 1e-8  # nu = L z inherits the kappa-limited error of L
 
 
-@pytest.mark.parametrize("n,m,C", [(150, 30, 2), (120, 45, 5)])
+@pytest.mark.parametrize("n,m,C", [(150, 30, 2), (120, 45, 5), (700, 21, 5), (90, 12, 2)])  # with and without the per-sweep term table
 def test_draw_theta_same_states(n, m, C):
     P = make_problem(n, m, C, seed=31, on_grid=True)
     rng = P["rng"]
