@@ -108,106 +108,205 @@ cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double
 namespace gpirt {
 
 // ------------------------------------------------------------------------------------------------
-// Cholesky of one NB x NB diagonal block, one CTA, block resident in shared memory.
-__global__ void __launch_bounds__(256) k_potf2(double* __restrict__ A, int ld, int kb, int* info, int k0) {
-    constexpr int NB = CHOL_NB;
-    __shared__ double S[NB][NB + 1];
-    const int tid = threadIdx.x;
-    for (int e = tid; e < NB * NB; e += 256) {
-        int r = e % NB, c = e / NB;
-        S[r][c] = (r < kb && c < kb && r >= c) ? A[(size_t)c * ld + r] : (r == c ? 1.0 : 0.0);
-    }
-    __syncthreads();
-    for (int j = 0; j < kb; ++j) {
-        if (tid == 0) {
-            double d = S[j][j];
-            if (!(d > 0.0)) {  // arma::chol would throw here; record the failing leading minor and keep going
-                atomicCAS(info, 0, k0 + j + 1);
-                d = 1.0;
+// 64 x 64 tile kernels with compact (I-cache resident) code: 256 threads as a 16 x 16 grid, thread (tr, tc)
+// keeps the 4 x 4 elements (tr + 16p, tc + 16q) of the tile in registers; the column/row being eliminated
+// travels through a double-buffered shared-memory vector, one __syncthreads per elimination step.
+// (A first version unrolled the 64-step substitution completely per thread: ~10k straight-line instructions
+// per warp, instruction-fetch bound at 70-150 us per launch, profiles/r01_launches_v2.csv.)
+constexpr int TILE_THREADS = 256;
+
+// In-register Cholesky of the tile held as a[4][4]; returns with the factor in a (lower part valid).
+__device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, double (*vec)[CHOL_NB], int* info, int k0, bool report) {
+#pragma unroll
+    for (int jq = 0; jq < 4; ++jq) {
+        for (int jj = 0; jj < 16; ++jj) {
+            const int j = 16 * jq + jj;
+            double* colL = vec[j & 1];
+            if (tc == jj) {  // the 16 owners of column j sit in one half-warp (tid = tr + 16 tc)
+                const unsigned half = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;
+                double d = __shfl_sync(half, a[jq][jq], (threadIdx.x & 16) + jj);  // diagonal element lives in lane tr == jj
+                if (!(d > 0.0)) {  // arma::chol would throw here; record the failing leading minor and keep going
+                    if (report && tr == jj) atomicCAS(info, 0, k0 + j + 1);
+                    d = 1.0;
+                }
+                d = sqrt(d);
+                const double inv_d = 1.0 / d;  // one division per column; the scaling below multiplies (a fp64 division
+                                               // inside this divergent section costs ~1500 cycles, tools/bench_tile.cu)
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    const int r = tr + 16 * p;
+                    double v = a[p][jq];
+                    if (r > j) v = v * inv_d;
+                    else if (r == j) v = d;
+                    a[p][jq] = v;
+                    colL[r] = (r > j) ? v : 0.0;
+                }
             }
-            S[j][j] = sqrt(d);
+            __syncthreads();
+            double lr[4], lc[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) { lr[p] = colL[tr + 16 * p]; lc[p] = colL[tc + 16 * p]; }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (tc + 16 * q > j) {
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) a[p][q] -= lr[p] * lc[q];
+                }
         }
-        __syncthreads();
-        const double d = S[j][j];
-        for (int i = j + 1 + tid; i < kb; i += 256) S[i][j] = S[i][j] / d;
-        __syncthreads();
-        const int t = kb - j - 1;
-        for (int e = tid; e < t * t; e += 256) {
-            int r = j + 1 + e % t, c = j + 1 + e / t;
-            if (r >= c) S[r][c] -= S[r][j] * S[c][j];
-        }
-        __syncthreads();
-    }
-    for (int e = tid; e < NB * NB; e += 256) {
-        int r = e % NB, c = e / NB;
-        if (r < kb && c < kb && r >= c) A[(size_t)c * ld + r] = S[r][c];
     }
 }
 
-// Panel solve X * L11^T = A21 (rows of the panel are independent): one thread per row keeps its 64
-// unknowns in registers, L11 is broadcast from shared memory. Backward-stable substitution.
-__global__ void __launch_bounds__(64) k_trsm_right_lt(double* __restrict__ A21, int ld, int rows,
-                                                      const double* __restrict__ L11) {
+// One panel of the blocked factorisation in ONE launch: every CTA factors the diagonal block (redundantly,
+// bit-identical), CTA 0 writes it back, CTA b >= 1 solves X * L11^T = A21 for its 64 rows of the panel by
+// substitution (backward stable). The chain potf2 -> trsm is the latency floor of a panel: no launch gap.
+__global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict__ A, int ld, int kb, int rows_below, int* info, int k0) {
     constexpr int NB = CHOL_NB;
     __shared__ double Ls[NB][NB + 1];
-    for (int e = threadIdx.x; e < NB * NB; e += 64) {
-        int r = e % NB, c = e / NB;
-        Ls[r][c] = (r >= c) ? L11[(size_t)c * ld + r] : 0.0;
+    __shared__ double vec[2][NB];
+    __shared__ double inv_diag[NB];
+    const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
+    double a[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            a[p][q] = (r < kb && c < kb && c <= r) ? A[(size_t)c * ld + r] : (c == r ? 1.0 : 0.0);
+        }
+    tile_potf2(a, tr, tc, vec, info, k0, blockIdx.x == 0);
+    if (blockIdx.x == 0) {
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+#pragma unroll
+            for (int p = 0; p < 4; ++p) {
+                const int r = tr + 16 * p, c = tc + 16 * q;
+                if (r < kb && c <= r) A[(size_t)c * ld + r] = a[p][q];
+            }
+        return;
     }
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            Ls[r][c] = (c <= r) ? a[p][q] : 0.0;
+        }
     __syncthreads();
-    const int r = blockIdx.x * 64 + threadIdx.x;
-    if (r >= rows) return;
-    double x[NB];
+    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+    // X * L11^T = A21 for rows [row0, row0 + 64) of the panel; kb == NB whenever rows_below > 0
+    const int row0 = (blockIdx.x - 1) * 64;
+    double* __restrict__ A21 = A + kb;
 #pragma unroll
-    for (int k = 0; k < NB; ++k) x[k] = A21[(size_t)k * ld + r];
+    for (int q = 0; q < 4; ++q)
 #pragma unroll
-    for (int k = 0; k < NB; ++k) {
-        const double xk = x[k] / Ls[k][k];
-        x[k] = xk;
+        for (int p = 0; p < 4; ++p) {
+            const int r = row0 + tr + 16 * p, c = tc + 16 * q;
+            a[p][q] = (r < rows_below) ? A21[(size_t)c * ld + r] : 0.0;
+        }
+    __syncthreads();  // inv_diag visible
 #pragma unroll
-        for (int i = k + 1; i < NB; ++i) x[i] -= xk * Ls[i][k];
+    for (int kq = 0; kq < 4; ++kq) {
+        for (int kk = 0; kk < 16; ++kk) {
+            const int k = 16 * kq + kk;
+            double* xcol = vec[k & 1];
+            if (tc == kk) {
+                const double d = inv_diag[k];
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                    const double v = a[p][kq] * d;
+                    a[p][kq] = v;
+                    xcol[tr + 16 * p] = v;
+                }
+            }
+            __syncthreads();
+            double xr[4], lc[4];
+#pragma unroll
+            for (int p = 0; p < 4; ++p) { xr[p] = xcol[tr + 16 * p]; lc[p] = Ls[tc + 16 * p][k]; }
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (tc + 16 * q > k) {
+#pragma unroll
+                    for (int p = 0; p < 4; ++p) a[p][q] -= xr[p] * lc[q];
+                }
+        }
     }
 #pragma unroll
-    for (int k = 0; k < NB; ++k) A21[(size_t)k * ld + r] = x[k];
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = row0 + tr + 16 * p, c = tc + 16 * q;
+            if (r < rows_below) A21[(size_t)c * ld + r] = a[p][q];
+        }
 }
 
-// Diagonal-block solves for many right-hand sides: one thread per column of B.
+// Diagonal-block solves for many right-hand sides: CTA b solves L11 X = B (or L11^T X = B) for 64 columns of B.
 template <bool TRANS>
-__global__ void __launch_bounds__(64) k_trsm_left(const double* __restrict__ L11, int ldl, int kb,
-                                                  double* __restrict__ B, int ldb, int nrhs) {
+__global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __restrict__ L11, int ldl, int kb,
+                                                            double* __restrict__ B, int ldb, int nrhs) {
     constexpr int NB = CHOL_NB;
     __shared__ double Ls[NB][NB + 1];
-    for (int e = threadIdx.x; e < NB * NB; e += 64) {
-        int r = e % NB, c = e / NB;
-        Ls[r][c] = (r < kb && c < kb) ? (r >= c ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
-    }
+    __shared__ double vec[2][NB];
+    __shared__ double inv_diag[NB];
+    const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
+        }
+    const int c0 = blockIdx.x * 64;
+    double a[4][4];  // a[p][q] = X(row tr + 16p, column c0 + tc + 16q)
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
+            a[p][q] = (r < kb && c < nrhs) ? B[(size_t)c * ldb + r] : 0.0;
+        }
     __syncthreads();
-    const int c = blockIdx.x * 64 + threadIdx.x;
-    if (c >= nrhs) return;
-    double* b = B + (size_t)c * ldb;
-    double x[NB];
+    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+    __syncthreads();
 #pragma unroll
-    for (int k = 0; k < NB; ++k) x[k] = (k < kb) ? b[k] : 0.0;
-    if (!TRANS) {
+    for (int s = 0; s < 4; ++s) {
+        const int kq = TRANS ? 3 - s : s;
+        for (int t = 0; t < 16; ++t) {
+            const int kk = TRANS ? 15 - t : t;
+            const int k = 16 * kq + kk;
+            double* xrow = vec[k & 1];
+            if (tr == kk) {  // owners of row k
+                const double d = inv_diag[k];
 #pragma unroll
-        for (int k = 0; k < NB; ++k) {
-            const double xk = x[k] / Ls[k][k];
-            x[k] = xk;
+                for (int q = 0; q < 4; ++q) {
+                    const double v = a[kq][q] * d;
+                    a[kq][q] = v;
+                    xrow[tc + 16 * q] = v;
+                }
+            }
+            __syncthreads();
+            double xc[4], lr[4];
 #pragma unroll
-            for (int i = k + 1; i < NB; ++i) x[i] -= xk * Ls[i][k];
-        }
-    } else {
+            for (int p = 0; p < 4; ++p) {
+                xc[p] = xrow[tc + 16 * p];
+                lr[p] = TRANS ? Ls[k][tr + 16 * p] : Ls[tr + 16 * p][k];  // L^T(r,k) = L(k,r)
+            }
 #pragma unroll
-        for (int k = NB - 1; k >= 0; --k) {
-            const double xk = x[k] / Ls[k][k];
-            x[k] = xk;
+            for (int p = 0; p < 4; ++p) {
+                const int r = tr + 16 * p;
+                if (TRANS ? (r < k) : (r > k)) {
 #pragma unroll
-            for (int i = 0; i < k; ++i) x[i] -= xk * Ls[k][i];
+                    for (int q = 0; q < 4; ++q) a[p][q] -= lr[p] * xc[q];
+                }
+            }
         }
     }
 #pragma unroll
-    for (int k = 0; k < NB; ++k)
-        if (k < kb) b[k] = x[k];
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
+            if (r < kb && c < nrhs) B[(size_t)c * ldb + r] = a[p][q];
+        }
 }
 
 __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
@@ -221,13 +320,11 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
     for (int k0 = 0; k0 < n; k0 += NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
         double* Akk = A + (size_t)k0 * ld + k0;
-        k_potf2<<<1, 256, 0, st>>>(Akk, ld, kb, info_dev, k0);
-        ++g_kernel_launches;
         const int rows = n - k0 - kb;
+        k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0);
+        ++g_kernel_launches;
         if (rows > 0) {
             double* A21 = Akk + kb;
-            k_trsm_right_lt<<<(rows + 63) / 64, 64, 0, st>>>(A21, ld, rows, Akk);
-            ++g_kernel_launches;
             GemmArgs g{};
             g.M = rows; g.N = rows; g.K = kb;
             g.A = A21; g.lda = ld; g.B = A21; g.ldb = ld;
@@ -247,7 +344,7 @@ cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, do
     constexpr int NB = CHOL_NB;
     for (int k0 = 0; k0 < n; k0 += NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
-        k_trsm_left<false><<<(nrhs + 63) / 64, 64, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
+        k_trsm_left<false><<<(nrhs + 63) / 64, TILE_THREADS, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
         ++g_kernel_launches;
         const int rows = n - k0 - kb;
         if (rows > 0) {
@@ -269,7 +366,7 @@ cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, 
     const int last = ((n - 1) / NB) * NB;
     for (int k0 = last; k0 >= 0; k0 -= NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
-        k_trsm_left<true><<<(nrhs + 63) / 64, 64, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
+        k_trsm_left<true><<<(nrhs + 63) / 64, TILE_THREADS, 0, st>>>(L + (size_t)k0 * ldl + k0, ldl, kb, B + k0, ldb, nrhs);
         ++g_kernel_launches;
         if (k0 > 0) {
             // B[0:k0, :] -= L[k0:k0+kb, 0:k0]^T * X_k
