@@ -56,6 +56,11 @@ def lib():
     return _lib
 
 
+def set_threads(k):
+    """OpenMP threads of samplers created after this call; 1 reproduces the reference's single-thread RNG order."""
+    lib().orc_set_threads(C.c_int(int(k)))
+
+
 def _f64(a):
     return np.ascontiguousarray(np.asarray(a, dtype=np.float64))
 
@@ -304,6 +309,21 @@ class Sampler:
         mg = np.empty(units)
         over = lib().orc_get_diag(self._h, C.c_int(BLOCKS[block]), _p(ev), _p(mg))
         return ev, mg, bool(over)
+
+    def record(self, on=True):
+        """keep every unit's normals / uniforms of the next block calls (see recorded())"""
+        lib().orc_record(self._h, C.c_int(int(on)))
+
+    def recorded(self, block, zcap, ucap=64):
+        """(z zcap x units, u ucap x units, nz, nu) drawn by the last call of `block`, zero padded"""
+        units = self.n if block == "theta" else self.m
+        z = np.zeros((zcap, units), order="F")
+        u = np.zeros((ucap, units), order="F")
+        nz = np.zeros(units, dtype=np.int32)
+        nu = np.zeros(units, dtype=np.int32)
+        over = lib().orc_get_record(self._h, C.c_int(BLOCKS[block]), _p(z), C.c_uint64(zcap), _p(u), C.c_uint64(ucap), _p(nz), _p(nu))
+        assert not over, "recorded stream longer than the requested capacity"
+        return z, u, nz, nu
 
     def run_mt(self, iter0, iters, store=True):
         th = np.empty((self.n, iters), order="F") if store else None

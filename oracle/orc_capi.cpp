@@ -1,5 +1,7 @@
 // TEST INFRASTRUCTURE — flat C entry points over the CPU oracle, loaded with ctypes by tests/,
 // __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs only.
+#include <omp.h>
+
 #include <cstdio>
 #include <cstring>
 
@@ -23,6 +25,13 @@ static Src to_src(Sampler* S, const orc_src* c, int block) {
     s.mode = c->mode; s.z = c->z; s.zstride = c->zstride; s.u = c->u; s.ustride = c->ustride;
     s.seed = c->seed; s.chain = c->chain; s.iter = c->iter; s.zs = zs[block]; s.us = us[block];
     s.mts = &S->mts;
+    if (S->record) {
+        const size_t units = block == B_THETA ? S->n : S->m;
+        S->rec_z[block].assign(units, {});
+        S->rec_u[block].assign(units, {});
+        s.rec_z = &S->rec_z[block];
+        s.rec_u = &S->rec_u[block];
+    }
     return s;
 }
 
@@ -114,6 +123,23 @@ int orc_update_cholesky(void* h) { return static_cast<Sampler*>(h)->update_chole
 void orc_mt_seed_all(void* h, uint32_t base) {  // WorkspacePool::seed_all, src/gpirt.h:178-182
     Sampler* S = static_cast<Sampler*>(h);
     for (size_t t = 0; t < S->mts.size(); ++t) S->mts[t].seed(base + uint32_t(t) * 1000u);
+}
+// worker threads of samplers created AFTER this call (single-thread runs reproduce the reference's RNG order)
+void orc_set_threads(int k) { omp_set_num_threads(k); }
+void orc_record(void* h, int on) { static_cast<Sampler*>(h)->record = on != 0; }
+// draws of the last call of `block`: z_out is zcap x units, u_out is ucap x units (column-major, zero padded); counts per unit
+int orc_get_record(void* h, int block, double* z_out, uint64_t zcap, double* u_out, uint64_t ucap, int32_t* nz, int32_t* nu) {
+    Sampler* S = static_cast<Sampler*>(h);
+    const auto& Z = S->rec_z[block];
+    const auto& U = S->rec_u[block];
+    int over = 0;
+    for (size_t k = 0; k < Z.size(); ++k) {
+        nz[k] = int32_t(Z[k].size()); nu[k] = int32_t(U[k].size());
+        if (Z[k].size() > zcap || U[k].size() > ucap) { over = 1; continue; }
+        for (size_t i = 0; i < Z[k].size(); ++i) z_out[k * zcap + i] = Z[k][i];
+        for (size_t i = 0; i < U[k].size(); ++i) u_out[k * ucap + i] = U[k][i];
+    }
+    return over;
 }
 int orc_num_threads(void* h) { return int(static_cast<Sampler*>(h)->mts.size()); }
 

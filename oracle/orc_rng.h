@@ -17,6 +17,7 @@
 #include <cstddef>
 #include <cstdint>
 #include <random>
+#include <vector>
 
 namespace orc {
 
@@ -105,6 +106,14 @@ struct MtRng : UnitRng {
     void seed(unsigned s) { gen.seed(s); }
     double norm() override { return nd(gen); }
     double unif() override { return ud(gen); }
+};
+
+// Wraps any source and keeps what a unit drew: tests replay an mt19937 run as supplied streams on the GPU path.
+struct RecordingRng : UnitRng {
+    UnitRng& base; std::vector<double>& z; std::vector<double>& u;
+    RecordingRng(UnitRng& b, std::vector<double>& z_, std::vector<double>& u_) : base(b), z(z_), u(u_) {}
+    double norm() override { double v = base.norm(); z.push_back(v); return v; }
+    double unif() override { double v = base.unif(); u.push_back(v); return v; }
 };
 
 }  // namespace orc

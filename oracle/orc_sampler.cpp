@@ -28,7 +28,7 @@ static inline int max_threads() {
 
 // Run body(rng) with the per-unit random source selected by s.
 template <class F>
-static inline bool with_rng(const Src& s, size_t unit, size_t nz, F&& body) {
+static inline bool with_rng_raw(const Src& s, size_t unit, size_t nz, F&& body) {
     if (s.mode == 0) {
         SuppliedRng r(s.z ? s.z + unit * s.zstride : nullptr, s.z ? nz : 0, s.u + unit * s.ustride, s.ustride);
         body(r);
@@ -41,6 +41,14 @@ static inline bool with_rng(const Src& s, size_t unit, size_t nz, F&& body) {
         body((*s.mts)[thread_id()]);
         return false;
     }
+}
+template <class F>
+static inline bool with_rng(const Src& s, size_t unit, size_t nz, F&& body) {
+    if (!s.rec_z) return with_rng_raw(s, unit, nz, body);
+    return with_rng_raw(s, unit, nz, [&](UnitRng& base) {
+        RecordingRng r(base, (*s.rec_z)[unit], (*s.rec_u)[unit]);
+        body(r);
+    });
 }
 
 // The elliptical-slice transition shared by all four samplers (src/draw-f.cpp:14-41).

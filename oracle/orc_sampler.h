@@ -43,6 +43,9 @@ struct Src {
     uint64_t seed = 0; uint32_t chain = 0, iter = 0, zs = 0, us = 0;
     // mt: one generator per worker thread
     std::vector<MtRng>* mts = nullptr;
+    // when set, every unit's draws are appended to (*rec_z)[unit] / (*rec_u)[unit]
+    std::vector<std::vector<double>>* rec_z = nullptr;
+    std::vector<std::vector<double>>* rec_u = nullptr;
 };
 
 struct Diag {  // per-unit diagnostics of one block call
@@ -72,6 +75,8 @@ struct Sampler {
     std::vector<double> f_new, mu, mu_star, Lpost, W;
     std::vector<MtRng> mts;
     Diag diag[N_BLOCKS];
+    bool record = false;  // keep the draws of the last call of each block (per unit)
+    std::vector<std::vector<double>> rec_z[N_BLOCKS], rec_u[N_BLOCKS];
 
     void init(size_t n_, size_t m_, size_t C_, const double* y_, const double* sds_, const double* tps_);
     void compute_mu();        // mu = X beta, mu_star = X* beta (src/gpirtMCMC.cpp:308-311)

@@ -1,0 +1,108 @@
+"""Generates tests/golden/*.npz from the REFERENCE'S OWN CODE (oracle/_ref/libgpirt_ref.so = /root/reference/src/*.cpp compiled
+against oracle/refshim). Run in the build container only (needs /root/reference):   python tests/golden/make_golden.py
+
+Each sweep case stores
+  * the inputs of gpirtMCMC() (src/gpirtMCMC.cpp:25-38) and the N(0,1) stream its R::rnorm initialisation consumed,
+  * the reference's stored draws after every sweep (theta, beta, threshold, ll, f, fstar), single OpenMP thread,
+  * the random streams each unit consumed in each block of each sweep. The reference draws them from per-thread mt19937
+    generators (src/gpirt.h:13-41,178-182); they are captured by running the CPU oracle in its mt19937 mode beside the reference
+    and are only kept if the oracle reproduces the reference's theta draws bit for bit (asserted below), i.e. the recorded streams
+    ARE the reference's. The CUDA path and the oracle replay them as supplied streams (tests/test_golden.py).
+The leaf file stores direct outputs of the reference's K, K_time, ll_bar_sparse, threshold transforms, update_cholesky_cache and
+double_solve on small inputs.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+from oracle import orc, ref  # noqa: E402
+from tests.problems import make_problem  # noqa: E402
+
+UCAP = 48
+
+
+def sweep_case(name, n, m, C, seed, iters, missing, empty_item=None, tps_sd=0.0):
+    P = make_problem(n, m, C, seed=seed, missing=missing)
+    y = P["y"].copy(order="F")
+    if empty_item is not None:
+        y[:, empty_item] = np.nan  # an item nobody answered: draw_beta keeps its beta and draws nothing (src/draw-beta.cpp:73,97-99)
+    rng = np.random.default_rng(seed + 1000)
+    z_init = rng.standard_normal(3 * m + n * m)
+    bpm = np.zeros((3, m), order="F")
+    bps = P["beta_prior_sds"]
+    tpm = np.zeros((2, n), order="F")
+    tps = np.full((2, n), tps_sd, order="F")
+    theta_in = P["theta0"] * 1.7  # some values beyond +-5 so the clamp (src/gpirtMCMC.cpp:133) is exercised
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, 1.0, 10.0, "Matern", P["thr0"], 0, z_init, store_f=True, store_fstar=True)
+
+    # the oracle beside it, mt19937 mode, recording every unit's draws
+    theta0 = np.clip(theta_in, -5.0, 5.0)
+    beta0 = np.asfortranarray(bpm + bps * z_init[:3 * m].reshape(m, 3).T)  # R::rnorm(mean, sd) per (item, coefficient)
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.asfortranarray(np.stack([L0 @ z_init[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1))
+    O = orc.Sampler(y, C, bps, tps)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.draw_fstar(orc.mt())  # the initial draw_fstar (src/gpirtMCMC.cpp:227) runs on the unseeded generators
+    fstar0 = O.state()["fstar"]
+    O.record(True)
+    rec = {}
+    for it in range(iters):
+        O.mt_seed_all(it * 10000)
+        assert O.sweep(orc.mt()) == 0
+        for blk, zcap in (("f", n), ("fstar", orc.NGRID), ("theta", 1), ("beta", 3), ("thr", C - 1)):
+            z, u, nz, nu = O.recorded(blk, zcap, UCAP)
+            rec[f"z_{blk}_{it}"] = z
+            if blk != "fstar":
+                rec[f"u_{blk}_{it}"] = u
+                rec[f"nu_{blk}_{it}"] = nu
+        s = O.state()
+        assert np.array_equal(s["theta"], R["theta"][it, :, 0]), f"{name}: oracle theta != reference theta at sweep {it}"
+        assert np.array_equal(s["beta"], R["beta"][:, :, 0, it]) and np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, 0, it])
+    out = dict(n=n, m=m, C=C, iters=iters, y=y, theta_in=theta_in, z_init=z_init, beta_prior_means=bpm, beta_prior_sds=bps,
+               theta_prior_sds=tps, thr0=P["thr0"], beta0=beta0, f0=f0, fstar0=fstar0,
+               ref_theta=R["theta"][:, :, 0], ref_beta=R["beta"][:, :, 0, :], ref_threshold=R["threshold"][:, :, 0, :], ref_ll=R["ll"],
+               ref_f=R["f"][:, :, 0, :], ref_fstar_last=R["fstar"][:, :, 0, -1], **rec)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "ll", R["ll"], "max evals recorded", max(int(v.max()) for k, v in rec.items() if k.startswith("nu_")))
+
+
+def leaf_case():
+    rng = np.random.default_rng(42)
+    x1, x2, sds = rng.standard_normal(17) * 2, rng.standard_normal(9) * 2, np.array([3.0, 2.5, 0.7])
+    ts = np.arange(5.0)
+    out = dict(x1=x1, x2=x2, sds=sds, K=ref.K(x1, x2, sds), ts=ts, K_time_matern=ref.K_time(ts, ts, 1.3, 2.0, [0.4, 0.2], "Matern"),
+               K_time_rbf=ref.K_time(ts, ts, 1.3, 2.0, [0.4, 0.2], "RBF"))
+    xs = np.concatenate([np.linspace(-38.5, 9.0, 400), rng.standard_normal(200) * 3, [0.0, -0.67448975, 0.67448975, 5.656854249492381]])
+    out.update(pnorm_x=xs, pnorm=ref.pnorm(xs))
+    n, C = 40, 5
+    f, mu = rng.standard_normal(n) * 2, rng.standard_normal(n)
+    y = rng.integers(1, C + 1, n).astype(np.float64)
+    y[rng.random(n) < 0.15] = np.nan
+    thr = np.array([-np.inf, -1.1, -0.2, 0.5, 1.7, np.inf])
+    out.update(ll_f=f, ll_mu=mu, ll_y=y, ll_thr=thr, ll=ref.ll_bar_sparse(f, y, mu, thr), delta=ref.threshold_to_delta(thr),
+               thr_back=ref.delta_to_threshold(ref.threshold_to_delta(thr)), thr2=ref.delta_to_threshold([0.25]))
+    theta = np.clip(rng.standard_normal(24) * 1.5, -5, 5)
+    bps = np.tile(np.array([[0.8], [0.5], [0.1]]), (1, 3))  # well-conditioned: 1e-10 element-wise is meaningful
+    L, _ = ref.update_cholesky_cache(theta, bps)
+    X = rng.standard_normal((24, 3))
+    out.update(chol_theta=theta, chol_sds=bps, chol_L=L[:, :, 0], solve_X=X, solve_out=ref.double_solve(L[:, :, 0], X))
+    theta2 = np.tile(theta[:, None], (1, 3))
+    _, Lt = ref.update_cholesky_cache(theta2, bps, 1.0, 2.0, "Matern")  # 0.1 < ls < 3H: the K_time branch (src/cholesky-cache.cpp:27-35)
+    out.update(L_time=Lt[:, :, 0])
+    np.savez_compressed(os.path.join(HERE, "leaves.npz"), **out)
+    print("leaves ok")
+
+
+if __name__ == "__main__":
+    assert ref.available(), "build oracle/_ref first (make -C oracle ref)"
+    orc.set_threads(1)
+    ref.set_threads(1)
+    leaf_case()
+    sweep_case("sweep_ordinal_c4", n=48, m=8, C=4, seed=11, iters=3, missing=0.1)
+    sweep_case("sweep_binary_c2", n=36, m=6, C=2, seed=23, iters=3, missing=0.2, empty_item=4, tps_sd=0.6)

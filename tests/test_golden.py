@@ -1,0 +1,154 @@
+"""Golden vectors recorded from the REFERENCE'S OWN CODE (tests/golden/make_golden.py: /root/reference/src/*.cpp compiled
+against oracle/refshim, single thread). They travel with the repo, so both the CPU oracle (here, no GPU) and the CUDA path
+(-m gpu, on the B200 box where /root/reference does not exist) are checked against the reference's outputs, not only against
+each other. The sweep fixtures hold the random streams every unit consumed in the reference run; both sides replay them as
+supplied streams.
+
+Tolerances: theta and indexing bit-exact; beta / thresholds / f 1e-9 relative (cos/sin/exp rounding and summation order of
+L*z); total log-likelihood 1e-9 relative (north star: 1e-10 on the likelihood itself, tested separately on fixed states below);
+f* and the f gathered from it 1e-6 norm-wise per item column (K^-1 f is kappa-limited with kappa ~ 1e10 under the default priors,
+SURVEY.md 7 — two correct fp64 codes differ at that level; the oracle itself differs from the reference by 1e-7)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import orc
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+SWEEPS = ["sweep_ordinal_c4", "sweep_binary_c2"]
+
+
+def load(name):
+    return dict(np.load(os.path.join(HERE, "golden", name + ".npz")))
+
+
+def rel(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    fin = np.isfinite(b)
+    assert np.array_equal(np.isfinite(a), fin)
+    return float(np.max(np.abs(a[fin] - b[fin]) / np.maximum(1.0, np.abs(b[fin])))) if fin.any() else 0.0
+
+
+# ---- CPU: the oracle against the reference's vectors -------------------------------------------------------------
+def test_leaves_oracle_matches_reference_vectors():
+    G = load("leaves")
+    assert np.array_equal(orc.K(G["x1"], G["x2"], G["sds"]), G["K"])
+    assert np.array_equal(orc.K_time(G["ts"], G["ts"], 1.3, 2.0, [0.4, 0.2], "Matern"), G["K_time_matern"])
+    assert np.array_equal(orc.K_time(G["ts"], G["ts"], 1.3, 2.0, [0.4, 0.2], "RBF"), G["K_time_rbf"])
+    assert np.array_equal(orc.pnorm(G["pnorm_x"]), G["pnorm"])
+    assert orc.ll_bar_sparse(G["ll_f"], G["ll_y"], G["ll_mu"], G["ll_thr"]) == float(G["ll"])
+    assert np.array_equal(orc.threshold_to_delta(G["ll_thr"]), G["delta"])
+    assert np.array_equal(orc.delta_to_threshold(G["delta"]), G["thr_back"])
+    assert np.array_equal(orc.delta_to_threshold([0.25]), G["thr2"])
+    th = G["chol_theta"]
+    A = orc.K(th, th, G["chol_sds"][:, 0]) + 1e-6 * np.eye(th.size)
+    L, info = orc.chol(A)
+    assert info == 0 and np.max(np.abs(L - G["chol_L"])) < 1e-13
+    out = np.stack([orc.double_solve(G["chol_L"], G["solve_X"][:, k]) for k in range(3)], axis=1)
+    assert rel(out, G["solve_out"]) < 1e-12
+
+
+def colrel(a, b):
+    """norm-wise relative difference per column (item): max |a - b| / max |b|"""
+    return float(np.max(np.max(np.abs(a - b), axis=0) / np.maximum(1.0, np.max(np.abs(b), axis=0))))
+
+
+def replay(G, S, kind):
+    """Drives one sampler (oracle or CUDA) through the fixture's sweeps with the recorded streams; yields its state after each."""
+    n, m, C = int(G["n"]), int(G["m"]), int(G["C"])
+    for it in range(int(G["iters"])):
+        zf, uf = G[f"z_f_{it}"], G[f"u_f_{it}"]
+        if kind == "orc":
+            S.compute_mu()
+            assert S.update_cholesky() == 0
+            nu = np.asfortranarray(S.L() @ zf)  # rmvnorm_threadsafe: nu_j = L z_j (src/mvnormal.h:17-24)
+            S.draw_f(orc.supplied(u=uf), nu=nu)
+            assert S.draw_fstar(orc.supplied(z=G[f"z_fstar_{it}"])) == 0
+            S.draw_theta(orc.supplied(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"]))
+            S.gather_f()
+            S.draw_beta(orc.supplied(z=G[f"z_beta_{it}"], u=G[f"u_beta_{it}"]))
+            S.compute_mu()
+            assert S.update_cholesky() == 0
+            S.draw_threshold(orc.supplied(z=G[f"z_thr_{it}"], u=G[f"u_thr_{it}"]))
+            st = S.state()
+            st["thresholds"] = st.pop("thr")
+            yield it, st, S.total_ll(), {b: S.diag(b)[0] for b in ("f", "theta", "beta", "thr")}
+        else:
+            S.draw_f(z=zf, u=uf)
+            S.draw_fstar(z=G[f"z_fstar_{it}"])
+            S.draw_theta(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"])
+            S.gather_f()
+            S.draw_beta(z=G[f"z_beta_{it}"], u=G[f"u_beta_{it}"])
+            S.update_cholesky_cache()
+            S.draw_threshold(z=G[f"z_thr_{it}"], u=G[f"u_thr_{it}"])
+            _, tot = S.ll_bar()
+            yield it, S.get_state(fstar=True), tot, {b: S.diag(b)[0] for b in ("f", "theta", "beta", "thr")}
+
+
+def check_against_reference(G, it, st, ll, evals, last):
+    assert np.array_equal(st["theta"], G["ref_theta"][it]), f"sweep {it}: theta differs from the reference's draw"
+    assert rel(st["beta"], G["ref_beta"][:, :, it]) < 1e-9
+    assert rel(st["thresholds"], G["ref_threshold"][:, :, it]) < 1e-9
+    assert colrel(st["f"], G["ref_f"][:, :, it]) < 1e-6  # f = rows of f* after the gather
+    assert abs(ll - G["ref_ll"][it]) <= 1e-7 * abs(G["ref_ll"][it])  # carries the f* difference; the likelihood itself is tested at 1e-10
+    # every unit made exactly the number of proposals the reference made (uniforms consumed: u, eps0, one per rejection = 1 + proposals = evals)
+    for b in ("f", "theta", "beta", "thr"):
+        nu = G[f"nu_{b}_{it}"]
+        assert np.array_equal(np.where(nu > 0, evals[b], 0), nu), f"sweep {it}: block {b} made a different number of proposals"
+    if last:
+        assert colrel(st["fstar"], G["ref_fstar_last"]) < 1e-6
+
+
+@pytest.mark.parametrize("name", SWEEPS)
+def test_oracle_replays_reference_sweeps(name):
+    G = load(name)
+    O = orc.Sampler(G["y"], int(G["C"]), G["beta_prior_sds"], G["theta_prior_sds"])
+    O.set_state(theta=np.clip(G["theta_in"], -5, 5), beta=G["beta0"], f=G["f0"], thr=G["thr0"], fstar=G["fstar0"])
+    for it, st, ll, ev in replay(G, O, "orc"):
+        check_against_reference(G, it, st, ll, ev, it == int(G["iters"]) - 1)
+
+
+# ---- GPU: the CUDA path against the same vectors -------------------------------------------------------------------
+@pytest.mark.gpu
+def test_leaves_cuda_matches_reference_vectors():
+    import gpirt_b200 as g
+
+    G = load("leaves")
+    assert rel(g.K(G["x1"], G["x2"], G["sds"]), G["K"]) < 1e-14
+    assert rel(g.K_time(G["ts"], G["ts"], 1.3, 2.0, [0.4, 0.2], "Matern"), G["K_time_matern"]) < 1e-14
+    assert rel(g.K_time(G["ts"], G["ts"], 1.3, 2.0, [0.4, 0.2], "RBF"), G["K_time_rbf"]) < 1e-14
+    from gpirt_b200.api import debug_probit
+
+    ph, _ = debug_probit(G["pnorm_x"])
+    assert np.max(np.abs(ph - G["pnorm"])) < 1e-15  # absolute: the likelihood adds 1e-6 inside the log
+    assert np.array_equal(g.threshold_to_delta(G["ll_thr"]), G["delta"])
+    assert np.array_equal(g.delta_to_threshold(G["delta"]), G["thr_back"])
+    th = G["chol_theta"]
+    A = g.K(th, th, G["chol_sds"][:, 0]) + 1e-6 * np.eye(th.size)
+    assert np.max(np.abs(g.chol(A) - G["chol_L"])) < 1e-10  # well-conditioned fixture: element-wise 1e-10
+    assert rel(g.double_solve(G["chol_L"], G["solve_X"]), G["solve_out"]) < 1e-10
+    # ll_bar_sparse through a one-item sampler
+    n, C = G["ll_f"].size, G["ll_thr"].size - 1
+    S = g.Sampler(n, 1, C)
+    S.set_data(G["ll_y"].reshape(n, 1))
+    S.set_priors(np.ones((3, 1)), np.zeros((2, n)))
+    # mu = X beta with theta = mu, beta = (0, 1, 0) reproduces the fixture's mu exactly
+    S.set_state(theta=np.clip(G["ll_mu"], -5, 5), beta=np.array([[0.0], [1.0], [0.0]]), f=G["ll_f"].reshape(n, 1), thresholds=G["ll_thr"].reshape(1, -1))
+    _, tot = S.ll_bar()
+    assert abs(tot - float(G["ll"])) <= 1e-10 * abs(float(G["ll"]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", SWEEPS)
+def test_cuda_replays_reference_sweeps(name):
+    import gpirt_b200 as g
+
+    G = load(name)
+    n, m, C = int(G["n"]), int(G["m"]), int(G["C"])
+    S = g.Sampler(n, m, C)
+    S.set_data(G["y"])
+    S.set_priors(G["beta_prior_sds"], G["theta_prior_sds"])
+    S.set_state(theta=G["theta_in"], beta=G["beta0"], f=G["f0"], thresholds=G["thr0"], fstar=G["fstar0"])  # set_state clamps theta (src/gpirtMCMC.cpp:133)
+    for it, st, ll, ev in replay(G, S, "cuda"):
+        check_against_reference(G, it, st, ll, ev, it == int(G["iters"]) - 1)

@@ -1,0 +1,134 @@
+"""Pins the CPU oracle to the REFERENCE'S OWN CODE: oracle/_ref/libgpirt_ref.so is /root/reference/src/*.cpp compiled where it
+lies against the stand-in headers of oracle/refshim (oracle/Makefile `ref`). Runs wherever that library exists (this container;
+it also travels to the GPU box as a built file); skipped otherwise — tests/test_golden.py then still checks the recorded vectors.
+
+Single OpenMP thread on both sides: the reference's RNG streams are keyed by thread id (src/gpirt.h:178-182)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import orc, ref
+from tests.problems import make_problem
+
+pytestmark = pytest.mark.skipif(not ref.available(), reason="oracle/_ref not built (needs /root/reference)")
+
+
+@pytest.fixture(autouse=True)
+def one_thread():
+    orc.set_threads(1)
+    ref.set_threads(1)
+    yield
+    orc.set_threads(os.cpu_count() or 1)
+
+
+def test_leaves_bit_identical():
+    rng = np.random.default_rng(3)
+    x1, x2, sds = rng.standard_normal(33) * 2.5, rng.standard_normal(21) * 2.5, [3.0, 3.0, 3.0]
+    assert np.array_equal(orc.K(x1, x2, sds), ref.K(x1, x2, sds))
+    ts = np.arange(6.0)
+    for kern in ("Matern", "RBF", "other"):
+        assert np.array_equal(orc.K_time(ts, ts, 0.9, 1.7, [0.2, 0.3], kern), ref.K_time(ts, ts, 0.9, 1.7, [0.2, 0.3], kern))
+    x = np.concatenate([np.linspace(-39, 9, 3000), rng.standard_normal(1000)])
+    assert np.array_equal(orc.pnorm(x), ref.pnorm(x))
+    for C in (2, 3, 7):
+        d = rng.standard_normal(C - 1)
+        t = ref.delta_to_threshold(d)
+        assert np.array_equal(orc.delta_to_threshold(d), t)
+        assert np.array_equal(orc.threshold_to_delta(t), ref.threshold_to_delta(t))
+    n = 200
+    f, mu = rng.standard_normal(n) * 2, rng.standard_normal(n)
+    y = rng.integers(1, 6, n).astype(float)
+    y[rng.random(n) < 0.1] = np.nan
+    thr = np.array([-np.inf, -1.0, -0.3, 0.4, 1.2, np.inf])
+    assert orc.ll_bar_sparse(f, y, mu, thr) == ref.ll_bar_sparse(f, y, mu, thr)
+    assert ref.ll_bar_sparse(f, np.full(n, np.nan), mu, thr) == 0.0  # an item nobody answered
+
+
+def test_cholesky_cache_and_double_solve():
+    rng = np.random.default_rng(4)
+    n = 90
+    theta = np.clip(rng.standard_normal(n), -5, 5)
+    sds = np.full((3, 4), 3.0)
+    L = ref.update_cholesky_cache(theta, sds)[0][:, :, 0]
+    Lo, info = orc.chol(orc.K(theta, theta, sds[:, 0]) + 1e-6 * np.eye(n))
+    assert info == 0 and np.array_equal(L, Lo)  # same unblocked column algorithm on both sides (LAPACK in the real reference)
+    x = rng.standard_normal(n)
+    assert np.array_equal(orc.double_solve(L, x), ref.double_solve(L, x)[:, 0])
+    with pytest.raises(RuntimeError, match="chol"):  # arma::chol throws on a non-PD matrix -> R error
+        ref.update_cholesky_cache(np.array([0.0, 0.0]), np.array([[0.0], [0.0], [np.nan]]))
+
+
+@pytest.mark.parametrize("C,seed", [(2, 1), (5, 2)])
+def test_blocks_same_state_and_same_rng_consumption(C, seed):
+    n, m = 70, 9
+    P = make_problem(n, m, C, seed=seed, missing=0.15, on_grid=True)
+    rng = P["rng"]
+    y, bps, tps = P["y"], P["beta_prior_sds"], np.asfortranarray(rng.random((2, n)))
+    theta, beta, thr = P["theta0"], P["beta0"], P["thr0"]
+    f = np.asfortranarray(rng.standard_normal((n, m)))
+    fstar = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+
+    def fresh():
+        O = orc.Sampler(y, C, bps, tps)
+        O.set_state(theta=theta, beta=beta, f=f, thr=thr, fstar=fstar)
+        O.compute_mu()
+        assert O.update_cholesky() == 0
+        return O
+
+    mu, mu_star = fresh().mu()
+    O = fresh(); O.mt_seed_all(777); O.draw_f(orc.mt())
+    assert np.array_equal(O.state()["f"], ref.draw_f(777, f, theta, y, bps, mu, thr)[:, :, 0])
+    O = fresh(); O.mt_seed_all(778); O.draw_theta(orc.mt())
+    assert np.array_equal(O.state()["theta"], ref.draw_theta(778, y, theta, tps, fstar, mu_star, thr, bps)[:, 0])
+    O = fresh(); O.mt_seed_all(779); O.draw_beta(orc.mt())
+    assert np.array_equal(O.state()["beta"], ref.draw_beta(779, beta, theta, y, f, np.zeros((3, m)), bps, thr)[:, :, 0])
+    O = fresh(); O.mt_seed_all(780); O.draw_threshold(orc.mt())
+    assert np.array_equal(O.state()["thr"], ref.draw_threshold(780, thr, y, f, mu)[:, :, 0])
+    O = fresh(); O.mt_seed_all(781); assert O.draw_fstar(orc.mt()) == 0
+    R = ref.draw_fstar(781, f, theta, bps, mu_star)[:, :, 0]
+    assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-5  # K^-1 f is kappa-limited (kappa ~ 1e10 with sds = 3)
+
+
+def test_gpirtMCMC_same_draws_over_several_sweeps():
+    n, m, C, iters = 64, 10, 5, 5
+    P = make_problem(n, m, C, seed=9, missing=0.1)
+    rng = np.random.default_rng(10)
+    z = rng.standard_normal(3 * m + n * m)
+    bpm, bps, tpm, tps = np.zeros((3, m)), P["beta_prior_sds"], np.zeros((2, n)), P["theta_prior_sds"]
+    R = ref.gpirtMCMC(P["y"], P["theta0"], iters, 1, 1, bpm, bps, tpm, tps, 1.0, 10.0, "Matern", P["thr0"], 0, z, store_f=True)
+    theta0 = np.clip(P["theta0"], -5, 5)
+    beta0 = bpm + bps * z[:3 * m].reshape(m, 3).T
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.stack([L0 @ z[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1)
+    O = orc.Sampler(P["y"], C, bps, tps)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.draw_fstar(orc.mt())  # initial draw on the unseeded generators (src/gpirtMCMC.cpp:227)
+    info, th, ll = O.run_mt(0, iters + 1)
+    assert info == 0
+    assert np.array_equal(th[:, 1:].T, R["theta"][:, :, 0])  # burn-in sweep dropped by the reference (src/gpirtMCMC.cpp:334)
+    assert np.allclose(ll[1:], R["ll"], rtol=1e-9, atol=0)
+    s = O.state()
+    assert np.array_equal(s["beta"], R["beta"][:, :, 0, -1])
+    assert np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, 0, -1])
+    assert np.max(np.abs(s["f"] - R["f"][:, :, 0, -1])) < 1e-5
+
+
+def test_recover_fstar():
+    n, m, C = 50, 6, 3
+    P = make_problem(n, m, C, seed=12, missing=0.1, on_grid=True)
+    rng = P["rng"]
+    f = np.asfortranarray(rng.standard_normal((n, m)))
+    beta2 = np.asfortranarray(rng.standard_normal((2, m)))
+    bps3 = np.vstack([np.full((2, m), 0.5), np.zeros((1, m))])  # third row: what K() reads past the 2-row matrix is taken as 0
+    R = ref.recover_fstar(321, f, P["y"], P["theta0"], beta2, P["thr0"], np.zeros((3, m)), bps3)[:, :, 0]
+    O = orc.Sampler(P["y"], C, bps3, None, p_beta=2)
+    O.set_state(theta=P["theta0"], beta=beta2, f=f, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.mt_seed_all(321)
+    O.draw_f(orc.mt())
+    assert O.draw_fstar(orc.mt()) == 0
+    assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-6
