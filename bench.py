@@ -209,6 +209,7 @@ def ours(args):
         "gemm_LZ": ("tensor", 1.0 * n * n * m_loc), "gemm_FtW": ("tensor", 2.0 * N * n * m_loc), "gemm_ZLpost": ("tensor", 1.0 * N * N * m_loc),
         "gemm_Kpost": ("tensor", 1.0 * n * N * N), "chol_K": ("tensor", n ** 3 / 3.0), "chol_Kpost": ("tensor", N ** 3 / 3.0),
         "trsm_kstar": ("tensor", 1.0 * n * n * N), "trsm_W": ("tensor", 1.0 * n * n * N),
+        "trtri": ("tensor", n ** 3 / 3.0), "gemm_tmp": ("tensor", 1.0 * n * n * N), "gemm_W": ("tensor", 1.0 * n * n * N),
     }
     peaks, peak_src = measured_peaks()
     kernels = []

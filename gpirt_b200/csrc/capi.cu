@@ -180,7 +180,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     cudaSetDevice(h->cfg.device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
-                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab};
+                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab, h->Linv, h->W2, h->tri_scratch};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int b = 0; b < 5; ++b) {
@@ -198,6 +198,13 @@ int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream) {
     CU(cudaStreamSynchronize(h->stream));
     if (h->own_stream) { cudaStreamDestroy(h->stream); h->own_stream = false; }
     h->stream = (cudaStream_t)cuda_stream;
+    return GPIRT_OK;
+}
+
+int gpirt_set_solver(gpirt_sampler* h, int solver) {
+    CHECK_H(h);
+    if (solver != 0 && solver != 1) return fail(GPIRT_ERR_INVALID, "solver %d: 0 (blocked substitution) or 1 (block inverse)", solver);
+    h->solver = solver;
     return GPIRT_OK;
 }
 
@@ -490,11 +497,28 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     const int n = h->n, N = NGRID;
     // shared over items: k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I, L_post = chol(K_post)
     SEC(h, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
-    SEC(h, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+    const double* tmp = h->W;  // L^-1 k*
+    if (h->solver == 1) {
+        // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
+        if (!h->Linv) {
+            TRY(dalloc(&h->Linv, (size_t)h->ldn * h->n));
+            TRY(dalloc(&h->W2, (size_t)h->ldn * NGRID));
+            TRY(dalloc(&h->tri_scratch, trtri_scratch_elems(h->n)));
+            CU(cudaDeviceSynchronize());  // dalloc zero-fills on the legacy stream
+        }
+        SEC(h, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
+        GemmArgs g{};
+        g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->W2; g.ldc = h->ldn;
+        g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
+        SEC(h, "gemm_tmp", CU(gemm_f64(st, false, false, g)));
+        tmp = h->W2;
+    } else {
+        SEC(h, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+    }
     CU(build_K(st, h->tstar, N, h->tstar, N, h->sds0, h->Kpost, h->ldN, 0.0));
     {
         GemmArgs g{};
-        g.M = N; g.N = N; g.K = n; g.A = h->W; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->Kpost; g.ldc = h->ldN;
+        g.M = N; g.N = N; g.K = n; g.A = tmp; g.lda = h->ldn; g.B = tmp; g.ldb = h->ldn; g.C = h->Kpost; g.ldc = h->ldN;
         g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
         SEC(h, "gemm_Kpost", CU(gemm_f64(st, true, false, g)));
     }
@@ -503,7 +527,14 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     CU(cudaGetLastError());
     SEC(h, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info)));
     // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
-    SEC(h, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+    if (h->solver == 1) {
+        GemmArgs g{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
+        g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W2; g.ldb = h->ldn; g.C = h->W; g.ldc = h->ldn;
+        g.alpha = 1.0; g.beta = 0.0; g.a_upper = 1;
+        SEC(h, "gemm_W", CU(gemm_f64(st, true, false, g)));
+    } else {
+        SEC(h, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+    }
     if (h->m_local == 0) return GPIRT_OK;
     double* chunk = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk;
     {

@@ -31,6 +31,12 @@ struct GemmArgs {
     int a_lower;      // op(A)[m][k] == 0 for k > m  (k loop of a row block stops at its last row)
     int b_upper;      // op(B)[k][n] == 0 for k > n  (k loop of a column block stops at its last column)
     int lower_only;   // skip output tiles strictly above the diagonal (symmetric updates)
+    int a_upper;      // op(A)[m][k] == 0 for k < m  (k loop of a row block starts at its first row)
+    int b_lower;      // op(B)[k][n] == 0 for k < n  (k loop of a column block starts at its first column)
+    // batching over blockIdx.z: operand z sits at base + z * stride (elements); the last batch may be ragged
+    int batch;        // 0 or 1: a single product
+    long long strideA, strideB, strideC;
+    int M_last, N_last, K_last;  // extents of batch (batch-1) when > 0, else M / N / K
 };
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
@@ -80,21 +86,34 @@ gemm_f64_kernel(GemmArgs g) {
     using Cfg = GemmCfg<BM, BN, BK, WM, WN, STAGES, TA, TB>;
     extern __shared__ __align__(16) double smem[];
     const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    if (g.batch > 1) {
+        const int z = blockIdx.z;
+        g.A += z * g.strideA; g.B += z * g.strideB; g.C += z * g.strideC;
+        if (z == g.batch - 1) {
+            if (g.M_last > 0) g.M = g.M_last;
+            if (g.N_last > 0) g.N = g.N_last;
+            if (g.K_last > 0) g.K = g.K_last;
+        }
+        if (m0 >= g.M || n0 >= g.N) return;
+    }
     if (g.lower_only && n0 >= m0 + BM) return;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int wm0 = (warp % Cfg::WARPS_M) * WM, wn0 = (warp / Cfg::WARPS_M) * WN;
     const int grp = lane >> 2, tig = lane & 3;
 
-    int k_end = g.K;
+    int k_end = g.K, k_begin = 0;
     if (g.a_lower) k_end = min(k_end, m0 + BM);
     if (g.b_upper) k_end = min(k_end, n0 + BN);
-    const int KT = (k_end + BK - 1) / BK;
+    if (g.a_upper) k_begin = max(k_begin, m0);
+    if (g.b_lower) k_begin = max(k_begin, n0);
+    k_begin = (k_begin / BK) * BK;
+    const int KT = k_end > k_begin ? (k_end - k_begin + BK - 1) / BK : 0;
 
     double* As = smem;
     double* Bs = smem + STAGES * Cfg::A_ELEMS;
 
     auto issue = [&](int kt, int stage) {
-        const int k0 = kt * BK;
+        const int k0 = k_begin + kt * BK;
         double* a = As + stage * Cfg::A_ELEMS;
         double* b = Bs + stage * Cfg::B_ELEMS;
         if (TA)  // op(A)[m][k] = A[k + m*lda]: rows are m, contiguous k

@@ -21,7 +21,7 @@ static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN);
+    dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, g.batch > 1 ? g.batch : 1);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(g);
     ++g_kernel_launches;
     return cudaGetLastError();
@@ -30,7 +30,7 @@ static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
 template <bool TA, bool TB>
 static cudaError_t gemm_pick(cudaStream_t st, const GemmArgs& g) {
     // big tiles only when they still fill the 148 SMs; otherwise 64x64 tiles (4x the CTAs)
-    long tiles128 = (long)((g.M + 127) / 128) * ((g.N + 127) / 128);
+    long tiles128 = (long)((g.M + 127) / 128) * ((g.N + 127) / 128) * (g.batch > 1 ? g.batch : 1);
     if (g.lower_only) tiles128 = tiles128 / 2 + 1;
     if (tiles128 >= 2 * 148 && g.N >= 128 && g.M >= 128) return launch_gemm<128, 128, 16, 64, 32, 3, TA, TB>(st, g);
     return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, g);
@@ -239,34 +239,10 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
         }
 }
 
-// Diagonal-block solves for many right-hand sides: CTA b solves L11 X = B (or L11^T X = B) for 64 columns of B.
+// Substitution with a 64 x 64 triangular block held in shared memory: on entry a[p][q] = B(row tr + 16p, column tc + 16q),
+// on exit the solution of L11 X = B (TRANS false) or L11^T X = B (TRANS true). One __syncthreads per eliminated row.
 template <bool TRANS>
-__global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __restrict__ L11, int ldl, int kb,
-                                                            double* __restrict__ B, int ldb, int nrhs) {
-    constexpr int NB = CHOL_NB;
-    __shared__ double Ls[NB][NB + 1];
-    __shared__ double vec[2][NB];
-    __shared__ double inv_diag[NB];
-    const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
-            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
-        }
-    const int c0 = blockIdx.x * 64;
-    double a[4][4];  // a[p][q] = X(row tr + 16p, column c0 + tc + 16q)
-#pragma unroll
-    for (int q = 0; q < 4; ++q)
-#pragma unroll
-        for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
-            a[p][q] = (r < kb && c < nrhs) ? B[(size_t)c * ldb + r] : 0.0;
-        }
-    __syncthreads();
-    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
-    __syncthreads();
+__device__ __forceinline__ void tile_solve(double (&a)[4][4], double (*Ls)[CHOL_NB + 1], double (*vec)[CHOL_NB], const double* inv_diag, int tr, int tc) {
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
         const int kq = TRANS ? 3 - s : s;
@@ -300,12 +276,77 @@ __global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __rest
             }
         }
     }
+}
+
+// Diagonal-block solves for many right-hand sides: CTA b solves L11 X = B (or L11^T X = B) for 64 columns of B.
+template <bool TRANS>
+__global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __restrict__ L11, int ldl, int kb,
+                                                            double* __restrict__ B, int ldb, int nrhs) {
+    constexpr int NB = CHOL_NB;
+    __shared__ double Ls[NB][NB + 1];
+    __shared__ double vec[2][NB];
+    __shared__ double inv_diag[NB];
+    const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
+        }
+    const int c0 = blockIdx.x * 64;
+    double a[4][4];  // a[p][q] = X(row tr + 16p, column c0 + tc + 16q)
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
+            a[p][q] = (r < kb && c < nrhs) ? B[(size_t)c * ldb + r] : 0.0;
+        }
+    __syncthreads();
+    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+    __syncthreads();
+    tile_solve<TRANS>(a, Ls, vec, inv_diag, tr, tc);
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
             const int r = tr + 16 * p, c = c0 + tc + 16 * q;
             if (r < kb && c < nrhs) B[(size_t)c * ldb + r] = a[p][q];
+        }
+}
+
+// Inverses of the 64 x 64 diagonal blocks of a lower-triangular L, one CTA per block: L_kk X = I by substitution.
+// Writes the whole block of Linv (zeros above the diagonal).
+__global__ void __launch_bounds__(TILE_THREADS) k_trtri_diag(const double* __restrict__ L, int ld, int n, double* __restrict__ Linv, int ldi) {
+    constexpr int NB = CHOL_NB;
+    __shared__ double Ls[NB][NB + 1];
+    __shared__ double vec[2][NB];
+    __shared__ double inv_diag[NB];
+    const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
+    const int k0 = blockIdx.x * NB;
+    const int kb = min(NB, n - k0);
+    const double* L11 = L + (size_t)k0 * ld + k0;
+    double a[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ld + r] : 0.0) : (r == c ? 1.0 : 0.0);
+            a[p][q] = (r == c) ? 1.0 : 0.0;
+        }
+    __syncthreads();
+    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+    __syncthreads();
+    tile_solve<false>(a, Ls, vec, inv_diag, tr, tc);
+    double* out = Linv + (size_t)k0 * ldi + k0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            const int r = tr + 16 * p, c = tc + 16 * q;
+            if (r < kb && c < kb) out[(size_t)c * ldi + r] = (c <= r) ? a[p][q] : 0.0;
         }
 }
 
@@ -379,6 +420,50 @@ cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, 
             cudaError_t e = gemm_f64(st, true, false, g);
             if (e != cudaSuccess) return e;
         }
+    }
+    return cudaGetLastError();
+}
+
+size_t trtri_scratch_elems(int n) {
+    size_t need = 1;
+    for (int b = CHOL_NB; b < n; b *= 2) {
+        const size_t pairs = ((size_t)n + 2 * b - 1) / (2 * b);
+        need = need > pairs * b * b ? need : pairs * b * b;
+    }
+    return need;
+}
+
+// Linv = L^-1 for lower-triangular L. Diagonal 64-blocks by substitution (one launch, all blocks in parallel), then log2(n/64)
+// merge levels: inv([A 0; C B]) = [A^-1 0; -B^-1 C A^-1  B^-1], each level two batched GEMMs over all pairs. No sequential chain
+// over the n/64 block rows, unlike a blocked TRSM: 1 + 2*levels launches in total. Linv's strict upper triangle must be zero on
+// entry (it is never written).
+cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch) {
+    constexpr int NB = CHOL_NB;
+    k_trtri_diag<<<(n + NB - 1) / NB, TILE_THREADS, 0, st>>>(L, ld, n, Linv, ldi);
+    ++g_kernel_launches;
+    for (int b = NB; b < n; b *= 2) {
+        // pair z covers rows/cols [z*2b, z*2b + 2b); it exists when its second half is not empty
+        int pairs = 0, last_b2 = 0;
+        for (int r0 = 0; r0 + b < n; r0 += 2 * b) { ++pairs; last_b2 = (n - r0 - b < b) ? n - r0 - b : b; }
+        if (pairs == 0) break;
+        GemmArgs g{};  // T_z = C_z * A_z^-1   (C_z = L[r0+b.., r0..], A_z^-1 lower triangular)
+        g.M = b; g.N = b; g.K = b;
+        g.A = L + b; g.lda = ld; g.strideA = (long long)2 * b * ((long long)ld + 1);
+        g.B = Linv; g.ldb = ldi; g.strideB = (long long)2 * b * ((long long)ldi + 1); g.b_lower = 1;
+        g.C = scratch; g.ldc = b; g.strideC = (long long)b * b;
+        g.alpha = 1.0; g.beta = 0.0; g.batch = pairs > 1 ? pairs : 0; g.M_last = last_b2;
+        if (pairs == 1) g.M = last_b2;
+        cudaError_t e = gemm_f64(st, false, false, g);
+        if (e != cudaSuccess) return e;
+        GemmArgs h{};  // Linv[r0+b.., r0..] = -B_z^-1 * T_z   (B_z^-1 lower triangular)
+        h.M = b; h.N = b; h.K = b;
+        h.A = Linv + (size_t)b * ldi + b; h.lda = ldi; h.strideA = (long long)2 * b * ((long long)ldi + 1); h.a_lower = 1;
+        h.B = scratch; h.ldb = b; h.strideB = (long long)b * b;
+        h.C = Linv + b; h.ldc = ldi; h.strideC = (long long)2 * b * ((long long)ldi + 1);
+        h.alpha = -1.0; h.beta = 0.0; h.batch = pairs > 1 ? pairs : 0; h.M_last = last_b2; h.K_last = last_b2;
+        if (pairs == 1) { h.M = last_b2; h.K = last_b2; }
+        e = gemm_f64(st, false, false, h);
+        if (e != cudaSuccess) return e;
     }
     return cudaGetLastError();
 }

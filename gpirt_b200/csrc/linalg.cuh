@@ -22,4 +22,8 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 
+// Linv <- L^-1 (lower triangular, strict upper triangle of Linv must already be zero); scratch holds trtri_scratch_elems(n) doubles.
+size_t trtri_scratch_elems(int n);
+cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch);
+
 }  // namespace gpirt

@@ -15,6 +15,7 @@
 //   L      f64   [ldn][n]                  chol(K(theta,theta) + 1e-6 I)
 //   W      f64   [ldn][NGRID]              k*, then L^-1 k*, then K^-1 k*
 //   Kpost  f64   [ldN][NGRID]              K** - tmp^T tmp + 1e-6 I, then its Cholesky factor
+//   Linv   f64   [ldn][n]                  L^-1 (solver 1), W2 [ldn][NGRID] = L^-1 k*
 #pragma once
 #include <cuda_runtime.h>
 
@@ -44,6 +45,8 @@ struct gpirt_sampler {
     double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;
     double *f = nullptr, *nu = nullptr, *zbuf = nullptr, *fstar = nullptr;
     double *L = nullptr, *W = nullptr, *Kpost = nullptr, *tstar = nullptr;
+    double *Linv = nullptr, *W2 = nullptr, *tri_scratch = nullptr;  // block-inverse solver: L^-1, L^-1 k*, merge scratch (allocated on first use)
+    int solver = 1;  // 0: blocked substitution TRSM (backward stable), 1: explicit L^-1 by parallel block inversion + GEMMs
     double* theta_tab = nullptr;  // [NGRID][m_total][C] per-sweep table of theta-step terms (allocated on first use)
     double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};

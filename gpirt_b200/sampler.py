@@ -158,6 +158,10 @@ class Sampler:
     def set_iter(self, it):
         check(self._L.gpirt_set_iter(self._h, C.c_uint32(it)))
 
+    def set_solver(self, solver):
+        """0: blocked substitution for L^-1 k* / L^-T(.) in draw_fstar; 1: explicit block inverse + GEMMs (default)"""
+        check(self._L.gpirt_set_solver(self._h, int(solver)))
+
     def set_stream(self, cuda_stream):
         check(self._L.gpirt_set_stream(self._h, C.c_void_p(cuda_stream)))
 

@@ -116,6 +116,10 @@ int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, c
 int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, double* thresholds, double* fstar);
 int gpirt_get_L(gpirt_sampler* h, double* L /* n x n, upper triangle zero */);
 int gpirt_set_iter(gpirt_sampler* h, uint32_t iter);         /* sweep counter used to key the Philox streams */
+/* How draw_fstar applies L^-1 / L^-T to k* (solve(trimatl(L), kstar) and double_solve, src/draw-fstar.cpp:30,51, src/cholesky-cache.cpp:4-9):
+ * 0 = blocked forward/back substitution (backward stable, n/64 dependent steps); 1 = explicit L^-1 by parallel block inversion, then
+ * GEMMs (default; forward error kappa(L)*eps like substitution's bound, no dependent chain). */
+int gpirt_set_solver(gpirt_sampler* h, int solver);
 int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin); /* per unit: 1+proposals, min |ll'-log_y| */
 int gpirt_sync(gpirt_sampler* h);                            /* wait for queued work; surfaces deferred errors */
 /* initial values the reference draws inside gpirtMCMC (src/gpirtMCMC.cpp:149-163): beta0 ~ N(prior mean, prior sd)

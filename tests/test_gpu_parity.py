@@ -242,3 +242,35 @@ def test_supplied_stream_overrun_is_reported():
     with pytest.raises(gpirt_b200.GpirtError) as e:  # u ~ 1: nothing but the current state is acceptable, stream of 2 runs dry
         S.draw_f(u=u, nu=np.ones((n, m)))
     assert e.value.code == 7
+
+
+@pytest.mark.parametrize("n", [64, 150, 333, 700])
+def test_draw_fstar_block_inverse_solver_matches_substitution(n):
+    """solver 1 (explicit L^-1 by parallel block inversion, ragged sizes, several merge levels) against solver 0 (blocked
+    forward/back substitution) and the oracle, default priors (kappa(K) ~ 1e10): norm-wise per item column."""
+    m, C = 10, 4
+    P = make_problem(n, m, C, seed=71, on_grid=True)
+    rng = P["rng"]
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    z = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+    out = {}
+    for solver in (0, 1):
+        S = gpirt_b200.Sampler(n, m, C)
+        S.set_solver(solver)
+        S.set_data(P["y"])
+        S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+        S.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thresholds=P["thr0"])
+        S.draw_fstar(z=z)
+        out[solver] = S.get_state(fstar=True)["fstar"]
+        S.close()
+    O = orc.Sampler(P["y"], C, P["beta_prior_sds"], P["theta_prior_sds"])
+    O.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    assert O.draw_fstar(orc.supplied(z=z)) == 0
+    want = O.state()["fstar"]
+    scale = np.max(np.abs(want), axis=0)
+    for solver in (0, 1):
+        # f0 is white noise, so K^-1 f0 is as large as kappa allows: two correct fp64 codes differ by ~kappa*eps*|f*| here
+        assert np.max(np.max(np.abs(out[solver] - want), axis=0) / scale) < 5e-5, f"solver {solver}"
+    assert np.max(np.max(np.abs(out[1] - out[0]), axis=0) / scale) < 5e-5
