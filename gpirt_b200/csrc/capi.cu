@@ -27,6 +27,11 @@ static int fail(int code, const char* fmt, ...) {
     } while (0)
 #define CHECK_H(h) \
     if (!(h)) return fail(GPIRT_ERR_INVALID, "NULL sampler handle")
+#define TRY_(x)                  \
+    do {                         \
+        int rc_ = (x);           \
+        if (rc_ != GPIRT_OK) return rc_; \
+    } while (0)
 
 static int select_device(int device) {
     int count = 0;
@@ -40,20 +45,42 @@ static int select_device(int device) {
 
 // SEC(h, "name", launch): times `launch` with CUDA events when profiling is on (never in the timed bench pass)
 struct SecScope {
-    gpirt_sampler* h; bool on; gpirt_sampler::Pending p;
-    SecScope(gpirt_sampler* h_, const char* name) : h(h_), on(h_->profiling) {
+    gpirt_sampler* h; bool on; gpirt_sampler::Pending p; cudaStream_t st;
+    SecScope(gpirt_sampler* h_, const char* name, cudaStream_t st_) : h(h_), on(h_->profiling), st(st_) {
         if (!on) return;
         p.name = name;
         cudaEventCreate(&p.a); cudaEventCreate(&p.b);
-        cudaEventRecord(p.a, h->stream);
+        cudaEventRecord(p.a, st);
     }
     ~SecScope() {
         if (!on) return;
-        cudaEventRecord(p.b, h->stream);
+        cudaEventRecord(p.b, st);
         h->pending.push_back(p);
     }
 };
-#define SEC(h, name, call) do { SecScope sec_(h, name); call; } while (0)
+#define SEC(h, name, call) do { SecScope sec_(h, name, (h)->stream); call; } while (0)
+#define SEC_ST(h, st, name, call) do { SecScope sec_(h, name, st); call; } while (0)
+
+// main stream joins the side stream's work (no-ops when nothing is in flight)
+static int wait_L(gpirt_sampler* h) {
+    if (h->pending_L) {
+        CU(cudaStreamWaitEvent(h->stream, h->ev_L, 0));
+        h->pending_L = false;
+    }
+    return GPIRT_OK;
+}
+static int wait_shared(gpirt_sampler* h) {
+    if (h->pending_shared) {
+        CU(cudaStreamWaitEvent(h->stream, h->ev_shared, 0));  // recorded after ev_L on the same stream
+        h->pending_shared = false;
+        h->pending_L = false;
+    }
+    return GPIRT_OK;
+}
+static int quiesce(gpirt_sampler* h) {
+    TRY_(wait_L(h));
+    return wait_shared(h);
+}
 
 template <class T>
 static int dalloc(T** p, size_t count) {
@@ -143,6 +170,14 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
 
     CU(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     h->own_stream = true;
+    {
+        int lo = 0, hi = 0;
+        CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        CU(cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi));
+        CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
+    }
     const size_t mt = (size_t)h->world * h->m_chunk;
     TRY(dalloc(&h->y_im, (size_t)h->ldy * std::max(h->m_local, 1)));
     TRY(dalloc(&h->y_rm, (size_t)h->ldm * std::max(h->n_local, 1)));
@@ -178,7 +213,12 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
 int gpirt_destroy(gpirt_sampler* h) {
     if (!h) return GPIRT_OK;
     cudaSetDevice(h->cfg.device);
+    if (h->side) cudaStreamSynchronize(h->side);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+    if (h->ev_L) cudaEventDestroy(h->ev_L);
+    if (h->ev_shared) cudaEventDestroy(h->ev_shared);
+    if (h->side) cudaStreamDestroy(h->side);
     void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
                     h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab, h->Linv, h->W2, h->tri_scratch};
     for (void* p : ptrs)
@@ -195,6 +235,7 @@ int gpirt_destroy(gpirt_sampler* h) {
 int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
+    TRY(quiesce(h));
     CU(cudaStreamSynchronize(h->stream));
     if (h->own_stream) { cudaStreamDestroy(h->stream); h->own_stream = false; }
     h->stream = (cudaStream_t)cuda_stream;
@@ -205,6 +246,13 @@ int gpirt_set_solver(gpirt_sampler* h, int solver) {
     CHECK_H(h);
     if (solver != 0 && solver != 1) return fail(GPIRT_ERR_INVALID, "solver %d: 0 (blocked substitution) or 1 (block inverse)", solver);
     h->solver = solver;
+    return GPIRT_OK;
+}
+
+int gpirt_set_overlap(gpirt_sampler* h, int on) {
+    CHECK_H(h);
+    TRY(quiesce(h));
+    h->overlap = on != 0;
     return GPIRT_OK;
 }
 
@@ -219,6 +267,7 @@ int gpirt_set_iter(gpirt_sampler* h, uint32_t iter) {
 // ---- deferred error flags ------------------------------------------------------------------------
 static int check_flags(gpirt_sampler* h) {
     DevFlags fl;
+    TRY(quiesce(h));
     CU(cudaMemcpyAsync(&fl, h->flags, sizeof(fl), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     if (fl.chol_info || fl.chol_post_info || fl.overrun || fl.stalled || fl.bad_code) {
@@ -305,7 +354,8 @@ int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds, const doubl
     if (beta_prior_sds) {
         CU(cudaMemcpyAsync(h->sds, beta_prior_sds, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, h->stream));
         for (int q = 0; q < 3; ++q) h->sds0[q] = beta_prior_sds[q];  // column 0 feeds every K() call
-        h->chol_valid = false;
+        TRY(quiesce(h));
+        h->chol_valid = h->shared_valid = false;
     }
     if (theta_prior_sds) CU(cudaMemcpyAsync(h->tps, theta_prior_sds, 2 * (size_t)h->n * 8, cudaMemcpyHostToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));
@@ -318,9 +368,10 @@ int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, c
     CU(cudaSetDevice(h->cfg.device));
     cudaStream_t st = h->stream;
     if (theta) {
+        TRY(quiesce(h));
         CU(cudaMemcpyAsync(h->theta, theta, (size_t)h->n * 8, cudaMemcpyHostToDevice, st));
         CU(launch_clamp_theta(st, h->theta, h->n));
-        h->chol_valid = false;
+        h->chol_valid = h->shared_valid = false;
     }
     if (beta) {  // p_beta x m_total -> 3 x m_total (third row zero when p_beta == 2)
         std::vector<double> b3(3 * (size_t)h->m_total, 0.0);
@@ -399,6 +450,7 @@ int gpirt_get_L(gpirt_sampler* h, double* L) {
     CHECK_H(h);
     if (!L) return fail(GPIRT_ERR_INVALID, "get_L: NULL output");
     CU(cudaSetDevice(h->cfg.device));
+    if (!h->chol_valid) return fail(GPIRT_ERR_INVALID, "get_L: the Cholesky cache is stale (theta changed); call gpirt_update_cholesky_cache");
     TRY(check_flags(h));
     CU(cudaMemcpy2DAsync(L, (size_t)h->n * 8, h->L, (size_t)h->ldn * 8, (size_t)h->n * 8, h->n, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
@@ -451,15 +503,21 @@ static int need_data(gpirt_sampler* h) {
     return GPIRT_OK;
 }
 
-static int do_update_cholesky(gpirt_sampler* h) {  // src/cholesky-cache.cpp:20-24
-    SEC(h, "K_build", CU(build_K(h->stream, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
-    SEC(h, "chol_K", CU(chol_lower_blocked(h->stream, h->L, h->ldn, h->n, &h->flags->chol_info)));
+static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
+    SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
+    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info)));
     h->chol_valid = true;
+    h->shared_valid = false;
     return GPIRT_OK;
+}
+static int do_update_cholesky(gpirt_sampler* h) {
+    TRY(quiesce(h));
+    return do_update_cholesky(h, h->stream);
 }
 
 static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
     if (!h->chol_valid) TRY(do_update_cholesky(h));  // the reference refactorises here (src/draw-f.cpp:59); same theta, same L
+    TRY(wait_L(h));
     cudaStream_t st = h->stream;
     ItemView v = item_view(h);
     const double* dz; long long zs;
@@ -491,12 +549,11 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
     return GPIRT_OK;
 }
 
-static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/draw-fstar.cpp:18-57
-    if (!h->chol_valid) TRY(do_update_cholesky(h));
-    cudaStream_t st = h->stream;
+// The part of draw_fstar shared by all items (src/draw-fstar.cpp:26-36): k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I,
+// L_post = chol(K_post), and W = L^-T tmp = K^-1 k*. Depends on theta only, so a sweep runs it on the side stream.
+static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
     const int n = h->n, N = NGRID;
-    // shared over items: k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I, L_post = chol(K_post)
-    SEC(h, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
+    SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
     const double* tmp = h->W;  // L^-1 k*
     if (h->solver == 1) {
         // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
@@ -506,35 +563,63 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
             TRY(dalloc(&h->tri_scratch, trtri_scratch_elems(h->n)));
             CU(cudaDeviceSynchronize());  // dalloc zero-fills on the legacy stream
         }
-        SEC(h, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
+        SEC_ST(h, st, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
         GemmArgs g{};
         g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->W2; g.ldc = h->ldn;
         g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
-        SEC(h, "gemm_tmp", CU(gemm_f64(st, false, false, g)));
+        SEC_ST(h, st, "gemm_tmp", CU(gemm_f64(st, false, false, g)));
         tmp = h->W2;
     } else {
-        SEC(h, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+        SEC_ST(h, st, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
     }
     CU(build_K(st, h->tstar, N, h->tstar, N, h->sds0, h->Kpost, h->ldN, 0.0));
     {
         GemmArgs g{};
         g.M = N; g.N = N; g.K = n; g.A = tmp; g.lda = h->ldn; g.B = tmp; g.ldb = h->ldn; g.C = h->Kpost; g.ldc = h->ldN;
         g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
-        SEC(h, "gemm_Kpost", CU(gemm_f64(st, true, false, g)));
+        SEC_ST(h, st, "gemm_Kpost", CU(gemm_f64(st, true, false, g)));
     }
     k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    SEC(h, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info)));
+    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info)));
     // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
     if (h->solver == 1) {
         GemmArgs g{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
         g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W2; g.ldb = h->ldn; g.C = h->W; g.ldc = h->ldn;
         g.alpha = 1.0; g.beta = 0.0; g.a_upper = 1;
-        SEC(h, "gemm_W", CU(gemm_f64(st, true, false, g)));
+        SEC_ST(h, st, "gemm_W", CU(gemm_f64(st, true, false, g)));
     } else {
-        SEC(h, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+        SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
     }
+    h->shared_valid = true;
+    return GPIRT_OK;
+}
+
+// After a new theta is committed inside a sweep: K, chol(K) and the shared draw_fstar terms of the NEXT sweep start on the side
+// stream right away (the reference refactorises at this point too, src/gpirtMCMC.cpp:314). The main stream joins at first use.
+static int launch_theta_chain(gpirt_sampler* h) {
+    if (!h->overlap || h->profiling) return GPIRT_OK;  // serial order: update_cholesky runs where the reference has it
+    CU(cudaEventRecord(h->ev_fork, h->stream));
+    CU(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
+    TRY(do_update_cholesky(h, h->side));
+    CU(cudaEventRecord(h->ev_L, h->side));
+    h->pending_L = true;
+    TRY(prep_fstar_shared(h, h->side));
+    CU(cudaEventRecord(h->ev_shared, h->side));
+    h->pending_shared = true;
+    return GPIRT_OK;
+}
+
+static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/draw-fstar.cpp:18-57
+    if (!h->chol_valid) TRY(do_update_cholesky(h));
+    if (!h->shared_valid) {
+        TRY(quiesce(h));
+        TRY(prep_fstar_shared(h, h->stream));
+    }
+    TRY(wait_shared(h));
+    cudaStream_t st = h->stream;
+    const int n = h->n, N = NGRID;
     if (h->m_local == 0) return GPIRT_OK;
     double* chunk = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk;
     {
@@ -583,8 +668,9 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
 }
 
 static int commit_theta(gpirt_sampler* h) {  // theta.swap(theta_new), src/gpirtMCMC.cpp:284
+    TRY(quiesce(h));  // nothing of the previous theta's chain may still be reading it
     CU(cudaMemcpyAsync(h->theta, h->theta_x, (size_t)h->n * 8, cudaMemcpyDeviceToDevice, h->stream));
-    h->chol_valid = false;
+    h->chol_valid = h->shared_valid = false;
     return GPIRT_OK;
 }
 
@@ -665,9 +751,10 @@ int gpirt_sweep_phase_theta(gpirt_sampler* h) { ENTER(h); return do_draw_theta(h
 int gpirt_sweep_phase_close(gpirt_sampler* h) {
     ENTER(h);
     TRY(commit_theta(h));
+    TRY(launch_theta_chain(h));
     TRY(do_gather_f(h));
     TRY(do_small_ess(h, IB_BETA, nullptr));
-    TRY(do_update_cholesky(h));
+    if (!h->chol_valid) TRY(do_update_cholesky(h));
     TRY(do_small_ess(h, IB_THR, nullptr));
     TRY(do_item_ll(h));
     h->iter += 1;
@@ -779,6 +866,7 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
     }
     if (draw_f && h->m_local > 0) {
         if (!h->chol_valid) TRY(do_update_cholesky(h));
+        TRY(wait_L(h));
         CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_INIT_F, h->item0));
         GemmArgs g{};
         g.M = h->n; g.N = h->m_local; g.K = h->n;
@@ -796,6 +884,8 @@ extern "C" {
 // Per-section device timing for bench.py's roofline block: CUDA events around each kernel group.
 int gpirt_profile_enable(gpirt_sampler* h, int on) {
     CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(quiesce(h));  // profiled sweeps run every kernel on the main stream, in the reference's order
     h->profiling = on != 0;
     return GPIRT_OK;
 }

@@ -40,6 +40,14 @@ struct gpirt_sampler {
     bool own_stream = false;
     uint32_t iter = 0;
     bool have_data = false, chol_valid = false;
+    // The theta-only chain of a sweep (K, chol(K), k*, L^-1, K_post, chol(K_post), K^-1 k*) runs on a second, higher-priority
+    // stream as soon as the new theta is committed, under the item kernels of the main stream (draw_beta, draw_threshold,
+    // ll, next draw_f): it is a long chain of small launches that cannot fill the GPU on its own.
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_shared = nullptr;
+    bool overlap = true;           // gpirt_set_overlap; profiling forces the serial order
+    bool shared_valid = false;     // W / Kpost hold the draw_fstar terms of the current theta
+    bool pending_L = false, pending_shared = false;  // the main stream has not yet waited for ev_L / ev_shared
 
     int8_t *y_im = nullptr, *y_rm = nullptr;
     double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;

@@ -162,6 +162,10 @@ class Sampler:
         """0: blocked substitution for L^-1 k* / L^-T(.) in draw_fstar; 1: explicit block inverse + GEMMs (default)"""
         check(self._L.gpirt_set_solver(self._h, int(solver)))
 
+    def set_overlap(self, on):
+        """run the theta-only chain of the next sweep on a second stream under the item samplers (default on)"""
+        check(self._L.gpirt_set_overlap(self._h, int(on)))
+
     def set_stream(self, cuda_stream):
         check(self._L.gpirt_set_stream(self._h, C.c_void_p(cuda_stream)))
 

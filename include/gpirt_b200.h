@@ -120,6 +120,10 @@ int gpirt_set_iter(gpirt_sampler* h, uint32_t iter);         /* sweep counter us
  * 0 = blocked forward/back substitution (backward stable, n/64 dependent steps); 1 = explicit L^-1 by parallel block inversion, then
  * GEMMs (default; forward error kappa(L)*eps like substitution's bound, no dependent chain). */
 int gpirt_set_solver(gpirt_sampler* h, int solver);
+/* 1 (default): inside gpirt_sweep*, the theta-only chain (K, Cholesky cache, shared draw_fstar terms: src/cholesky-cache.cpp:20-24,
+ * src/draw-fstar.cpp:26-36) of the next sweep runs on a second CUDA stream under the item samplers; 0: every kernel in the
+ * reference's order on one stream. Results are identical either way. */
+int gpirt_set_overlap(gpirt_sampler* h, int on);
 int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin); /* per unit: 1+proposals, min |ll'-log_y| */
 int gpirt_sync(gpirt_sampler* h);                            /* wait for queued work; surfaces deferred errors */
 /* initial values the reference draws inside gpirtMCMC (src/gpirtMCMC.cpp:149-163): beta0 ~ N(prior mean, prior sd)
