@@ -37,6 +37,7 @@ struct GemmArgs {
     int batch;        // 0 or 1: a single product
     long long strideA, strideB, strideC;
     int M_last, N_last, K_last;  // extents of batch (batch-1) when > 0, else M / N / K
+    int m_off;        // row index of C(0,0) inside the full product (a launch over a row slice keeps the triangular k ranges right)
 };
 
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem, int src_bytes) {
@@ -85,7 +86,18 @@ __global__ void __launch_bounds__(GemmCfg<BM, BN, BK, WM, WN, STAGES, TA, TB>::T
 gemm_f64_kernel(GemmArgs g) {
     using Cfg = GemmCfg<BM, BN, BK, WM, WN, STAGES, TA, TB>;
     extern __shared__ __align__(16) double smem[];
-    const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    // 1-D grid over the tiles. Tiles whose k range is longest are dispatched first (a triangular operand makes the work per
+    // tile vary by the number of row / column tiles; heavy-first keeps the last wave short).
+    const int tiles_m = (g.M + BM - 1) / BM, tiles_n = (g.N + BN - 1) / BN;
+    int mt, nt;
+    if (g.b_upper || g.b_lower) {  // work varies with the column tile: column tiles are the slow index
+        nt = blockIdx.x / tiles_m; mt = blockIdx.x - nt * tiles_m;
+        if (g.b_upper) nt = tiles_n - 1 - nt;
+    } else {                       // row tiles are the slow index
+        mt = blockIdx.x / tiles_n; nt = blockIdx.x - mt * tiles_n;
+        if (g.a_lower) mt = tiles_m - 1 - mt;
+    }
+    const int m0 = mt * BM, n0 = nt * BN;
     if (g.batch > 1) {
         const int z = blockIdx.z;
         g.A += z * g.strideA; g.B += z * g.strideB; g.C += z * g.strideC;
@@ -102,9 +114,9 @@ gemm_f64_kernel(GemmArgs g) {
     const int grp = lane >> 2, tig = lane & 3;
 
     int k_end = g.K, k_begin = 0;
-    if (g.a_lower) k_end = min(k_end, m0 + BM);
+    if (g.a_lower) k_end = min(k_end, g.m_off + m0 + BM);
     if (g.b_upper) k_end = min(k_end, n0 + BN);
-    if (g.a_upper) k_begin = max(k_begin, m0);
+    if (g.a_upper) k_begin = max(k_begin, g.m_off + m0);
     if (g.b_lower) k_begin = max(k_begin, n0);
     k_begin = (k_begin / BK) * BK;
     const int KT = k_end > k_begin ? (k_end - k_begin + BK - 1) / BK : 0;

@@ -21,19 +21,50 @@ static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    dim3 grid((g.M + BM - 1) / BM, (g.N + BN - 1) / BN, g.batch > 1 ? g.batch : 1);
+    dim3 grid(((g.N + BN - 1) / BN) * ((g.M + BM - 1) / BM), 1, g.batch > 1 ? g.batch : 1);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(g);
     ++g_kernel_launches;
     return cudaGetLastError();
 }
 
+static int sm_count() {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+    }
+    return sms;
+}
+
 template <bool TA, bool TB>
 static cudaError_t gemm_pick(cudaStream_t st, const GemmArgs& g) {
-    // big tiles only when they still fill the 148 SMs; otherwise 64x64 tiles (4x the CTAs)
-    long tiles128 = (long)((g.M + 127) / 128) * ((g.N + 127) / 128) * (g.batch > 1 ? g.batch : 1);
+    // big tiles only when they still fill the SMs; otherwise 64x64 tiles (4x the CTAs)
+    const long tm = (g.M + 127) / 128, tn = (g.N + 127) / 128;
+    long tiles128 = tm * tn * (g.batch > 1 ? g.batch : 1);
     if (g.lower_only) tiles128 = tiles128 / 2 + 1;
-    if (tiles128 >= 2 * 148 && g.N >= 128 && g.M >= 128) return launch_gemm<128, 128, 16, 64, 32, 3, TA, TB>(st, g);
-    return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, g);
+    const int slots = sm_count();  // the 128x128 kernel holds ~200 registers per thread: one CTA per SM
+    if (!(tiles128 >= 2 * slots && g.N >= 128 && g.M >= 128)) return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, g);
+    // Wave quantisation: with T equal tiles on S slots the last wave runs (T mod S)/S full. When that fraction is small, the rows
+    // of the last partial wave go to the 64x64 kernel instead (4 CTAs per SM, a quarter of the tile): e.g. the f* mean F^T W at
+    // C3 is 40 x 8 = 320 tiles on 148 SMs: 2 full waves of 128x128 tiles + 3 row tiles as 64x64 tiles instead of 3 waves.
+    const bool uniform = !g.a_lower && !g.a_upper && !g.b_lower && !g.b_upper && !g.lower_only && g.batch <= 1;
+    const long full = tiles128 / slots, rem = tiles128 % slots;
+    if (uniform && rem > 0 && rem * 10 < slots * 6) {
+        const long rows_main = (full * slots) / tn;  // whole row tiles that fit the full waves
+        if (rows_main >= 1 && rows_main < tm) {
+            GemmArgs a = g, b = g;
+            a.M = (int)rows_main * 128;
+            b.M = g.M - a.M;
+            b.m_off = g.m_off + a.M;
+            b.A = TA ? g.A + (size_t)a.M * g.lda : g.A + a.M;
+            b.C = g.C + a.M;
+            cudaError_t e = launch_gemm<128, 128, 16, 64, 32, 3, TA, TB>(st, a);
+            if (e != cudaSuccess) return e;
+            return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, b);
+        }
+    }
+    return launch_gemm<128, 128, 16, 64, 32, 3, TA, TB>(st, g);
 }
 
 cudaError_t gemm_f64(cudaStream_t st, bool ta, bool tb, const GemmArgs& g) {
