@@ -1,0 +1,62 @@
+"""Item-sharded sweeps on 2 GPUs (one process per GPU, NCCL) against the same chain on 1 GPU: bit-identical state, because the
+Philox streams are keyed by global item / respondent index and every reduction has a fixed order. Skipped with fewer than 2 GPUs."""
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+import numpy as np
+import torch, torch.distributed as dist
+sys.path.insert(0, os.environ["GPIRT_ROOT"])
+import gpirt_b200
+from gpirt_b200.distributed import ShardedSampler
+from tests.problems import make_problem
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+n, m, C, sweeps = 203, 61, 4, 3   # ragged on purpose: 61 items -> chunks of 31 + 30, 203 respondents -> 102 + 101
+P = make_problem(n, m, C, seed=5)
+def run(S):
+    S.set_data(P["y"]); S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+    S.init_draw(draw_beta=False, draw_f=True)
+    S.sweep(sweeps); S.sync()
+    st = S.get_state(fstar=False); st["ll"] = S.total_ll()
+    return st
+sh = run(ShardedSampler(n, m, C, rank=rank, world=world, device=local, seed=77))
+# gather the f columns of every rank on rank 0 (get_state writes only the local item block)
+f = torch.from_numpy(np.ascontiguousarray(sh["f"].T)).cuda()
+dist.all_reduce(f)  # the other ranks' blocks are zero
+if rank == 0:
+    one = run(gpirt_b200.Sampler(n, m, C, seed=77, device=local))
+    ok = all(np.array_equal(sh[k], one[k]) for k in ("theta", "beta", "thresholds")) and sh["ll"] == one["ll"]
+    ok = ok and np.array_equal(f.cpu().numpy().T, one["f"])
+    print("WORLD2_EQUALS_WORLD1", ok, sh["ll"], one["ll"])
+dist.barrier(); dist.destroy_process_group()
+'''
+
+
+def _gpus():
+    from gpirt_b200 import _lib
+    return _lib.lib().gpirt_device_count()
+
+
+def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path):
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, GPIRT_ROOT=ROOT)
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+                        "--master-port", str(port), str(script)], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "WORLD2_EQUALS_WORLD1 True" in r.stdout, r.stdout[-2000:]
