@@ -63,11 +63,11 @@ SYMBOLS = [
     "gpirt_last_error", "gpirt_device_count", "gpirt_K", "gpirt_K_time", "gpirt_delta_to_threshold",
     "gpirt_threshold_to_delta", "gpirt_chol", "gpirt_double_solve", "gpirt_create", "gpirt_destroy", "gpirt_set_stream",
     "gpirt_set_data_f64", "gpirt_set_data_i8", "gpirt_set_priors", "gpirt_set_state", "gpirt_get_state", "gpirt_get_L",
-    "gpirt_set_iter", "gpirt_set_solver", "gpirt_set_overlap", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
+    "gpirt_set_iter", "gpirt_set_solver", "gpirt_set_overlap", "gpirt_set_screen", "gpirt_get_exact_evals", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_exchange_buffer",
     "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
-    "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit",
+    "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit", "gpirt_debug_cell32",
 ]
 
 _lib = None

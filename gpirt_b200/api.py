@@ -165,3 +165,11 @@ def debug_probit(x, device=0):
     ph, lg = np.empty_like(x), np.empty_like(x)
     check(_lib.lib().gpirt_debug_probit(device, _p(x), int(x.size), _p(ph), _p(lg)))
     return ph, lg
+
+
+def debug_cell32(g, tau_lo, tau_hi, device=0):
+    """(t32, e32, t64): the fp32 screening term, its error bound and the fp64 cell term, per element (test hook)."""
+    g, lo, hi = _F(g).ravel(), _F(tau_lo).ravel(), _F(tau_hi).ravel()
+    t32, e32, t64 = np.empty_like(g), np.empty_like(g), np.empty_like(g)
+    check(_lib.lib().gpirt_debug_cell32(device, _p(g), _p(lo), _p(hi), int(g.size), _p(t32), _p(e32), _p(t64)))
+    return t32, e32, t64

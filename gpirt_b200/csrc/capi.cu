@@ -198,9 +198,11 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     TRY(dalloc(&h->item_ll, mt));
     TRY(dalloc(&h->total_ll, 1));
     TRY(dalloc(&h->flags, 1));
+    TRY(dalloc(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID))));
     for (int b = 0; b < 5; ++b) {
         size_t units = (b == GPIRT_BLOCK_THETA) ? (size_t)h->world * h->n_chunk : mt;
         TRY(dalloc(&h->evals[b], units));
+        TRY(dalloc(&h->exact[b], units));
         TRY(dalloc(&h->margin[b], units));
     }
     k_fill_grid<<<(NGRID + 255) / 256, 256, 0, h->stream>>>(h->tstar);
@@ -220,11 +222,12 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
     if (h->side) cudaStreamDestroy(h->side);
     void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
-                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab, h->Linv, h->W2, h->tri_scratch};
+                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab, h->Linv, h->W2, h->tri_scratch, h->chol_ws};
     for (void* p : ptrs)
         if (p) cudaFree(p);
     for (int b = 0; b < 5; ++b) {
         if (h->evals[b]) cudaFree(h->evals[b]);
+        if (h->exact[b]) cudaFree(h->exact[b]);
         if (h->margin[b]) cudaFree(h->margin[b]);
     }
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -246,6 +249,21 @@ int gpirt_set_solver(gpirt_sampler* h, int solver) {
     CHECK_H(h);
     if (solver != 0 && solver != 1) return fail(GPIRT_ERR_INVALID, "solver %d: 0 (blocked substitution) or 1 (block inverse)", solver);
     h->solver = solver;
+    return GPIRT_OK;
+}
+
+int gpirt_set_screen(gpirt_sampler* h, int on) {
+    CHECK_H(h);
+    h->screen = on != 0;
+    return GPIRT_OK;
+}
+int gpirt_get_exact_evals(gpirt_sampler* h, int block, int32_t* out) {
+    CHECK_H(h);
+    if (block < 0 || block > 4 || !out) return fail(GPIRT_ERR_INVALID, "get_exact_evals: block %d", block);
+    CU(cudaSetDevice(h->cfg.device));
+    const size_t units = (block == GPIRT_BLOCK_THETA) ? h->n : h->m_total;
+    CU(cudaMemcpyAsync(out, h->exact[block], units * 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
     return GPIRT_OK;
 }
 
@@ -476,7 +494,7 @@ static ItemView item_view(gpirt_sampler* h) {
     v.n = h->n; v.ldn = h->ldn; v.m_local = h->m_local; v.item0 = h->item0; v.m_total = h->m_total; v.C = h->C; v.p_beta = h->cfg.p_beta;
     v.y_im = h->y_im; v.ldy = h->ldy; v.theta = h->theta; v.beta = h->beta; v.thr = h->thr; v.f = h->f; v.nu = h->nu; v.sds = h->sds;
     v.z = nullptr; v.z_stride = 0; v.us.u = nullptr; v.us.stride = 0; v.key = h->key();
-    v.item_ll = h->item_ll; v.flags = h->flags;
+    v.item_ll = h->item_ll; v.flags = h->flags; v.screen = h->screen; v.exact_evals = nullptr;
     return v;
 }
 
@@ -505,7 +523,7 @@ static int need_data(gpirt_sampler* h) {
 
 static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
-    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info)));
+    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws)));
     h->chol_valid = true;
     h->shared_valid = false;
     return GPIRT_OK;
@@ -544,7 +562,7 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
             SEC(h, "gemm_LZ", CU(gemm_f64(st, false, false, g)));
         }
     }
-    v.evals = h->evals[GPIRT_BLOCK_F]; v.margin = h->margin[GPIRT_BLOCK_F];
+    v.evals = h->evals[GPIRT_BLOCK_F]; v.margin = h->margin[GPIRT_BLOCK_F]; v.exact_evals = h->exact[GPIRT_BLOCK_F];
     SEC(h, "ess_f", CU(launch_ess_items(st, IB_F, v)));
     return GPIRT_OK;
 }
@@ -582,7 +600,7 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
     k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info)));
+    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws)));
     // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
     if (h->solver == 1) {
         GemmArgs g{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
@@ -685,7 +703,7 @@ static int do_small_ess(gpirt_sampler* h, int which, const gpirt_streams* s) {
     const int blk = which == IB_BETA ? GPIRT_BLOCK_BETA : GPIRT_BLOCK_THR;
     const size_t nz = which == IB_BETA ? 3 : (size_t)(h->C - 1);
     TRY(stage_streams(h, s, h->m_total, nz, &v.z, &v.z_stride, &v.us));
-    v.evals = h->evals[blk]; v.margin = h->margin[blk];
+    v.evals = h->evals[blk]; v.margin = h->margin[blk]; v.exact_evals = h->exact[blk];
     SEC(h, which == IB_BETA ? "ess_beta" : "ess_thr", CU(launch_ess_items(h->stream, which, v)));
     return GPIRT_OK;
 }
@@ -816,10 +834,10 @@ int gpirt_chol(int device, const double* A, int64_t n, double* L) {
     TRY(select_device(device));
     const int ld = pad_ld(n);
     double* dA; int* info; int hinfo = 0;
-    CU(cudaMalloc((void**)&dA, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&info, 4));
+    CU(cudaMalloc((void**)&dA, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&info, 4 * (1 + chol_ws_ints((int)n))));
     CU(cudaMemset(dA, 0, (size_t)ld * n * 8)); CU(cudaMemset(info, 0, 4));
     CU(cudaMemcpy2D(dA, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
-    CU(chol_lower_blocked(0, dA, ld, (int)n, info));
+    CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1));
     CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(&hinfo, info, 4, cudaMemcpyDeviceToHost));
     cudaFree(dA); cudaFree(info);
@@ -963,6 +981,34 @@ extern "C" int gpirt_debug_probit(int device, const double* x, int n, double* ph
     CU(cudaGetLastError());
     CU(cudaMemcpy(phi_out, d + n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(log_out, d + 2 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    cudaFree(d);
+    return GPIRT_OK;
+}
+
+// Test hook: the fp32 screening term, its error bound, and the fp64 cell term the ESS kernels use, element-wise.
+__global__ void k_debug_cell32(const double* g, const double* lo, const double* hi, int n, double* t32, double* e32, double* t64) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float t, e;
+    cell_ll32(g[i], lo[i], hi[i], t, e);
+    t32[i] = (double)t;
+    e32[i] = (double)e;
+    t64[i] = cell_ll(g[i], lo[i], hi[i], isinf(lo[i]) && lo[i] < 0, isinf(hi[i]) && hi[i] > 0);
+}
+extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const double* tau_hi, int n, double* t32, double* e32,
+                                  double* t64) {
+    if (!g || !tau_lo || !tau_hi || !t32 || !e32 || !t64 || n < 1) return fail(GPIRT_ERR_INVALID, "debug_cell32: bad arguments");
+    TRY(select_device(device));
+    double* d = nullptr;
+    CU(cudaMalloc((void**)&d, (size_t)6 * n * 8));
+    CU(cudaMemcpy(d, g, (size_t)n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d + n, tau_lo, (size_t)n * 8, cudaMemcpyHostToDevice));
+    CU(cudaMemcpy(d + 2 * (size_t)n, tau_hi, (size_t)n * 8, cudaMemcpyHostToDevice));
+    k_debug_cell32<<<(n + 255) / 256, 256>>>(d, d + n, d + 2 * (size_t)n, n, d + 3 * (size_t)n, d + 4 * (size_t)n, d + 5 * (size_t)n);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(t32, d + 3 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(e32, d + 4 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(t64, d + 5 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     cudaFree(d);
     return GPIRT_OK;
 }

@@ -190,7 +190,11 @@ __device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, do
 // One panel of the blocked factorisation in ONE launch: every CTA factors the diagonal block (redundantly,
 // bit-identical), CTA 0 writes it back, CTA b >= 1 solves X * L11^T = A21 for its 64 rows of the panel by
 // substitution (backward stable). The chain potf2 -> trsm is the latency floor of a panel: no launch gap.
-__global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict__ A, int ld, int kb, int rows_below, int* info, int k0) {
+// In-place hazard: CTAs b >= 1 read the ORIGINAL diagonal block that CTA 0 overwrites with its factor. A CTA may start late (the
+// panel runs next to other streams' kernels), so CTA 0 holds its write-back until every other CTA has announced, through *readers,
+// that its copy of the block is in registers.
+__global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict__ A, int ld, int kb, int rows_below, int* info, int k0,
+                                                             int* readers) {
     constexpr int NB = CHOL_NB;
     __shared__ double Ls[NB][NB + 1];
     __shared__ double vec[2][NB];
@@ -204,8 +208,18 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
             const int r = tr + 16 * p, c = tc + 16 * q;
             a[p][q] = (r < kb && c < kb && c <= r) ? A[(size_t)c * ld + r] : (c == r ? 1.0 : 0.0);
         }
+    if (blockIdx.x != 0) {
+        __threadfence();  // this thread's loads of the block are performed
+        __syncthreads();
+        if (threadIdx.x == 0) atomicAdd(readers, 1);
+    }
     tile_potf2(a, tr, tc, vec, info, k0, blockIdx.x == 0);
     if (blockIdx.x == 0) {
+        if (threadIdx.x == 0) {
+            while (atomicAdd(readers, 0) < (int)gridDim.x - 1) __nanosleep(64);
+            __threadfence();
+        }
+        __syncthreads();
 #pragma unroll
         for (int q = 0; q < 4; ++q)
 #pragma unroll
@@ -387,13 +401,15 @@ __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
     if (i < n && j < n && i < j) A[(size_t)j * ld + i] = 0.0;
 }
 
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev) {
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws) {
     constexpr int NB = CHOL_NB;
+    cudaError_t e0 = cudaMemsetAsync(readers_ws, 0, chol_ws_ints(n) * sizeof(int), st);
+    if (e0 != cudaSuccess) return e0;
     for (int k0 = 0; k0 < n; k0 += NB) {
         const int kb = (n - k0 < NB) ? n - k0 : NB;
         double* Akk = A + (size_t)k0 * ld + k0;
         const int rows = n - k0 - kb;
-        k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0);
+        k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0, readers_ws + k0 / NB);
         ++g_kernel_launches;
         if (rows > 0) {
             double* A21 = Akk + kb;

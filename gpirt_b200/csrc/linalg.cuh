@@ -17,7 +17,9 @@ cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double
 
 // In-place lower Cholesky of the n x n matrix A (lower triangle read, upper triangle zeroed on exit).
 // *info_dev (device int, must be 0 on entry) receives the 1-based index of the first non-positive pivot.
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev);
+// readers_ws: chol_ws_ints(n) device ints of workspace (zeroed by the call; one arrival counter per panel).
+inline size_t chol_ws_ints(int n) { return (size_t)(n + CHOL_NB - 1) / CHOL_NB + 1; }
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);

@@ -130,6 +130,56 @@ __host__ __device__ __forceinline__ double cell_ll(double g, double tau_lo, doub
     return cell_from_probs(p_lo, p_hi);
 }
 
+#ifdef __CUDACC__
+// ---- fp32 screening of ESS proposals ---------------------------------------------------------------------------
+// An ESS proposal is accepted iff ll' > log_y. Most proposals miss log_y by far more than fp32 can blur, so the kernels first
+// evaluate ll' in fp32 TOGETHER WITH a rigorous bound E on |ll'_fp32 - ll'_fp64|, and only fall back to the fp64 evaluation when
+// |ll'_fp32 - log_y| <= E. The decision — hence every accepted state, every proposal count and every uniform consumed — is
+// exactly the fp64 decision (tests: screening on vs off is bit-identical); the fp32 value itself is never stored.
+// Per cell, with a = tau_lo - g, b = tau_hi - g (formed in fp64, then rounded), u = |a|, v = |b| and Q the upper tail:
+//   Phi(b) - Phi(a) =  Q(u) - Q(v)        if a >= 0      (both in the upper tail: no cancellation against 1)
+//                      Q(v) - Q(u)        if b <= 0
+//                      1 - Q(u) - Q(v)    otherwise
+//   Q(x) = 2^(-x^2 log2(e)/2) * P7((x-4)/(x+4)), x clamped to 9.25 (Q < 1.2e-20 beyond), relative error rho(x) <= 4e-6 + 4e-7 x^2
+//   (polynomial 4e-7, fp32 Horner ~1e-6, ex2.approx 2^-22, rounding of x and of the exponent: 1.8e-7 x^2; 2x margin)
+//   dp = rho(u) Q(u) + rho(v) Q(v) + 4 ulp32 (p + [straddle])        bound on the error of p = Phi(b) - Phi(a) + 1e-6
+//   e  = dp / (p - dp) + 2e-6 + 5e-7 |t|                              bound on the error of t = log p (lg2.approx: 2^-22)
+// tools/emul_screen32.py reproduces this arithmetic in numpy over 2e6 random cells: observed error / bound <= 0.29.
+__device__ __forceinline__ float f_rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_ex2(float x) { float r; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float f_lg2(float x) { float r; asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+
+__device__ __forceinline__ float q_tail32(float x) {  // x already clamped to [0, 9.25]
+    const float s = (x - 4.0f) * f_rcp(x + 4.0f);
+    float p = 0.000785236840738696f;
+    p = fmaf(p, s, 0.0005041266204986191f);
+    p = fmaf(p, s, -0.008529436410853592f);
+    p = fmaf(p, s, 0.03085854142686483f);
+    p = fmaf(p, s, -0.07170505823364434f);
+    p = fmaf(p, s, 0.12437966746436852f);
+    p = fmaf(p, s, -0.1703977371436323f);
+    p = fmaf(p, s, 0.09441063861780297f);
+    return p * f_ex2(x * x * -0.72134752f);
+}
+
+// t ~ log(Phi(tau_hi - g) - Phi(tau_lo - g) + 1e-6) in fp32 and e >= |t - (the fp64 cell term)|. Infinite thresholds (edge
+// categories) need no special case: their tail clamps to Q(9.25) ~ 1e-20. A NaN anywhere gives e = NaN, which fails both
+// screening comparisons and sends the proposal to the fp64 path.
+__device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi, float& t, float& e) {
+    const float a = (float)__dsub_rn(tau_lo, g), b = (float)__dsub_rn(tau_hi, g);
+    const float u = fminf(fabsf(a), 9.25f), v = fminf(fabsf(b), 9.25f);
+    const float qu = q_tail32(u), qv = q_tail32(v);
+    const bool sa = a >= 0.0f, sb = b <= 0.0f;
+    const float straddle = (sa || sb) ? 0.0f : 1.0f;
+    const float d = sa ? qu - qv : (sb ? qv - qu : (1.0f - qu) - qv);
+    const float p = d + 1e-6f;
+    t = f_lg2(p) * 0.6931472f;
+    const float dp = fmaf(fmaf(4e-7f, u * u, 4e-6f), qu, fmaf(4e-7f, v * v, 4e-6f) * qv) + 2.4e-7f * (p + straddle);
+    const float den = p - dp;
+    e = (den > dp ? dp * f_rcp(den) * 1.0001f : 14.0f) + fmaf(5e-7f, fabsf(t), 2e-6f);
+}
+#endif
+
 // grid index of theta on theta* = -5:0.01:5 (src/draw-theta.cpp:10-11, src/gpirtMCMC.cpp:291-296):
 // round-half-away((theta + 5.0) / 0.01), clamped. Explicit IEEE add/div so no contraction can change it.
 __host__ __device__ __forceinline__ int grid_index(double theta) {

@@ -58,8 +58,11 @@ struct gpirt_sampler {
     double* theta_tab = nullptr;  // [NGRID][m_total][C] per-sweep table of theta-step terms (allocated on first use)
     double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    int32_t* exact[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per unit: evaluations that ran in fp64 (screening diagnostics)
+    int screen = 1;  // fp32 screening of ESS proposals with a rigorous error bound; decisions identical to fp64 (gpirt_set_screen)
     double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     gpirt::DevFlags* flags = nullptr;
+    int* chol_ws = nullptr;  // per-panel arrival counters of the blocked Cholesky
     double sds0[3] = {0, 0, 0};  // beta_prior_sds.col(0): the sds every K() call uses (src/cholesky-cache.cpp:21)
 
     // optional per-section device timing (gpirt_profile_*): CUDA events around each kernel group

@@ -64,11 +64,28 @@ __device__ __forceinline__ double block_sum(double v, double* s_part) {
     return t;
 }
 
+// two sums at once (same fixed order): a and b come back on every thread
+template <int WARPS>
+__device__ __forceinline__ void block_sum2(double& a, double& b, double (*s_part2)[WARPS]) {
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if (WARPS == 1) return;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) { s_part2[0][warp] = a; s_part2[1][warp] = b; }
+    __syncthreads();
+    double ta = 0.0, tb = 0.0;
+#pragma unroll
+    for (int w = 0; w < WARPS; ++w) { ta += s_part2[0][w]; tb += s_part2[1][w]; }
+    a = ta; b = tb;
+}
+
 template <int MODE, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
     constexpr int T = WARPS * 32;
     __shared__ double tau[MAX_C + 1];
     __shared__ double s_part[WARPS];
+    __shared__ double s_part2[2][WARPS];
     const int tid = threadIdx.x;
     const int j = blockIdx.x;
     const int J = v.item0 + j;
@@ -102,6 +119,30 @@ __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
         }
         if (i < n) acc0 += term(i, ce, se, current);
         return block_sum<WARPS>(acc0 + acc1, s_part);
+    };
+
+    // fp32 screening pass (probit.cuh): the proposal's log-likelihood in fp32 (summed in fp64) and the bound on its distance to
+    // the fp64 value
+    auto loglik32 = [&](double ce, double se, double& L, double& E) {
+        double l0 = 0.0, l1 = 0.0;
+        float e0 = 0.f, e1 = 0.f;
+        auto one = [&](int i, double& l, float& e) {
+            const int y = yj[i];
+            if (y == 0) return;
+            double fi = fj[i];
+            if (MODE == IB_F) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
+            const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
+            float t, et;
+            cell_ll32(g, tau[y - 1], tau[y], t, et);
+            l += (double)t;
+            e += et;
+        };
+        int i = tid;
+        for (; i + T < n; i += 2 * T) { one(i, l0, e0); one(i + T, l1, e1); }
+        if (i < n) one(i, l0, e0);
+        L = l0 + l1;
+        E = (double)(e0 + e1);
+        block_sum2<WARPS>(L, E, s_part2);
     };
 
     // prior draw for the low-dimensional blocks
@@ -145,7 +186,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
     double eps_min = 0.0, eps_max = TWO_PI_R;
     double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
     eps_min = __dsub_rn(eps, TWO_PI_R);
-    int evals = 1;
+    int evals = 1, n_exact = 1;  // n_exact: evaluations that ran in fp64 (the current state always does)
     double margin = CUDART_INF;
     double ce = 1.0, se = 0.0;
     bool accepted = false;
@@ -166,10 +207,24 @@ __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
             }
             __syncthreads();
         }
-        const double llp = loglik(ce, se, false);  // identical on every thread of the CTA
         ++evals;
-        margin = fmin(margin, fabs(llp - log_y));
-        if (llp > log_y) { accepted = true; break; }
+        bool decided = false, accept = false;
+        if (v.screen) {
+            double L32, E32;
+            loglik32(ce, se, L32, E32);
+            // fp32 rounding of the E accumulation (relative 1e-5 at most) and the fp64 pass's own summation noise
+            const double Eb = E32 * 1.00002 + 1e-10 * (fabs(L32) + 1.0);
+            if (L32 - Eb > log_y) { decided = true; accept = true; }
+            else if (L32 + Eb < log_y) { decided = true; }
+            if (decided) margin = fmin(margin, fabs(L32 - log_y) - Eb);  // a lower bound of the true margin
+        }
+        if (!decided) {
+            const double llp = loglik(ce, se, false);  // identical on every thread of the CTA
+            margin = fmin(margin, fabs(llp - log_y));
+            accept = llp > log_y;
+            ++n_exact;
+        }
+        if (accept) { accepted = true; break; }
         if (eps < 0.0) eps_min = eps; else eps_max = eps;
         eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
         if (overrun) break;
@@ -177,6 +232,7 @@ __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
     if (tid == 0) {
         v.evals[J] = evals;
         v.margin[J] = margin;
+        if (v.exact_evals) v.exact_evals[J] = n_exact;
         if (overrun) atomicExch(&v.flags->overrun, 1);
         else if (!accepted) atomicExch(&v.flags->stalled, 1);
     }

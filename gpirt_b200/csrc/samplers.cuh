@@ -39,6 +39,8 @@ struct ItemView {
     UniformSrc us;
     RngKey key;
     int32_t* evals;           // per global item
+    int32_t* exact_evals;     // per global item: evaluations that needed the fp64 pass (screening diagnostics), or nullptr
+    int screen;               // 1: fp32 screening of proposals with a rigorous error bound (probit.cuh)
     double* margin;
     double* item_ll;          // per global item (k_item_ll)
     DevFlags* flags;

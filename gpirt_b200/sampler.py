@@ -166,6 +166,17 @@ class Sampler:
         """run the theta-only chain of the next sweep on a second stream under the item samplers (default on)"""
         check(self._L.gpirt_set_overlap(self._h, int(on)))
 
+    def set_screen(self, on):
+        """fp32 screening of ESS proposals with a rigorous error bound (default on); decisions are identical to fp64"""
+        check(self._L.gpirt_set_screen(self._h, int(on)))
+
+    def exact_evals(self, block):
+        """per unit: evaluations of the last call of `block` that ran in fp64"""
+        units = self.n if block == "theta" else self.m
+        out = np.zeros(units, dtype=np.int32)
+        check(self._L.gpirt_get_exact_evals(self._h, _lib.BLOCK[block], _p(out)))
+        return out
+
     def set_stream(self, cuda_stream):
         check(self._L.gpirt_set_stream(self._h, C.c_void_p(cuda_stream)))
 

@@ -124,6 +124,12 @@ int gpirt_set_solver(gpirt_sampler* h, int solver);
  * src/draw-fstar.cpp:26-36) of the next sweep runs on a second CUDA stream under the item samplers; 0: every kernel in the
  * reference's order on one stream. Results are identical either way. */
 int gpirt_set_overlap(gpirt_sampler* h, int on);
+/* 1 (default): the ESS kernels (draw_f / draw_beta / draw_threshold: src/draw-f.cpp:23-41 and its three siblings) first evaluate a
+ * proposal's log-likelihood in fp32 together with a rigorous bound on its distance to the fp64 value and only run the fp64 pass
+ * when the accept test ll' > log_y is closer than that bound. Decisions, states and stream consumption are identical to 0 (every
+ * evaluation in fp64). gpirt_get_exact_evals: per unit, how many evaluations of the last call of `block` ran in fp64. */
+int gpirt_set_screen(gpirt_sampler* h, int on);
+int gpirt_get_exact_evals(gpirt_sampler* h, int block, int32_t* out);
 int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin); /* per unit: 1+proposals, min |ll'-log_y| */
 int gpirt_sync(gpirt_sampler* h);                            /* wait for queued work; surfaces deferred errors */
 /* initial values the reference draws inside gpirtMCMC (src/gpirtMCMC.cpp:149-163): beta0 ~ N(prior mean, prior sd)
@@ -160,6 +166,8 @@ long long gpirt_launch_count(void);                          /* kernels launched
 int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int count, double* out);
 int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out); /* device Phi(x), log(x) */
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
+/* fp32 screening term, its error bound and the fp64 cell term log(Phi(tau_hi-g) - Phi(tau_lo-g) + 1e-6), element-wise */
+int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const double* tau_hi, int n, double* t32, double* e32, double* t64);
 
 /* ---- the two Rcpp entry points ---- */
 typedef struct {

@@ -298,3 +298,78 @@ def test_overlapped_sweeps_equal_serial_sweeps_bit_for_bit():
     for k in ("theta", "beta", "f", "thresholds", "fstar", "L"):
         assert np.array_equal(states[0][k], states[1][k]), k
     assert states[0]["ll"] == states[1]["ll"]
+
+
+def test_fp32_screening_term_stays_inside_its_error_bound():
+    """cell_ll32 (csrc/probit.cuh): |t32 - t64| <= e32 over random and adversarial cells (tails, narrow bins, edge categories)."""
+    from gpirt_b200.api import debug_cell32
+
+    rng = np.random.default_rng(5)
+    n = 1_000_000
+    g = rng.normal(0, 3, n)
+    lo = rng.normal(0, 2, n)
+    hi = lo + np.exp(rng.normal(-0.5, 2.0, n))  # bins from 1e-4 to 50 wide
+    kind = rng.integers(0, 4, n)
+    lo = np.where(kind == 1, -np.inf, lo)
+    hi = np.where(kind == 2, np.inf, hi)
+    far = kind == 3  # deep tails on either side
+    g = np.where(far, g + rng.choice([-1.0, 1.0], n) * rng.uniform(4, 14, n), g)
+    t32, e32, t64 = debug_cell32(g, lo, hi)
+    assert np.all(np.isfinite(t64)) and np.all(np.isfinite(e32))
+    ratio = np.abs(t32 - t64) / e32
+    assert ratio.max() <= 0.6, f"observed error reaches {ratio.max():.2f} of the bound"  # the bound carries a 2x margin by design
+    assert np.median(e32) < 5e-5  # and it is tight enough to decide: ~0.03 per 2000 cells against margins of O(1..1000)
+
+
+@pytest.mark.parametrize("n,m,C", [(300, 40, 5), (257, 33, 2), (500, 20, 7)])
+def test_screened_sweeps_equal_unscreened_sweeps_bit_for_bit(n, m, C):
+    """fp32 screening on vs off: the same decisions, so identical states after several production sweeps; and the screen decides most
+    proposals on its own."""
+    P = make_problem(n, m, C, seed=91)
+    states, exact, evals = [], None, None
+    for screen in (1, 0):
+        S = gpirt_b200.Sampler(n, m, C, seed=5)
+        S.set_screen(screen)
+        S.set_data(P["y"])
+        S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+        S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+        S.init_draw(draw_beta=False, draw_f=True)
+        S.sweep(5)
+        S.sync()
+        st = S.get_state(fstar=True)
+        st["ll"] = S.total_ll()
+        st["evals"] = {b: S.diag(b)[0] for b in ("f", "beta", "thr")}
+        if screen:
+            exact = {b: S.exact_evals(b) for b in ("f", "beta", "thr")}
+        states.append(st)
+        S.close()
+    for k in ("theta", "beta", "f", "thresholds", "fstar"):
+        assert np.array_equal(states[0][k], states[1][k]), k
+    assert states[0]["ll"] == states[1]["ll"]
+    for b in ("f", "beta", "thr"):
+        assert np.array_equal(states[0]["evals"][b], states[1]["evals"][b])
+        ev = states[0]["evals"][b]
+        frac = (exact[b][ev > 0] - 1).sum() / max(1, (ev[ev > 0] - 1).sum())  # proposals that needed the fp64 pass
+        assert frac < 0.25, f"{b}: {frac:.2f} of the proposals fell back to fp64"
+
+
+def test_full_size_chain_is_deterministic_across_overlap_and_screening():
+    """At the C3 size (n=2000, m=5000) the side-stream chain really runs under the item kernels, with delayed CTAs: the chain must
+    still be bit-identical to the serial, unscreened order (this caught an in-place race in the Cholesky panel kernel)."""
+    n, m, C, sweeps = 2000, 5000, 5, 6
+    P = make_problem(n, m, C, seed=20261104 + 3, dtype="i8")
+    out = []
+    for overlap, screen in ((0, 0), (1, 1), (1, 1)):
+        S = gpirt_b200.Sampler(n, m, C, seed=20261104)
+        S.set_overlap(overlap)
+        S.set_screen(screen)
+        S.set_data(P["y"])
+        S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+        S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+        S.init_draw(draw_beta=False, draw_f=True)
+        S.sweep(sweeps)
+        S.sync()
+        out.append((S.total_ll(), S.get_state(f=False)["theta"], S.get_state(f=False)["beta"]))
+        S.close()
+    for k in (1, 2):
+        assert out[k][0] == out[0][0] and np.array_equal(out[k][1], out[0][1]) and np.array_equal(out[k][2], out[0][2])

@@ -16,13 +16,13 @@ int main() {
     std::vector<double> th(n); for (int i = 0; i < n; ++i) th[i] = -5.0 + 0.01 * ((i * 7919) % 1001);
     double *dth, *K, *A, *B, *C; int* info;
     CK(cudaMalloc(&dth, n * 8)); CK(cudaMalloc(&K, (size_t)ld * n * 8)); CK(cudaMalloc(&A, (size_t)ld * n * 8));
-    CK(cudaMalloc(&B, (size_t)ld * m * 8)); CK(cudaMalloc(&C, (size_t)ld * m * 8)); CK(cudaMalloc(&info, 4));
+    CK(cudaMalloc(&B, (size_t)ld * m * 8)); CK(cudaMalloc(&C, (size_t)ld * m * 8)); CK(cudaMalloc(&info, 4)); int* ws; CK(cudaMalloc(&ws, 4 * chol_ws_ints(n)));
     CK(cudaMemcpy(dth, th.data(), n * 8, cudaMemcpyHostToDevice)); CK(cudaMemset(info, 0, 4)); CK(cudaMemset(B, 0, (size_t)ld * m * 8));
     double sds[3] = {3, 3, 3};
     CK(build_K(0, dth, n, dth, n, sds, K, ld, 1e-6));
     auto reset = [&] { cudaMemcpyAsync(A, K, (size_t)ld * n * 8, cudaMemcpyDeviceToDevice, 0); };
     float t_copy = timeit(reset, 20);
-    float t_chol = timeit([&] { reset(); chol_lower_blocked(0, A, ld, n, info); }, 20) - t_copy;
+    float t_chol = timeit([&] { reset(); chol_lower_blocked(0, A, ld, n, info, ws); }, 20) - t_copy;
     printf("chol n=%d: %.3f ms (%.2f TFLOP/s)\n", n, t_chol, n * 1.0 * n * n / 3 / t_chol / 1e9);
     int h; CK(cudaMemcpy(&h, info, 4, cudaMemcpyDeviceToHost)); printf("info %d\n", h);
     float t_trsm = timeit([&] { trsm_left_lower(0, A, ld, n, B, ld, N); }, 20);
