@@ -4,6 +4,7 @@
 #include "linalg.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 
 namespace gpirt {
 
@@ -37,21 +38,24 @@ static int sm_count() {
     return sms;
 }
 
+// Tile shape: 64 x 64 x 16 CTA tiles, four warps of 32 x 32, three cp.async stages: 124 registers, 4 CTAs (16 warps) per SM. Measured
+// on B200 over the three big products of a C3 sweep (tools/bench_gemm.cu, profiles/r01_gemm_tiles.txt) it beats every larger tile —
+// 128 x 128 needs ~200 registers, so one CTA (8 warps) per SM, and stalls on its own latency — and ncu shows the DMMA pipe 90-91 %
+// busy (math-pipe throttle is the top stall). GPIRT_GEMM_TILE=128 selects the old big-tile path for experiments.
 template <bool TA, bool TB>
 static cudaError_t gemm_pick(cudaStream_t st, const GemmArgs& g) {
-    // big tiles only when they still fill the SMs; otherwise 64x64 tiles (4x the CTAs)
+    static const int force = getenv("GPIRT_GEMM_TILE") ? atoi(getenv("GPIRT_GEMM_TILE")) : 0;
+    if (force != 128) return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, g);
     const long tm = (g.M + 127) / 128, tn = (g.N + 127) / 128;
     long tiles128 = tm * tn * (g.batch > 1 ? g.batch : 1);
     if (g.lower_only) tiles128 = tiles128 / 2 + 1;
-    const int slots = sm_count();  // the 128x128 kernel holds ~200 registers per thread: one CTA per SM
+    const int slots = sm_count();  // one 128 x 128 CTA per SM
     if (!(tiles128 >= 2 * slots && g.N >= 128 && g.M >= 128)) return launch_gemm<64, 64, 16, 32, 32, 3, TA, TB>(st, g);
-    // Wave quantisation: with T equal tiles on S slots the last wave runs (T mod S)/S full. When that fraction is small, the rows
-    // of the last partial wave go to the 64x64 kernel instead (4 CTAs per SM, a quarter of the tile): e.g. the f* mean F^T W at
-    // C3 is 40 x 8 = 320 tiles on 148 SMs: 2 full waves of 128x128 tiles + 3 row tiles as 64x64 tiles instead of 3 waves.
+    // wave quantisation: the rows of a mostly empty last wave go to the small-tile kernel
     const bool uniform = !g.a_lower && !g.a_upper && !g.b_lower && !g.b_upper && !g.lower_only && g.batch <= 1;
     const long full = tiles128 / slots, rem = tiles128 % slots;
     if (uniform && rem > 0 && rem * 10 < slots * 6) {
-        const long rows_main = (full * slots) / tn;  // whole row tiles that fit the full waves
+        const long rows_main = (full * slots) / tn;
         if (rows_main >= 1 && rows_main < tm) {
             GemmArgs a = g, b = g;
             a.M = (int)rows_main * 128;
