@@ -64,14 +64,14 @@ struct SecScope {
 // main stream joins the side stream's work (no-ops when nothing is in flight)
 static int wait_L(gpirt_sampler* h) {
     if (h->pending_L) {
-        CU(cudaStreamWaitEvent(h->stream, h->ev_L, 0));
+        SEC(h, "wait_L", CU(cudaStreamWaitEvent(h->stream, h->ev_L, 0)));
         h->pending_L = false;
     }
     return GPIRT_OK;
 }
 static int wait_shared(gpirt_sampler* h) {
     if (h->pending_shared) {
-        CU(cudaStreamWaitEvent(h->stream, h->ev_shared, 0));  // recorded after ev_L on the same stream
+        SEC(h, "wait_shared", CU(cudaStreamWaitEvent(h->stream, h->ev_shared, 0)));  // recorded after ev_L on the same stream
         h->pending_shared = false;
         h->pending_L = false;
     }
@@ -617,7 +617,9 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
 // After a new theta is committed inside a sweep: K, chol(K) and the shared draw_fstar terms of the NEXT sweep start on the side
 // stream right away (the reference refactorises at this point too, src/gpirtMCMC.cpp:314). The main stream joins at first use.
 static int launch_theta_chain(gpirt_sampler* h) {
-    if (!h->overlap || h->profiling) return GPIRT_OK;  // serial order: update_cholesky runs where the reference has it
+    // serial order when profiling (update_cholesky runs where the reference has it) unless the timeline of the overlapped
+    // schedule itself is wanted (profiling level 2: section times then include waiting and sharing the SMs)
+    if (!h->overlap || (h->profiling && h->profile_level < 2)) return GPIRT_OK;
     CU(cudaEventRecord(h->ev_fork, h->stream));
     CU(cudaStreamWaitEvent(h->side, h->ev_fork, 0));
     TRY(do_update_cholesky(h, h->side));
@@ -903,8 +905,9 @@ extern "C" {
 int gpirt_profile_enable(gpirt_sampler* h, int on) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
-    TRY(quiesce(h));  // profiled sweeps run every kernel on the main stream, in the reference's order
+    TRY(quiesce(h));  // profiled sweeps (level 1) run every kernel on the main stream, in the reference's order
     h->profiling = on != 0;
+    h->profile_level = on;
     return GPIRT_OK;
 }
 // Collects finished sections; writes up to `cap` entries "name\0" (32 bytes each) with total ms and launch counts.

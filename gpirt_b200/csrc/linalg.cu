@@ -143,57 +143,118 @@ cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double
 namespace gpirt {
 
 // ------------------------------------------------------------------------------------------------
-// 64 x 64 tile kernels with compact (I-cache resident) code: 256 threads as a 16 x 16 grid, thread (tr, tc)
-// keeps the 4 x 4 elements (tr + 16p, tc + 16q) of the tile in registers; the column/row being eliminated
-// travels through a double-buffered shared-memory vector, one __syncthreads per elimination step.
-// (A first version unrolled the 64-step substitution completely per thread: ~10k straight-line instructions
-// per warp, instruction-fetch bound at 70-150 us per launch, profiles/r01_launches_v2.csv.)
+// 64 x 64 tile kernels: 256 threads as a 16 x 16 grid, thread (tr, tc) keeps the CONTIGUOUS 4 x 4 block rows 4tr..4tr+3,
+// columns 4tc..4tc+3 of the tile in registers. Eliminations advance four columns (or rows) per step: the thread that owns the
+// diagonal 4 x 4 block factors / inverts it locally, the 16 owners of the block column solve their 4 x 4 blocks against it, and
+// everybody applies a rank-4 update — 16 steps of two barriers instead of 64 steps of one, and the sqrt / reciprocal chains
+// (MUFU.RSQ64H + Newton; no fp64 division, which costs ~1500 cycles in divergent code, tools/bench_tile.cu) sit in one thread.
+// (History: a fully unrolled 64-step substitution was instruction-fetch bound at 70-150 us per launch; the one-column-per-barrier
+// version that followed spent ~600 cycles per column, profiles/r01_launches_v3.csv.)
 constexpr int TILE_THREADS = 256;
 
-// In-register Cholesky of the tile held as a[4][4]; returns with the factor in a (lower part valid).
-__device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, double (*vec)[CHOL_NB], int* info, int k0, bool report) {
+struct TileShared {       // state of one elimination step; kernels keep two and alternate (one barrier less per step)
+    double D[4][4];        // factored diagonal 4 x 4 block (lower part valid)
+    double Dinv[4];        // reciprocals of its diagonal
+    double P[4][CHOL_NB];  // the current block column, k-major: a thread's 4 rows are 32 contiguous bytes (two conflict-free LDS.128)
+};
+
+// sqrt(d) and 1/sqrt(d) without a division; s is corrected once so that it is the correctly rounded root up to 1 ulp.
+__device__ __forceinline__ void sqrt_rsqrt(double d, double& s, double& r) {
+    r = rsqrt(d);
+    s = d * r;
+    s = fma(fma(-s, s, d), 0.5 * r, s);
+}
+
+// X * D^T = A for one 4 x 4 block held by rows: x[q] <- (a[q] - sum_{k<q} x[k] D[q][k]) * Dinv[q]
+__device__ __forceinline__ void row_solve4(double (&x)[4], const double (&D)[4][4], const double (&Dinv)[4]) {
+    x[0] = x[0] * Dinv[0];
+    x[1] = (x[1] - x[0] * D[1][0]) * Dinv[1];
+    x[2] = (x[2] - x[0] * D[2][0] - x[1] * D[2][1]) * Dinv[2];
+    x[3] = (x[3] - x[0] * D[3][0] - x[1] * D[3][1] - x[2] * D[3][2]) * Dinv[3];
+}
+
+// One elimination step s of X * L^T = A restricted to block column s (shared by the Cholesky and its panel solve): owners
+// (tc == s, row block >= first_rb) solve against the 4 x 4 block D and publish their rows in P; after the barrier the columns to
+// the right take the rank-4 update a[p][q] -= sum_k P[row][k] * Lcol(4tc+q, 4s+k), Lcol read from P itself (Cholesky: the
+// panel is the factor; only tr >= tc matters) or from Ls (panel solve). One barrier; P is double-buffered by the caller.
+template <bool FROM_LS>
+__device__ __forceinline__ void step_block_column(double (&a)[4][4], int s, int tr, int tc, const double (&D)[4][4], const double (&Dinv)[4],
+                                                  double (*P)[CHOL_NB], double (*Ls)[CHOL_NB + 1], int first_rb) {
+    if (tc == s && tr >= first_rb) {
 #pragma unroll
-    for (int jq = 0; jq < 4; ++jq) {
-        for (int jj = 0; jj < 16; ++jj) {
-            const int j = 16 * jq + jj;
-            double* colL = vec[j & 1];
-            if (tc == jj) {  // the 16 owners of column j sit in one half-warp (tid = tr + 16 tc)
-                const unsigned half = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;
-                double d = __shfl_sync(half, a[jq][jq], (threadIdx.x & 16) + jj);  // diagonal element lives in lane tr == jj
-                if (!(d > 0.0)) {  // arma::chol would throw here; record the failing leading minor and keep going
-                    if (report && tr == jj) atomicCAS(info, 0, k0 + j + 1);
-                    d = 1.0;
-                }
-                d = sqrt(d);
-                const double inv_d = 1.0 / d;  // one division per column; the scaling below multiplies (a fp64 division
-                                               // inside this divergent section costs ~1500 cycles, tools/bench_tile.cu)
+        for (int p = 0; p < 4; ++p) {
+            row_solve4(a[p], D, Dinv);
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    const int r = tr + 16 * p;
-                    double v = a[p][jq];
-                    if (r > j) v = v * inv_d;
-                    else if (r == j) v = d;
-                    a[p][jq] = v;
-                    colL[r] = (r > j) ? v : 0.0;
-                }
+            for (int q = 0; q < 4; ++q) P[q][4 * tr + p] = a[p][q];
+        }
+    }
+    __syncthreads();
+    if (tc > s && (FROM_LS || tr >= tc)) {
+        double xr[4][4], lc[4][4];
+#pragma unroll
+        for (int p = 0; p < 4; ++p)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                xr[p][k] = P[k][4 * tr + p];
+                lc[p][k] = FROM_LS ? Ls[4 * tc + p][4 * s + k] : P[k][4 * tc + p];
             }
-            __syncthreads();
-            double lr[4], lc[4];
 #pragma unroll
-            for (int p = 0; p < 4; ++p) { lr[p] = colL[tr + 16 * p]; lc[p] = colL[tc + 16 * p]; }
+        for (int p = 0; p < 4; ++p)
 #pragma unroll
             for (int q = 0; q < 4; ++q)
-                if (tc + 16 * q > j) {
 #pragma unroll
-                    for (int p = 0; p < 4; ++p) a[p][q] -= lr[p] * lc[q];
-                }
-        }
+                for (int k = 0; k < 4; ++k) a[p][q] -= xr[p][k] * lc[q][k];
     }
 }
 
-// One panel of the blocked factorisation in ONE launch: every CTA factors the diagonal block (redundantly,
-// bit-identical), CTA 0 writes it back, CTA b >= 1 solves X * L11^T = A21 for its 64 rows of the panel by
-// substitution (backward stable). The chain potf2 -> trsm is the latency floor of a panel: no launch gap.
+// In-register Cholesky of the tile held as a[4][4] per thread; returns with the factor in a (lower part valid).
+__device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, TileShared* sh2, int* info, int k0, bool report) {
+    for (int s = 0; s < 16; ++s) {
+        TileShared& sh = sh2[s & 1];
+        if (tr == s && tc == s) {  // the diagonal 4 x 4 block: unblocked Cholesky in registers
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                double d = a[j][j];
+                if (!(d > 0.0)) {  // arma::chol would throw here; record the failing leading minor and keep going
+                    if (report) atomicCAS(info, 0, k0 + 4 * s + j + 1);
+                    d = 1.0;
+                }
+                double sq, rs;
+                sqrt_rsqrt(d, sq, rs);
+                a[j][j] = sq;
+                sh.Dinv[j] = rs;
+#pragma unroll
+                for (int i = j + 1; i < 4; ++i) a[i][j] *= rs;
+#pragma unroll
+                for (int jj = j + 1; jj < 4; ++jj)
+#pragma unroll
+                    for (int i = jj; i < 4; ++i) a[i][jj] -= a[i][j] * a[jj][j];
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (j > i) a[i][j] = 0.0;
+                    sh.D[i][j] = a[i][j];
+                    sh.P[j][4 * s + i] = a[i][j];  // the factor's own rows of the block column (upper part zero)
+                }
+        }
+        __syncthreads();
+        double D[4][4], Dinv[4];
+        if (tc == s && tr > s) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                Dinv[i] = sh.Dinv[i];
+#pragma unroll
+                for (int j = 0; j < 4; ++j) D[i][j] = sh.D[i][j];
+            }
+        }
+        step_block_column<false>(a, s, tr, tc, D, Dinv, sh.P, nullptr, s + 1);
+    }
+}
+
+// One panel of the blocked factorisation in ONE launch: every CTA factors the diagonal block (redundantly, bit-identical), CTA 0
+// writes it back, CTA b >= 1 solves X * L11^T = A21 for its 64 rows of the panel by substitution (backward stable).
 // In-place hazard: CTAs b >= 1 read the ORIGINAL diagonal block that CTA 0 overwrites with its factor. A CTA may start late (the
 // panel runs next to other streams' kernels), so CTA 0 holds its write-back until every other CTA has announced, through *readers,
 // that its copy of the block is in registers.
@@ -201,7 +262,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
                                                              int* readers) {
     constexpr int NB = CHOL_NB;
     __shared__ double Ls[NB][NB + 1];
-    __shared__ double vec[2][NB];
+    __shared__ TileShared sh2[2];
     __shared__ double inv_diag[NB];
     const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
     double a[4][4];
@@ -209,7 +270,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
+            const int r = 4 * tr + p, c = 4 * tc + q;
             a[p][q] = (r < kb && c < kb && c <= r) ? A[(size_t)c * ld + r] : (c == r ? 1.0 : 0.0);
         }
     if (blockIdx.x != 0) {
@@ -217,7 +278,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
         __syncthreads();
         if (threadIdx.x == 0) atomicAdd(readers, 1);
     }
-    tile_potf2(a, tr, tc, vec, info, k0, blockIdx.x == 0);
+    tile_potf2(a, tr, tc, sh2, info, k0, blockIdx.x == 0);
     if (blockIdx.x == 0) {
         if (threadIdx.x == 0) {
             while (atomicAdd(readers, 0) < (int)gridDim.x - 1) __nanosleep(64);
@@ -228,20 +289,23 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
         for (int q = 0; q < 4; ++q)
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
-                const int r = tr + 16 * p, c = tc + 16 * q;
+                const int r = 4 * tr + p, c = 4 * tc + q;
                 if (r < kb && c <= r) A[(size_t)c * ld + r] = a[p][q];
             }
         return;
     }
+    __syncthreads();  // the last update of tile_potf2 still reads sh2
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
+            const int r = 4 * tr + p, c = 4 * tc + q;
             Ls[r][c] = (c <= r) ? a[p][q] : 0.0;
         }
-    __syncthreads();
-    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
+    if (tr == tc) {
+#pragma unroll
+        for (int p = 0; p < 4; ++p) inv_diag[4 * tr + p] = rsqrt(a[p][p] * a[p][p]);  // 1 / L(jj): no fp64 division
+    }
     // X * L11^T = A21 for rows [row0, row0 + 64) of the panel; kb == NB whenever rows_below > 0
     const int row0 = (blockIdx.x - 1) * 64;
     double* __restrict__ A21 = A + kb;
@@ -249,80 +313,81 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = row0 + tr + 16 * p, c = tc + 16 * q;
+            const int r = row0 + 4 * tr + p, c = 4 * tc + q;
             a[p][q] = (r < rows_below) ? A21[(size_t)c * ld + r] : 0.0;
         }
-    __syncthreads();  // inv_diag visible
+    __syncthreads();  // Ls, inv_diag visible
+    for (int s = 0; s < 16; ++s) {
+        double D[4][4], Dinv[4];
+        if (tc == s) {
 #pragma unroll
-    for (int kq = 0; kq < 4; ++kq) {
-        for (int kk = 0; kk < 16; ++kk) {
-            const int k = 16 * kq + kk;
-            double* xcol = vec[k & 1];
-            if (tc == kk) {
-                const double d = inv_diag[k];
+            for (int i = 0; i < 4; ++i) {
+                Dinv[i] = inv_diag[4 * s + i];
 #pragma unroll
-                for (int p = 0; p < 4; ++p) {
-                    const double v = a[p][kq] * d;
-                    a[p][kq] = v;
-                    xcol[tr + 16 * p] = v;
-                }
+                for (int j = 0; j < 4; ++j) D[i][j] = Ls[4 * s + i][4 * s + j];
             }
-            __syncthreads();
-            double xr[4], lc[4];
-#pragma unroll
-            for (int p = 0; p < 4; ++p) { xr[p] = xcol[tr + 16 * p]; lc[p] = Ls[tc + 16 * p][k]; }
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-                if (tc + 16 * q > k) {
-#pragma unroll
-                    for (int p = 0; p < 4; ++p) a[p][q] -= xr[p] * lc[q];
-                }
         }
+        step_block_column<true>(a, s, tr, tc, D, Dinv, sh2[s & 1].P, Ls, 0);
     }
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = row0 + tr + 16 * p, c = tc + 16 * q;
+            const int r = row0 + 4 * tr + p, c = 4 * tc + q;
             if (r < rows_below) A21[(size_t)c * ld + r] = a[p][q];
         }
 }
 
-// Substitution with a 64 x 64 triangular block held in shared memory: on entry a[p][q] = B(row tr + 16p, column tc + 16q),
-// on exit the solution of L11 X = B (TRANS false) or L11^T X = B (TRANS true). One __syncthreads per eliminated row.
+// Substitution with a 64 x 64 triangular block held in shared memory as M[i][j] = L(j, i) (TRANS false) or L(i, j) (TRANS true), so
+// that the coefficients a thread needs for its 4 rows are contiguous: on entry a[p][q] = B(row 4tr + p, column 4tc + q), on exit
+// the solution of L X = B or L^T X = B. Four rows per step: the 16 owners of the row block solve their 4 x 4 blocks against the
+// diagonal block, publish them in XR, and the remaining row blocks take a rank-4 update. One barrier per step (XR double-buffered).
 template <bool TRANS>
-__device__ __forceinline__ void tile_solve(double (&a)[4][4], double (*Ls)[CHOL_NB + 1], double (*vec)[CHOL_NB], const double* inv_diag, int tr, int tc) {
+__device__ __forceinline__ void tile_solve(double (&a)[4][4], double (*M)[CHOL_NB], double (*XR2)[4][CHOL_NB], const double* inv_diag, int tr, int tc) {
+    for (int t = 0; t < 16; ++t) {
+        const int s = TRANS ? 15 - t : t;
+        double (*XR)[CHOL_NB] = XR2[t & 1];
+        if (tr == s) {
+            double D[4][4], Dinv[4];  // D[i][j] = L(4s+i, 4s+j)
 #pragma unroll
-    for (int s = 0; s < 4; ++s) {
-        const int kq = TRANS ? 3 - s : s;
-        for (int t = 0; t < 16; ++t) {
-            const int kk = TRANS ? 15 - t : t;
-            const int k = 16 * kq + kk;
-            double* xrow = vec[k & 1];
-            if (tr == kk) {  // owners of row k
-                const double d = inv_diag[k];
+            for (int i = 0; i < 4; ++i) {
+                Dinv[i] = inv_diag[4 * s + i];
 #pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const double v = a[kq][q] * d;
-                    a[kq][q] = v;
-                    xrow[tc + 16 * q] = v;
+                for (int j = 0; j < 4; ++j) D[i][j] = TRANS ? M[4 * s + i][4 * s + j] : M[4 * s + j][4 * s + i];
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (!TRANS) {
+                    a[0][q] = a[0][q] * Dinv[0];
+                    a[1][q] = (a[1][q] - D[1][0] * a[0][q]) * Dinv[1];
+                    a[2][q] = (a[2][q] - D[2][0] * a[0][q] - D[2][1] * a[1][q]) * Dinv[2];
+                    a[3][q] = (a[3][q] - D[3][0] * a[0][q] - D[3][1] * a[1][q] - D[3][2] * a[2][q]) * Dinv[3];
+                } else {  // D^T x = b: back substitution, D^T(i, j) = D[j][i]
+                    a[3][q] = a[3][q] * Dinv[3];
+                    a[2][q] = (a[2][q] - D[3][2] * a[3][q]) * Dinv[2];
+                    a[1][q] = (a[1][q] - D[3][1] * a[3][q] - D[2][1] * a[2][q]) * Dinv[1];
+                    a[0][q] = (a[0][q] - D[3][0] * a[3][q] - D[2][0] * a[2][q] - D[1][0] * a[1][q]) * Dinv[0];
                 }
+#pragma unroll
+                for (int k = 0; k < 4; ++k) XR[k][4 * tc + q] = a[k][q];
             }
-            __syncthreads();
-            double xc[4], lr[4];
+        }
+        __syncthreads();
+        if (TRANS ? (tr < s) : (tr > s)) {
+            double l[4][4], x[4][4];
 #pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                xc[p] = xrow[tc + 16 * p];
-                lr[p] = TRANS ? Ls[k][tr + 16 * p] : Ls[tr + 16 * p][k];  // L^T(r,k) = L(k,r)
-            }
+            for (int k = 0; k < 4; ++k)
 #pragma unroll
-            for (int p = 0; p < 4; ++p) {
-                const int r = tr + 16 * p;
-                if (TRANS ? (r < k) : (r > k)) {
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) a[p][q] -= lr[p] * xc[q];
+                for (int p = 0; p < 4; ++p) {
+                    l[p][k] = M[4 * s + k][4 * tr + p];  // coefficient of x_(4s+k) in the equation of row 4tr+p
+                    x[k][p] = XR[k][4 * tc + p];
                 }
-            }
+#pragma unroll
+            for (int p = 0; p < 4; ++p)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) a[p][q] -= l[p][k] * x[k][q];
         }
     }
 }
@@ -332,35 +397,35 @@ template <bool TRANS>
 __global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __restrict__ L11, int ldl, int kb,
                                                             double* __restrict__ B, int ldb, int nrhs) {
     constexpr int NB = CHOL_NB;
-    __shared__ double Ls[NB][NB + 1];
-    __shared__ double vec[2][NB];
+    __shared__ __align__(16) double M[NB][NB];
+    __shared__ __align__(16) double XR2[2][4][NB];
     __shared__ double inv_diag[NB];
     const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
-            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
+            const int r = 4 * tr + p, c = 4 * tc + q;
+            const double v = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ldl + r] : 0.0) : (r == c ? 1.0 : 0.0);
+            if (TRANS) M[r][c] = v; else M[c][r] = v;
+            if (r == c) inv_diag[r] = rsqrt(v * v);  // 1 / L(r, r) without an fp64 division
         }
     const int c0 = blockIdx.x * 64;
-    double a[4][4];  // a[p][q] = X(row tr + 16p, column c0 + tc + 16q)
+    double a[4][4];  // a[p][q] = X(row 4tr + p, column c0 + 4tc + q)
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
+            const int r = 4 * tr + p, c = c0 + 4 * tc + q;
             a[p][q] = (r < kb && c < nrhs) ? B[(size_t)c * ldb + r] : 0.0;
         }
     __syncthreads();
-    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
-    __syncthreads();
-    tile_solve<TRANS>(a, Ls, vec, inv_diag, tr, tc);
+    tile_solve<TRANS>(a, M, XR2, inv_diag, tr, tc);
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = c0 + tc + 16 * q;
+            const int r = 4 * tr + p, c = c0 + 4 * tc + q;
             if (r < kb && c < nrhs) B[(size_t)c * ldb + r] = a[p][q];
         }
 }
@@ -369,8 +434,8 @@ __global__ void __launch_bounds__(TILE_THREADS) k_trsm_left(const double* __rest
 // Writes the whole block of Linv (zeros above the diagonal).
 __global__ void __launch_bounds__(TILE_THREADS) k_trtri_diag(const double* __restrict__ L, int ld, int n, double* __restrict__ Linv, int ldi) {
     constexpr int NB = CHOL_NB;
-    __shared__ double Ls[NB][NB + 1];
-    __shared__ double vec[2][NB];
+    __shared__ __align__(16) double M[NB][NB];
+    __shared__ __align__(16) double XR2[2][4][NB];
     __shared__ double inv_diag[NB];
     const int tr = threadIdx.x & 15, tc = threadIdx.x >> 4;
     const int k0 = blockIdx.x * NB;
@@ -381,20 +446,20 @@ __global__ void __launch_bounds__(TILE_THREADS) k_trtri_diag(const double* __res
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
-            Ls[r][c] = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ld + r] : 0.0) : (r == c ? 1.0 : 0.0);
+            const int r = 4 * tr + p, c = 4 * tc + q;
+            const double v = (r < kb && c < kb) ? (c <= r ? L11[(size_t)c * ld + r] : 0.0) : (r == c ? 1.0 : 0.0);
+            M[c][r] = v;
+            if (r == c) inv_diag[r] = rsqrt(v * v);
             a[p][q] = (r == c) ? 1.0 : 0.0;
         }
     __syncthreads();
-    if (threadIdx.x < NB) inv_diag[threadIdx.x] = 1.0 / Ls[threadIdx.x][threadIdx.x];
-    __syncthreads();
-    tile_solve<false>(a, Ls, vec, inv_diag, tr, tc);
+    tile_solve<false>(a, M, XR2, inv_diag, tr, tc);
     double* out = Linv + (size_t)k0 * ldi + k0;
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
-            const int r = tr + 16 * p, c = tc + 16 * q;
+            const int r = 4 * tr + p, c = 4 * tc + q;
             if (r < kb && c < kb) out[(size_t)c * ldi + r] = (c <= r) ? a[p][q] : 0.0;
         }
 }

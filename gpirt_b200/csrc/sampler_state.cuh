@@ -68,6 +68,7 @@ struct gpirt_sampler {
     // optional per-section device timing (gpirt_profile_*): CUDA events around each kernel group
     struct Pending { const char* name; cudaEvent_t a, b; };
     bool profiling = false;
+    int profile_level = 0;  // 1: serial per-kernel times; 2: timeline of the overlapped schedule (times include waits / SM sharing)
     std::vector<Pending> pending;
     std::map<std::string, std::pair<double, long>> sections;  // name -> (total ms, launches)
 
