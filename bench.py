@@ -199,6 +199,9 @@ def ours(args):
     per_sweep = {k: v[0] / prof_sweeps for k, v in sections.items()}
     launches_per = {k: v[1] / prof_sweeps for k, v in sections.items()}
     ev = {b: S.diag(b)[0] for b in ("f", "theta", "beta", "thr")}
+    inner = S.S if hasattr(S, "S") else S
+    ex = {b: inner.exact_evals(b) for b in ("f", "beta", "thr")}
+    screened = {b: round(1.0 - float((ex[b][ev[b] > 0] - 1).sum()) / max(1.0, float((ev[b][ev[b] > 0] - 1).sum())), 4) for b in ex}
     E = {b: float(np.mean(ev[b][ev[b] > 0])) if np.any(ev[b] > 0) else 0.0 for b in ev}
     m_loc, N = M_PER_GPU, 1001
     nm = n * m_loc
@@ -219,13 +222,24 @@ def ours(args):
         peak = peaks["hbm_gbs"] if bound == "hbm" else FP64_DMMA_PEAK_TFLOPS
         kernels.append({"group": k, "ms_per_sweep": round(t, 4), "launches_per_sweep": launches_per[k], "bound": bound,
                         "achieved": round(ach, 2), "unit": "GB/s" if bound == "hbm" else "TFLOP/s", "frac": round(ach / peak, 4)})
-    top = kernels[0]
-    roofline = {"kernel": top["group"], "bound": top["bound"], "achieved": top["achieved"],
-                "peak": peaks["hbm_gbs"] if top["bound"] == "hbm" else FP64_DMMA_PEAK_TFLOPS, "unit": top["unit"], "frac": top["frac"],
-                "traffic": None, "peak_source": f"{peak_src} MEASURED_PEAKS.json hbm_gbs" if top["bound"] == "hbm" else
-                "fp64 DMMA.8x8x4 issue-rate microbenchmark on this pool (profiles/r01_microbench_fp64.txt); MEASURED_PEAKS.json has no fp64 figure",
-                "share_of_sweep": round(top["ms_per_sweep"] / sum(per_sweep.values()), 3),
-                "note": "ESS groups are fp64-ALU bound (2 Phi + 1 log per cell), not HBM bound: algorithmic bytes / time stays far below the copy peak by construction"}
+    # The dominant KERNEL of a sweep is the fp64 DMMA GEMM (one kernel, seven call sites); chol_K is the largest GROUP but it is 64
+    # launches of two small kernels and runs on the side stream, off the critical path (profiles/r01_launches_v5.csv).
+    gemm_groups = [k for k in per_sweep if k.startswith("gemm_") or k == "trtri"]
+    gemm_ms = sum(per_sweep[k] for k in gemm_groups)
+    gemm_flops = sum(algo[k][1] for k in gemm_groups)
+    gemm_launches = sum(launches_per[k] for k in gemm_groups)
+    ach = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
+    roofline = {"kernel": "gemm_f64_kernel<64,64,16,32,32,3> (mma.sync m8n8k4 f64 = SASS DMMA.8x8x4; tcgen05 has no fp64 kind)",
+                "bound": "tensor", "achieved": round(ach, 2), "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": round(ach / FP64_DMMA_PEAK_TFLOPS, 4),
+                "traffic": 305.3e6,
+                "traffic_note": "dram read+write of the largest launch (L*Z: algorithmic 176 MB), ncu --set full, profiles/r01_ncu_gemm64.txt",
+                "peak_source": "fp64 DMMA.8x8x4 issue-rate microbenchmark on this pool (profiles/r01_microbench_fp64.txt); MEASURED_PEAKS.json has no fp64 figure",
+                "groups": gemm_groups, "ms_per_sweep": round(gemm_ms, 4), "call_sites_per_sweep": gemm_launches,
+                "share_of_sweep": round(gemm_ms / sum(per_sweep.values()), 3),
+                "algorithmic_flops_per_sweep": gemm_flops,
+                "note": "useful flops (triangular operands counted once) over the summed durations of the kernel's launches; ncu shows the DMMA pipe "
+                        "90-91 % busy in these launches. The ESS / likelihood groups in `kernels` are issue-bound on fp64+fp32 arithmetic (2 Phi + 1 log "
+                        "per cell and evaluation), not HBM-bound: their algorithmic GB/s stays far below the copy peak by construction."}
     # log-likelihood GB/s (BASELINE metric, second half): the full-matrix ll_bar pass timed alone
     ll_ms = per_sweep.get("item_ll", 0.0)
     loglik_gbs = algo["item_ll"][1] / (ll_ms * 1e-3) / 1e9 if ll_ms > 0 else None
@@ -235,7 +249,10 @@ def ours(args):
             "config": {"workload": f"C3 synthetic ordinal n={n} x m={m} ({M_PER_GPU} items per GPU), C={C}, 5% missing", "n": n, "m": m, "C": C,
                        "l2": "working set per sweep (f, nu, Z, f*, L, W: >350 MB) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"items sharded over {world} GPU(s), theta step sharded over respondents"},
-            "gpu_launches": int(launches), "ll_after": ll, "mean_evals": E, "kernels": kernels, "roofline": roofline,
+            "gpu_launches": int(launches), "ll_after": ll, "mean_evals": E, "proposals_decided_in_fp32": screened,
+            "kernels_note": "per-group device times of a separate pass in the serial order (profiling level 1); the timed pass overlaps the "
+                            "theta-only chain (K_build, chol_K, trtri, gemm_tmp, gemm_Kpost, chol_Kpost, gemm_W) with the item kernels on a second stream",
+            "kernels": kernels, "roofline": roofline,
             "loglik_gbs": loglik_gbs}
     if rank == 0:
         line["clocks"] = clk
@@ -247,16 +264,18 @@ def ours(args):
         y_host = y_pin.numpy().T
         y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
         k = args.steps
-        t0 = time.perf_counter()
-        res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=1, beta_prior_sds=P["beta_prior_sds"],
-                                   theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104,
-                                   beta_init=P["beta0"], device=local)
-        dt = time.perf_counter() - t0
-        assert np.all(np.isfinite(res[0]["ll"]))
+        rates = []
+        for _ in range(3):  # wall clock on a shared host: the median of three calls is reported
+            t0 = time.perf_counter()
+            res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=1, beta_prior_sds=P["beta_prior_sds"],
+                                       theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104,
+                                       beta_init=P["beta0"], device=local)
+            rates.append(k / (time.perf_counter() - t0))
+            assert np.all(np.isfinite(res[0]["ll"]))
         h2d = (y_host.nbytes + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
-        line["e2e"] = {"value": k / dt, "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock incl. handle creation, fp64 y upload from pinned memory, per-sweep D2H of theta/beta/threshold/ll draws"}
+        line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
+                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 3 calls) incl. handle creation, fp64 y upload from pinned memory, per-sweep D2H of theta/beta/threshold/ll draws"}
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
             r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)

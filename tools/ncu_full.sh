@@ -10,6 +10,6 @@ cap() {  # name, kernel regex, skip, count
 }
 cap ess k_ess_items 6 3
 cap theta "k_ess_theta|k_theta_table|k_item_ll" 6 3
-cap gemm "gemm_f64_kernel<128" 6 4
-cap panel "k_chol_panel|k_trsm_left" 200 4
+cap gemm "gemm_f64_kernel" 150 6
+cap panel "k_chol_panel|k_trtri_diag" 40 4
 ls -la gpurun_out/*.ncu-rep
