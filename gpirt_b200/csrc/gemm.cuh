@@ -179,21 +179,41 @@ gemm_f64_kernel(GemmArgs g) {
     }
     cp_async_wait<0>();
 
-    // epilogue: thread holds rows grp, columns 2*tig, 2*tig+1 of each 8x8 tile
+    // epilogue: thread holds rows grp, columns 2*tig, 2*tig+1 of each 8x8 tile. With beta != 0 the C values of half a warp tile are
+    // loaded in one batch before anything is stored: load -> fma -> store per element would serialise 2*MI*NI memory round trips
+    // (the compiler must assume the store aliases the next load), which is the whole cost of a short-K update (19 us at K = 64).
+    constexpr int MH = (MI + 1) / 2;
 #pragma unroll
-    for (int i = 0; i < MI; ++i) {
-        const int row = m0 + wm0 + i * 8 + grp;
-        if (row >= g.M) continue;
+    for (int ih = 0; ih < MI; ih += MH) {
+        double cv[MH][NI][2];
+        if (g.beta != 0.0) {
 #pragma unroll
-        for (int j = 0; j < NI; ++j) {
+            for (int ii = 0; ii < MH; ++ii) {
+                const int row = m0 + wm0 + (ih + ii) * 8 + grp;
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = n0 + wn0 + j * 8 + 2 * tig + e;
-                if (col >= g.N) continue;
-                double* c = g.C + (size_t)col * g.ldc + row;
-                double v = g.alpha * acc[i][j][e];
-                if (g.beta != 0.0) v += g.beta * (*c);
-                *c = v;
+                for (int j = 0; j < NI; ++j)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int col = n0 + wn0 + j * 8 + 2 * tig + e;
+                        cv[ii][j][e] = (ih + ii < MI && row < g.M && col < g.N) ? __ldcg(g.C + (size_t)col * g.ldc + row) : 0.0;
+                    }
+            }
+        }
+#pragma unroll
+        for (int ii = 0; ii < MH; ++ii) {
+            if (ih + ii >= MI) continue;
+            const int row = m0 + wm0 + (ih + ii) * 8 + grp;
+            if (row >= g.M) continue;
+#pragma unroll
+            for (int j = 0; j < NI; ++j) {
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int col = n0 + wn0 + j * 8 + 2 * tig + e;
+                    if (col >= g.N) continue;
+                    double v = g.alpha * acc[ih + ii][j][e];
+                    if (g.beta != 0.0) v += g.beta * cv[ii][j][e];
+                    g.C[(size_t)col * g.ldc + row] = v;
+                }
             }
         }
     }

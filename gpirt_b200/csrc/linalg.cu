@@ -151,6 +151,14 @@ namespace gpirt {
 // (History: a fully unrolled 64-step substitution was instruction-fetch bound at 70-150 us per launch; the one-column-per-barrier
 // version that followed spent ~600 cycles per column, profiles/r01_launches_v3.csv.)
 constexpr int TILE_THREADS = 256;
+#ifdef GPIRT_PANEL_CLOCKS
+__device__ unsigned long long g_potf2_clk[4];
+#define TCLK_BEGIN long long tclk_ = clock64()
+#define TCLK_END(i, cond) do { if ((cond) && blockIdx.x == 1) atomicAdd(&g_potf2_clk[i], (unsigned long long)(clock64() - tclk_)); } while (0)
+#else
+#define TCLK_BEGIN
+#define TCLK_END(i, cond)
+#endif
 
 struct TileShared {       // state of one elimination step; kernels keep two and alternate (one barrier less per step)
     double D[4][4];        // factored diagonal 4 x 4 block (lower part valid)
@@ -181,15 +189,18 @@ template <bool FROM_LS>
 __device__ __forceinline__ void step_block_column(double (&a)[4][4], int s, int tr, int tc, const double (&D)[4][4], const double (&Dinv)[4],
                                                   double (*P)[CHOL_NB], double (*Ls)[CHOL_NB + 1], int first_rb) {
     if (tc == s && tr >= first_rb) {
+        TCLK_BEGIN;
 #pragma unroll
         for (int p = 0; p < 4; ++p) {
             row_solve4(a[p], D, Dinv);
 #pragma unroll
             for (int q = 0; q < 4; ++q) P[q][4 * tr + p] = a[p][q];
         }
+        TCLK_END(1, !FROM_LS && tr == 15);
     }
     __syncthreads();
     if (tc > s && (FROM_LS || tr >= tc)) {
+        TCLK_BEGIN;
         double xr[4][4], lc[4][4];
 #pragma unroll
         for (int p = 0; p < 4; ++p)
@@ -204,6 +215,7 @@ __device__ __forceinline__ void step_block_column(double (&a)[4][4], int s, int 
             for (int q = 0; q < 4; ++q)
 #pragma unroll
                 for (int k = 0; k < 4; ++k) a[p][q] -= xr[p][k] * lc[q][k];
+        TCLK_END(2, !FROM_LS && tr == 15 && tc == 15);
     }
 }
 
@@ -212,6 +224,7 @@ __device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, Ti
     for (int s = 0; s < 16; ++s) {
         TileShared& sh = sh2[s & 1];
         if (tr == s && tc == s) {  // the diagonal 4 x 4 block: unblocked Cholesky in registers
+            TCLK_BEGIN;
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
                 double d = a[j][j];
@@ -238,6 +251,7 @@ __device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, Ti
                     sh.D[i][j] = a[i][j];
                     sh.P[j][4 * s + i] = a[i][j];  // the factor's own rows of the block column (upper part zero)
                 }
+            TCLK_END(0, true);
         }
         __syncthreads();
         double D[4][4], Dinv[4];
@@ -258,6 +272,12 @@ __device__ __forceinline__ void tile_potf2(double (&a)[4][4], int tr, int tc, Ti
 // In-place hazard: CTAs b >= 1 read the ORIGINAL diagonal block that CTA 0 overwrites with its factor. A CTA may start late (the
 // panel runs next to other streams' kernels), so CTA 0 holds its write-back until every other CTA has announced, through *readers,
 // that its copy of the block is in registers.
+#ifdef GPIRT_PANEL_CLOCKS
+__device__ long long g_panel_clk[8];
+#define PCLK(i) do { __syncthreads(); if (blockIdx.x == 1 && threadIdx.x == 0) g_panel_clk[i] = clock64(); } while (0)
+#else
+#define PCLK(i)
+#endif
 __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict__ A, int ld, int kb, int rows_below, int* info, int k0,
                                                              int* readers) {
     constexpr int NB = CHOL_NB;
@@ -273,12 +293,15 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
             const int r = 4 * tr + p, c = 4 * tc + q;
             a[p][q] = (r < kb && c < kb && c <= r) ? A[(size_t)c * ld + r] : (c == r ? 1.0 : 0.0);
         }
+    PCLK(0);
     if (blockIdx.x != 0) {
         __threadfence();  // this thread's loads of the block are performed
         __syncthreads();
         if (threadIdx.x == 0) atomicAdd(readers, 1);
     }
+    PCLK(1);
     tile_potf2(a, tr, tc, sh2, info, k0, blockIdx.x == 0);
+    PCLK(2);
     if (blockIdx.x == 0) {
         if (threadIdx.x == 0) {
             while (atomicAdd(readers, 0) < (int)gridDim.x - 1) __nanosleep(64);
@@ -317,6 +340,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
             a[p][q] = (r < rows_below) ? A21[(size_t)c * ld + r] : 0.0;
         }
     __syncthreads();  // Ls, inv_diag visible
+    PCLK(3);
     for (int s = 0; s < 16; ++s) {
         double D[4][4], Dinv[4];
         if (tc == s) {
@@ -329,6 +353,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
         }
         step_block_column<true>(a, s, tr, tc, D, Dinv, sh2[s & 1].P, Ls, 0);
     }
+    PCLK(4);
 #pragma unroll
     for (int q = 0; q < 4; ++q)
 #pragma unroll
@@ -336,6 +361,7 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
             const int r = row0 + 4 * tr + p, c = 4 * tc + q;
             if (r < rows_below) A21[(size_t)c * ld + r] = a[p][q];
         }
+    PCLK(5);
 }
 
 // Substitution with a 64 x 64 triangular block held in shared memory as M[i][j] = L(j, i) (TRANS false) or L(i, j) (TRANS true), so
