@@ -63,6 +63,7 @@ SYMBOLS = [
     "gpirt_last_error", "gpirt_device_count", "gpirt_K", "gpirt_K_time", "gpirt_delta_to_threshold",
     "gpirt_threshold_to_delta", "gpirt_chol", "gpirt_double_solve", "gpirt_create", "gpirt_destroy", "gpirt_set_stream",
     "gpirt_set_data_f64", "gpirt_set_data_i8", "gpirt_set_priors", "gpirt_set_state", "gpirt_get_state", "gpirt_get_L",
+    "gpirt_store_open", "gpirt_store_push", "gpirt_store_count", "gpirt_store_flush", "gpirt_store_close", "gpirt_store_sample_bytes",
     "gpirt_set_iter", "gpirt_set_solver", "gpirt_set_overlap", "gpirt_set_screen", "gpirt_get_exact_evals", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_exchange_buffer",
@@ -83,6 +84,7 @@ def lib():
         L = C.CDLL(LIB_PATH)
         L.gpirt_last_error.restype = C.c_char_p
         L.gpirt_launch_count.restype = C.c_longlong
+        L.gpirt_store_sample_bytes.restype = C.c_int64
         for s in SYMBOLS:
             getattr(L, s)  # AttributeError if the build is stale
         _lib = L

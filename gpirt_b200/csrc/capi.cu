@@ -111,6 +111,15 @@ __global__ void k_init_beta(double* beta, const double* means, const double* sds
     for (int q = 0; q < 3; ++q) beta[3 * (size_t)J + q] = means[3 * (size_t)J + q] + sds[3 * (size_t)J + q] * philox_normal(key, ST_INIT_BETA, J, q);
 }
 
+// thresholds item-major (C+1) x m -> the reference's m x (C+1) column-major slice of threshold_draws
+__global__ void k_store_thr(const double* __restrict__ thr, int C1, int m, double* __restrict__ out) {
+    int e = blockIdx.x * blockDim.x + threadIdx.x;  // e = c * m + J
+    if (e < C1 * m) {
+        const int c = e / m, J = e - c * m;
+        out[e] = thr[(size_t)J * C1 + c];
+    }
+}
+
 extern "C" {
 
 const char* gpirt_last_error(void) { return g_err; }
@@ -212,6 +221,8 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     return GPIRT_OK;
 }
 
+static void store_free(gpirt_sampler* h);
+
 int gpirt_destroy(gpirt_sampler* h) {
     if (!h) return GPIRT_OK;
     cudaSetDevice(h->cfg.device);
@@ -230,6 +241,7 @@ int gpirt_destroy(gpirt_sampler* h) {
         if (h->exact[b]) cudaFree(h->exact[b]);
         if (h->margin[b]) cudaFree(h->margin[b]);
     }
+    store_free(h);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
     return GPIRT_OK;
@@ -461,6 +473,101 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
         cudaFree(tmp);
     }
     CU(cudaStreamSynchronize(st));
+    return GPIRT_OK;
+}
+
+
+// ---- device-side draw store ----
+static void store_free(gpirt_sampler* h) {
+    auto& s = h->store;
+    for (double* p : {s.theta, s.beta, s.thr, s.ll, s.f, s.fstar})
+        if (p) cudaFree(p);
+    s = gpirt_sampler::DrawStore();
+}
+int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar) {
+    if (!h) return 0;
+    int64_t b = 8LL * (h->n + 3LL * h->m_total + (int64_t)(h->C + 1) * h->m_total + 1);
+    if (store_f) b += 8LL * h->n * h->m_total;
+    if (store_fstar) b += 8LL * NGRID * h->m_total;
+    return b;
+}
+int gpirt_store_open(gpirt_sampler* h, int capacity, int store_f, int store_fstar) {
+    CHECK_H(h);
+    if (h->world != 1) return fail(GPIRT_ERR_UNSUPPORTED, "draw store on an item shard: not built (gather the state per sample instead)");
+    if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "draw store needs 3 mean coefficients per item");
+    if (capacity < 1) return fail(GPIRT_ERR_INVALID, "store_open: capacity %d", capacity);
+    CU(cudaSetDevice(h->cfg.device));
+    store_free(h);
+    auto& s = h->store;
+    const size_t cap = (size_t)capacity, m = (size_t)h->m_total;
+    CU(cudaMalloc((void**)&s.theta, cap * h->n * 8));
+    CU(cudaMalloc((void**)&s.beta, cap * 3 * m * 8));
+    CU(cudaMalloc((void**)&s.thr, cap * (h->C + 1) * m * 8));
+    CU(cudaMalloc((void**)&s.ll, cap * 8));
+    if (store_f) CU(cudaMalloc((void**)&s.f, cap * h->n * m * 8));
+    if (store_fstar) CU(cudaMalloc((void**)&s.fstar, cap * NGRID * m * 8));
+    s.cap = capacity;
+    s.count = 0;
+    return GPIRT_OK;
+}
+int gpirt_store_push(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    auto& s = h->store;
+    if (s.cap < 1) return fail(GPIRT_ERR_INVALID, "store_push: no store open");
+    if (s.count >= s.cap) return fail(GPIRT_ERR_INVALID, "store_push: store full (%d samples): flush first", s.cap);
+    cudaStream_t st = h->stream;
+    const size_t k = (size_t)s.count, m = (size_t)h->m_total;
+    const int C1 = h->C + 1;
+    // theta, beta, thresholds, f and f* are written by main-stream kernels only (the side stream owns L, L^-1, W, K_post)
+    CU(cudaMemcpyAsync(s.theta + k * h->n, h->theta, (size_t)h->n * 8, cudaMemcpyDeviceToDevice, st));
+    CU(cudaMemcpyAsync(s.beta + k * 3 * m, h->beta, 3 * m * 8, cudaMemcpyDeviceToDevice, st));
+    k_store_thr<<<(C1 * h->m_total + 255) / 256, 256, 0, st>>>(h->thr, C1, h->m_total, s.thr + k * C1 * m);
+    ++g_kernel_launches;
+    CU(cudaGetLastError());
+    CU(launch_ordered_sum(st, h->item_ll, h->m_total, s.ll + k));  // the per-item terms of the sweep's last step (src/gpirtMCMC.cpp:324-331)
+    if (s.f)
+        CU(cudaMemcpy2DAsync(s.f + k * h->n * m, (size_t)h->n * 8, h->f, (size_t)h->ldn * 8, (size_t)h->n * 8, h->m_total, cudaMemcpyDeviceToDevice, st));
+    if (s.fstar)  // the table is m x NGRID (ld_chunk) column-major in (item, grid point): back to NGRID x m
+        CU(launch_transpose(st, h->fstar, h->ld_chunk, h->m_total, NGRID, s.fstar + k * NGRID * m, NGRID));
+    s.count += 1;
+    return GPIRT_OK;
+}
+int gpirt_store_count(gpirt_sampler* h, int* count, int* capacity) {
+    CHECK_H(h);
+    if (count) *count = h->store.count;
+    if (capacity) *capacity = h->store.cap;
+    return GPIRT_OK;
+}
+int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_draws, double* beta_draws, double* threshold_draws,
+                      double* ll_draws, double* f_draws, double* fstar_draws) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    auto& s = h->store;
+    if (s.cap < 1) return fail(GPIRT_ERR_INVALID, "store_flush: no store open");
+    if (first < 0 || first + s.count > n_samples) return fail(GPIRT_ERR_INVALID, "store_flush: samples %d..%d outside 0..%d", first, first + s.count, n_samples);
+    TRY(check_flags(h));  // one synchronisation for everything pushed since the last flush
+    const size_t cnt = (size_t)s.count, m = (size_t)h->m_total, n = (size_t)h->n, C1 = (size_t)h->C + 1;
+    if (cnt == 0) return GPIRT_OK;
+    if (theta_draws) {  // cube n_samples x n x 1: sample index is the fast one
+        std::vector<double> t(cnt * n);
+        CU(cudaMemcpy(t.data(), s.theta, t.size() * 8, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < n; ++i)
+            for (size_t k = 0; k < cnt; ++k) theta_draws[(size_t)first + k + i * (size_t)n_samples] = t[k * n + i];
+    }
+    if (beta_draws) CU(cudaMemcpy(beta_draws + (size_t)first * 3 * m, s.beta, cnt * 3 * m * 8, cudaMemcpyDeviceToHost));
+    if (threshold_draws) CU(cudaMemcpy(threshold_draws + (size_t)first * C1 * m, s.thr, cnt * C1 * m * 8, cudaMemcpyDeviceToHost));
+    if (ll_draws) CU(cudaMemcpy(ll_draws + first, s.ll, cnt * 8, cudaMemcpyDeviceToHost));
+    if (f_draws && s.f) CU(cudaMemcpy(f_draws + (size_t)first * n * m, s.f, cnt * n * m * 8, cudaMemcpyDeviceToHost));
+    if (fstar_draws && s.fstar) CU(cudaMemcpy(fstar_draws + (size_t)first * NGRID * m, s.fstar, cnt * NGRID * m * 8, cudaMemcpyDeviceToHost));
+    s.count = 0;
+    return GPIRT_OK;
+}
+int gpirt_store_close(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));
+    store_free(h);
     return GPIRT_OK;
 }
 

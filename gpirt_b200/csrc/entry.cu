@@ -4,6 +4,7 @@
 // Host side only: sample storage, thinning and the progress/interrupt poll; all arithmetic runs in the
 // kernels behind the subsystem calls.
 #include <cstdio>
+#include <algorithm>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -49,20 +50,36 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
 
     const int total = a->sample_iterations + a->burn_iterations;
     const int n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
-    const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1;
-    std::vector<double> theta(n);
+    // The kept draws stay on the device and come back in bulk: no host synchronisation per sweep, so the next sweep's theta-only
+    // chain keeps running under this sweep's tail. Capacity: as many samples as fit in a quarter of the free device memory.
+    int cap = 0, first = 0;
+    if (n_samples > 0) {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return GPIRT_ERR_CUDA;
+        const int64_t per = gpirt_store_sample_bytes(h, a->f_draws != nullptr, a->fstar_draws != nullptr);
+        cap = (int)std::max<int64_t>(1, std::min<int64_t>(n_samples, (int64_t)(free_b / 4) / per));
+        TRYC(gpirt_store_open(h, cap, a->f_draws != nullptr, a->fstar_draws != nullptr));
+    }
+    auto flush = [&]() -> int {
+        int cnt = 0;
+        TRYC(gpirt_store_count(h, &cnt, nullptr));
+        TRYC(gpirt_store_flush(h, n_samples, first, a->theta_draws, a->beta_draws, a->threshold_draws, a->ll_draws, a->f_draws, a->fstar_draws));
+        first += cnt;
+        return GPIRT_OK;
+    };
     for (int iter = 0; iter < total; ++iter) {
         if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;  // user interrupt
         TRYC(gpirt_sweep(h, 1));
         if (iter >= a->burn_iterations && iter % a->THIN == 0) {  // src/gpirtMCMC.cpp:334-335
             const int s = (iter - a->burn_iterations) / a->THIN;
             if (s >= n_samples) continue;  // the reference would write past theta_draws here
-            TRYC(gpirt_get_state(h, theta.data(), a->beta_draws + (size_t)s * 3 * m, a->f_draws ? a->f_draws + (size_t)s * n * m : nullptr,
-                                 a->threshold_draws + (size_t)s * m * C1, a->fstar_draws ? a->fstar_draws + (size_t)s * GPIRT_NGRID * m : nullptr));
-            for (size_t i = 0; i < n; ++i) a->theta_draws[(size_t)s + i * n_samples] = theta[i];  // cube n_samples x n x 1
-            TRYC(gpirt_total_ll(h, &a->ll_draws[s]));
+            TRYC(gpirt_store_push(h));
+            int cnt = 0;
+            TRYC(gpirt_store_count(h, &cnt, nullptr));
+            if (cnt == cap) TRYC(flush());
         }
     }
+    if (n_samples > 0) TRYC(flush());
     return gpirt_sync(h);
 }
 

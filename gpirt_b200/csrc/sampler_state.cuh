@@ -75,6 +75,11 @@ struct gpirt_sampler {
     // staging for supplied streams
     double *d_z = nullptr, *d_u = nullptr;
     size_t d_z_cap = 0, d_u_cap = 0;
+    // device-side store of the draws gpirtMCMC keeps (src/gpirtMCMC.cpp:230-255,334-356): appended on the stream, read back in bulk
+    struct DrawStore {
+        int cap = 0, count = 0;
+        double *theta = nullptr, *beta = nullptr, *thr = nullptr, *ll = nullptr, *f = nullptr, *fstar = nullptr;  // [cap][per-sample block]
+    } store;
 
     gpirt::RngKey key() const {
         gpirt::RngKey k;

@@ -155,6 +155,33 @@ class Sampler:
         check(self._L.gpirt_get_L(self._h, _p(out)))
         return out
 
+    # ---- device-side store of kept draws (src/gpirtMCMC.cpp:230-255,334-356) ----
+    def store_open(self, capacity, store_f=False, store_fstar=False):
+        check(self._L.gpirt_store_open(self._h, int(capacity), int(store_f), int(store_fstar)))
+        self._store_flags = (bool(store_f), bool(store_fstar))
+
+    def store_push(self):
+        """Appends the current state as the next sample; no host synchronisation."""
+        check(self._L.gpirt_store_push(self._h))
+
+    def store_count(self):
+        cnt, cap = C.c_int(), C.c_int()
+        check(self._L.gpirt_store_count(self._h, C.byref(cnt), C.byref(cap)))
+        return cnt.value, cap.value
+
+    def store_sample_bytes(self, store_f=False, store_fstar=False):
+        return int(self._L.gpirt_store_sample_bytes(self._h, int(store_f), int(store_fstar)))
+
+    def store_flush(self, out, first):
+        """Writes the buffered samples as samples first.. of the reference-layout arrays in `out` (keys theta [n_samples, n, 1], beta
+        [3, m, 1, n_samples], threshold [m, C+1, 1, n_samples], ll [n_samples], optional f, fstar), all Fortran-ordered."""
+        n_samples = out["ll"].shape[0]
+        check(self._L.gpirt_store_flush(self._h, int(n_samples), int(first), _p(out.get("theta")), _p(out.get("beta")), _p(out.get("threshold")),
+                                        _p(out.get("ll")), _p(out.get("f")), _p(out.get("fstar"))))
+
+    def store_close(self):
+        check(self._L.gpirt_store_close(self._h))
+
     def set_iter(self, it):
         check(self._L.gpirt_set_iter(self._h, C.c_uint32(it)))
 

@@ -115,6 +115,21 @@ int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, c
                     const double* fstar);
 int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, double* thresholds, double* fstar);
 int gpirt_get_L(gpirt_sampler* h, double* L /* n x n, upper triangle zero */);
+/* Device-side store of the draws gpirtMCMC() keeps (theta_draws / beta_draws / threshold_draws / ll_draws / f_draws / fstar_draws,
+ * src/gpirtMCMC.cpp:230-255,334-356). gpirt_store_push appends the current state as sample number `count` WITHOUT a host
+ * synchronisation (copies and the ordered log-likelihood sum are enqueued on the sampler's stream, in the reference's layouts);
+ * gpirt_store_flush synchronises once, reports any error raised by the sweeps since the last synchronisation, and writes the
+ * `count` buffered samples as samples first .. first+count-1 of the reference's output arrays (theta: cube n_samples x n x 1;
+ * per sample: beta 3 x m, thresholds m x (C+1), f n x m, fstar NGRID x m; ll: n_samples), then empties the store.
+ * NULL outputs are skipped. world == 1 only. */
+int gpirt_store_open(gpirt_sampler* h, int capacity, int store_f, int store_fstar);
+int gpirt_store_push(gpirt_sampler* h);
+int gpirt_store_count(gpirt_sampler* h, int* count, int* capacity);
+int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_draws, double* beta_draws, double* threshold_draws,
+                      double* ll_draws, double* f_draws, double* fstar_draws);
+int gpirt_store_close(gpirt_sampler* h);
+/* bytes of device memory one stored sample takes (to size `capacity`) */
+int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar);
 int gpirt_set_iter(gpirt_sampler* h, uint32_t iter);         /* sweep counter used to key the Philox streams */
 /* How draw_fstar applies L^-1 / L^-T to k* (solve(trimatl(L), kstar) and double_solve, src/draw-fstar.cpp:30,51, src/cholesky-cache.cpp:4-9):
  * 0 = blocked forward/back substitution (backward stable, n/64 dependent steps); 1 = explicit L^-1 by parallel block inversion, then
