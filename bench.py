@@ -275,7 +275,7 @@ def ours(args):
         h2d = (y_host.nbytes + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
-                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 3 calls) incl. handle creation, fp64 y upload from pinned memory, per-sweep D2H of theta/beta/threshold/ll draws"}
+                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 3 calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
             r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)

@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstring>
 #include <limits>
+#include <type_traits>
 #include <vector>
 
 #include "probit.cuh"
@@ -82,14 +83,6 @@ static int quiesce(gpirt_sampler* h) {
     return wait_shared(h);
 }
 
-template <class T>
-static int dalloc(T** p, size_t count) {
-    *p = nullptr;
-    if (count == 0) count = 1;
-    CU(cudaMalloc((void**)p, count * sizeof(T)));
-    CU(cudaMemset(*p, 0, count * sizeof(T)));
-    return GPIRT_OK;
-}
 #define TRY(x)                   \
     do {                         \
         int rc_ = (x);           \
@@ -188,36 +181,55 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
     }
     const size_t mt = (size_t)h->world * h->m_chunk;
-    TRY(dalloc(&h->y_im, (size_t)h->ldy * std::max(h->m_local, 1)));
-    TRY(dalloc(&h->y_rm, (size_t)h->ldm * std::max(h->n_local, 1)));
-    TRY(dalloc(&h->theta, (size_t)h->world * h->n_chunk));
-    TRY(dalloc(&h->theta_x, (size_t)h->world * h->n_chunk));
-    TRY(dalloc(&h->beta, 3 * mt));
-    TRY(dalloc(&h->thr, (size_t)(h->C + 1) * mt));
-    TRY(dalloc(&h->f, (size_t)h->ldn * h->m_local));
-    TRY(dalloc(&h->nu, (size_t)h->ldn * h->m_local));
-    TRY(dalloc(&h->zbuf, (size_t)h->ldz * h->m_local));
-    TRY(dalloc(&h->fstar, (size_t)h->world * NGRID * h->ld_chunk));
-    TRY(dalloc(&h->L, (size_t)h->ldn * h->n));
-    TRY(dalloc(&h->W, (size_t)h->ldn * NGRID));
-    TRY(dalloc(&h->Kpost, (size_t)h->ldN * NGRID));
-    TRY(dalloc(&h->tstar, (size_t)h->ldN));
-    TRY(dalloc(&h->sds, 3 * mt));
-    TRY(dalloc(&h->tps, 2 * (size_t)h->n));
-    TRY(dalloc(&h->item_ll, mt));
-    TRY(dalloc(&h->total_ll, 1));
-    TRY(dalloc(&h->flags, 1));
-    TRY(dalloc(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID))));
+    // one device allocation for everything a handle owns for life (create + destroy cost one cudaMalloc / cudaFree, which is what an
+    // end-to-end gpirtMCMC() call of a few sweeps notices), carved into 256-byte aligned pieces, zero-filled on the handle's stream
+    struct Piece { void** p; size_t bytes; };
+    std::vector<Piece> pieces;
+    size_t arena_bytes = 0;
+    auto want = [&](auto** p, size_t count) {
+        using T = std::remove_pointer_t<std::remove_pointer_t<decltype(p)>>;
+        const size_t b = ((std::max<size_t>(count, 1) * sizeof(T)) + 255) & ~(size_t)255;
+        pieces.push_back({(void**)p, b});
+        arena_bytes += b;
+    };
+    want(&h->y_im, (size_t)h->ldy * std::max(h->m_local, 1));
+    want(&h->y_rm, (size_t)h->ldm * std::max(h->n_local, 1));
+    want(&h->theta, (size_t)h->world * h->n_chunk);
+    want(&h->theta_x, (size_t)h->world * h->n_chunk);
+    want(&h->beta, 3 * mt);
+    want(&h->thr, (size_t)(h->C + 1) * mt);
+    want(&h->f, (size_t)h->ldn * h->m_local);
+    want(&h->nu, (size_t)h->ldn * h->m_local);
+    want(&h->zbuf, (size_t)h->ldz * h->m_local);
+    want(&h->fstar, (size_t)h->world * NGRID * h->ld_chunk);
+    want(&h->L, (size_t)h->ldn * h->n);
+    want(&h->W, (size_t)h->ldn * NGRID);
+    want(&h->Kpost, (size_t)h->ldN * NGRID);
+    want(&h->tstar, (size_t)h->ldN);
+    want(&h->sds, 3 * mt);
+    want(&h->tps, 2 * (size_t)h->n);
+    want(&h->item_ll, mt);
+    want(&h->total_ll, 1);
+    want(&h->flags, 1);
+    want(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID)));
+    want(&h->Linv, (size_t)h->ldn * h->n);  // block-inverse solver of draw_fstar (the default)
+    want(&h->W2, (size_t)h->ldn * NGRID);
+    want(&h->tri_scratch, trtri_scratch_elems(h->n));
     for (int b = 0; b < 5; ++b) {
         size_t units = (b == GPIRT_BLOCK_THETA) ? (size_t)h->world * h->n_chunk : mt;
-        TRY(dalloc(&h->evals[b], units));
-        TRY(dalloc(&h->exact[b], units));
-        TRY(dalloc(&h->margin[b], units));
+        want(&h->evals[b], units);
+        want(&h->exact[b], units);
+        want(&h->margin[b], units);
+    }
+    CU(cudaMalloc((void**)&h->arena, arena_bytes));
+    CU(cudaMemsetAsync(h->arena, 0, arena_bytes, h->stream));
+    {
+        size_t off = 0;
+        for (const Piece& pc : pieces) { *pc.p = h->arena + off; off += pc.bytes; }
     }
     k_fill_grid<<<(NGRID + 255) / 256, 256, 0, h->stream>>>(h->tstar);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    CU(cudaDeviceSynchronize());  // the zero-fills above ran on the legacy stream
     return GPIRT_OK;
 }
 
@@ -232,15 +244,8 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_L) cudaEventDestroy(h->ev_L);
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
     if (h->side) cudaStreamDestroy(h->side);
-    void* ptrs[] = {h->y_im, h->y_rm, h->theta, h->theta_x, h->beta, h->thr, h->f, h->nu, h->zbuf, h->fstar, h->L, h->W, h->Kpost,
-                    h->tstar, h->sds, h->tps, h->item_ll, h->total_ll, h->flags, h->d_z, h->d_u, h->theta_tab, h->Linv, h->W2, h->tri_scratch, h->chol_ws};
-    for (void* p : ptrs)
+    for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
         if (p) cudaFree(p);
-    for (int b = 0; b < 5; ++b) {
-        if (h->evals[b]) cudaFree(h->evals[b]);
-        if (h->exact[b]) cudaFree(h->exact[b]);
-        if (h->margin[b]) cudaFree(h->margin[b]);
-    }
     store_free(h);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -682,12 +687,6 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
     const double* tmp = h->W;  // L^-1 k*
     if (h->solver == 1) {
         // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
-        if (!h->Linv) {
-            TRY(dalloc(&h->Linv, (size_t)h->ldn * h->n));
-            TRY(dalloc(&h->W2, (size_t)h->ldn * NGRID));
-            TRY(dalloc(&h->tri_scratch, trtri_scratch_elems(h->n)));
-            CU(cudaDeviceSynchronize());  // dalloc zero-fills on the legacy stream
-        }
         SEC_ST(h, st, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
         GemmArgs g{};
         g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->W2; g.ldc = h->ldn;

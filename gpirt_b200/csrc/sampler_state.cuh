@@ -74,6 +74,7 @@ struct gpirt_sampler {
 
     // staging for supplied streams
     double *d_z = nullptr, *d_u = nullptr;
+    char* arena = nullptr;  // the one allocation behind every buffer above
     size_t d_z_cap = 0, d_u_cap = 0;
     // device-side store of the draws gpirtMCMC keeps (src/gpirtMCMC.cpp:230-255,334-356): appended on the stream, read back in bulk
     struct DrawStore {
