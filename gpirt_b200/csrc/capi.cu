@@ -343,27 +343,60 @@ int gpirt_sync(gpirt_sampler* h) {
     return check_flags(h);
 }
 
+// Rows [row0, row0 + nrows) x columns [col0, col0 + ncols) of the host matrix y (n x m_total doubles, NaN = missing) as int8 codes on the
+// device (nrows x ncols, column-major), staged in column slabs so the fp64 copy never needs more than 256 MB of device memory.
+static int upload_block_i8(gpirt_sampler* h, const double* y, long long row0, long long nrows, long long col0, long long ncols, int8_t* d_out,
+                           double* d_stage, long long slab_cols) {
+    for (long long c0 = 0; c0 < ncols; c0 += slab_cols) {
+        const long long cols = std::min<long long>(slab_cols, ncols - c0);
+        CU(cudaMemcpy2DAsync(d_stage, (size_t)nrows * 8, y + (col0 + c0) * h->n + row0, (size_t)h->n * 8, (size_t)nrows * 8, (size_t)cols,
+                             cudaMemcpyHostToDevice, h->stream));
+        CU(launch_y_to_i8(h->stream, d_stage, cols * nrows, h->C, d_out + c0 * nrows, h->flags));
+    }
+    return GPIRT_OK;
+}
+
 int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
     CHECK_H(h);
     if (!y) return fail(GPIRT_ERR_INVALID, "set_data: NULL y");
     CU(cudaSetDevice(h->cfg.device));
-    const long long count = (long long)h->n * h->m_total;
-    double* d_y = nullptr;
-    int8_t* d_full = nullptr;
-    // staged in column slabs so the fp64 copy of y never needs more than 256 MB of device memory
-    const long long slab_cols = std::max(1LL, (256LL << 20) / (8LL * h->n));
-    CU(cudaMalloc((void**)&d_full, (size_t)count));
-    CU(cudaMalloc((void**)&d_y, (size_t)std::min<long long>(slab_cols, h->m_total) * h->n * 8));
-    for (long long c0 = 0; c0 < h->m_total; c0 += slab_cols) {
-        const long long cols = std::min<long long>(slab_cols, h->m_total - c0);
-        CU(cudaMemcpyAsync(d_y, y + c0 * h->n, (size_t)cols * h->n * 8, cudaMemcpyHostToDevice, h->stream));
-        CU(launch_y_to_i8(h->stream, d_y, cols * h->n, h->C, d_full + c0 * h->n, h->flags));
+    // A shard uploads what it keeps: its items' columns (item-major layout) and its respondents' rows (theta step) — 2/world of y.
+    struct Block { long long row0, nrows, col0, ncols; };
+    std::vector<Block> blocks;
+    if (h->world == 1) blocks.push_back({0, h->n, 0, h->m_total});
+    else {
+        blocks.push_back({0, h->n, h->item0, h->m_local});
+        blocks.push_back({h->resp0, h->n_local, 0, h->m_total});
     }
-    int rc = build_layouts(h, d_full);
+    long long max_rows = 1, max_count = 1;
+    for (const Block& b : blocks) { max_rows = std::max(max_rows, b.nrows); max_count = std::max(max_count, b.nrows * b.ncols); }
+    const long long slab_cols = std::max(1LL, (256LL << 20) / (8LL * max_rows));
+    double* d_y = nullptr;
+    int8_t* d_i8 = nullptr;
+    CU(cudaMalloc((void**)&d_i8, (size_t)max_count));
+    CU(cudaMalloc((void**)&d_y, (size_t)std::min<long long>(slab_cols * max_rows, max_count) * 8));
+    int rc = GPIRT_OK;
+    CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
+    CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
+    for (size_t k = 0; k < blocks.size() && rc == GPIRT_OK; ++k) {
+        const Block& b = blocks[k];
+        if (b.nrows <= 0 || b.ncols <= 0) continue;
+        rc = upload_block_i8(h, y, b.row0, b.nrows, b.col0, b.ncols, d_i8, d_y, slab_cols);
+        if (rc != GPIRT_OK) break;
+        cudaError_t e;
+        if (h->world == 1)
+            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_total, 0, h->m_total, h->y_im, h->ldy, 0, h->n, h->y_rm, h->ldm);
+        else if (k == 0)  // the block IS the local items: item-major layout only
+            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_local, 0, h->m_local, h->y_im, h->ldy, 0, 0, h->y_rm, h->ldm);
+        else              // the block IS the local respondents: respondent-major layout only
+            e = launch_y_layouts(h->stream, d_i8, h->n_local, h->m_total, 0, 0, h->y_im, h->ldy, 0, h->n_local, h->y_rm, h->ldm);
+        if (e != cudaSuccess) rc = fail(GPIRT_ERR_CUDA, "y layouts: %s", cudaGetErrorString(e));
+    }
     cudaStreamSynchronize(h->stream);
     cudaFree(d_y);
-    cudaFree(d_full);
+    cudaFree(d_i8);
     if (rc != GPIRT_OK) return rc;
+    h->have_data = true;
     return check_flags(h);
 }
 
@@ -498,7 +531,8 @@ int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar)
 }
 int gpirt_store_open(gpirt_sampler* h, int capacity, int store_f, int store_fstar) {
     CHECK_H(h);
-    if (h->world != 1) return fail(GPIRT_ERR_UNSUPPORTED, "draw store on an item shard: not built (gather the state per sample instead)");
+    if (h->world != 1 && (store_f || store_fstar))  // theta, beta, thresholds and the item terms are complete on every rank after the exchanges
+        return fail(GPIRT_ERR_UNSUPPORTED, "draw store of f / f* on an item shard: not built (each rank holds its own items only)");
     if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "draw store needs 3 mean coefficients per item");
     if (capacity < 1) return fail(GPIRT_ERR_INVALID, "store_open: capacity %d", capacity);
     CU(cudaSetDevice(h->cfg.device));

@@ -84,3 +84,46 @@ class ShardedSampler:
 
     def __getattr__(self, name):  # set_data, set_priors, set_state, get_state, sync, ...
         return getattr(self.S, name)
+
+
+def gpirtMCMC_sharded(data, sample_iterations, burn_iterations, THIN=1, *, rank, world, device, group=None, beta_prior_sds=None,
+                      theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern", theta_init=None, thresholds=None, SEED=1, chain=0,
+                      beta_init=None, f_init=None):
+    """gpirtMCMC() (R/gpirtMCMC.R:98-167, src/gpirtMCMC.cpp:25-406) for one chain sharded over `world` ranks: every rank calls it with
+    the same host arrays and gets the same theta / beta / threshold / ll draws back (reference layouts). Each rank uploads only its
+    items' columns and its respondents' rows of y; kept draws are buffered on the device and read back in bulk. f / f* draws are
+    not kept (each rank holds its own items only). The chain is the one the single-GPU gpirtMCMC(SEED=SEED) produces."""
+    from .api import _as_cube, _F
+
+    y = _as_cube(data)
+    n, m, H = y.shape
+    if H != 1:
+        raise NotImplementedError("horizon > 1")
+    thr = np.asfortranarray(np.asarray(thresholds, dtype=np.float64).reshape(m, -1))
+    Ccat = thr.shape[1] - 1
+    bps = _F(np.full((3, m), 3.0) if beta_prior_sds is None else beta_prior_sds)
+    tps = _F(np.zeros((2, n)) if theta_prior_sds is None else theta_prior_sds)
+    S = ShardedSampler(n, m, Ccat, rank=rank, world=world, device=device, group=group, theta_os=theta_os, theta_ls=theta_ls, KERNEL=KERNEL,
+                       seed=SEED, chain=chain)
+    try:
+        S.set_data(y[:, :, 0])
+        S.set_priors(bps, tps)
+        S.set_state(theta=theta_init, beta=beta_init, f=f_init, thresholds=thr)
+        S.set_iter(0xFFFFFFFF)  # as gpirt_mcmc: the initial draws use a sweep id no sweep reaches
+        S.init_draw(draw_beta=beta_init is None, draw_f=f_init is None)
+        S.set_iter(0)
+        n_samples = int(sample_iterations / THIN)  # src/gpirtMCMC.cpp:48
+        out = dict(theta=np.zeros((n_samples, n, 1), order="F"), beta=np.zeros((3, m, 1, n_samples), order="F"),
+                   threshold=np.zeros((m, Ccat + 1, 1, n_samples), order="F"), ll=np.zeros(n_samples))
+        if n_samples > 0:
+            S.store_open(n_samples)
+        for it in range(sample_iterations + burn_iterations):
+            S.sweep(1)
+            if it >= burn_iterations and it % THIN == 0 and (it - burn_iterations) // THIN < n_samples:  # :334-335
+                S.store_push()
+        if n_samples > 0:
+            S.store_flush(out, 0)
+    finally:
+        S.close()
+    return dict(theta=out["theta"], beta=[out["beta"][..., s] for s in range(n_samples)],
+                threshold=[out["threshold"][..., s] for s in range(n_samples)], ll=out["ll"], f=None, fstar=None)

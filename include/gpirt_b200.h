@@ -121,7 +121,8 @@ int gpirt_get_L(gpirt_sampler* h, double* L /* n x n, upper triangle zero */);
  * gpirt_store_flush synchronises once, reports any error raised by the sweeps since the last synchronisation, and writes the
  * `count` buffered samples as samples first .. first+count-1 of the reference's output arrays (theta: cube n_samples x n x 1;
  * per sample: beta 3 x m, thresholds m x (C+1), f n x m, fstar NGRID x m; ll: n_samples), then empties the store.
- * NULL outputs are skipped. world == 1 only. */
+ * NULL outputs are skipped. On an item shard (world > 1) theta, beta, thresholds and ll can be stored — they are complete on every
+ * rank after the sweep's exchanges — f and f* cannot (each rank holds its own items). */
 int gpirt_store_open(gpirt_sampler* h, int capacity, int store_f, int store_fstar);
 int gpirt_store_push(gpirt_sampler* h);
 int gpirt_store_count(gpirt_sampler* h, int* count, int* capacity);

@@ -40,6 +40,15 @@ if rank == 0:
     ok = all(np.array_equal(sh[k], one[k]) for k in ("theta", "beta", "thresholds")) and sh["ll"] == one["ll"]
     ok = ok and np.array_equal(f.cpu().numpy().T, one["f"])
     print("WORLD2_EQUALS_WORLD1", ok, sh["ll"], one["ll"])
+# the sharded mirror of gpirtMCMC (partial y uploads, device-side draw store) against the single-GPU entry point
+from gpirt_b200.distributed import gpirtMCMC_sharded
+kw = dict(beta_prior_sds=P["beta_prior_sds"], theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=123, beta_init=P["beta0"])
+a = gpirtMCMC_sharded(P["y"], 5, 1, THIN=2, rank=rank, world=world, device=local, **kw)
+if rank == 0:
+    b = gpirt_b200.gpirtMCMC(P["y"], 5, 1, THIN=2, CHAIN=1, device=local, **kw)[0]
+    ok = np.array_equal(a["theta"], b["theta"]) and np.array_equal(a["ll"], b["ll"]) and len(a["beta"]) == len(b["beta"]) == 2
+    ok = ok and all(np.array_equal(x, y) for x, y in zip(a["beta"] + a["threshold"], b["beta"] + b["threshold"]))
+    print("SHARDED_MCMC_EQUALS_SINGLE", ok, a["ll"], b["ll"])
 dist.barrier(); dist.destroy_process_group()
 '''
 
@@ -60,3 +69,4 @@ def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path):
                         "--master-port", str(port), str(script)], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "WORLD2_EQUALS_WORLD1 True" in r.stdout, r.stdout[-2000:]
+    assert "SHARDED_MCMC_EQUALS_SINGLE True" in r.stdout, r.stdout[-2000:]
