@@ -25,7 +25,7 @@ def _as_cube(data):
 def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_codes=None, beta_prior_means=None,
               beta_prior_sds=None, theta_prior_means=None, theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern",
               theta_init=None, thresholds=None, SEED=1, constant_IRF=0, store_f=False, store_fstar=False, beta_init=None,
-              f_init=None, device=0, progress=None):
+              f_init=None, device=0, progress=None, f_init_z=None):
     """Drop-in for gpirtMCMC() (R/gpirtMCMC.R:98-167). `vote_codes` must stay None: the reference's recoding
     path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing."""
     if vote_codes is not None:
@@ -65,7 +65,7 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
                    f=np.zeros((n, m, H, n_samples), order="F") if store_f else None,
                    fstar=np.zeros((NGRID, m, H, n_samples), order="F") if store_fstar else None)
         a = McmcArgs()
-        b0, f0 = _F(beta_init), _F(f_init)
+        b0, f0, z0 = _F(beta_init), _F(f_init), _F(f_init_z)
         a.y, a.n, a.m, a.horizon = y.ctypes.data, n, m, H
         a.theta = th0.ctypes.data
         a.sample_iterations, a.burn_iterations, a.THIN = int(sample_iterations), int(burn_iterations), int(THIN)
@@ -76,6 +76,7 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         a.constant_IRF, a.store_f, a.store_fstar = int(constant_IRF), int(store_f), int(store_fstar)
         a.beta_init = b0.ctypes.data if b0 is not None else None
         a.f_init = f0.ctypes.data if f0 is not None else None
+        a.f_init_z = z0.ctypes.data if z0 is not None else None  # f0_j = L z_j on the device (rmvnorm(L), src/mvnormal.h:7-14)
         a.seed, a.chain, a.device = int(SEED), chain, int(device)
         a.theta_draws, a.beta_draws = out["theta"].ctypes.data, out["beta"].ctypes.data
         a.threshold_draws, a.ll_draws = out["threshold"].ctypes.data, out["ll"].ctypes.data

@@ -1008,6 +1008,16 @@ extern "C" {
 
 // Initial values the reference draws with R's RNG inside gpirtMCMC (src/gpirtMCMC.cpp:149-163):
 // beta0 ~ N(prior mean, prior sd) per coefficient, f0_j = L z_j. Here from the Philox INIT streams.
+// f_j = L z_j for the local items, z in zbuf (rmvnorm(L), src/mvnormal.h:7-14)
+static int f_from_zbuf(gpirt_sampler* h) {
+    GemmArgs g{};
+    g.M = h->n; g.N = h->m_local; g.K = h->n;
+    g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->f; g.ldc = h->ldn;
+    g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
+    CU(gemm_f64(h->stream, false, false, g));
+    return GPIRT_OK;
+}
+
 int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_beta, int draw_f) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
@@ -1028,12 +1038,22 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
         if (!h->chol_valid) TRY(do_update_cholesky(h));
         TRY(wait_L(h));
         CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_INIT_F, h->item0));
-        GemmArgs g{};
-        g.M = h->n; g.N = h->m_local; g.K = h->n;
-        g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->f; g.ldc = h->ldn;
-        g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
-        CU(gemm_f64(st, false, false, g));
+        TRY(f_from_zbuf(h));
     }
+    return GPIRT_OK;
+}
+
+int gpirt_init_f_from_z(gpirt_sampler* h, const double* z) {
+    CHECK_H(h);
+    if (!z) return fail(GPIRT_ERR_INVALID, "init_f_from_z: NULL z");
+    CU(cudaSetDevice(h->cfg.device));
+    if (h->m_local <= 0) return GPIRT_OK;
+    if (!h->chol_valid) TRY(do_update_cholesky(h));
+    TRY(wait_L(h));
+    CU(cudaMemcpy2DAsync(h->zbuf, (size_t)h->ldz * 8, z + (size_t)h->item0 * h->n, (size_t)h->n * 8, (size_t)h->n * 8, h->m_local,
+                         cudaMemcpyHostToDevice, h->stream));
+    TRY(f_from_zbuf(h));
+    CU(cudaStreamSynchronize(h->stream));  // z is the caller's memory
     return GPIRT_OK;
 }
 

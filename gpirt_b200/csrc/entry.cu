@@ -45,7 +45,8 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     TRYC(gpirt_set_priors(h, a->beta_prior_sds, a->theta_prior_sds));
     TRYC(gpirt_set_state(h, a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
     TRYC(gpirt_set_iter(h, 0xFFFFFFFFu));  // initial draws use a sweep id no sweep reaches
-    TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr));
+    TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
+    if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h, a->f_init_z));
     TRYC(gpirt_set_iter(h, 0));
 
     const int total = a->sample_iterations + a->burn_iterations;

@@ -221,6 +221,13 @@ class Sampler:
         b = _F(beta_prior_means)
         check(self._L.gpirt_init_draw(self._h, _p(b), int(draw_beta), int(draw_f)))
 
+    def init_f_from_z(self, z):
+        """f_j = L z_j for every local item (rmvnorm(L), src/mvnormal.h:7-14; the reference's initial f, src/gpirtMCMC.cpp:158-162)."""
+        zz = _F(z)
+        if zz.shape != (self.n, self.m):
+            raise GpirtError(_lib.ERR_SHAPE, f"z has shape {zz.shape}, expected {(self.n, self.m)}")
+        check(self._L.gpirt_init_f_from_z(self._h, _p(zz)))
+
     # ---- subsystems (reference names) ----
     def update_cholesky_cache(self):
         check(self._L.gpirt_update_cholesky_cache(self._h))

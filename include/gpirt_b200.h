@@ -131,6 +131,8 @@ int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_
 int gpirt_store_close(gpirt_sampler* h);
 /* bytes of device memory one stored sample takes (to size `capacity`) */
 int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar);
+/* f_j = L z_j for every local item from host normals z (n x m_total): the reference's initial f (src/gpirtMCMC.cpp:158-162) */
+int gpirt_init_f_from_z(gpirt_sampler* h, const double* z);
 int gpirt_set_iter(gpirt_sampler* h, uint32_t iter);         /* sweep counter used to key the Philox streams */
 /* How draw_fstar applies L^-1 / L^-T to k* (solve(trimatl(L), kstar) and double_solve, src/draw-fstar.cpp:30,51, src/cholesky-cache.cpp:4-9):
  * 0 = blocked forward/back substitution (backward stable, n/64 dependent steps); 1 = explicit L^-1 by parallel block inversion, then
@@ -213,6 +215,10 @@ typedef struct {
     /* progress / interrupt poll, called once per sweep on the calling thread (Rprintf + checkUserInterrupt,
      * src/gpirtMCMC.cpp:262-264); return non-zero to stop. May be NULL. */
     int (*progress)(int iter, int total, void* user); void* user;
+    /* n x m N(0,1) draws or NULL: f0_j = L z_j is formed on the device (rmvnorm(L), src/mvnormal.h:7-14, src/gpirtMCMC.cpp:158-162), so
+     * an R shim that draws z with R::rnorm starts from the reference's own initial state without factorising K on the host.
+     * Ignored when f_init is given. */
+    const double* f_init_z;
 } gpirt_mcmc_args;
 int gpirt_mcmc(const gpirt_mcmc_args* a);
 

@@ -554,6 +554,7 @@ inline void interp1(const vec& X, const subview_col<double>& Y, const vec& XI, v
 
 // ---- Rmath ------------------------------------------------------------------------------------------
 extern "C" double refshim_next_normal(void);  // defined in ref_capi.cpp: the caller-supplied N(0,1) stream
+extern "C" double refshim_next_unif(void);    // defined by whoever uses R::unif_rand (tests/rshim/driver.cpp)
 namespace R {
 // pnorm(x, mu, sigma, lower_tail, log_p): Cody (1969) as in nmath/pnorm.c (pnorm_both); only the
 // lower_tail = 1, log_p = 0 combination the reference uses is restated.
@@ -626,6 +627,7 @@ inline double rnorm(double mu, double sigma) {
     if (sigma == 0. || !std::isfinite(mu)) return mu;
     return mu + sigma * refshim_next_normal();
 }
+inline double unif_rand() { return refshim_next_unif(); }
 }  // namespace R
 
 // ---- Rcpp -------------------------------------------------------------------------------------------
@@ -664,6 +666,7 @@ struct List : RObject {
     }
 };
 inline void checkUserInterrupt() {}
+inline void stop(const std::string& msg) { throw std::runtime_error(msg); }  // Rcpp::stop -> R error through END_RCPP
 struct NullStream { template <class T> NullStream& operator<<(const T&) { return *this; } };
 static NullStream Rcout, Rcerr;
 struct NumericVector {};

@@ -88,3 +88,17 @@ def test_store_index_arithmetic_of_the_mcmc_wrapper():
         n_samples = int(sample / thin)
         idx = [(it - burn) // thin for it in range(sample + burn) if it >= burn and it % thin == 0]
         assert idx == list(range(n_samples))
+
+
+def test_r_shim_builds_against_stand_in_rcpp_and_links_the_c_abi():
+    """integration/r-package/src/*.cpp (the bodies a maintainer swaps into the R package) compile against the stand-in headers and resolve
+    gpirt_mcmc / gpirt_recover_fstar from libgpirt_b200.so; running them needs a GPU (tests/test_gpu_entry.py)."""
+    import ctypes as C
+    import os
+    import subprocess
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    subprocess.run(["make", "-C", os.path.join(root, "tests", "rshim")], check=True, capture_output=True)
+    L = C.CDLL(os.path.join(root, "tests", "rshim", "_build", "librshim_test.so"))
+    for sym in ("shim_gpirtMCMC", "shim_recover_fstar", "shim_last_error", "shim_normals_used"):
+        getattr(L, sym)

@@ -130,3 +130,88 @@ def test_recover_fstar_equals_draw_f_then_draw_fstar():
     S.draw_f()
     S.draw_fstar()
     assert np.array_equal(got, S.get_state(fstar=True)["fstar"])
+
+
+# ---- the R-package shim (integration/r-package/src) driven without R, tests/rshim ------------------------------------
+def _rshim():
+    import ctypes as C
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "rshim", "_build", "librshim_test.so")
+    if not os.path.exists(path):
+        pytest.skip("tests/rshim/_build/librshim_test.so not built (make -C tests/rshim, or __graft_entry__.build())")
+    L = C.CDLL(path)
+    L.shim_last_error.restype = C.c_char_p
+    L.shim_normals_used.restype = C.c_uint64
+    return L
+
+
+def test_r_shim_gpirtMCMC_returns_what_the_c_abi_returns():
+    """gpirtMCMC() of the R shim (stand-in Rcpp/Armadillo types, R's RNG = a supplied stream) against gpirt_b200.gpirtMCMC with the initial
+    values the shim must have drawn: beta0 = mean + sd z in (item, coefficient) order, then n normals per item for f0 = L z."""
+    import ctypes as C
+
+    import gpirt_b200 as g
+
+    L = _rshim()
+    n, m, Ccat, sample, burn, thin = 80, 12, 4, 6, 2, 2
+    P = make_problem(n, m, Ccat, seed=41)
+    rng = np.random.default_rng(8)
+    z = rng.standard_normal(3 * m + n * m + 5)
+    unif = 0.3712
+    bpm = np.asfortranarray(rng.standard_normal((3, m)) * 0.1)
+    bps, tps = P["beta_prior_sds"], P["theta_prior_sds"]
+    tpm = np.zeros((2, n), order="F")
+    ns = sample // thin
+    out = dict(theta=np.zeros((ns, n, 1), order="F"), beta=np.zeros((3, m, 1, ns), order="F"), thr=np.zeros((m, Ccat + 1, 1, ns), order="F"),
+               ll=np.zeros(ns), f=np.zeros((n, m, 1, ns), order="F"), fstar=np.zeros((g.NGRID, m, 1, ns), order="F"))
+    y = np.asfortranarray(P["y"])
+    th0 = np.ascontiguousarray(P["theta0"] * 1.6)  # beyond +-5 somewhere: the clamp of src/gpirtMCMC.cpp:133 happens behind the ABI
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    u64 = C.c_uint64
+    rc = L.shim_gpirtMCMC(u64(n), u64(m), u64(1), u64(Ccat), p(y), p(th0), sample, burn, thin, p(bpm), p(bps), p(tpm), p(tps), C.c_double(1.0),
+                          C.c_double(10.0), b"Matern", p(P["thr0"]), 0, p(z), u64(z.size), C.c_double(unif), p(out["theta"]), p(out["beta"]),
+                          p(out["thr"]), p(out["ll"]), p(out["f"]), p(out["fstar"]))
+    assert rc == 0, L.shim_last_error().decode()
+    assert L.shim_normals_used() == 3 * m + n * m  # src/gpirtMCMC.cpp:149-163: 3 per item, then n per item
+    beta0 = np.asfortranarray(bpm + bps * z[:3 * m].reshape(m, 3).T)
+    z0 = np.asfortranarray(z[3 * m:3 * m + n * m].reshape(m, n).T)
+    ref = g.gpirtMCMC(y, sample, burn, THIN=thin, CHAIN=1, beta_prior_means=bpm, beta_prior_sds=bps, theta_prior_sds=tps, theta_init=th0,
+                      thresholds=P["thr0"], SEED=int(unif * 4294967296.0), beta_init=beta0, f_init_z=z0, store_f=True, store_fstar=True)[0]
+    assert np.array_equal(out["theta"], ref["theta"]) and np.array_equal(out["ll"], ref["ll"])
+    for s in range(ns):
+        assert np.array_equal(out["beta"][..., s], ref["beta"][s]) and np.array_equal(out["thr"][..., s], ref["threshold"][s])
+        assert np.array_equal(out["f"][..., s], ref["f"][s]) and np.array_equal(out["fstar"][..., s], ref["fstar"][s])
+    # and f_init_z is what it says: the first sweep starts from f0 = L z
+    S = g.Sampler(n, m, Ccat, seed=1)
+    S.set_priors(bps, tps)
+    S.set_state(theta=th0)
+    Lk = g.chol(g.K(np.clip(th0, -5, 5), np.clip(th0, -5, 5), bps[:, 0]) + 1e-6 * np.eye(n))
+    S.init_f_from_z(z0)
+    f0 = S.get_state(theta=False, beta=False, thresholds=False)["f"]
+    assert np.max(np.abs(f0 - Lk @ z0)) <= 1e-9 * np.max(np.abs(f0))
+
+
+def test_r_shim_recover_fstar_and_error_path():
+    import ctypes as C
+
+    import gpirt_b200 as g
+
+    L = _rshim()
+    n, m, Ccat = 70, 9, 3
+    P = make_problem(n, m, Ccat, seed=2)
+    rng = np.random.default_rng(1)
+    f = np.asfortranarray(rng.standard_normal((n, m)))
+    beta2 = np.asfortranarray(rng.standard_normal((2, m)))
+    bpm, bps = np.zeros((2, m), order="F"), np.full((2, m), 0.5, order="F")
+    y = np.asfortranarray(P["y"])
+    th = np.ascontiguousarray(P["theta0"])
+    out = np.zeros((g.NGRID, m), order="F")
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    u64 = C.c_uint64
+    rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(Ccat), p(f), p(y), p(th), p(beta2), p(P["thr0"]), p(bpm), p(bps), 0, p(out))
+    assert rc == 0, L.shim_last_error().decode()
+    assert np.array_equal(out, g.recover_fstar(321, f, y, th, beta2, P["thr0"], beta_prior_sds=bps)["fstar"][:, :, 0])
+    # a library error becomes Rcpp::stop(message) -> an R error; here a C++ exception carrying gpirt_last_error()
+    rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(Ccat), p(f), p(y), p(th), p(beta2), p(P["thr0"]), p(bpm), p(bps), 1, p(out))
+    assert rc == 1 and b"constant_IRF" in L.shim_last_error()
