@@ -25,7 +25,8 @@ def build(force=False):
 
 class Src(C.Structure):
     _fields_ = [("mode", C.c_int32), ("z", C.c_void_p), ("zstride", C.c_uint64), ("u", C.c_void_p),
-                ("ustride", C.c_uint64), ("seed", C.c_uint64), ("chain", C.c_uint32), ("iter", C.c_uint32)]
+                ("ustride", C.c_uint64), ("seed", C.c_uint64), ("chain", C.c_uint32), ("iter", C.c_uint32),
+                ("session", C.c_uint32), ("pad_", C.c_uint32)]
 
 
 _lib = None
@@ -185,9 +186,9 @@ def supplied(z=None, u=None):
     return s
 
 
-def philox(seed, chain, it):
+def philox(seed, chain, it, session=0):
     s = Src()
-    s.mode, s.seed, s.chain, s.iter = 1, seed, chain, it
+    s.mode, s.seed, s.chain, s.iter, s.session = 1, seed, chain, it, session
     return s
 
 
@@ -330,3 +331,94 @@ class Sampler:
         ll = np.empty(iters) if store else None
         info = lib().orc_run_mt(self._h, C.c_int(iter0), C.c_int(iters), _p(th), _p(ll))
         return info, th, ll
+
+
+class Panel:
+    """CPU oracle at horizon > 1, constant_IRF 0: H single-session Samplers (sessions are independent given theta) plus the
+    reference's joint theta step (src/draw-theta.cpp:171-236): RDM (theta_ls <= 0.1) or GP over time (0.1 < theta_ls < 3H).
+    The CST regime (theta_ls >= 3H) is an out-of-bounds read of the thresholds in the reference at H > 1 and is refused.
+    Arrays follow the reference's cubes: y n x m x H, theta n x H, beta 3 x m x H, f n x m x H, thr m x (C+1) x H, fstar NGRID x m x H."""
+
+    def __init__(self, y, C_, beta_prior_sds, theta_prior_sds=None, theta_os=1.0, theta_ls=10.0, KERNEL="Matern"):
+        y = np.asfortranarray(np.asarray(y, dtype=np.float64))
+        self.n, self.m, self.H = y.shape
+        self.C = int(C_)
+        H = self.H
+        if theta_ls >= 3 * H:
+            raise ValueError("CST regime at horizon > 1: the reference reads thresholds out of bounds (src/draw-theta.cpp:162)")
+        self.regime = 1 if theta_ls <= 0.1 else 2
+        self.S = [Sampler(y[:, :, h], C_, beta_prior_sds, theta_prior_sds) for h in range(H)]
+        for h in range(1, H):
+            lib().orc_share_mts(self.S[h]._h, self.S[0]._h)
+        ts = np.arange(float(H))  # linspace(0, H-1, H), src/cholesky-cache.cpp:28
+        V = K_time(ts, ts, theta_os, theta_ls, [0.0, 0.0], KERNEL) + 1e-6 * np.eye(H)  # :29-32 (theta_prior_sds is NOT used there)
+        self.L_time, info = chol(V)
+        assert info == 0
+        self.L_time = _F(self.L_time)
+
+    def set_state(self, theta=None, beta=None, f=None, thr=None, fstar=None):
+        for h, S in enumerate(self.S):
+            S.set_state(theta=None if theta is None else np.asarray(theta)[:, h], beta=None if beta is None else np.asarray(beta)[:, :, h],
+                        f=None if f is None else np.asarray(f)[:, :, h], thr=None if thr is None else np.asarray(thr)[:, :, h],
+                        fstar=None if fstar is None else np.asarray(fstar)[:, :, h])
+
+    def state(self):
+        st = [S.state() for S in self.S]
+        return dict(theta=np.stack([s["theta"] for s in st], axis=1), beta=np.stack([s["beta"] for s in st], axis=2),
+                    f=np.stack([s["f"] for s in st], axis=2), thr=np.stack([s["thr"] for s in st], axis=2),
+                    fstar=np.stack([s["fstar"] for s in st], axis=2))
+
+    def mt_seed_all(self, base):
+        self.S[0].mt_seed_all(base)  # the one pool every session consumes
+
+    def record(self, on=True):
+        for S in self.S:
+            S.record(on)
+
+    def compute_mu(self):
+        for S in self.S:
+            S.compute_mu()
+
+    def update_cholesky(self):
+        return max(S.update_cholesky() for S in self.S)
+
+    def draw_theta(self, srcs):
+        """srcs: one Src per session (RDM) or a single Src (GP; H normals per respondent)"""
+        srcs = list(srcs) if isinstance(srcs, (list, tuple)) else [srcs]
+        arr = (Src * len(srcs))()
+        for k, s in enumerate(srcs):
+            for fld, _ in Src._fields_:
+                setattr(arr[k], fld, getattr(s, fld))
+        hs = (C.c_void_p * self.H)(*[S._h for S in self.S])
+        lib().orc_panel_draw_theta(hs, C.c_uint64(self.H), C.c_int(self.regime), _p(self.L_time), arr)
+        self._keep = srcs
+
+    def sweep(self, src_of):
+        """One sweep in the reference's order (src/gpirtMCMC.cpp:267-331). src_of(block, h) -> Src for session h (h is None for the GP theta step)."""
+        for S in self.S:  # draw_f calls update_cholesky_cache itself (src/draw-f.cpp:59)
+            S.compute_mu()
+            if S.update_cholesky() != 0:
+                return 1
+        for h, S in enumerate(self.S):
+            S.draw_f(src_of("f", h))
+        for h, S in enumerate(self.S):
+            if S.draw_fstar(src_of("fstar", h)) != 0:
+                return 2
+        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime == 1 else src_of("theta", None))
+        for S in self.S:
+            S.gather_f()
+        for h, S in enumerate(self.S):
+            S.draw_beta(src_of("beta", h))
+        for S in self.S:
+            S.compute_mu()
+            if S.update_cholesky() != 0:
+                return 1
+        for h, S in enumerate(self.S):
+            S.draw_threshold(src_of("thr", h))
+        return 0
+
+    def total_ll(self):
+        ll = 0.0
+        for S in self.S:  # src/gpirtMCMC.cpp:324-331: one running sum over (h, j); per session here, then across sessions in order
+            ll += S.total_ll()
+        return ll

@@ -16,6 +16,7 @@ struct orc_src {
     const double* z; uint64_t zstride;
     const double* u; uint64_t ustride;
     uint64_t seed; uint32_t chain, iter;
+    uint32_t session, pad_;
 };
 
 static Src to_src(Sampler* S, const orc_src* c, int block) {
@@ -24,7 +25,8 @@ static Src to_src(Sampler* S, const orc_src* c, int block) {
     Src s;
     s.mode = c->mode; s.z = c->z; s.zstride = c->zstride; s.u = c->u; s.ustride = c->ustride;
     s.seed = c->seed; s.chain = c->chain; s.iter = c->iter; s.zs = zs[block]; s.us = us[block];
-    s.mts = &S->mts;
+    s.session = c->session;
+    s.mts = S->mts_shared ? S->mts_shared : &S->mts;
     if (S->record) {
         const size_t units = block == B_THETA ? S->n : S->m;
         S->rec_z[block].assign(units, {});
@@ -145,6 +147,16 @@ int orc_num_threads(void* h) { return int(static_cast<Sampler*>(h)->mts.size());
 
 void orc_draw_f(void* h, const orc_src* c, const double* nu) { Sampler* S = static_cast<Sampler*>(h); S->draw_f(to_src(S, c, B_F), nu); }
 int orc_draw_fstar(void* h, const orc_src* c) { Sampler* S = static_cast<Sampler*>(h); return S->draw_fstar(to_src(S, c, B_FSTAR)); }
+// horizon > 1: session `dst` consumes the ThreadRNGs of `src` (one ws_pool for all sessions, src/gpirtMCMC.cpp:90)
+void orc_share_mts(void* dst, void* src) { static_cast<Sampler*>(dst)->mts_shared = &static_cast<Sampler*>(src)->mts; }
+void orc_panel_draw_theta(void** hs, uint64_t H, int regime, const double* L_time, const orc_src* cs) {
+    std::vector<Sampler*> S(H);
+    std::vector<Src> srcs;
+    for (uint64_t h = 0; h < H; ++h) S[h] = static_cast<Sampler*>(hs[h]);
+    if (regime == 1) for (uint64_t h = 0; h < H; ++h) srcs.push_back(to_src(S[h], &cs[h], B_THETA));
+    else srcs.push_back(to_src(S[0], &cs[0], B_THETA));
+    panel_draw_theta(S.data(), H, regime, L_time, srcs.data());
+}
 void orc_draw_theta(void* h, const orc_src* c) { Sampler* S = static_cast<Sampler*>(h); S->draw_theta(to_src(S, c, B_THETA)); }
 void orc_gather_f(void* h) { static_cast<Sampler*>(h)->gather_f(); }
 void orc_draw_beta(void* h, const orc_src* c) { Sampler* S = static_cast<Sampler*>(h); S->draw_beta(to_src(S, c, B_BETA)); }

@@ -34,7 +34,7 @@ static inline bool with_rng_raw(const Src& s, size_t unit, size_t nz, F&& body) 
         body(r);
         return r.overrun;
     } else if (s.mode == 1) {
-        PhiloxRng r(s.seed, s.chain, s.iter, s.zs, s.us, uint32_t(unit));
+        PhiloxRng r(s.seed, s.chain, s.iter, s.zs | (s.session << 8), s.us | (s.session << 8), uint32_t(unit));
         body(r);
         return false;
     } else {
@@ -198,14 +198,15 @@ int Sampler::draw_fstar(const Src& s) {
 }
 
 // compute_ll_sparse (src/draw-theta.cpp:4-24) for respondent i at a raw theta value
-static inline double theta_ll(const Sampler& S, size_t i, double theta, const double* fst, const double* must) {
+static inline double theta_ll(const Sampler& S, size_t i, double theta, const double* fst, const double* must, const double* thr = nullptr) {
     const size_t N = NGRID;
+    if (!thr) thr = S.thr.data();
     int idx = grid_index(theta);
     double result = 0.0;
     for (uint64_t j : S.obs_items[i]) {
         int c = static_cast<int>(S.y[i + j * S.n]);
         double g = fst[idx + j * N] + must[idx + j * N];
-        result += cell_ll(g, c, &S.thr[j], S.m);
+        result += cell_ll(g, c, &thr[j], S.m);
     }
     return result;
 }
@@ -250,6 +251,76 @@ void Sampler::draw_theta(const Src& s) {
     }
     diag[B_THETA].overrun = over;
     theta.swap(theta_new);
+}
+
+void panel_draw_theta(Sampler* const* S, size_t H, int regime, const double* L_time, const Src* srcs) {
+    const size_t n = S[0]->n;
+    std::vector<std::vector<double>> theta_new(H, std::vector<double>(n));
+    if (regime == 1) {
+        for (size_t h = 0; h < H; ++h) S[h]->diag[B_THETA].reset(n);
+        std::vector<char> over(H, 0);
+#pragma omp parallel for schedule(dynamic)
+        for (size_t i = 0; i < n; ++i) {
+            for (size_t h = 0; h < H; ++h) {  // src/draw-theta.cpp:182-202
+                Sampler& Sh = *S[h];
+                // QUIRK kept: the RDM branch hands the whole thresholds cube to the 1-session ESS (src/draw-theta.cpp:196-198), which reads
+                // thresholds.slice(0) (:44-47) — every session's theta is scored against SESSION 0's thresholds.
+                const double* thr0 = S[0]->thr.data();
+                const double Li = std::sqrt(1.0 + std::pow(Sh.theta_prior_sds[0 + 2 * i], 2));  // :194
+                double raw = 0.0;
+                Diag& d = Sh.diag[B_THETA];
+                bool o = with_rng(srcs[h], i, 1, [&](UnitRng& rng) {
+                    double nu = Li * rng.norm();
+                    double u = rng.unif();
+                    double log_y = std::log(u);
+                    log_y += theta_ll(Sh, i, Sh.theta[i], Sh.fstar.data(), Sh.mu_star.data(), thr0);
+                    d.evals[i] = 1;
+                    ess_loop(rng, log_y, [&](double ce, double se) {
+                        raw = Sh.theta[i] * ce + nu * se;
+                        raw = std::max(-5.0, std::min(5.0, raw));
+                        double lp = 0.0;
+                        lp += theta_ll(Sh, i, raw, Sh.fstar.data(), Sh.mu_star.data(), thr0);
+                        return lp;
+                    }, d.evals[i], d.margin[i]);
+                });
+                if (o) {
+#pragma omp critical
+                    over[h] = 1;
+                }
+                theta_new[h][i] = grid_value(grid_index(raw));  // :199-201
+            }
+        }
+        for (size_t h = 0; h < H; ++h) S[h]->diag[B_THETA].overrun = over[h] != 0;
+    } else {
+        Diag& d = S[0]->diag[B_THETA];
+        d.reset(n);
+        bool over = false;
+#pragma omp parallel for schedule(dynamic) reduction(|| : over)
+        for (size_t i = 0; i < n; ++i) {
+            std::vector<double> z(H), nu(H), raw(H, 0.0);
+            bool o = with_rng(srcs[0], i, H, [&](UnitRng& rng) {
+                for (size_t h = 0; h < H; ++h) z[h] = rng.norm();
+                gemv(L_time, H, H, z.data(), nu.data());  // rmvnorm_threadsafe(L, rng): dense L * z, src/mvnormal.h:17-24
+                double u = rng.unif();
+                double log_y = std::log(u);
+                for (size_t h = 0; h < H; ++h) log_y += theta_ll(*S[h], i, S[h]->theta[i], S[h]->fstar.data(), S[h]->mu_star.data());  // :43-47
+                d.evals[i] = 1;
+                ess_loop(rng, log_y, [&](double ce, double se) {
+                    for (size_t h = 0; h < H; ++h) {
+                        raw[h] = S[h]->theta[i] * ce + nu[h] * se;
+                        raw[h] = std::max(-5.0, std::min(5.0, raw[h]));  // :58-62
+                    }
+                    double lp = 0.0;
+                    for (size_t h = 0; h < H; ++h) lp += theta_ll(*S[h], i, raw[h], S[h]->fstar.data(), S[h]->mu_star.data());
+                    return lp;
+                }, d.evals[i], d.margin[i]);
+            });
+            over = over || o;
+            for (size_t h = 0; h < H; ++h) theta_new[h][i] = grid_value(grid_index(raw[h]));  // :229-233
+        }
+        d.overrun = over;
+    }
+    for (size_t h = 0; h < H; ++h) S[h]->theta.swap(theta_new[h]);
 }
 
 void Sampler::gather_f() {  // src/gpirtMCMC.cpp:291-298

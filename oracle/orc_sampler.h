@@ -9,7 +9,10 @@
 //   draw_beta                 src/draw-beta.cpp:51-101
 //   draw_threshold            src/draw_threshold.cpp:206-228
 //   sweep order / total ll    src/gpirtMCMC.cpp:261-331
-// Scope: horizon == 1, constant_IRF == 0 (every BASELINE.json config). Parity of this file itself
+// Scope: constant_IRF == 0. horizon == 1 (every BASELINE.json config) is one Sampler; horizon > 1 is a panel of H Samplers (sessions are
+// independent given theta: src/draw-f.cpp:62, src/draw-fstar.cpp:20, src/draw-beta.cpp:60, src/draw_threshold.cpp:206) plus
+// panel_draw_theta below for the RDM and GP-over-time regimes; the CST regime at horizon > 1 indexes thresholds out of bounds in the
+// reference (src/draw-theta.cpp:162 passes the m-row cube for m*H stacked items) and is not restated. Parity of this file itself
 // is pinned against the reference's own translation units compiled under oracle/_ref (see
 // oracle/Makefile and tests/test_oracle_vs_ref.py).
 #pragma once
@@ -41,6 +44,7 @@ struct Src {
     const double* u = nullptr; size_t ustride = 0;
     // philox
     uint64_t seed = 0; uint32_t chain = 0, iter = 0, zs = 0, us = 0;
+    uint32_t session = 0;  // horizon > 1: folded into the stream id (stream | session << 8), as gpirt_b200/csrc/rng.cuh does
     // mt: one generator per worker thread
     std::vector<MtRng>* mts = nullptr;
     // when set, every unit's draws are appended to (*rec_z)[unit] / (*rec_u)[unit]
@@ -74,6 +78,7 @@ struct Sampler {
     // scratch
     std::vector<double> f_new, mu, mu_star, Lpost, W;
     std::vector<MtRng> mts;
+    std::vector<MtRng>* mts_shared = nullptr;  // horizon > 1: the sessions of a panel consume ONE set of ThreadRNGs, as the reference's ws_pool
     Diag diag[N_BLOCKS];
     bool record = false;  // keep the draws of the last call of each block (per unit)
     std::vector<std::vector<double>> rec_z[N_BLOCKS], rec_u[N_BLOCKS];
@@ -90,5 +95,12 @@ struct Sampler {
     double total_ll();
     int sweep(const Src srcs[N_BLOCKS]);
 };
+
+// draw_theta at horizon > 1 (src/draw-theta.cpp:171-236) over the H single-session samplers of a panel.
+//   regime 1 (RDM, ls <= 0.1):           every (respondent, session) is its own 1-dim ESS, L_i = sqrt(1 + sd0_i^2); loop order i, then h (:178-203);
+//                                        srcs[h] feeds session h (unit = respondent)
+//   regime 2 (GP over time, 0.1<ls<3H):  one H-dim ESS per respondent with nu = L_time z (:206-235); srcs[0] feeds it (H normals per unit)
+// Diagnostics / recordings land in each session's diag[B_THETA] (RDM) or in session 0's (GP).
+void panel_draw_theta(Sampler* const* S, size_t H, int regime, const double* L_time, const Src* srcs);
 
 }  // namespace orc

@@ -221,8 +221,10 @@ public:
     }
     T& at(uword i, uword j) { return mem[i + size_t(j) * n_rows]; }
     const T& at(uword i, uword j) const { return mem[i + size_t(j) * n_rows]; }
-    T& operator()(uword i, uword j) { return at(i, j); }
-    const T& operator()(uword i, uword j) const { return at(i, j); }
+    // Armadillo checks bounds in operator() unless ARMA_NO_DEBUG is defined (RcppArmadillo does not define it); .at() is unchecked
+    void check_bounds(uword i, uword j) const { if (i >= n_rows || j >= n_cols) throw std::logic_error("Mat::operator(): index out of bounds"); }
+    T& operator()(uword i, uword j) { check_bounds(i, j); return at(i, j); }
+    const T& operator()(uword i, uword j) const { check_bounds(i, j); return at(i, j); }
     T& operator()(uword i) { return mem[i]; }
     const T& operator()(uword i) const { return mem[i]; }
     T& operator[](uword i) { return mem[i]; }

@@ -132,3 +132,75 @@ def test_recover_fstar():
     O.draw_f(orc.mt())
     assert O.draw_fstar(orc.mt()) == 0
     assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-6
+
+
+@pytest.mark.parametrize("regime,ls,kernel", [("RDM", 0.05, "Matern"), ("GP", 2.0, "Matern"), ("GP", 4.0, "RBF")])
+def test_gpirtMCMC_horizon_3_same_draws(regime, ls, kernel):
+    """horizon > 1 (dynamic GPIRT): the oracle's panel of single-session samplers + joint theta step against the reference's own
+    gpirtMCMC run, one thread: theta / beta / thresholds bit for bit in the RDM (src/draw-theta.cpp:171-205) and GP-over-time
+    (:206-235) regimes."""
+    n, m, C, H, iters = 40, 7, 4, 3, 4
+    rng = np.random.default_rng(5)
+    Ps = [make_problem(n, m, C, seed=20 + h, missing=0.15) for h in range(H)]
+    y = np.stack([P["y"] for P in Ps], axis=2)
+    theta_in = np.stack([P["theta0"] for P in Ps], axis=1)
+    thr0 = np.stack([Ps[0]["thr0"]] * H, axis=2)
+    z = rng.standard_normal(H * (3 * m + n * m))
+    bpm, bps, tpm = np.zeros((3, m)), Ps[0]["beta_prior_sds"], np.zeros((2, n))
+    tps = np.asfortranarray(np.vstack([np.full((1, n), 0.4), np.zeros((1, n))]))
+    os_ = 1.3
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, os_, ls, kernel, thr0, 0, z, store_f=True, store_fstar=True)
+    # initial state as the reference draws it (src/gpirtMCMC.cpp:149-163): beta for every (h, j, p) first, then f = L_h z per (h, j)
+    theta0 = np.clip(theta_in, -5, 5)
+    beta0 = np.stack([bpm + bps * z[h * 3 * m:(h + 1) * 3 * m].reshape(m, 3).T for h in range(H)], axis=2)
+    zf = z[H * 3 * m:]
+    L0 = ref.update_cholesky_cache(theta0, bps)[0]
+    f0 = np.stack([np.stack([L0[:, :, h] @ zf[(h * m + j) * n:(h * m + j + 1) * n] for j in range(m)], axis=1) for h in range(H)], axis=2)
+    O = orc.Panel(y, C, bps, tps, theta_os=os_, theta_ls=ls, KERNEL=kernel)
+    assert O.regime == (1 if regime == "RDM" else 2)
+    Lt = ref.update_cholesky_cache(theta0, bps, os_, ls, kernel)[1][:, :, 0]
+    if regime == "GP":  # L_time is only formed when 0.1 < ls < 3H (src/cholesky-cache.cpp:27)
+        assert np.array_equal(np.tril(O.L_time), np.tril(Lt)) and np.all(np.triu(O.L_time, 1) == 0)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=thr0)
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    for S in O.S:
+        assert S.draw_fstar(orc.mt()) == 0  # initial draw_fstar on the unseeded generators (src/gpirtMCMC.cpp:227)
+    for it in range(iters):
+        O.mt_seed_all(it * 10000)
+        assert O.sweep(lambda block, h: orc.mt()) == 0
+        s = O.state()
+        assert np.array_equal(s["theta"], R["theta"][it]), f"sweep {it}"
+        assert np.array_equal(s["beta"], R["beta"][..., it])
+        assert np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, :, it])
+        assert abs(O.total_ll() - R["ll"][it]) <= 1e-9 * abs(R["ll"][it])
+    assert np.max(np.abs(s["f"] - R["f"][..., -1])) < 1e-5
+    assert np.max(np.abs(s["fstar"] - R["fstar"][..., -1])) < 1e-5
+
+
+def test_reference_CST_regime_at_horizon_2_reads_thresholds_out_of_bounds():
+    """theta_ls >= 3H with H > 1 (the R default theta_ls = 10 for H <= 3): compute_ll_sparse indexes thresholds(j, c) with j up to m*H - 1 on
+    an m-row matrix (src/draw-theta.cpp:139,162 -> :17-19). Armadillo's bounds check (kept in the stand-in) throws inside the
+    `omp parallel for` of draw_theta, which terminates the process — so the reference's own code is run in a child process here. This is
+    why gpirt_b200 refuses that regime with an error instead of restating it."""
+    import subprocess
+    import sys
+
+    code = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np
+from oracle import ref
+from tests.problems import make_problem
+n, m, C, H = 20, 4, 3, 2
+Ps = [make_problem(n, m, C, seed=30 + h, missing=0.0) for h in range(H)]
+y = np.stack([P["y"] for P in Ps], axis=2)
+z = np.random.default_rng(0).standard_normal(H * (3 * m + n * m))
+ref.set_threads(1)
+ref.gpirtMCMC(y, np.stack([P["theta0"] for P in Ps], axis=1), 1, 0, 1, np.zeros((3, m)), Ps[0]["beta_prior_sds"], np.zeros((2, n)),
+              np.zeros((2, n)), 1.0, 10.0, "Matern", np.stack([Ps[0]["thr0"]] * H, axis=2), 0, z)
+print("SURVIVED")
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=300)
+    assert r.returncode != 0 and "SURVIVED" not in r.stdout
+    assert "index out of bounds" in r.stderr
