@@ -805,11 +805,13 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     return GPIRT_OK;
 }
 
-static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
+// table_only != nullptr: only prepare the per-sweep term table (or decide against it) and report it — the joint step of a panel launches its own kernel
+static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double** table_only = nullptr) {
     ThetaView v{};
     v.n = h->n; v.resp0 = h->resp0; v.n_local = h->n_local; v.m_total = h->m_total; v.m_chunk = h->m_chunk; v.ld_chunk = h->ld_chunk;
     v.world = h->world; v.C = h->C; v.y_rm = h->y_rm; v.ldm = h->ldm; v.theta = h->theta; v.theta_new = h->theta_x;
-    v.fstar_all = h->fstar; v.chunk_elems = (long long)NGRID * h->ld_chunk; v.beta = h->beta; v.thr = h->thr; v.theta_prior_sds = h->tps;
+    v.fstar_all = h->fstar; v.chunk_elems = (long long)NGRID * h->ld_chunk; v.beta = h->beta; v.thr = h->thr_theta ? h->thr_theta : h->thr;
+    v.theta_prior_sds = h->tps;
     v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os; v.key = h->key();
     v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
     TRY(stage_streams(h, s, h->n, 1, &v.z, &v.z_stride, &v.us));
@@ -823,6 +825,7 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s) {
         SEC(h, "theta_table", CU(launch_theta_table(h->stream, v, h->theta_tab)));
         v.table = h->theta_tab;
     }
+    if (table_only) { *table_only = v.table; return GPIRT_OK; }
     SEC(h, "ess_theta", CU(launch_ess_theta(h->stream, v)));
     return GPIRT_OK;
 }
@@ -1054,6 +1057,204 @@ int gpirt_init_f_from_z(gpirt_sampler* h, const double* z) {
                          cudaMemcpyHostToDevice, h->stream));
     TRY(f_from_zbuf(h));
     CU(cudaStreamSynchronize(h->stream));  // z is the caller's memory
+    return GPIRT_OK;
+}
+
+
+// ================================================================================================
+// horizon > 1 (dynamic GPIRT), constant_IRF == 0. Given theta the sessions are independent (the reference loops h outside every
+// per-item block: src/draw-f.cpp:62, src/draw-fstar.cpp:20, src/draw-beta.cpp:60, src/draw_threshold.cpp:206; gather and K per session:
+// src/gpirtMCMC.cpp:291-298, src/cholesky-cache.cpp:20-24), so a panel is H single-session samplers on one main stream (each keeps its
+// own side stream for its theta-only chain) plus the joint theta step of src/draw-theta.cpp:171-236.
+struct gpirt_panel {
+    gpirt_config cfg;
+    int H = 0, regime = 0;  // 0: H == 1 (the session's own rule); 1: RDM (ls <= 0.1); 2: GP over time (0.1 < ls < 3H)
+    std::vector<gpirt_sampler*> ses;
+    std::vector<double> L_time;      // H x H, host
+    double* d_L_time = nullptr;
+    ThetaSession* d_ses = nullptr;
+};
+
+static int panel_fail_free(gpirt_panel* p, int rc) {
+    gpirt_panel_destroy(p);
+    return rc;
+}
+
+int gpirt_panel_create(const gpirt_config* cfg, gpirt_panel** out) {
+    if (!cfg || !out) return fail(GPIRT_ERR_INVALID, "gpirt_panel_create: NULL argument");
+    *out = nullptr;
+    const int H = cfg->horizon;
+    if (H < 1 || H > GPIRT_MAX_HORIZON) return fail(GPIRT_ERR_SHAPE, "horizon %d outside 1..%d", H, GPIRT_MAX_HORIZON);
+    if (H > 1 && cfg->world != 1) return fail(GPIRT_ERR_UNSUPPORTED, "horizon > 1 on an item shard: not built");
+    if (H > 1 && cfg->theta_ls >= 3.0 * H)
+        return fail(GPIRT_ERR_UNSUPPORTED, "theta_ls = %g >= 3 * horizon (CST regime) with horizon %d: the reference indexes thresholds(j, c) with j up to "
+                    "m*horizon-1 on an m-row matrix there (src/draw-theta.cpp:139,162 -> :17-19) and aborts; use theta_ls <= 0.1 (RDM) or "
+                    "0.1 < theta_ls < 3*horizon (GP over time)", cfg->theta_ls, H);
+    gpirt_panel* p = new gpirt_panel();
+    p->cfg = *cfg; p->H = H;
+    p->regime = H == 1 ? 0 : (cfg->theta_ls <= 0.1 ? 1 : 2);
+    for (int h = 0; h < H; ++h) {
+        gpirt_config c = *cfg;
+        c.horizon = 1;
+        if (p->regime == 1) c.theta_ls = 0.0;  // the session's own theta step uses L_i = sqrt(1 + sd0_i^2) (src/draw-theta.cpp:194)
+        gpirt_sampler* s = nullptr;
+        int rc = gpirt_create(&c, &s);
+        if (s) p->ses.push_back(s);
+        if (rc != GPIRT_OK) return panel_fail_free(p, rc);
+        s->session = h;
+        if (h > 0) {
+            rc = gpirt_set_stream(s, (void*)p->ses[0]->stream);
+            if (rc != GPIRT_OK) return panel_fail_free(p, rc);
+            // QUIRK kept: the RDM branch scores every session's theta against SESSION 0's thresholds (the whole cube goes to a 1-session
+            // ESS that reads slice 0: src/draw-theta.cpp:196-198 -> :44-47)
+            if (p->regime == 1) s->thr_theta = p->ses[0]->thr;
+        }
+    }
+    if (p->regime == 2) {
+        // L_time = chol(K_time(ts, ts, os, ls, (0, 0), KERNEL) + 1e-6 I), ts = 0..H-1; the same factor for every respondent
+        // (src/cholesky-cache.cpp:27-35 passes zeros for the linear terms). Host arithmetic, H is tiny.
+        std::vector<double>& L = p->L_time;
+        L.assign((size_t)H * H, 0.0);
+        const double os = cfg->theta_os, ls = cfg->theta_ls;
+        for (int j = 0; j < H; ++j)
+            for (int i = 0; i < H; ++i) {
+                const double diff = std::fabs((double)i - (double)j);
+                double r;
+                if (cfg->kernel == 0) {  // src/covariance-function.cpp:31-35
+                    r = os * os * (1 + std::sqrt(5.0) * diff / ls + 5 * diff * diff / ls / ls / 3);
+                    r = r * std::exp(-std::sqrt(5.0) * diff / ls);
+                } else {                 // :36-38
+                    r = os * os * std::exp(-diff * diff / ls / ls);
+                }
+                r += (double)i * 0.0 * (double)j;
+                r += 0.0;
+                L[i + (size_t)j * H] = r + (i == j ? 1e-6 : 0.0);
+            }
+        for (int j = 0; j < H; ++j) {  // left-looking column Cholesky, upper triangle zeroed (arma::chol(V, "lower"))
+            double* cj = &L[(size_t)j * H];
+            for (int k = 0; k < j; ++k) {
+                const double* ck = &L[(size_t)k * H];
+                const double ljk = ck[j];
+                if (ljk == 0.0) continue;
+                for (int i = j; i < H; ++i) cj[i] -= ck[i] * ljk;
+            }
+            if (!(cj[j] > 0.0)) { fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K_time + 1e-6 I not positive definite at leading minor %d", j + 1); return panel_fail_free(p, GPIRT_ERR_NOT_PD); }
+            const double d = std::sqrt(cj[j]);
+            cj[j] = d;
+            for (int i = j + 1; i < H; ++i) cj[i] /= d;
+            for (int i = 0; i < j; ++i) cj[i] = 0.0;
+        }
+        if (cudaMalloc((void**)&p->d_L_time, (size_t)H * H * 8) != cudaSuccess || cudaMalloc((void**)&p->d_ses, (size_t)H * sizeof(ThetaSession)) != cudaSuccess ||
+            cudaMemcpy(p->d_L_time, L.data(), (size_t)H * H * 8, cudaMemcpyHostToDevice) != cudaSuccess) {
+            fail(GPIRT_ERR_CUDA, "panel: device allocation failed");
+            return panel_fail_free(p, GPIRT_ERR_CUDA);
+        }
+    }
+    *out = p;
+    return GPIRT_OK;
+}
+
+int gpirt_panel_destroy(gpirt_panel* p) {
+    if (!p) return GPIRT_OK;
+    for (gpirt_sampler* s : p->ses) {  // sessions 1.. borrowed session 0's stream: give them none to destroy
+        if (s != p->ses[0]) { cudaSetDevice(s->cfg.device); quiesce(s); cudaStreamSynchronize(s->stream); s->own_stream = false; }
+    }
+    for (size_t h = p->ses.size(); h-- > 0;) gpirt_destroy(p->ses[h]);
+    if (p->d_L_time) cudaFree(p->d_L_time);
+    if (p->d_ses) cudaFree(p->d_ses);
+    delete p;
+    return GPIRT_OK;
+}
+
+int gpirt_panel_session(gpirt_panel* p, int h, gpirt_sampler** out) {
+    if (!p || !out || h < 0 || h >= p->H) return fail(GPIRT_ERR_INVALID, "panel_session: bad arguments");
+    *out = p->ses[h];
+    return GPIRT_OK;
+}
+
+int gpirt_panel_get_L_time(gpirt_panel* p, double* out) {
+    if (!p || !out) return fail(GPIRT_ERR_INVALID, "panel_get_L_time: NULL argument");
+    if (p->regime != 2) return fail(GPIRT_ERR_INVALID, "L_time exists in the GP-over-time regime only (0.1 < theta_ls < 3*horizon, horizon > 1)");
+    std::memcpy(out, p->L_time.data(), p->L_time.size() * 8);
+    return GPIRT_OK;
+}
+
+// RDM: `s` is an array of H stream sets (or NULL), session h draws with s[h]; GP: one set with H normals per respondent.
+int gpirt_panel_draw_theta(gpirt_panel* p, const gpirt_streams* s) {
+    if (!p) return fail(GPIRT_ERR_INVALID, "panel_draw_theta: NULL panel");
+    CU(cudaSetDevice(p->cfg.device));
+    const int H = p->H;
+    if (p->regime != 2) {
+        for (int h = 0; h < H; ++h) {
+            gpirt_sampler* S = p->ses[h];
+            TRY(need_data(S));
+            TRY(do_draw_theta(S, s ? &s[h] : nullptr));
+        }
+        for (int h = 0; h < H; ++h) TRY(commit_theta(p->ses[h]));
+        return GPIRT_OK;
+    }
+    gpirt_sampler* S0 = p->ses[0];
+    std::vector<ThetaSession> hs(H);
+    for (int h = 0; h < H; ++h) {
+        gpirt_sampler* S = p->ses[h];
+        TRY(need_data(S));
+        const double* table = nullptr;
+        TRY(do_draw_theta(S, nullptr, &table));  // builds the session's term table when it pays
+        hs[h] = ThetaSession{S->y_rm, S->theta, S->theta_x, S->fstar, S->beta, S->thr, table};
+    }
+    CU(cudaMemcpyAsync(p->d_ses, hs.data(), (size_t)H * sizeof(ThetaSession), cudaMemcpyHostToDevice, S0->stream));
+    ThetaPanelView v{};
+    v.n = S0->n; v.m = S0->m_total; v.ld_chunk = S0->ld_chunk; v.C = S0->C; v.H = H; v.ldm = S0->ldm;
+    v.ses = p->d_ses; v.L_time = p->d_L_time; v.key = S0->key();
+    v.evals = S0->evals[GPIRT_BLOCK_THETA]; v.margin = S0->margin[GPIRT_BLOCK_THETA]; v.flags = S0->flags;
+    TRY(stage_streams(S0, s, S0->n, (size_t)H, &v.z, &v.z_stride, &v.us));
+    SEC(S0, "ess_theta", CU(launch_ess_theta_panel(S0->stream, v)));
+    CU(cudaStreamSynchronize(S0->stream));  // hs (host) was the source of an async copy
+    for (int h = 0; h < H; ++h) TRY(commit_theta(p->ses[h]));
+    return GPIRT_OK;
+}
+
+int gpirt_panel_sweep(gpirt_panel* p, int n_sweeps) {
+    if (!p) return fail(GPIRT_ERR_INVALID, "panel_sweep: NULL panel");
+    CU(cudaSetDevice(p->cfg.device));
+    for (gpirt_sampler* S : p->ses) {
+        TRY(need_data(S));
+        if (S->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "a sweep needs 3 mean coefficients per item");
+    }
+    for (int k = 0; k < n_sweeps; ++k) {
+        for (gpirt_sampler* S : p->ses) {  // draw_f, draw_fstar (src/gpirtMCMC.cpp:270-277)
+            TRY(do_draw_f(S, nullptr));
+            TRY(do_draw_fstar(S, nullptr));
+        }
+        TRY(gpirt_panel_draw_theta(p, nullptr));  // :280-284, commits theta
+        for (gpirt_sampler* S : p->ses) {  // :286-331; commit_theta already ran
+            TRY(launch_theta_chain(S));
+            TRY(do_gather_f(S));
+            TRY(do_small_ess(S, IB_BETA, nullptr));
+            if (!S->chol_valid) TRY(do_update_cholesky(S));
+            TRY(do_small_ess(S, IB_THR, nullptr));
+            TRY(do_item_ll(S));
+            S->iter += 1;
+        }
+    }
+    return GPIRT_OK;
+}
+
+int gpirt_panel_total_ll(gpirt_panel* p, double* total) {
+    if (!p || !total) return fail(GPIRT_ERR_INVALID, "panel_total_ll: NULL argument");
+    double acc = 0.0;
+    for (gpirt_sampler* S : p->ses) {  // one running sum over (h, j) in the reference (src/gpirtMCMC.cpp:324-331); per session, then in session order here
+        double t = 0.0;
+        TRY(gpirt_total_ll(S, &t));
+        acc += t;
+    }
+    *total = acc;
+    return GPIRT_OK;
+}
+
+int gpirt_panel_sync(gpirt_panel* p) {
+    if (!p) return fail(GPIRT_ERR_INVALID, "panel_sync: NULL panel");
+    for (gpirt_sampler* S : p->ses) TRY(gpirt_sync(S));
     return GPIRT_OK;
 }
 

@@ -15,7 +15,7 @@ enum Stream : uint32_t {
 
 struct RngKey {
     uint32_t k0, k1;   // seed
-    uint32_t chain, iter;
+    uint32_t tag, iter;  // tag = session << 8 | chain << 16: ORed into the stream id (streams are < 256; session 0 of chain c is the plain chain)
 };
 
 __host__ __device__ inline void philox4x32_10(uint32_t c[4], uint32_t k0, uint32_t k1) {
@@ -43,7 +43,7 @@ __host__ __device__ inline double u01_from_bits(uint32_t a, uint32_t b) {
 
 __host__ __device__ inline void philox_uniform2(const RngKey& key, uint32_t stream, uint32_t unit, uint32_t block,
                                                 double& a, double& b) {
-    uint32_t c[4] = {block, unit, key.iter, stream | (key.chain << 16)};
+    uint32_t c[4] = {block, unit, key.iter, stream | key.tag};
     philox4x32_10(c, key.k0, key.k1);
     a = u01_from_bits(c[0], c[1]);
     b = u01_from_bits(c[2], c[3]);

@@ -74,6 +74,8 @@ struct gpirt_sampler {
 
     // staging for supplied streams
     double *d_z = nullptr, *d_u = nullptr;
+    int session = 0;                    // horizon > 1: which session of a gpirt_panel this handle is (keys the Philox streams)
+    const double* thr_theta = nullptr;  // thresholds the theta step scores against when they are not this handle's own (RDM quirk, capi.cu)
     char* arena = nullptr;  // the one allocation behind every buffer above
     size_t d_z_cap = 0, d_u_cap = 0;
     // device-side store of the draws gpirtMCMC keeps (src/gpirtMCMC.cpp:230-255,334-356): appended on the stream, read back in bulk
@@ -86,7 +88,7 @@ struct gpirt_sampler {
         gpirt::RngKey k;
         k.k0 = (uint32_t)cfg.seed;
         k.k1 = (uint32_t)(cfg.seed >> 32);
-        k.chain = cfg.chain;
+        k.tag = ((uint32_t)session << 8) | (cfg.chain << 16);
         k.iter = iter;
         return k;
     }

@@ -428,6 +428,92 @@ cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     return cudaGetLastError();
 }
 
+
+// One CTA per respondent; the H sessions' log-likelihood sums are formed one after the other (each a block reduction in the
+// fixed order of k_ess_theta) and added in session order, as the reference's `log_y += compute_ll_sparse(...)` loop does.
+__global__ void __launch_bounds__(THETA_THREADS) k_ess_theta_panel(ThetaPanelView v) {
+    __shared__ double s_part[THETA_THREADS / 32];
+    const int i = blockIdx.x;
+    if (i >= v.n) return;
+    const int tid = threadIdx.x;
+    const int C = v.C, m = v.m, H = v.H;
+
+    auto loglik_h = [&](int h, double th) -> double {  // compute_ll_sparse of session h, src/draw-theta.cpp:4-24
+        const ThetaSession& S = v.ses[h];
+        const int8_t* __restrict__ yrow = S.y_rm + (size_t)i * v.ldm;
+        const double* __restrict__ table = S.table;
+        const int idx = grid_index(th);
+        const double ts = grid_value(idx);
+        auto term = [&](int J) -> double {
+            const int y = yrow[J];
+            if (y == 0) return 0.0;
+            if (table) return table[((size_t)idx * m + J) * C + (y - 1)];
+            const double fs = S.fstar[(size_t)idx * v.ld_chunk + J];
+            const double mu = mu_of(ts, S.beta[3 * (size_t)J], S.beta[3 * (size_t)J + 1], S.beta[3 * (size_t)J + 2]);
+            const double g = __dadd_rn(fs, mu);  // f* already holds mu*; the reference adds it again (:17)
+            return cell_ll(g, S.thr[(size_t)J * (C + 1) + y - 1], S.thr[(size_t)J * (C + 1) + y], y == 1, y == C);
+        };
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+        int J = tid;
+        for (; J + 3 * THETA_THREADS < m; J += 4 * THETA_THREADS) {
+            a0 += term(J);
+            a1 += term(J + THETA_THREADS);
+            a2 += term(J + 2 * THETA_THREADS);
+            a3 += term(J + 3 * THETA_THREADS);
+        }
+        for (; J < m; J += THETA_THREADS) a0 += term(J);
+        return block_sum<THETA_THREADS / 32>((a0 + a1) + (a2 + a3), s_part);
+    };
+
+    // nu = L_time z, dense column sweep (rmvnorm_threadsafe: L * z, src/mvnormal.h:17-24)
+    double nu[GPIRT_MAX_HORIZON], th0[GPIRT_MAX_HORIZON], raw[GPIRT_MAX_HORIZON];
+    for (int h = 0; h < H; ++h) { nu[h] = 0.0; th0[h] = v.ses[h].theta[i]; raw[h] = th0[h]; }
+    for (int k = 0; k < H; ++k) {
+        const double zk = v.z ? v.z[(size_t)i * v.z_stride + k] : philox_normal(v.key, ST_THETA_Z, i, k);
+        for (int h = 0; h < H; ++h) nu[h] = __dadd_rn(nu[h], __dmul_rn(v.L_time[h + (size_t)k * H], zk));
+    }
+    int overrun = 0;
+    uint32_t k = 0;
+    const double u = v.us.get(v.key, ST_THETA_U, i, k++, &overrun);
+    double log_y = log(u);
+    for (int h = 0; h < H; ++h) log_y = __dadd_rn(log_y, loglik_h(h, th0[h]));  // :43-47
+    double eps_min = 0.0, eps_max = TWO_PI_R;
+    double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+    eps_min = __dsub_rn(eps, TWO_PI_R);
+    int evals = 1;
+    double margin = CUDART_INF;
+    bool accepted = false;
+    for (int it = 0; it < ESS_MAX_PROPOSALS; ++it) {
+        const double ce = cos(eps), se = sin(eps);
+        double llp = 0.0;
+        for (int h = 0; h < H; ++h) {
+            raw[h] = __dadd_rn(__dmul_rn(th0[h], ce), __dmul_rn(nu[h], se));
+            raw[h] = fmax(-5.0, fmin(5.0, raw[h]));  // :58-62
+        }
+        for (int h = 0; h < H; ++h) llp = __dadd_rn(llp, loglik_h(h, raw[h]));
+        ++evals;
+        margin = fmin(margin, fabs(llp - log_y));
+        if (llp > log_y) { accepted = true; break; }
+        if (eps < 0.0) eps_min = eps; else eps_max = eps;
+        eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+        if (overrun) break;
+    }
+    if (tid == 0) {
+        for (int h = 0; h < H; ++h) v.ses[h].theta_new[i] = grid_value(grid_index(raw[h]));  // :229-233
+        v.evals[i] = evals;
+        v.margin[i] = margin;
+        if (overrun) atomicExch(&v.flags->overrun, 1);
+        else if (!accepted) atomicExch(&v.flags->stalled, 1);
+    }
+}
+
+cudaError_t launch_ess_theta_panel(cudaStream_t st, const ThetaPanelView& v) {
+    if (v.n <= 0) return cudaSuccess;
+    k_ess_theta_panel<<<v.n, THETA_THREADS, 0, st>>>(v);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
 // ------------------------------------------------------------------------------------------------
 __global__ void k_gather_f(const double* __restrict__ theta, int n, const double* __restrict__ fstar, int ld_chunk,
                            int m_local, double* __restrict__ f, int ldn) {

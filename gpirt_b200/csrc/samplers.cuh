@@ -69,6 +69,31 @@ struct ThetaView {
     DevFlags* flags;
 };
 
+// horizon > 1, GP-over-time regime (src/draw-theta.cpp:206-235): one H-dimensional ESS per respondent over the sessions' tables
+struct ThetaSession {       // what the joint step reads / writes of one session (device pointers of that session's handle)
+    const int8_t* y_rm;
+    const double* theta;    // n (current)
+    double* theta_new;      // n
+    const double* fstar;    // NGRID x ld_chunk grid-row-major (world == 1)
+    const double* beta;     // 3 x m
+    const double* thr;      // (C+1) x m item-major
+    const double* table;    // optional [NGRID][m][C] term table, or nullptr
+};
+constexpr int GPIRT_MAX_HORIZON = 32;
+struct ThetaPanelView {
+    int n, m, ld_chunk, C, H;
+    long long ldm;
+    const ThetaSession* ses;   // device array of H
+    const double* L_time;      // H x H column-major lower factor (device)
+    const double* z; long long z_stride;
+    UniformSrc us;
+    RngKey key;
+    int32_t* evals;
+    double* margin;
+    DevFlags* flags;
+};
+cudaError_t launch_ess_theta_panel(cudaStream_t st, const ThetaPanelView& v);
+
 enum ItemBlock { IB_F = 0, IB_BETA = 1, IB_THR = 2 };
 
 cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, int cols, RngKey key, uint32_t stream, uint32_t unit0);

@@ -99,9 +99,19 @@ class Sampler:
         self.m_chunk = (self.m + world - 1) // world
         self.n_chunk = (self.n + world - 1) // world
 
+    @classmethod
+    def _borrowed(cls, handle, n, m, Ccat, p_beta=3):
+        """A Sampler over a handle somebody else owns (a session of a Panel): close() forgets it instead of destroying it."""
+        self = cls.__new__(cls)
+        self.n, self.m, self.C, self.p_beta, self.rank, self.world = int(n), int(m), int(Ccat), p_beta, 0, 1
+        self._L, self._h, self._owned = _lib.lib(), handle, False
+        self.m_chunk, self.n_chunk = self.m, self.n
+        return self
+
     def close(self):
         if getattr(self, "_h", None):
-            self._L.gpirt_destroy(self._h)
+            if getattr(self, "_owned", True):
+                self._L.gpirt_destroy(self._h)
             self._h = None
 
     __del__ = close

@@ -62,7 +62,7 @@ typedef struct gpirt_sampler gpirt_sampler; /* opaque: owns all device memory, s
 typedef struct {
     int32_t n;             /* respondents */
     int32_t m_total;       /* items of the whole problem */
-    int32_t horizon;       /* must be 1 */
+    int32_t horizon;       /* 1 for gpirt_create; gpirt_panel_create takes horizon >= 1 */
     int32_t C;             /* response categories, 2..21 */
     int32_t constant_IRF;  /* must be 0 */
     int32_t p_beta;        /* rows of beta: 3 (gpirtMCMC) or 2 (recover_fstar, src/recover_fstar.cpp:58-60) */
@@ -186,6 +186,27 @@ int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, doub
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
 /* fp32 screening term, its error bound and the fp64 cell term log(Phi(tau_hi-g) - Phi(tau_lo-g) + 1e-6), element-wise */
 int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const double* tau_hi, int n, double* t32, double* e32, double* t64);
+
+/* ---- horizon > 1 (dynamic GPIRT), constant_IRF == 0 ----
+ * A panel is `horizon` single-session samplers (given theta the sessions are independent: the reference loops h outside every per-item
+ * block) plus the joint theta step of src/draw-theta.cpp:171-236. cfg->horizon = H; regime by cfg->theta_ls as in the reference:
+ *   theta_ls <= 0.1           RDM: every (respondent, session) its own ESS, prior sd sqrt(1 + theta_prior_sds(0,i)^2)
+ *   0.1 < theta_ls < 3H       GP over time: one H-dim ESS per respondent, nu = L_time z, L_time = chol(K_time(0..H-1) + 1e-6 I)
+ *   theta_ls >= 3H, H > 1     refused (GPIRT_ERR_UNSUPPORTED): the reference reads thresholds out of bounds there and aborts
+ * Session handles are borrowed with gpirt_panel_session and take every per-session call above (set_data / set_priors / set_state /
+ * get_state / draw_f / draw_fstar / gather_f / draw_beta / draw_threshold / ll_bar ...) on slice h of the reference's cubes; do not
+ * destroy them or call gpirt_draw_theta / gpirt_sweep on them. Philox streams are keyed by (chain, session). world == 1 only. */
+typedef struct gpirt_panel gpirt_panel;
+int gpirt_panel_create(const gpirt_config* cfg, gpirt_panel** out);
+int gpirt_panel_destroy(gpirt_panel* p);
+int gpirt_panel_session(gpirt_panel* p, int h, gpirt_sampler** out);
+int gpirt_panel_get_L_time(gpirt_panel* p, double* out /* H x H */);
+/* streams: NULL (Philox), or RDM: an array of H gpirt_streams (session h: 1 normal + uniforms per respondent); GP: one gpirt_streams
+ * with z_stride >= H normals per respondent */
+int gpirt_panel_draw_theta(gpirt_panel* p, const gpirt_streams* streams);
+int gpirt_panel_sweep(gpirt_panel* p, int n_sweeps);
+int gpirt_panel_total_ll(gpirt_panel* p, double* total);
+int gpirt_panel_sync(gpirt_panel* p);
 
 /* ---- the two Rcpp entry points ---- */
 typedef struct {

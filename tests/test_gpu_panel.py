@@ -1,0 +1,102 @@
+"""horizon > 1 (dynamic GPIRT): the CUDA panel (gpirt_panel_*: H single-session samplers + the joint theta step) against the CPU oracle's
+panel, which is pinned bit for bit to the reference's own gpirtMCMC at H = 3 (tests/test_oracle_vs_ref.py). theta is bit-exact (it lives on
+the 0.01 grid), proposal counts identical, beta / thresholds 1e-9, f / f* norm-wise 1e-6 on well-conditioned priors."""
+import numpy as np
+import pytest
+
+from oracle import orc
+from tests.problems import make_problem, uniform_streams
+
+pytestmark = pytest.mark.gpu
+REGIMES = [("RDM", 0.05, "Matern"), ("GP", 2.0, "Matern"), ("GP", 4.5, "RBF")]
+
+
+def problem(n, m, C, H, seed):
+    Ps = [make_problem(n, m, C, seed=seed + h, missing=0.12, on_grid=True) for h in range(H)]
+    rng = np.random.default_rng(seed + 100)
+    P = dict(n=n, m=m, C=C, H=H, rng=rng)
+    P["y"] = np.asfortranarray(np.stack([p["y"] for p in Ps], axis=2))
+    P["theta0"] = np.asfortranarray(np.stack([p["theta0"] for p in Ps], axis=1))
+    P["beta0"] = np.asfortranarray(np.stack([p["beta0"] * 0.3 for p in Ps], axis=2))
+    thr = []
+    for h in range(H):  # different thresholds per session: the RDM step scores every session against session 0's
+        t = Ps[h]["thr0"].copy()
+        t[:, 1:-1] += 0.15 * h + 0.05 * rng.standard_normal((m, 1))
+        thr.append(t)
+    P["thr0"] = np.asfortranarray(np.stack(thr, axis=2))
+    P["bps"] = np.asfortranarray(np.tile(np.array([[0.8], [0.5], [0.1]]), (1, m)))  # well-conditioned K
+    P["tps"] = np.asfortranarray(np.vstack([rng.uniform(0.0, 0.8, (1, n)), np.zeros((1, n))]))
+    return P
+
+
+def make_pair(P, ls, kernel, os_=1.3, seed=99):
+    import gpirt_b200 as g
+
+    G = g.Panel(P["n"], P["m"], P["C"], P["H"], theta_os=os_, theta_ls=ls, KERNEL=kernel, seed=seed, chain=2)
+    G.set_data(P["y"])
+    G.set_priors(P["bps"], P["tps"])
+    O = orc.Panel(P["y"], P["C"], P["bps"], P["tps"], theta_os=os_, theta_ls=ls, KERNEL=kernel)
+    return G, O
+
+
+@pytest.mark.parametrize("regime,ls,kernel", REGIMES)
+def test_panel_theta_step_same_states_given_same_streams(regime, ls, kernel):
+    n, m, C, H = 90, 26, 4, 3
+    P = problem(n, m, C, H, seed=3)
+    rng = P["rng"]
+    G, O = make_pair(P, ls, kernel)
+    assert G.regime == regime
+    f = np.asfortranarray(rng.standard_normal((n, m, H)))
+    fstar = np.asfortranarray(rng.standard_normal((orc.NGRID, m, H)) * 0.7)
+    G.set_state(theta=P["theta0"], beta=P["beta0"], f=f, thresholds=P["thr0"], fstar=fstar)
+    O.set_state(theta=P["theta0"], beta=P["beta0"], f=f, thr=P["thr0"], fstar=fstar)
+    O.compute_mu()
+    if regime == "GP":
+        assert np.max(np.abs(G.L_time() - O.L_time)) < 1e-15
+        z, u = np.asfortranarray(rng.standard_normal((H, n))), uniform_streams(rng, n)
+        G.draw_theta(z=z, u=u)
+        O.draw_theta(orc.supplied(z=z, u=u))
+        ev_g, mg = G.diag_theta()
+        ev_o = O.S[0].diag("theta")[0]
+    else:
+        z = [np.asfortranarray(rng.standard_normal((1, n))) for _ in range(H)]
+        u = [uniform_streams(rng, n) for _ in range(H)]
+        G.draw_theta(z=z, u=u)
+        O.draw_theta([orc.supplied(z=z[h], u=u[h]) for h in range(H)])
+        ev_g, mg = G.diag_theta()
+        ev_o = np.stack([S.diag("theta")[0] for S in O.S])
+    assert np.array_equal(ev_g, ev_o), "different numbers of proposals"
+    assert np.min(mg) > 1e-9  # no accept decision sat on a knife edge: the comparison below is meaningful
+    assert np.array_equal(G.get_state()["theta"], O.state()["theta"])
+    assert np.any(ev_g > 2)
+
+
+@pytest.mark.parametrize("regime,ls,kernel", REGIMES)
+def test_panel_sweeps_match_oracle_on_the_same_philox_streams(regime, ls, kernel):
+    n, m, C, H, sweeps = 70, 18, 4, 3, 3
+    P = problem(n, m, C, H, seed=11)
+    G, O = make_pair(P, ls, kernel, seed=4242)
+    rng = P["rng"]
+    f0 = np.asfortranarray(rng.standard_normal((n, m, H)) * 0.5)
+    G.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thresholds=P["thr0"])
+    O.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thr=P["thr0"])
+    for it in range(sweeps):
+        G.set_iter(it)
+        G.sweep(1)
+        assert O.sweep(lambda block, h: orc.philox(4242, 2, it, session=0 if h is None else h)) == 0
+        a, b = G.get_state(fstar=True), O.state()
+        assert np.array_equal(a["theta"], b["theta"]), f"sweep {it}: theta"
+        assert np.max(np.abs(a["beta"] - b["beta"])) < 1e-9 and np.max(np.abs(a["thresholds"][:, 1:-1] - b["thr"][:, 1:-1])) < 1e-9
+        assert np.max(np.abs(a["f"] - b["f"])) < 1e-6 * max(1.0, np.max(np.abs(b["f"])))
+        assert np.max(np.abs(a["fstar"] - b["fstar"])) < 1e-6 * max(1.0, np.max(np.abs(b["fstar"])))
+        assert abs(G.total_ll() - O.total_ll()) <= 1e-9 * abs(O.total_ll())
+
+
+def test_panel_refuses_the_regime_the_reference_aborts_in():
+    import gpirt_b200 as g
+
+    with pytest.raises(g.GpirtError) as e:
+        g.Panel(20, 5, 3, 2, theta_ls=10.0)  # the R default theta_ls = 10 >= 3H for H <= 3
+    assert "out of bounds" in str(e.value) or "thresholds" in str(e.value)
+    P1 = g.Panel(20, 5, 3, 1, theta_ls=10.0)  # horizon 1 is the plain sampler
+    assert P1.regime == "H1"
