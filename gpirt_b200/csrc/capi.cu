@@ -578,29 +578,45 @@ int gpirt_store_count(gpirt_sampler* h, int* count, int* capacity) {
     if (capacity) *capacity = h->store.cap;
     return GPIRT_OK;
 }
-int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_draws, double* beta_draws, double* threshold_draws,
-                      double* ll_draws, double* f_draws, double* fstar_draws) {
+int gpirt_store_flush_slice(gpirt_sampler* h, int n_samples, int first, int horizon, int slice, double* theta_draws, double* beta_draws,
+                            double* threshold_draws, double* ll_draws, double* f_draws, double* fstar_draws) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
     auto& s = h->store;
     if (s.cap < 1) return fail(GPIRT_ERR_INVALID, "store_flush: no store open");
     if (first < 0 || first + s.count > n_samples) return fail(GPIRT_ERR_INVALID, "store_flush: samples %d..%d outside 0..%d", first, first + s.count, n_samples);
+    if (horizon < 1 || slice < 0 || slice >= horizon) return fail(GPIRT_ERR_INVALID, "store_flush: slice %d of %d", slice, horizon);
     TRY(check_flags(h));  // one synchronisation for everything pushed since the last flush
-    const size_t cnt = (size_t)s.count, m = (size_t)h->m_total, n = (size_t)h->n, C1 = (size_t)h->C + 1;
+    const size_t cnt = (size_t)s.count, m = (size_t)h->m_total, n = (size_t)h->n, C1 = (size_t)h->C + 1, H = (size_t)horizon, sl = (size_t)slice;
     if (cnt == 0) return GPIRT_OK;
-    if (theta_draws) {  // cube n_samples x n x 1: sample index is the fast one
+    if (theta_draws) {  // cube n_samples x n x horizon: sample index is the fast one
         std::vector<double> t(cnt * n);
         CU(cudaMemcpy(t.data(), s.theta, t.size() * 8, cudaMemcpyDeviceToHost));
+        double* base = theta_draws + sl * (size_t)n_samples * n;
         for (size_t i = 0; i < n; ++i)
-            for (size_t k = 0; k < cnt; ++k) theta_draws[(size_t)first + k + i * (size_t)n_samples] = t[k * n + i];
+            for (size_t k = 0; k < cnt; ++k) base[(size_t)first + k + i * (size_t)n_samples] = t[k * n + i];
     }
-    if (beta_draws) CU(cudaMemcpy(beta_draws + (size_t)first * 3 * m, s.beta, cnt * 3 * m * 8, cudaMemcpyDeviceToHost));
-    if (threshold_draws) CU(cudaMemcpy(threshold_draws + (size_t)first * C1 * m, s.thr, cnt * C1 * m * 8, cudaMemcpyDeviceToHost));
-    if (ll_draws) CU(cudaMemcpy(ll_draws + first, s.ll, cnt * 8, cudaMemcpyDeviceToHost));
-    if (f_draws && s.f) CU(cudaMemcpy(f_draws + (size_t)first * n * m, s.f, cnt * n * m * 8, cudaMemcpyDeviceToHost));
-    if (fstar_draws && s.fstar) CU(cudaMemcpy(fstar_draws + (size_t)first * NGRID * m, s.fstar, cnt * NGRID * m * 8, cudaMemcpyDeviceToHost));
+    // per sample a cube of `horizon` slices: slice `slice` of sample first + k sits at ((first + k) * horizon + slice) * slice_size
+    auto rows = [&](double* dst, const double* src, size_t per) -> int {
+        if (H == 1) { CU(cudaMemcpy(dst + (size_t)first * per, src, cnt * per * 8, cudaMemcpyDeviceToHost)); return GPIRT_OK; }
+        CU(cudaMemcpy2D(dst + ((size_t)first * H + sl) * per, H * per * 8, src, per * 8, per * 8, cnt, cudaMemcpyDeviceToHost));
+        return GPIRT_OK;
+    };
+    if (beta_draws) TRY(rows(beta_draws, s.beta, 3 * m));
+    if (threshold_draws) TRY(rows(threshold_draws, s.thr, C1 * m));
+    if (f_draws && s.f) TRY(rows(f_draws, s.f, n * m));
+    if (fstar_draws && s.fstar) TRY(rows(fstar_draws, s.fstar, (size_t)NGRID * m));
+    if (ll_draws) {  // the reference's ll is one sum over sessions and items (src/gpirtMCMC.cpp:324-331): slice 0 sets, later slices add
+        std::vector<double> l(cnt);
+        CU(cudaMemcpy(l.data(), s.ll, cnt * 8, cudaMemcpyDeviceToHost));
+        for (size_t k = 0; k < cnt; ++k) ll_draws[(size_t)first + k] = (slice == 0 ? 0.0 : ll_draws[(size_t)first + k]) + l[k];
+    }
     s.count = 0;
     return GPIRT_OK;
+}
+int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_draws, double* beta_draws, double* threshold_draws,
+                      double* ll_draws, double* f_draws, double* fstar_draws) {
+    return gpirt_store_flush_slice(h, n_samples, first, 1, 0, theta_draws, beta_draws, threshold_draws, ll_draws, f_draws, fstar_draws);
 }
 int gpirt_store_close(gpirt_sampler* h) {
     CHECK_H(h);

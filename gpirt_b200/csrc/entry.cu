@@ -26,6 +26,60 @@ struct Guard {
         if (rc_ != GPIRT_OK) return rc_; \
     } while (0)
 
+
+// horizon > 1: the same run over a gpirt_panel. Every per-session array is slice h of the reference's cubes (column-major, slices contiguous).
+static int mcmc_panel(const gpirt_mcmc_args* a, const gpirt_config& cfg) {
+    struct PanelGuard { gpirt_panel* p = nullptr; ~PanelGuard() { if (p) gpirt_panel_destroy(p); } } g;
+    TRYC(gpirt_panel_create(&cfg, &g.p));
+    const int H = a->horizon;
+    const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1;
+    std::vector<gpirt_sampler*> S(H);
+    for (int h = 0; h < H; ++h) {
+        TRYC(gpirt_panel_session(g.p, h, &S[h]));
+        TRYC(gpirt_set_data_f64(S[h], a->y + (size_t)h * n * m));
+        TRYC(gpirt_set_priors(S[h], a->beta_prior_sds, a->theta_prior_sds));
+        TRYC(gpirt_set_state(S[h], a->theta + (size_t)h * n, a->beta_init ? a->beta_init + (size_t)h * 3 * m : nullptr,
+                             a->f_init ? a->f_init + (size_t)h * n * m : nullptr, a->thresholds + (size_t)h * m * C1, nullptr));
+        TRYC(gpirt_set_iter(S[h], 0xFFFFFFFFu));
+        TRYC(gpirt_init_draw(S[h], a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
+        if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(S[h], a->f_init_z + (size_t)h * n * m));
+        TRYC(gpirt_set_iter(S[h], 0));
+    }
+    const int total = a->sample_iterations + a->burn_iterations;
+    const int n_samples = a->sample_iterations / a->THIN;
+    int cap = 0, first = 0;
+    if (n_samples > 0) {
+        size_t free_b = 0, total_b = 0;
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return GPIRT_ERR_CUDA;
+        const int64_t per = gpirt_store_sample_bytes(S[0], a->f_draws != nullptr, a->fstar_draws != nullptr) * H;
+        cap = (int)std::max<int64_t>(1, std::min<int64_t>(n_samples, (int64_t)(free_b / 4) / per));
+        for (int h = 0; h < H; ++h) TRYC(gpirt_store_open(S[h], cap, a->f_draws != nullptr, a->fstar_draws != nullptr));
+    }
+    auto flush = [&]() -> int {
+        int cnt = 0;
+        TRYC(gpirt_store_count(S[0], &cnt, nullptr));
+        for (int h = 0; h < H; ++h)
+            TRYC(gpirt_store_flush_slice(S[h], n_samples, first, H, h, a->theta_draws, a->beta_draws, a->threshold_draws, a->ll_draws, a->f_draws,
+                                         a->fstar_draws));
+        first += cnt;
+        return GPIRT_OK;
+    };
+    for (int iter = 0; iter < total; ++iter) {
+        if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;
+        TRYC(gpirt_panel_sweep(g.p, 1));
+        if (iter >= a->burn_iterations && iter % a->THIN == 0) {
+            const int s = (iter - a->burn_iterations) / a->THIN;
+            if (s >= n_samples) continue;
+            int cnt = 0;
+            for (int h = 0; h < H; ++h) TRYC(gpirt_store_push(S[h]));
+            TRYC(gpirt_store_count(S[0], &cnt, nullptr));
+            if (cnt == cap) TRYC(flush());
+        }
+    }
+    if (n_samples > 0) TRYC(flush());
+    return gpirt_panel_sync(g.p);
+}
+
 extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     if (!a || !a->y || !a->theta || !a->beta_prior_sds || !a->theta_prior_sds || !a->thresholds || !a->theta_draws || !a->beta_draws ||
         !a->threshold_draws || !a->ll_draws)
@@ -38,6 +92,7 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     const std::string kern = a->KERNEL ? a->KERNEL : "Matern";
     cfg.kernel = kern == "RBF" ? 1 : 0;
     cfg.device = a->device; cfg.seed = a->seed; cfg.chain = a->chain; cfg.rank = 0; cfg.world = 1;
+    if (a->horizon > 1) return mcmc_panel(a, cfg);
     Guard g;
     TRYC(gpirt_create(&cfg, &g.h));
     gpirt_sampler* h = g.h;

@@ -128,6 +128,10 @@ int gpirt_store_push(gpirt_sampler* h);
 int gpirt_store_count(gpirt_sampler* h, int* count, int* capacity);
 int gpirt_store_flush(gpirt_sampler* h, int n_samples, int first, double* theta_draws, double* beta_draws, double* threshold_draws,
                       double* ll_draws, double* f_draws, double* fstar_draws);
+/* the same for session `slice` of a horizon-`horizon` run: outputs are the reference's cubes with `horizon` slices per sample; ll_draws is
+ * set by slice 0 and added to by later slices (flush the sessions in order) */
+int gpirt_store_flush_slice(gpirt_sampler* h, int n_samples, int first, int horizon, int slice, double* theta_draws, double* beta_draws,
+                            double* threshold_draws, double* ll_draws, double* f_draws, double* fstar_draws);
 int gpirt_store_close(gpirt_sampler* h);
 /* bytes of device memory one stored sample takes (to size `capacity`) */
 int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar);

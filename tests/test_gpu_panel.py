@@ -100,3 +100,36 @@ def test_panel_refuses_the_regime_the_reference_aborts_in():
     assert "out of bounds" in str(e.value) or "thresholds" in str(e.value)
     P1 = g.Panel(20, 5, 3, 1, theta_ls=10.0)  # horizon 1 is the plain sampler
     assert P1.regime == "H1"
+
+
+@pytest.mark.parametrize("regime,ls,kernel", REGIMES[:2])
+def test_gpirtMCMC_at_horizon_3_equals_the_stepwise_panel(regime, ls, kernel):
+    """gpirt_mcmc with horizon > 1 (cubes in, cubes out, burn-in / thinning, per-session device stores flushed slice by slice) against the same
+    chain driven through the panel calls: bit for bit."""
+    import gpirt_b200 as g
+
+    n, m, C, H, sample, burn, thin = 60, 14, 4, 3, 6, 1, 2
+    P = problem(n, m, C, H, seed=21)
+    res = g.gpirtMCMC(P["y"], sample, burn, THIN=thin, CHAIN=1, beta_prior_sds=P["bps"], theta_prior_sds=P["tps"], theta_os=1.3, theta_ls=ls,
+                      KERNEL=kernel, theta_init=P["theta0"], thresholds=P["thr0"], SEED=606, beta_init=P["beta0"], store_f=True, store_fstar=True)[0]
+    ns = sample // thin
+    assert res["theta"].shape == (ns, n, H) and res["beta"][0].shape == (3, m, H) and res["fstar"][0].shape == (g.NGRID, m, H)
+    G = g.Panel(n, m, C, H, theta_os=1.3, theta_ls=ls, KERNEL=kernel, seed=606, chain=0)
+    G.set_data(P["y"])
+    G.set_priors(P["bps"], P["tps"])
+    G.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+    G.set_iter(0xFFFFFFFF)
+    for S in G.S:
+        S.init_draw(draw_beta=False, draw_f=True)
+    G.set_iter(0)
+    s = 0
+    for it in range(sample + burn):
+        G.sweep(1)
+        if it >= burn and it % thin == 0 and (it - burn) // thin < ns:
+            st = G.get_state(fstar=True)
+            assert np.array_equal(res["theta"][s], st["theta"]) and np.array_equal(res["beta"][s], st["beta"])
+            assert np.array_equal(res["threshold"][s], st["thresholds"]) and np.array_equal(res["f"][s], st["f"])
+            assert np.array_equal(res["fstar"][s], st["fstar"])
+            assert res["ll"][s] == G.total_ll()
+            s += 1
+    assert s == ns
