@@ -72,6 +72,57 @@ def sweep_case(name, n, m, C, seed, iters, missing, empty_item=None, tps_sd=0.0)
     print(name, "ll", R["ll"], "max evals recorded", max(int(v.max()) for k, v in rec.items() if k.startswith("nu_")))
 
 
+def panel_case(name, n, m, C, H, seed, iters, ls, kernel, os_=1.3):
+    """horizon > 1: the reference's gpirtMCMC at H sessions (RDM for ls <= 0.1, GP over time for 0.1 < ls < 3H) and the streams every unit of
+    every session consumed, captured from the oracle's panel in mt19937 mode run beside it (kept only if it reproduces the reference's theta,
+    beta and thresholds bit for bit). Keys: z_<block>_<it>_<h> / u_... / nu_... per session; the GP theta step has no session suffix."""
+    Ps = [make_problem(n, m, C, seed=seed + h, missing=0.12) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    theta_in = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1)) * 1.5
+    rng = np.random.default_rng(seed + 1000)
+    thr0 = np.asfortranarray(np.stack([Ps[0]["thr0"]] * H, axis=2))
+    z_init = rng.standard_normal(H * (3 * m + n * m))
+    bpm, bps, tpm = np.zeros((3, m), order="F"), Ps[0]["beta_prior_sds"], np.zeros((2, n), order="F")
+    tps = np.asfortranarray(np.vstack([rng.uniform(0.0, 0.7, (1, n)), np.zeros((1, n))]))
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, os_, ls, kernel, thr0, 0, z_init, store_f=True, store_fstar=True)
+    theta0 = np.clip(theta_in, -5.0, 5.0)
+    beta0 = np.asfortranarray(np.stack([bpm + bps * z_init[h * 3 * m:(h + 1) * 3 * m].reshape(m, 3).T for h in range(H)], axis=2))
+    zf = z_init[H * 3 * m:]
+    L0 = ref.update_cholesky_cache(theta0, bps)[0]
+    f0 = np.asfortranarray(np.stack([np.stack([L0[:, :, h] @ zf[(h * m + j) * n:(h * m + j + 1) * n] for j in range(m)], axis=1) for h in range(H)], axis=2))
+    O = orc.Panel(y, C, bps, tps, theta_os=os_, theta_ls=ls, KERNEL=kernel)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=thr0)
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    for S in O.S:
+        S.draw_fstar(orc.mt())  # the initial draw_fstar (src/gpirtMCMC.cpp:227), unseeded generators
+    fstar0 = O.state()["fstar"]
+    O.record(True)
+    rec = {}
+    for it in range(iters):
+        O.mt_seed_all(it * 10000)
+        assert O.sweep(lambda block, h: orc.mt()) == 0
+        for h, S in enumerate(O.S):
+            blocks = [("f", n), ("fstar", orc.NGRID), ("beta", 3), ("thr", C - 1)] + ([("theta", 1)] if O.regime == 1 else [])
+            for blk, zcap in blocks:
+                z, u, nz, nu = S.recorded(blk, zcap, UCAP)
+                rec[f"z_{blk}_{it}_{h}"] = z
+                if blk != "fstar":
+                    rec[f"u_{blk}_{it}_{h}"] = u
+                    rec[f"nu_{blk}_{it}_{h}"] = nu
+        if O.regime == 2:
+            z, u, nz, nu = O.S[0].recorded("theta", H, UCAP)
+            rec[f"z_theta_{it}"], rec[f"u_theta_{it}"], rec[f"nu_theta_{it}"] = z, u, nu
+        s = O.state()
+        assert np.array_equal(s["theta"], R["theta"][it]), f"{name}: oracle theta != reference theta at sweep {it}"
+        assert np.array_equal(s["beta"], R["beta"][..., it]) and np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, :, it])
+    out = dict(n=n, m=m, C=C, H=H, iters=iters, ls=ls, os=os_, kernel=kernel, y=y, theta_in=theta_in, beta_prior_sds=bps, theta_prior_sds=tps,
+               thr0=thr0, beta0=beta0, f0=f0, fstar0=fstar0, ref_theta=R["theta"], ref_beta=R["beta"], ref_threshold=R["threshold"], ref_ll=R["ll"],
+               ref_f=R["f"], ref_fstar_last=R["fstar"][..., -1], **rec)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "ll", R["ll"])
+
+
 def leaf_case():
     rng = np.random.default_rng(42)
     x1, x2, sds = rng.standard_normal(17) * 2, rng.standard_normal(9) * 2, np.array([3.0, 2.5, 0.7])
@@ -106,3 +157,5 @@ if __name__ == "__main__":
     leaf_case()
     sweep_case("sweep_ordinal_c4", n=48, m=8, C=4, seed=11, iters=3, missing=0.1)
     sweep_case("sweep_binary_c2", n=36, m=6, C=2, seed=23, iters=3, missing=0.2, empty_item=4, tps_sd=0.6)
+    panel_case("panel_rdm_h3", n=30, m=5, C=4, H=3, seed=51, iters=2, ls=0.05, kernel="Matern")
+    panel_case("panel_gp_h3", n=30, m=5, C=3, H=3, seed=61, iters=2, ls=2.5, kernel="Matern")

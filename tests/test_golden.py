@@ -152,3 +152,102 @@ def test_cuda_replays_reference_sweeps(name):
     S.set_state(theta=G["theta_in"], beta=G["beta0"], f=G["f0"], thresholds=G["thr0"], fstar=G["fstar0"])  # set_state clamps theta (src/gpirtMCMC.cpp:133)
     for it, st, ll, ev in replay(G, S, "cuda"):
         check_against_reference(G, it, st, ll, ev, it == int(G["iters"]) - 1)
+
+
+# ---- horizon > 1: the reference's own H = 3 runs (RDM and GP-over-time regimes), streams recorded per session --------------------
+PANELS = ["panel_rdm_h3", "panel_gp_h3"]
+
+
+def replay_panel(G, P, kind):
+    """P: oracle Panel (kind 'orc') or gpirt_b200.Panel (kind 'cuda'); yields (sweep, state, ll, theta evals) after each replayed sweep."""
+    H, rdm = int(G["H"]), float(G["ls"]) <= 0.1
+    for it in range(int(G["iters"])):
+        k = lambda blk, h: (G[f"z_{blk}_{it}_{h}"], G.get(f"u_{blk}_{it}_{h}"))
+        if kind == "orc":
+            for S in P.S:
+                S.compute_mu()
+                assert S.update_cholesky() == 0
+            for h, S in enumerate(P.S):
+                z, u = k("f", h)
+                S.draw_f(orc.supplied(u=u), nu=np.asfortranarray(S.L() @ z))
+            for h, S in enumerate(P.S):
+                assert S.draw_fstar(orc.supplied(z=k("fstar", h)[0])) == 0
+            if rdm:
+                P.draw_theta([orc.supplied(z=k("theta", h)[0], u=k("theta", h)[1]) for h in range(H)])
+                ev = np.stack([S.diag("theta")[0] for S in P.S])
+            else:
+                P.draw_theta(orc.supplied(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"]))
+                ev = P.S[0].diag("theta")[0]
+            for S in P.S:
+                S.gather_f()
+            for h, S in enumerate(P.S):
+                S.draw_beta(orc.supplied(z=k("beta", h)[0], u=k("beta", h)[1]))
+            for S in P.S:
+                S.compute_mu()
+                assert S.update_cholesky() == 0
+            for h, S in enumerate(P.S):
+                S.draw_threshold(orc.supplied(z=k("thr", h)[0], u=k("thr", h)[1]))
+            st = P.state()
+            st["thresholds"] = st.pop("thr")
+            yield it, st, P.total_ll(), ev
+        else:
+            for h, S in enumerate(P.S):
+                z, u = k("f", h)
+                S.draw_f(z=z, u=u)
+            for h, S in enumerate(P.S):
+                S.draw_fstar(z=k("fstar", h)[0])
+            if rdm:
+                P.draw_theta(z=[k("theta", h)[0] for h in range(H)], u=[k("theta", h)[1] for h in range(H)])
+            else:
+                P.draw_theta(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"])
+            ev = P.diag_theta()[0]
+            for S in P.S:
+                S.gather_f()
+            for h, S in enumerate(P.S):
+                S.draw_beta(z=k("beta", h)[0], u=k("beta", h)[1])
+            for S in P.S:
+                S.update_cholesky_cache()
+            for h, S in enumerate(P.S):
+                S.draw_threshold(z=k("thr", h)[0], u=k("thr", h)[1])
+            ll = sum(S.ll_bar()[1] for S in P.S)
+            yield it, P.get_state(fstar=True), ll, ev
+
+
+def check_panel(G, it, st, ll, ev, last):
+    H, rdm = int(G["H"]), float(G["ls"]) <= 0.1
+    assert np.array_equal(st["theta"], G["ref_theta"][it]), f"sweep {it}: theta differs from the reference's draw"
+    assert rel(st["beta"], G["ref_beta"][..., it]) < 1e-9 and rel(st["thresholds"], G["ref_threshold"][..., it]) < 1e-9
+    for h in range(H):
+        assert colrel(st["f"][:, :, h], G["ref_f"][:, :, h, it]) < 4e-6
+        if last:
+            assert colrel(st["fstar"][:, :, h], G["ref_fstar_last"][:, :, h]) < 4e-6
+    assert abs(ll - G["ref_ll"][it]) <= 1e-7 * abs(G["ref_ll"][it])
+    if rdm:
+        nu = np.stack([G[f"nu_theta_{it}_{h}"] for h in range(H)])
+    else:
+        nu = G[f"nu_theta_{it}"]
+    assert np.array_equal(np.where(nu > 0, ev, 0), nu), f"sweep {it}: the theta step made a different number of proposals"
+
+
+@pytest.mark.parametrize("name", PANELS)
+def test_oracle_panel_replays_reference_horizon_3_sweeps(name):
+    G = load(name)
+    O = orc.Panel(G["y"], int(G["C"]), G["beta_prior_sds"], G["theta_prior_sds"], theta_os=float(G["os"]), theta_ls=float(G["ls"]), KERNEL=str(G["kernel"]))
+    O.set_state(theta=np.clip(G["theta_in"], -5, 5), beta=G["beta0"], f=G["f0"], thr=G["thr0"], fstar=G["fstar0"])
+    for it, st, ll, ev in replay_panel(G, O, "orc"):
+        check_panel(G, it, st, ll, ev, it == int(G["iters"]) - 1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", PANELS)
+def test_cuda_panel_replays_reference_horizon_3_sweeps(name):
+    import gpirt_b200 as g
+
+    G = load(name)
+    n, m, C, H = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"])
+    P = g.Panel(n, m, C, H, theta_os=float(G["os"]), theta_ls=float(G["ls"]), KERNEL=str(G["kernel"]))
+    P.set_data(G["y"])
+    P.set_priors(G["beta_prior_sds"], G["theta_prior_sds"])
+    P.set_state(theta=G["theta_in"], beta=G["beta0"], f=G["f0"], thresholds=G["thr0"], fstar=G["fstar0"])
+    for it, st, ll, ev in replay_panel(G, P, "cuda"):
+        check_panel(G, it, st, ll, ev, it == int(G["iters"]) - 1)

@@ -215,3 +215,34 @@ def test_r_shim_recover_fstar_and_error_path():
     # a library error becomes Rcpp::stop(message) -> an R error; here a C++ exception carrying gpirt_last_error()
     rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(Ccat), p(f), p(y), p(th), p(beta2), p(P["thr0"]), p(bpm), p(bps), 1, p(out))
     assert rc == 1 and b"constant_IRF" in L.shim_last_error()
+
+
+def test_r_shim_gpirtMCMC_at_horizon_2():
+    """The shim hands cubes with H slices through unchanged: dynamic GPIRT (GP over time) through the R entry point."""
+    import ctypes as C
+
+    import gpirt_b200 as g
+
+    L = _rshim()
+    n, m, Ccat, H, sample = 40, 7, 3, 2, 3
+    Ps = [make_problem(n, m, Ccat, seed=70 + h) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    th0 = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1))
+    thr = np.asfortranarray(np.stack([Ps[0]["thr0"]] * H, axis=2))
+    rng = np.random.default_rng(3)
+    z = rng.standard_normal(H * (3 * m + n * m))
+    bpm, bps, tpm, tps = np.zeros((3, m), order="F"), Ps[0]["beta_prior_sds"], np.zeros((2, n), order="F"), np.zeros((2, n), order="F")
+    out = dict(theta=np.zeros((sample, n, H), order="F"), beta=np.zeros((3, m, H, sample), order="F"), thr=np.zeros((m, Ccat + 1, H, sample), order="F"),
+               ll=np.zeros(sample))
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    u64 = C.c_uint64
+    rc = L.shim_gpirtMCMC(u64(n), u64(m), u64(H), u64(Ccat), p(y), p(th0), sample, 0, 1, p(bpm), p(bps), p(tpm), p(tps), C.c_double(1.0), C.c_double(1.5),
+                          b"RBF", p(thr), 0, p(z), u64(z.size), C.c_double(0.25), p(out["theta"]), p(out["beta"]), p(out["thr"]), p(out["ll"]), None, None)
+    assert rc == 0, L.shim_last_error().decode()
+    beta0 = np.asfortranarray(np.stack([bpm + bps * z[h * 3 * m:(h + 1) * 3 * m].reshape(m, 3).T for h in range(H)], axis=2))
+    z0 = np.asfortranarray(z[H * 3 * m:].reshape(H, m, n).transpose(2, 1, 0))
+    ref = g.gpirtMCMC(y, sample, 0, THIN=1, CHAIN=1, beta_prior_means=bpm, beta_prior_sds=bps, theta_prior_sds=tps, theta_os=1.0, theta_ls=1.5, KERNEL="RBF",
+                      theta_init=th0, thresholds=thr, SEED=int(0.25 * 4294967296.0), beta_init=beta0, f_init_z=z0)[0]
+    assert np.array_equal(out["theta"], ref["theta"]) and np.array_equal(out["ll"], ref["ll"])
+    for s in range(sample):
+        assert np.array_equal(out["beta"][..., s], ref["beta"][s]) and np.array_equal(out["thr"][..., s], ref["threshold"][s])
