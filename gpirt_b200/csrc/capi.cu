@@ -269,6 +269,12 @@ int gpirt_set_solver(gpirt_sampler* h, int solver) {
     return GPIRT_OK;
 }
 
+int gpirt_debug_theta_threads(int threads) {
+    if (threads != 0 && threads != 256 && threads != 1024) return fail(GPIRT_ERR_INVALID, "theta threads %d: 0 (automatic), 256 or 1024", threads);
+    g_theta_threads = threads;
+    return GPIRT_OK;
+}
+
 int gpirt_set_screen(gpirt_sampler* h, int on) {
     CHECK_H(h);
     h->screen = on != 0;
@@ -831,9 +837,11 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double*
     v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os; v.key = h->key();
     v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
     TRY(stage_streams(h, s, h->n, 1, &v.z, &v.z_stride, &v.us));
-    // Every term the step can ask for is a function of (grid point, item, category) only: when the respondents of this
-    // rank would evaluate more terms than the table holds (about 8 evaluations each), build the table once instead.
-    const double table_cost = (double)NGRID * (1.4 * h->C - 1.0), direct_cost = (double)h->n_local * 8.0 * 2.4;
+    // Every term the step can ask for is a function of (grid point, item, category) only: unless this rank has very few respondents, build
+    // the table of all NGRID x C terms per item once per sweep instead of evaluating ~12 terms per (respondent, item) on the fly. Measured
+    // on B200 (profiles/r01_scaling.txt): the table kernel makes ~190 G terms/s (coalesced, every SM busy), the on-the-fly path ~21 G terms/s
+    // (one CTA per respondent, gathers across the f* chunks, two Phi and a log per term) -> a term costs ~9x more on the fly.
+    const double table_cost = (double)NGRID * h->C, direct_cost = (double)h->n_local * 12.0 * 9.0;
     const size_t table_bytes = (size_t)NGRID * h->m_total * h->C * 8;
     v.table = nullptr;
     if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {

@@ -319,6 +319,7 @@ namespace gpirt {
 // draw_theta: one CTA per respondent. The f* table is grid-row-major, so the row a proposal lands on
 // is one contiguous run of m doubles per shard chunk (the reference gathers it with stride N).
 constexpr int THETA_THREADS = 256;
+int g_theta_threads = 0;  // 0: by the number of local respondents; 256 / 1024: forced (tests: both give the same bits)
 
 __global__ void __launch_bounds__(128) k_theta_table(ThetaView v, double* __restrict__ table) {
     const int J = blockIdx.x * 128 + threadIdx.x;
@@ -346,8 +347,15 @@ cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* tabl
     return cudaGetLastError();
 }
 
-__global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
-    __shared__ double s_part[THETA_THREADS / 32];
+// T threads per respondent: 256 when there are respondents enough to fill the GPU, 1024 for a rank with few of them (item-sharded runs:
+// n / world respondents against m * world items). Both sum an evaluation in the SAME order — 1024 virtual lanes (lane l takes items l,
+// l + 1024, ...), lanes t, t+256, t+512, t+768 combined as (S_t + S_t+256) + (S_t+512 + S_t+768), then the 8-warp block sum — so a chain
+// does not depend on which one ran (bit-identical for any world size).
+template <int T>
+__global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
+    static_assert(T == 256 || T == 1024, "virtual-lane scheme");
+    __shared__ double s_part[8];
+    __shared__ double s_lane[T == 1024 ? 1024 : 1];
     const int il = blockIdx.x;
     if (il >= v.n_local) return;
     const int i = v.resp0 + il;
@@ -369,16 +377,35 @@ __global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
     auto loglik = [&](double th) -> double {
         const int idx = grid_index(th);
         const double ts = grid_value(idx);
-        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-        int J = tid;
-        for (; J + 3 * THETA_THREADS < m_total; J += 4 * THETA_THREADS) {
-            a0 += term(J, idx, ts);
-            a1 += term(J + THETA_THREADS, idx, ts);
-            a2 += term(J + 2 * THETA_THREADS, idx, ts);
-            a3 += term(J + 3 * THETA_THREADS, idx, ts);
+        if (T == 256) {
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+            int J = tid;
+            for (; J + 768 < m_total; J += 1024) {
+                a0 += term(J, idx, ts);
+                a1 += term(J + 256, idx, ts);
+                a2 += term(J + 512, idx, ts);
+                a3 += term(J + 768, idx, ts);
+            }
+            if (J < m_total) a0 += term(J, idx, ts);          // the ragged last group: every item still goes to its own lane
+            if (J + 256 < m_total) a1 += term(J + 256, idx, ts);
+            if (J + 512 < m_total) a2 += term(J + 512, idx, ts);
+            return block_sum<8>((a0 + a1) + (a2 + a3), s_part);
+        } else {
+            double a = 0.0;
+            for (int J = tid; J < m_total; J += 1024) a += term(J, idx, ts);
+            __syncthreads();  // previous readers of s_lane / s_part are done
+            s_lane[tid] = a;
+            __syncthreads();
+            if (tid < 256) {
+                double w = warp_sum((s_lane[tid] + s_lane[tid + 256]) + (s_lane[tid + 512] + s_lane[tid + 768]));
+                if ((tid & 31) == 0) s_part[tid >> 5] = w;
+            }
+            __syncthreads();
+            double t = 0.0;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) t += s_part[w];
+            return t;
         }
-        for (; J < m_total; J += THETA_THREADS) a0 += term(J, idx, ts);
-        return block_sum<THETA_THREADS / 32>((a0 + a1) + (a2 + a3), s_part);
     };
 
     double Li;
@@ -423,7 +450,10 @@ __global__ void __launch_bounds__(THETA_THREADS) k_ess_theta(ThetaView v) {
 
 cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     if (v.n_local <= 0) return cudaSuccess;
-    k_ess_theta<<<v.n_local, THETA_THREADS, 0, st>>>(v);
+    // few respondents on this rank (an item shard): four times the threads per respondent keep the SMs' memory pipes busy
+    const bool wide = g_theta_threads ? g_theta_threads == 1024 : v.n_local <= 600;
+    if (wide) k_ess_theta<1024><<<v.n_local, 1024, 0, st>>>(v);
+    else k_ess_theta<256><<<v.n_local, 256, 0, st>>>(v);
     ++g_kernel_launches;
     return cudaGetLastError();
 }

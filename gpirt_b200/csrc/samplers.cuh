@@ -100,6 +100,7 @@ cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, i
 cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v);
 cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v);
 cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v);
+extern int g_theta_threads;
 // table[(idx*m_total + J)*C + c-1] = log(Phi(tau_c - g) - Phi(tau_{c-1} - g) + 1e-6), g = f*(idx,J) + mu*(idx,J): every term the theta
 // step can ask for, computed once per sweep instead of once per (respondent, proposal)
 cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* table);

@@ -151,6 +151,9 @@ int gpirt_set_overlap(gpirt_sampler* h, int on);
  * when the accept test ll' > log_y is closer than that bound. Decisions, states and stream consumption are identical to 0 (every
  * evaluation in fp64). gpirt_get_exact_evals: per unit, how many evaluations of the last call of `block` ran in fp64. */
 int gpirt_set_screen(gpirt_sampler* h, int on);
+/* Threads per respondent of the theta kernel: 0 = by the number of local respondents (256, or 1024 on a rank with few respondents), or forced;
+ * process-wide. Both sum in the same order, so the choice never changes a chain (tests). */
+int gpirt_debug_theta_threads(int threads);
 int gpirt_get_exact_evals(gpirt_sampler* h, int block, int32_t* out);
 int gpirt_get_diag(gpirt_sampler* h, int block, int32_t* evals, double* margin); /* per unit: 1+proposals, min |ll'-log_y| */
 int gpirt_sync(gpirt_sampler* h);                            /* wait for queued work; surfaces deferred errors */

@@ -373,3 +373,33 @@ def test_full_size_chain_is_deterministic_across_overlap_and_screening():
         S.close()
     for k in (1, 2):
         assert out[k][0] == out[0][0] and np.array_equal(out[k][1], out[0][1]) and np.array_equal(out[k][2], out[0][2])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,m,C", [(300, 1500, 5), (150, 2100, 3), (64, 1024, 2), (80, 37, 4)])  # ragged and exact multiples of the 1024 virtual lanes
+def test_theta_kernel_gives_the_same_bits_with_256_and_1024_threads_per_respondent(n, m, C):
+    """The theta step runs 256 threads per respondent, or 1024 on a rank with few respondents (item shards); both sum an evaluation in the same
+    order, so a chain must not depend on the choice — with and without the per-sweep term table."""
+    import gpirt_b200 as g
+    from gpirt_b200 import _lib
+
+    P = make_problem(n, m, C, seed=13)
+    states = {}
+    try:
+        for threads in (256, 1024):
+            _lib.check(_lib.lib().gpirt_debug_theta_threads(threads))
+            S = g.Sampler(n, m, C, seed=5)
+            S.set_data(P["y"])
+            S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+            S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+            S.init_draw(draw_beta=False, draw_f=True)
+            S.sweep(3)
+            st = S.get_state(fstar=True)
+            st["ll"], st["ev"], st["mg"] = S.total_ll(), S.diag("theta")[0], S.diag("theta")[1]
+            states[threads] = st
+    finally:
+        _lib.lib().gpirt_debug_theta_threads(0)
+    a, b = states[256], states[1024]
+    for k in ("theta", "beta", "thresholds", "f", "fstar", "ev", "mg"):
+        assert np.array_equal(a[k], b[k]), k
+    assert a["ll"] == b["ll"]
