@@ -500,18 +500,39 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
     constexpr int NB = CHOL_NB;
     cudaError_t e0 = cudaMemsetAsync(readers_ws, 0, chol_ws_ints(n) * sizeof(int), st);
     if (e0 != cudaSuccess) return e0;
-    for (int k0 = 0; k0 < n; k0 += NB) {
-        const int kb = (n - k0 < NB) ? n - k0 : NB;
-        double* Akk = A + (size_t)k0 * ld + k0;
-        const int rows = n - k0 - kb;
-        k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0, readers_ws + k0 / NB);
-        ++g_kernel_launches;
-        if (rows > 0) {
-            double* A21 = Akk + kb;
+    // Two levels of blocking for large matrices: 64-column panels (the serial part) inside OB-column outer blocks. After a panel only the
+    // rest of its outer block is updated (a narrow K = 64 product); the trailing matrix takes one K = OB update per outer block, where the
+    // DMMA GEMM runs near its peak. At n = 2000 the K = 64 updates are latency-bound launches either way (no gain, profiles/
+    // r01_gemm_tiles.txt: OB = NB there); at n = 10 000 (config C4) the flops dominate and the K = 64 updates reach only ~16 TFLOP/s.
+    static const int ob_env = getenv("GPIRT_CHOL_OB") ? atoi(getenv("GPIRT_CHOL_OB")) : 0;
+    const int OB = ob_env > 0 ? ob_env : (n >= 4096 ? 256 : NB);
+    for (int o0 = 0; o0 < n; o0 += OB) {
+        const int ob = (n - o0 < OB) ? n - o0 : OB;
+        for (int k0 = o0; k0 < o0 + ob; k0 += NB) {
+            const int kb = (n - k0 < NB) ? n - k0 : NB;
+            double* Akk = A + (size_t)k0 * ld + k0;
+            const int rows = n - k0 - kb;
+            k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0, readers_ws + k0 / NB);
+            ++g_kernel_launches;
+            const int wcols = (OB == NB) ? rows : o0 + ob - (k0 + kb);  // columns updated now: everything (one level) or the rest of the outer block
+            if (rows > 0 && wcols > 0) {
+                double* A21 = Akk + kb;
+                GemmArgs g{};
+                g.M = rows; g.N = wcols; g.K = kb;
+                g.A = A21; g.lda = ld; g.B = A21; g.ldb = ld;
+                g.C = A + (size_t)(k0 + kb) * ld + (k0 + kb); g.ldc = ld;
+                g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
+                cudaError_t e = gemm_f64(st, false, true, g);
+                if (e != cudaSuccess) return e;
+            }
+        }
+        const int rows_t = n - o0 - ob;
+        if (OB != NB && rows_t > 0) {
+            double* P = A + (size_t)o0 * ld + (o0 + ob);  // rows below the outer block, its ob columns
             GemmArgs g{};
-            g.M = rows; g.N = rows; g.K = kb;
-            g.A = A21; g.lda = ld; g.B = A21; g.ldb = ld;
-            g.C = A + (size_t)(k0 + kb) * ld + (k0 + kb); g.ldc = ld;
+            g.M = rows_t; g.N = rows_t; g.K = ob;
+            g.A = P; g.lda = ld; g.B = P; g.ldb = ld;
+            g.C = A + (size_t)(o0 + ob) * ld + (o0 + ob); g.ldc = ld;
             g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
             cudaError_t e = gemm_f64(st, false, true, g);
             if (e != cudaSuccess) return e;

@@ -403,3 +403,21 @@ def test_theta_kernel_gives_the_same_bits_with_256_and_1024_threads_per_responde
     for k in ("theta", "beta", "thresholds", "f", "fstar", "ev", "mg"):
         assert np.array_equal(a[k], b[k]), k
     assert a["ll"] == b["ll"]
+
+
+@pytest.mark.gpu
+def test_chol_large_matrix_two_level_blocking_backward_error():
+    """n >= 4096 switches the blocked Cholesky to two levels (K = 256 trailing updates, config C4 has n = 10 000): backward error and agreement
+    with LAPACK on a well-conditioned covariance."""
+    import gpirt_b200 as g
+
+    n = 4200  # not a multiple of 64 or 256
+    rng = np.random.default_rng(4)
+    th = np.clip(rng.standard_normal(n) * 1.5, -5, 5)
+    A = g.K(th, th, np.array([0.8, 0.5, 0.1])) + 0.5 * np.eye(n)
+    L = g.chol(A)
+    assert np.all(np.triu(L, 1) == 0)
+    R = L @ L.T - A
+    assert np.max(np.abs(R)) <= 2e-14 * np.max(np.abs(A)) * 8
+    Lref = np.linalg.cholesky(A)
+    assert np.max(np.abs(L - Lref)) < 1e-11
