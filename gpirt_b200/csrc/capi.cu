@@ -70,11 +70,20 @@ static int wait_L(gpirt_sampler* h) {
     }
     return GPIRT_OK;
 }
+static int wait_W(gpirt_sampler* h) {
+    if (h->pending_W) {
+        SEC(h, "wait_W", CU(cudaStreamWaitEvent(h->stream, h->ev_W, 0)));  // recorded after ev_L on the same stream
+        h->pending_W = false;
+        h->pending_L = false;
+    }
+    return GPIRT_OK;
+}
 static int wait_shared(gpirt_sampler* h) {
     if (h->pending_shared) {
-        SEC(h, "wait_shared", CU(cudaStreamWaitEvent(h->stream, h->ev_shared, 0)));  // recorded after ev_L on the same stream
+        SEC(h, "wait_shared", CU(cudaStreamWaitEvent(h->stream, h->ev_shared, 0)));  // recorded after ev_L and ev_W on the same stream
         h->pending_shared = false;
         h->pending_L = false;
+        h->pending_W = false;
     }
     return GPIRT_OK;
 }
@@ -179,6 +188,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_W, cudaEventDisableTiming));
     }
     const size_t mt = (size_t)h->world * h->m_chunk;
     // one device allocation for everything a handle owns for life (create + destroy cost one cudaMalloc / cudaFree, which is what an
@@ -243,6 +253,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_L) cudaEventDestroy(h->ev_L);
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
+    if (h->ev_W) cudaEventDestroy(h->ev_W);
     if (h->side) cudaStreamDestroy(h->side);
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
         if (p) cudaFree(p);
@@ -737,7 +748,7 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
 
 // The part of draw_fstar shared by all items (src/draw-fstar.cpp:26-36): k*, tmp = L^-1 k*, K_post = K** - tmp^T tmp + 1e-6 I,
 // L_post = chol(K_post), and W = L^-T tmp = K^-1 k*. Depends on theta only, so a sweep runs it on the side stream.
-static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
+static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_after_W = nullptr) {
     const int n = h->n, N = NGRID;
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
     const double* tmp = h->W;  // L^-1 k*
@@ -749,6 +760,13 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
         g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
         SEC_ST(h, st, "gemm_tmp", CU(gemm_f64(st, false, false, g)));
         tmp = h->W2;
+        // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W. Formed BEFORE K_post and its
+        // Cholesky: the consumer's first product (F^T W) then starts while the latency-bound chol(K_post) is still running.
+        GemmArgs w{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
+        w.M = n; w.N = N; w.K = n; w.A = h->Linv; w.lda = h->ldn; w.B = h->W2; w.ldb = h->ldn; w.C = h->W; w.ldc = h->ldn;
+        w.alpha = 1.0; w.beta = 0.0; w.a_upper = 1;
+        SEC_ST(h, st, "gemm_W", CU(gemm_f64(st, true, false, w)));
+        if (ev_after_W) CU(cudaEventRecord(ev_after_W, st));
     } else {
         SEC_ST(h, st, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
     }
@@ -763,14 +781,9 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st) {
     ++g_kernel_launches;
     CU(cudaGetLastError());
     SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws)));
-    // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W
-    if (h->solver == 1) {
-        GemmArgs g{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
-        g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W2; g.ldb = h->ldn; g.C = h->W; g.ldc = h->ldn;
-        g.alpha = 1.0; g.beta = 0.0; g.a_upper = 1;
-        SEC_ST(h, st, "gemm_W", CU(gemm_f64(st, true, false, g)));
-    } else {
+    if (h->solver != 1) {  // substitution overwrites tmp in place, so it comes after K_post
         SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
+        if (ev_after_W) CU(cudaEventRecord(ev_after_W, st));
     }
     h->shared_valid = true;
     return GPIRT_OK;
@@ -787,7 +800,8 @@ static int launch_theta_chain(gpirt_sampler* h) {
     TRY(do_update_cholesky(h, h->side));
     CU(cudaEventRecord(h->ev_L, h->side));
     h->pending_L = true;
-    TRY(prep_fstar_shared(h, h->side));
+    TRY(prep_fstar_shared(h, h->side, h->ev_W));
+    h->pending_W = true;
     CU(cudaEventRecord(h->ev_shared, h->side));
     h->pending_shared = true;
     return GPIRT_OK;
@@ -799,10 +813,10 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
         TRY(quiesce(h));
         TRY(prep_fstar_shared(h, h->stream));
     }
-    TRY(wait_shared(h));
+    TRY(wait_W(h));  // W only; L_post is waited for where it is used
     cudaStream_t st = h->stream;
     const int n = h->n, N = NGRID;
-    if (h->m_local == 0) return GPIRT_OK;
+    if (h->m_local == 0) return quiesce(h);
     double* chunk = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk;
     {
         GemmArgs g{};
@@ -817,6 +831,7 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     } else {
         SEC(h, "gen_Z", CU(launch_gen_normals(st, h->zbuf, h->ldz, N, h->m_local, h->key(), ST_FSTAR_Z, h->item0)));
     }
+    TRY(wait_shared(h));
     {   // + (L_post Z*)^T : op(A) = Z*^T, op(B) = L_post^T (upper triangular)
         GemmArgs g{};
         g.M = h->m_local; g.N = N; g.K = N; g.A = h->zbuf; g.lda = h->ldz; g.B = h->Kpost; g.ldb = h->ldN; g.C = chunk; g.ldc = h->ld_chunk;

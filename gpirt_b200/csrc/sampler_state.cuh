@@ -44,10 +44,10 @@ struct gpirt_sampler {
     // stream as soon as the new theta is committed, under the item kernels of the main stream (draw_beta, draw_threshold,
     // ll, next draw_f): it is a long chain of small launches that cannot fill the GPU on its own.
     cudaStream_t side = nullptr;
-    cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_shared = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_W = nullptr, ev_shared = nullptr;
     bool overlap = true;           // gpirt_set_overlap; profiling forces the serial order
     bool shared_valid = false;     // W / Kpost hold the draw_fstar terms of the current theta
-    bool pending_L = false, pending_shared = false;  // the main stream has not yet waited for ev_L / ev_shared
+    bool pending_L = false, pending_W = false, pending_shared = false;  // the main stream has not yet waited for ev_L / ev_W / ev_shared
 
     int8_t *y_im = nullptr, *y_rm = nullptr;
     double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;
