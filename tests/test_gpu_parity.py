@@ -421,3 +421,39 @@ def test_chol_large_matrix_two_level_blocking_backward_error():
     assert np.max(np.abs(R)) <= 2e-14 * np.max(np.abs(A)) * 8
     Lref = np.linalg.cholesky(A)
     assert np.max(np.abs(L - Lref)) < 1e-11
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged")])
+def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_streams(n, m, C, name):
+    """Whole sweeps (gpirt_sweep: overlapped schedule, fp32 screening, block inverse) against the oracle's sweep on the SAME Philox streams, at the
+    shapes of BASELINE.json's configs 1 and 2 (synthetic responses; the .rda front-end is out of scope) with the reference's default priors
+    (beta_prior_sds = 3: kappa(K) ~ 1e10, so f / f* are compared norm-wise per item and theta exactly)."""
+    import gpirt_b200 as g
+
+    P = make_problem(n, m, C, seed=77, missing=0.06)
+    seed, chain, sweeps = 2024, 1, 2
+    S = g.Sampler(n, m, C, seed=seed, chain=chain)
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    O = orc.Sampler(P["y"], C, P["beta_prior_sds"], P["theta_prior_sds"])
+    rng = np.random.default_rng(1)
+    O.set_state(theta=P["theta0"], beta=P["beta0"], thr=P["thr0"])
+    O.compute_mu()  # the oracle's sweep, like the reference's loop body, starts from mu and L of the current state (src/gpirtMCMC.cpp:136,308-314)
+    assert O.update_cholesky() == 0
+    f0 = np.asfortranarray(O.L() @ rng.standard_normal((n, m)))  # f0_j = L z_j as the reference initialises it (:158-162); white noise is not a GP draw
+    S.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thresholds=P["thr0"])
+    O.set_state(f=f0)
+    for it in range(sweeps):
+        S.set_iter(it)
+        S.sweep(1)
+        assert O.sweep(orc.philox(seed, chain, it)) == 0
+        a, b = S.get_state(fstar=True), O.state()
+        for blk in ("f", "theta", "beta", "thr"):
+            assert np.array_equal(S.diag(blk)[0], O.diag(blk)[0]), f"sweep {it}: block {blk} made a different number of proposals"
+        assert np.array_equal(a["theta"], b["theta"])
+        assert np.max(np.abs(a["beta"] - b["beta"])) < 1e-9 and np.max(np.abs(a["thresholds"][:, 1:-1] - b["thr"][:, 1:-1])) < 1e-9
+        colrel = lambda x, y: float(np.max(np.max(np.abs(x - y), axis=0) / np.maximum(1.0, np.max(np.abs(y), axis=0))))
+        # f* also extrapolates to |theta*| = 5 from respondents inside about +-2.7 (values ~100): K^-1 f is kappa-limited there (SURVEY 7)
+        assert colrel(a["f"], b["f"]) < 4e-6 and colrel(a["fstar"], b["fstar"]) < 3e-5
+        assert abs(S.total_ll() - O.total_ll()) <= 1e-7 * abs(O.total_ll())
