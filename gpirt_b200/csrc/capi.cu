@@ -189,6 +189,15 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_W, cudaEventDisableTiming));
+        // milestones of chol(K): rows 50 %, 75 %, 87.5 % and 100 % (multiples of the panel width), see do_draw_f
+        int prev = 0;
+        for (double frac : {0.5, 0.75, 0.875, 1.0}) {
+            int r = frac >= 1.0 ? h->n : ((int)(h->n * frac) / CHOL_NB) * CHOL_NB;
+            if (r <= prev) continue;
+            CU(cudaEventCreateWithFlags(&h->L_rows.ev[h->L_rows.count], cudaEventDisableTiming));
+            h->L_rows.rows[h->L_rows.count++] = r;
+            prev = r;
+        }
     }
     const size_t mt = (size_t)h->world * h->m_chunk;
     // one device allocation for everything a handle owns for life (create + destroy cost one cudaMalloc / cudaFree, which is what an
@@ -254,6 +263,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_L) cudaEventDestroy(h->ev_L);
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
     if (h->ev_W) cudaEventDestroy(h->ev_W);
+    for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
         if (p) cudaFree(p);
@@ -702,7 +712,9 @@ static int need_data(gpirt_sampler* h) {
 
 static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
-    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws)));
+    const bool marks = st == h->side && h->L_rows.count > 0;
+    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws, marks ? &h->L_rows : nullptr)));
+    h->pending_rows = marks;
     h->chol_valid = true;
     h->shared_valid = false;
     return GPIRT_OK;
@@ -714,7 +726,11 @@ static int do_update_cholesky(gpirt_sampler* h) {
 
 static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
     if (!h->chol_valid) TRY(do_update_cholesky(h));  // the reference refactorises here (src/draw-f.cpp:59); same theta, same L
-    TRY(wait_L(h));
+    // chol(K) still in flight on the side stream: nu = L Z is launched in row slices, each as soon as its rows of L are final (row block i of
+    // L is complete after panel i), so most of the product runs UNDER the factorisation instead of after it. Same tiles, same k ranges:
+    // the slices give the bits of the single launch.
+    const bool sliced = h->pending_L && h->pending_rows && !(s && s->nu);
+    if (!sliced) TRY(wait_L(h));
     cudaStream_t st = h->stream;
     ItemView v = item_view(h);
     const double* dz; long long zs;
@@ -734,13 +750,21 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
                 SEC(h, "gen_Z", CU(launch_gen_normals(st, h->zbuf, h->ldz, h->n, h->m_local, h->key(), ST_F_Z, h->item0)));
             }
             // nu = L * Z for every local item at once (rmvnorm_threadsafe per item, src/mvnormal.h:17-24)
-            GemmArgs g{};
-            g.M = h->n; g.N = h->m_local; g.K = h->n;
-            g.A = h->L; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->nu; g.ldc = h->ldn;
-            g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
-            SEC(h, "gemm_LZ", CU(gemm_f64(st, false, false, g)));
+            int r0 = 0;
+            const int n_slices = sliced ? h->L_rows.count : 1;
+            for (int c = 0; c < n_slices; ++c) {
+                const int r1 = sliced ? h->L_rows.rows[c] : h->n;
+                if (sliced) CU(cudaStreamWaitEvent(st, h->L_rows.ev[c], 0));
+                GemmArgs g{};
+                g.M = r1 - r0; g.N = h->m_local; g.K = h->n; g.m_off = r0;
+                g.A = h->L + r0; g.lda = h->ldn; g.B = h->zbuf; g.ldb = h->ldz; g.C = h->nu + r0; g.ldc = h->ldn;
+                g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
+                SEC(h, "gemm_LZ", CU(gemm_f64(st, false, false, g)));
+                r0 = r1;
+            }
         }
     }
+    if (sliced) h->pending_rows = false;  // pending_L stays set: whoever needs ALL of chol's work (the zeroed upper triangle) still waits for ev_L
     v.evals = h->evals[GPIRT_BLOCK_F]; v.margin = h->margin[GPIRT_BLOCK_F]; v.exact_evals = h->exact[GPIRT_BLOCK_F];
     SEC(h, "ess_f", CU(launch_ess_items(st, IB_F, v)));
     return GPIRT_OK;

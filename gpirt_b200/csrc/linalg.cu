@@ -313,7 +313,8 @@ __global__ void __launch_bounds__(TILE_THREADS) k_chol_panel(double* __restrict_
 #pragma unroll
             for (int p = 0; p < 4; ++p) {
                 const int r = 4 * tr + p, c = 4 * tc + q;
-                if (r < kb && c <= r) A[(size_t)c * ld + r] = a[p][q];
+                if (r < kb && c < kb) A[(size_t)c * ld + r] = (c <= r) ? a[p][q] : 0.0;  // the block's upper part is zeroed here: consumers of leading rows
+                                                                                          // (CholMilestones) read the diagonal block before k_zero_upper runs
             }
         return;
     }
@@ -496,7 +497,8 @@ __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
     if (i < n && j < n && i < j) A[(size_t)j * ld + i] = 0.0;
 }
 
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws) {
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks) {
+    int next_mark = 0;
     constexpr int NB = CHOL_NB;
     cudaError_t e0 = cudaMemsetAsync(readers_ws, 0, chol_ws_ints(n) * sizeof(int), st);
     if (e0 != cudaSuccess) return e0;
@@ -514,6 +516,11 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
             const int rows = n - k0 - kb;
             k_chol_panel<<<1 + (rows + 63) / 64, TILE_THREADS, 0, st>>>(Akk, ld, kb, rows, info_dev, k0, readers_ws + k0 / NB);
             ++g_kernel_launches;
+            while (marks && next_mark < marks->count && marks->rows[next_mark] <= k0 + kb) {  // rows [0, k0 + kb) of L are final now
+                cudaError_t em = cudaEventRecord(marks->ev[next_mark], st);
+                if (em != cudaSuccess) return em;
+                ++next_mark;
+            }
             const int wcols = (OB == NB) ? rows : o0 + ob - (k0 + kb);  // columns updated now: everything (one level) or the rest of the outer block
             if (rows > 0 && wcols > 0) {
                 double* A21 = Akk + kb;

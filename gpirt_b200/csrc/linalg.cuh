@@ -19,7 +19,14 @@ cudaError_t build_K_time(cudaStream_t st, const double* x1, int n1, const double
 // *info_dev (device int, must be 0 on entry) receives the 1-based index of the first non-positive pivot.
 // readers_ws: chol_ws_ints(n) device ints of workspace (zeroed by the call; one arrival counter per panel).
 inline size_t chol_ws_ints(int n) { return (size_t)(n + CHOL_NB - 1) / CHOL_NB + 1; }
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws);
+// Optional milestones: ev[c] is recorded on st as soon as rows [0, rows[c]) of L are final (right after the panel kernel that ends at or
+// beyond rows[c]; rows ascending, the last one n), so a consumer of leading row blocks (nu = L Z) can start under the factorisation.
+struct CholMilestones {
+    int count = 0;
+    int rows[4] = {0, 0, 0, 0};
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+};
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);

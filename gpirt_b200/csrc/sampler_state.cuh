@@ -45,6 +45,8 @@ struct gpirt_sampler {
     // ll, next draw_f): it is a long chain of small launches that cannot fill the GPU on its own.
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_W = nullptr, ev_shared = nullptr;
+    gpirt::CholMilestones L_rows;  // leading row blocks of L signalled while chol(K) is still running on the side stream (nu = L Z starts under it)
+    bool pending_rows = false;
     bool overlap = true;           // gpirt_set_overlap; profiling forces the serial order
     bool shared_valid = false;     // W / Kpost hold the draw_fstar terms of the current theta
     bool pending_L = false, pending_W = false, pending_shared = false;  // the main stream has not yet waited for ev_L / ev_W / ev_shared
