@@ -189,9 +189,9 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_W, cudaEventDisableTiming));
-        // milestones of chol(K): rows 50 %, 75 %, 87.5 % and 100 % (multiples of the panel width), see do_draw_f
+        // milestones of chol(K): rows 50 %, 75 %, 87.5 %, 93.75 % and 100 % (multiples of the panel width), see do_draw_f
         int prev = 0;
-        for (double frac : {0.5, 0.75, 0.875, 1.0}) {
+        for (double frac : {0.5, 0.75, 0.875, 0.9375, 1.0}) {
             int r = frac >= 1.0 ? h->n : ((int)(h->n * frac) / CHOL_NB) * CHOL_NB;
             if (r <= prev) continue;
             CU(cudaEventCreateWithFlags(&h->L_rows.ev[h->L_rows.count], cudaEventDisableTiming));

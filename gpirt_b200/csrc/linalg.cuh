@@ -23,8 +23,8 @@ inline size_t chol_ws_ints(int n) { return (size_t)(n + CHOL_NB - 1) / CHOL_NB +
 // beyond rows[c]; rows ascending, the last one n), so a consumer of leading row blocks (nu = L Z) can start under the factorisation.
 struct CholMilestones {
     int count = 0;
-    int rows[4] = {0, 0, 0, 0};
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    int rows[6] = {0, 0, 0, 0, 0, 0};
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
