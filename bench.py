@@ -267,7 +267,7 @@ def ours(args):
         y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
         k = args.steps
         rates = []
-        for _ in range(3):  # wall clock on a shared host: the median of three calls is reported
+        for _ in range(5):  # wall clock on a shared host (set_data / create vary by several ms between calls): the median of five calls is reported
             t0 = time.perf_counter()
             res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=1, beta_prior_sds=P["beta_prior_sds"],
                                        theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104,
@@ -277,7 +277,7 @@ def ours(args):
         h2d = (y_host.nbytes + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
-                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 3 calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
+                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 5 calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
             r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)
@@ -293,7 +293,7 @@ def ours(args):
         y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
         k = args.steps
         rates = []
-        for _ in range(3):
+        for _ in range(5):
             barrier()
             t0 = time.perf_counter()
             res = gpirtMCMC_sharded(y_host, k, 0, THIN=1, rank=rank, world=world, device=local, beta_prior_sds=P["beta_prior_sds"],
@@ -307,7 +307,7 @@ def ours(args):
         h2d = world * (2.0 * y_host.nbytes / world + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = world * 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
-                       "what": f"gpirtMCMC_sharded(sample_iterations={k}) on {world} ranks, wall clock between barriers (max over ranks, median of 3 calls) incl. handle "
+                       "what": f"gpirtMCMC_sharded(sample_iterations={k}) on {world} ranks, wall clock between barriers (max over ranks, median of 5 calls) incl. handle "
                                "creation, each rank's partial fp64 y upload from pinned memory, initial draws, exchanges, kept draws read back on every rank; "
                                f"value = {world} C3-sized item blocks x sweeps per second, as `value`"}
     if rank == 0:

@@ -198,6 +198,14 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
             h->L_rows.rows[h->L_rows.count++] = r;
             prev = r;
         }
+        prev = 0;
+        for (double frac : {0.5, 0.75, 0.875, 0.9375, 1.0}) {
+            int r = frac >= 1.0 ? (int)NGRID : ((int)(NGRID * frac) / CHOL_NB) * CHOL_NB;
+            if (r <= prev) continue;
+            CU(cudaEventCreateWithFlags(&h->Lpost_rows.ev[h->Lpost_rows.count], cudaEventDisableTiming));
+            h->Lpost_rows.rows[h->Lpost_rows.count++] = r;
+            prev = r;
+        }
     }
     const size_t mt = (size_t)h->world * h->m_chunk;
     // one device allocation for everything a handle owns for life (create + destroy cost one cudaMalloc / cudaFree, which is what an
@@ -264,6 +272,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
     if (h->ev_W) cudaEventDestroy(h->ev_W);
     for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
+    for (int c = 0; c < h->Lpost_rows.count; ++c) cudaEventDestroy(h->Lpost_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
         if (p) cudaFree(p);
@@ -804,7 +813,9 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws)));
+    const bool post_marks = st == h->side && h->Lpost_rows.count > 0;
+    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws, post_marks ? &h->Lpost_rows : nullptr)));
+    h->pending_post_rows = post_marks;
     if (h->solver != 1) {  // substitution overwrites tmp in place, so it comes after K_post
         SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
         if (ev_after_W) CU(cudaEventRecord(ev_after_W, st));
@@ -855,13 +866,26 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
     } else {
         SEC(h, "gen_Z", CU(launch_gen_normals(st, h->zbuf, h->ldz, N, h->m_local, h->key(), ST_FSTAR_Z, h->item0)));
     }
-    TRY(wait_shared(h));
-    {   // + (L_post Z*)^T : op(A) = Z*^T, op(B) = L_post^T (upper triangular)
-        GemmArgs g{};
-        g.M = h->m_local; g.N = N; g.K = N; g.A = h->zbuf; g.lda = h->ldz; g.B = h->Kpost; g.ldb = h->ldN; g.C = chunk; g.ldc = h->ld_chunk;
-        g.alpha = 1.0; g.beta = 1.0; g.b_upper = 1;
-        SEC(h, "gemm_ZLpost", CU(gemm_f64(st, true, true, g)));
+    // + (L_post Z*)^T : op(A) = Z*^T, op(B) = L_post^T (upper triangular). Grid-point block c of the result needs rows [0, end of block c) of
+    // L_post only, which are final after panel c of chol(K_post): while that factorisation is still running on the side stream the product
+    // goes out in column slices behind its milestones (same tiles, same k ranges, same bits).
+    const bool post_sliced = h->pending_shared && h->pending_post_rows;
+    if (!post_sliced) TRY(wait_shared(h));
+    {
+        int c0 = 0;
+        const int n_slices = post_sliced ? h->Lpost_rows.count : 1;
+        for (int c = 0; c < n_slices; ++c) {
+            const int c1 = post_sliced ? h->Lpost_rows.rows[c] : N;
+            if (post_sliced) CU(cudaStreamWaitEvent(st, h->Lpost_rows.ev[c], 0));
+            GemmArgs g{};
+            g.M = h->m_local; g.N = c1 - c0; g.K = N; g.n_off = c0;
+            g.A = h->zbuf; g.lda = h->ldz; g.B = h->Kpost + c0; g.ldb = h->ldN; g.C = chunk + (size_t)c0 * h->ld_chunk; g.ldc = h->ld_chunk;
+            g.alpha = 1.0; g.beta = 1.0; g.b_upper = 1;
+            SEC(h, "gemm_ZLpost", CU(gemm_f64(st, true, true, g)));
+            c0 = c1;
+        }
     }
+    if (post_sliced) h->pending_post_rows = false;  // pending_shared stays set (the tail of chol(K_post): zeroing the upper triangle)
     SEC(h, "add_mustar", CU(launch_add_mustar(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta)));
     return GPIRT_OK;
 }

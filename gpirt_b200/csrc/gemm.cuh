@@ -37,6 +37,7 @@ struct GemmArgs {
     int batch;        // 0 or 1: a single product
     long long strideA, strideB, strideC;
     int M_last, N_last, K_last;  // extents of batch (batch-1) when > 0, else M / N / K
+    int n_off;        // column index of C(0,0) inside the full product (column slices with b_upper / b_lower)
     int m_off;        // row index of C(0,0) inside the full product (a launch over a row slice keeps the triangular k ranges right)
 };
 
@@ -115,9 +116,9 @@ gemm_f64_kernel(GemmArgs g) {
 
     int k_end = g.K, k_begin = 0;
     if (g.a_lower) k_end = min(k_end, g.m_off + m0 + BM);
-    if (g.b_upper) k_end = min(k_end, n0 + BN);
+    if (g.b_upper) k_end = min(k_end, g.n_off + n0 + BN);
     if (g.a_upper) k_begin = max(k_begin, g.m_off + m0);
-    if (g.b_lower) k_begin = max(k_begin, n0);
+    if (g.b_lower) k_begin = max(k_begin, g.n_off + n0);
     k_begin = (k_begin / BK) * BK;
     const int KT = k_end > k_begin ? (k_end - k_begin + BK - 1) / BK : 0;
 
