@@ -20,6 +20,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 from oracle import orc, ref  # noqa: E402
+from gpirt_b200 import response_matrix as rmx  # noqa: E402
+from gpirt_b200.sampler import default_thresholds  # noqa: E402
 from tests.problems import make_problem  # noqa: E402
 
 UCAP = 48
@@ -123,6 +125,30 @@ def panel_case(name, n, m, C, H, seed, iters, ls, kernel, os_=1.3):
     print(name, "ll", R["ll"])
 
 
+def dataset_case(name, cube, C, seed, iters, keep_items=8):
+    """BASELINE configs 1 and 2: the reference's gpirtMCMC() on its own datasets (data/senate116.rda, data/SDO.rda read by
+    gpirt_b200.response_matrix) with the R wrapper's defaults (R/gpirtMCMC.R:98-109: beta sds 3, theta_prior_sds 0, os 1, ls 10, Matern,
+    thresholds qnorm(i/C)) and theta_init ~ N(0,1) (the wrapper's own default rnorm(mean, sd = 0) starts every respondent at 0).
+    The fixture keeps the response cube (int8, 0 = missing), the initialisation stream and the reference's theta / beta / threshold / ll
+    draws, f and f* for the first `keep_items` items. The per-unit random streams are NOT stored (10 MB): the tests regenerate them by
+    running the oracle in its mt19937 mode, which must reproduce the reference's theta bit for bit before its streams are trusted."""
+    y = np.asfortranarray(cube[:, :, 0])
+    n, m = y.shape
+    rng = np.random.default_rng(seed)
+    theta_in = rng.standard_normal(n)
+    z_init = rng.standard_normal(3 * m + n * m)
+    bpm, bps = np.zeros((3, m), order="F"), np.full((3, m), 3.0, order="F")
+    tpm, tps = np.zeros((2, n), order="F"), np.zeros((2, n), order="F")
+    thr0 = default_thresholds(m, C)
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, 1.0, 10.0, "Matern", thr0, 0, z_init, store_f=True, store_fstar=True)
+    k = min(keep_items, m)
+    out = dict(n=n, m=m, C=C, iters=iters, y=np.where(np.isfinite(y), y, 0).astype(np.int8), theta_in=theta_in, z_init=z_init,
+               ref_theta=R["theta"][:, :, 0], ref_beta=R["beta"][:, :, 0, :], ref_threshold=R["threshold"][:, :, 0, :], ref_ll=R["ll"],
+               ref_f_head=R["f"][:, :k, 0, :], ref_fstar_last_head=R["fstar"][:, :k, 0, -1])
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, y.shape, "C", C, "ll", R["ll"])
+
+
 def leaf_case():
     rng = np.random.default_rng(42)
     x1, x2, sds = rng.standard_normal(17) * 2, rng.standard_normal(9) * 2, np.array([3.0, 2.5, 0.7])
@@ -150,12 +176,23 @@ def leaf_case():
     print("leaves ok")
 
 
+def datasets():
+    cube, C, _, _ = rmx.senate116_responses("/root/reference/data/senate116.rda")
+    dataset_case("senate116", cube, C, seed=116, iters=3)
+    cube, C = rmx.sdo_responses("/root/reference/data/SDO.rda")
+    dataset_case("sdo", cube, C, seed=1500, iters=2)
+
+
 if __name__ == "__main__":
     assert ref.available(), "build oracle/_ref first (make -C oracle ref)"
     orc.set_threads(1)
     ref.set_threads(1)
+    if sys.argv[1:] == ["datasets"]:
+        datasets()
+        sys.exit(0)
     leaf_case()
     sweep_case("sweep_ordinal_c4", n=48, m=8, C=4, seed=11, iters=3, missing=0.1)
     sweep_case("sweep_binary_c2", n=36, m=6, C=2, seed=23, iters=3, missing=0.2, empty_item=4, tps_sd=0.6)
     panel_case("panel_rdm_h3", n=30, m=5, C=4, H=3, seed=51, iters=2, ls=0.05, kernel="Matern")
     panel_case("panel_gp_h3", n=30, m=5, C=3, H=3, seed=61, iters=2, ls=2.5, kernel="Matern")
+    datasets()
