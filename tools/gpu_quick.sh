@@ -1,7 +1,7 @@
 #!/bin/bash
 # tests + bench line (no cpu baseline), summary printed
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -15
+timeout 1200 python -m pytest tests -m gpu -q 2>&1 | tail -15
 timeout 600 python bench.py --steps 20 --warmup 3 --no-cpu-baseline > gpurun_out/bench.json 2> gpurun_out/bench.err; tail -3 gpurun_out/bench.err
 python - <<'PY'
 import json
