@@ -25,7 +25,7 @@ def _as_cube(data):
 def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_codes=None, beta_prior_means=None,
               beta_prior_sds=None, theta_prior_means=None, theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern",
               theta_init=None, thresholds=None, SEED=1, constant_IRF=0, store_f=False, store_fstar=False, beta_init=None,
-              f_init=None, device=0, progress=None, f_init_z=None):
+              f_init=None, device=0, progress=None, f_init_z=None, first_chain=0):
     """Drop-in for gpirtMCMC() (R/gpirtMCMC.R:98-167). `vote_codes` must stay None: the reference's recoding
     path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing."""
     if vote_codes is not None:
@@ -51,21 +51,25 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         Ccat = thr.shape[1] - 1
     thr = np.asfortranarray(thr)
     n_samples = int(sample_iterations / THIN)
-    result = []
+    outs, keep = [], []
+    args = (McmcArgs * CHAIN)()
+    cb = _lib.PROGRESS_FN(progress) if progress is not None else _lib.PROGRESS_FN()
     for chain in range(CHAIN):
-        rng = np.random.default_rng(SEED + chain)  # stands in for set.seed(SEED+chain-1) (R/gpirtMCMC.R:114)
+        rng = np.random.default_rng(SEED + first_chain + chain)  # stands in for set.seed(SEED+chain-1) (R/gpirtMCMC.R:114)
         if theta_init is None:
             th0 = np.empty((n, H), order="F")
             th0[:, 0] = tpm[0] + tps[0] * rng.standard_normal(n)  # rnorm(1, mean, sd) per respondent (:124-126)
             th0[:, 1:] = th0[:, :1]
+            theta_init = th0  # as in R: the first chain's draw is assigned in the function's scope, later chains find it non-NULL (:120-134)
         else:
             th0 = _F(np.asarray(theta_init, dtype=np.float64).reshape(n, H))
         out = dict(theta=np.zeros((n_samples, n, H), order="F"), beta=np.zeros((3, m, H, n_samples), order="F"),
                    threshold=np.zeros((m, Ccat + 1, H, n_samples), order="F"), ll=np.zeros(n_samples),
                    f=np.zeros((n, m, H, n_samples), order="F") if store_f else None,
                    fstar=np.zeros((NGRID, m, H, n_samples), order="F") if store_fstar else None)
-        a = McmcArgs()
+        a = args[chain]
         b0, f0, z0 = _F(beta_init), _F(f_init), _F(f_init_z)
+        keep.append((th0, b0, f0, z0))
         a.y, a.n, a.m, a.horizon = y.ctypes.data, n, m, H
         a.theta = th0.ctypes.data
         a.sample_iterations, a.burn_iterations, a.THIN = int(sample_iterations), int(burn_iterations), int(THIN)
@@ -77,14 +81,17 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         a.beta_init = b0.ctypes.data if b0 is not None else None
         a.f_init = f0.ctypes.data if f0 is not None else None
         a.f_init_z = z0.ctypes.data if z0 is not None else None  # f0_j = L z_j on the device (rmvnorm(L), src/mvnormal.h:7-14)
-        a.seed, a.chain, a.device = int(SEED), chain, int(device)
+        a.seed, a.chain, a.device = int(SEED), first_chain + chain, int(device)
         a.theta_draws, a.beta_draws = out["theta"].ctypes.data, out["beta"].ctypes.data
         a.threshold_draws, a.ll_draws = out["threshold"].ctypes.data, out["ll"].ctypes.data
         a.f_draws = out["f"].ctypes.data if store_f else None
         a.fstar_draws = out["fstar"].ctypes.data if store_fstar else None
-        cb = _lib.PROGRESS_FN(progress) if progress is not None else _lib.PROGRESS_FN()
         a.progress = cb
-        check(_lib.lib().gpirt_mcmc(C.byref(a)))
+        outs.append(out)
+    # all chains in one call: they share y on the device and run side by side (gpirt_mcmc_chains; CHAIN == 1 is gpirt_mcmc)
+    check(_lib.lib().gpirt_mcmc_chains(args, CHAIN) if CHAIN > 1 else _lib.lib().gpirt_mcmc(C.byref(args[0])))
+    result = []
+    for out in outs:
         result.append(dict(theta=out["theta"],
                            f=[out["f"][..., s] for s in range(n_samples)] if store_f else None,
                            beta=[out["beta"][..., s] for s in range(n_samples)],

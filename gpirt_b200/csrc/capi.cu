@@ -452,6 +452,24 @@ int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y) {
     return rc;
 }
 
+// Batched chains (BASELINE config 5, R/gpirtMCMC.R:111 `for(chain in 1:CHAIN)`): every chain scores the same responses, so chains after the
+// first take the two int8 layouts from a handle that already holds them (device-to-device, 2 n m bytes) instead of re-uploading 8 n m bytes.
+int gpirt_copy_data(gpirt_sampler* h, gpirt_sampler* src) {
+    CHECK_H(h);
+    CHECK_H(src);
+    if (!src->have_data) return fail(GPIRT_ERR_INVALID, "copy_data: the source handle holds no response data");
+    if (h->cfg.device != src->cfg.device || h->n != src->n || h->m_total != src->m_total || h->C != src->C || h->world != src->world ||
+        h->rank != src->rank || h->ldy != src->ldy || h->ldm != src->ldm)
+        return fail(GPIRT_ERR_SHAPE, "copy_data: the two handles differ in shape, shard or device");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(src->stream));
+    CU(cudaMemcpyAsync(h->y_im, src->y_im, (size_t)h->ldy * std::max(h->m_local, 1), cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaMemcpyAsync(h->y_rm, src->y_rm, (size_t)h->ldm * std::max(h->n_local, 1), cudaMemcpyDeviceToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
+    h->have_data = true;
+    return GPIRT_OK;
+}
+
 int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds, const double* theta_prior_sds) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));

@@ -80,11 +80,14 @@ static int mcmc_panel(const gpirt_mcmc_args* a, const gpirt_config& cfg) {
     return gpirt_panel_sync(g.p);
 }
 
-extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
+static bool args_ok(const gpirt_mcmc_args* a) {
     if (!a || !a->y || !a->theta || !a->beta_prior_sds || !a->theta_prior_sds || !a->thresholds || !a->theta_draws || !a->beta_draws ||
         !a->threshold_draws || !a->ll_draws)
-        return GPIRT_ERR_INVALID;
-    if (a->THIN < 1 || a->sample_iterations < 0 || a->burn_iterations < 0) return GPIRT_ERR_INVALID;
+        return false;
+    return a->THIN >= 1 && a->sample_iterations >= 0 && a->burn_iterations >= 0;
+}
+
+static gpirt_config config_of(const gpirt_mcmc_args* a) {
     gpirt_config cfg;
     std::memset(&cfg, 0, sizeof(cfg));
     cfg.n = a->n; cfg.m_total = a->m; cfg.horizon = a->horizon; cfg.C = a->C; cfg.constant_IRF = a->constant_IRF; cfg.p_beta = 3;
@@ -92,51 +95,103 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     const std::string kern = a->KERNEL ? a->KERNEL : "Matern";
     cfg.kernel = kern == "RBF" ? 1 : 0;
     cfg.device = a->device; cfg.seed = a->seed; cfg.chain = a->chain; cfg.rank = 0; cfg.world = 1;
-    if (a->horizon > 1) return mcmc_panel(a, cfg);
-    Guard g;
-    TRYC(gpirt_create(&cfg, &g.h));
-    gpirt_sampler* h = g.h;
-    TRYC(gpirt_set_data_f64(h, a->y));
-    TRYC(gpirt_set_priors(h, a->beta_prior_sds, a->theta_prior_sds));
-    TRYC(gpirt_set_state(h, a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
-    TRYC(gpirt_set_iter(h, 0xFFFFFFFFu));  // initial draws use a sweep id no sweep reaches
-    TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
-    if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h, a->f_init_z));
-    TRYC(gpirt_set_iter(h, 0));
+    return cfg;
+}
 
-    const int total = a->sample_iterations + a->burn_iterations;
-    const int n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
-    // The kept draws stay on the device and come back in bulk: no host synchronisation per sweep, so the next sweep's theta-only
-    // chain keeps running under this sweep's tail. Capacity: as many samples as fit in a quarter of the free device memory.
-    int cap = 0, first = 0;
-    if (n_samples > 0) {
-        size_t free_b = 0, total_b = 0;
-        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return GPIRT_ERR_CUDA;
-        const int64_t per = gpirt_store_sample_bytes(h, a->f_draws != nullptr, a->fstar_draws != nullptr);
-        cap = (int)std::max<int64_t>(1, std::min<int64_t>(n_samples, (int64_t)(free_b / 4) / per));
-        TRYC(gpirt_store_open(h, cap, a->f_draws != nullptr, a->fstar_draws != nullptr));
+namespace {
+// One chain of gpirtMCMC() at horizon 1: the state before the loop (src/gpirtMCMC.cpp:133-227), one sweep + store decision per step()
+// (:261-356), bulk read-back of the kept draws. Nothing in step() synchronises with the host, so several chains can be stepped round-robin
+// from one thread and overlap on the device.
+struct ChainRun {
+    const gpirt_mcmc_args* a = nullptr;
+    Guard g;
+    int n_samples = 0, cap = 0, first = 0;
+
+    int open(const gpirt_mcmc_args* args, gpirt_sampler* data_from, int n_chains) {
+        a = args;
+        gpirt_config cfg = config_of(a);
+        TRYC(gpirt_create(&cfg, &g.h));
+        gpirt_sampler* h = g.h;
+        if (data_from) TRYC(gpirt_copy_data(h, data_from));
+        else TRYC(gpirt_set_data_f64(h, a->y));
+        TRYC(gpirt_set_priors(h, a->beta_prior_sds, a->theta_prior_sds));
+        TRYC(gpirt_set_state(h, a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
+        TRYC(gpirt_set_iter(h, 0xFFFFFFFFu));  // initial draws use a sweep id no sweep reaches
+        TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
+        if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h, a->f_init_z));
+        TRYC(gpirt_set_iter(h, 0));
+        n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
+        (void)n_chains;
+        return GPIRT_OK;
     }
-    auto flush = [&]() -> int {
+    // The kept draws stay on the device and come back in bulk: no host synchronisation per sweep, so the next sweep's theta-only
+    // chain keeps running under this sweep's tail. Capacity: as many samples as fit in this chain's share of a quarter of the free memory.
+    int open_store(size_t budget_bytes) {
+        if (n_samples <= 0) return GPIRT_OK;
+        const int64_t per = gpirt_store_sample_bytes(g.h, a->f_draws != nullptr, a->fstar_draws != nullptr);
+        cap = (int)std::max<int64_t>(1, std::min<int64_t>(n_samples, (int64_t)budget_bytes / per));
+        return gpirt_store_open(g.h, cap, a->f_draws != nullptr, a->fstar_draws != nullptr);
+    }
+    int flush() {
         int cnt = 0;
-        TRYC(gpirt_store_count(h, &cnt, nullptr));
-        TRYC(gpirt_store_flush(h, n_samples, first, a->theta_draws, a->beta_draws, a->threshold_draws, a->ll_draws, a->f_draws, a->fstar_draws));
+        TRYC(gpirt_store_count(g.h, &cnt, nullptr));
+        TRYC(gpirt_store_flush(g.h, n_samples, first, a->theta_draws, a->beta_draws, a->threshold_draws, a->ll_draws, a->f_draws, a->fstar_draws));
         first += cnt;
         return GPIRT_OK;
-    };
-    for (int iter = 0; iter < total; ++iter) {
-        if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;  // user interrupt
-        TRYC(gpirt_sweep(h, 1));
+    }
+    int step(int iter) {
+        TRYC(gpirt_sweep(g.h, 1));
         if (iter >= a->burn_iterations && iter % a->THIN == 0) {  // src/gpirtMCMC.cpp:334-335
             const int s = (iter - a->burn_iterations) / a->THIN;
-            if (s >= n_samples) continue;  // the reference would write past theta_draws here
-            TRYC(gpirt_store_push(h));
+            if (s >= n_samples) return GPIRT_OK;  // the reference would write past theta_draws here
+            TRYC(gpirt_store_push(g.h));
             int cnt = 0;
-            TRYC(gpirt_store_count(h, &cnt, nullptr));
+            TRYC(gpirt_store_count(g.h, &cnt, nullptr));
             if (cnt == cap) TRYC(flush());
         }
+        return GPIRT_OK;
     }
-    if (n_samples > 0) TRYC(flush());
-    return gpirt_sync(h);
+    int close() {
+        if (n_samples > 0) TRYC(flush());
+        return gpirt_sync(g.h);
+    }
+};
+}  // namespace
+
+extern "C" int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains) {
+    if (!chains || n_chains < 1) return GPIRT_ERR_INVALID;
+    const gpirt_mcmc_args* a0 = &chains[0];
+    for (int c = 0; c < n_chains; ++c) {
+        const gpirt_mcmc_args* a = &chains[c];
+        if (!args_ok(a)) return GPIRT_ERR_INVALID;
+        if (a->n != a0->n || a->m != a0->m || a->horizon != a0->horizon || a->C != a0->C || a->device != a0->device ||
+            a->sample_iterations != a0->sample_iterations || a->burn_iterations != a0->burn_iterations || a->THIN != a0->THIN)
+            return GPIRT_ERR_SHAPE;
+    }
+    if (a0->horizon > 1) {  // dynamic GPIRT: chains one after the other (a panel already keeps H samplers in flight)
+        for (int c = 0; c < n_chains; ++c) TRYC(mcmc_panel(&chains[c], config_of(&chains[c])));
+        return GPIRT_OK;
+    }
+    std::vector<ChainRun> runs(n_chains);
+    for (int c = 0; c < n_chains; ++c) {
+        const bool same_y = c > 0 && chains[c].y == a0->y;
+        TRYC(runs[c].open(&chains[c], same_y ? runs[0].g.h : nullptr, n_chains));
+    }
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return GPIRT_ERR_CUDA;
+    for (int c = 0; c < n_chains; ++c) TRYC(runs[c].open_store(free_b / 4 / (size_t)n_chains));
+    const int total = a0->sample_iterations + a0->burn_iterations;
+    for (int iter = 0; iter < total; ++iter) {
+        if (a0->progress && a0->progress(iter, total, a0->user)) return GPIRT_ERR_INVALID;  // user interrupt
+        for (int c = 0; c < n_chains; ++c) TRYC(runs[c].step(iter));
+    }
+    for (int c = 0; c < n_chains; ++c) TRYC(runs[c].close());
+    return GPIRT_OK;
+}
+
+extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
+    if (!args_ok(a)) return GPIRT_ERR_INVALID;
+    return gpirt_mcmc_chains(a, 1);
 }
 
 extern "C" int gpirt_recover_fstar(const gpirt_recover_fstar_args* a) {

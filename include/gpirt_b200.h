@@ -108,6 +108,8 @@ int gpirt_destroy(gpirt_sampler* h);
 int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream);  /* run on the caller's stream (e.g. torch's current stream) */
 int gpirt_set_data_f64(gpirt_sampler* h, const double* y);  /* n x m_total, NaN missing */
 int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y);   /* n x m_total, 0 missing */
+/* chains share their responses (R/gpirtMCMC.R:111-158 passes the same `data` to every chain): take src's device layouts of y, no upload */
+int gpirt_copy_data(gpirt_sampler* h, gpirt_sampler* src);
 int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds /*3 x m_total*/, const double* theta_prior_sds /*2 x n*/);
 /* any pointer may be NULL (left unchanged). beta: p_beta x m_total; f: n x m_total; thresholds: m_total x (C+1);
  * fstar: NGRID x m_total. Setting theta clamps it to [-5,5] (src/gpirtMCMC.cpp:133). */
@@ -249,6 +251,14 @@ typedef struct {
     const double* f_init_z;
 } gpirt_mcmc_args;
 int gpirt_mcmc(const gpirt_mcmc_args* a);
+/* The chain loop of the R wrapper (R/gpirtMCMC.R:111-158: `for(chain in 1:CHAIN)`, one .gpirtMCMC call per chain, run back to back) as ONE
+ * call that runs the chains side by side on the device - BASELINE config 5 "independent chains batched per GPU". chains[c] is chain c's
+ * argument block: same y (the first chain's is uploaded once and shared on the device), n, m, horizon == 1, C, iteration counts, THIN, KERNEL
+ * and device; its own theta / beta_init / f_init / f_init_z, priors, seed, chain id and output buffers. Sweeps are issued round-robin, every
+ * chain on its own pair of streams, so one chain's latency-bound Cholesky chain runs under the others' throughput-bound item kernels. Each
+ * chain's draws are bit-identical to gpirt_mcmc() on the same argument block (Philox streams are keyed by chain id, kernels are
+ * deterministic). progress is polled from chains[0] once per sweep. */
+int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains);
 
 typedef struct {
     int32_t seed; const double* f; const double* y; int32_t n, m, horizon;
