@@ -278,6 +278,15 @@ def ours(args):
         d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
                        "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 5 calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
+        # ---- batched chains (BASELINE config 5's mode at the C3 shape): the same call with CHAIN = 4, chains side by side on the device ----
+        nch = 4
+        t0 = time.perf_counter()
+        res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=nch, beta_prior_sds=P["beta_prior_sds"],
+                                   theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104, device=local)
+        line["batched_chains"] = {"chains": nch, "value": nch * k / (time.perf_counter() - t0), "unit": "chain-sweeps/s",
+                                  "what": f"gpirtMCMC(CHAIN={nch}, sample_iterations={k}) end to end with host buffers (one gpirt_mcmc_chains call: y uploaded "
+                                          "once, chains on their own streams, sweeps issued round-robin); each chain is bit-identical to the chain run alone"}
+        assert all(np.all(np.isfinite(r["ll"])) for r in res)
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
             r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)
