@@ -210,7 +210,7 @@ def ours(args):
     algo = {  # algorithmic bytes (HBM-bound groups) or flops (FP64-tensor groups) per sweep, SURVEY.md 8(d)
         "ess_f": ("hbm", 25.0 * nm), "ess_theta": ("hbm", E["theta"] * (n / world) * m * 9.0), "ess_beta": ("hbm", 9.0 * nm),
         "ess_thr": ("hbm", 9.0 * nm), "item_ll": ("hbm", 9.0 * nm + 8.0 * (n + 3 * m_loc + (C + 1) * m_loc)), "gather_f": ("hbm", 16.0 * nm),
-        "gen_Z": ("hbm", 8.0 * (n + N) * m_loc), "theta_table": ("hbm", 8.0 * N * m * (C + 1)), "add_mustar": ("hbm", 16.0 * N * m_loc), "K_build": ("hbm", 8.0 * (n * n + n * N + N * N)),
+        "gen_Z": ("hbm", 8.0 * (n + N) * m_loc), "theta_table": ("hbm", 8.0 * N * m * (C + 1)), "add_mustar": ("hbm", 16.0 * N * m_loc), "add_mustar_push": ("hbm", 8.0 * (world + 1) * N * m_loc), "K_build": ("hbm", 8.0 * (n * n + n * N + N * N)),
         "gemm_LZ": ("tensor", 1.0 * n * n * m_loc), "gemm_FtW": ("tensor", 2.0 * N * n * m_loc), "gemm_ZLpost": ("tensor", 1.0 * N * N * m_loc),
         "gemm_Kpost": ("tensor", 1.0 * n * N * N), "chol_K": ("tensor", n ** 3 / 3.0), "chol_Kpost": ("tensor", N ** 3 / 3.0),
         "trsm_kstar": ("tensor", 1.0 * n * n * N), "trsm_W": ("tensor", 1.0 * n * n * N),

@@ -238,6 +238,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     want(&h->item_ll, mt);
     want(&h->total_ll, 1);
     want(&h->flags, 1);
+    want(&h->flags_x, gpirt::MAX_PEERS + 1);
     want(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID)));
     want(&h->Linv, (size_t)h->ldn * h->n);  // block-inverse solver of draw_fstar (the default)
     want(&h->W2, (size_t)h->ldn * NGRID);
@@ -274,6 +275,8 @@ int gpirt_destroy(gpirt_sampler* h) {
     for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
     for (int c = 0; c < h->Lpost_rows.count; ++c) cudaEventDestroy(h->Lpost_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
+    for (char*& pa : h->peer_arena)
+        if (pa) { cudaIpcCloseMemHandle(pa); pa = nullptr; }
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
         if (p) cudaFree(p);
     store_free(h);
@@ -341,8 +344,9 @@ static int check_flags(gpirt_sampler* h) {
     TRY(quiesce(h));
     CU(cudaMemcpyAsync(&fl, h->flags, sizeof(fl), cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    if (fl.chol_info || fl.chol_post_info || fl.overrun || fl.stalled || fl.bad_code) {
+    if (fl.chol_info || fl.chol_post_info || fl.overrun || fl.stalled || fl.bad_code || fl.peer_timeout) {
         CU(cudaMemsetAsync(h->flags, 0, sizeof(fl), h->stream));
+        if (fl.peer_timeout) return fail(GPIRT_ERR_CUDA, "f* exchange: the chunk of rank %d did not arrive within 4 s", fl.peer_timeout - 1);
         if (fl.bad_code) return fail(GPIRT_ERR_CATEGORIES, "response code outside 1..%d", h->C);
         if (fl.chol_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K(theta,theta) + 1e-6 I not positive definite at leading minor %d", fl.chol_info);
         if (fl.chol_post_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K_post not positive definite at leading minor %d", fl.chol_post_info);
@@ -860,7 +864,7 @@ static int launch_theta_chain(gpirt_sampler* h) {
     return GPIRT_OK;
 }
 
-static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/draw-fstar.cpp:18-57
+static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s, bool push_to_peers = false) {  // src/draw-fstar.cpp:18-57
     if (!h->chol_valid) TRY(do_update_cholesky(h));
     if (!h->shared_valid) {
         TRY(quiesce(h));
@@ -904,6 +908,21 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s) {  // src/dra
         }
     }
     if (post_sliced) h->pending_post_rows = false;  // pending_shared stays set (the tail of chol(K_post): zeroing the upper triangle)
+    if (push_to_peers && h->world > 1 && h->peers_attached == h->world - 1) {
+        // the exchange that feeds the theta step, fused into the last kernel of the f* draw: finished values go straight into every
+        // peer's table over NVLink, then the epoch is published in the peers' flag words (gpirt_peer_wait on the other side)
+        PeerPush pp{};
+        for (int p = 0; p < h->world; ++p) {  // a peer's arena is laid out for ITS shard sizes: its own offsets, chunk / word `rank` within them
+            if (p == h->rank) continue;
+            pp.chunk[pp.count] = (double*)(h->peer_arena[p] + h->peer_fstar_off[p]) + (size_t)h->rank * NGRID * h->ld_chunk;
+            pp.flag[pp.count] = (unsigned long long*)(h->peer_arena[p] + h->peer_flags_off[p]) + h->rank;
+            ++pp.count;
+        }
+        h->push_epoch += 1;
+        SEC(h, "add_mustar_push", CU(launch_add_mustar_push(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta, pp)));
+        CU(launch_signal_peers(st, pp, h->push_epoch));
+        return GPIRT_OK;
+    }
     SEC(h, "add_mustar", CU(launch_add_mustar(st, chunk, h->ld_chunk, h->m_local, h->item0, h->beta, h->cfg.p_beta)));
     return GPIRT_OK;
 }
@@ -1013,7 +1032,55 @@ int gpirt_ll_bar(gpirt_sampler* h, double* per_item, double* total) {
 int gpirt_sweep_phase_items(gpirt_sampler* h) {
     ENTER(h);
     TRY(do_draw_f(h, nullptr));
-    return do_draw_fstar(h, nullptr);
+    return do_draw_fstar(h, nullptr, true);
+}
+
+// ---- f* exchange through peer memory (one process per GPU: cudaIpc mappings of the peers' arenas) ----
+int gpirt_ipc_export(gpirt_sampler* h, void* handle64, int64_t* fstar_offset, int64_t* flags_offset) {
+    CHECK_H(h);
+    if (!handle64 || !fstar_offset || !flags_offset) return fail(GPIRT_ERR_INVALID, "ipc_export: NULL output");
+    *fstar_offset = (int64_t)((char*)h->fstar - h->arena);
+    *flags_offset = (int64_t)((char*)h->flags_x - h->arena);
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));  // the arena's zero fill (flag words included) is complete before anyone maps it
+    cudaIpcMemHandle_t mh;
+    CU(cudaIpcGetMemHandle(&mh, h->arena));
+    std::memcpy(handle64, &mh, 64);
+    return GPIRT_OK;
+}
+int gpirt_ipc_attach(gpirt_sampler* h, int peer_rank, const void* handle64, int64_t fstar_offset, int64_t flags_offset) {
+    CHECK_H(h);
+    if (!handle64 || peer_rank < 0 || peer_rank >= h->world || peer_rank == h->rank || h->world > gpirt::MAX_PEERS + 1)
+        return fail(GPIRT_ERR_INVALID, "ipc_attach: peer rank %d of a world of %d (at most %d ranks)", peer_rank, h->world, gpirt::MAX_PEERS + 1);
+    if (h->peer_arena[peer_rank]) return fail(GPIRT_ERR_INVALID, "ipc_attach: rank %d is attached already", peer_rank);
+    CU(cudaSetDevice(h->cfg.device));
+    cudaIpcMemHandle_t mh;
+    std::memcpy(&mh, handle64, 64);
+    void* base = nullptr;
+    CU(cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+    h->peer_arena[peer_rank] = (char*)base;
+    h->peer_fstar_off[peer_rank] = (size_t)fstar_offset;
+    h->peer_flags_off[peer_rank] = (size_t)flags_offset;
+    h->peers_attached += 1;
+    return GPIRT_OK;
+}
+int gpirt_ipc_detach(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(quiesce(h));
+    CU(cudaStreamSynchronize(h->stream));
+    for (char*& pa : h->peer_arena)
+        if (pa) { CU(cudaIpcCloseMemHandle(pa)); pa = nullptr; }
+    h->peers_attached = 0;
+    return GPIRT_OK;
+}
+int gpirt_peer_wait(gpirt_sampler* h) {
+    ENTER(h);
+    if (h->world == 1) return GPIRT_OK;
+    if (h->peers_attached != h->world - 1) return fail(GPIRT_ERR_INVALID, "peer_wait: %d of %d peers attached", h->peers_attached, h->world - 1);
+    CU(launch_wait_peers(h->stream, h->flags_x, h->world, h->rank, h->push_epoch, h->flags));
+    return GPIRT_OK;
 }
 int gpirt_sweep_phase_theta(gpirt_sampler* h) { ENTER(h); return do_draw_theta(h, nullptr); }
 int gpirt_sweep_phase_close(gpirt_sampler* h) {

@@ -81,6 +81,12 @@ struct gpirt_sampler {
     int session = 0;                    // horizon > 1: which session of a gpirt_panel this handle is (keys the Philox streams)
     const double* thr_theta = nullptr;  // thresholds the theta step scores against when they are not this handle's own (RDM quirk, capi.cu)
     char* arena = nullptr;  // the one allocation behind every buffer above
+    // f* exchange through NVLink peer memory (item-sharded sweeps): peers' arenas opened with cudaIpc, addressed at the same offsets as ours
+    unsigned long long* flags_x = nullptr;      // [MAX_PEERS + 1] arrival epochs, word p written by rank p
+    char* peer_arena[gpirt::MAX_PEERS + 1] = {};  // index = peer rank
+    size_t peer_fstar_off[gpirt::MAX_PEERS + 1] = {}, peer_flags_off[gpirt::MAX_PEERS + 1] = {};  // where the peer keeps its f* table / flag words
+    int peers_attached = 0;
+    unsigned long long push_epoch = 0;
     size_t d_z_cap = 0, d_u_cap = 0;
     // device-side store of the draws gpirtMCMC keeps (src/gpirtMCMC.cpp:230-255,334-356): appended on the stream, read back in bulk
     struct DrawStore {

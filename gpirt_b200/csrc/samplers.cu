@@ -586,6 +586,74 @@ cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk
     return cudaGetLastError();
 }
 
+// f* += mu* on the local chunk and, in the same pass, the finished values go to chunk `rank` of every peer's table (16-byte stores over
+// NVLink; ld_chunk is a multiple of 16 doubles and the chunk is 256-byte aligned on every rank). One thread per pair of items of one grid row.
+__global__ void __launch_bounds__(128) k_add_mustar_push(double* __restrict__ fstar, int ld_chunk, int m_local, int item0, const double* __restrict__ beta,
+                                                         int p_beta, PeerPush peers) {
+    const int j = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int idx = blockIdx.y;
+    if (j >= m_local) return;
+    const double ts = grid_value(idx);
+    const size_t off = (size_t)idx * ld_chunk + j;
+    double2 v = *reinterpret_cast<const double2*>(fstar + off);
+    const size_t J = (size_t)item0 + j;
+    v.x += mu_of(ts, beta[3 * J], beta[3 * J + 1], p_beta == 3 ? beta[3 * J + 2] : 0.0);
+    if (j + 1 < m_local) v.y += mu_of(ts, beta[3 * J + 3], beta[3 * J + 4], p_beta == 3 ? beta[3 * J + 5] : 0.0);
+    *reinterpret_cast<double2*>(fstar + off) = v;
+#pragma unroll 1
+    for (int p = 0; p < peers.count; ++p) *reinterpret_cast<double2*>(peers.chunk[p] + off) = v;
+}
+
+cudaError_t launch_add_mustar_push(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta,
+                                   const PeerPush& peers) {
+    dim3 grid(((m_local + 1) / 2 + 127) / 128, NGRID);
+    k_add_mustar_push<<<grid, 128, 0, st>>>(fstar_chunk, ld_chunk, m_local, item0, beta, p_beta, peers);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+// Runs after k_add_mustar_push on the same stream: the pushed values are ordered before the flag by the kernel boundary and the system fence.
+__global__ void k_signal_peers(PeerPush peers, unsigned long long epoch) {
+    __threadfence_system();
+    const int p = threadIdx.x;
+    if (p < peers.count) {
+        volatile unsigned long long* f = peers.flag[p];
+        *f = epoch;
+    }
+    __threadfence_system();
+}
+cudaError_t launch_signal_peers(cudaStream_t st, const PeerPush& peers, unsigned long long epoch) {
+    k_signal_peers<<<1, 32, 0, st>>>(peers, epoch);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+// Holds the stream until every peer's flag word has reached `epoch` (their chunks of the f* table are then complete in this GPU's memory).
+// Bounded: after ~4 s without progress it reports peer_timeout instead of hanging the device.
+__global__ void k_wait_peers(const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags) {
+    const int p = threadIdx.x;
+    if (p < world && p != rank) {
+        const volatile unsigned long long* f = flags + p;
+        unsigned long long t0 = 0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        while (*f < epoch) {
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > 4000000000ULL) {
+                atomicExch(&dev_flags->peer_timeout, p + 1);
+                break;
+            }
+            __nanosleep(200);
+        }
+    }
+    __threadfence_system();
+}
+cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags) {
+    k_wait_peers<<<1, 32, 0, st>>>(flags, world, rank, epoch, dev_flags);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
 __global__ void k_ordered_sum(const double* __restrict__ x, int n, double* out) {
     // fixed-shape reduction: 256 strided partial sums, combined in index order by thread 0
     __shared__ double s[256];

@@ -20,6 +20,18 @@ struct DevFlags {
     int overrun;         // a supplied uniform stream ran dry
     int stalled;         // an ESS loop hit ESS_MAX_PROPOSALS
     int bad_code;        // a y code outside 0..C
+    int peer_timeout;    // a peer's f* chunk did not arrive within the wait limit (item-sharded sweeps over NVLink peer memory)
+};
+
+// Item-sharded sweeps: the f* exchange that feeds the theta step (the all-gather of SURVEY.md 8e) is done by the producing kernel itself.
+// Rank r's k_add_mustar_push finishes its chunk of the f* table and stores every finished value into chunk r of every peer's table through
+// NVLink peer mappings (cudaIpc), k_signal_peers publishes the epoch in the peers' flag words, k_wait_peers holds the theta step back
+// until all chunks of this epoch have landed.
+constexpr int MAX_PEERS = 15;
+struct PeerPush {
+    int count;                              // world - 1
+    double* chunk[MAX_PEERS];               // peer p's address of chunk `rank` of its f* table
+    unsigned long long* flag[MAX_PEERS];    // peer p's flag word for `rank`
 };
 
 // Everything the item-parallel kernels need (one warp per local item).
@@ -108,6 +120,10 @@ cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* tabl
 cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const double* fstar_chunk, int ld_chunk, int m_local, double* f, int ldn);
 // fstar_chunk[idx*ld_chunk + j] += mu_star(idx, item0 + j)  (src/draw-fstar.cpp:52)
 cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta);
+cudaError_t launch_add_mustar_push(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta,
+                                   const PeerPush& peers);
+cudaError_t launch_signal_peers(cudaStream_t st, const PeerPush& peers, unsigned long long epoch);
+cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags);
 // sum of per-item values in index order (src/gpirtMCMC.cpp:325-331 accumulates item by item)
 cudaError_t launch_ordered_sum(cudaStream_t st, const double* x, int n, double* out);
 // layout converters between the reference's N x m column-major f* and the grid-row-major device table

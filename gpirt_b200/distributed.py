@@ -15,6 +15,8 @@ item (src/draw-theta.cpp:123), so it is sharded by respondents and fed by one al
 
 Random streams are keyed by GLOBAL item / respondent index, so a chain is bit-identical for any world size.
 """
+import os
+
 import numpy as np
 
 from .sampler import Sampler
@@ -64,6 +66,19 @@ class ShardedSampler:
         for name in ("fstar", "beta", "thr", "theta", "item_ll"):
             ptr, chunk_bytes = self.S.exchange_buffer(name)
             self._bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * world), device=f"cuda:{device}")
+        # The f* exchange (8 x 1001 x m bytes per sweep, the only large one) goes through NVLink peer memory: every rank maps its peers'
+        # arenas and the last kernel of the f* draw stores into all of them (gpirt_ipc_*, include/gpirt_b200.h). GPIRT_FSTAR_EXCHANGE=nccl
+        # keeps the in-place NCCL all-gather instead (same bits either way: the exchange moves finished values).
+        self.p2p = world > 1 and os.environ.get("GPIRT_FSTAR_EXCHANGE", "p2p") != "nccl"
+        if self.p2p:
+            import torch.distributed as dist
+
+            handles = [None] * world
+            dist.all_gather_object(handles, self.S.ipc_export(), group=group)
+            for r, hnd in enumerate(handles):
+                if r != rank:
+                    self.S.ipc_attach(r, hnd)
+            dist.barrier(group=group)
 
     def _gather(self, name):
         all_gather_chunks(self._bufs[name], self.rank, self.world, self.group)
@@ -71,7 +86,10 @@ class ShardedSampler:
     def sweep(self, k=1):
         for _ in range(k):
             self.S.phase_items()
-            self._gather("fstar")
+            if self.p2p:
+                self.S.peer_wait()
+            else:
+                self._gather("fstar")
             self.S.phase_theta()
             self._gather("theta")
             self.S.phase_close()
@@ -81,6 +99,15 @@ class ShardedSampler:
 
     def total_ll(self):
         return self.S.total_ll()
+
+    def close(self):
+        if self.p2p:  # no rank frees its arena while a peer still maps it
+            import torch.distributed as dist
+
+            self.S.ipc_detach()
+            dist.barrier(group=self.group)
+            self.p2p = False
+        self.S.close()
 
     def __getattr__(self, name):  # set_data, set_priors, set_state, get_state, sync, ...
         return getattr(self.S, name)

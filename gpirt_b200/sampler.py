@@ -289,6 +289,23 @@ class Sampler:
     def phase_close(self):
         check(self._L.gpirt_sweep_phase_close(self._h))
 
+    # ---- f* exchange through NVLink peer memory (item shards, one process per GPU) ----
+    def ipc_export(self):
+        buf, o1, o2 = (C.c_ubyte * 64)(), C.c_int64(), C.c_int64()
+        check(self._L.gpirt_ipc_export(self._h, buf, C.byref(o1), C.byref(o2)))
+        return bytes(buf), o1.value, o2.value
+
+    def ipc_attach(self, peer_rank, exported):
+        handle, o1, o2 = exported
+        buf = (C.c_ubyte * 64).from_buffer_copy(handle)
+        check(self._L.gpirt_ipc_attach(self._h, int(peer_rank), buf, C.c_int64(o1), C.c_int64(o2)))
+
+    def ipc_detach(self):
+        check(self._L.gpirt_ipc_detach(self._h))
+
+    def peer_wait(self):
+        check(self._L.gpirt_peer_wait(self._h))
+
     def exchange_buffer(self, which):
         ptr, nbytes = C.c_void_p(), C.c_int64()
         check(self._L.gpirt_exchange_buffer(self._h, _lib.XCHG[which], C.byref(ptr), C.byref(nbytes)))

@@ -184,6 +184,16 @@ typedef enum { GPIRT_XCHG_FSTAR = 0, GPIRT_XCHG_BETA = 1, GPIRT_XCHG_THR = 2, GP
 /* device pointer of the all-gather buffer `which`; it holds `world` equal chunks of chunk_bytes, chunk r owned by rank r */
 int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
 int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */
+/* The f* exchange (the all-gather that feeds the theta step) without a collective call: every rank maps its peers' device
+ * arenas (one process per GPU: cudaIpc handles, exchanged by the caller, e.g. over torch.distributed) and gpirt_sweep_phase_items' last
+ * kernel stores each finished f* value into its own table AND into every peer's table over NVLink, then publishes an epoch flag;
+ * gpirt_peer_wait enqueues the wait for all peers' flags on the handle's stream in place of the FSTAR all-gather. The theta all-gather
+ * that follows the theta step orders a rank's next push after its peers' reads. Without attached peers the phases behave as before and
+ * the caller all-gathers GPIRT_XCHG_FSTAR itself. gpirt_ipc_detach (then a barrier) must precede gpirt_destroy on every rank. */
+int gpirt_ipc_export(gpirt_sampler* h, void* handle64 /* 64 bytes out: cudaIpcMemHandle_t */, int64_t* fstar_offset, int64_t* flags_offset);
+int gpirt_ipc_attach(gpirt_sampler* h, int peer_rank, const void* handle64, int64_t fstar_offset, int64_t flags_offset); /* the PEER's export */
+int gpirt_ipc_detach(gpirt_sampler* h);
+int gpirt_peer_wait(gpirt_sampler* h);
 
 /* ---- measurement and test hooks (no reference counterpart) ---- */
 int gpirt_profile_enable(gpirt_sampler* h, int on);          /* CUDA events around every kernel group of a sweep */

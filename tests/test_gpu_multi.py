@@ -30,6 +30,7 @@ def run(S):
     S.init_draw(draw_beta=False, draw_f=True)
     S.sweep(sweeps); S.sync()
     st = S.get_state(fstar=False); st["ll"] = S.total_ll()
+    S.close()
     return st
 sh = run(ShardedSampler(n, m, C, rank=rank, world=world, device=local, seed=77))
 # gather the f columns of every rank on rank 0 (get_state writes only the local item block)
@@ -58,13 +59,14 @@ def _gpus():
     return _lib.lib().gpirt_device_count()
 
 
-def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path):
+@pytest.mark.parametrize("exchange", ["p2p", "nccl"])  # f* chunks pushed through NVLink peer memory by the producing kernel / NCCL all-gather
+def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path, exchange):
     if _gpus() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    env = dict(os.environ, GPIRT_ROOT=ROOT)
+    env = dict(os.environ, GPIRT_ROOT=ROOT, GPIRT_FSTAR_EXCHANGE=exchange)
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                         "--master-port", str(port), str(script)], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
