@@ -66,10 +66,12 @@ class ShardedSampler:
         for name in ("fstar", "beta", "thr", "theta", "item_ll"):
             ptr, chunk_bytes = self.S.exchange_buffer(name)
             self._bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * world), device=f"cuda:{device}")
-        # The f* exchange (8 x 1001 x m bytes per sweep, the only large one) goes through NVLink peer memory: every rank maps its peers'
-        # arenas and the last kernel of the f* draw stores into all of them (gpirt_ipc_*, include/gpirt_b200.h). GPIRT_FSTAR_EXCHANGE=nccl
-        # keeps the in-place NCCL all-gather instead (same bits either way: the exchange moves finished values).
-        self.p2p = world > 1 and os.environ.get("GPIRT_FSTAR_EXCHANGE", "p2p") != "nccl"
+        # The f* exchange (8 x 1001 x m bytes per sweep, the only large one) has two implementations with the same bits (it moves finished
+        # values): the in-place NCCL all-gather (default), and GPIRT_FSTAR_EXCHANGE=p2p — every rank maps its peers' arenas (cudaIpc) and the
+        # last kernel of the f* draw stores into all of them over NVLink (gpirt_ipc_*, include/gpirt_b200.h). Measured at 8 x B200 on C3 blocks
+        # (profiles/r01_scaling.txt): the push costs 0.41 ms (280 MB per GPU at 680 GB/s, the NVLink egress floor) against ~0.45 ms for NCCL,
+        # 6.80 vs 6.86 ms per sweep — but mapping 7 peers costs ~200 ms per handle, which a 20-sweep gpirtMCMC call never earns back, hence opt-in.
+        self.p2p = world > 1 and os.environ.get("GPIRT_FSTAR_EXCHANGE", "nccl") == "p2p"
         if self.p2p:
             import torch.distributed as dist
 
