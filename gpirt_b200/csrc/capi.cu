@@ -944,10 +944,19 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double*
     const double table_cost = (double)NGRID * h->C, direct_cost = (double)h->n_local * 12.0 * 9.0;
     const size_t table_bytes = (size_t)NGRID * h->m_total * h->C * 8;
     v.table = nullptr;
+    v.table32 = nullptr;
+    v.exact_evals = h->exact[GPIRT_BLOCK_THETA];
     if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {
         if (!h->theta_tab) CU(cudaMalloc((void**)&h->theta_tab, table_bytes));
-        SEC(h, "theta_table", CU(launch_theta_table(h->stream, v, h->theta_tab)));
-        v.table = h->theta_tab;
+        if (h->screen && !table_only) {
+            // fp32 screening (gpirt_set_screen): the table holds (fp32 term, error bound) pairs — the same bytes, a quarter of the
+            // arithmetic to build — and the few proposals it cannot decide are evaluated in fp64 on the fly
+            SEC(h, "theta_table", CU(launch_theta_table32(h->stream, v, (float2*)h->theta_tab)));
+            v.table32 = (const float2*)h->theta_tab;
+        } else {
+            SEC(h, "theta_table", CU(launch_theta_table(h->stream, v, h->theta_tab)));
+            v.table = h->theta_tab;
+        }
     }
     if (table_only) { *table_only = v.table; return GPIRT_OK; }
     SEC(h, "ess_theta", CU(launch_ess_theta(h->stream, v)));

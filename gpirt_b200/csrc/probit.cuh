@@ -165,10 +165,8 @@ __device__ __forceinline__ float q_tail32(float x) {  // x already clamped to [0
 // t ~ log(Phi(tau_hi - g) - Phi(tau_lo - g) + 1e-6) in fp32 and e >= |t - (the fp64 cell term)|. Infinite thresholds (edge
 // categories) need no special case: their tail clamps to Q(9.25) ~ 1e-20. A NaN anywhere gives e = NaN, which fails both
 // screening comparisons and sends the proposal to the fp64 path.
-__device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi, float& t, float& e) {
-    const float a = (float)__dsub_rn(tau_lo, g), b = (float)__dsub_rn(tau_hi, g);
-    const float u = fminf(fabsf(a), 9.25f), v = fminf(fabsf(b), 9.25f);
-    const float qu = q_tail32(u), qv = q_tail32(v);
+// the cell term from the two rounded arguments a = tau_lo - g, b = tau_hi - g and their tails qu = Q(min(|a|, 9.25)), qv = Q(min(|b|, 9.25))
+__device__ __forceinline__ void cell_ll32_core(float a, float b, float u, float v, float qu, float qv, float& t, float& e) {
     const bool sa = a >= 0.0f, sb = b <= 0.0f;
     const float straddle = (sa || sb) ? 0.0f : 1.0f;
     const float d = sa ? qu - qv : (sb ? qv - qu : (1.0f - qu) - qv);
@@ -177,6 +175,11 @@ __device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi
     const float dp = fmaf(fmaf(4e-7f, u * u, 4e-6f), qu, fmaf(4e-7f, v * v, 4e-6f) * qv) + 2.4e-7f * (p + straddle);
     const float den = p - dp;
     e = (den > dp ? dp * f_rcp(den) * 1.0001f : 14.0f) + fmaf(5e-7f, fabsf(t), 2e-6f);
+}
+__device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi, float& t, float& e) {
+    const float a = (float)__dsub_rn(tau_lo, g), b = (float)__dsub_rn(tau_hi, g);
+    const float u = fminf(fabsf(a), 9.25f), v = fminf(fabsf(b), 9.25f);
+    cell_ll32_core(a, b, u, v, q_tail32(u), q_tail32(v), t, e);
 }
 #endif
 

@@ -347,6 +347,41 @@ cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* tabl
     return cudaGetLastError();
 }
 
+// The same table in fp32 with a rigorous bound per term (probit.cuh, "fp32 screening"): (t, e) with |t - fp64 term| <= e, one 8-byte record
+// per term (a 5-byte form, fp32 term + 8-bit code of the bound in a second array, was measured: the second gather makes the latency-bound
+// theta kernel 0.39 -> 0.62 ms at C3). The C + 1 tails
+// of one (grid point, item) are shared by its C cells, so a cell costs ~1.2 tails and one lg2 on the fp32 / MUFU pipes instead of 1.2 fp64
+// Phi and one fp64 log: the theta step's ESS decisions are screened on this table and only undecided proposals are evaluated in fp64.
+__global__ void __launch_bounds__(128) k_theta_table32(ThetaView v, float2* __restrict__ table32) {
+    const int J = blockIdx.x * 128 + threadIdx.x;
+    const int idx = blockIdx.y;
+    if (J >= v.m_total) return;
+    const int C = v.C;
+    const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
+    const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+    const double mu = mu_of(grid_value(idx), v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
+    const double g = __dadd_rn(fs, mu);
+    const double* tau = v.thr + (size_t)J * (C + 1);
+    float2* out = table32 + ((size_t)idx * v.m_total + J) * C;
+    float a = (float)__dsub_rn(tau[0], g);  // -inf: clamps to Q(9.25)
+    float u = fminf(fabsf(a), 9.25f), qu = q_tail32(u);
+    for (int c = 1; c <= C; ++c) {
+        const float b = (float)__dsub_rn(tau[c], g);
+        const float w = fminf(fabsf(b), 9.25f), qw = q_tail32(w);
+        float t, e;
+        cell_ll32_core(a, b, u, w, qu, qw, t, e);
+        out[c - 1] = make_float2(t, e);
+        a = b; u = w; qu = qw;
+    }
+}
+
+cudaError_t launch_theta_table32(cudaStream_t st, const ThetaView& v, float2* table32) {
+    dim3 grid((v.m_total + 127) / 128, NGRID);
+    k_theta_table32<<<grid, 128, 0, st>>>(v, table32);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
 // T threads per respondent: 256 when there are respondents enough to fill the GPU, 1024 for a rank with few of them (item-sharded runs:
 // n / world respondents against m * world items). Both sum an evaluation in the SAME order — 1024 virtual lanes (lane l takes items l,
 // l + 1024, ...), lanes t, t+256, t+512, t+768 combined as (S_t + S_t+256) + (S_t+512 + S_t+768), then the 8-warp block sum — so a chain
@@ -356,12 +391,23 @@ __global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
     static_assert(T == 256 || T == 1024, "virtual-lane scheme");
     __shared__ double s_part[8];
     __shared__ double s_lane[T == 1024 ? 1024 : 1];
+    __shared__ double s_part2[2][T / 32];
     const int il = blockIdx.x;
     if (il >= v.n_local) return;
     const int i = v.resp0 + il;
     const int tid = threadIdx.x;
-    const int8_t* __restrict__ yrow = v.y_rm + (size_t)il * v.ldm;
     const int C = v.C, m_total = v.m_total;
+    // the respondent's row of y is read by every one of its ~12 evaluations: staged in shared memory once (when it fits), so an evaluation
+    // is one independent gather per item instead of a y load followed by a dependent gather
+    extern __shared__ __align__(16) int8_t s_y[];
+    const int8_t* yrow = v.y_rm + (size_t)il * v.ldm;
+    if (v.y_in_smem) {
+        const int4* src = reinterpret_cast<const int4*>(yrow);  // rows are 16-byte aligned (ldm is a multiple of 16)
+        int4* dst = reinterpret_cast<int4*>(s_y);
+        for (int q = tid; q < (m_total + 15) / 16; q += T) dst[q] = src[q];
+        __syncthreads();
+        yrow = s_y;
+    }
     const double* __restrict__ table = v.table;
 
     auto term = [&](int J, int idx, double ts) -> double {  // one item's term of compute_ll_sparse, src/draw-theta.cpp:14-22
@@ -408,6 +454,26 @@ __global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
         }
     };
 
+    // screening pass: the evaluation's fp32 terms and their bounds from the (t, e) table, summed in fp64 (any order: the bound covers it)
+    const float2* __restrict__ table32 = v.table32;
+    auto loglik32 = [&](double th, double& S, double& E) {
+        const float2* __restrict__ row = table32 + (size_t)grid_index(th) * m_total * C;
+        double s0 = 0.0, s1 = 0.0, e0 = 0.0, e1 = 0.0;
+        auto one = [&](int J, double& s, double& e) {
+            const int y = yrow[J];
+            if (y == 0) return;
+            const float2 te = row[(size_t)J * C + (y - 1)];
+            s += (double)te.x;
+            e += (double)te.y;
+        };
+        int J = tid;
+        for (; J + 3 * T < m_total; J += 4 * T) { one(J, s0, e0); one(J + T, s1, e1); one(J + 2 * T, s0, e0); one(J + 3 * T, s1, e1); }
+        for (; J < m_total; J += T) one(J, s0, e0);
+        S = s0 + s1;
+        E = e0 + e1;
+        block_sum2<T / 32>(S, E, s_part2);
+    };
+
     double Li;
     if (v.regime == 0) {
         const double sd = v.theta_prior_sds[2 * (size_t)i];
@@ -421,7 +487,16 @@ __global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
     int overrun = 0;
     uint32_t k = 0;
     const double u = v.us.get(v.key, ST_THETA_U, i, k++, &overrun);
-    const double log_y = __dadd_rn(log(u), loglik(th0));
+    const double log_u = log(u);
+    // Exact path: log_y = log(u) + ll(theta) in fp64, every proposal in fp64. Screened path (table32): the current state and the proposal
+    // are both read from the fp32 table; the decision is taken there when |S' - S0 - log u| exceeds the two accumulated bounds, otherwise the
+    // fp64 values are computed (the current state's once) and decide — so every decision is the fp64 decision.
+    const bool screen = table32 != nullptr;
+    double S0 = 0.0, E0 = 0.0, log_y = 0.0;
+    bool have_exact0 = false;
+    int n_exact = 0;
+    if (screen) loglik32(th0, S0, E0);
+    else { log_y = __dadd_rn(log_u, loglik(th0)); have_exact0 = true; n_exact = 1; }
     double eps_min = 0.0, eps_max = TWO_PI_R;
     double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
     eps_min = __dsub_rn(eps, TWO_PI_R);
@@ -431,10 +506,26 @@ __global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
     for (int it = 0; it < ESS_MAX_PROPOSALS; ++it) {
         raw = __dadd_rn(__dmul_rn(th0, cos(eps)), __dmul_rn(nu, sin(eps)));
         raw = fmax(-5.0, fmin(5.0, raw));
-        const double llp = loglik(raw);
         ++evals;
-        margin = fmin(margin, fabs(llp - log_y));
-        if (llp > log_y) { accepted = true; break; }
+        bool decided = false, accept = false;
+        if (screen) {
+            double Sp, Ep;
+            loglik32(raw, Sp, Ep);
+            const double d = Sp - (S0 + log_u);
+            // + the fp64 pass's own summation / rounding noise (1e-16 relative per operation on sums of magnitude |S|)
+            const double Eb = (Ep + E0) * 1.000001 + 1e-10 * (fabs(Sp) + fabs(S0) + 1.0);
+            if (d > Eb) { decided = true; accept = true; }
+            else if (d < -Eb) { decided = true; }
+            if (decided) margin = fmin(margin, fabs(d) - Eb);  // a lower bound of the true margin
+        }
+        if (!decided) {
+            if (!have_exact0) { log_y = __dadd_rn(log_u, loglik(th0)); have_exact0 = true; ++n_exact; }
+            const double llp = loglik(raw);
+            ++n_exact;
+            margin = fmin(margin, fabs(llp - log_y));
+            accept = llp > log_y;
+        }
+        if (accept) { accepted = true; break; }
         if (eps < 0.0) eps_min = eps; else eps_max = eps;
         eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
         if (overrun) break;
@@ -443,6 +534,7 @@ __global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
         v.theta_new[i] = grid_value(grid_index(raw));  // snapped to the grid, src/draw-theta.cpp:165-169
         v.evals[i] = evals;
         v.margin[i] = margin;
+        if (v.exact_evals) v.exact_evals[i] = n_exact;
         if (overrun) atomicExch(&v.flags->overrun, 1);
         else if (!accepted) atomicExch(&v.flags->stalled, 1);
     }
@@ -452,8 +544,17 @@ cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     if (v.n_local <= 0) return cudaSuccess;
     // few respondents on this rank (an item shard): four times the threads per respondent keep the SMs' memory pipes busy
     const bool wide = g_theta_threads ? g_theta_threads == 1024 : v.n_local <= 600;
-    if (wide) k_ess_theta<1024><<<v.n_local, 1024, 0, st>>>(v);
-    else k_ess_theta<256><<<v.n_local, 256, 0, st>>>(v);
+    ThetaView w = v;
+    const size_t row_bytes = ((size_t)v.m_total + 15) / 16 * 16;
+    w.y_in_smem = row_bytes <= (wide ? (size_t)96 << 10 : (size_t)24 << 10) && row_bytes <= (size_t)v.ldm;  // keeps >= 2 wide / 8 narrow CTAs per SM
+    const size_t smem = w.y_in_smem ? row_bytes : 0;
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_ess_theta<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+        attr_set = true;
+    }
+    if (wide) k_ess_theta<1024><<<v.n_local, 1024, smem, st>>>(w);
+    else k_ess_theta<256><<<v.n_local, 256, smem, st>>>(w);
     ++g_kernel_launches;
     return cudaGetLastError();
 }

@@ -70,6 +70,10 @@ struct ThetaView {
     const double* beta;       // 3 x m_total
     const double* thr;        // (C+1) x m_total item-major
     const double* table;      // optional [NGRID][m_total][C] table of cell terms (k_theta_table), or nullptr
+    const float2* table32;    // optional [NGRID][m_total][C] table of (fp32 cell term, bound on its distance to the fp64 term) (k_theta_table32):
+                              // proposals are screened on it, undecided ones are evaluated exactly (table, or on the fly when table == nullptr)
+    int32_t* exact_evals;     // per respondent: evaluations that ran in fp64, or nullptr
+    int y_in_smem;            // set by launch_ess_theta: the respondent's row of y fits the CTA's shared memory
     const double* theta_prior_sds;  // 2 x n
     int regime;               // 0: L_i = sqrt(1 + sd0_i^2) (CST/RDM), 1: sqrt(os^2 + 1e-6) (GP over time, H = 1)
     double theta_os;
@@ -119,6 +123,7 @@ cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* tabl
 // f[i + j*ldn] = fstar_chunk[grid_index(theta_i)*ld_chunk + j]  (src/gpirtMCMC.cpp:291-298)
 cudaError_t launch_gather_f(cudaStream_t st, const double* theta, int n, const double* fstar_chunk, int ld_chunk, int m_local, double* f, int ldn);
 // fstar_chunk[idx*ld_chunk + j] += mu_star(idx, item0 + j)  (src/draw-fstar.cpp:52)
+cudaError_t launch_theta_table32(cudaStream_t st, const ThetaView& v, float2* table32);
 cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta);
 cudaError_t launch_add_mustar_push(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta,
                                    const PeerPush& peers);
