@@ -353,26 +353,33 @@ cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* tabl
 // of one (grid point, item) are shared by its C cells, so a cell costs ~1.2 tails and one lg2 on the fp32 / MUFU pipes instead of 1.2 fp64
 // Phi and one fp64 log: the theta step's ESS decisions are screened on this table and only undecided proposals are evaluated in fp64.
 __global__ void __launch_bounds__(128) k_theta_table32(ThetaView v, float2* __restrict__ table32) {
-    const int J = blockIdx.x * 128 + threadIdx.x;
+    // the C records of the CTA's 128 items are one contiguous run of the table: staged in shared memory, written out coalesced
+    __shared__ float2 s_out[128 * MAX_C];
+    const int J0 = blockIdx.x * 128, J = J0 + threadIdx.x;
     const int idx = blockIdx.y;
-    if (J >= v.m_total) return;
     const int C = v.C;
-    const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
-    const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
-    const double mu = mu_of(grid_value(idx), v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
-    const double g = __dadd_rn(fs, mu);
-    const double* tau = v.thr + (size_t)J * (C + 1);
-    float2* out = table32 + ((size_t)idx * v.m_total + J) * C;
-    float a = (float)__dsub_rn(tau[0], g);  // -inf: clamps to Q(9.25)
-    float u = fminf(fabsf(a), 9.25f), qu = q_tail32(u);
-    for (int c = 1; c <= C; ++c) {
-        const float b = (float)__dsub_rn(tau[c], g);
-        const float w = fminf(fabsf(b), 9.25f), qw = q_tail32(w);
-        float t, e;
-        cell_ll32_core(a, b, u, w, qu, qw, t, e);
-        out[c - 1] = make_float2(t, e);
-        a = b; u = w; qu = qw;
+    if (J < v.m_total) {
+        const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
+        const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+        const double mu = mu_of(grid_value(idx), v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
+        const double g = __dadd_rn(fs, mu);
+        const double* tau = v.thr + (size_t)J * (C + 1);
+        float2* out = s_out + threadIdx.x * C;
+        float a = (float)__dsub_rn(tau[0], g);  // -inf: clamps to Q(9.25)
+        float u = fminf(fabsf(a), 9.25f), qu = q_tail32(u);
+        for (int c = 1; c <= C; ++c) {
+            const float b = (float)__dsub_rn(tau[c], g);
+            const float w = fminf(fabsf(b), 9.25f), qw = q_tail32(w);
+            float t, e;
+            cell_ll32_core(a, b, u, w, qu, qw, t, e);
+            out[c - 1] = make_float2(t, e);
+            a = b; u = w; qu = qw;
+        }
     }
+    __syncthreads();
+    const int count = min(128, v.m_total - J0) * C;
+    float2* dst = table32 + ((size_t)idx * v.m_total + J0) * C;
+    for (int q = threadIdx.x; q < count; q += 128) dst[q] = s_out[q];
 }
 
 cudaError_t launch_theta_table32(cudaStream_t st, const ThetaView& v, float2* table32) {
