@@ -7,6 +7,8 @@
 #include <limits>
 #include <type_traits>
 #include <vector>
+#include <mutex>
+#include <map>
 
 #include "probit.cuh"
 #include "sampler_state.cuh"
@@ -33,6 +35,95 @@ static int fail(int code, const char* fmt, ...) {
         int rc_ = (x);           \
         if (rc_ != GPIRT_OK) return rc_; \
     } while (0)
+
+// Device allocations go through a small per-process cache: gpirtMCMC() creates and destroys a handle per call (arena, theta-step table, draw
+// store, upload staging: ~1 GB at C3), and cudaMalloc / cudaFree of blocks that size map and unmap device memory — tens of milliseconds on a
+// busy host, more than the sweeps of a short call. A freed block of >= 1 MB is kept (exact size match on reuse, at most 32 blocks / 24 GB,
+// oldest evicted) until gpirt_release_cached_memory(); like cudaFree, dev_free synchronises the device first.
+namespace {
+struct CachedBlock { void* p; size_t bytes; int device; };
+std::mutex g_alloc_mu;
+std::vector<CachedBlock> g_free_blocks;
+std::map<void*, std::pair<size_t, int>> g_live_blocks;
+size_t g_cached_bytes = 0;
+constexpr size_t CACHE_MIN_BLOCK = (size_t)1 << 20, CACHE_MAX_BYTES = (size_t)24 << 30, CACHE_MAX_BLOCKS = 32;
+}  // namespace
+
+static cudaError_t dev_malloc(void** p, size_t bytes) {
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    if (e != cudaSuccess) return e;
+    {
+        std::lock_guard<std::mutex> lk(g_alloc_mu);
+        for (size_t k = 0; k < g_free_blocks.size(); ++k)
+            if (g_free_blocks[k].bytes == bytes && g_free_blocks[k].device == device) {
+                *p = g_free_blocks[k].p;
+                g_cached_bytes -= bytes;
+                g_free_blocks.erase(g_free_blocks.begin() + k);
+                g_live_blocks[*p] = {bytes, device};
+                return cudaSuccess;
+            }
+    }
+    e = cudaMalloc(p, bytes);
+    if (e != cudaSuccess) {  // out of memory with blocks parked in the cache: release them and retry once
+        cudaGetLastError();
+        std::vector<CachedBlock> drop;
+        {
+            std::lock_guard<std::mutex> lk(g_alloc_mu);
+            drop.swap(g_free_blocks);
+            g_cached_bytes = 0;
+        }
+        for (const CachedBlock& b : drop) cudaFree(b.p);
+        e = cudaMalloc(p, bytes);
+        if (e != cudaSuccess) return e;
+    }
+    std::lock_guard<std::mutex> lk(g_alloc_mu);
+    g_live_blocks[*p] = {bytes, device};
+    return cudaSuccess;
+}
+
+static cudaError_t dev_free(void* p) {
+    if (!p) return cudaSuccess;
+    size_t bytes = 0;
+    int device = 0;
+    {
+        std::lock_guard<std::mutex> lk(g_alloc_mu);
+        auto it = g_live_blocks.find(p);
+        if (it == g_live_blocks.end()) return cudaFree(p);
+        bytes = it->second.first;
+        device = it->second.second;
+        g_live_blocks.erase(it);
+    }
+    if (bytes < CACHE_MIN_BLOCK) return cudaFree(p);
+    cudaDeviceSynchronize();  // cudaFree's implicit synchronisation: nothing in flight may still use the block when it is handed out again
+    void* evict = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_alloc_mu);
+        if (bytes > CACHE_MAX_BYTES) evict = p;
+        else {
+            g_free_blocks.push_back({p, bytes, device});
+            g_cached_bytes += bytes;
+            while (g_free_blocks.size() > CACHE_MAX_BLOCKS || g_cached_bytes > CACHE_MAX_BYTES) {
+                if (evict) break;  // one eviction per call keeps this simple; the next free evicts the next
+                evict = g_free_blocks.front().p;
+                g_cached_bytes -= g_free_blocks.front().bytes;
+                g_free_blocks.erase(g_free_blocks.begin());
+            }
+        }
+    }
+    return evict ? cudaFree(evict) : cudaSuccess;
+}
+
+extern "C" int gpirt_release_cached_memory(void) {
+    std::vector<CachedBlock> drop;
+    {
+        std::lock_guard<std::mutex> lk(g_alloc_mu);
+        drop.swap(g_free_blocks);
+        g_cached_bytes = 0;
+    }
+    for (const CachedBlock& b : drop) cudaFree(b.p);
+    return GPIRT_OK;
+}
 
 static int select_device(int device) {
     int count = 0;
@@ -249,7 +340,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         want(&h->exact[b], units);
         want(&h->margin[b], units);
     }
-    CU(cudaMalloc((void**)&h->arena, arena_bytes));
+    CU(dev_malloc((void**)&h->arena, arena_bytes));
     CU(cudaMemsetAsync(h->arena, 0, arena_bytes, h->stream));
     {
         size_t off = 0;
@@ -278,7 +369,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     for (char*& pa : h->peer_arena)
         if (pa) { cudaIpcCloseMemHandle(pa); pa = nullptr; }
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
-        if (p) cudaFree(p);
+        if (p) dev_free(p);
     store_free(h);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -358,9 +449,9 @@ static int check_flags(gpirt_sampler* h) {
 
 static int upload(gpirt_sampler* h, double** buf, size_t* cap, const double* host, size_t count) {
     if (count > *cap) {
-        if (*buf) CU(cudaFree(*buf));
+        if (*buf) CU(dev_free(*buf));
         *buf = nullptr;
-        CU(cudaMalloc((void**)buf, count * sizeof(double)));
+        CU(dev_malloc((void**)buf, count * sizeof(double)));
         *cap = count;
     }
     CU(cudaMemcpyAsync(*buf, host, count * sizeof(double), cudaMemcpyHostToDevice, h->stream));
@@ -413,8 +504,8 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
     const long long slab_cols = std::max(1LL, (256LL << 20) / (8LL * max_rows));
     double* d_y = nullptr;
     int8_t* d_i8 = nullptr;
-    CU(cudaMalloc((void**)&d_i8, (size_t)max_count));
-    CU(cudaMalloc((void**)&d_y, (size_t)std::min<long long>(slab_cols * max_rows, max_count) * 8));
+    CU(dev_malloc((void**)&d_i8, (size_t)max_count));
+    CU(dev_malloc((void**)&d_y, (size_t)std::min<long long>(slab_cols * max_rows, max_count) * 8));
     int rc = GPIRT_OK;
     CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
     CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
@@ -433,8 +524,8 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
         if (e != cudaSuccess) rc = fail(GPIRT_ERR_CUDA, "y layouts: %s", cudaGetErrorString(e));
     }
     cudaStreamSynchronize(h->stream);
-    cudaFree(d_y);
-    cudaFree(d_i8);
+    dev_free(d_y);
+    dev_free(d_i8);
     if (rc != GPIRT_OK) return rc;
     h->have_data = true;
     return check_flags(h);
@@ -448,11 +539,11 @@ int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y) {
     for (size_t e = 0; e < count; ++e)
         if (y[e] < 0 || y[e] > h->C) return fail(GPIRT_ERR_CATEGORIES, "response code %d outside 0..%d at element %zu", (int)y[e], h->C, e);
     int8_t* d_full = nullptr;
-    CU(cudaMalloc((void**)&d_full, count));
+    CU(dev_malloc((void**)&d_full, count));
     CU(cudaMemcpyAsync(d_full, y, count, cudaMemcpyHostToDevice, h->stream));
     int rc = build_layouts(h, d_full);
     cudaStreamSynchronize(h->stream);
-    cudaFree(d_full);
+    dev_free(d_full);
     return rc;
 }
 
@@ -519,14 +610,14 @@ int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, c
                              cudaMemcpyHostToDevice, st));
     if (fstar) {  // NGRID x m_total column-major -> every chunk of the grid-row-major table
         double* tmp = nullptr;
-        CU(cudaMalloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        CU(dev_malloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
         CU(cudaMemcpyAsync(tmp, fstar, (size_t)NGRID * h->m_total * 8, cudaMemcpyHostToDevice, st));
         for (int r = 0; r < h->world; ++r) {
             const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
             if (cols > 0) CU(launch_transpose(st, tmp + (size_t)j0 * NGRID, NGRID, NGRID, cols, h->fstar + (size_t)r * NGRID * h->ld_chunk, h->ld_chunk));
         }
         CU(cudaStreamSynchronize(st));
-        cudaFree(tmp);
+        dev_free(tmp);
     }
     CU(cudaStreamSynchronize(st));
     return GPIRT_OK;
@@ -558,7 +649,7 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
                              cudaMemcpyDeviceToHost, st));
     if (fstar) {
         double* tmp = nullptr;
-        CU(cudaMalloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        CU(dev_malloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
         for (int r = 0; r < h->world; ++r) {
             const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
             // chunk is cols x NGRID (ld_chunk) column-major in (j, idx); transpose back to NGRID x cols
@@ -566,7 +657,7 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
         }
         CU(cudaMemcpyAsync(fstar, tmp, (size_t)NGRID * h->m_total * 8, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        cudaFree(tmp);
+        dev_free(tmp);
     }
     CU(cudaStreamSynchronize(st));
     return GPIRT_OK;
@@ -577,7 +668,7 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
 static void store_free(gpirt_sampler* h) {
     auto& s = h->store;
     for (double* p : {s.theta, s.beta, s.thr, s.ll, s.f, s.fstar})
-        if (p) cudaFree(p);
+        if (p) dev_free(p);
     s = gpirt_sampler::DrawStore();
 }
 int64_t gpirt_store_sample_bytes(gpirt_sampler* h, int store_f, int store_fstar) {
@@ -597,12 +688,12 @@ int gpirt_store_open(gpirt_sampler* h, int capacity, int store_f, int store_fsta
     store_free(h);
     auto& s = h->store;
     const size_t cap = (size_t)capacity, m = (size_t)h->m_total;
-    CU(cudaMalloc((void**)&s.theta, cap * h->n * 8));
-    CU(cudaMalloc((void**)&s.beta, cap * 3 * m * 8));
-    CU(cudaMalloc((void**)&s.thr, cap * (h->C + 1) * m * 8));
-    CU(cudaMalloc((void**)&s.ll, cap * 8));
-    if (store_f) CU(cudaMalloc((void**)&s.f, cap * h->n * m * 8));
-    if (store_fstar) CU(cudaMalloc((void**)&s.fstar, cap * NGRID * m * 8));
+    CU(dev_malloc((void**)&s.theta, cap * h->n * 8));
+    CU(dev_malloc((void**)&s.beta, cap * 3 * m * 8));
+    CU(dev_malloc((void**)&s.thr, cap * (h->C + 1) * m * 8));
+    CU(dev_malloc((void**)&s.ll, cap * 8));
+    if (store_f) CU(dev_malloc((void**)&s.f, cap * h->n * m * 8));
+    if (store_fstar) CU(dev_malloc((void**)&s.fstar, cap * NGRID * m * 8));
     s.cap = capacity;
     s.count = 0;
     return GPIRT_OK;
@@ -947,7 +1038,7 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double*
     v.table32 = nullptr;
     v.exact_evals = h->exact[GPIRT_BLOCK_THETA];
     if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {
-        if (!h->theta_tab) CU(cudaMalloc((void**)&h->theta_tab, table_bytes));
+        if (!h->theta_tab) CU(dev_malloc((void**)&h->theta_tab, table_bytes));
         if (h->screen && !table_only) {
             // fp32 screening (gpirt_set_screen): the table holds (fp32 term, error bound) pairs — the same bytes, a quarter of the
             // arithmetic to build — and the few proposals it cannot decide are evaluated in fp64 on the fly
@@ -1135,11 +1226,11 @@ int gpirt_K(int device, const double* x1, int64_t n1, const double* x2, int64_t 
     if (!x1 || !x2 || !sds3 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K: bad arguments");
     TRY(select_device(device));
     double *d1, *d2, *dK;
-    CU(cudaMalloc((void**)&d1, n1 * 8)); CU(cudaMalloc((void**)&d2, n2 * 8)); CU(cudaMalloc((void**)&dK, n1 * n2 * 8));
+    CU(dev_malloc((void**)&d1, n1 * 8)); CU(dev_malloc((void**)&d2, n2 * 8)); CU(dev_malloc((void**)&dK, n1 * n2 * 8));
     CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
     CU(build_K(0, d1, (int)n1, d2, (int)n2, sds3, dK, (int)n1, 0.0));
     CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
-    cudaFree(d1); cudaFree(d2); cudaFree(dK);
+    dev_free(d1); dev_free(d2); dev_free(dK);
     return GPIRT_OK;
 }
 int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, double os, double ls, const double* tsds2,
@@ -1147,12 +1238,12 @@ int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int
     if (!x1 || !x2 || !tsds2 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K_time: bad arguments");
     TRY(select_device(device));
     double *d1, *d2, *dK;
-    CU(cudaMalloc((void**)&d1, n1 * 8)); CU(cudaMalloc((void**)&d2, n2 * 8)); CU(cudaMalloc((void**)&dK, n1 * n2 * 8));
+    CU(dev_malloc((void**)&d1, n1 * 8)); CU(dev_malloc((void**)&d2, n2 * 8)); CU(dev_malloc((void**)&dK, n1 * n2 * 8));
     CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
     CU(cudaMemset(dK, 0, n1 * n2 * 8));  // an unknown KERNEL string leaves the matrix untouched in the reference; here zeros
     CU(build_K_time(0, d1, (int)n1, d2, (int)n2, os, ls, tsds2[0], tsds2[1], kernel, dK, (int)n1));
     CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
-    cudaFree(d1); cudaFree(d2); cudaFree(dK);
+    dev_free(d1); dev_free(d2); dev_free(dK);
     return GPIRT_OK;
 }
 int gpirt_chol(int device, const double* A, int64_t n, double* L) {
@@ -1160,13 +1251,13 @@ int gpirt_chol(int device, const double* A, int64_t n, double* L) {
     TRY(select_device(device));
     const int ld = pad_ld(n);
     double* dA; int* info; int hinfo = 0;
-    CU(cudaMalloc((void**)&dA, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&info, 4 * (1 + chol_ws_ints((int)n))));
+    CU(dev_malloc((void**)&dA, (size_t)ld * n * 8)); CU(dev_malloc((void**)&info, 4 * (1 + chol_ws_ints((int)n))));
     CU(cudaMemset(dA, 0, (size_t)ld * n * 8)); CU(cudaMemset(info, 0, 4));
     CU(cudaMemcpy2D(dA, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
     CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1));
     CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(&hinfo, info, 4, cudaMemcpyDeviceToHost));
-    cudaFree(dA); cudaFree(info);
+    dev_free(dA); dev_free(info);
     if (hinfo) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed at leading minor %d", hinfo);
     return GPIRT_OK;
 }
@@ -1175,14 +1266,14 @@ int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, 
     TRY(select_device(device));
     const int ld = pad_ld(n);
     double *dL, *dX;
-    CU(cudaMalloc((void**)&dL, (size_t)ld * n * 8)); CU(cudaMalloc((void**)&dX, (size_t)ld * nrhs * 8));
+    CU(dev_malloc((void**)&dL, (size_t)ld * n * 8)); CU(dev_malloc((void**)&dX, (size_t)ld * nrhs * 8));
     CU(cudaMemset(dL, 0, (size_t)ld * n * 8)); CU(cudaMemset(dX, 0, (size_t)ld * nrhs * 8));
     CU(cudaMemcpy2D(dL, (size_t)ld * 8, L, n * 8, n * 8, n, cudaMemcpyHostToDevice));
     CU(cudaMemcpy2D(dX, (size_t)ld * 8, X, n * 8, n * 8, nrhs, cudaMemcpyHostToDevice));
     CU(trsm_left_lower(0, dL, ld, (int)n, dX, ld, (int)nrhs));
     CU(trsm_left_lower_t(0, dL, ld, (int)n, dX, ld, (int)nrhs));
     CU(cudaMemcpy2D(out, n * 8, dX, (size_t)ld * 8, n * 8, nrhs, cudaMemcpyDeviceToHost));
-    cudaFree(dL); cudaFree(dX);
+    dev_free(dL); dev_free(dX);
     return GPIRT_OK;
 }
 
@@ -1209,14 +1300,14 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
     if (draw_beta) {
         if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "init_draw: beta has 3 rows in gpirtMCMC");
         double* d_means = nullptr;
-        CU(cudaMalloc((void**)&d_means, 3 * (size_t)h->m_total * 8));
+        CU(dev_malloc((void**)&d_means, 3 * (size_t)h->m_total * 8));
         if (beta_prior_means) CU(cudaMemcpyAsync(d_means, beta_prior_means, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, st));
         else CU(cudaMemsetAsync(d_means, 0, 3 * (size_t)h->m_total * 8, st));
         k_init_beta<<<(h->m_total + 127) / 128, 128, 0, st>>>(h->beta, d_means, h->sds, h->m_total, h->key());
         ++g_kernel_launches;
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(st));
-        cudaFree(d_means);
+        dev_free(d_means);
     }
     if (draw_f && h->m_local > 0) {
         if (!h->chol_valid) TRY(do_update_cholesky(h));
@@ -1325,7 +1416,7 @@ int gpirt_panel_create(const gpirt_config* cfg, gpirt_panel** out) {
             for (int i = j + 1; i < H; ++i) cj[i] /= d;
             for (int i = 0; i < j; ++i) cj[i] = 0.0;
         }
-        if (cudaMalloc((void**)&p->d_L_time, (size_t)H * H * 8) != cudaSuccess || cudaMalloc((void**)&p->d_ses, (size_t)H * sizeof(ThetaSession)) != cudaSuccess ||
+        if (dev_malloc((void**)&p->d_L_time, (size_t)H * H * 8) != cudaSuccess || dev_malloc((void**)&p->d_ses, (size_t)H * sizeof(ThetaSession)) != cudaSuccess ||
             cudaMemcpy(p->d_L_time, L.data(), (size_t)H * H * 8, cudaMemcpyHostToDevice) != cudaSuccess) {
             fail(GPIRT_ERR_CUDA, "panel: device allocation failed");
             return panel_fail_free(p, GPIRT_ERR_CUDA);
@@ -1341,8 +1432,8 @@ int gpirt_panel_destroy(gpirt_panel* p) {
         if (s != p->ses[0]) { cudaSetDevice(s->cfg.device); quiesce(s); cudaStreamSynchronize(s->stream); s->own_stream = false; }
     }
     for (size_t h = p->ses.size(); h-- > 0;) gpirt_destroy(p->ses[h]);
-    if (p->d_L_time) cudaFree(p->d_L_time);
-    if (p->d_ses) cudaFree(p->d_ses);
+    if (p->d_L_time) dev_free(p->d_L_time);
+    if (p->d_ses) dev_free(p->d_ses);
     delete p;
     return GPIRT_OK;
 }
@@ -1497,11 +1588,11 @@ int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int r
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
     double* d = nullptr;
-    CU(cudaMalloc((void**)&d, (size_t)rows * cols * 8));
+    CU(dev_malloc((void**)&d, (size_t)rows * cols * 8));
     CU(launch_gen_normals(h->stream, d, rows, rows, cols, h->key(), stream, unit0));
     CU(cudaMemcpyAsync(out, d, (size_t)rows * cols * 8, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    cudaFree(d);
+    dev_free(d);
     return GPIRT_OK;
 }
 
@@ -1520,13 +1611,13 @@ extern "C" int gpirt_debug_probit(int device, const double* x, int n, double* ph
     if (!x || !phi_out || !log_out || n < 1) return fail(GPIRT_ERR_INVALID, "debug_probit: bad arguments");
     TRY(select_device(device));
     double* d = nullptr;
-    CU(cudaMalloc((void**)&d, (size_t)3 * n * 8));
+    CU(dev_malloc((void**)&d, (size_t)3 * n * 8));
     CU(cudaMemcpy(d, x, (size_t)n * 8, cudaMemcpyHostToDevice));
     k_debug_probit<<<(n + 255) / 256, 256>>>(d, n, d + n, d + 2 * (size_t)n);
     CU(cudaGetLastError());
     CU(cudaMemcpy(phi_out, d + n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(log_out, d + 2 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
-    cudaFree(d);
+    dev_free(d);
     return GPIRT_OK;
 }
 
@@ -1545,7 +1636,7 @@ extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau
     if (!g || !tau_lo || !tau_hi || !t32 || !e32 || !t64 || n < 1) return fail(GPIRT_ERR_INVALID, "debug_cell32: bad arguments");
     TRY(select_device(device));
     double* d = nullptr;
-    CU(cudaMalloc((void**)&d, (size_t)6 * n * 8));
+    CU(dev_malloc((void**)&d, (size_t)6 * n * 8));
     CU(cudaMemcpy(d, g, (size_t)n * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d + n, tau_lo, (size_t)n * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d + 2 * (size_t)n, tau_hi, (size_t)n * 8, cudaMemcpyHostToDevice));
@@ -1554,6 +1645,6 @@ extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau
     CU(cudaMemcpy(t32, d + 3 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(e32, d + 4 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(t64, d + 5 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
-    cudaFree(d);
+    dev_free(d);
     return GPIRT_OK;
 }

@@ -394,7 +394,7 @@ cudaError_t launch_theta_table32(cudaStream_t st, const ThetaView& v, float2* ta
 // l + 1024, ...), lanes t, t+256, t+512, t+768 combined as (S_t + S_t+256) + (S_t+512 + S_t+768), then the 8-warp block sum — so a chain
 // does not depend on which one ran (bit-identical for any world size).
 template <int T>
-__global__ void __launch_bounds__(T) k_ess_theta(ThetaView v) {
+__global__ void __launch_bounds__(T, T == 256 ? 4 : 1) k_ess_theta(ThetaView v) {
     static_assert(T == 256 || T == 1024, "virtual-lane scheme");
     __shared__ double s_part[8];
     __shared__ double s_lane[T == 1024 ? 1024 : 1];

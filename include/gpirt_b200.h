@@ -105,6 +105,9 @@ int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, 
 /* ---- lifetime, data, state ---- */
 int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out);
 int gpirt_destroy(gpirt_sampler* h);
+/* Large device blocks of destroyed handles are kept in a per-process cache and handed to the next handle of the same shape (a gpirtMCMC()
+ * call creates and destroys one per chain); this returns them to the driver. */
+int gpirt_release_cached_memory(void);
 int gpirt_set_stream(gpirt_sampler* h, void* cuda_stream);  /* run on the caller's stream (e.g. torch's current stream) */
 int gpirt_set_data_f64(gpirt_sampler* h, const double* y);  /* n x m_total, NaN missing */
 int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y);   /* n x m_total, 0 missing */
