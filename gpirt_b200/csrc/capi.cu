@@ -1039,7 +1039,10 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double*
     v.exact_evals = h->exact[GPIRT_BLOCK_THETA];
     if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {
         if (!h->theta_tab) CU(dev_malloc((void**)&h->theta_tab, table_bytes));
-        if (h->screen && !table_only) {
+        // The bounds add up over the items (~3e-6 per term): at m = 5000 0.8 % of the proposals stay undecided, at m = 40 000 (8 item shards of C3)
+        // 4 %, and an undecided proposal costs two fp64 evaluations of all m items on ONE SM (75 us at m = 40 000) — measured at 8 GPUs the
+        // screened step is then slower than the fp64 table (0.85 + 0.92 ms against 1.03 + 0.45 ms), so it is used up to 12 000 items.
+        if (h->screen && !table_only && h->m_total <= 12000) {
             // fp32 screening (gpirt_set_screen): the table holds (fp32 term, error bound) pairs — the same bytes, a quarter of the
             // arithmetic to build — and the few proposals it cannot decide are evaluated in fp64 on the fly
             SEC(h, "theta_table", CU(launch_theta_table32(h->stream, v, (float2*)h->theta_tab)));
