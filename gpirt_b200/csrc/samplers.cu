@@ -8,6 +8,8 @@
 //     draw_theta        src/draw-theta.cpp:4-84,112-170
 // The shrink-bracket loop runs entirely on chip: the only per-proposal traffic is the re-read of the
 // item's f / nu / y columns, which stay L1/L2 resident between proposals.
+#include <cstdlib>
+#include <algorithm>
 #include "samplers.cuh"
 
 #include "probit.cuh"
@@ -81,13 +83,9 @@ __device__ __forceinline__ void block_sum2(double& a, double& b, double (*s_part
 }
 
 template <int MODE, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
+__device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, double* tau, double* s_part, double (*s_part2)[WARPS]) {
     constexpr int T = WARPS * 32;
-    __shared__ double tau[MAX_C + 1];
-    __shared__ double s_part[WARPS];
-    __shared__ double s_part2[2][WARPS];
     const int tid = threadIdx.x;
-    const int j = blockIdx.x;
     const int J = v.item0 + j;
     const int C = v.C;
     for (int c = tid; c <= C; c += T) tau[c] = v.thr[(size_t)J * (C + 1) + c];
@@ -252,16 +250,40 @@ __global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
     }
 }
 
+// One CTA per item when the grid covers the items; with a smaller grid (launch_ess_mode: beta / threshold blocks, which share the SMs with the
+// theta-only chain on the side stream) every CTA walks the items with the grid's stride. An item's arithmetic does not depend on which CTA ran it.
+template <int MODE, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
+    __shared__ double tau[MAX_C + 1];
+    __shared__ double s_part[WARPS];
+    __shared__ double s_part2[2][WARPS];
+    for (int j = blockIdx.x; j < v.m_local; j += gridDim.x) {
+        ess_one_item<MODE, WARPS>(v, j, tau, s_part, s_part2);
+        __syncthreads();  // tau / s_part are reused by the next item
+    }
+}
+
 // warps per item: each thread should own <= ~8 cells of a pass
 static int item_warps(int n) { return n <= 256 ? 1 : (n <= 1024 ? 4 : (n <= 4096 ? 8 : 16)); }
 
+int g_ess_threads_per_sm = -1;  // beta / threshold ESS: resident threads per SM the grid is sized for (0: one CTA per item); -1: environment / default
+
 template <int MODE>
 static void launch_ess_mode(cudaStream_t st, const ItemView& v) {
-    switch (item_warps(v.n)) {
-        case 1: k_ess_items<MODE, 1><<<v.m_local, 32, 0, st>>>(v); break;
-        case 4: k_ess_items<MODE, 4><<<v.m_local, 128, 0, st>>>(v); break;
-        case 8: k_ess_items<MODE, 8><<<v.m_local, 256, 0, st>>>(v); break;
-        default: k_ess_items<MODE, 16><<<v.m_local, 512, 0, st>>>(v); break;
+    if (g_ess_threads_per_sm < 0) {
+        const char* e = getenv("GPIRT_ESS_THREADS_PER_SM");
+        g_ess_threads_per_sm = e ? atoi(e) : 0;
+    }
+    const int warps = item_warps(v.n);
+    int grid = v.m_local;
+    // The beta and threshold blocks run while the theta-only chain of the next sweep (Cholesky panels, small GEMMs) is on the side stream: a grid
+    // that leaves a share of every SM's thread slots free lets those latency-bound kernels start at once instead of waiting for an ESS CTA to retire.
+    if (MODE != IB_F && g_ess_threads_per_sm > 0) grid = std::min(grid, 148 * std::max(1, g_ess_threads_per_sm / (warps * 32)));
+    switch (warps) {
+        case 1: k_ess_items<MODE, 1><<<grid, 32, 0, st>>>(v); break;
+        case 4: k_ess_items<MODE, 4><<<grid, 128, 0, st>>>(v); break;
+        case 8: k_ess_items<MODE, 8><<<grid, 256, 0, st>>>(v); break;
+        default: k_ess_items<MODE, 16><<<grid, 512, 0, st>>>(v); break;
     }
     ++g_kernel_launches;
 }
