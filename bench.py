@@ -203,7 +203,7 @@ def ours(args):
     ev = {b: S.diag(b)[0] for b in ("f", "theta", "beta", "thr")}
     inner = S.S if hasattr(S, "S") else S
     ex = {b: inner.exact_evals(b) for b in ("f", "beta", "thr")}
-    screened = {b: round(1.0 - float((ex[b][ev[b] > 0] - 1).sum()) / max(1.0, float((ev[b][ev[b] > 0] - 1).sum())), 4) for b in ex}
+    screened = {b: round(1.0 - float(np.maximum(ex[b][ev[b] > 0] - 1, 0).sum()) / max(1.0, float((ev[b][ev[b] > 0] - 1).sum())), 4) for b in ex}
     ext = inner.exact_evals("theta")  # theta step: the current state is screened too; an undecided proposal costs two exact evaluations the first time
     sel = ev["theta"] > 0
     screened["theta"] = round(1.0 - float(np.maximum(ext[sel] - 1, 0).sum()) / max(1.0, float((ev["theta"][sel] - 1).sum())), 4)

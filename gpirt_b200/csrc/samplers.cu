@@ -179,44 +179,70 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
     int overrun = 0;
     uint32_t k = 0;
     const double u = v.us.get(v.key, ustream, J, k++, &overrun);
-    const double ll_cur = loglik(1.0, 0.0, true);
-    const double log_y = __dadd_rn(ll_cur, log(u));
+    const double log_u = log(u);
+    // the point (ce, se) of the ellipse as the block's parameters: beta' (registers) or tau' = delta_to_threshold(delta') (shared)
+    auto set_params = [&](double ce_, double se_) {
+        if (MODE == IB_BETA) {
+            pb0 = __dadd_rn(__dmul_rn(b0, ce_), __dmul_rn(nu_small[0], se_));
+            pb1 = __dadd_rn(__dmul_rn(b1, ce_), __dmul_rn(nu_small[1], se_));
+            pb2 = __dadd_rn(__dmul_rn(b2, ce_), __dmul_rn(nu_small[2], se_));
+        }
+        if (MODE == IB_THR) {
+            __syncthreads();
+            if (tid == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
+                tau[1] = __dadd_rn(__dmul_rn(delta[0], ce_), __dmul_rn(nu_small[0], se_));
+                for (int q = 1; q < C - 1; ++q)
+                    tau[q + 1] = __dadd_rn(tau[q], exp(__dadd_rn(__dmul_rn(delta[q], ce_), __dmul_rn(nu_small[q], se_))));
+            }
+            __syncthreads();
+        }
+    };
+    // Unscreened: log_y = ll(current) + log(u) in fp64, every proposal in fp64. Screened: the current state is evaluated in fp32 with its bound
+    // like the proposals, and a proposal is decided when |S' - S0 - log u| exceeds both bounds; only an undecided proposal makes the kernel
+    // compute the two fp64 values (the current state's once) — the decision is the fp64 decision either way.
+    double S0 = 0.0, E0 = 0.0, log_y = 0.0;
+    bool have_exact0 = false;
+    int evals = 1, n_exact = 0;  // n_exact: evaluations that ran in fp64
+    if (v.screen) loglik32(1.0, 0.0, S0, E0);
+    else { log_y = __dadd_rn(loglik(1.0, 0.0, true), log_u); have_exact0 = true; n_exact = 1; }
     double eps_min = 0.0, eps_max = TWO_PI_R;
     double eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ustream, J, k++, &overrun)));
     eps_min = __dsub_rn(eps, TWO_PI_R);
-    int evals = 1, n_exact = 1;  // n_exact: evaluations that ran in fp64 (the current state always does)
     double margin = CUDART_INF;
     double ce = 1.0, se = 0.0;
     bool accepted = false;
     for (int it = 0; it < ESS_MAX_PROPOSALS; ++it) {
         ce = cos(eps);
         se = sin(eps);
-        if (MODE == IB_BETA) {
-            pb0 = __dadd_rn(__dmul_rn(b0, ce), __dmul_rn(nu_small[0], se));
-            pb1 = __dadd_rn(__dmul_rn(b1, ce), __dmul_rn(nu_small[1], se));
-            pb2 = __dadd_rn(__dmul_rn(b2, ce), __dmul_rn(nu_small[2], se));
-        }
-        if (MODE == IB_THR) {
-            __syncthreads();
-            if (tid == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
-                tau[1] = __dadd_rn(__dmul_rn(delta[0], ce), __dmul_rn(nu_small[0], se));
-                for (int q = 1; q < C - 1; ++q)
-                    tau[q + 1] = __dadd_rn(tau[q], exp(__dadd_rn(__dmul_rn(delta[q], ce), __dmul_rn(nu_small[q], se))));
-            }
-            __syncthreads();
-        }
+        set_params(ce, se);
         ++evals;
         bool decided = false, accept = false;
         if (v.screen) {
             double L32, E32;
             loglik32(ce, se, L32, E32);
-            // fp32 rounding of the E accumulation (relative 1e-5 at most) and the fp64 pass's own summation noise
-            const double Eb = E32 * 1.00002 + 1e-10 * (fabs(L32) + 1.0);
-            if (L32 - Eb > log_y) { decided = true; accept = true; }
-            else if (L32 + Eb < log_y) { decided = true; }
-            if (decided) margin = fmin(margin, fabs(L32 - log_y) - Eb);  // a lower bound of the true margin
+            const double d = L32 - (S0 + log_u);
+            // fp32 rounding of the E accumulations (relative 1e-5 at most) and the fp64 passes' own summation noise
+            const double Eb = (E32 + E0) * 1.00002 + 1e-10 * (fabs(L32) + fabs(S0) + 1.0);
+            if (d > Eb) { decided = true; accept = true; }
+            else if (d < -Eb) { decided = true; }
+            if (decided) margin = fmin(margin, fabs(d) - Eb);  // a lower bound of the true margin
         }
         if (!decided) {
+            if (!have_exact0) {  // the current state in fp64: its own parameters for the pass, then the proposal's again
+                if (MODE == IB_BETA) { pb0 = b0; pb1 = b1; pb2 = b2; }
+                if (MODE == IB_THR) {
+                    __syncthreads();
+                    if (tid == 0) {
+                        tau[1] = delta[0];
+                        for (int q = 1; q < C - 1; ++q) tau[q + 1] = __dadd_rn(tau[q], exp(delta[q]));
+                    }
+                    __syncthreads();
+                }
+                log_y = __dadd_rn(loglik(1.0, 0.0, true), log_u);
+                set_params(ce, se);
+                have_exact0 = true;
+                ++n_exact;
+            }
             const double llp = loglik(ce, se, false);  // identical on every thread of the CTA
             margin = fmin(margin, fabs(llp - log_y));
             accept = llp > log_y;
