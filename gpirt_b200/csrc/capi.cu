@@ -280,6 +280,11 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_W, cudaEventDisableTiming));
+        if (h->n >= 4096) {  // look-ahead of the two-level Cholesky (linalg.cuh, CholAux): the bulk of a trailing update runs beside the next panels
+            CU(cudaStreamCreateWithPriority(&h->chol_aux.helper, cudaStreamNonBlocking, lo));  // below the side stream: the panels must not queue behind the bulk GEMM's pending tiles
+            CU(cudaEventCreateWithFlags(&h->chol_aux.ev_panel, cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&h->chol_aux.ev_rest, cudaEventDisableTiming));
+        }
         // milestones of chol(K): rows 50 %, 75 %, 87.5 %, 93.75 % and 100 % (multiples of the panel width), see do_draw_f
         int prev = 0;
         for (double frac : {0.5, 0.75, 0.875, 0.9375, 1.0}) {
@@ -366,6 +371,9 @@ int gpirt_destroy(gpirt_sampler* h) {
     for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
     for (int c = 0; c < h->Lpost_rows.count; ++c) cudaEventDestroy(h->Lpost_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
+    if (h->chol_aux.helper) { cudaStreamSynchronize(h->chol_aux.helper); cudaStreamDestroy(h->chol_aux.helper); }
+    if (h->chol_aux.ev_panel) cudaEventDestroy(h->chol_aux.ev_panel);
+    if (h->chol_aux.ev_rest) cudaEventDestroy(h->chol_aux.ev_rest);
     for (char*& pa : h->peer_arena)
         if (pa) { cudaIpcCloseMemHandle(pa); pa = nullptr; }
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
@@ -835,7 +843,8 @@ static int need_data(gpirt_sampler* h) {
 static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
     const bool marks = st == h->side && h->L_rows.count > 0;
-    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws, marks ? &h->L_rows : nullptr)));
+    SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws, marks ? &h->L_rows : nullptr,
+                                                      h->chol_aux.helper ? &h->chol_aux : nullptr)));
     h->pending_rows = marks;
     h->chol_valid = true;
     h->shared_valid = false;

@@ -497,8 +497,11 @@ __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
     if (i < n && j < n && i < j) A[(size_t)j * ld + i] = 0.0;
 }
 
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks) {
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks,
+                               const CholAux* aux) {
     int next_mark = 0;
+    static const int lookahead_env = getenv("GPIRT_CHOL_LOOKAHEAD") ? atoi(getenv("GPIRT_CHOL_LOOKAHEAD")) : 1;
+    bool rest_pending = false;  // a part of a trailing update is in flight on the helper stream
     constexpr int NB = CHOL_NB;
     cudaError_t e0 = cudaMemsetAsync(readers_ws, 0, chol_ws_ints(n) * sizeof(int), st);
     if (e0 != cudaSuccess) return e0;
@@ -536,14 +539,37 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
         const int rows_t = n - o0 - ob;
         if (OB != NB && rows_t > 0) {
             double* P = A + (size_t)o0 * ld + (o0 + ob);  // rows below the outer block, its ob columns
+            const bool split = aux && aux->helper && lookahead_env && rows_t > OB;
+            cudaError_t e;
+            if (split) {  // the outer block's panels are done: the helper stream may start on the columns beyond the next outer block
+                if ((e = cudaEventRecord(aux->ev_panel, st)) != cudaSuccess) return e;
+            }
+            if (rest_pending) {  // the previous block's share on the helper stream wrote the entries this update adds to
+                if ((e = cudaStreamWaitEvent(st, aux->ev_rest, 0)) != cudaSuccess) return e;
+                rest_pending = false;
+            }
             GemmArgs g{};
-            g.M = rows_t; g.N = rows_t; g.K = ob;
+            g.M = rows_t; g.N = split ? OB : rows_t; g.K = ob;
             g.A = P; g.lda = ld; g.B = P; g.ldb = ld;
             g.C = A + (size_t)(o0 + ob) * ld + (o0 + ob); g.ldc = ld;
             g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
-            cudaError_t e = gemm_f64(st, false, true, g);
-            if (e != cudaSuccess) return e;
+            if ((e = gemm_f64(st, false, true, g)) != cudaSuccess) return e;
+            if (split) {
+                if ((e = cudaStreamWaitEvent(aux->helper, aux->ev_panel, 0)) != cudaSuccess) return e;
+                GemmArgs r{};
+                r.M = rows_t - OB; r.N = rows_t - OB; r.K = ob;
+                r.A = P + OB; r.lda = ld; r.B = P + OB; r.ldb = ld;
+                r.C = A + (size_t)(o0 + ob + OB) * ld + (o0 + ob + OB); r.ldc = ld;
+                r.alpha = -1.0; r.beta = 1.0; r.lower_only = 1;
+                if ((e = gemm_f64(aux->helper, false, true, r)) != cudaSuccess) return e;
+                if ((e = cudaEventRecord(aux->ev_rest, aux->helper)) != cudaSuccess) return e;
+                rest_pending = true;
+            }
         }
+    }
+    if (rest_pending) {
+        cudaError_t e = cudaStreamWaitEvent(st, aux->ev_rest, 0);
+        if (e != cudaSuccess) return e;
     }
     dim3 grid((n + 255) / 256, n);
     k_zero_upper<<<grid, 256, 0, st>>>(A, ld, n);

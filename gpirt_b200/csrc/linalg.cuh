@@ -26,7 +26,15 @@ struct CholMilestones {
     int rows[6] = {0, 0, 0, 0, 0, 0};
     cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
 };
-cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr);
+// Look-ahead for the two-level factorisation (n >= 4096): a helper stream and two events owned by the caller. With it the K = OB trailing update of
+// an outer block is split by columns: the next outer block's columns are updated on `st`, whose latency-bound panel chain then runs while the rest
+// of the update (the bulk of the flops) goes to the helper stream. Same tiles and k ranges as the single launch: bit-identical factor.
+struct CholAux {
+    cudaStream_t helper = nullptr;
+    cudaEvent_t ev_panel = nullptr, ev_rest = nullptr;
+};
+cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr,
+                               const CholAux* aux = nullptr);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);

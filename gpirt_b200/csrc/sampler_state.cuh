@@ -47,6 +47,7 @@ struct gpirt_sampler {
     cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_W = nullptr, ev_shared = nullptr;
     gpirt::CholMilestones L_rows;  // leading row blocks of L signalled while chol(K) is still running on the side stream (nu = L Z starts under it)
     bool pending_rows = false;
+    gpirt::CholAux chol_aux;       // helper stream + events of the two-level Cholesky's look-ahead (n >= 4096)
     gpirt::CholMilestones Lpost_rows;  // the same for chol(K_post): the f* noise term Z*^T L_post^T is launched in column slices under it
     bool pending_post_rows = false;
     bool overlap = true;           // gpirt_set_overlap; profiling forces the serial order

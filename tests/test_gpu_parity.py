@@ -434,6 +434,26 @@ def test_chol_large_matrix_two_level_blocking_backward_error():
 
 
 @pytest.mark.gpu
+def test_cholesky_cache_with_look_ahead_equals_the_plain_two_level_factorisation_bit_for_bit():
+    """A sampler with n >= 4096 factorises K with the look-ahead schedule (the bulk of every K = 256 trailing update on a helper stream beside the
+    next panels, linalg.cuh CholAux); gpirt_chol() on the same matrix runs the plain two-level order. Same tiles, same k ranges: identical L."""
+    import gpirt_b200 as g
+
+    n, m, C = 4500, 8, 3
+    P = make_problem(n, m, C, seed=41, on_grid=True)
+    S = g.Sampler(n, m, C)
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+    S.update_cholesky_cache()
+    L = S.get_L()
+    th = S.get_state(f=False)["theta"]
+    A = g.K(th, th, P["beta_prior_sds"][:, 0]) + 1e-6 * np.eye(n)
+    assert np.array_equal(L, g.chol(A))
+    assert np.max(np.abs(L @ L.T - A)) <= 1e-13 * np.max(np.abs(A)) * 8
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged")])
 def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_streams(n, m, C, name):
     """Whole sweeps (gpirt_sweep: overlapped schedule, fp32 screening, block inverse) against the oracle's sweep on the SAME Philox streams, at the
