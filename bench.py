@@ -242,6 +242,10 @@ def ours(args):
                 "groups": gemm_groups, "ms_per_sweep": round(gemm_ms, 4), "call_sites_per_sweep": gemm_launches,
                 "share_of_sweep": round(gemm_ms / sum(per_sweep.values()), 3),
                 "algorithmic_flops_per_sweep": gemm_flops,
+                "ncu_share_note": "ncu launch list of the same sweep (profiles/r01_launches_v9_summary.txt; cold-cache, serialised): the kernel's launches outside "
+                                  "the Cholesky (templates <...,0,0>, <...,1,0>, <...,1,1>: 70 launches) take 41 % of the summed kernel time, its 184 K = 64 "
+                                  "trailing updates inside chol_K (<...,0,1>, ~11 us each, counted in the chol_K group here) another 10 %; the live share above "
+                                  "is lower because the latency-bound Cholesky panels (22 % under ncu) are not inflated by serialisation and cold caches there",
                 "note": "useful flops (triangular operands counted once) over the summed durations of the kernel's launches; ncu shows the DMMA pipe "
                         "90-91 % busy in these launches. The ESS / likelihood groups in `kernels` are issue-bound on fp64+fp32 arithmetic (2 Phi + 1 log "
                         "per cell and evaluation), not HBM-bound: their algorithmic GB/s stays far below the copy peak by construction."}
