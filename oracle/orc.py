@@ -422,3 +422,96 @@ class Panel:
         for S in self.S:  # src/gpirtMCMC.cpp:324-331: one running sum over (h, j); per session here, then across sessions in order
             ll += S.total_ll()
         return ll
+
+
+class ConstantPanel(Panel):
+    """CPU oracle at constant_IRF == 1 (one item response function shared by all sessions), restated from src/draw-f.cpp:84-139,
+    src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96,181-205 and the constant branch of the initialisation (src/gpirtMCMC.cpp:164-200).
+    It is the horizon > 1 panel plus one STACKED sampler T over the n*H (respondent, session) rows:
+      draw_f          one ESS per item on the stacked column, nu = chol(K(theta_stacked) + 1e-6 I) z, thresholds of session 0,
+                      mean = the sessions' own mu_h stacked (mu_h = X_h beta_h; in the first sweep X_h beta_0, as the initialisation leaves it)
+      draw_fstar      inducing-point posterior (Sampler.draw_fstar_cst) from the stacked f, mu* of session 0, the same f* for every session
+      draw_theta, f <- f* gather, draw_beta, mu / mu* update: per session, unchanged (they take no constant_IRF argument)
+      draw_threshold  one ESS per item over all sessions' cells against session 0's thresholds, result copied to every session
+    TEST INFRASTRUCTURE (CPU); the CUDA path does not implement constant_IRF == 1 yet (GPIRT_ERR_UNSUPPORTED)."""
+
+    def __init__(self, y, C_, beta_prior_sds, theta_prior_sds=None, theta_os=1.0, theta_ls=10.0, KERNEL="Matern"):
+        super().__init__(y, C_, beta_prior_sds, theta_prior_sds, theta_os, theta_ls, KERNEL)
+        y = np.asfortranarray(np.asarray(y, dtype=np.float64))
+        n, m, H = y.shape
+        ystack = np.asfortranarray(np.concatenate([y[:, :, h] for h in range(H)], axis=0))  # row h*n + i, src/draw-f.cpp:94-103
+        tps = np.zeros((2, n * H)) if theta_prior_sds is None else np.tile(np.asarray(theta_prior_sds), (1, H))
+        self.T = Sampler(ystack, C_, beta_prior_sds, tps)
+        lib().orc_share_mts(self.T._h, self.S[0]._h)
+        lib().orc_draw_fstar_cst.argtypes = None
+        lib().orc_set_mu.argtypes = None
+
+    # ---- helpers ----
+    def _stack(self, key):
+        return np.asfortranarray(np.concatenate([S.state()[key] if key != "mu" else S.mu()[0] for S in self.S], axis=0))
+
+    def _load_stacked(self, thr0):
+        st0 = self.S[0].state()
+        theta = np.concatenate([S.state()["theta"] for S in self.S])
+        self.T.set_state(theta=theta, beta=st0["beta"], f=self._stack("f"), thr=thr0)
+        self.T.compute_mu()  # mu* = X* beta_0 (src/draw-fstar.cpp:114 uses mu_star.slice(0)); mu is replaced by the sessions' own below
+        mu = self._stack("mu")
+        lib().orc_set_mu(self.T._h, _p(mu))
+        self._keep_mu = mu
+
+    def set_mu(self, h, mu):
+        mu = _F(mu)
+        lib().orc_set_mu(self.S[h]._h, _p(mu))
+
+    def init_constant(self, theta, beta0, f0, thr):
+        """State after the constant branch of the initialisation: beta drawn for session 0 only (the other slices stay zero), every session's
+        mu = X_h beta_0, the same f0 columns in every session (src/gpirtMCMC.cpp:164-200); mu* per session from its own beta slice (:214-216)."""
+        H = self.H
+        theta = np.asarray(theta)
+        for h, S in enumerate(self.S):
+            S.set_state(theta=theta[:, h], beta=beta0 if h == 0 else np.zeros_like(beta0), f=f0, thr=np.asarray(thr)[:, :, h])
+            S.compute_mu()  # mu* = X* beta_h
+            X = np.stack([np.ones(self.n), theta[:, h], theta[:, h] ** 2], axis=1)
+            self.set_mu(h, X @ beta0)
+        return H
+
+    def draw_f(self, src):
+        self._load_stacked(self.S[0].state()["thr"])
+        assert self.T.update_cholesky() == 0  # chol(K(theta_constant) + 1e-6 I), src/draw-f.cpp:106-108
+        self.T.draw_f(src)
+        f = self.T.state()["f"]
+        for h, S in enumerate(self.S):
+            S.set_state(f=f[h * self.n:(h + 1) * self.n])
+
+    def draw_fstar(self, src):
+        self._load_stacked(self.S[0].state()["thr"])
+        info = lib().orc_draw_fstar_cst(self.T._h, C.byref(src))
+        fs = self.T.state()["fstar"]
+        for S in self.S:
+            S.set_state(fstar=fs)
+        return info
+
+    def draw_threshold(self, src):
+        self._load_stacked(self.S[0].state()["thr"])
+        self.T.draw_threshold(src)
+        thr = self.T.state()["thr"]
+        for S in self.S:
+            S.set_state(thr=thr)
+
+    def sweep(self, src_of):
+        """One sweep (src/gpirtMCMC.cpp:267-331) at constant_IRF == 1. src_of(block, h): h is None for the stacked blocks and the GP theta step.
+        mu is NOT recomputed at the top: it is what the previous sweep (or the initialisation) left."""
+        self.draw_f(src_of("f", None))
+        if self.draw_fstar(src_of("fstar", None)) != 0:
+            return 2
+        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime == 1 else src_of("theta", None))
+        for S in self.S:
+            S.gather_f()
+        for h, S in enumerate(self.S):
+            S.draw_beta(src_of("beta", h))
+        for S in self.S:
+            S.compute_mu()
+            if S.update_cholesky() != 0:
+                return 1
+        self.draw_threshold(src_of("thr", None))
+        return 0

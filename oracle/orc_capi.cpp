@@ -148,6 +148,9 @@ int orc_num_threads(void* h) { return int(static_cast<Sampler*>(h)->mts.size());
 void orc_draw_f(void* h, const orc_src* c, const double* nu) { Sampler* S = static_cast<Sampler*>(h); S->draw_f(to_src(S, c, B_F), nu); }
 int orc_draw_fstar(void* h, const orc_src* c) { Sampler* S = static_cast<Sampler*>(h); return S->draw_fstar(to_src(S, c, B_FSTAR)); }
 // horizon > 1: session `dst` consumes the ThreadRNGs of `src` (one ws_pool for all sessions, src/gpirtMCMC.cpp:90)
+int orc_draw_fstar_cst(void* h, const orc_src* c) { Sampler* S = static_cast<Sampler*>(h); return S->draw_fstar_cst(to_src(S, c, B_FSTAR)); }
+// constant-IRF panel: the stacked sampler's mean is assembled from the sessions' own mu = X_h beta_h (src/draw-f.cpp:93-104)
+void orc_set_mu(void* h, const double* mu) { Sampler* S = static_cast<Sampler*>(h); S->mu.assign(mu, mu + S->n * S->m); }
 void orc_share_mts(void* dst, void* src) { static_cast<Sampler*>(dst)->mts_shared = &static_cast<Sampler*>(src)->mts; }
 void orc_panel_draw_theta(void** hs, uint64_t H, int regime, const double* L_time, const orc_src* cs) {
     std::vector<Sampler*> S(H);

@@ -197,6 +197,82 @@ int Sampler::draw_fstar(const Src& s) {
     return 0;
 }
 
+// arma::interp1(X, Y, XI, YI, "linear") as the reference uses it (src/draw-fstar.cpp:79-80): X sorted, duplicated abscissae dropped (the first
+// in sorted order is kept; with std::stable_sort that is the lowest index — Armadillo's own sort is not stable, so WHICH duplicate it keeps is
+// unspecified there), piecewise-linear in between, NaN outside [min X, max X].
+static void interp1_linear(const double* X, const double* Y, size_t nx, const double* XI, size_t nq, double* YI) {
+    std::vector<size_t> ord(nx);
+    for (size_t i = 0; i < nx; ++i) ord[i] = i;
+    std::stable_sort(ord.begin(), ord.end(), [&](size_t a, size_t b) { return X[a] < X[b]; });
+    std::vector<double> xs, ys;
+    for (size_t k : ord) {
+        if (!xs.empty() && X[k] == xs.back()) continue;
+        xs.push_back(X[k]);
+        ys.push_back(Y[k]);
+    }
+    for (size_t q = 0; q < nq; ++q) {
+        const double x = XI[q];
+        if (xs.empty() || x < xs.front() || x > xs.back()) { YI[q] = std::numeric_limits<double>::quiet_NaN(); continue; }
+        size_t hi = std::lower_bound(xs.begin(), xs.end(), x) - xs.begin();
+        if (xs[hi] == x) { YI[q] = ys[hi]; continue; }
+        const size_t lo = hi - 1;
+        const double w = (x - xs[lo]) / (xs[hi] - xs[lo]);
+        YI[q] = (1.0 - w) * ys[lo] + w * ys[hi];
+    }
+}
+
+int Sampler::draw_fstar_cst(const Src& s) {
+    const size_t N = NGRID, P = 100;  // n_induced_points, src/draw-fstar.cpp:73
+    std::vector<double> tstar(N), tind(P);
+    for (size_t k = 0; k < N; ++k) tstar[k] = grid_value(int(k));
+    const double lo = *std::min_element(theta.begin(), theta.end()), hi = *std::max_element(theta.begin(), theta.end());
+    const double delta = (hi - lo) / double(P - 1);  // arma::linspace: start + i * delta, last element = end
+    for (size_t i = 0; i + 1 < P; ++i) tind[i] = lo + double(i) * delta;
+    tind[P - 1] = hi;
+    std::vector<double> find(P * m);
+    for (size_t j = 0; j < m; ++j) interp1_linear(theta.data(), &f[j * n], n, tind.data(), P, &find[j * P]);  // :77-82
+    std::vector<double> Lc(P * P);
+    K(tind.data(), P, tind.data(), P, sds.data(), Lc.data());  // :85
+    for (size_t k = 0; k < P; ++k) Lc[k + k * P] += 1e-6;
+    int info = chol_lower_blocked(Lc.data(), P);
+    if (info) return info;
+    std::vector<double> kstar(P * N), tmp;
+    K(tind.data(), P, tstar.data(), N, sds.data(), kstar.data());  // :90
+    tmp = kstar;
+    for (size_t k = 0; k < N; ++k) trsv_lower(Lc.data(), P, &tmp[k * P]);  // :92
+    Lpost.assign(N * N, 0.0);
+    K(tstar.data(), N, tstar.data(), N, sds.data(), Lpost.data());  // :93
+#pragma omp parallel for schedule(static)
+    for (size_t b = 0; b < N; ++b)
+        for (size_t a = 0; a < N; ++a) {
+            double acc = 0.0;
+            for (size_t i = 0; i < P; ++i) acc += tmp[a * P + i] * tmp[b * P + i];
+            Lpost[a + b * N] -= acc;  // :94
+        }
+    for (size_t k = 0; k < N; ++k) Lpost[k + k * N] += 1e-6;  // :95
+    info = chol_lower_blocked(Lpost.data(), N);                // :96
+    if (info) return info;
+    diag[B_FSTAR].reset(m);
+    bool over = false;
+#pragma omp parallel for schedule(dynamic) reduction(|| : over)
+    for (size_t j = 0; j < m; ++j) {
+        std::vector<double> alpha(&find[j * P], &find[j * P] + P), z(N), dz(N);
+        double_solve(Lc.data(), P, alpha.data());  // :113
+        bool o = with_rng(s, j, N, [&](UnitRng& rng) {
+            for (size_t k = 0; k < N; ++k) z[k] = rng.norm();
+        });
+        over = over || o;
+        gemv(Lpost.data(), N, N, z.data(), dz.data());
+        for (size_t k = 0; k < N; ++k) {
+            double acc = 0.0;
+            for (size_t i = 0; i < P; ++i) acc += kstar[k * P + i] * alpha[i];
+            fstar[k + j * N] = (acc + mu_star[k + j * N]) + dz[k];  // :114,117 (mu_star of session 0)
+        }
+    }
+    diag[B_FSTAR].overrun = over;
+    return 0;
+}
+
 // compute_ll_sparse (src/draw-theta.cpp:4-24) for respondent i at a raw theta value
 static inline double theta_ll(const Sampler& S, size_t i, double theta, const double* fst, const double* must, const double* thr = nullptr) {
     const size_t N = NGRID;

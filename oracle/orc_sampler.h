@@ -9,7 +9,10 @@
 //   draw_beta                 src/draw-beta.cpp:51-101
 //   draw_threshold            src/draw_threshold.cpp:206-228
 //   sweep order / total ll    src/gpirtMCMC.cpp:261-331
-// Scope: constant_IRF == 0. horizon == 1 (every BASELINE.json config) is one Sampler; horizon > 1 is a panel of H Samplers (sessions are
+//   constant_IRF == 1         src/draw-fstar.cpp:58-125 (Sampler::draw_fstar_cst); the stacked-session ESS of src/draw-f.cpp:84-139 and
+//                             src/draw_threshold.cpp:5-96,181-205 are the single-session blocks run on a sampler over the n*H stacked rows
+//                             (oracle/orc.py ConstantPanel)
+// Scope: constant_IRF == 0 in this file's sweep; horizon == 1 (every BASELINE.json config) is one Sampler; horizon > 1 is a panel of H Samplers (sessions are
 // independent given theta: src/draw-f.cpp:62, src/draw-fstar.cpp:20, src/draw-beta.cpp:60, src/draw_threshold.cpp:206) plus
 // panel_draw_theta below for the RDM and GP-over-time regimes; the CST regime at horizon > 1 indexes thresholds out of bounds in the
 // reference (src/draw-theta.cpp:162 passes the m-row cube for m*H stacked items) and is not restated. Parity of this file itself
@@ -88,6 +91,10 @@ struct Sampler {
     int update_cholesky();    // src/cholesky-cache.cpp:20-24
     void draw_f(const Src& s, const double* nu_supplied);
     int draw_fstar(const Src& s);
+    // constant_IRF == 1 (src/draw-fstar.cpp:58-125) on the STACKED sampler of a constant-IRF panel (theta, f: the n*H stacked rows; beta:
+    // session 0's): 100 inducing points on linspace(min theta, max theta), f interpolated onto them (arma::interp1, "linear": abscissae sorted,
+    // duplicates dropped keeping the first), GP posterior on the grid from the inducing values, one f* for all sessions.
+    int draw_fstar_cst(const Src& s);
     void draw_theta(const Src& s);
     void gather_f();
     void draw_beta(const Src& s);

@@ -149,6 +149,55 @@ def dataset_case(name, cube, C, seed, iters, keep_items=8):
     print(name, y.shape, "C", C, "ll", R["ll"])
 
 
+def cst_case(name, n, m, C, H, seed, iters, ls):
+    """constant_IRF == 1: the reference's own gpirtMCMC run and the streams every unit consumed, captured from the oracle's ConstantPanel in
+    mt19937 mode beside it (kept only if it reproduces the reference's theta, beta and thresholds bit for bit). Stacked blocks (f, fstar, thr)
+    have one stream set per sweep (units = items over the n*H stacked rows), beta one per session, theta per session (RDM) or one (GP)."""
+    Ps = [make_problem(n, m, C, seed=seed + h, missing=0.1) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    theta_in = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1))
+    thr0 = np.asfortranarray(np.stack([Ps[0]["thr0"]] * H, axis=2))
+    z_init = np.random.default_rng(seed + 1000).standard_normal(3 * m + n * m)
+    bpm, bps, tpm, tps = np.zeros((3, m), order="F"), Ps[0]["beta_prior_sds"], np.zeros((2, n), order="F"), np.zeros((2, n), order="F")
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, 1.0, ls, "Matern", thr0, 1, z_init, store_f=True, store_fstar=True)
+    theta0 = np.clip(theta_in, -5.0, 5.0)
+    beta0 = np.asfortranarray(bpm + bps * z_init[:3 * m].reshape(m, 3).T)
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.asfortranarray(np.stack([L0 @ z_init[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1))
+    O = orc.ConstantPanel(y, C, bps, tps, theta_os=1.0, theta_ls=ls, KERNEL="Matern")
+    O.init_constant(theta0, beta0, f0, thr0)
+    assert O.draw_fstar(orc.mt()) == 0
+    fstar0 = O.state()["fstar"][:, :, 0]
+    O.record(True)
+    O.T.record(True)
+    rec = {}
+    for it in range(iters):
+        O.mt_seed_all(it * 10000)
+        assert O.sweep(lambda block, h: orc.mt()) == 0
+        for blk, zcap in (("f", n * H), ("fstar", orc.NGRID), ("thr", C - 1)):
+            zz, u, nz, nu = O.T.recorded(blk, zcap, UCAP)
+            rec[f"z_{blk}_{it}"] = zz
+            if blk != "fstar":
+                rec[f"u_{blk}_{it}"], rec[f"nu_{blk}_{it}"] = u, nu
+        for h, S in enumerate(O.S):
+            zz, u, nz, nu = S.recorded("beta", 3, UCAP)
+            rec[f"z_beta_{it}_{h}"], rec[f"u_beta_{it}_{h}"], rec[f"nu_beta_{it}_{h}"] = zz, u, nu
+            if O.regime == 1:
+                zz, u, nz, nu = S.recorded("theta", 1, UCAP)
+                rec[f"z_theta_{it}_{h}"], rec[f"u_theta_{it}_{h}"], rec[f"nu_theta_{it}_{h}"] = zz, u, nu
+        if O.regime == 2:
+            zz, u, nz, nu = O.S[0].recorded("theta", H, UCAP)
+            rec[f"z_theta_{it}"], rec[f"u_theta_{it}"], rec[f"nu_theta_{it}"] = zz, u, nu
+        s = O.state()
+        assert np.array_equal(s["theta"], R["theta"][it]), f"{name}: oracle theta != reference theta at sweep {it}"
+        assert np.array_equal(s["beta"], R["beta"][..., it]) and np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, :, it])
+    out = dict(n=n, m=m, C=C, H=H, iters=iters, ls=ls, y=y, theta_in=theta_in, beta_prior_sds=bps, theta_prior_sds=tps, thr0=thr0, beta0=beta0,
+               f0=f0, fstar0=fstar0, ref_theta=R["theta"], ref_beta=R["beta"], ref_threshold=R["threshold"], ref_ll=R["ll"], ref_f=R["f"],
+               ref_fstar_last=R["fstar"][..., -1], **rec)
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **out)
+    print(name, "ll", R["ll"])
+
+
 def leaf_case():
     rng = np.random.default_rng(42)
     x1, x2, sds = rng.standard_normal(17) * 2, rng.standard_normal(9) * 2, np.array([3.0, 2.5, 0.7])
@@ -190,9 +239,15 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["datasets"]:
         datasets()
         sys.exit(0)
+    if sys.argv[1:] == ["cst"]:
+        cst_case("cst_rdm_h2", n=30, m=5, C=4, H=2, seed=81, iters=2, ls=0.05)
+        cst_case("cst_gp_h2", n=30, m=5, C=3, H=2, seed=91, iters=2, ls=2.5)
+        sys.exit(0)
     leaf_case()
     sweep_case("sweep_ordinal_c4", n=48, m=8, C=4, seed=11, iters=3, missing=0.1)
     sweep_case("sweep_binary_c2", n=36, m=6, C=2, seed=23, iters=3, missing=0.2, empty_item=4, tps_sd=0.6)
     panel_case("panel_rdm_h3", n=30, m=5, C=4, H=3, seed=51, iters=2, ls=0.05, kernel="Matern")
     panel_case("panel_gp_h3", n=30, m=5, C=3, H=3, seed=61, iters=2, ls=2.5, kernel="Matern")
     datasets()
+    cst_case("cst_rdm_h2", n=30, m=5, C=4, H=2, seed=81, iters=2, ls=0.05)
+    cst_case("cst_gp_h2", n=30, m=5, C=3, H=2, seed=91, iters=2, ls=2.5)

@@ -251,3 +251,44 @@ def test_cuda_panel_replays_reference_horizon_3_sweeps(name):
     P.set_state(theta=G["theta_in"], beta=G["beta0"], f=G["f0"], thresholds=G["thr0"], fstar=G["fstar0"])
     for it, st, ll, ev in replay_panel(G, P, "cuda"):
         check_panel(G, it, st, ll, ev, it == int(G["iters"]) - 1)
+
+
+# ---- constant_IRF == 1: the reference's own H = 2 runs, streams recorded for the stacked blocks / per session -----------------------------
+CSTS = ["cst_rdm_h2", "cst_gp_h2"]
+
+
+@pytest.mark.parametrize("name", CSTS)
+def test_oracle_constant_irf_panel_replays_reference_sweeps(name):
+    """The oracle's ConstantPanel (oracle/orc.py) driven by the streams the reference consumed (tests/golden/make_golden.py cst_case): theta
+    bit-exact, identical proposal counts in the stacked f / threshold blocks, beta / thresholds 1e-9. The CUDA path returns
+    GPIRT_ERR_UNSUPPORTED for constant_IRF == 1; this fixture is what its implementation will be replayed against on the GPU box."""
+    G = load(name)
+    n, m, C, H, rdm = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"]), float(G["ls"]) <= 0.1
+    O = orc.ConstantPanel(G["y"], C, G["beta_prior_sds"], G["theta_prior_sds"], theta_os=1.0, theta_ls=float(G["ls"]), KERNEL="Matern")
+    O.init_constant(np.clip(G["theta_in"], -5, 5), G["beta0"], G["f0"], G["thr0"])
+    for S in O.S:
+        S.set_state(fstar=G["fstar0"])
+    for it in range(int(G["iters"])):
+        O.draw_f(orc.supplied(z=G[f"z_f_{it}"], u=G[f"u_f_{it}"]))
+        ev_f = O.T.diag("f")[0]
+        assert O.draw_fstar(orc.supplied(z=G[f"z_fstar_{it}"])) == 0
+        if rdm:
+            O.draw_theta([orc.supplied(z=G[f"z_theta_{it}_{h}"], u=G[f"u_theta_{it}_{h}"]) for h in range(H)])
+        else:
+            O.draw_theta(orc.supplied(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"]))
+        for S in O.S:
+            S.gather_f()
+        for h, S in enumerate(O.S):
+            S.draw_beta(orc.supplied(z=G[f"z_beta_{it}_{h}"], u=G[f"u_beta_{it}_{h}"]))
+        for S in O.S:
+            S.compute_mu()
+        O.draw_threshold(orc.supplied(z=G[f"z_thr_{it}"], u=G[f"u_thr_{it}"]))
+        ev_thr = O.T.diag("thr")[0]
+        s = O.state()
+        assert np.array_equal(s["theta"], G["ref_theta"][it]), f"sweep {it}: theta differs from the reference's draw"
+        assert rel(s["beta"], G["ref_beta"][..., it]) < 1e-9 and rel(s["thr"], G["ref_threshold"][..., it]) < 1e-9
+        assert abs(O.total_ll() - G["ref_ll"][it]) <= 1e-7 * abs(G["ref_ll"][it])
+        for ev, key in ((ev_f, "f"), (ev_thr, "thr")):
+            nu = G[f"nu_{key}_{it}"]
+            assert np.array_equal(np.where(nu > 0, ev, 0), nu), f"sweep {it}: stacked block {key} made a different number of proposals"
+        assert np.max(np.abs(s["f"] - G["ref_f"][..., it])) < 1e-4

@@ -178,6 +178,39 @@ def test_gpirtMCMC_horizon_3_same_draws(regime, ls, kernel):
     assert np.max(np.abs(s["fstar"] - R["fstar"][..., -1])) < 1e-5
 
 
+@pytest.mark.parametrize("regime,ls", [("RDM", 0.05), ("GP", 2.5)])
+def test_gpirtMCMC_constant_IRF_same_draws(regime, ls):
+    """constant_IRF == 1 (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96,181-205, init src/gpirtMCMC.cpp:164-200):
+    the oracle's ConstantPanel (panel + one stacked sampler over the n*H rows + the inducing-point f* draw) against the reference's own run,
+    one thread: theta / beta / thresholds bit for bit; f* is the solution of a 100-point inducing system with kappa ~ 1e12 (1e-3 absolute)."""
+    n, m, C, H, iters = 30, 5, 4, 2, 3
+    Ps = [make_problem(n, m, C, seed=70 + h, missing=0.1) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    theta_in = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1))
+    thr0 = np.asfortranarray(np.stack([Ps[0]["thr0"]] * H, axis=2))
+    z = np.random.default_rng(5).standard_normal(3 * m + n * m)  # the constant branch draws beta for session 0 and ONE f0 per item (:176-188)
+    bpm, bps, tpm, tps = np.zeros((3, m)), Ps[0]["beta_prior_sds"], np.zeros((2, n)), np.zeros((2, n))
+    R = ref.gpirtMCMC(y, theta_in, iters, 0, 1, bpm, bps, tpm, tps, 1.0, ls, "Matern", thr0, 1, z, store_f=True, store_fstar=True)
+    theta0 = np.clip(theta_in, -5, 5)
+    beta0 = np.asfortranarray(bpm + bps * z[:3 * m].reshape(m, 3).T)
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.asfortranarray(np.stack([L0 @ z[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1))
+    O = orc.ConstantPanel(y, C, bps, tps, theta_os=1.0, theta_ls=ls, KERNEL="Matern")
+    assert O.regime == (1 if regime == "RDM" else 2)
+    O.init_constant(theta0, beta0, f0, thr0)
+    assert O.draw_fstar(orc.mt()) == 0  # initial draw_fstar on the unseeded generators (src/gpirtMCMC.cpp:227)
+    for it in range(iters):
+        O.mt_seed_all(it * 10000)
+        assert O.sweep(lambda block, h: orc.mt()) == 0
+        s = O.state()
+        assert np.array_equal(s["theta"], R["theta"][it]), f"sweep {it}"
+        assert np.array_equal(s["beta"], R["beta"][..., it])
+        assert np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, :, it])
+        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, 1]) and np.array_equal(s["thr"][:, :, 0], s["thr"][:, :, 1])
+        assert abs(O.total_ll() - R["ll"][it]) <= 1e-7 * abs(R["ll"][it])
+        assert np.max(np.abs(s["f"] - R["f"][..., it])) < 1e-4 and np.max(np.abs(s["fstar"] - R["fstar"][..., it])) < 2e-3
+
+
 def test_reference_CST_regime_at_horizon_2_reads_thresholds_out_of_bounds():
     """theta_ls >= 3H with H > 1 (the R default theta_ls = 10 for H <= 3): compute_ll_sparse indexes thresholds(j, c) with j up to m*H - 1 on
     an m-row matrix (src/draw-theta.cpp:139,162 -> :17-19). Armadillo's bounds check (kept in the stand-in) throws inside the
