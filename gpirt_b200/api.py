@@ -153,6 +153,16 @@ def double_solve(L, X, device=0):
     return out
 
 
+def interp1(X, Y, XI, device=0):
+    """arma::interp1(X, Y[:, j], XI, "linear") for every column j, on the GPU (gpirt_interp1; src/draw-fstar.cpp:77-82)."""
+    X, Y, XI = _F(np.asarray(X, dtype=np.float64).ravel()), _F(np.asarray(Y, dtype=np.float64)), _F(np.asarray(XI, dtype=np.float64).ravel())
+    if Y.ndim == 1:
+        Y = _F(Y[:, None])
+    out = np.empty((XI.size, Y.shape[1]), order="F")
+    check(_lib.lib().gpirt_interp1(int(device), _p(X), C.c_int64(X.size), _p(Y), C.c_int64(Y.shape[1]), _p(XI), C.c_int64(XI.size), _p(out)))
+    return out
+
+
 def delta_to_threshold(deltas):
     d = _F(deltas).ravel()
     out = np.empty(d.size + 2)

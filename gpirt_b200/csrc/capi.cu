@@ -376,7 +376,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->chol_aux.ev_rest) cudaEventDestroy(h->chol_aux.ev_rest);
     for (char*& pa : h->peer_arena)
         if (pa) { cudaIpcCloseMemHandle(pa); pa = nullptr; }
-    for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->arena})
+    for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->mu_rows, (void*)h->arena})
         if (p) dev_free(p);
     store_free(h);
     if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -570,6 +570,28 @@ int gpirt_copy_data(gpirt_sampler* h, gpirt_sampler* src) {
     CU(cudaMemcpyAsync(h->y_rm, src->y_rm, (size_t)h->ldm * std::max(h->n_local, 1), cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->have_data = true;
+    return GPIRT_OK;
+}
+
+// The stacked sampler of a constant-IRF panel (src/draw-f.cpp:84-139, src/draw_threshold.cpp:5-96): its n = n_resp * horizon rows belong to
+// different sessions, and row (h, i) has the mean X_h(i,:) beta_h of ITS session — not a function of one beta per item. mu: n x m_total host
+// matrix used by draw_f and draw_threshold instead of X beta; NULL returns to X beta. world == 1 only.
+int gpirt_set_mean_rows(gpirt_sampler* h, const double* mu) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    if (h->world != 1) return fail(GPIRT_ERR_UNSUPPORTED, "set_mean_rows on an item shard");
+    TRY(quiesce(h));
+    CU(cudaStreamSynchronize(h->stream));
+    if (!mu) {
+        if (h->mu_rows) { dev_free(h->mu_rows); h->mu_rows = nullptr; }
+        return GPIRT_OK;
+    }
+    if (!h->mu_rows) {
+        CU(dev_malloc((void**)&h->mu_rows, (size_t)h->ldn * std::max(h->m_local, 1) * 8));
+        CU(cudaMemsetAsync(h->mu_rows, 0, (size_t)h->ldn * std::max(h->m_local, 1) * 8, h->stream));
+    }
+    CU(cudaMemcpy2DAsync(h->mu_rows, (size_t)h->ldn * 8, mu, (size_t)h->n * 8, (size_t)h->n * 8, h->m_local, cudaMemcpyHostToDevice, h->stream));
+    CU(cudaStreamSynchronize(h->stream));
     return GPIRT_OK;
 }
 
@@ -814,6 +836,7 @@ static ItemView item_view(gpirt_sampler* h) {
     v.y_im = h->y_im; v.ldy = h->ldy; v.theta = h->theta; v.beta = h->beta; v.thr = h->thr; v.f = h->f; v.nu = h->nu; v.sds = h->sds;
     v.z = nullptr; v.z_stride = 0; v.us.u = nullptr; v.us.stride = 0; v.key = h->key();
     v.item_ll = h->item_ll; v.flags = h->flags; v.screen = h->screen; v.exact_evals = nullptr;
+    v.mu_rows = h->mu_rows;
     return v;
 }
 

@@ -1,0 +1,69 @@
+// arma::interp1(X, Y, XI, YI, "linear") as the reference's constant-IRF f* draw uses it (src/draw-fstar.cpp:77-82): the stacked abilities X
+// (n * horizon values, many of them equal once theta lives on the 0.01 grid) are sorted, duplicated abscissae dropped keeping the first in
+// stable order (lowest row index), and every item's column of f is interpolated linearly onto the inducing points XI; NaN outside [min X, max X].
+// Device side: a stable key-index sort and a unique pass (thrust), then one thread per (inducing point, item) with a binary search.
+#include <cstdint>
+#include <limits>
+
+#include <thrust/device_ptr.h>
+#include <thrust/execution_policy.h>
+#include <thrust/sequence.h>
+#include <thrust/sort.h>
+#include <thrust/unique.h>
+
+#include "../../include/gpirt_b200.h"
+
+namespace gpirt { extern long long g_kernel_launches; }
+
+namespace {
+__global__ void k_interp1(const double* __restrict__ xs, const int* __restrict__ src, int k, const double* __restrict__ Y, long long nx,
+                          const double* __restrict__ XI, int nq, int m, double* __restrict__ YI) {
+    const int q = blockIdx.x * blockDim.x + threadIdx.x;
+    const int j = blockIdx.y;
+    if (q >= nq || j >= m) return;
+    const double x = XI[q];
+    const double* y = Y + (size_t)j * nx;
+    double out;
+    if (k == 0 || x < xs[0] || x > xs[k - 1]) out = std::numeric_limits<double>::quiet_NaN();
+    else {
+        int lo = 0, hi = k - 1;  // first index with xs[idx] >= x (std::lower_bound)
+        while (lo < hi) {
+            const int mid = (lo + hi) >> 1;
+            if (xs[mid] < x) lo = mid + 1; else hi = mid;
+        }
+        if (xs[lo] == x) out = y[src[lo]];
+        else {
+            const double w = __ddiv_rn(__dsub_rn(x, xs[lo - 1]), __dsub_rn(xs[lo], xs[lo - 1]));
+            out = __dadd_rn(__dmul_rn(__dsub_rn(1.0, w), y[src[lo - 1]]), __dmul_rn(w, y[src[lo]]));
+        }
+    }
+    YI[(size_t)j * nq + q] = out;
+}
+}  // namespace
+
+extern "C" int gpirt_interp1(int device, const double* X, int64_t nx, const double* Y, int64_t m, const double* XI, int64_t nq, double* YI) {
+    if (!X || !Y || !XI || !YI || nx < 1 || m < 1 || nq < 1) return GPIRT_ERR_INVALID;
+    if (cudaSetDevice(device) != cudaSuccess) return GPIRT_ERR_NO_DEVICE;
+    double *dX = nullptr, *dY = nullptr, *dXI = nullptr, *dYI = nullptr;
+    int* dIdx = nullptr;
+    int rc = GPIRT_OK;
+    auto ok = [&](cudaError_t e) { if (e != cudaSuccess && rc == GPIRT_OK) rc = GPIRT_ERR_CUDA; return e == cudaSuccess; };
+    if (ok(cudaMalloc(&dX, nx * 8)) && ok(cudaMalloc(&dY, nx * m * 8)) && ok(cudaMalloc(&dXI, nq * 8)) && ok(cudaMalloc(&dYI, nq * m * 8)) &&
+        ok(cudaMalloc(&dIdx, nx * 4)) && ok(cudaMemcpy(dX, X, nx * 8, cudaMemcpyHostToDevice)) &&
+        ok(cudaMemcpy(dY, Y, nx * m * 8, cudaMemcpyHostToDevice)) && ok(cudaMemcpy(dXI, XI, nq * 8, cudaMemcpyHostToDevice))) {
+        thrust::device_ptr<double> keys(dX);
+        thrust::device_ptr<int> idx(dIdx);
+        thrust::sequence(thrust::device, idx, idx + nx);
+        thrust::stable_sort_by_key(thrust::device, keys, keys + nx, idx);
+        const int k = (int)(thrust::unique_by_key(thrust::device, keys, keys + nx, idx).first - keys);  // keeps the first of each run
+        gpirt::g_kernel_launches += 3;
+        dim3 grid((unsigned)((nq + 127) / 128), (unsigned)m);
+        k_interp1<<<grid, 128>>>(dX, dIdx, k, dY, nx, dXI, (int)nq, (int)m, dYI);
+        ++gpirt::g_kernel_launches;
+        ok(cudaGetLastError());
+        ok(cudaMemcpy(YI, dYI, nq * m * 8, cudaMemcpyDeviceToHost));
+    }
+    for (void* p : {(void*)dX, (void*)dY, (void*)dXI, (void*)dYI, (void*)dIdx})
+        if (p) cudaFree(p);
+    return rc;
+}

@@ -60,6 +60,7 @@ struct gpirt_sampler {
     double *L = nullptr, *W = nullptr, *Kpost = nullptr, *tstar = nullptr;
     double *Linv = nullptr, *W2 = nullptr, *tri_scratch = nullptr;  // block-inverse solver: L^-1, L^-1 k*, merge scratch (allocated on first use)
     int solver = 1;  // 0: blocked substitution TRSM (backward stable), 1: explicit L^-1 by parallel block inversion + GEMMs
+    double* mu_rows = nullptr;    // optional per-row means of the f / threshold blocks (gpirt_set_mean_rows), [ldn][m_local]
     double* theta_tab = nullptr;  // [NGRID][m_total][C] per-sweep table of theta-step terms (allocated on first use)
     double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};

@@ -95,6 +95,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
     double* __restrict__ fj = v.f + (size_t)j * v.ldn;
     const double* __restrict__ nuj = (MODE == IB_F) ? v.nu + (size_t)j * v.ldn : nullptr;
     const double* __restrict__ theta = v.theta;
+    const double* __restrict__ mur = (v.mu_rows && MODE != IB_BETA) ? v.mu_rows + (size_t)j * v.ldn : nullptr;
     const int n = v.n;
     const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
     double pb0 = b0, pb1 = b1, pb2 = b2;
@@ -105,7 +106,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
         if (y == 0) return 0.0;
         double fi = fj[i];
         if (MODE == IB_F && !current) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
-        const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
+        const double g = __dadd_rn(fi, mur ? mur[i] : mu_of(theta[i], pb0, pb1, pb2));
         return cell_ll(g, tau[y - 1], tau[y], y == 1, y == C);
     };
     auto loglik = [&](double ce, double se, bool current) -> double {
@@ -129,7 +130,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
             if (y == 0) return;
             double fi = fj[i];
             if (MODE == IB_F) fi = __dadd_rn(__dmul_rn(fi, ce), __dmul_rn(nuj[i], se));
-            const double g = __dadd_rn(fi, mu_of(theta[i], pb0, pb1, pb2));
+            const double g = __dadd_rn(fi, mur ? mur[i] : mu_of(theta[i], pb0, pb1, pb2));
             float t, et;
             cell_ll32(g, tau[y - 1], tau[y], t, et);
             l += (double)t;

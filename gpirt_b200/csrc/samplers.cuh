@@ -47,6 +47,8 @@ struct ItemView {
     double* f;                // n x m_local
     const double* nu;         // n x m_local (draw_f)
     const double* sds;        // 3 x m_total beta_prior_sds
+    const double* mu_rows;    // optional n x m_local means (leading dimension ldn) used INSTEAD of X beta in the f and threshold blocks: the
+                              // stacked sampler of a constant-IRF panel, whose rows carry their own session's X_h beta_h (src/draw-f.cpp:93-104)
     const double* z; long long z_stride;   // supplied normals (beta / thresholds) or nullptr
     UniformSrc us;
     RngKey key;

@@ -128,6 +128,16 @@ class Sampler:
             yy = _F(y)
             check(self._L.gpirt_set_data_f64(self._h, _p(yy)))
 
+    def set_mean_rows(self, mu):
+        """per-row means for draw_f / draw_threshold (the stacked sampler of a constant-IRF panel); None returns to X beta"""
+        if mu is None:
+            check(self._L.gpirt_set_mean_rows(self._h, None))
+            return
+        mu = _F(mu)
+        if mu.shape != (self.n, self.m):
+            raise GpirtError(_lib.ERR_SHAPE, f"mu has shape {mu.shape}, expected {(self.n, self.m)}")
+        check(self._L.gpirt_set_mean_rows(self._h, _p(mu)))
+
     def set_priors(self, beta_prior_sds=None, theta_prior_sds=None):
         b, t = _F(beta_prior_sds), _F(theta_prior_sds)
         if b is not None and b.shape != (3, self.m):

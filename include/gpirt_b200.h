@@ -100,6 +100,9 @@ int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int
 int gpirt_delta_to_threshold(const double* deltas, int C, double* thresholds);   /* host-only bookkeeping, bit-exact */
 int gpirt_threshold_to_delta(const double* thresholds, int C, double* deltas);
 int gpirt_chol(int device, const double* A, int64_t n, double* L);               /* arma::chol(A,"lower") */
+/* arma::interp1(X, Y.col(j), XI, YI.col(j), "linear") for every column j of Y (src/draw-fstar.cpp:77-82, the inducing points of the constant-IRF
+ * f* draw): X sorted, duplicated abscissae dropped keeping the lowest row index, NaN outside [min X, max X]. Y: nx x m, YI: nq x m, column-major. */
+int gpirt_interp1(int device, const double* X, int64_t nx, const double* Y, int64_t m, const double* XI, int64_t nq, double* YI);
 int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, int64_t nrhs, double* out);
 
 /* ---- lifetime, data, state ---- */
@@ -113,6 +116,9 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y);  /* n x m_total, NaN 
 int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y);   /* n x m_total, 0 missing */
 /* chains share their responses (R/gpirtMCMC.R:111-158 passes the same `data` to every chain): take src's device layouts of y, no upload */
 int gpirt_copy_data(gpirt_sampler* h, gpirt_sampler* src);
+/* constant_IRF == 1 building block: per-row means for draw_f / draw_threshold on a sampler whose rows are the stacked (session, respondent)
+ * pairs (src/draw-f.cpp:93-104 stacks mu.slice(h)); mu is n x m_total (host), NULL switches back to X beta */
+int gpirt_set_mean_rows(gpirt_sampler* h, const double* mu);
 int gpirt_set_priors(gpirt_sampler* h, const double* beta_prior_sds /*3 x m_total*/, const double* theta_prior_sds /*2 x n*/);
 /* any pointer may be NULL (left unchanged). beta: p_beta x m_total; f: n x m_total; thresholds: m_total x (C+1);
  * fstar: NGRID x m_total. Setting theta clamps it to [-5,5] (src/gpirtMCMC.cpp:133). */

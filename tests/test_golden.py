@@ -292,3 +292,71 @@ def test_oracle_constant_irf_panel_replays_reference_sweeps(name):
             nu = G[f"nu_{key}_{it}"]
             assert np.array_equal(np.where(nu > 0, ev, 0), nu), f"sweep {it}: stacked block {key} made a different number of proposals"
         assert np.max(np.abs(s["f"] - G["ref_f"][..., it])) < 1e-4
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CSTS)
+def test_cuda_constant_irf_panel_replays_reference_sweeps(name):
+    """gpirt_b200.ConstantPanel (panel + stacked sampler with per-row means + 100-respondent inducing sampler + gpirt_interp1) driven by the streams
+    the reference consumed: theta bit-exact, identical proposal counts in the stacked f / threshold blocks, beta / thresholds 1e-9; f* is the
+    solution of the 100-point inducing system (kappa ~ 1e12): compared to the reference's at 5e-3 absolute."""
+    from gpirt_b200.constant_panel import ConstantPanel
+
+    G = load(name)
+    n, m, C, H, rdm = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"]), float(G["ls"]) <= 0.1
+    P = ConstantPanel(n, m, C, H, theta_os=1.0, theta_ls=float(G["ls"]), KERNEL="Matern")
+    P.set_data(G["y"])
+    P.set_priors(G["beta_prior_sds"], G["theta_prior_sds"])
+    P.init_constant(G["theta_in"], G["beta0"], G["f0"], G["thr0"])
+    for S in P.S:
+        S.set_state(fstar=G["fstar0"])
+    for it in range(int(G["iters"])):
+        P.draw_f(z=G[f"z_f_{it}"], u=G[f"u_f_{it}"])
+        ev_f = P.T.diag("f")[0]
+        P.draw_fstar(z=G[f"z_fstar_{it}"])
+        if rdm:
+            P.draw_theta(z=[G[f"z_theta_{it}_{h}"] for h in range(H)], u=[G[f"u_theta_{it}_{h}"] for h in range(H)])
+        else:
+            P.draw_theta(z=G[f"z_theta_{it}"], u=G[f"u_theta_{it}"])
+        P.gather_f()
+        P.draw_beta(z=[G[f"z_beta_{it}_{h}"] for h in range(H)], u=[G[f"u_beta_{it}_{h}"] for h in range(H)])
+        for S in P.S:
+            S.update_cholesky_cache()
+        P.draw_threshold(z=G[f"z_thr_{it}"], u=G[f"u_thr_{it}"])
+        ev_thr = P.T.diag("thr")[0]
+        s = P.get_state(fstar=True)
+        assert np.array_equal(s["theta"], G["ref_theta"][it]), f"sweep {it}: theta differs from the reference's draw"
+        assert rel(s["beta"], G["ref_beta"][..., it]) < 1e-9 and rel(s["thresholds"], G["ref_threshold"][..., it]) < 1e-9
+        assert abs(P.total_ll() - G["ref_ll"][it]) <= 2e-5 * abs(G["ref_ll"][it])  # carries the f* difference of the kappa ~ 1e12 inducing system
+        for ev, key in ((ev_f, "f"), (ev_thr, "thr")):
+            nu = G[f"nu_{key}_{it}"]
+            assert np.array_equal(np.where(nu > 0, ev, 0), nu), f"sweep {it}: stacked block {key} made a different number of proposals"
+        assert np.max(np.abs(s["f"] - G["ref_f"][..., it])) < 5e-3
+        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, 1])
+    assert np.max(np.abs(s["fstar"] - G["ref_fstar_last"])) < 5e-3
+    P.close()
+
+
+@pytest.mark.gpu
+def test_interp1_on_the_gpu_matches_the_oracle_restatement():
+    import gpirt_b200.api as api
+
+    rng = np.random.default_rng(12)
+    X = np.round(rng.standard_normal(400) * 1.5, 2)  # duplicated abscissae, as theta on the 0.01 grid
+    Y = np.asfortranarray(rng.standard_normal((400, 7)))
+    XI = np.concatenate([np.linspace(X.min(), X.max(), 100), [X.min() - 1.0, X.max() + 0.5, X[17]]])
+    got = api.interp1(X, Y, XI)
+    order = np.argsort(X, kind="stable")
+    xs, first = np.unique(X[order], return_index=True)  # first of each run in stable order = lowest row index
+    ys = Y[order[first]]
+    want = np.full_like(got, np.nan)
+    for q, x in enumerate(XI):
+        if x < xs[0] or x > xs[-1]:
+            continue
+        hi = int(np.searchsorted(xs, x, side="left"))
+        if xs[hi] == x:
+            want[q] = ys[hi]
+        else:
+            w = (x - xs[hi - 1]) / (xs[hi] - xs[hi - 1])
+            want[q] = (1.0 - w) * ys[hi - 1] + w * ys[hi]
+    assert np.array_equal(np.isnan(got), np.isnan(want)) and np.array_equal(got[~np.isnan(want)], want[~np.isnan(want)])
