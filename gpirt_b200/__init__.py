@@ -7,3 +7,4 @@ from ._lib import LIB_PATH, NGRID, GpirtError  # noqa: F401
 from .api import K, K_time, chol, delta_to_threshold, double_solve, gpirtMCMC, recover_fstar, threshold_to_delta  # noqa: F401
 from .sampler import Sampler, default_thresholds  # noqa: F401
 from .panel import Panel  # noqa: F401
+from .constant_panel import ConstantPanel  # noqa: F401

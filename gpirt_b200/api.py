@@ -32,6 +32,10 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         raise GpirtError(_lib.ERR_UNSUPPORTED, "vote_codes recoding is not part of the sampler path; pass codes 1..C")
     y = _as_cube(data)
     n, m, H = y.shape
+    if constant_IRF:
+        return _gpirtMCMC_constant_irf(y, sample_iterations, burn_iterations, THIN, CHAIN, beta_prior_means, beta_prior_sds, theta_prior_means,
+                                       theta_prior_sds, theta_os, theta_ls, KERNEL, theta_init, thresholds, SEED, store_f, store_fstar, device,
+                                       progress, first_chain)
     bpm = _F(np.zeros((3, m)) if beta_prior_means is None else beta_prior_means)
     bps = _F(np.full((3, m), 3.0) if beta_prior_sds is None else beta_prior_sds)
     tpm = _F(np.zeros((2, n)) if theta_prior_means is None else theta_prior_means)
@@ -97,6 +101,73 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
                            beta=[out["beta"][..., s] for s in range(n_samples)],
                            fstar=[out["fstar"][..., s] for s in range(n_samples)] if store_fstar else None,
                            threshold=[out["threshold"][..., s] for s in range(n_samples)], ll=out["ll"]))
+    return result
+
+
+def _gpirtMCMC_constant_irf(y, sample_iterations, burn_iterations, THIN, CHAIN, beta_prior_means, beta_prior_sds, theta_prior_means,
+                            theta_prior_sds, theta_os, theta_ls, KERNEL, theta_init, thresholds, SEED, store_f, store_fstar, device, progress,
+                            first_chain):
+    """gpirtMCMC(constant_IRF = 1): the sweep loop of src/gpirtMCMC.cpp:261-356 over a ConstantPanel (constant_panel.py). The C entry point
+    gpirt_mcmc refuses constant_IRF == 1; this host loop drives the same CUDA kernels block by block."""
+    from .constant_panel import ConstantPanel
+
+    n, m, H = y.shape
+    bpm = _F(np.zeros((3, m)) if beta_prior_means is None else beta_prior_means)
+    bps = _F(np.full((3, m), 3.0) if beta_prior_sds is None else beta_prior_sds)
+    tpm = _F(np.zeros((2, n)) if theta_prior_means is None else theta_prior_means)
+    tps = _F(np.zeros((2, n)) if theta_prior_sds is None else theta_prior_sds)
+    if thresholds is None:
+        Ccat = len(np.unique(y[np.isfinite(y)]))
+        thr = default_thresholds(m, Ccat)[:, :, None].repeat(H, axis=2)
+    else:
+        thr = np.asarray(thresholds, dtype=np.float64)
+        thr = thr[:, :, None].repeat(H, axis=2) if thr.ndim == 2 else thr
+        Ccat = thr.shape[1] - 1
+    n_samples = int(sample_iterations / THIN)
+    result = []
+    for chain in range(CHAIN):
+        rng = np.random.default_rng(SEED + first_chain + chain)
+        if theta_init is None:
+            th0 = np.empty((n, H), order="F")
+            th0[:, 0] = tpm[0] + tps[0] * rng.standard_normal(n)
+            th0[:, 1:] = th0[:, :1]
+            theta_init = th0
+        th0 = np.clip(np.asarray(theta_init, dtype=np.float64).reshape(n, H), -5.0, 5.0)
+        P = ConstantPanel(n, m, Ccat, H, theta_os=theta_os, theta_ls=theta_ls, KERNEL=KERNEL, seed=SEED, chain=first_chain + chain, device=device)
+        try:
+            P.set_data(y)
+            P.set_priors(bps, tps)
+            # the constant branch of the initialisation (src/gpirtMCMC.cpp:164-200): beta for session 0 only, one f0 = L_0 z per item for all sessions
+            S0 = P.S[0]
+            S0.set_state(theta=th0[:, 0], thresholds=thr[:, :, 0])
+            S0.set_iter(0xFFFFFFFF)
+            S0.init_draw(beta_prior_means=bpm, draw_beta=True, draw_f=True)
+            st0 = S0.get_state()
+            P.init_constant(th0, st0["beta"], st0["f"], thr)
+            P.set_iter(0xFFFFFFFF)
+            P.draw_fstar()  # src/gpirtMCMC.cpp:227
+            P.set_iter(0)
+            out = dict(theta=np.zeros((n_samples, n, H), order="F"), beta=[], threshold=[], ll=np.zeros(n_samples), f=[] if store_f else None,
+                       fstar=[] if store_fstar else None)
+            total = sample_iterations + burn_iterations
+            for it in range(total):
+                if progress is not None and progress(it, total, None):
+                    raise GpirtError(_lib.ERR_INVALID, "interrupted")
+                P.sweep()
+                if it >= burn_iterations and it % THIN == 0 and (it - burn_iterations) // THIN < n_samples:  # src/gpirtMCMC.cpp:334-335
+                    k = (it - burn_iterations) // THIN
+                    s = P.get_state(fstar=True)
+                    out["theta"][k] = s["theta"]
+                    out["beta"].append(s["beta"])
+                    out["threshold"].append(s["thresholds"])
+                    out["ll"][k] = P.total_ll()
+                    if store_f:
+                        out["f"].append(s["f"])
+                    if store_fstar:
+                        out["fstar"].append(s["fstar"])
+            result.append(out)
+        finally:
+            P.close()
     return result
 
 

@@ -133,3 +133,35 @@ def test_gpirtMCMC_at_horizon_3_equals_the_stepwise_panel(regime, ls, kernel):
             assert res["ll"][s] == G.total_ll()
             s += 1
     assert s == ns
+
+
+@pytest.mark.parametrize("regime,ls", [("RDM", 0.05), ("GP", 2.0)])
+def test_gpirtMCMC_constant_IRF_runs_the_constant_panel(regime, ls):
+    """gpirtMCMC(constant_IRF = 1) (gpirt_b200/api.py -> constant_panel.py): one f* and one set of thresholds for all sessions in every kept draw,
+    per-session beta, finite log-likelihood; the same call twice gives the same chain (Philox streams), another chain id a different one; and
+    the C entry point still refuses the mode."""
+    import gpirt_b200 as g
+    from gpirt_b200 import _lib
+
+    n, m, C, H = 60, 9, 4, 3
+    Ps = [make_problem(n, m, C, seed=300 + h, missing=0.1) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    th0 = np.asfortranarray(np.stack([Ps[0]["theta0"]] * H, axis=1))
+    kw = dict(theta_ls=ls, theta_os=1.2, theta_init=th0, thresholds=Ps[0]["thr0"], SEED=9, constant_IRF=1, store_f=True, store_fstar=True)
+    a = g.gpirtMCMC(y, 4, 2, THIN=2, **kw)[0]
+    assert a["theta"].shape == (2, n, H) and len(a["beta"]) == 2 and np.all(np.isfinite(a["ll"])) and np.all(a["ll"] < 0)
+    for k in range(2):
+        fs, thr, be = a["fstar"][k], a["threshold"][k], a["beta"][k]
+        assert fs.shape == (1001, m, H) and all(np.array_equal(fs[:, :, 0], fs[:, :, h]) for h in range(1, H))
+        assert all(np.array_equal(thr[:, :, 0], thr[:, :, h]) for h in range(1, H))
+        assert not np.array_equal(be[:, :, 0], be[:, :, 1])
+        assert np.all(np.abs(a["theta"][k]) <= 5.0)
+    b = g.gpirtMCMC(y, 4, 2, THIN=2, **kw)[0]
+    assert np.array_equal(a["theta"], b["theta"]) and np.array_equal(a["ll"], b["ll"])
+    c = g.gpirtMCMC(y, 4, 2, THIN=2, first_chain=1, **kw)[0]
+    assert not np.array_equal(a["theta"], c["theta"])
+    cfg = _lib.Config(n=n, m_total=m, horizon=H, C=C, constant_IRF=1, p_beta=3, theta_os=1.0, theta_ls=ls, kernel=0, device=0, seed=1, chain=0, rank=0, world=1)
+    import ctypes
+
+    h = ctypes.c_void_p()
+    assert _lib.lib().gpirt_panel_create(ctypes.byref(cfg), ctypes.byref(h)) == _lib.ERR_UNSUPPORTED
