@@ -32,10 +32,6 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         raise GpirtError(_lib.ERR_UNSUPPORTED, "vote_codes recoding is not part of the sampler path; pass codes 1..C")
     y = _as_cube(data)
     n, m, H = y.shape
-    if constant_IRF:
-        return _gpirtMCMC_constant_irf(y, sample_iterations, burn_iterations, THIN, CHAIN, beta_prior_means, beta_prior_sds, theta_prior_means,
-                                       theta_prior_sds, theta_os, theta_ls, KERNEL, theta_init, thresholds, SEED, store_f, store_fstar, device,
-                                       progress, first_chain)
     bpm = _F(np.zeros((3, m)) if beta_prior_means is None else beta_prior_means)
     bps = _F(np.full((3, m), 3.0) if beta_prior_sds is None else beta_prior_sds)
     tpm = _F(np.zeros((2, n)) if theta_prior_means is None else theta_prior_means)
@@ -50,8 +46,10 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         thr = default_thresholds(m, Ccat)[:, :, None].repeat(H, axis=2)
     else:
         thr = np.asarray(thresholds, dtype=np.float64)
-        if thr.ndim == 2:
-            thr = thr[:, :, None]
+        if thr.ndim == 2:  # one m x (C+1) matrix: the same initial thresholds in every session
+            thr = thr[:, :, None].repeat(H, axis=2)
+        if thr.shape != (m, thr.shape[1], H):
+            raise GpirtError(_lib.ERR_SHAPE, f"thresholds has shape {thr.shape}, expected {(m, thr.shape[1], H)}")
         Ccat = thr.shape[1] - 1
     thr = np.asfortranarray(thr)
     n_samples = int(sample_iterations / THIN)
@@ -107,8 +105,9 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
 def _gpirtMCMC_constant_irf(y, sample_iterations, burn_iterations, THIN, CHAIN, beta_prior_means, beta_prior_sds, theta_prior_means,
                             theta_prior_sds, theta_os, theta_ls, KERNEL, theta_init, thresholds, SEED, store_f, store_fstar, device, progress,
                             first_chain):
-    """gpirtMCMC(constant_IRF = 1): the sweep loop of src/gpirtMCMC.cpp:261-356 over a ConstantPanel (constant_panel.py). The C entry point
-    gpirt_mcmc refuses constant_IRF == 1; this host loop drives the same CUDA kernels block by block."""
+    """gpirtMCMC(constant_IRF = 1) step by step: the sweep loop of src/gpirtMCMC.cpp:261-356 over a ConstantPanel (constant_panel.py). The C entry
+    point gpirt_mcmc runs the same composition (csrc/entry.cu mcmc_constant) and is what gpirtMCMC() calls; this host loop exists so the tests
+    can hold the entry point to the block-by-block chain, bit for bit."""
     from .constant_panel import ConstantPanel
 
     n, m, H = y.shape

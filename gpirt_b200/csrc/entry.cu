@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <algorithm>
 #include <cstring>
+#include <limits>
 #include <string>
 #include <vector>
 
@@ -78,6 +79,151 @@ static int mcmc_panel(const gpirt_mcmc_args* a, const gpirt_config& cfg) {
     }
     if (n_samples > 0) TRYC(flush());
     return gpirt_panel_sync(g.p);
+}
+
+// constant_IRF == 1 (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96,181-205, init src/gpirtMCMC.cpp:164-200) as a
+// composition of the handles above: the panel's H sessions (theta step, gather, draw_beta, log-likelihood — no constant_IRF argument in the
+// reference), a STACKED sampler T over the n*H (session, respondent) rows whose ordinary draw_f / draw_threshold are the constant-IRF blocks once
+// the rows carry their own session's mean (gpirt_set_mean_rows), and a 100-respondent sampler I whose ordinary draw_fstar is the inducing-point
+// posterior once theta is the inducing grid and f the stacked f interpolated onto it (gpirt_interp1). State moves between the handles through
+// host buffers: every likelihood / ESS / factorisation runs in the kernels, the mode is not tuned. Same composition as
+// gpirt_b200/constant_panel.py (bit-identical chains, tests/test_gpu_panel.py).
+static int mcmc_constant(const gpirt_mcmc_args* a, gpirt_config cfg) {
+    const int H = a->horizon, P = 100;  // n_induced_points, src/draw-fstar.cpp:73
+    const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1, N = 1001;
+    if (H < 2) return GPIRT_ERR_UNSUPPORTED;  // one session: nothing to share (the reference then only differs by the inducing-point f* draw)
+    cfg.constant_IRF = 0;  // the handles are the ordinary ones
+    struct Owner {
+        gpirt_panel* p = nullptr; gpirt_sampler* T = nullptr; gpirt_sampler* I = nullptr;
+        ~Owner() { if (T) gpirt_destroy(T); if (I) gpirt_destroy(I); if (p) gpirt_panel_destroy(p); }
+    } o;
+    TRYC(gpirt_panel_create(&cfg, &o.p));
+    std::vector<gpirt_sampler*> S(H);
+    for (int h = 0; h < H; ++h) TRYC(gpirt_panel_session(o.p, h, &S[h]));
+    gpirt_config ct = cfg; ct.horizon = 1; ct.n = (int32_t)(n * H);
+    TRYC(gpirt_create(&ct, &o.T));
+    gpirt_config ci = cfg; ci.horizon = 1; ci.n = P;
+    TRYC(gpirt_create(&ci, &o.I));
+    // data and priors
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    std::vector<double> ystack(n * H * m), tps_stack(2 * n * H), zeros_i(2 * (size_t)P, 0.0), y_i((size_t)P * m, nan);
+    for (size_t j = 0; j < m; ++j)
+        for (int h = 0; h < H; ++h) std::memcpy(&ystack[j * n * H + h * n], a->y + (size_t)h * n * m + j * n, n * 8);  // row h*n + i, src/draw-f.cpp:94-103
+    for (int h = 0; h < H; ++h) std::memcpy(&tps_stack[(size_t)h * 2 * n], a->theta_prior_sds, 2 * n * 8);
+    for (int h = 0; h < H; ++h) {
+        TRYC(gpirt_set_data_f64(S[h], a->y + (size_t)h * n * m));
+        TRYC(gpirt_set_priors(S[h], a->beta_prior_sds, a->theta_prior_sds));
+    }
+    TRYC(gpirt_set_data_f64(o.T, ystack.data()));
+    TRYC(gpirt_set_priors(o.T, a->beta_prior_sds, tps_stack.data()));
+    TRYC(gpirt_set_data_f64(o.I, y_i.data()));
+    TRYC(gpirt_set_priors(o.I, a->beta_prior_sds, zeros_i.data()));
+    // initialisation, constant branch: beta for session 0 only, one f0 = L_0 z per item for every session, every session's mu = X_h beta_0
+    std::vector<double> th(n * H), beta0(3 * m), f0(n * m), zero_beta(3 * m, 0.0), mu(n * m * H);
+    for (size_t k = 0; k < n * H; ++k) th[k] = std::min(5.0, std::max(-5.0, a->theta[k]));  // src/gpirtMCMC.cpp:133
+    auto set_iter_all = [&](uint32_t it) -> int {
+        for (int h = 0; h < H; ++h) TRYC(gpirt_set_iter(S[h], it));
+        TRYC(gpirt_set_iter(o.T, it));
+        return gpirt_set_iter(o.I, it);
+    };
+    TRYC(gpirt_set_state(S[0], th.data(), a->beta_init, a->f_init, a->thresholds, nullptr));
+    TRYC(gpirt_set_iter(S[0], 0xFFFFFFFFu));
+    TRYC(gpirt_init_draw(S[0], a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
+    if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(S[0], a->f_init_z));
+    TRYC(gpirt_get_state(S[0], nullptr, beta0.data(), f0.data(), nullptr, nullptr));
+    auto x_beta = [&](const double* theta, const double* beta, double* out) {  // mu = X beta, left to right (src/gpirtMCMC.cpp:308)
+        for (size_t j = 0; j < m; ++j)
+            for (size_t i = 0; i < n; ++i) {
+                const double t = theta[i];
+                out[j * n + i] = (beta[3 * j] + t * beta[3 * j + 1]) + (t * t) * beta[3 * j + 2];
+            }
+    };
+    for (int h = 0; h < H; ++h) {
+        TRYC(gpirt_set_state(S[h], &th[(size_t)h * n], h == 0 ? beta0.data() : zero_beta.data(), f0.data(), a->thresholds + (size_t)h * m * C1, nullptr));
+        x_beta(&th[(size_t)h * n], beta0.data(), &mu[(size_t)h * n * m]);
+    }
+    // stacked views of the sessions' state
+    std::vector<double> th_s(n * H), f_s(n * H * m), mu_s(n * H * m), f_h(n * m), beta_h(3 * m), thr0(m * C1), fs(N * m), tind(P), find((size_t)P * m);
+    auto stack = [&]() -> int {
+        for (int h = 0; h < H; ++h) {
+            TRYC(gpirt_get_state(S[h], &th_s[(size_t)h * n], nullptr, f_h.data(), nullptr, nullptr));
+            for (size_t j = 0; j < m; ++j) {
+                std::memcpy(&f_s[j * n * H + h * n], &f_h[j * n], n * 8);
+                std::memcpy(&mu_s[j * n * H + h * n], &mu[(size_t)h * n * m + j * n], n * 8);
+            }
+        }
+        TRYC(gpirt_get_state(S[0], nullptr, beta_h.data(), nullptr, thr0.data(), nullptr));
+        return GPIRT_OK;
+    };
+    auto draw_f = [&]() -> int {
+        TRYC(stack());
+        TRYC(gpirt_set_state(o.T, th_s.data(), beta_h.data(), f_s.data(), thr0.data(), nullptr));
+        TRYC(gpirt_set_mean_rows(o.T, mu_s.data()));
+        TRYC(gpirt_draw_f(o.T, nullptr));
+        TRYC(gpirt_get_state(o.T, nullptr, nullptr, f_s.data(), nullptr, nullptr));
+        for (int h = 0; h < H; ++h) {
+            for (size_t j = 0; j < m; ++j) std::memcpy(&f_h[j * n], &f_s[j * n * H + h * n], n * 8);
+            TRYC(gpirt_set_state(S[h], nullptr, nullptr, f_h.data(), nullptr, nullptr));
+        }
+        return GPIRT_OK;
+    };
+    auto draw_fstar = [&]() -> int {
+        TRYC(stack());
+        const double lo = *std::min_element(th_s.begin(), th_s.end()), hi = *std::max_element(th_s.begin(), th_s.end());
+        const double delta = (hi - lo) / double(P - 1);  // arma::linspace: start + i * delta, last element = end
+        for (int i = 0; i + 1 < P; ++i) tind[i] = lo + double(i) * delta;
+        tind[P - 1] = hi;
+        TRYC(gpirt_interp1(cfg.device, th_s.data(), (int64_t)(n * H), f_s.data(), (int64_t)m, tind.data(), P, find.data()));  // src/draw-fstar.cpp:77-82
+        TRYC(gpirt_set_state(o.I, tind.data(), beta_h.data(), find.data(), nullptr, nullptr));
+        TRYC(gpirt_draw_fstar(o.I, nullptr));
+        TRYC(gpirt_get_state(o.I, nullptr, nullptr, nullptr, nullptr, fs.data()));
+        for (int h = 0; h < H; ++h) TRYC(gpirt_set_state(S[h], nullptr, nullptr, nullptr, nullptr, fs.data()));  // one f* for all sessions (:121-124)
+        return GPIRT_OK;
+    };
+    auto draw_threshold = [&]() -> int {
+        TRYC(stack());
+        TRYC(gpirt_set_state(o.T, th_s.data(), nullptr, f_s.data(), thr0.data(), nullptr));
+        TRYC(gpirt_set_mean_rows(o.T, mu_s.data()));
+        TRYC(gpirt_draw_threshold(o.T, nullptr));
+        TRYC(gpirt_get_state(o.T, nullptr, nullptr, nullptr, thr0.data(), nullptr));
+        for (int h = 0; h < H; ++h) TRYC(gpirt_set_state(S[h], nullptr, nullptr, nullptr, thr0.data(), nullptr));  // src/draw_threshold.cpp:199-203
+        return GPIRT_OK;
+    };
+    TRYC(set_iter_all(0xFFFFFFFFu));
+    TRYC(draw_fstar());  // src/gpirtMCMC.cpp:227
+    TRYC(set_iter_all(0));
+    const int total = a->sample_iterations + a->burn_iterations;
+    const int n_samples = a->sample_iterations / a->THIN;
+    for (int iter = 0; iter < total; ++iter) {
+        if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;
+        TRYC(draw_f());
+        TRYC(draw_fstar());
+        TRYC(gpirt_panel_draw_theta(o.p, nullptr));
+        for (int h = 0; h < H; ++h) TRYC(gpirt_gather_f(S[h]));
+        for (int h = 0; h < H; ++h) TRYC(gpirt_draw_beta(S[h], nullptr));
+        for (int h = 0; h < H; ++h) {  // mu.slice(h) = X.slice(h) * beta.slice(h), src/gpirtMCMC.cpp:307-311
+            TRYC(gpirt_get_state(S[h], &th_s[(size_t)h * n], beta_h.data(), nullptr, nullptr, nullptr));
+            x_beta(&th_s[(size_t)h * n], beta_h.data(), &mu[(size_t)h * n * m]);
+            TRYC(gpirt_update_cholesky_cache(S[h]));
+        }
+        TRYC(draw_threshold());
+        TRYC(set_iter_all((uint32_t)iter + 1));
+        if (iter >= a->burn_iterations && iter % a->THIN == 0) {  // src/gpirtMCMC.cpp:334-335
+            const size_t s = (size_t)(iter - a->burn_iterations) / a->THIN;
+            if ((int)s >= n_samples) continue;
+            double ll = 0.0;
+            for (int h = 0; h < H; ++h) {
+                double part = 0.0;
+                TRYC(gpirt_ll_bar(S[h], nullptr, &part));
+                ll += part;
+                TRYC(gpirt_get_state(S[h], &th_s[(size_t)h * n], a->beta_draws + s * 3 * m * H + (size_t)h * 3 * m, a->f_draws ? a->f_draws + s * n * m * H + (size_t)h * n * m : nullptr,
+                                     a->threshold_draws + s * m * C1 * H + (size_t)h * m * C1, a->fstar_draws ? a->fstar_draws + s * N * m * H + (size_t)h * N * m : nullptr));
+                for (size_t i = 0; i < n; ++i) a->theta_draws[s + (size_t)n_samples * (i + n * h)] = th_s[(size_t)h * n + i];
+            }
+            a->ll_draws[s] = ll;
+        }
+    }
+    return gpirt_panel_sync(o.p);
 }
 
 static bool args_ok(const gpirt_mcmc_args* a) {
@@ -167,6 +313,10 @@ extern "C" int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains
         if (a->n != a0->n || a->m != a0->m || a->horizon != a0->horizon || a->C != a0->C || a->device != a0->device ||
             a->sample_iterations != a0->sample_iterations || a->burn_iterations != a0->burn_iterations || a->THIN != a0->THIN)
             return GPIRT_ERR_SHAPE;
+    }
+    if (a0->constant_IRF) {  // one item response function for all sessions: the composed mode, chains one after the other
+        for (int c = 0; c < n_chains; ++c) TRYC(mcmc_constant(&chains[c], config_of(&chains[c])));
+        return GPIRT_OK;
     }
     if (a0->horizon > 1) {  // dynamic GPIRT: chains one after the other (a panel already keeps H samplers in flight)
         for (int c = 0; c < n_chains; ++c) TRYC(mcmc_panel(&chains[c], config_of(&chains[c])));

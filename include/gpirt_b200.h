@@ -51,7 +51,7 @@ typedef enum {
     GPIRT_ERR_CATEGORIES = 3,     /* C < 2 or C > 21, or a y code outside 1..C */
     GPIRT_ERR_NOT_PD = 4,         /* chol failed (arma::chol throws); gpirt_last_error names the leading minor */
     GPIRT_ERR_CUDA = 5,
-    GPIRT_ERR_UNSUPPORTED = 6,    /* horizon > 1, constant_IRF != 0 */
+    GPIRT_ERR_UNSUPPORTED = 6,    /* a mode that is not built (e.g. constant_IRF != 0 at horizon 1 or on a single handle, theta_ls >= 3H at H > 1) */
     GPIRT_ERR_STREAM_OVERRUN = 7, /* a supplied uniform stream ran dry before an ESS loop accepted */
     GPIRT_ERR_NO_DEVICE = 8,
     GPIRT_ERR_ESS_STALLED = 9     /* an ESS loop hit the proposal cap (reference would spin forever) */
@@ -269,6 +269,9 @@ typedef struct {
      * Ignored when f_init is given. */
     const double* f_init_z;
 } gpirt_mcmc_args;
+/* constant_IRF == 1 (horizon > 1): composed from a panel, a stacked sampler over the n*horizon rows and a 100-respondent inducing-point sampler
+ * (csrc/entry.cu mcmc_constant; src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96). beta_init / f_init / f_init_z are
+ * then read for session 0 only (the reference's constant branch draws nothing else, src/gpirtMCMC.cpp:176-188). */
 int gpirt_mcmc(const gpirt_mcmc_args* a);
 /* The chain loop of the R wrapper (R/gpirtMCMC.R:111-158: `for(chain in 1:CHAIN)`, one .gpirtMCMC call per chain, run back to back) as ONE
  * call that runs the chains side by side on the device - BASELINE config 5 "independent chains batched per GPU". chains[c] is chain c's

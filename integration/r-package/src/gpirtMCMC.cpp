@@ -33,11 +33,13 @@ Rcpp::List gpirtMCMC(const arma::cube& y, arma::mat theta, const int sample_iter
     const int n_samples = int(sample_iterations / THIN);  // src/gpirtMCMC.cpp:48
 
     // initial values with R's RNG, in the reference's order
-    arma::cube beta0(3, m, horizon), z0(n, m, horizon);
-    for (arma::uword h = 0; h < horizon; ++h)
+    // constant_IRF == 1 draws beta for session 0 only and ONE f0 = L_0 z per item (src/gpirtMCMC.cpp:176-188): the library reads slice 0 then
+    arma::cube beta0(3, m, horizon, arma::fill::zeros), z0(n, m, horizon, arma::fill::zeros);
+    const arma::uword h_drawn = constant_IRF ? 1 : horizon;
+    for (arma::uword h = 0; h < h_drawn; ++h)
         for (arma::uword j = 0; j < m; ++j)
             for (arma::uword p = 0; p < 3; ++p) beta0(p, j, h) = R::rnorm(beta_prior_means(p, j), beta_prior_sds(p, j));
-    for (arma::uword h = 0; h < horizon; ++h)
+    for (arma::uword h = 0; h < h_drawn; ++h)
         for (arma::uword j = 0; j < m; ++j)
             for (arma::uword i = 0; i < n; ++i) z0(i, j, h) = R::rnorm(0.0, 1.0);
 

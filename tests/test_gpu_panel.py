@@ -137,9 +137,9 @@ def test_gpirtMCMC_at_horizon_3_equals_the_stepwise_panel(regime, ls, kernel):
 
 @pytest.mark.parametrize("regime,ls", [("RDM", 0.05), ("GP", 2.0)])
 def test_gpirtMCMC_constant_IRF_runs_the_constant_panel(regime, ls):
-    """gpirtMCMC(constant_IRF = 1) (gpirt_b200/api.py -> constant_panel.py): one f* and one set of thresholds for all sessions in every kept draw,
-    per-session beta, finite log-likelihood; the same call twice gives the same chain (Philox streams), another chain id a different one; and
-    the C entry point still refuses the mode."""
+    """gpirtMCMC(constant_IRF = 1) through the C entry point (gpirt_mcmc -> mcmc_constant, csrc/entry.cu): one f* and one set of thresholds for all
+    sessions in every kept draw, per-session beta, finite log-likelihood; bit-identical to the block-by-block ConstantPanel loop in Python
+    (constant_panel.py, the composition the golden replays pin to the reference); another chain id gives a different chain."""
     import gpirt_b200 as g
     from gpirt_b200 import _lib
 
@@ -156,12 +156,12 @@ def test_gpirtMCMC_constant_IRF_runs_the_constant_panel(regime, ls):
         assert all(np.array_equal(thr[:, :, 0], thr[:, :, h]) for h in range(1, H))
         assert not np.array_equal(be[:, :, 0], be[:, :, 1])
         assert np.all(np.abs(a["theta"][k]) <= 5.0)
-    b = g.gpirtMCMC(y, 4, 2, THIN=2, **kw)[0]
+    from gpirt_b200.api import _as_cube, _gpirtMCMC_constant_irf
+
+    b = _gpirtMCMC_constant_irf(_as_cube(y), 4, 2, 2, 1, None, None, None, None, 1.2, ls, "Matern", th0, Ps[0]["thr0"], 9, True, True, 0, None, 0)[0]
     assert np.array_equal(a["theta"], b["theta"]) and np.array_equal(a["ll"], b["ll"])
+    for k in range(2):
+        for key in ("beta", "threshold", "f", "fstar"):
+            assert np.array_equal(a[key][k], b[key][k]), f"{key} draw {k}: C entry point != stepwise ConstantPanel"
     c = g.gpirtMCMC(y, 4, 2, THIN=2, first_chain=1, **kw)[0]
     assert not np.array_equal(a["theta"], c["theta"])
-    cfg = _lib.Config(n=n, m_total=m, horizon=H, C=C, constant_IRF=1, p_beta=3, theta_os=1.0, theta_ls=ls, kernel=0, device=0, seed=1, chain=0, rank=0, world=1)
-    import ctypes
-
-    h = ctypes.c_void_p()
-    assert _lib.lib().gpirt_panel_create(ctypes.byref(cfg), ctypes.byref(h)) == _lib.ERR_UNSUPPORTED
