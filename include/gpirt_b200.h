@@ -29,8 +29,9 @@
  * gpirt_last_error() holds the message (R shim: Rcpp::stop(gpirt_last_error())). There is no CPU
  * fallback: without a CUDA device every compute call returns GPIRT_ERR_NO_DEVICE.
  *
- * Scope of this build: horizon == 1 and constant_IRF == 0 (all BASELINE configs); other values
- * return GPIRT_ERR_UNSUPPORTED.
+ * Scope of this build: a gpirt_sampler is one session with constant_IRF == 0 (all BASELINE configs); horizon > 1 is a gpirt_panel
+ * (RDM and GP-over-time theta regimes); constant_IRF == 1 at horizon > 1 runs through gpirt_mcmc as a composition of those handles.
+ * What is not built returns GPIRT_ERR_UNSUPPORTED.
  */
 #ifndef GPIRT_B200_H
 #define GPIRT_B200_H
