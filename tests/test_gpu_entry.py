@@ -248,6 +248,41 @@ def test_r_shim_gpirtMCMC_at_horizon_2():
         assert np.array_equal(out["beta"][..., s], ref["beta"][s]) and np.array_equal(out["thr"][..., s], ref["threshold"][s])
 
 
+def test_r_shim_gpirtMCMC_with_constant_IRF():
+    """constant_IRF = 1 through the R entry point: the shim draws beta for session 0 and one N(0,1) vector per item with R's RNG — 3m + nm draws,
+    the reference's constant branch (src/gpirtMCMC.cpp:176-188) — and the library composes the mode (mcmc_constant); thresholds are shared by the
+    sessions in every kept draw, and the result equals gpirtMCMC() given the same initial values."""
+    import ctypes as C
+
+    import gpirt_b200 as g
+
+    L = _rshim()
+    n, m, Ccat, H, sample = 40, 7, 3, 2, 3
+    Ps = [make_problem(n, m, Ccat, seed=170 + h) for h in range(H)]
+    y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
+    th0 = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1))
+    thr = np.asfortranarray(np.stack([Ps[0]["thr0"]] * H, axis=2))
+    z = np.random.default_rng(3).standard_normal(3 * m + n * m)  # exactly what the constant branch consumes: a longer stream is not needed
+    bpm, bps, tpm, tps = np.zeros((3, m), order="F"), Ps[0]["beta_prior_sds"], np.zeros((2, n), order="F"), np.zeros((2, n), order="F")
+    out = dict(theta=np.zeros((sample, n, H), order="F"), beta=np.zeros((3, m, H, sample), order="F"), thr=np.zeros((m, Ccat + 1, H, sample), order="F"),
+               ll=np.zeros(sample))
+    p = lambda a: a.ctypes.data_as(C.c_void_p)
+    u64 = C.c_uint64
+    rc = L.shim_gpirtMCMC(u64(n), u64(m), u64(H), u64(Ccat), p(y), p(th0), sample, 0, 1, p(bpm), p(bps), p(tpm), p(tps), C.c_double(1.0), C.c_double(1.5),
+                          b"Matern", p(thr), 1, p(z), u64(z.size), C.c_double(0.25), p(out["theta"]), p(out["beta"]), p(out["thr"]), p(out["ll"]), None, None)
+    assert rc == 0, L.shim_last_error().decode()
+    beta0 = np.zeros((3, m, H), order="F")
+    beta0[:, :, 0] = bpm + bps * z[:3 * m].reshape(m, 3).T
+    z0 = np.zeros((n, m, H), order="F")
+    z0[:, :, 0] = z[3 * m:].reshape(m, n).T
+    ref = g.gpirtMCMC(y, sample, 0, THIN=1, CHAIN=1, beta_prior_means=bpm, beta_prior_sds=bps, theta_prior_sds=tps, theta_os=1.0, theta_ls=1.5, KERNEL="Matern",
+                      theta_init=th0, thresholds=thr, SEED=int(0.25 * 4294967296.0), beta_init=beta0, f_init_z=z0, constant_IRF=1)[0]
+    assert np.array_equal(out["theta"], ref["theta"]) and np.array_equal(out["ll"], ref["ll"]) and np.all(np.isfinite(out["ll"]))
+    for s in range(sample):
+        assert np.array_equal(out["beta"][..., s], ref["beta"][s]) and np.array_equal(out["thr"][..., s], ref["threshold"][s])
+        assert np.array_equal(out["thr"][:, :, 0, s], out["thr"][:, :, 1, s])
+
+
 @pytest.mark.parametrize("n,m,C,chains", [(150, 40, 5, 4), (100, 418, 2, 3), (500, 64, 2, 8)])
 def test_batched_chains_equal_the_chains_run_one_at_a_time(n, m, C, chains):
     """BASELINE config 5 (independent chains batched per GPU): gpirtMCMC(CHAIN = k) runs the k chains side by side in one gpirt_mcmc_chains
