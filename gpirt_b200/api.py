@@ -178,7 +178,9 @@ def recover_fstar(seed, f, y, theta, beta, thresholds, beta_prior_means=None, be
     th = _F(np.asarray(theta, dtype=np.float64).reshape(n, H))
     be = np.asfortranarray(np.asarray(beta, dtype=np.float64).reshape(2, m, H))
     thr = np.asarray(thresholds, dtype=np.float64)
-    thr = np.asfortranarray(thr[:, :, None] if thr.ndim == 2 else thr)
+    thr = np.asfortranarray(np.repeat(thr[:, :, None], H, axis=2) if thr.ndim == 2 else thr)
+    if thr.shape[0] != m or thr.shape[2] != H:
+        raise ValueError("thresholds must be m x (C+1) or m x (C+1) x horizon")
     bpm = _F(np.zeros((2, m)) if beta_prior_means is None else beta_prior_means)
     bps = _F(np.full((2, m), 0.5) if beta_prior_sds is None else beta_prior_sds)
     out = np.zeros((NGRID, m, H), order="F")

@@ -23,6 +23,7 @@ static int fail(int code, const char* fmt, ...) {
     va_end(ap);
     return code;
 }
+namespace gpirt { int fail_msg(int code, const char* msg) { return fail(code, "%s", msg); } }  // for entry.cu
 #define CU(x)                                                                                           \
     do {                                                                                                \
         cudaError_t e_ = (x);                                                                           \

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "../../include/gpirt_b200.h"
+namespace gpirt { int fail_msg(int code, const char* msg); }  // capi.cu: sets gpirt_last_error()
 
 extern "C" int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_beta, int draw_f);
 
@@ -91,7 +92,7 @@ static int mcmc_panel(const gpirt_mcmc_args* a, const gpirt_config& cfg) {
 static int mcmc_constant(const gpirt_mcmc_args* a, gpirt_config cfg) {
     const int H = a->horizon, P = 100;  // n_induced_points, src/draw-fstar.cpp:73
     const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1, N = 1001;
-    if (H < 2) return GPIRT_ERR_UNSUPPORTED;  // one session: nothing to share (the reference then only differs by the inducing-point f* draw)
+    if (H < 2) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "constant_IRF = 1 needs horizon >= 2 (one session has nothing to share)");  // one session: nothing to share (the reference then only differs by the inducing-point f* draw)
     cfg.constant_IRF = 0;  // the handles are the ordinary ones
     struct Owner {
         gpirt_panel* p = nullptr; gpirt_sampler* T = nullptr; gpirt_sampler* I = nullptr;
@@ -344,26 +345,76 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     return gpirt_mcmc_chains(a, 1);
 }
 
+// recover_fstar(): ws_pool.seed_all(seed), then draw_f and draw_fstar from the stored f (src/recover_fstar.cpp:80-90). Sessions are independent
+// (constant_IRF == 0: one ordinary handle per session, Philox streams tagged with the session as the chain id) or share one item response
+// function (constant_IRF == 1 at horizon > 1: the stacked sampler + inducing-point sampler of mcmc_constant, 2-row beta).
 extern "C" int gpirt_recover_fstar(const gpirt_recover_fstar_args* a) {
     if (!a || !a->f || !a->y || !a->theta || !a->beta || !a->thresholds || !a->beta_prior_sds || !a->fstar) return GPIRT_ERR_INVALID;
+    if (a->horizon < 1) return GPIRT_ERR_SHAPE;
+    if (a->constant_IRF && a->horizon < 2) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "constant_IRF = 1 needs horizon >= 2 (one session has nothing to share)");
+    const int H = a->horizon;
+    const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1, N = 1001;
     gpirt_config cfg;
     std::memset(&cfg, 0, sizeof(cfg));
-    cfg.n = a->n; cfg.m_total = a->m; cfg.horizon = a->horizon; cfg.C = a->C; cfg.constant_IRF = a->constant_IRF; cfg.p_beta = 2;
+    cfg.n = a->n; cfg.m_total = a->m; cfg.horizon = 1; cfg.C = a->C; cfg.constant_IRF = 0; cfg.p_beta = 2;
     cfg.theta_os = 1.0; cfg.theta_ls = 10.0; cfg.kernel = 0; cfg.device = a->device;
     cfg.seed = (uint64_t)(uint32_t)a->seed;  // ws_pool.seed_all(seed), src/recover_fstar.cpp:80
     cfg.chain = 0; cfg.rank = 0; cfg.world = 1;
-    Guard g;
-    TRYC(gpirt_create(&cfg, &g.h));
-    gpirt_sampler* h = g.h;
-    TRYC(gpirt_set_data_f64(h, a->y));
     // recover_fstar passes a 2 x m beta_prior_sds (R/recover_fstar.R:37-38); K() reads rows 0..2 of column 0
     // (src/covariance-function.cpp:12-14) — an out-of-bounds read in the reference. Row 2 is taken as 0 here.
-    std::vector<double> sds3(3 * (size_t)a->m, 0.0);
-    for (int j = 0; j < a->m; ++j) { sds3[3 * (size_t)j] = a->beta_prior_sds[2 * (size_t)j]; sds3[3 * (size_t)j + 1] = a->beta_prior_sds[2 * (size_t)j + 1]; }
-    TRYC(gpirt_set_priors(h, sds3.data(), nullptr));
-    TRYC(gpirt_set_state(h, a->theta, a->beta, a->f, a->thresholds, nullptr));
-    TRYC(gpirt_set_iter(h, 0));
-    TRYC(gpirt_draw_f(h, nullptr));      // src/recover_fstar.cpp:87-88
-    TRYC(gpirt_draw_fstar(h, nullptr));  // :89-90
-    return gpirt_get_state(h, nullptr, nullptr, nullptr, nullptr, a->fstar);
+    std::vector<double> sds3(3 * m, 0.0);
+    for (size_t j = 0; j < m; ++j) { sds3[3 * j] = a->beta_prior_sds[2 * j]; sds3[3 * j + 1] = a->beta_prior_sds[2 * j + 1]; }
+    if (!a->constant_IRF) {
+        for (int h = 0; h < H; ++h) {
+            Guard g;
+            cfg.chain = (uint32_t)h;
+            TRYC(gpirt_create(&cfg, &g.h));
+            TRYC(gpirt_set_data_f64(g.h, a->y + (size_t)h * n * m));
+            TRYC(gpirt_set_priors(g.h, sds3.data(), nullptr));
+            TRYC(gpirt_set_state(g.h, a->theta + (size_t)h * n, a->beta + (size_t)h * 2 * m, a->f + (size_t)h * n * m, a->thresholds + (size_t)h * m * C1, nullptr));
+            TRYC(gpirt_set_iter(g.h, 0));
+            TRYC(gpirt_draw_f(g.h, nullptr));      // src/recover_fstar.cpp:87-88
+            TRYC(gpirt_draw_fstar(g.h, nullptr));  // :89-90
+            TRYC(gpirt_get_state(g.h, nullptr, nullptr, nullptr, nullptr, a->fstar + (size_t)h * N * m));
+        }
+        return GPIRT_OK;
+    }
+    // constant_IRF == 1: stacked draw_f (src/draw-f.cpp:84-139) with mu_h = [1, theta_h] beta_h, then the inducing-point f* draw (src/draw-fstar.cpp:58-125)
+    const int P = 100;
+    Guard T, I;
+    gpirt_config ct = cfg; ct.n = (int32_t)(n * H);
+    gpirt_config ci = cfg; ci.n = P;
+    TRYC(gpirt_create(&ct, &T.h));
+    TRYC(gpirt_create(&ci, &I.h));
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    std::vector<double> ys(n * H * m), fs(n * H * m), mus(n * H * m), ths(n * H), y_i((size_t)P * m, nan), tind(P), find((size_t)P * m), fstar(N * m);
+    for (int h = 0; h < H; ++h)
+        for (size_t i = 0; i < n; ++i) ths[(size_t)h * n + i] = a->theta[(size_t)h * n + i];
+    for (size_t j = 0; j < m; ++j)
+        for (int h = 0; h < H; ++h) {
+            std::memcpy(&ys[j * n * H + h * n], a->y + (size_t)h * n * m + j * n, n * 8);
+            std::memcpy(&fs[j * n * H + h * n], a->f + (size_t)h * n * m + j * n, n * 8);
+            const double* b = a->beta + (size_t)h * 2 * m + 2 * j;
+            for (size_t i = 0; i < n; ++i) mus[j * n * H + h * n + i] = b[0] + ths[(size_t)h * n + i] * b[1];  // X = [1, theta], :58-66
+        }
+    TRYC(gpirt_set_data_f64(T.h, ys.data()));
+    TRYC(gpirt_set_priors(T.h, sds3.data(), nullptr));
+    TRYC(gpirt_set_state(T.h, ths.data(), a->beta, fs.data(), a->thresholds, nullptr));
+    TRYC(gpirt_set_mean_rows(T.h, mus.data()));
+    TRYC(gpirt_set_iter(T.h, 0));
+    TRYC(gpirt_draw_f(T.h, nullptr));
+    TRYC(gpirt_get_state(T.h, nullptr, nullptr, fs.data(), nullptr, nullptr));
+    const double lo = *std::min_element(ths.begin(), ths.end()), hi = *std::max_element(ths.begin(), ths.end());
+    const double delta = (hi - lo) / double(P - 1);
+    for (int i = 0; i + 1 < P; ++i) tind[i] = lo + double(i) * delta;
+    tind[P - 1] = hi;
+    TRYC(gpirt_interp1(a->device, ths.data(), (int64_t)(n * H), fs.data(), (int64_t)m, tind.data(), P, find.data()));
+    TRYC(gpirt_set_data_f64(I.h, y_i.data()));
+    TRYC(gpirt_set_priors(I.h, sds3.data(), nullptr));
+    TRYC(gpirt_set_state(I.h, tind.data(), a->beta, find.data(), nullptr, nullptr));  // mu* of session 0 (src/draw-fstar.cpp:114)
+    TRYC(gpirt_set_iter(I.h, 0));
+    TRYC(gpirt_draw_fstar(I.h, nullptr));
+    TRYC(gpirt_get_state(I.h, nullptr, nullptr, nullptr, nullptr, fstar.data()));
+    for (int h = 0; h < H; ++h) std::memcpy(a->fstar + (size_t)h * N * m, fstar.data(), N * m * 8);  // :121-124
+    return GPIRT_OK;
 }

@@ -289,6 +289,10 @@ typedef struct {
     const double* beta_prior_means; const double* beta_prior_sds; int32_t constant_IRF; int32_t device;
     double* fstar /* NGRID x m x horizon */;
 } gpirt_recover_fstar_args;
+/* One draw_f + draw_fstar from a stored f, RNG seeded with `seed` (src/recover_fstar.cpp:80-90). f, y: n x m x horizon; theta: n x horizon;
+ * thresholds: m x (C+1) x horizon; beta_prior_sds: 2 x m. constant_IRF == 0: the sessions are drawn one after the other, session h on the
+ * Philox streams of chain id h. constant_IRF == 1 (horizon >= 2): the stacked draw_f with mu_h = [1, theta_h] beta_h, f interpolated onto 100
+ * inducing points, one f* copied to every slice (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125); at horizon == 1 GPIRT_ERR_UNSUPPORTED. */
 int gpirt_recover_fstar(const gpirt_recover_fstar_args* a);
 
 #ifdef __cplusplus

@@ -132,6 +132,79 @@ def test_recover_fstar_equals_draw_f_then_draw_fstar():
     assert np.array_equal(got, S.get_state(fstar=True)["fstar"])
 
 
+def _recover_inputs(n, m, C, H, seed):
+    rng = np.random.default_rng(seed)
+    Ps = [make_problem(n, m, C, seed=seed + h) for h in range(H)]
+    y = np.asfortranarray(np.stack([p["y"] for p in Ps], axis=2))
+    theta = np.asfortranarray(np.stack([p["theta0"] for p in Ps], axis=1))
+    thr = np.asfortranarray(np.stack([p["thr0"] for p in Ps], axis=2))
+    f = np.asfortranarray(rng.standard_normal((n, m, H)))
+    beta = np.asfortranarray(rng.standard_normal((2, m, H)))
+    sds3 = np.zeros((3, m), order="F")
+    sds3[:2] = 0.5
+    return y, theta, thr, f, beta, sds3
+
+
+def test_recover_fstar_over_a_panel_runs_every_session():
+    """horizon > 1, constant_IRF = 0: draw_f / draw_fstar session by session (src/draw-f.cpp:141-179, src/draw-fstar.cpp:127-168)."""
+    import gpirt_b200 as g
+
+    n, m, C, H, seed = 70, 9, 3, 3, 77
+    y, theta, thr, f, beta, sds3 = _recover_inputs(n, m, C, H, 11)
+    got = g.recover_fstar(seed, f, y, theta, beta, thr, beta_prior_sds=sds3[:2])["fstar"]
+    assert got.shape == (g.NGRID, m, H)
+    for h in range(H):
+        S = g.Sampler(n, m, C, seed=seed, chain=h, p_beta=2)
+        S.set_data(y[:, :, h])
+        S.set_priors(sds3, None)
+        S.set_state(theta=theta[:, h], beta=beta[:, :, h], f=f[:, :, h], thresholds=thr[:, :, h])
+        S.set_iter(0)
+        S.draw_f()
+        S.draw_fstar()
+        assert np.array_equal(got[:, :, h], S.get_state(fstar=True)["fstar"])
+        S.close()
+    assert not np.array_equal(got[:, :, 0], got[:, :, 1])
+
+
+def test_recover_fstar_with_constant_IRF_shares_one_curve():
+    """constant_IRF = 1: stacked draw_f (src/draw-f.cpp:84-139), f interpolated to 100 inducing points, one f* for all sessions (src/draw-fstar.cpp:58-125)."""
+    import gpirt_b200 as g
+
+    n, m, C, H, seed = 60, 7, 3, 2, 5
+    y, theta, thr, f, beta, sds3 = _recover_inputs(n, m, C, H, 23)
+    got = g.recover_fstar(seed, f, y, theta, beta, thr, beta_prior_sds=sds3[:2], constant_IRF=1)["fstar"]
+    for h in range(1, H):
+        assert np.array_equal(got[:, :, h], got[:, :, 0])
+    assert np.isfinite(got).all()
+    ths = np.concatenate([theta[:, h] for h in range(H)])
+    ys = np.asfortranarray(np.concatenate([y[:, :, h] for h in range(H)], axis=0))
+    fs = np.asfortranarray(np.concatenate([f[:, :, h] for h in range(H)], axis=0))
+    mu = np.asfortranarray(np.concatenate([beta[0, :, h][None, :] + theta[:, h][:, None] * beta[1, :, h][None, :] for h in range(H)], axis=0))
+    T = g.Sampler(n * H, m, C, seed=seed, p_beta=2)
+    T.set_data(ys)
+    T.set_priors(sds3, None)
+    T.set_state(theta=ths, beta=beta[:, :, 0], f=fs, thresholds=thr[:, :, 0])
+    T.set_mean_rows(mu)
+    T.set_iter(0)
+    T.draw_f()
+    fn = T.get_state()["f"]
+    lo, hi = float(ths.min()), float(ths.max())
+    tind = lo + np.arange(100, dtype=np.float64) * ((hi - lo) / 99)
+    tind[-1] = hi
+    find = g.interp1(ths, fn, tind)
+    I = g.Sampler(100, m, C, seed=seed, p_beta=2)
+    I.set_data(np.full((100, m), np.nan, order="F"))
+    I.set_priors(sds3, None)
+    I.set_state(theta=tind, beta=beta[:, :, 0], f=find)
+    I.set_iter(0)
+    I.draw_fstar()
+    assert np.array_equal(got[:, :, 0], I.get_state(fstar=True)["fstar"])
+    T.close()
+    I.close()
+    with pytest.raises(g.GpirtError):
+        g.recover_fstar(seed, f[:, :, :1], y[:, :, :1], theta[:, :1], beta[:, :, :1], thr[:, :, :1], beta_prior_sds=sds3[:2], constant_IRF=1)
+
+
 # ---- the R-package shim (integration/r-package/src) driven without R, tests/rshim ------------------------------------
 def _rshim():
     import ctypes as C
