@@ -433,7 +433,7 @@ class ConstantPanel(Panel):
       draw_fstar      inducing-point posterior (Sampler.draw_fstar_cst) from the stacked f, mu* of session 0, the same f* for every session
       draw_theta, f <- f* gather, draw_beta, mu / mu* update: per session, unchanged (they take no constant_IRF argument)
       draw_threshold  one ESS per item over all sessions' cells against session 0's thresholds, result copied to every session
-    TEST INFRASTRUCTURE (CPU); the CUDA path does not implement constant_IRF == 1 yet (GPIRT_ERR_UNSUPPORTED)."""
+    TEST INFRASTRUCTURE (CPU); the CUDA counterpart is gpirt_b200.ConstantPanel / mcmc_constant (csrc/entry.cu)."""
 
     def __init__(self, y, C_, beta_prior_sds, theta_prior_sds=None, theta_os=1.0, theta_ls=10.0, KERNEL="Matern"):
         super().__init__(y, C_, beta_prior_sds, theta_prior_sds, theta_os, theta_ls, KERNEL)

@@ -134,6 +134,54 @@ def test_recover_fstar():
     assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-6
 
 
+def _recover_panel_inputs(n, m, C, H):
+    Ps = [make_problem(n, m, C, seed=40 + h, missing=0.1, on_grid=True) for h in range(H)]
+    rng = Ps[0]["rng"]
+    y = np.stack([P["y"] for P in Ps], axis=2)
+    theta = np.stack([P["theta0"] for P in Ps], axis=1)
+    thr = np.stack([P["thr0"] for P in Ps], axis=2)
+    f = np.asfortranarray(rng.standard_normal((n, m, H)))
+    beta2 = np.asfortranarray(rng.standard_normal((2, m, H)))
+    bps3 = np.vstack([np.full((2, m), 0.5), np.zeros((1, m))])
+    beta3 = np.concatenate([beta2, np.zeros((1, m, H))], axis=0)  # a zero quadratic row: the same mu and mu* as the 2-row beta
+    return y, theta, thr, f, beta2, beta3, bps3
+
+
+def test_recover_fstar_over_a_panel():
+    """recover_fstar at horizon 3, constant_IRF 0 (src/recover_fstar.cpp:86-90 -> src/draw-f.cpp:141-179, src/draw-fstar.cpp:127-168): sessions in order."""
+    n, m, C, H = 40, 5, 3, 3
+    y, theta, thr, f, beta2, beta3, bps3 = _recover_panel_inputs(n, m, C, H)
+    R = ref.recover_fstar(77, f, y, theta, beta2, thr, np.zeros((3, m)), bps3)
+    O = orc.Panel(y, C, bps3, None, theta_ls=1.0)
+    O.set_state(theta=theta, beta=beta3, f=f, thr=thr)
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.mt_seed_all(77)
+    for S in O.S:
+        S.draw_f(orc.mt())
+    for S in O.S:
+        assert S.draw_fstar(orc.mt()) == 0
+    assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-6
+
+
+def test_recover_fstar_constant_IRF():
+    """recover_fstar at horizon 2, constant_IRF 1: stacked draw_f with mu_h = [1, theta_h] beta_h (src/draw-f.cpp:84-139), inducing-point f*
+    with mu* of session 0, copied to every slice (src/draw-fstar.cpp:58-125)."""
+    n, m, C, H = 40, 5, 3, 2
+    y, theta, thr, f, beta2, beta3, bps3 = _recover_panel_inputs(n, m, C, H)
+    R = ref.recover_fstar(78, f, y, theta, beta2, thr, np.zeros((3, m)), bps3, constant_IRF=1)
+    assert np.array_equal(R[:, :, 0], R[:, :, 1])
+    O = orc.ConstantPanel(y, C, bps3, None, theta_ls=1.0)
+    O.set_state(theta=theta, beta=beta3, f=f, thr=thr)
+    O.compute_mu()
+    O.mt_seed_all(78)
+    O.draw_f(orc.mt())
+    assert O.draw_fstar(orc.mt()) == 0
+    got = O.state()["fstar"]
+    assert np.array_equal(got[:, :, 0], got[:, :, 1])
+    assert np.max(np.abs(got - R)) < 2e-5  # the inducing-point solve runs at kappa ~ 1e12 (DESIGN 11b)
+
+
 @pytest.mark.parametrize("regime,ls,kernel", [("RDM", 0.05, "Matern"), ("GP", 2.0, "Matern"), ("GP", 4.0, "RBF")])
 def test_gpirtMCMC_horizon_3_same_draws(regime, ls, kernel):
     """horizon > 1 (dynamic GPIRT): the oracle's panel of single-session samplers + joint theta step against the reference's own
