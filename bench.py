@@ -296,7 +296,8 @@ def ours(args):
         assert all(np.all(np.isfinite(r["ll"])) for r in res)
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
-            r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 1, 0, args.ref_items)
+            # ~10-30 s of CPU work: 1000 of the 5000 items (the extrapolation in m is then 5x, not 125x), 1 warm + 8 timed sweeps
+            r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 8, 1, max(args.ref_items, 1000))
             line["cpu_baseline"] = {"value": r["value"], "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
     else:
         # the same call sharded: every rank uploads its columns / rows of the pinned fp64 y, runs the chain with the exchanges, and reads
@@ -344,7 +345,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ref-items", type=int, default=40, help="items in the CPU baseline's bounded sample")
+    ap.add_argument("--ref-items", type=int, default=200, help="items in the CPU baseline's bounded sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
