@@ -288,6 +288,14 @@ def test_r_shim_recover_fstar_and_error_path():
     # a library error becomes Rcpp::stop(message) -> an R error; here a C++ exception carrying gpirt_last_error()
     rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(Ccat), p(f), p(y), p(th), p(beta2), p(P["thr0"]), p(bpm), p(bps), 1, p(out))
     assert rc == 1 and b"constant_IRF" in L.shim_last_error()
+    # cubes with 2 slices through the same entry point, per-session and with one shared curve
+    y2, th2, thr2, f2, b2, sds3 = _recover_inputs(n, m, Ccat, 2, 31)
+    out2 = np.zeros((g.NGRID, m, 2), order="F")
+    for cirf in (0, 1):
+        rc = L.shim_recover_fstar(55, u64(n), u64(m), u64(2), u64(Ccat), p(f2), p(y2), p(th2), p(b2), p(thr2), p(bpm), p(bps), cirf, p(out2))
+        assert rc == 0, L.shim_last_error().decode()
+        assert np.array_equal(out2, g.recover_fstar(55, f2, y2, th2, b2, thr2, beta_prior_sds=bps, constant_IRF=cirf)["fstar"])
+        assert np.array_equal(out2[:, :, 0], out2[:, :, 1]) == bool(cirf)
 
 
 def test_r_shim_gpirtMCMC_at_horizon_2():
