@@ -344,9 +344,10 @@ class Panel:
         self.n, self.m, self.H = y.shape
         self.C = int(C_)
         H = self.H
-        if theta_ls >= 3 * H:
+        if theta_ls >= 3 * H and H > 1:
             raise ValueError("CST regime at horizon > 1: the reference reads thresholds out of bounds (src/draw-theta.cpp:162)")
-        self.regime = 1 if theta_ls <= 0.1 else 2
+        # regime 0: one session in the CST regime (theta_ls >= 3, R's default 10): the session's own theta step (src/draw-theta.cpp:112-170)
+        self.regime = 0 if theta_ls >= 3 * H else (1 if theta_ls <= 0.1 else 2)
         self.S = [Sampler(y[:, :, h], C_, beta_prior_sds, theta_prior_sds) for h in range(H)]
         for h in range(1, H):
             lib().orc_share_mts(self.S[h]._h, self.S[0]._h)
@@ -385,6 +386,9 @@ class Panel:
     def draw_theta(self, srcs):
         """srcs: one Src per session (RDM) or a single Src (GP; H normals per respondent)"""
         srcs = list(srcs) if isinstance(srcs, (list, tuple)) else [srcs]
+        if self.regime == 0:
+            self.S[0].draw_theta(srcs[0])
+            return
         arr = (Src * len(srcs))()
         for k, s in enumerate(srcs):
             for fld, _ in Src._fields_:
@@ -404,7 +408,7 @@ class Panel:
         for h, S in enumerate(self.S):
             if S.draw_fstar(src_of("fstar", h)) != 0:
                 return 2
-        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime == 1 else src_of("theta", None))
+        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime != 2 else src_of("theta", None))
         for S in self.S:
             S.gather_f()
         for h, S in enumerate(self.S):
@@ -504,7 +508,7 @@ class ConstantPanel(Panel):
         self.draw_f(src_of("f", None))
         if self.draw_fstar(src_of("fstar", None)) != 0:
             return 2
-        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime == 1 else src_of("theta", None))
+        self.draw_theta([src_of("theta", h) for h in range(self.H)] if self.regime != 2 else src_of("theta", None))
         for S in self.S:
             S.gather_f()
         for h, S in enumerate(self.S):

@@ -226,12 +226,37 @@ def test_gpirtMCMC_horizon_3_same_draws(regime, ls, kernel):
     assert np.max(np.abs(s["fstar"] - R["fstar"][..., -1])) < 1e-5
 
 
-@pytest.mark.parametrize("regime,ls", [("RDM", 0.05), ("GP", 2.5)])
-def test_gpirtMCMC_constant_IRF_same_draws(regime, ls):
+@pytest.mark.parametrize("ls,os_,tp", [(10.0, 1.0, 0.4), (0.05, 1.0, 0.4), (2.5, 1.3, 0.4), (2.5, 1.0, 0.0)])
+def test_gpirtMCMC_one_session_in_every_theta_regime(ls, os_, tp):
+    """horizon 1 with theta_ls in the CST (>= 3), RDM (<= 0.1) and GP (between) branches of src/draw-theta.cpp:112,171,206 and non-zero
+    theta_prior_sds: the oracle's single-session sampler against the reference's own run, theta bit for bit."""
+    n, m, C, iters = 64, 10, 5, 4
+    P = make_problem(n, m, C, seed=9, missing=0.1)
+    z = np.random.default_rng(10).standard_normal(3 * m + n * m)
+    tps = np.asfortranarray(np.vstack([np.full((1, n), tp), np.zeros((1, n))]))
+    bpm, bps, tpm = np.zeros((3, m)), P["beta_prior_sds"], np.zeros((2, n))
+    R = ref.gpirtMCMC(P["y"], P["theta0"], iters, 1, 1, bpm, bps, tpm, tps, os_, ls, "Matern", P["thr0"], 0, z)
+    theta0 = np.clip(P["theta0"], -5, 5)
+    beta0 = bpm + bps * z[:3 * m].reshape(m, 3).T
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.stack([L0 @ z[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1)
+    O = orc.Sampler(P["y"], C, bps, tps, theta_regime=1 if 0.1 < ls < 3.0 else 0, theta_os=os_)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.draw_fstar(orc.mt())
+    info, th, ll = O.run_mt(0, iters + 1)
+    assert info == 0
+    assert np.array_equal(th[:, 1:].T, R["theta"][:, :, 0])
+    assert np.allclose(ll[1:], R["ll"], rtol=1e-9, atol=0)
+
+
+@pytest.mark.parametrize("regime,ls,H", [("RDM", 0.05, 2), ("GP", 2.5, 2), ("CST", 10.0, 1), ("GP", 2.5, 1)])
+def test_gpirtMCMC_constant_IRF_same_draws(regime, ls, H):
     """constant_IRF == 1 (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96,181-205, init src/gpirtMCMC.cpp:164-200):
     the oracle's ConstantPanel (panel + one stacked sampler over the n*H rows + the inducing-point f* draw) against the reference's own run,
     one thread: theta / beta / thresholds bit for bit; f* is the solution of a 100-point inducing system with kappa ~ 1e12 (1e-3 absolute)."""
-    n, m, C, H, iters = 30, 5, 4, 2, 3
+    n, m, C, iters = 30, 5, 4, 3
     Ps = [make_problem(n, m, C, seed=70 + h, missing=0.1) for h in range(H)]
     y = np.asfortranarray(np.stack([P["y"] for P in Ps], axis=2))
     theta_in = np.asfortranarray(np.stack([P["theta0"] for P in Ps], axis=1))
@@ -244,7 +269,7 @@ def test_gpirtMCMC_constant_IRF_same_draws(regime, ls):
     L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
     f0 = np.asfortranarray(np.stack([L0 @ z[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1))
     O = orc.ConstantPanel(y, C, bps, tps, theta_os=1.0, theta_ls=ls, KERNEL="Matern")
-    assert O.regime == (1 if regime == "RDM" else 2)
+    assert O.regime == {"CST": 0, "RDM": 1, "GP": 2}[regime]  # CST: one session only (at H > 1 the reference aborts there)
     O.init_constant(theta0, beta0, f0, thr0)
     assert O.draw_fstar(orc.mt()) == 0  # initial draw_fstar on the unseeded generators (src/gpirtMCMC.cpp:227)
     for it in range(iters):
@@ -254,7 +279,7 @@ def test_gpirtMCMC_constant_IRF_same_draws(regime, ls):
         assert np.array_equal(s["theta"], R["theta"][it]), f"sweep {it}"
         assert np.array_equal(s["beta"], R["beta"][..., it])
         assert np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, :, it])
-        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, 1]) and np.array_equal(s["thr"][:, :, 0], s["thr"][:, :, 1])
+        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, -1]) and np.array_equal(s["thr"][:, :, 0], s["thr"][:, :, -1])
         assert abs(O.total_ll() - R["ll"][it]) <= 1e-7 * abs(R["ll"][it])
         assert np.max(np.abs(s["f"] - R["f"][..., it])) < 1e-4 and np.max(np.abs(s["fstar"] - R["fstar"][..., it])) < 2e-3
 
