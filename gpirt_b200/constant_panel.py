@@ -26,8 +26,6 @@ N_INDUCED = 100  # src/draw-fstar.cpp:73
 
 class ConstantPanel:
     def __init__(self, n, m, Ccat, horizon, *, theta_os=1.0, theta_ls=10.0, KERNEL="Matern", seed=0, chain=0, device=0):
-        if horizon < 2:
-            raise GpirtError(_lib.ERR_UNSUPPORTED, "constant_IRF == 1 needs horizon > 1 (with one session it is the ordinary sampler up to the f* draw)")
         self.n, self.m, self.C, self.H, self.device = int(n), int(m), int(Ccat), int(horizon), device
         self.P = Panel(n, m, Ccat, horizon, theta_os=theta_os, theta_ls=theta_ls, KERNEL=KERNEL, seed=seed, chain=chain, device=device)
         self.S = self.P.S

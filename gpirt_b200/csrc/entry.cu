@@ -92,7 +92,7 @@ static int mcmc_panel(const gpirt_mcmc_args* a, const gpirt_config& cfg) {
 static int mcmc_constant(const gpirt_mcmc_args* a, gpirt_config cfg) {
     const int H = a->horizon, P = 100;  // n_induced_points, src/draw-fstar.cpp:73
     const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1, N = 1001;
-    if (H < 2) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "constant_IRF = 1 needs horizon >= 2 (one session has nothing to share)");  // one session: nothing to share (the reference then only differs by the inducing-point f* draw)
+    // H == 1 is a legal call in the reference too: the ordinary sampler with the f* draw taken through the inducing points
     cfg.constant_IRF = 0;  // the handles are the ordinary ones
     struct Owner {
         gpirt_panel* p = nullptr; gpirt_sampler* T = nullptr; gpirt_sampler* I = nullptr;
@@ -347,11 +347,10 @@ extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
 
 // recover_fstar(): ws_pool.seed_all(seed), then draw_f and draw_fstar from the stored f (src/recover_fstar.cpp:80-90). Sessions are independent
 // (constant_IRF == 0: one ordinary handle per session, Philox streams tagged with the session as the chain id) or share one item response
-// function (constant_IRF == 1 at horizon > 1: the stacked sampler + inducing-point sampler of mcmc_constant, 2-row beta).
+// function (constant_IRF == 1: the stacked sampler + inducing-point sampler of mcmc_constant, 2-row beta).
 extern "C" int gpirt_recover_fstar(const gpirt_recover_fstar_args* a) {
     if (!a || !a->f || !a->y || !a->theta || !a->beta || !a->thresholds || !a->beta_prior_sds || !a->fstar) return GPIRT_ERR_INVALID;
     if (a->horizon < 1) return GPIRT_ERR_SHAPE;
-    if (a->constant_IRF && a->horizon < 2) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "constant_IRF = 1 needs horizon >= 2 (one session has nothing to share)");
     const int H = a->horizon;
     const size_t n = a->n, m = a->m, C1 = (size_t)a->C + 1, N = 1001;
     gpirt_config cfg;

@@ -30,7 +30,7 @@
  * fallback: without a CUDA device every compute call returns GPIRT_ERR_NO_DEVICE.
  *
  * Scope of this build: a gpirt_sampler is one session with constant_IRF == 0 (all BASELINE configs); horizon > 1 is a gpirt_panel
- * (RDM and GP-over-time theta regimes); constant_IRF == 1 at horizon > 1 runs through gpirt_mcmc as a composition of those handles.
+ * (RDM and GP-over-time theta regimes); constant_IRF == 1 (any horizon) runs through gpirt_mcmc / gpirt_recover_fstar as a composition of those handles.
  * What is not built returns GPIRT_ERR_UNSUPPORTED.
  */
 #ifndef GPIRT_B200_H
@@ -52,7 +52,7 @@ typedef enum {
     GPIRT_ERR_CATEGORIES = 3,     /* C < 2 or C > 21, or a y code outside 1..C */
     GPIRT_ERR_NOT_PD = 4,         /* chol failed (arma::chol throws); gpirt_last_error names the leading minor */
     GPIRT_ERR_CUDA = 5,
-    GPIRT_ERR_UNSUPPORTED = 6,    /* a mode that is not built (e.g. constant_IRF != 0 at horizon 1 or on a single handle, theta_ls >= 3H at H > 1) */
+    GPIRT_ERR_UNSUPPORTED = 6,    /* a mode that is not built (e.g. constant_IRF != 0 on a single handle - gpirt_mcmc composes it -, theta_ls >= 3H at H > 1) */
     GPIRT_ERR_STREAM_OVERRUN = 7, /* a supplied uniform stream ran dry before an ESS loop accepted */
     GPIRT_ERR_NO_DEVICE = 8,
     GPIRT_ERR_ESS_STALLED = 9     /* an ESS loop hit the proposal cap (reference would spin forever) */
@@ -270,7 +270,7 @@ typedef struct {
      * Ignored when f_init is given. */
     const double* f_init_z;
 } gpirt_mcmc_args;
-/* constant_IRF == 1 (horizon > 1): composed from a panel, a stacked sampler over the n*horizon rows and a 100-respondent inducing-point sampler
+/* constant_IRF == 1 (any horizon; with one session the reference's branch is the ordinary sampler with the inducing-point f* draw): composed from a panel, a stacked sampler over the n*horizon rows and a 100-respondent inducing-point sampler
  * (csrc/entry.cu mcmc_constant; src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96). beta_init / f_init / f_init_z are
  * then read for session 0 only (the reference's constant branch draws nothing else, src/gpirtMCMC.cpp:176-188). */
 int gpirt_mcmc(const gpirt_mcmc_args* a);
@@ -291,8 +291,8 @@ typedef struct {
 } gpirt_recover_fstar_args;
 /* One draw_f + draw_fstar from a stored f, RNG seeded with `seed` (src/recover_fstar.cpp:80-90). f, y: n x m x horizon; theta: n x horizon;
  * thresholds: m x (C+1) x horizon; beta_prior_sds: 2 x m. constant_IRF == 0: the sessions are drawn one after the other, session h on the
- * Philox streams of chain id h. constant_IRF == 1 (horizon >= 2): the stacked draw_f with mu_h = [1, theta_h] beta_h, f interpolated onto 100
- * inducing points, one f* copied to every slice (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125); at horizon == 1 GPIRT_ERR_UNSUPPORTED. */
+ * Philox streams of chain id h. constant_IRF == 1: the stacked draw_f with mu_h = [1, theta_h] beta_h, f interpolated onto 100
+ * inducing points, one f* copied to every slice (src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125). */
 int gpirt_recover_fstar(const gpirt_recover_fstar_args* a);
 
 #ifdef __cplusplus

@@ -182,7 +182,7 @@ def cst_case(name, n, m, C, H, seed, iters, ls):
         for h, S in enumerate(O.S):
             zz, u, nz, nu = S.recorded("beta", 3, UCAP)
             rec[f"z_beta_{it}_{h}"], rec[f"u_beta_{it}_{h}"], rec[f"nu_beta_{it}_{h}"] = zz, u, nu
-            if O.regime == 1:
+            if O.regime != 2:  # RDM, or one session in the CST regime: the session's own theta streams
                 zz, u, nz, nu = S.recorded("theta", 1, UCAP)
                 rec[f"z_theta_{it}_{h}"], rec[f"u_theta_{it}_{h}"], rec[f"nu_theta_{it}_{h}"] = zz, u, nu
         if O.regime == 2:
@@ -242,6 +242,7 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["cst"]:
         cst_case("cst_rdm_h2", n=30, m=5, C=4, H=2, seed=81, iters=2, ls=0.05)
         cst_case("cst_gp_h2", n=30, m=5, C=3, H=2, seed=91, iters=2, ls=2.5)
+        cst_case("cst_cst_h1", n=40, m=6, C=4, H=1, seed=101, iters=2, ls=10.0)
         sys.exit(0)
     leaf_case()
     sweep_case("sweep_ordinal_c4", n=48, m=8, C=4, seed=11, iters=3, missing=0.1)
@@ -251,3 +252,4 @@ if __name__ == "__main__":
     datasets()
     cst_case("cst_rdm_h2", n=30, m=5, C=4, H=2, seed=81, iters=2, ls=0.05)
     cst_case("cst_gp_h2", n=30, m=5, C=3, H=2, seed=91, iters=2, ls=2.5)
+    cst_case("cst_cst_h1", n=40, m=6, C=4, H=1, seed=101, iters=2, ls=10.0)

@@ -63,12 +63,9 @@ def test_argument_validation_before_any_device_work():
     assert L.gpirt_sweep(None, 1) == _lib.ERR_INVALID
     with pytest.raises(gpirt_b200.GpirtError):
         gpirt_b200.gpirtMCMC(np.ones((4, 3)), 2, 0, vote_codes={"yea": [1]})
-    # recover_fstar: constant_IRF = 1 needs sessions to share the curve across (refused before any device work, with a message);
-    # a thresholds cube must carry one slice per session
+    # recover_fstar: a thresholds cube must carry one slice per session
     n, m, Ccat = 6, 3, 3
     thr = gpirt_b200.default_thresholds(m, Ccat)
-    with pytest.raises(gpirt_b200.GpirtError, match="horizon >= 2"):
-        gpirt_b200.recover_fstar(1, np.zeros((n, m)), np.ones((n, m)), np.zeros(n), np.zeros((2, m)), thr, constant_IRF=1)
     with pytest.raises(ValueError, match="thresholds"):
         gpirt_b200.recover_fstar(1, np.zeros((n, m, 2)), np.ones((n, m, 2)), np.zeros((n, 2)), np.zeros((2, m, 2)), thr[:, :, None])
 

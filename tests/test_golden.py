@@ -254,16 +254,17 @@ def test_cuda_panel_replays_reference_horizon_3_sweeps(name):
 
 
 # ---- constant_IRF == 1: the reference's own H = 2 runs, streams recorded for the stacked blocks / per session -----------------------------
-CSTS = ["cst_rdm_h2", "cst_gp_h2"]
+CSTS = ["cst_rdm_h2", "cst_gp_h2", "cst_cst_h1"]  # the last: one session, R's default theta_ls = 10 (CST regime)
 
 
 @pytest.mark.parametrize("name", CSTS)
 def test_oracle_constant_irf_panel_replays_reference_sweeps(name):
     """The oracle's ConstantPanel (oracle/orc.py) driven by the streams the reference consumed (tests/golden/make_golden.py cst_case): theta
-    bit-exact, identical proposal counts in the stacked f / threshold blocks, beta / thresholds 1e-9. The CUDA path returns
-    GPIRT_ERR_UNSUPPORTED for constant_IRF == 1; this fixture is what its implementation will be replayed against on the GPU box."""
+    bit-exact, identical proposal counts in the stacked f / threshold blocks, beta / thresholds 1e-9. The same fixtures are
+    replayed by the CUDA composition in test_cuda_constant_irf_panel_replays_reference_sweeps."""
     G = load(name)
-    n, m, C, H, rdm = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"]), float(G["ls"]) <= 0.1
+    n, m, C, H = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"])
+    rdm = float(G["ls"]) <= 0.1 or H == 1  # per-session theta streams
     O = orc.ConstantPanel(G["y"], C, G["beta_prior_sds"], G["theta_prior_sds"], theta_os=1.0, theta_ls=float(G["ls"]), KERNEL="Matern")
     O.init_constant(np.clip(G["theta_in"], -5, 5), G["beta0"], G["f0"], G["thr0"])
     for S in O.S:
@@ -303,7 +304,8 @@ def test_cuda_constant_irf_panel_replays_reference_sweeps(name):
     from gpirt_b200.constant_panel import ConstantPanel
 
     G = load(name)
-    n, m, C, H, rdm = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"]), float(G["ls"]) <= 0.1
+    n, m, C, H = int(G["n"]), int(G["m"]), int(G["C"]), int(G["H"])
+    rdm = float(G["ls"]) <= 0.1 or H == 1  # per-session theta streams
     P = ConstantPanel(n, m, C, H, theta_os=1.0, theta_ls=float(G["ls"]), KERNEL="Matern")
     P.set_data(G["y"])
     P.set_priors(G["beta_prior_sds"], G["theta_prior_sds"])
@@ -332,7 +334,7 @@ def test_cuda_constant_irf_panel_replays_reference_sweeps(name):
             nu = G[f"nu_{key}_{it}"]
             assert np.array_equal(np.where(nu > 0, ev, 0), nu), f"sweep {it}: stacked block {key} made a different number of proposals"
         assert np.max(np.abs(s["f"] - G["ref_f"][..., it])) < 5e-3
-        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, 1])
+        assert np.array_equal(s["fstar"][:, :, 0], s["fstar"][:, :, -1])
     assert np.max(np.abs(s["fstar"] - G["ref_fstar_last"])) < 5e-3
     P.close()
 

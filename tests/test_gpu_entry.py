@@ -201,8 +201,10 @@ def test_recover_fstar_with_constant_IRF_shares_one_curve():
     assert np.array_equal(got[:, :, 0], I.get_state(fstar=True)["fstar"])
     T.close()
     I.close()
-    with pytest.raises(g.GpirtError):
-        g.recover_fstar(seed, f[:, :, :1], y[:, :, :1], theta[:, :1], beta[:, :, :1], thr[:, :, :1], beta_prior_sds=sds3[:2], constant_IRF=1)
+    # one session: the reference runs the same branch (the f* draw then goes through the inducing points instead of the n respondents)
+    one = g.recover_fstar(seed, f[:, :, :1], y[:, :, :1], theta[:, :1], beta[:, :, :1], thr[:, :, :1], beta_prior_sds=sds3[:2], constant_IRF=1)["fstar"]
+    plain = g.recover_fstar(seed, f[:, :, :1], y[:, :, :1], theta[:, :1], beta[:, :, :1], thr[:, :, :1], beta_prior_sds=sds3[:2])["fstar"]
+    assert one.shape == plain.shape == (g.NGRID, m, 1) and np.isfinite(one).all() and not np.array_equal(one, plain)
 
 
 # ---- the R-package shim (integration/r-package/src) driven without R, tests/rshim ------------------------------------
@@ -286,8 +288,9 @@ def test_r_shim_recover_fstar_and_error_path():
     assert rc == 0, L.shim_last_error().decode()
     assert np.array_equal(out, g.recover_fstar(321, f, y, th, beta2, P["thr0"], beta_prior_sds=bps)["fstar"][:, :, 0])
     # a library error becomes Rcpp::stop(message) -> an R error; here a C++ exception carrying gpirt_last_error()
-    rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(Ccat), p(f), p(y), p(th), p(beta2), p(P["thr0"]), p(bpm), p(bps), 1, p(out))
-    assert rc == 1 and b"constant_IRF" in L.shim_last_error()
+    thr_bad = np.zeros((m, 31), order="F")
+    rc = L.shim_recover_fstar(321, u64(n), u64(m), u64(1), u64(30), p(f), p(y), p(th), p(beta2), p(thr_bad), p(bpm), p(bps), 0, p(out))
+    assert rc == 1 and b"C = 30 outside" in L.shim_last_error()
     # cubes with 2 slices through the same entry point, per-session and with one shared curve
     y2, th2, thr2, f2, b2, sds3 = _recover_inputs(n, m, Ccat, 2, 31)
     out2 = np.zeros((g.NGRID, m, 2), order="F")

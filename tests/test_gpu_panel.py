@@ -165,3 +165,25 @@ def test_gpirtMCMC_constant_IRF_runs_the_constant_panel(regime, ls):
             assert np.array_equal(a[key][k], b[key][k]), f"{key} draw {k}: C entry point != stepwise ConstantPanel"
     c = g.gpirtMCMC(y, 4, 2, THIN=2, first_chain=1, **kw)[0]
     assert not np.array_equal(a["theta"], c["theta"])
+
+
+@pytest.mark.gpu
+def test_gpirtMCMC_constant_IRF_with_one_session():
+    """constant_IRF = 1 at horizon 1 with R's default theta_ls = 10 (CST regime): a legal call in the reference (the f* draw then runs through the
+    100 inducing points); C entry point == the block-by-block ConstantPanel loop, bit for bit. The composition itself is pinned to the reference's
+    own run by tests/golden/cst_cst_h1.npz (test_golden.py)."""
+    import gpirt_b200 as g
+    from gpirt_b200.api import _as_cube, _gpirtMCMC_constant_irf
+
+    n, m, C = 80, 7, 3
+    P = make_problem(n, m, C, seed=410, missing=0.1)
+    kw = dict(theta_init=P["theta0"], thresholds=P["thr0"], SEED=4, constant_IRF=1, store_f=True, store_fstar=True)
+    a = g.gpirtMCMC(P["y"], 4, 1, THIN=2, **kw)[0]
+    assert a["theta"].shape == (2, n, 1) and np.all(np.isfinite(a["ll"])) and np.all(a["ll"] < 0)
+    b = _gpirtMCMC_constant_irf(_as_cube(P["y"]), 4, 1, 2, 1, None, None, None, None, 1, 10, "Matern", P["theta0"].reshape(n, 1), P["thr0"], 4, True, True, 0, None, 0)[0]
+    assert np.array_equal(a["theta"], b["theta"]) and np.array_equal(a["ll"], b["ll"])
+    for k in range(2):
+        for key in ("beta", "threshold", "f", "fstar"):
+            assert np.array_equal(a[key][k], b[key][k]), f"{key} draw {k}"
+    plain = g.gpirtMCMC(P["y"], 4, 1, THIN=2, **dict(kw, constant_IRF=0))[0]
+    assert not np.array_equal(a["theta"], plain["theta"])  # the f* draw differs, and with it the theta step
