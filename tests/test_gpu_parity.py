@@ -181,6 +181,31 @@ def test_draw_theta_same_states(n, m, C):
     assert np.array_equal(S.get_state()["f"], O.state()["f"])  # pure indexing: bit-exact
 
 
+@pytest.mark.parametrize("ls,os_", [(10.0, 1.0), (0.05, 1.0), (2.5, 1.3), (1.5, 0.7)])
+def test_draw_theta_of_one_session_in_every_regime(ls, os_):
+    """horizon 1 takes the branch theta_ls selects (src/draw-theta.cpp:112 CST, :171 RDM, :206 GP with the 1 x 1 L_time): each with its own
+    prior scale, as the oracle restates it (pinned to the reference's own runs in
+    tests/test_oracle_vs_ref.py::test_gpirtMCMC_one_session_in_every_theta_regime); non-zero theta_prior_sds."""
+    n, m, C = 160, 25, 4
+    P = make_problem(n, m, C, seed=33, on_grid=True)
+    P["theta_prior_sds"] = np.asfortranarray(np.vstack([np.full((1, n), 0.4), np.zeros((1, n))]))
+    rng = P["rng"]
+    S = gpirt_b200.Sampler(n, m, C, seed=1, theta_ls=ls, theta_os=os_)
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    O = orc.Sampler(P["y"], C, P["beta_prior_sds"], P["theta_prior_sds"], theta_regime=1 if 0.1 < ls < 3.0 else 0, theta_os=os_)
+    f0 = np.asfortranarray(rng.standard_normal((n, m)))
+    fstar = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+    _set_both(S, O, P["theta0"], P["beta0"], f0, P["thr0"], fstar)
+    z = np.asfortranarray(rng.standard_normal((1, n)))
+    u = uniform_streams(rng, n)
+    S.draw_theta(z=z, u=u)
+    O.draw_theta(orc.supplied(z=z, u=u))
+    assert np.array_equal(S.diag("theta")[0], O.diag("theta")[0])
+    assert np.array_equal(S.get_state()["theta"], O.state()["theta"])
+    S.close()
+
+
 @pytest.mark.parametrize("n,m,C", [(150, 30, 2), (120, 45, 5)])
 def test_draw_beta_and_threshold_same_states(n, m, C):
     P = make_problem(n, m, C, seed=41, on_grid=True)
