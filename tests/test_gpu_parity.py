@@ -479,7 +479,8 @@ def test_cholesky_cache_with_look_ahead_equals_the_plain_two_level_factorisation
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged")])
+@pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged"),
+                                        (90, 14, 3, "holes")])
 def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_streams(n, m, C, name):
     """Whole sweeps (gpirt_sweep: overlapped schedule, fp32 screening, block inverse) against the oracle's sweep on the SAME Philox streams, at the
     shapes of BASELINE.json's configs 1 and 2 (synthetic responses; the .rda front-end is out of scope) with the reference's default priors
@@ -487,6 +488,11 @@ def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_stream
     import gpirt_b200 as g
 
     P = make_problem(n, m, C, seed=77, missing=0.06)
+    if name == "holes":  # a respondent without answers, an item nobody answered, an item with one answer (the reference's own run on such
+        P["y"][5, :] = np.nan  # an input: tests/test_oracle_vs_ref.py::test_gpirtMCMC_with_a_respondent_and_an_item_without_answers)
+        P["y"][:, 2] = np.nan
+        P["y"][:, 4] = np.nan
+        P["y"][11, 4] = 2.0
     seed, chain, sweeps = 2024, 1, 2
     S = g.Sampler(n, m, C, seed=seed, chain=chain)
     S.set_data(P["y"])

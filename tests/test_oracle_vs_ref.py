@@ -116,6 +116,36 @@ def test_gpirtMCMC_same_draws_over_several_sweeps():
     assert np.max(np.abs(s["f"] - R["f"][:, :, 0, -1])) < 1e-5
 
 
+def test_gpirtMCMC_with_a_respondent_and_an_item_without_answers():
+    """Ragged input: respondent 5 answered nothing (empty obs_items: every theta proposal has ll = 0 and the first one is accepted,
+    src/draw-theta.cpp:4-24,44-84), item 2 was answered by nobody (draw_beta skips it, src/draw-beta.cpp:73), item 4 by one respondent only."""
+    n, m, C, iters = 40, 7, 3, 4
+    P = make_problem(n, m, C, seed=19, missing=0.3)
+    P["y"][5, :] = np.nan
+    P["y"][:, 2] = np.nan
+    P["y"][:, 4] = np.nan
+    P["y"][11, 4] = 2.0
+    z = np.random.default_rng(20).standard_normal(3 * m + n * m)
+    bpm, bps, tpm, tps = np.zeros((3, m)), P["beta_prior_sds"], np.zeros((2, n)), P["theta_prior_sds"]
+    R = ref.gpirtMCMC(P["y"], P["theta0"], iters, 0, 1, bpm, bps, tpm, tps, 1.0, 10.0, "Matern", P["thr0"], 0, z)
+    theta0 = np.clip(P["theta0"], -5, 5)
+    beta0 = bpm + bps * z[:3 * m].reshape(m, 3).T
+    L0 = ref.update_cholesky_cache(theta0, bps)[0][:, :, 0]
+    f0 = np.stack([L0 @ z[3 * m + j * n:3 * m + (j + 1) * n] for j in range(m)], axis=1)
+    O = orc.Sampler(P["y"], C, bps, tps)
+    O.set_state(theta=theta0, beta=beta0, f=f0, thr=P["thr0"])
+    O.compute_mu()
+    assert O.update_cholesky() == 0
+    O.draw_fstar(orc.mt())
+    info, th, ll = O.run_mt(0, iters)
+    assert info == 0
+    assert np.array_equal(th.T, R["theta"][:, :, 0])
+    assert np.allclose(ll, R["ll"], rtol=1e-9, atol=0)
+    s = O.state()
+    assert np.array_equal(s["beta"], R["beta"][:, :, 0, -1]) and np.array_equal(s["beta"][:, 2], beta0[:, 2])
+    assert np.array_equal(s["thr"][:, 1:-1], R["threshold"][:, 1:-1, 0, -1])
+
+
 def test_recover_fstar():
     n, m, C = 50, 6, 3
     P = make_problem(n, m, C, seed=12, missing=0.1, on_grid=True)
