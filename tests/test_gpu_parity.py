@@ -480,7 +480,7 @@ def test_cholesky_cache_with_look_ahead_equals_the_plain_two_level_factorisation
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged"),
-                                        (90, 14, 3, "holes")])
+                                        (90, 14, 3, "holes"), (220, 18, 21, "GPIRT_MAX_C categories")])
 def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_streams(n, m, C, name):
     """Whole sweeps (gpirt_sweep: overlapped schedule, fp32 screening, block inverse) against the oracle's sweep on the SAME Philox streams, at the
     shapes of BASELINE.json's configs 1 and 2 (synthetic responses; the .rda front-end is out of scope) with the reference's default priors

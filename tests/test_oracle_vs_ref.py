@@ -59,7 +59,7 @@ def test_cholesky_cache_and_double_solve():
         ref.update_cholesky_cache(np.array([0.0, 0.0]), np.array([[0.0], [0.0], [np.nan]]))
 
 
-@pytest.mark.parametrize("C,seed", [(2, 1), (5, 2)])
+@pytest.mark.parametrize("C,seed", [(2, 1), (5, 2), (12, 3), (21, 4)])  # 21 = GPIRT_MAX_C
 def test_blocks_same_state_and_same_rng_consumption(C, seed):
     n, m = 70, 9
     P = make_problem(n, m, C, seed=seed, missing=0.15, on_grid=True)
