@@ -194,13 +194,14 @@ def test_recover_fstar_over_a_panel():
     assert np.max(np.abs(O.state()["fstar"] - R)) < 1e-6
 
 
-def test_recover_fstar_constant_IRF():
-    """recover_fstar at horizon 2, constant_IRF 1: stacked draw_f with mu_h = [1, theta_h] beta_h (src/draw-f.cpp:84-139), inducing-point f*
+@pytest.mark.parametrize("H", [2, 1])
+def test_recover_fstar_constant_IRF(H):
+    """recover_fstar at horizon 2 (and with one session), constant_IRF 1: stacked draw_f with mu_h = [1, theta_h] beta_h (src/draw-f.cpp:84-139), inducing-point f*
     with mu* of session 0, copied to every slice (src/draw-fstar.cpp:58-125)."""
-    n, m, C, H = 40, 5, 3, 2
+    n, m, C = 40, 5, 3
     y, theta, thr, f, beta2, beta3, bps3 = _recover_panel_inputs(n, m, C, H)
     R = ref.recover_fstar(78, f, y, theta, beta2, thr, np.zeros((3, m)), bps3, constant_IRF=1)
-    assert np.array_equal(R[:, :, 0], R[:, :, 1])
+    assert np.array_equal(R[:, :, 0], R[:, :, -1])
     O = orc.ConstantPanel(y, C, bps3, None, theta_ls=1.0)
     O.set_state(theta=theta, beta=beta3, f=f, thr=thr)
     O.compute_mu()
@@ -208,7 +209,7 @@ def test_recover_fstar_constant_IRF():
     O.draw_f(orc.mt())
     assert O.draw_fstar(orc.mt()) == 0
     got = O.state()["fstar"]
-    assert np.array_equal(got[:, :, 0], got[:, :, 1])
+    assert np.array_equal(got[:, :, 0], got[:, :, -1])
     assert np.max(np.abs(got - R)) < 2e-5  # the inducing-point solve runs at kappa ~ 1e12
 
 
