@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <type_traits>
@@ -39,15 +40,37 @@ namespace gpirt { int fail_msg(int code, const char* msg) { return fail(code, "%
 
 // Device allocations go through a small per-process cache: gpirtMCMC() creates and destroys a handle per call (arena, theta-step table, draw
 // store, upload staging: ~1 GB at C3), and cudaMalloc / cudaFree of blocks that size map and unmap device memory — tens of milliseconds on a
-// busy host, more than the sweeps of a short call. A freed block of >= 1 MB is kept (exact size match on reuse, at most 32 blocks / 24 GB,
-// oldest evicted) until gpirt_release_cached_memory(); like cudaFree, dev_free synchronises the device first.
+// busy host, more than the sweeps of a short call. A freed block of >= 1 MB is kept for an exact-size reuse on the same device. The cache is
+// bounded by GPIRT_CACHE_MB (default 4096 MB per process, 0 disables it; at most 32 blocks, oldest evicted) because other allocators in the
+// process (torch, NCCL) cannot see or reclaim what is parked here; gpirt_release_cached_memory() empties it. Like cudaFree, dev_free
+// synchronises the block's device first.
 namespace {
 struct CachedBlock { void* p; size_t bytes; int device; };
 std::mutex g_alloc_mu;
 std::vector<CachedBlock> g_free_blocks;
 std::map<void*, std::pair<size_t, int>> g_live_blocks;
 size_t g_cached_bytes = 0;
-constexpr size_t CACHE_MIN_BLOCK = (size_t)1 << 20, CACHE_MAX_BYTES = (size_t)24 << 30, CACHE_MAX_BLOCKS = 32;
+constexpr size_t CACHE_MIN_BLOCK = (size_t)1 << 20, CACHE_MAX_BLOCKS = 32;
+size_t cache_max_bytes() {
+    static const size_t cap = [] {
+        const char* e = getenv("GPIRT_CACHE_MB");
+        const long long mb = e ? atoll(e) : 4096;
+        return (size_t)(mb > 0 ? mb : 0) << 20;
+    }();
+    return cap;
+}
+struct DeviceScope {  // run a few calls on another device, then return to the caller's
+    int prev = -1;
+    explicit DeviceScope(int device) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev != device) cudaSetDevice(device); else prev = -1;
+    }
+    ~DeviceScope() { if (prev >= 0) cudaSetDevice(prev); }
+};
+cudaError_t free_on(void* p, int device) {
+    DeviceScope ds(device);
+    return cudaFree(p);
+}
 }  // namespace
 
 static cudaError_t dev_malloc(void** p, size_t bytes) {
@@ -74,7 +97,7 @@ static cudaError_t dev_malloc(void** p, size_t bytes) {
             drop.swap(g_free_blocks);
             g_cached_bytes = 0;
         }
-        for (const CachedBlock& b : drop) cudaFree(b.p);
+        for (const CachedBlock& b : drop) free_on(b.p, b.device);
         e = cudaMalloc(p, bytes);
         if (e != cudaSuccess) return e;
     }
@@ -95,25 +118,38 @@ static cudaError_t dev_free(void* p) {
         device = it->second.second;
         g_live_blocks.erase(it);
     }
-    if (bytes < CACHE_MIN_BLOCK) return cudaFree(p);
+    DeviceScope ds(device);  // the block's device, not whatever the calling thread has current
+    if (bytes < CACHE_MIN_BLOCK || bytes > cache_max_bytes()) return cudaFree(p);
     cudaDeviceSynchronize();  // cudaFree's implicit synchronisation: nothing in flight may still use the block when it is handed out again
-    void* evict = nullptr;
+    std::vector<CachedBlock> evict;
     {
         std::lock_guard<std::mutex> lk(g_alloc_mu);
-        if (bytes > CACHE_MAX_BYTES) evict = p;
-        else {
-            g_free_blocks.push_back({p, bytes, device});
-            g_cached_bytes += bytes;
-            while (g_free_blocks.size() > CACHE_MAX_BLOCKS || g_cached_bytes > CACHE_MAX_BYTES) {
-                if (evict) break;  // one eviction per call keeps this simple; the next free evicts the next
-                evict = g_free_blocks.front().p;
-                g_cached_bytes -= g_free_blocks.front().bytes;
-                g_free_blocks.erase(g_free_blocks.begin());
-            }
+        g_free_blocks.push_back({p, bytes, device});
+        g_cached_bytes += bytes;
+        while (g_free_blocks.size() > CACHE_MAX_BLOCKS || g_cached_bytes > cache_max_bytes()) {
+            evict.push_back(g_free_blocks.front());
+            g_cached_bytes -= g_free_blocks.front().bytes;
+            g_free_blocks.erase(g_free_blocks.begin());
         }
     }
-    return evict ? cudaFree(evict) : cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    for (const CachedBlock& b : evict) {
+        cudaError_t eb = free_on(b.p, b.device);
+        if (eb != cudaSuccess) e = eb;
+    }
+    return e;
 }
+
+// temporaries of one call: freed on every return path
+struct DevTemp {
+    void* p = nullptr;
+    DevTemp() = default;
+    DevTemp(const DevTemp&) = delete;
+    DevTemp& operator=(const DevTemp&) = delete;
+    ~DevTemp() { if (p) dev_free(p); }
+    cudaError_t alloc(size_t bytes) { return dev_malloc(&p, bytes); }
+    template <class T> T* as() const { return (T*)p; }
+};
 
 extern "C" int gpirt_release_cached_memory(void) {
     std::vector<CachedBlock> drop;
@@ -122,7 +158,7 @@ extern "C" int gpirt_release_cached_memory(void) {
         drop.swap(g_free_blocks);
         g_cached_bytes = 0;
     }
-    for (const CachedBlock& b : drop) cudaFree(b.p);
+    for (const CachedBlock& b : drop) free_on(b.p, b.device);
     return GPIRT_OK;
 }
 
@@ -511,10 +547,11 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
     long long max_rows = 1, max_count = 1;
     for (const Block& b : blocks) { max_rows = std::max(max_rows, b.nrows); max_count = std::max(max_count, b.nrows * b.ncols); }
     const long long slab_cols = std::max(1LL, (256LL << 20) / (8LL * max_rows));
-    double* d_y = nullptr;
-    int8_t* d_i8 = nullptr;
-    CU(dev_malloc((void**)&d_i8, (size_t)max_count));
-    CU(dev_malloc((void**)&d_y, (size_t)std::min<long long>(slab_cols * max_rows, max_count) * 8));
+    DevTemp t_y, t_i8;
+    CU(t_i8.alloc((size_t)max_count));
+    CU(t_y.alloc((size_t)std::min<long long>(slab_cols * max_rows, max_count) * 8));
+    double* d_y = t_y.as<double>();
+    int8_t* d_i8 = t_i8.as<int8_t>();
     int rc = GPIRT_OK;
     CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
     CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
@@ -533,8 +570,6 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
         if (e != cudaSuccess) rc = fail(GPIRT_ERR_CUDA, "y layouts: %s", cudaGetErrorString(e));
     }
     cudaStreamSynchronize(h->stream);
-    dev_free(d_y);
-    dev_free(d_i8);
     if (rc != GPIRT_OK) return rc;
     h->have_data = true;
     return check_flags(h);
@@ -547,12 +582,11 @@ int gpirt_set_data_i8(gpirt_sampler* h, const int8_t* y) {
     const size_t count = (size_t)h->n * h->m_total;
     for (size_t e = 0; e < count; ++e)
         if (y[e] < 0 || y[e] > h->C) return fail(GPIRT_ERR_CATEGORIES, "response code %d outside 0..%d at element %zu", (int)y[e], h->C, e);
-    int8_t* d_full = nullptr;
-    CU(dev_malloc((void**)&d_full, count));
-    CU(cudaMemcpyAsync(d_full, y, count, cudaMemcpyHostToDevice, h->stream));
-    int rc = build_layouts(h, d_full);
+    DevTemp t_full;
+    CU(t_full.alloc(count));
+    CU(cudaMemcpyAsync(t_full.p, y, count, cudaMemcpyHostToDevice, h->stream));
+    int rc = build_layouts(h, t_full.as<int8_t>());
     cudaStreamSynchronize(h->stream);
-    dev_free(d_full);
     return rc;
 }
 
@@ -640,15 +674,15 @@ int gpirt_set_state(gpirt_sampler* h, const double* theta, const double* beta, c
         CU(cudaMemcpy2DAsync(h->f, (size_t)h->ldn * 8, f + (size_t)h->item0 * h->n, (size_t)h->n * 8, (size_t)h->n * 8, h->m_local,
                              cudaMemcpyHostToDevice, st));
     if (fstar) {  // NGRID x m_total column-major -> every chunk of the grid-row-major table
-        double* tmp = nullptr;
-        CU(dev_malloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        DevTemp t_tmp;
+        CU(t_tmp.alloc((size_t)NGRID * h->m_total * 8));
+        double* tmp = t_tmp.as<double>();
         CU(cudaMemcpyAsync(tmp, fstar, (size_t)NGRID * h->m_total * 8, cudaMemcpyHostToDevice, st));
         for (int r = 0; r < h->world; ++r) {
             const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
             if (cols > 0) CU(launch_transpose(st, tmp + (size_t)j0 * NGRID, NGRID, NGRID, cols, h->fstar + (size_t)r * NGRID * h->ld_chunk, h->ld_chunk));
         }
         CU(cudaStreamSynchronize(st));
-        dev_free(tmp);
     }
     CU(cudaStreamSynchronize(st));
     return GPIRT_OK;
@@ -679,8 +713,9 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
         CU(cudaMemcpy2DAsync(f + (size_t)h->item0 * h->n, (size_t)h->n * 8, h->f, (size_t)h->ldn * 8, (size_t)h->n * 8, h->m_local,
                              cudaMemcpyDeviceToHost, st));
     if (fstar) {
-        double* tmp = nullptr;
-        CU(dev_malloc((void**)&tmp, (size_t)NGRID * h->m_total * 8));
+        DevTemp t_tmp;
+        CU(t_tmp.alloc((size_t)NGRID * h->m_total * 8));
+        double* tmp = t_tmp.as<double>();
         for (int r = 0; r < h->world; ++r) {
             const int j0 = r * h->m_chunk, cols = std::min(h->m_chunk, h->m_total - j0);
             // chunk is cols x NGRID (ld_chunk) column-major in (j, idx); transpose back to NGRID x cols
@@ -688,7 +723,6 @@ int gpirt_get_state(gpirt_sampler* h, double* theta, double* beta, double* f, do
         }
         CU(cudaMemcpyAsync(fstar, tmp, (size_t)NGRID * h->m_total * 8, cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
-        dev_free(tmp);
     }
     CU(cudaStreamSynchronize(st));
     return GPIRT_OK;
@@ -1261,39 +1295,41 @@ int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* 
 int gpirt_K(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, const double* sds3, double* out) {
     if (!x1 || !x2 || !sds3 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K: bad arguments");
     TRY(select_device(device));
-    double *d1, *d2, *dK;
-    CU(dev_malloc((void**)&d1, n1 * 8)); CU(dev_malloc((void**)&d2, n2 * 8)); CU(dev_malloc((void**)&dK, n1 * n2 * 8));
+    DevTemp t1, t2, tK;
+    CU(t1.alloc(n1 * 8)); CU(t2.alloc(n2 * 8)); CU(tK.alloc(n1 * n2 * 8));
+    double *d1 = t1.as<double>(), *d2 = t2.as<double>(), *dK = tK.as<double>();
     CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
     CU(build_K(0, d1, (int)n1, d2, (int)n2, sds3, dK, (int)n1, 0.0));
     CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
-    dev_free(d1); dev_free(d2); dev_free(dK);
     return GPIRT_OK;
 }
 int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int64_t n2, double os, double ls, const double* tsds2,
                  int kernel, double* out) {
     if (!x1 || !x2 || !tsds2 || !out || n1 < 1 || n2 < 1) return fail(GPIRT_ERR_INVALID, "gpirt_K_time: bad arguments");
     TRY(select_device(device));
-    double *d1, *d2, *dK;
-    CU(dev_malloc((void**)&d1, n1 * 8)); CU(dev_malloc((void**)&d2, n2 * 8)); CU(dev_malloc((void**)&dK, n1 * n2 * 8));
+    DevTemp t1, t2, tK;
+    CU(t1.alloc(n1 * 8)); CU(t2.alloc(n2 * 8)); CU(tK.alloc(n1 * n2 * 8));
+    double *d1 = t1.as<double>(), *d2 = t2.as<double>(), *dK = tK.as<double>();
     CU(cudaMemcpy(d1, x1, n1 * 8, cudaMemcpyHostToDevice)); CU(cudaMemcpy(d2, x2, n2 * 8, cudaMemcpyHostToDevice));
     CU(cudaMemset(dK, 0, n1 * n2 * 8));  // an unknown KERNEL string leaves the matrix untouched in the reference; here zeros
     CU(build_K_time(0, d1, (int)n1, d2, (int)n2, os, ls, tsds2[0], tsds2[1], kernel, dK, (int)n1));
     CU(cudaMemcpy(out, dK, n1 * n2 * 8, cudaMemcpyDeviceToHost));
-    dev_free(d1); dev_free(d2); dev_free(dK);
     return GPIRT_OK;
 }
 int gpirt_chol(int device, const double* A, int64_t n, double* L) {
     if (!A || !L || n < 1) return fail(GPIRT_ERR_INVALID, "gpirt_chol: bad arguments");
     TRY(select_device(device));
     const int ld = pad_ld(n);
-    double* dA; int* info; int hinfo = 0;
-    CU(dev_malloc((void**)&dA, (size_t)ld * n * 8)); CU(dev_malloc((void**)&info, 4 * (1 + chol_ws_ints((int)n))));
+    DevTemp tA, tI;
+    int hinfo = 0;
+    CU(tA.alloc((size_t)ld * n * 8)); CU(tI.alloc(4 * (1 + chol_ws_ints((int)n))));
+    double* dA = tA.as<double>();
+    int* info = tI.as<int>();
     CU(cudaMemset(dA, 0, (size_t)ld * n * 8)); CU(cudaMemset(info, 0, 4));
     CU(cudaMemcpy2D(dA, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
     CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1));
     CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(&hinfo, info, 4, cudaMemcpyDeviceToHost));
-    dev_free(dA); dev_free(info);
     if (hinfo) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed at leading minor %d", hinfo);
     return GPIRT_OK;
 }
@@ -1301,15 +1337,15 @@ int gpirt_double_solve(int device, const double* L, int64_t n, const double* X, 
     if (!L || !X || !out || n < 1 || nrhs < 1) return fail(GPIRT_ERR_INVALID, "gpirt_double_solve: bad arguments");
     TRY(select_device(device));
     const int ld = pad_ld(n);
-    double *dL, *dX;
-    CU(dev_malloc((void**)&dL, (size_t)ld * n * 8)); CU(dev_malloc((void**)&dX, (size_t)ld * nrhs * 8));
+    DevTemp tL, tX;
+    CU(tL.alloc((size_t)ld * n * 8)); CU(tX.alloc((size_t)ld * nrhs * 8));
+    double *dL = tL.as<double>(), *dX = tX.as<double>();
     CU(cudaMemset(dL, 0, (size_t)ld * n * 8)); CU(cudaMemset(dX, 0, (size_t)ld * nrhs * 8));
     CU(cudaMemcpy2D(dL, (size_t)ld * 8, L, n * 8, n * 8, n, cudaMemcpyHostToDevice));
     CU(cudaMemcpy2D(dX, (size_t)ld * 8, X, n * 8, n * 8, nrhs, cudaMemcpyHostToDevice));
     CU(trsm_left_lower(0, dL, ld, (int)n, dX, ld, (int)nrhs));
     CU(trsm_left_lower_t(0, dL, ld, (int)n, dX, ld, (int)nrhs));
     CU(cudaMemcpy2D(out, n * 8, dX, (size_t)ld * 8, n * 8, nrhs, cudaMemcpyDeviceToHost));
-    dev_free(dL); dev_free(dX);
     return GPIRT_OK;
 }
 
@@ -1335,15 +1371,15 @@ int gpirt_init_draw(gpirt_sampler* h, const double* beta_prior_means, int draw_b
     cudaStream_t st = h->stream;
     if (draw_beta) {
         if (h->cfg.p_beta != 3) return fail(GPIRT_ERR_SHAPE, "init_draw: beta has 3 rows in gpirtMCMC");
-        double* d_means = nullptr;
-        CU(dev_malloc((void**)&d_means, 3 * (size_t)h->m_total * 8));
+        DevTemp t_means;
+        CU(t_means.alloc(3 * (size_t)h->m_total * 8));
+        double* d_means = t_means.as<double>();
         if (beta_prior_means) CU(cudaMemcpyAsync(d_means, beta_prior_means, 3 * (size_t)h->m_total * 8, cudaMemcpyHostToDevice, st));
         else CU(cudaMemsetAsync(d_means, 0, 3 * (size_t)h->m_total * 8, st));
         k_init_beta<<<(h->m_total + 127) / 128, 128, 0, st>>>(h->beta, d_means, h->sds, h->m_total, h->key());
         ++g_kernel_launches;
         CU(cudaGetLastError());
         CU(cudaStreamSynchronize(st));
-        dev_free(d_means);
     }
     if (draw_f && h->m_local > 0) {
         if (!h->chol_valid) TRY(do_update_cholesky(h));
@@ -1623,12 +1659,12 @@ int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int c
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
-    double* d = nullptr;
-    CU(dev_malloc((void**)&d, (size_t)rows * cols * 8));
+    DevTemp t_d;
+    CU(t_d.alloc((size_t)rows * cols * 8));
+    double* d = t_d.as<double>();
     CU(launch_gen_normals(h->stream, d, rows, rows, cols, h->key(), stream, unit0));
     CU(cudaMemcpyAsync(out, d, (size_t)rows * cols * 8, cudaMemcpyDeviceToHost, h->stream));
     CU(cudaStreamSynchronize(h->stream));
-    dev_free(d);
     return GPIRT_OK;
 }
 
@@ -1646,14 +1682,14 @@ __global__ void k_debug_probit(const double* x, int n, double* phi_out, double* 
 extern "C" int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out) {
     if (!x || !phi_out || !log_out || n < 1) return fail(GPIRT_ERR_INVALID, "debug_probit: bad arguments");
     TRY(select_device(device));
-    double* d = nullptr;
-    CU(dev_malloc((void**)&d, (size_t)3 * n * 8));
+    DevTemp t_d;
+    CU(t_d.alloc((size_t)3 * n * 8));
+    double* d = t_d.as<double>();
     CU(cudaMemcpy(d, x, (size_t)n * 8, cudaMemcpyHostToDevice));
     k_debug_probit<<<(n + 255) / 256, 256>>>(d, n, d + n, d + 2 * (size_t)n);
     CU(cudaGetLastError());
     CU(cudaMemcpy(phi_out, d + n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(log_out, d + 2 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
-    dev_free(d);
     return GPIRT_OK;
 }
 
@@ -1671,8 +1707,9 @@ extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau
                                   double* t64) {
     if (!g || !tau_lo || !tau_hi || !t32 || !e32 || !t64 || n < 1) return fail(GPIRT_ERR_INVALID, "debug_cell32: bad arguments");
     TRY(select_device(device));
-    double* d = nullptr;
-    CU(dev_malloc((void**)&d, (size_t)6 * n * 8));
+    DevTemp t_d;
+    CU(t_d.alloc((size_t)6 * n * 8));
+    double* d = t_d.as<double>();
     CU(cudaMemcpy(d, g, (size_t)n * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d + n, tau_lo, (size_t)n * 8, cudaMemcpyHostToDevice));
     CU(cudaMemcpy(d + 2 * (size_t)n, tau_hi, (size_t)n * 8, cudaMemcpyHostToDevice));
@@ -1681,6 +1718,5 @@ extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau
     CU(cudaMemcpy(t32, d + 3 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(e32, d + 4 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(t64, d + 5 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
-    dev_free(d);
     return GPIRT_OK;
 }

@@ -3,6 +3,7 @@
 // behind double_solve / solve(trimatl(L), kstar) (src/cholesky-cache.cpp:4-9, src/draw-fstar.cpp:30).
 #include "linalg.cuh"
 
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 
@@ -16,11 +17,13 @@ template <int BM, int BN, int BK, int WM, int WN, int STAGES, bool TA, bool TB>
 static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
     using Cfg = GemmCfg<BM, BN, BK, WM, WN, STAGES, TA, TB>;
     auto kern = gemm_f64_kernel<BM, BN, BK, WM, WN, STAGES, TA, TB>;
-    static bool configured = false;  // per instantiation
-    if (!configured) {
+    static std::atomic<unsigned long long> configured{0};  // per instantiation, one bit per device: the opt-in is a per-device attribute
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 64 || !(configured.load(std::memory_order_relaxed) >> dev & 1ULL)) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
         if (e != cudaSuccess) return e;
-        configured = true;
+        if (dev < 64) configured.fetch_or(1ULL << dev, std::memory_order_relaxed);
     }
     dim3 grid(((g.N + BN - 1) / BN) * ((g.M + BM - 1) / BM), 1, g.batch > 1 ? g.batch : 1);
     kern<<<grid, Cfg::THREADS, Cfg::SMEM_BYTES, st>>>(g);
@@ -29,12 +32,9 @@ static cudaError_t launch_gemm(cudaStream_t st, const GemmArgs& g) {
 }
 
 static int sm_count() {
-    static int sms = 0;
-    if (!sms) {
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
-    }
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
     return sms;
 }
 

@@ -83,6 +83,9 @@ __host__ __device__ __forceinline__ double phi(double x) {
 
 // log(x) for positive normal x (the likelihood's argument lies in [1e-6, 1 + 1e-6])
 __host__ __device__ __forceinline__ double log_pos(double x) {
+    // the exponent-bit arithmetic below reads NaN as ~ +-710: a NaN state must reach the ESS test as NaN (never accepted -> stall flag), as std::log
+    // gives it in the reference (log(0) = -inf, log(negative) = NaN)
+    if (!(x > 0.0)) return x == 0.0 ? -HUGE_VAL : x * HUGE_VAL * 0.0;
 #ifdef __CUDA_ARCH__
     const long long bits = __double_as_longlong(x);
 #else
@@ -175,6 +178,9 @@ __device__ __forceinline__ void cell_ll32_core(float a, float b, float u, float 
     const float dp = fmaf(fmaf(4e-7f, u * u, 4e-6f), qu, fmaf(4e-7f, v * v, 4e-6f) * qv) + 2.4e-7f * (p + straddle);
     const float den = p - dp;
     e = (den > dp ? dp * f_rcp(den) * 1.0001f : 14.0f) + fmaf(5e-7f, fabsf(t), 2e-6f);
+    // fminf(|NaN|, 9.25) is 9.25: a NaN argument (NaN in f / beta / a threshold, or inf - inf) would otherwise pass as a deep-tail cell with a small bound.
+    // A NaN bound fails both screening comparisons, so the proposal goes to the fp64 pass, which carries the NaN into the ESS test (never accepted -> stall flag).
+    if (a != a || b != b) e = CUDART_NAN_F;
 }
 __device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi, float& t, float& e) {
     const float a = (float)__dsub_rn(tau_lo, g), b = (float)__dsub_rn(tau_hi, g);

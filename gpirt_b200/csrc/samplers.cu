@@ -604,10 +604,9 @@ cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     const size_t row_bytes = ((size_t)v.m_total + 15) / 16 * 16;
     w.y_in_smem = row_bytes <= (wide ? (size_t)96 << 10 : (size_t)24 << 10) && row_bytes <= (size_t)v.ldm;  // keeps >= 2 wide / 8 narrow CTAs per SM
     const size_t smem = w.y_in_smem ? row_bytes : 0;
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_ess_theta<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
-        attr_set = true;
+    if (wide && smem > ((size_t)48 << 10)) {  // the opt-in is per device (one process may drive several): set where it is needed, it costs microseconds
+        cudaError_t ea = cudaFuncSetAttribute(k_ess_theta<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
+        if (ea != cudaSuccess) return ea;
     }
     if (wide) k_ess_theta<1024><<<v.n_local, 1024, smem, st>>>(w);
     else k_ess_theta<256><<<v.n_local, 256, smem, st>>>(w);

@@ -387,3 +387,32 @@ def test_batched_chains_equal_the_chains_run_one_at_a_time(n, m, C, chains):
             for s in range(3):
                 assert np.array_equal(together[c][key][s], alone[key][s]), f"chain {c}: {key} draw {s} differs"
     assert not np.array_equal(together[0]["theta"], together[1]["theta"])
+
+
+@pytest.mark.parametrize("screen", [1, 0])
+def test_a_NaN_state_stalls_the_ESS_loop_instead_of_scoring_finite_garbage(screen):
+    """A NaN in the latent state makes every likelihood NaN: std::log / R::pnorm carry it in the reference, where `ll > log_y` is then never
+    true and the shrink loop spins for ever (src/draw-f.cpp:23-41 has no cap). Here the fp32 screen must not decide such a proposal (its bound
+    becomes NaN) and the fp64 pass must not turn NaN into a finite number (log_pos reads exponent bits): the loop runs into
+    ESS_MAX_PROPOSALS and the call returns GPIRT_ERR_ESS_STALLED."""
+    import gpirt_b200
+    from gpirt_b200 import _lib
+
+    n, m, C = 96, 6, 4
+    P = make_problem(n, m, C, seed=3)
+    S = gpirt_b200.Sampler(n, m, C, seed=11)
+    S.set_screen(screen)
+    S.set_data(P["y"])
+    S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+    f0 = np.zeros((n, m), order="F")
+    f0[7, 2] = np.nan
+    P["y"][7, 2] = 2.0  # the poisoned cell is observed
+    S.set_data(P["y"])
+    S.set_state(theta=P["theta0"], beta=P["beta0"], f=f0, thresholds=P["thr0"])
+    rng = np.random.default_rng(0)
+    nu = np.asfortranarray(rng.standard_normal((n, m)))
+    with pytest.raises(gpirt_b200.GpirtError) as e:
+        S.draw_f(nu=nu)
+        S.sync()
+    assert e.value.code == _lib.ERR_ESS_STALLED
+    S.close()

@@ -480,7 +480,11 @@ def test_cholesky_cache_with_look_ahead_equals_the_plain_two_level_factorisation
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("n,m,C,name", [(100, 418, 2, "C1 senate116 shape"), (1500, 16, 5, "C2 SDO shape"), (333, 75, 7, "ragged"),
-                                        (90, 14, 3, "holes"), (220, 18, 21, "GPIRT_MAX_C categories")])
+                                        (90, 14, 3, "holes"), (220, 18, 21, "GPIRT_MAX_C categories"),
+                                        # the kernel variants BASELINE configs 3 / 4 / 5 select (samplers.cu item_warps, linalg.cu two-level blocking):
+                                        (2000, 96, 5, "C3 respondent count: 8-warp item kernels, 32 Cholesky panels"),
+                                        (5000, 24, 2, "C5 respondent count: 16-warp item kernels, two-level Cholesky with look-ahead inside a sweep"),
+                                        (4500, 16, 7, "C4 category count at n > 4096")])
 def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_streams(n, m, C, name):
     """Whole sweeps (gpirt_sweep: overlapped schedule, fp32 screening, block inverse) against the oracle's sweep on the SAME Philox streams, at the
     shapes of BASELINE.json's configs 1 and 2 (synthetic responses; the .rda front-end is out of scope) with the reference's default priors
@@ -518,3 +522,33 @@ def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_stream
         # f* also extrapolates to |theta*| = 5 from respondents inside about +-2.7 (values ~100): K^-1 f is kappa-limited there
         assert colrel(a["f"], b["f"]) < 4e-6 and colrel(a["fstar"], b["fstar"]) < 3e-5
         assert abs(S.total_ll() - O.total_ll()) <= 1e-7 * abs(O.total_ll())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("threads", [256, 1024])
+def test_draw_theta_over_a_wide_item_row_matches_oracle(threads):
+    """Config 4's theta step: m = 50 000 items per respondent row. With m > 24 576 the 256-thread kernel no longer stages the respondent's row of y
+    in shared memory (samplers.cu launch_ess_theta, y_in_smem == false) and with m > 12 000 the per-sweep term table is the unscreened fp64 one
+    (capi.cu do_draw_theta): both branches against the oracle on supplied streams, theta bit-exact, identical proposal counts
+    (src/draw-theta.cpp:4-84,112-170)."""
+    from gpirt_b200 import _lib
+
+    n, m, C = 48, 26500, 2
+    P = make_problem(n, m, C, seed=35, on_grid=True)
+    rng = P["rng"]
+    try:
+        _lib.check(_lib.lib().gpirt_debug_theta_threads(threads))
+        S, O = _pair(P)
+        f0 = np.zeros((n, m), order="F")
+        fstar = np.asfortranarray(rng.standard_normal((orc.NGRID, m)) * 0.3)
+        _set_both(S, O, P["theta0"], P["beta0"] * 0.1, f0, P["thr0"], fstar)
+        z = np.asfortranarray(rng.standard_normal((1, n)))
+        u = uniform_streams(rng, n, stride=96)
+        S.draw_theta(z=z, u=u)
+        O.draw_theta(orc.supplied(z=z, u=u))
+        assert np.array_equal(S.diag("theta")[0], O.diag("theta")[0])
+        assert O.diag("theta")[1].min() > 1e-9
+        assert np.array_equal(S.get_state(f=False)["theta"], O.state()["theta"])
+        S.close()
+    finally:
+        _lib.lib().gpirt_debug_theta_threads(0)
