@@ -2,8 +2,8 @@
 // (n * horizon values, many of them equal once theta lives on the 0.01 grid) are sorted, duplicated abscissae dropped keeping the first in
 // stable order (lowest row index), and every item's column of f is interpolated linearly onto the inducing points XI; NaN outside [min X, max X].
 // Device side: a stable key-index sort and a unique pass (thrust), then one thread per (inducing point, item) with a binary search.
-// LIMIT OF THE PARITY CLAIM: keeping the LOWEST row index among equal abscissae is this library's deterministic rule (shared with the oracle and
-// the stand-in header oracle/refshim/RcppArmadillo.h), not Armadillo's documented behaviour: arma::interp1 removes duplicates through find_unique,
+// LIMIT OF THE PARITY CLAIM: keeping the LOWEST row index among equal abscissae is this library's deterministic rule (shared with the test checker and
+// its stand-in Armadillo header), not Armadillo's documented behaviour: arma::interp1 removes duplicates through find_unique,
 // which runs an unstable std::sort over (value, index) packets, so which duplicate survives in a real R build is implementation-defined. After
 // draw_f the duplicated thetas carry different f values, hence the constant_IRF = 1 draws are pinned to the reference's own code run against the
 // stand-in interp1 only — not to a real Armadillo build.
