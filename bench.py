@@ -26,7 +26,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_RESP, M_PER_GPU, C_CAT = 2000, 5000, 5
-FP64_DMMA_PEAK_TFLOPS = 37.1  # measured on this pool's B200, profiles/r01_microbench_fp64.txt (MEASURED_PEAKS.json has no fp64 entry)
+FP64_DMMA_PEAK_FALLBACK = 37.1  # profiles/r01_microbench_fp64.txt; used only if the in-run microbenchmark (gpirt_debug_fp64_peak) fails
 
 
 def measured_peaks():
@@ -46,7 +46,7 @@ class ClockSampler:
     def start(self):
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i", str(self.index), "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -79,51 +79,123 @@ def synth(n, m, C, seed):
 
 
 # ------------------------------------------------------------------------------------------------------------------
-def cpu_reference_sweeps(n, m_full, C, seed, steps, warmup, m_sub):
-    """The reference algorithm (oracle port, faithful mode: second Cholesky, per-respondent table copies, per-item
-    gemv/trsv — SURVEY.md A.7) on all host cores, on a BOUNDED sample: the first m_sub items of the workload.
-    The oracle clocks the work shared by all items (Cholesky of K, k* solves, K_post) separately from the per-item /
-    per-respondent work, which is linear in m; the full-size rate is 1/(t_shared + t_items * m_full/m_sub)."""
+def cpu_sweeps(n, m, C, seed, *, faithful, warm, max_timed, min_timed, budget_s, state=None, blas=True):
+    """Full-size sweeps of the reference algorithm on the host cores (the oracle port; R is absent from this image).
+
+    faithful=1 ("ref-faithful"): the sweep as the reference codes it — second Cholesky per sweep (src/draw-f.cpp:59), both N x m tables copied
+    per respondent in draw_theta (src/draw-theta.cpp:144-156), per-item dense gemv / two trsv (src/mvnormal.h:23, src/cholesky-cache.cpp:4-9).
+    faithful=0 ("ref-tidy"): the same arithmetic without the redundant Cholesky and the table copies.
+    blas: chol / trsm / syrk / gemv / trsv through the OpenBLAS of the scipy wheel (oracle/orc_blas.h), as an R linked against an optimised
+    BLAS would run Armadillo's calls; otherwise the oracle's own loops. Threads are set explicitly (torchrun exports OMP_NUM_THREADS=1).
+    Every timed sweep is a whole sweep over all m items; nothing is extrapolated. Timed sweeps stop at max_timed, or once min_timed are done
+    and the next one would overrun budget_s."""
     from oracle import orc
 
-    cores = os.cpu_count() or 1
-    P = synth(n, m_sub, C, seed)
-
-    mm = m_sub
-    y = np.where(P["y"][:, :mm] == 0, np.nan, P["y"][:, :mm].astype(np.float64))
-    O = orc.Sampler(y, C, P["beta_prior_sds"][:, :mm], P["theta_prior_sds"], faithful=1)
-    O.set_state(theta=P["theta0"], beta=P["beta0"][:, :mm], thr=P["thr0"][:mm], f=np.zeros((n, mm)))
-    O.compute_mu()
-    assert O.update_cholesky() == 0
-    O.run_mt(0, warmup, store=False)
+    threads = os.cpu_count() or 1
+    orc.set_threads(threads)
+    blas_path = orc.use_blas(True, threads) if blas else (orc.use_blas(False) or None)
+    P = synth(n, m, C, seed)
+    y = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
+    O = orc.Sampler(y, C, P["beta_prior_sds"], P["theta_prior_sds"], faithful=faithful)
+    if state is None:
+        O.set_state(theta=P["theta0"], beta=P["beta0"], thr=P["thr0"])
+        O.compute_mu()
+        assert O.update_cholesky() == 0
+        f0 = np.asfortranarray(O.L() @ np.random.default_rng(seed).standard_normal((n, m)))  # f0_j = L z_j, src/gpirtMCMC.cpp:158-162
+        O.set_state(f=f0)
+        start = "the bench's initial state (theta0, beta0, default thresholds, f0 = L z)"
+    else:
+        O.set_state(theta=state["theta"], beta=state["beta"], thr=state["thresholds"], f=state["f"])
+        O.compute_mu()
+        assert O.update_cholesky() == 0
+        start = "the state the GPU chain reached after its warm-up and timed sweeps"
+    t_begin = time.perf_counter()
+    it = 0
+    for _ in range(warm):
+        info, _, _ = O.run_mt(it, 1, store=False)
+        assert info == 0
+        it += 1
+    t_warm = time.perf_counter() - t_begin
     O.times(reset=True)
-    t0 = time.perf_counter()
-    info, _, _ = O.run_mt(warmup, steps, store=False)
-    t1 = (time.perf_counter() - t0) / steps
-    assert info == 0
-    fixed, items = (t / steps for t in O.times())
-    t_full = fixed + items * m_full / m_sub
-    return dict(value=1.0 / t_full, t_step_sample=t1, threads=O.num_threads(), cores=cores,
-                sample=f"first {m_sub} of {m_full} items, all n={n} respondents, {steps} timed sweep(s) of the faithful port on {O.num_threads()} threads: "
-                       f"{t1:.2f} s/sweep = {fixed:.2f} s shared by all items (2x chol(K), k* solves, chol(K_post)) + {items:.2f} s per-item/per-respondent "
-                       f"work, which is linear in m; value = 1/({fixed:.2f} + {items:.2f}*{m_full}/{m_sub}) (extrapolated)")
+    times = []
+    while len(times) < max_timed:
+        t0 = time.perf_counter()
+        info, _, _ = O.run_mt(it, 1, store=False)
+        assert info == 0
+        it += 1
+        times.append(time.perf_counter() - t0)
+        if len(times) >= min_timed and (time.perf_counter() - t_begin) + float(np.mean(times)) > budget_s:
+            break
+    fixed, items = (t / len(times) for t in O.times())
+    mean = float(np.mean(times))
+    name = ("ref-faithful" if faithful else "ref-tidy") + ("+openblas" if blas_path else "")
+    return dict(variant=name, value=1.0 / mean, ms_per_step=1e3 * mean, steps=len(times), warmup=warm, threads=O.num_threads(), cores=os.cpu_count(),
+                blas=os.path.basename(blas_path) if blas_path else None, sweep_s=[round(t, 3) for t in times], warm_s=round(t_warm, 3),
+                shared_s=round(fixed, 3), items_s=round(items, 3),
+                sample=f"{len(times)} whole sweep(s) over ALL {m} items x {n} respondents ({name}, {O.num_threads()} threads) after {warm} warm-up sweep(s) from {start}: "
+                       f"{mean:.2f} s/sweep = {fixed:.2f} s shared by all items (chol(K), k* solves, chol(K_post)) + {items:.2f} s per-item / per-respondent work; measured, not extrapolated")
 
 
 def reference_arm(args):
+    """--impl reference: the reference's own algorithm on this box's host cores, on the `ours` arm's config. At N = 1 the full C3 workload is
+    swept (a faithful sweep takes tens of seconds: the line reports how many sweeps were really timed, never more than --steps). At N > 1 the
+    weak-scaled workload (5000 N items) does not fit the time limit on a CPU: the C3 block is timed and the line says extrapolated: true."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     m_full = M_PER_GPU * args.gpus
-    r = cpu_reference_sweeps(N_RESP, m_full, C_CAT, 20261104 + 3, args.steps, args.warmup, args.ref_items)
-    line = {"impl": "reference", "metric": "mcmc_sweeps_per_sec_c3_blocks", "value": r["value"] * args.gpus, "unit": "sweeps/s", "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / r["value"], "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C3 synthetic ordinal n={N_RESP} x m={m_full} ({M_PER_GPU} items per GPU), C={C_CAT}, 5% missing",
-                       "n": N_RESP, "m": m_full, "C": C_CAT},
-            "cpu_baseline": {"value": r["value"] * args.gpus, "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]},
-            "e2e": {"value": r["value"] * args.gpus, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    main = cpu_sweeps(N_RESP, M_PER_GPU, C_CAT, 20261104 + 3, faithful=1, warm=1, max_timed=max(1, args.steps), min_timed=min(3, max(1, args.steps)),
+                      budget_s=args.ref_budget, blas=True)
+    tidy = cpu_sweeps(N_RESP, M_PER_GPU, C_CAT, 20261104 + 3, faithful=0, warm=1, max_timed=min(3, max(1, args.steps)), min_timed=1, budget_s=40.0, blas=True)
+    extrap = args.gpus > 1
+    # weak-scaling metric: C3-sized item blocks swept per second. A CPU sweeping 5000 N items does N blocks per sweep in ~N times the time.
+    value = main["value"]
+    workload = (f"C3 synthetic ordinal n={N_RESP} x m={M_PER_GPU}, C={C_CAT}, 5% missing" if not extrap else
+                f"C3 block (n={N_RESP} x m={M_PER_GPU}, C={C_CAT}) timed in full; the {args.gpus}-GPU workload n={N_RESP} x m={m_full} is NOT swept on the CPU: "
+                f"blocks/s assumed constant in m (per-item work is linear in m), extrapolated")
+    line = {"impl": "reference", "metric": "mcmc_sweeps_per_sec_c3_blocks", "value": value, "unit": "sweeps/s", "n_gpus": args.gpus,
+            "steps": main["steps"], "warmup": main["warmup"], "steps_requested": args.steps, "warmup_requested": args.warmup,
+            "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "extrapolated": extrap,
+            "config": {"workload": workload, "n": N_RESP, "m": M_PER_GPU if extrap else m_full, "C": C_CAT},
+            "cpu_baseline": {"value": value, "unit": "sweeps/s", "cores": main["threads"], "kind": "port", "sample": main["sample"]},
+            "variants": {main["variant"]: {k: main[k] for k in ("value", "ms_per_step", "steps", "warmup", "threads", "blas", "sweep_s", "shared_s", "items_s")},
+                         tidy["variant"]: {k: tidy[k] for k in ("value", "ms_per_step", "steps", "warmup", "threads", "blas", "sweep_s", "shared_s", "items_s")}},
+            "variants_note": "value is ref-faithful (the sweep as the reference codes it); ref-tidy drops the reference's per-respondent table copies and its second "
+                             "Cholesky (same arithmetic) and is the denominator to use for a speed-up that is not inflated by a reference inefficiency",
+            "e2e": {"value": value, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
+
+
+def sharded_equals_single(rank, world, local):
+    """Outside the timed region, N > 1: two sweeps of a small ragged problem item-sharded over the N ranks and unsharded on this rank's GPU;
+    True iff theta, beta, thresholds and the total log-likelihood agree bit for bit on every rank (Philox streams are keyed by global unit)."""
+    import torch
+    import torch.distributed as dist
+
+    import gpirt_b200
+    from gpirt_b200.distributed import ShardedSampler
+
+    n, m, C = 320, 64 * world + 3, 5
+    P = synth(n, m, C, 99)
+    out = []
+    for sharded in (True, False):
+        S = (ShardedSampler(n, m, C, rank=rank, world=world, device=local, seed=7, chain=0) if sharded else
+             gpirt_b200.Sampler(n, m, C, device=local, seed=7, chain=0))
+        S.set_data(P["y"])
+        S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+        S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+        S.init_draw(draw_beta=False, draw_f=True)
+        S.sweep(2)
+        S.sync()
+        st = S.get_state(f=False)
+        out.append((st["theta"].copy(), st["beta"].copy(), st["thresholds"].copy(), S.total_ll()))
+        S.close()
+    same = all(np.array_equal(a, b) for a, b in zip(out[0][:3], out[1][:3])) and out[0][3] == out[1][3]
+    t = torch.tensor([1 if same else 0], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    return bool(t.item())
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -220,6 +292,13 @@ def ours(args):
         "trtri": ("tensor", n ** 3 / 3.0), "gemm_tmp": ("tensor", 1.0 * n * n * N), "gemm_W": ("tensor", 1.0 * n * n * N),
     }
     peaks, peak_src = measured_peaks()
+    try:  # fp64 roofline denominator measured in this run, on this GPU, outside the timed region (MEASURED_PEAKS.json has no fp64 figure)
+        from gpirt_b200.api import fp64_peak
+
+        FP64_DMMA_PEAK_TFLOPS, dfma_peak = fp64_peak(local)
+        fp64_src = f"gpirt_debug_fp64_peak in this run: DMMA.8x8x4 issue rate {FP64_DMMA_PEAK_TFLOPS:.2f} TFLOP/s, scalar DFMA {dfma_peak:.2f} TFLOP/s"
+    except Exception as exc:  # noqa: BLE001
+        FP64_DMMA_PEAK_TFLOPS, fp64_src = FP64_DMMA_PEAK_FALLBACK, f"fallback literal (microbenchmark failed: {exc})"
     kernels = []
     for k, t in sorted(per_sweep.items(), key=lambda kv: -kv[1]):
         bound, amount = algo.get(k, ("hbm", 0.0))
@@ -238,7 +317,7 @@ def ours(args):
                 "bound": "tensor", "achieved": round(ach, 2), "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": round(ach / FP64_DMMA_PEAK_TFLOPS, 4),
                 "traffic": 305.3e6,
                 "traffic_note": "dram read+write of the largest launch (L*Z: algorithmic 176 MB), ncu --set full, profiles/r01_ncu_gemm64.txt",
-                "peak_source": "fp64 DMMA.8x8x4 issue-rate microbenchmark on this pool (profiles/r01_microbench_fp64.txt); MEASURED_PEAKS.json has no fp64 figure",
+                "peak_source": fp64_src + "; MEASURED_PEAKS.json has no fp64 figure",
                 "groups": gemm_groups, "ms_per_sweep": round(gemm_ms, 4), "call_sites_per_sweep": gemm_launches,
                 "share_of_sweep": round(gemm_ms / sum(per_sweep.values()), 3),
                 "algorithmic_flops_per_sweep": gemm_flops,
@@ -265,6 +344,9 @@ def ours(args):
             "loglik_gbs": loglik_gbs}
     if rank == 0:
         line["clocks"] = clk
+    gpu_state = S.get_state() if world == 1 and not args.no_cpu_baseline else None  # where the CPU baseline below starts from
+    if world > 1:
+        line["sharded_equals_single"] = sharded_equals_single(rank, world, local)
 
     # ---- e2e: the reference-facing call with HOST buffers (gpirtMCMC -> gpirt_mcmc C-ABI), copies inside the timed region ----
     if world == 1:
@@ -296,9 +378,12 @@ def ours(args):
         assert all(np.all(np.isfinite(r["ll"])) for r in res)
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
         if not args.no_cpu_baseline:
-            # ~10-30 s of CPU work: 1000 of the 5000 items (the extrapolation in m is then 5x, not 125x), 1 warm + 8 timed sweeps
-            r = cpu_reference_sweeps(n, m, C, 20261104 + 3, 8, 1, max(args.ref_items, 1000))
-            line["cpu_baseline"] = {"value": r["value"], "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"]}
+            # bounded sample: ONE whole faithful sweep of the full workload (tens of seconds) and two tidy ones, from the GPU chain's own state
+            r = cpu_sweeps(n, m, C, 20261104 + 3, faithful=1, warm=0, max_timed=1, min_timed=1, budget_s=0.0, state=gpu_state, blas=True)
+            t = cpu_sweeps(n, m, C, 20261104 + 3, faithful=0, warm=0, max_timed=2, min_timed=1, budget_s=30.0, state=gpu_state, blas=True)
+            line["cpu_baseline"] = {"value": r["value"], "unit": "sweeps/s", "cores": r["threads"], "kind": "port", "sample": r["sample"],
+                                    "variant": r["variant"], "blas": r["blas"],
+                                    "tidy": {"value": t["value"], "variant": t["variant"], "sample": t["sample"]}}
     else:
         # the same call sharded: every rank uploads its columns / rows of the pinned fp64 y, runs the chain with the exchanges, and reads
         # the kept draws back; wall clock between barriers, max over ranks
@@ -345,7 +430,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ref-items", type=int, default=200, help="items in the CPU baseline's bounded sample")
+    ap.add_argument("--ref-budget", type=float, default=210.0, help="--impl reference: wall-clock budget (s) of the faithful variant's warm-up + timed sweeps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

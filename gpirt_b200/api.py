@@ -263,3 +263,12 @@ def debug_cell32(g, tau_lo, tau_hi, device=0):
     t32, e32, t64 = np.empty_like(g), np.empty_like(g), np.empty_like(g)
     check(_lib.lib().gpirt_debug_cell32(device, _p(g), _p(lo), _p(hi), int(g.size), _p(t32), _p(e32), _p(t64)))
     return t32, e32, t64
+
+
+def fp64_peak(device=0):
+    """(DMMA.8x8x4, DFMA) issue-rate peaks of the device in TFLOP/s, measured now (bench.py's fp64 roofline denominator)."""
+    import ctypes as C
+
+    a, b = C.c_double(), C.c_double()
+    check(_lib.lib().gpirt_debug_fp64_peak(int(device), C.byref(a), C.byref(b)))
+    return a.value, b.value

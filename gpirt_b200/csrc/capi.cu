@@ -444,9 +444,10 @@ int gpirt_debug_theta_threads(int threads) {
     return GPIRT_OK;
 }
 
-int gpirt_set_screen(gpirt_sampler* h, int on) {
+int gpirt_set_screen(gpirt_sampler* h, int on) {  // 0: every evaluation in fp64; 1: fp32 screen + early rejection (default); 2: fp32 screen, whole evaluations
     CHECK_H(h);
     h->screen = on != 0;
+    h->early_exit = on == 1;
     return GPIRT_OK;
 }
 int gpirt_get_exact_evals(gpirt_sampler* h, int block, int32_t* out) {
@@ -870,7 +871,7 @@ static ItemView item_view(gpirt_sampler* h) {
     v.n = h->n; v.ldn = h->ldn; v.m_local = h->m_local; v.item0 = h->item0; v.m_total = h->m_total; v.C = h->C; v.p_beta = h->cfg.p_beta;
     v.y_im = h->y_im; v.ldy = h->ldy; v.theta = h->theta; v.beta = h->beta; v.thr = h->thr; v.f = h->f; v.nu = h->nu; v.sds = h->sds;
     v.z = nullptr; v.z_stride = 0; v.us.u = nullptr; v.us.stride = 0; v.key = h->key();
-    v.item_ll = h->item_ll; v.flags = h->flags; v.screen = h->screen; v.exact_evals = nullptr;
+    v.item_ll = h->item_ll; v.flags = h->flags; v.screen = h->screen; v.early_exit = h->screen && h->early_exit; v.exact_evals = nullptr;
     v.mu_rows = h->mu_rows;
     return v;
 }
@@ -1718,5 +1719,61 @@ extern "C" int gpirt_debug_cell32(int device, const double* g, const double* tau
     CU(cudaMemcpy(t32, d + 3 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(e32, d + 4 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(t64, d + 5 * (size_t)n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    return GPIRT_OK;
+}
+
+// Measurement hook: fp64 issue-rate peaks of this device (include/gpirt_b200.h). Eight independent accumulator chains per thread, 2048 threads per SM.
+__global__ void k_peak_dmma(double* out, int iters, double a, double b) {
+    double c[8][2];
+    for (int k = 0; k < 8; ++k) { c[k][0] = threadIdx.x; c[k][1] = k; }
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) dmma884(c[k][0], c[k][1], a, b);
+    }
+    double s = 0;
+    for (int k = 0; k < 8; ++k) s += c[k][0] + c[k][1];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+__global__ void k_peak_dfma(double* out, int iters, double a, double b) {
+    double c[8];
+    for (int k = 0; k < 8; ++k) c[k] = threadIdx.x + k;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) c[k] = fma(c[k], a, b);
+    }
+    double s = 0;
+    for (int k = 0; k < 8; ++k) s += c[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+extern "C" int gpirt_debug_fp64_peak(int device, double* dmma_tflops, double* dfma_tflops) {
+    if (!dmma_tflops || !dfma_tflops) return fail(GPIRT_ERR_INVALID, "fp64_peak: NULL output");
+    TRY(select_device(device));
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    const int threads = 512, blocks = sms * 4, iters = 20000;
+    DevTemp t_out;
+    CU(t_out.alloc((size_t)blocks * threads * 8));
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    float ms = 0.f;
+    double best[2] = {0.0, 0.0};
+    for (int rep = 0; rep < 3; ++rep) {  // first repetition warms the clocks up; best of three
+        for (int which = 0; which < 2; ++which) {
+            cudaEventRecord(e0, 0);
+            if (which == 0) k_peak_dmma<<<blocks, threads>>>(t_out.as<double>(), iters, 1.0000001, 1e-9);
+            else k_peak_dfma<<<blocks, threads>>>(t_out.as<double>(), iters, 1.0000001, 1e-9);
+            cudaEventRecord(e1, 0);
+            cudaError_t e = cudaEventSynchronize(e1);
+            if (e != cudaSuccess) { cudaEventDestroy(e0); cudaEventDestroy(e1); return fail(GPIRT_ERR_CUDA, "fp64_peak: %s", cudaGetErrorString(e)); }
+            cudaEventElapsedTime(&ms, e0, e1);
+            const double flop = which == 0 ? 2.0 * 256 * 8 * iters * (double)blocks * (threads / 32) : 2.0 * 8 * iters * (double)blocks * threads;
+            best[which] = std::max(best[which], flop / ms / 1e9);
+        }
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *dmma_tflops = best[0];
+    *dfma_tflops = best[1];
     return GPIRT_OK;
 }

@@ -19,6 +19,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdlib>
 #include <map>
 #include <string>
 #include <vector>
@@ -66,6 +67,7 @@ struct gpirt_sampler {
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int32_t* exact[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per unit: evaluations that ran in fp64 (screening diagnostics)
     int screen = 1;  // fp32 screening of ESS proposals with a rigorous error bound; decisions identical to fp64 (gpirt_set_screen)
+    int early_exit = getenv("GPIRT_ESS_EARLY") ? atoi(getenv("GPIRT_ESS_EARLY")) != 0 : 1;  // screened proposals stop at the first partial sum that already decides a rejection
     double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     gpirt::DevFlags* flags = nullptr;
     int* chol_ws = nullptr;  // per-panel arrival counters of the blocked Cholesky

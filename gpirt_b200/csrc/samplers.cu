@@ -97,6 +97,14 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
     const double* __restrict__ theta = v.theta;
     const double* __restrict__ mur = (v.mu_rows && MODE != IB_BETA) ? v.mu_rows + (size_t)j * v.ldn : nullptr;
     const int n = v.n;
+    // Early rejection (screened mode): every cell term is log(p + 1e-6) with p <= 1, i.e. at most log(1 + 1e-6) < 1.000001e-6, so a partial sum
+    // over the first cells plus that cap for the cells still to come is an upper bound of the proposal's log-likelihood. The first proposals of
+    // a shrink loop land far out on the ellipse (prior sds of 3 move g by several units: terms near log(1e-6)), and are certainly below log_y
+    // after an eighth of the cells; the evaluation then stops there. Three phases: cells [0, c1), [c1, c2), [c2, CPT) per thread. The decision
+    // is the one the full fp64 evaluation takes (test: screened == unscreened bit for bit), only rejections can come early.
+    const int CPT = (n + T - 1) / T;                       // cells per thread
+    const int c1 = CPT >= 4 ? max(1, CPT / 8) : CPT;       // fewer than 4 cells per thread: one phase
+    const int c2 = CPT >= 4 ? max(c1 + 1, (3 * CPT) / 8) : CPT;
     const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
     double pb0 = b0, pb1 = b1, pb2 = b2;
 
@@ -120,9 +128,9 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
         return block_sum<WARPS>(acc0 + acc1, s_part);
     };
 
-    // fp32 screening pass (probit.cuh): the proposal's log-likelihood in fp32 (summed in fp64) and the bound on its distance to
-    // the fp64 value
-    auto loglik32 = [&](double ce, double se, double& L, double& E) {
+    // fp32 screening pass (probit.cuh) over the thread's cells c_begin <= c < c_end (cell c of thread tid is respondent tid + c * T): the
+    // log-likelihood terms in fp32 (summed in fp64) and the bound on their distance to the fp64 terms, reduced over the CTA
+    auto partial32 = [&](int c_begin, int c_end, double ce, double se, double& L, double& E) {
         double l0 = 0.0, l1 = 0.0;
         float e0 = 0.f, e1 = 0.f;
         auto one = [&](int i, double& l, float& e) {
@@ -136,13 +144,15 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
             l += (double)t;
             e += et;
         };
-        int i = tid;
-        for (; i + T < n; i += 2 * T) { one(i, l0, e0); one(i + T, l1, e1); }
-        if (i < n) one(i, l0, e0);
+        const int i_end = min(n, c_end * T);
+        int i = tid + c_begin * T;
+        for (; i + T < i_end; i += 2 * T) { one(i, l0, e0); one(i + T, l1, e1); }
+        if (i < i_end) one(i, l0, e0);
         L = l0 + l1;
         E = (double)(e0 + e1);
         block_sum2<WARPS>(L, E, s_part2);
     };
+    auto loglik32 = [&](double ce, double se, double& L, double& E) { partial32(0, CPT, ce, se, L, E); };
 
     // prior draw for the low-dimensional blocks
     double nu_small[MAX_C];  // beta: 3 used; thresholds: C-1 used
@@ -219,14 +229,33 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
         ++evals;
         bool decided = false, accept = false;
         if (v.screen) {
-            double L32, E32;
-            loglik32(ce, se, L32, E32);
-            const double d = L32 - (S0 + log_u);
-            // fp32 rounding of the E accumulations (relative 1e-5 at most) and the fp64 passes' own summation noise
-            const double Eb = (E32 + E0) * 1.00002 + 1e-10 * (fabs(L32) + fabs(S0) + 1.0);
-            if (d > Eb) { decided = true; accept = true; }
-            else if (d < -Eb) { decided = true; }
-            if (decided) margin = fmin(margin, fabs(d) - Eb);  // a lower bound of the true margin
+            double L32 = 0.0, E32 = 0.0;
+            int c_done = 0;
+            if (v.early_exit && c1 < CPT) {
+                // noise of the fp64 passes this stands in for: their sums are at most 13.9 n in magnitude (every term >= log(1e-6 - eps))
+                const double noise = 1e-10 * (13.9 * (double)n + fabs(S0) + 1.0);
+                for (int ph = 0; ph < 2 && !decided; ++ph) {
+                    const int c_to = ph == 0 ? c1 : c2;
+                    double Lp, Ep;
+                    partial32(c_done, c_to, ce, se, Lp, Ep);
+                    L32 += Lp; E32 += Ep; c_done = c_to;
+                    const double cap = 1.000001e-6 * (double)max(0, n - c_to * T);  // the cells still to come add at most this
+                    const double d = (L32 + cap) - (S0 + log_u);
+                    const double Eb = (E32 + E0) * 1.00002 + noise;
+                    if (d < -Eb) { decided = true; margin = fmin(margin, -d - Eb); }
+                }
+            }
+            if (!decided) {
+                double Lp, Ep;
+                partial32(c_done, CPT, ce, se, Lp, Ep);
+                L32 += Lp; E32 += Ep;
+                const double d = L32 - (S0 + log_u);
+                // fp32 rounding of the E accumulations (relative 1e-5 at most) and the fp64 passes' own summation noise
+                const double Eb = (E32 + E0) * 1.00002 + 1e-10 * (fabs(L32) + fabs(S0) + 1.0);
+                if (d > Eb) { decided = true; accept = true; }
+                else if (d < -Eb) { decided = true; }
+                if (decided) margin = fmin(margin, fabs(d) - Eb);  // a lower bound of the true margin
+            }
         }
         if (!decided) {
             if (!have_exact0) {  // the current state in fp64: its own parameters for the pass, then the proposal's again

@@ -55,6 +55,7 @@ struct ItemView {
     int32_t* evals;           // per global item
     int32_t* exact_evals;     // per global item: evaluations that needed the fp64 pass (screening diagnostics), or nullptr
     int screen;               // 1: fp32 screening of proposals with a rigorous error bound (probit.cuh)
+    int early_exit;           // 1 (with screen): a proposal is rejected as soon as a partial sum plus the cap of the remaining terms is below log_y
     double* margin;
     double* item_ll;          // per global item (k_item_ll)
     DevFlags* flags;

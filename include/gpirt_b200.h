@@ -215,6 +215,10 @@ int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, doub
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
 /* fp32 screening term, its error bound and the fp64 cell term log(Phi(tau_hi-g) - Phi(tau_lo-g) + 1e-6), element-wise */
 int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const double* tau_hi, int n, double* t32, double* e32, double* t64);
+/* Measurement hook (bench.py's roofline denominator; MEASURED_PEAKS.json carries no fp64 figure): issue-rate microbenchmarks of the two fp64
+ * pipes the sweep's contractions run on, ~20 ms each on an otherwise idle device: mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) and scalar DFMA,
+ * in TFLOP/s. No reference counterpart. */
+int gpirt_debug_fp64_peak(int device, double* dmma_tflops, double* dfma_tflops);
 
 /* ---- horizon > 1 (dynamic GPIRT), constant_IRF == 0 ----
  * A panel is `horizon` single-session samplers (given theta the sessions are independent: the reference loops h outside every per-item

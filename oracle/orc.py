@@ -57,6 +57,32 @@ def lib():
     return _lib
 
 
+def find_openblas():
+    """The OpenBLAS inside the scipy wheel of this image (LP64, symbols prefixed scipy_), or None."""
+    import glob
+    import importlib.util
+
+    spec = importlib.util.find_spec("scipy")
+    if spec is None or not spec.submodule_search_locations:
+        return None
+    base = os.path.dirname(list(spec.submodule_search_locations)[0])
+    hits = sorted(glob.glob(os.path.join(base, "scipy.libs", "libscipy_openblas-*.so")))
+    return hits[0] if hits else None
+
+
+def use_blas(on=True, threads=None):
+    """TIMED BASELINE ONLY (oracle/orc_blas.h): route chol / triangular solves / gemv of the oracle through an optimised BLAS, as the
+    reference's Armadillo calls would be in an R linked against one. Returns the library path, or None when it is unavailable."""
+    if not on:
+        lib().orc_blas_off()
+        return None
+    path = find_openblas()
+    if path is None:
+        return None
+    rc = lib().orc_blas_load(path.encode(), C.c_int(int(threads or os.cpu_count() or 1)))
+    return path if rc == 0 else None
+
+
 def set_threads(k):
     """OpenMP threads of samplers created after this call; 1 reproduces the reference's single-thread RNG order."""
     lib().orc_set_threads(C.c_int(int(k)))

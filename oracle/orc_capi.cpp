@@ -37,6 +37,11 @@ static Src to_src(Sampler* S, const orc_src* c, int block) {
     return s;
 }
 
+// ---- optional BLAS backend of the TIMED baseline (orc_blas.h); the parity tests leave it off ----
+int orc_blas_load(const char* path, int threads_all) { return blas_load(path, threads_all); }
+void orc_blas_off(void) { blas_off(); }
+int orc_blas_on(void) { return blas().on ? 1 : 0; }
+
 // ---- leaves -------------------------------------------------------------------------------
 double orc_pnorm(double x) { return pnorm(x); }
 void orc_pnorm_vec(const double* x, uint64_t n, double* out) { for (uint64_t i = 0; i < n; ++i) out[i] = pnorm(x[i]); }
@@ -127,7 +132,10 @@ void orc_mt_seed_all(void* h, uint32_t base) {  // WorkspacePool::seed_all, src/
     for (size_t t = 0; t < S->mts.size(); ++t) S->mts[t].seed(base + uint32_t(t) * 1000u);
 }
 // worker threads of samplers created AFTER this call (single-thread runs reproduce the reference's RNG order)
-void orc_set_threads(int k) { omp_set_num_threads(k); }
+void orc_set_threads(int k) {
+    omp_set_num_threads(k);
+    if (blas().on) { blas().threads_all = k; blas().set_threads(k); }
+}
 void orc_record(void* h, int on) { static_cast<Sampler*>(h)->record = on != 0; }
 // draws of the last call of `block`: z_out is zcap x units, u_out is ucap x units (column-major, zero padded); counts per unit
 int orc_get_record(void* h, int block, double* z_out, uint64_t zcap, double* u_out, uint64_t ucap, int32_t* nz, int32_t* nu) {

@@ -18,7 +18,10 @@
 #include <cstddef>
 #include <cstdint>
 #include <limits>
+#include <type_traits>
 #include <vector>
+
+#include "orc_blas.h"
 
 namespace orc {
 
@@ -146,6 +149,13 @@ inline int chol_lower(T* A, size_t n) {
 // tiles): what the timed CPU baseline uses so that the O(n^3) part is cache-blocked and threaded, as
 // the LAPACK dpotrf behind arma::chol would be. Same arithmetic up to summation order.
 inline int chol_lower_blocked(double* A, size_t n) {
+    if (blas().on) {  // timed baseline only (orc_blas.h): LAPACK dpotrf, as arma::chol(S, "lower") calls it; upper triangle zeroed like Armadillo does
+        int nn = int(n), info = 0;
+        blas().dpotrf("L", &nn, A, &nn, &info);
+        for (size_t j = 0; j < n; ++j)
+            for (size_t i = 0; i < j; ++i) A[i + j * n] = 0.0;
+        return info;
+    }
     const size_t NB = 64;
     if (n <= 2 * NB) return chol_lower(A, n);
     for (size_t k0 = 0; k0 < n; k0 += NB) {
@@ -206,6 +216,9 @@ inline int chol_lower_blocked(double* A, size_t n) {
 // forward substitution L x = b (in place), back substitution L^T x = b (in place)
 template <typename T>
 inline void trsv_lower(const T* L, size_t n, T* x) {
+    if constexpr (std::is_same<T, double>::value) {
+        if (blas().on) { blas().dtrsv(102, 122, 111, 131, int(n), L, int(n), x, 1); return; }
+    }
     // column-oriented (axpy form): streams L column by column
     for (size_t j = 0; j < n; ++j) {
         T xj = x[j] / L[j + j * n];
@@ -216,6 +229,9 @@ inline void trsv_lower(const T* L, size_t n, T* x) {
 }
 template <typename T>
 inline void trsv_lower_t(const T* L, size_t n, T* x) {
+    if constexpr (std::is_same<T, double>::value) {
+        if (blas().on) { blas().dtrsv(102, 122, 112, 131, int(n), L, int(n), x, 1); return; }
+    }
     for (size_t jj = n; jj-- > 0;) {
         const T* cj = L + jj * n;
         T s = x[jj];
@@ -231,6 +247,7 @@ inline void double_solve(const double* L, size_t n, double* x) {
 
 // dense y = A x, A is r x c column-major (src/mvnormal.h:23 uses a dense product, ignoring triangularity)
 inline void gemv(const double* A, size_t r, size_t c, const double* x, double* y) {
+    if (blas().on) { blas().dgemv(102, 111, int(r), int(c), 1.0, A, int(r), x, 1, 0.0, y, 1); return; }
     for (size_t i = 0; i < r; ++i) y[i] = 0.0;
     for (size_t j = 0; j < c; ++j) {
         const double xj = x[j];

@@ -117,6 +117,7 @@ void Sampler::draw_f(const Src& s, const double* nu_supplied) {
     t_fixed += now() - t0; t0 = now();
     diag[B_F].reset(m);
     bool over = false;
+    BlasSerialScope blas_serial;
 #pragma omp parallel for schedule(dynamic) reduction(|| : over)
     for (size_t j = 0; j < m; ++j) {
         std::vector<double> nu(n), z(n), fp(n), thr_j(C + 1);
@@ -156,18 +157,24 @@ int Sampler::draw_fstar(const Src& s) {
     std::vector<double> kstar(n * N), tmp;
     K(theta.data(), n, tstar.data(), N, sds.data(), kstar.data());  // src/draw-fstar.cpp:26
     tmp = kstar;
-#pragma omp parallel for schedule(static)
-    for (size_t k = 0; k < N; ++k) trsv_lower(L.data(), n, &tmp[k * n]);  // :30
     Lpost.assign(N * N, 0.0);
-    K(tstar.data(), N, tstar.data(), N, sds.data(), Lpost.data());  // :33
+    if (blas().on) {  // timed baseline only (orc_blas.h): dtrtrs with N right-hand sides and the product tmp^T tmp as a BLAS-linked Armadillo runs them
+        blas().dtrsm(102, 141, 122, 111, 131, int(n), int(N), 1.0, L.data(), int(n), tmp.data(), int(n));  // :30
+        K(tstar.data(), N, tstar.data(), N, sds.data(), Lpost.data());                                     // :33
+        blas().dsyrk(102, 122, 112, int(N), int(n), -1.0, tmp.data(), int(n), 1.0, Lpost.data(), int(N));   // :34 (lower triangle; chol reads only that)
+    } else {
 #pragma omp parallel for schedule(static)
-    for (size_t b = 0; b < N; ++b) {
-        for (size_t a = 0; a < N; ++a) {
-            double acc = 0.0;
-            const double* ta = &tmp[a * n];
-            const double* tb = &tmp[b * n];
-            for (size_t i = 0; i < n; ++i) acc += ta[i] * tb[i];
-            Lpost[a + b * N] -= acc;  // :34
+        for (size_t k = 0; k < N; ++k) trsv_lower(L.data(), n, &tmp[k * n]);  // :30
+        K(tstar.data(), N, tstar.data(), N, sds.data(), Lpost.data());  // :33
+#pragma omp parallel for schedule(static)
+        for (size_t b = 0; b < N; ++b) {
+            for (size_t a = 0; a < N; ++a) {
+                double acc = 0.0;
+                const double* ta = &tmp[a * n];
+                const double* tb = &tmp[b * n];
+                for (size_t i = 0; i < n; ++i) acc += ta[i] * tb[i];
+                Lpost[a + b * N] -= acc;  // :34
+            }
         }
     }
     for (size_t k = 0; k < N; ++k) Lpost[k + k * N] += 1e-6;  // :35
@@ -176,19 +183,24 @@ int Sampler::draw_fstar(const Src& s) {
     if (info) return info;
     diag[B_FSTAR].reset(m);
     bool over = false;
+    BlasSerialScope blas_serial;
 #pragma omp parallel for schedule(dynamic) reduction(|| : over)
     for (size_t j = 0; j < m; ++j) {
-        std::vector<double> alpha(&f[j * n], &f[j * n] + n), z(N), dz(N);
+        std::vector<double> alpha(&f[j * n], &f[j * n] + n), z(N), dz(N), mean(N);
         double_solve(L.data(), n, alpha.data());  // :51 (uses f, not f - mu)
         bool o = with_rng(s, j, N, [&](UnitRng& rng) {
             for (size_t k = 0; k < N; ++k) z[k] = rng.norm();
         });
         over = over || o;
         gemv(Lpost.data(), N, N, z.data(), dz.data());
+        if (blas().on) blas().dgemv(102, 112, int(n), int(N), 1.0, kstar.data(), int(n), alpha.data(), 1, 0.0, mean.data(), 1);  // kstar^T alpha, :52
         for (size_t k = 0; k < N; ++k) {
             double acc = 0.0;
-            const double* ck = &kstar[k * n];
-            for (size_t i = 0; i < n; ++i) acc += ck[i] * alpha[i];
+            if (blas().on) acc = mean[k];
+            else {
+                const double* ck = &kstar[k * n];
+                for (size_t i = 0; i < n; ++i) acc += ck[i] * alpha[i];
+            }
             fstar[k + j * N] = (acc + mu_star[k + j * N]) + dz[k];  // :52,55
         }
     }
