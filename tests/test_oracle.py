@@ -170,3 +170,40 @@ def test_full_sweep_supplied_streams_is_reproducible_and_on_grid():
     assert all(orc.grid_value(orc.grid_index(t)) == t for t in th)
     thr = states[0]["thr"]
     assert np.all(np.diff(thr[:, 1:C], axis=1) > 0)  # thresholds stay ordered by construction
+
+
+def test_blas_backend_of_the_timed_baseline_agrees_with_the_oracle_loops():
+    """bench.py times the oracle with chol / trsm / syrk / gemv / trsv routed through the scipy wheel's OpenBLAS (oracle/orc_blas.h), as a
+    BLAS-linked R would run Armadillo's calls. Same algorithm, different summation order: L agrees norm-wise to kappa * eps, a draw_f with the same
+    mt19937 streams makes the same number of proposals on a small well-separated problem, f* agrees to the kappa-limited tolerance."""
+    from oracle import orc
+    from tests.problems import make_problem
+
+    if orc.find_openblas() is None:
+        pytest.skip("no scipy OpenBLAS on this machine")
+    n, m, C = 130, 9, 4
+    P = make_problem(n, m, C, seed=5)
+    sds = np.full((3, m), 0.4, order="F")  # well conditioned: decisions do not hinge on the last bits of L
+    out = []
+    try:
+        for blas in (False, True):
+            assert (orc.use_blas(blas, 2) is not None) == blas
+            O = orc.Sampler(P["y"], C, sds, P["theta_prior_sds"])
+            rng = np.random.default_rng(3)
+            O.set_state(theta=np.sort(rng.uniform(-2.5, 2.5, n)), beta=P["beta0"], thr=P["thr0"], f=np.asfortranarray(rng.standard_normal((n, m))))
+            O.compute_mu()
+            assert O.update_cholesky() == 0
+            L = O.L().copy()
+            z = np.asfortranarray(rng.standard_normal((n, m)))
+            u = np.asfortranarray(rng.random((64, m)))
+            O.draw_f(orc.supplied(z=z, u=u))
+            zs = np.asfortranarray(rng.standard_normal((orc.NGRID, m)))
+            assert O.draw_fstar(orc.supplied(z=zs)) == 0
+            out.append((L, O.diag("f")[0].copy(), O.state()["f"].copy(), O.state()["fstar"].copy()))
+    finally:
+        orc.use_blas(False)
+    (L0, e0, f0, s0), (L1, e1, f1, s1) = out
+    assert np.linalg.norm(L0 - L1) / np.linalg.norm(L0) < 1e-9
+    assert np.array_equal(e0, e1)
+    assert np.max(np.abs(f0 - f1)) < 1e-8
+    assert np.max(np.abs(s0 - s1)) / np.max(np.abs(s0)) < 1e-6
