@@ -373,6 +373,11 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     want(&h->flags, 1);
     want(&h->flags_x, gpirt::MAX_PEERS + 1);
     want(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID)));
+    const std::vector<uint32_t> tasks_n = h->n < 4096 ? chol_plan_tasks(h->n) : std::vector<uint32_t>(), tasks_N = chol_plan_tasks(NGRID);
+    want(&h->chol_tasks_n, tasks_n.size());
+    want(&h->chol_tasks_N, tasks_N.size());
+    want(&h->chol_state_n, chol_plan_state_ints(h->n < 4096 ? h->n : 64));
+    want(&h->chol_state_N, chol_plan_state_ints(NGRID));
     want(&h->Linv, (size_t)h->ldn * h->n);  // block-inverse solver of draw_fstar (the default)
     want(&h->W2, (size_t)h->ldn * NGRID);
     want(&h->tri_scratch, trtri_scratch_elems(h->n));
@@ -387,6 +392,16 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     {
         size_t off = 0;
         for (const Piece& pc : pieces) { *pc.p = h->arena + off; off += pc.bytes; }
+    }
+    {
+        static const int chol_ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 128;
+        if (!tasks_n.empty()) CU(cudaMemcpyAsync(h->chol_tasks_n, tasks_n.data(), tasks_n.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        if (!tasks_N.empty()) CU(cudaMemcpyAsync(h->chol_tasks_N, tasks_N.data(), tasks_N.size() * 4, cudaMemcpyHostToDevice, h->stream));
+        CU(cudaStreamSynchronize(h->stream));  // the host vectors go out of scope
+        if (h->n < 4096) {
+            h->plan_n.tasks = h->chol_tasks_n; h->plan_n.n_tasks = (int)tasks_n.size(); h->plan_n.state = h->chol_state_n; h->plan_n.max_ctas = chol_ctas;
+        }
+        h->plan_N.tasks = h->chol_tasks_N; h->plan_N.n_tasks = (int)tasks_N.size(); h->plan_N.state = h->chol_state_N; h->plan_N.max_ctas = chol_ctas;
     }
     k_fill_grid<<<(NGRID + 255) / 256, 256, 0, h->stream>>>(h->tstar);
     ++g_kernel_launches;
@@ -444,10 +459,10 @@ int gpirt_debug_theta_threads(int threads) {
     return GPIRT_OK;
 }
 
-int gpirt_set_screen(gpirt_sampler* h, int on) {  // 0: every evaluation in fp64; 1: fp32 screen + early rejection (default); 2: fp32 screen, whole evaluations
+int gpirt_set_screen(gpirt_sampler* h, int on) {  // 0: every evaluation in fp64; 1: fp32 screen (default); 2: fp32 screen + early rejection on partial sums
     CHECK_H(h);
     h->screen = on != 0;
-    h->early_exit = on == 1;
+    if (on == 2) h->early_exit = 1;
     return GPIRT_OK;
 }
 int gpirt_get_exact_evals(gpirt_sampler* h, int block, int32_t* out) {
@@ -485,6 +500,7 @@ static int check_flags(gpirt_sampler* h) {
         CU(cudaMemsetAsync(h->flags, 0, sizeof(fl), h->stream));
         if (fl.peer_timeout) return fail(GPIRT_ERR_CUDA, "f* exchange: the chunk of rank %d did not arrive within 4 s", fl.peer_timeout - 1);
         if (fl.bad_code) return fail(GPIRT_ERR_CATEGORIES, "response code outside 1..%d", h->C);
+        if (fl.chol_info < 0 || fl.chol_post_info < 0) return fail(GPIRT_ERR_CUDA, "chol(): the persistent factorisation kernel gave up waiting for a tile (device stalled?)");
         if (fl.chol_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K(theta,theta) + 1e-6 I not positive definite at leading minor %d", fl.chol_info);
         if (fl.chol_post_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K_post not positive definite at leading minor %d", fl.chol_post_info);
         if (fl.overrun) return fail(GPIRT_ERR_STREAM_OVERRUN, "a supplied uniform stream ran dry before its ESS loop accepted");
@@ -903,7 +919,7 @@ static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/chole
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
     const bool marks = st == h->side && h->L_rows.count > 0;
     SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws, marks ? &h->L_rows : nullptr,
-                                                      h->chol_aux.helper ? &h->chol_aux : nullptr)));
+                                                      h->chol_aux.helper ? &h->chol_aux : nullptr, h->plan_n.state ? &h->plan_n : nullptr)));
     h->pending_rows = marks;
     h->chol_valid = true;
     h->shared_valid = false;
@@ -995,7 +1011,8 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     ++g_kernel_launches;
     CU(cudaGetLastError());
     const bool post_marks = st == h->side && h->Lpost_rows.count > 0;
-    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws, post_marks ? &h->Lpost_rows : nullptr)));
+    SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws, post_marks ? &h->Lpost_rows : nullptr,
+                                                          nullptr, &h->plan_N)));
     h->pending_post_rows = post_marks;
     if (h->solver != 1) {  // substitution overwrites tmp in place, so it comes after K_post
         SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
@@ -1328,9 +1345,19 @@ int gpirt_chol(int device, const double* A, int64_t n, double* L) {
     int* info = tI.as<int>();
     CU(cudaMemset(dA, 0, (size_t)ld * n * 8)); CU(cudaMemset(info, 0, 4));
     CU(cudaMemcpy2D(dA, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
-    CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1));
+    DevTemp tT, tS;
+    CholPlan plan;
+    if (n < 4096) {
+        const std::vector<uint32_t> tasks = chol_plan_tasks((int)n);
+        CU(tT.alloc(std::max<size_t>(tasks.size(), 1) * 4));
+        CU(tS.alloc(chol_plan_state_ints((int)n) * 4));
+        if (!tasks.empty()) CU(cudaMemcpy(tT.p, tasks.data(), tasks.size() * 4, cudaMemcpyHostToDevice));
+        plan.tasks = tT.as<uint32_t>(); plan.n_tasks = (int)tasks.size(); plan.state = tS.as<int>(); plan.max_ctas = 128;
+    }
+    CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1, nullptr, nullptr, plan.state ? &plan : nullptr));
     CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));
     CU(cudaMemcpy(&hinfo, info, 4, cudaMemcpyDeviceToHost));
+    if (hinfo < 0) return fail(GPIRT_ERR_CUDA, "chol(): the persistent factorisation kernel gave up waiting for a tile");
     if (hinfo) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed at leading minor %d", hinfo);
     return GPIRT_OK;
 }

@@ -498,7 +498,15 @@ __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
 }
 
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks,
-                               const CholAux* aux) {
+                               const CholAux* aux, const CholPlan* plan) {
+    static const int persistent_env = getenv("GPIRT_CHOL_PERSISTENT") ? atoi(getenv("GPIRT_CHOL_PERSISTENT")) : 1;
+    if (plan && plan->state && persistent_env && n < 4096) {
+        cudaError_t e = chol_lower_persistent(st, A, ld, n, info_dev, plan->state, plan->tasks, plan->n_tasks, plan->max_ctas);
+        if (e != cudaSuccess) return e;
+        for (int c = 0; marks && c < marks->count; ++c)
+            if ((e = cudaEventRecord(marks->ev[c], st)) != cudaSuccess) return e;
+        return cudaSuccess;
+    }
     int next_mark = 0;
     static const int lookahead_env = getenv("GPIRT_CHOL_LOOKAHEAD") ? atoi(getenv("GPIRT_CHOL_LOOKAHEAD")) : 1;
     bool rest_pending = false;  // a part of a trailing update is in flight on the helper stream

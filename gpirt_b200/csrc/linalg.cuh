@@ -2,6 +2,9 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cstdint>
+#include <vector>
+
 #include "gemm.cuh"
 
 namespace gpirt {
@@ -33,8 +36,22 @@ struct CholAux {
     cudaStream_t helper = nullptr;
     cudaEvent_t ev_panel = nullptr, ev_rest = nullptr;
 };
+// Persistent single-kernel factorisation (chol_persistent.cu): the task list of an n x n matrix, uploaded once per handle, and its state words.
+struct CholPlan {
+    const uint32_t* tasks = nullptr;  // device: chol_plan_tasks(n)
+    int n_tasks = 0;
+    int* state = nullptr;             // device: chol_plan_state_ints(n) ints
+    int max_ctas = 0;
+};
+int chol_plan_tiles(int n);
+size_t chol_plan_state_ints(int n);
+std::vector<uint32_t> chol_plan_tasks(int n);
+// info_dev: 0, the failing leading minor (1-based), or -1 when the kernel gave up waiting (never on a healthy device)
+cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* state_dev, const uint32_t* tasks_dev, int n_tasks,
+                                  int max_ctas);
+// plan != nullptr and n below the two-level threshold: the persistent kernel; milestones are then all recorded at the end.
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr,
-                               const CholAux* aux = nullptr);
+                               const CholAux* aux = nullptr, const CholPlan* plan = nullptr);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);

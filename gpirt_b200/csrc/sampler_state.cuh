@@ -67,10 +67,17 @@ struct gpirt_sampler {
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int32_t* exact[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per unit: evaluations that ran in fp64 (screening diagnostics)
     int screen = 1;  // fp32 screening of ESS proposals with a rigorous error bound; decisions identical to fp64 (gpirt_set_screen)
-    int early_exit = getenv("GPIRT_ESS_EARLY") ? atoi(getenv("GPIRT_ESS_EARLY")) != 0 : 1;  // screened proposals stop at the first partial sum that already decides a rejection
+    // screened proposals stop at the first partial sum that already decides a rejection. OFF by default: measured on B200 at C3 (profiles/
+    // r02_ess_early_exit.txt) only 4 % / 22 % of the proposals are decided after 1/8 / 3/8 of the cells (the cap on the unseen terms is 0, so a proposal
+    // must be 8x / 2.7x worse than the state) and each extra block reduction costs ~14 % of a pass: 0.63 -> 0.68 ms for the f block.
+    int early_exit = getenv("GPIRT_ESS_EARLY") ? atoi(getenv("GPIRT_ESS_EARLY")) != 0 : 0;
     double* margin[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     gpirt::DevFlags* flags = nullptr;
     int* chol_ws = nullptr;  // per-panel arrival counters of the blocked Cholesky
+    // persistent single-kernel Cholesky (chol_persistent.cu): task lists of the n x n and the NGRID x NGRID factorisation, one state block each
+    uint32_t *chol_tasks_n = nullptr, *chol_tasks_N = nullptr;
+    int *chol_state_n = nullptr, *chol_state_N = nullptr;
+    gpirt::CholPlan plan_n, plan_N;
     double sds0[3] = {0, 0, 0};  // beta_prior_sds.col(0): the sds every K() call uses (src/cholesky-cache.cpp:21)
 
     // optional per-section device timing (gpirt_profile_*): CUDA events around each kernel group

