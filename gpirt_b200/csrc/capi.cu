@@ -1804,3 +1804,23 @@ extern "C" int gpirt_debug_fp64_peak(int device, double* dmma_tflops, double* df
     *dfma_tflops = best[1];
     return GPIRT_OK;
 }
+
+// Measurement hook: the persistent Cholesky with clock64 stamps of its critical CTA (16 per panel step) and of its first worker (8 per task, 256 tasks);
+// trace_out holds 16 T + 8 * 256 values (T = ceil(n / 64)). tools/chol_trace.py turns them into a per-phase table.
+extern "C" int gpirt_debug_chol_trace(int device, const double* A, int64_t n, int ctas, long long* trace_out) {
+    if (!A || !trace_out || n < 1 || n >= 4096) return fail(GPIRT_ERR_INVALID, "chol_trace: bad arguments");
+    TRY(select_device(device));
+    const int ld = pad_ld(n), T = chol_plan_tiles((int)n);
+    const size_t tl = (size_t)16 * T + 8 * 256;
+    DevTemp tA, tI, tT, tS, tR;
+    CU(tA.alloc((size_t)ld * n * 8)); CU(tI.alloc(4)); CU(tR.alloc(tl * 8));
+    const std::vector<uint32_t> tasks = chol_plan_tasks((int)n);
+    CU(tT.alloc(std::max<size_t>(tasks.size(), 1) * 4));
+    CU(tS.alloc(chol_plan_state_ints((int)n) * 4));
+    if (!tasks.empty()) CU(cudaMemcpy(tT.p, tasks.data(), tasks.size() * 4, cudaMemcpyHostToDevice));
+    CU(cudaMemset(tA.p, 0, (size_t)ld * n * 8)); CU(cudaMemset(tI.p, 0, 4)); CU(cudaMemset(tR.p, 0, tl * 8));
+    CU(cudaMemcpy2D(tA.p, (size_t)ld * 8, A, n * 8, n * 8, n, cudaMemcpyHostToDevice));
+    CU(chol_lower_persistent(0, tA.as<double>(), ld, (int)n, tI.as<int>(), tS.as<int>(), tT.as<uint32_t>(), (int)tasks.size(), ctas, tR.as<long long>()));
+    CU(cudaMemcpy(trace_out, tR.p, tl * 8, cudaMemcpyDeviceToHost));
+    return GPIRT_OK;
+}

@@ -83,6 +83,7 @@ struct Ctx {
     int* info; int info_base;
     Shared* sh;
     uint32_t par[3];     // phase parity of the three mbarriers (thread-uniform bookkeeping)
+    long long* trace;    // optional clock64 stamps (gpirt_debug_chol_trace): [k * 16 + s] for the critical CTA, [T * 16 + t * 8 + s] for worker 1
     __device__ int* ver(int i, int j) const { return state + 4 + i * T + j; }
 };
 
@@ -102,15 +103,13 @@ __device__ __forceinline__ bool wait_ge(Ctx& c, const int* p, int want) {
     __syncthreads();
     return c.sh->abort == 0;
 }
+#define TRACE(slot) do { if (c.trace && threadIdx.x == 0) c.trace[(slot)] = clock64(); } while (0)
 __device__ __forceinline__ bool ready(const int* p, int want) { return ld_acquire(p) >= want; }
 
 // all threads have written the tile to global memory: publish its new version
 __device__ __forceinline__ void publish(Ctx& c, int* p, int v) {
     __syncthreads();
-    if (threadIdx.x == 0) {
-        __threadfence();
-        st_release(p, v);
-    }
+    if (threadIdx.x == 0) st_release(p, v);  // release at gpu scope is cumulative over the stores the barrier ordered before this thread
 }
 
 // TMA: columns [0, cols) of the tile at g (leading dimension ld), rows_pad rows (even, within the zero-padded leading dimension) -> sm, column pitch TP.
@@ -167,28 +166,38 @@ __device__ void potf2_tile(Ctx& c, double* sm, int kb) {
     for (int s = 0; s < 8; ++s) {
         const int c0 = 8 * s;
         if (tid == 0) {
-            double a[8][8];
+            // The pivot chain, the only serial part of the factorisation: kept to reciprocal -> multiply -> fma per column by eliminating in
+            // the unnormalised (L D L^T) form, c(i, j) = a(i, j) - sum_k c(i, k) c(j, k) / d_k; the square roots that turn it into the Cholesky
+            // columns l(i, j) = c(i, j) / sqrt(d_j) are independent of each other and come after the chain.
+            double a[8][8], d[8];
 #pragma unroll
             for (int col = 0; col < 8; ++col)
 #pragma unroll
                 for (int r = col; r < 8; ++r) a[r][col] = sm[(c0 + col) * TP + c0 + r];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                double d = a[j][j];
-                if (!(d > 0.0)) {  // arma::chol throws here: record the failing leading minor, keep the arithmetic finite
+                double dj = a[j][j];
+                if (!(dj > 0.0)) {  // arma::chol throws here: record the failing leading minor, keep the arithmetic finite
                     atomicCAS(c.info, 0, c.info_base + c0 + j + 1);
-                    d = 1.0;
+                    dj = 1.0;
                 }
+                d[j] = dj;
+                const double inv = __drcp_rn(dj);
+#pragma unroll
+                for (int jj = j + 1; jj < 8; ++jj) {
+                    const double t = a[jj][j] * inv;
+#pragma unroll
+                    for (int i = jj; i < 8; ++i) a[i][jj] = fma(-a[i][j], t, a[i][jj]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
                 double sq, rs;
-                sqrt_rsqrt2(d, sq, rs);
-                a[j][j] = sq;
+                sqrt_rsqrt2(d[j], sq, rs);
                 c.sh->invd[c0 + j] = rs;
+                a[j][j] = sq;
 #pragma unroll
                 for (int i = j + 1; i < 8; ++i) a[i][j] *= rs;
-#pragma unroll
-                for (int jj = j + 1; jj < 8; ++jj)
-#pragma unroll
-                    for (int i = jj; i < 8; ++i) a[i][jj] -= a[i][j] * a[jj][j];
             }
 #pragma unroll
             for (int col = 0; col < 8; ++col)
@@ -212,22 +221,47 @@ __device__ void potf2_tile(Ctx& c, double* sm, int kb) {
             for (int col = 0; col < 8; ++col) sm[(c0 + col) * TP + r] = x[col];
         }
         __syncthreads();
-        // (c) blocks (bi, bj), s < bj <= bi < 8: tile(bi, bj) -= X(bi) X(bj)^T
-        int cnt = 0;
-        for (int bi = s + 1; bi < 8; ++bi)
-            for (int bj = s + 1; bj <= bi; ++bj, ++cnt) {
-                if ((cnt & 7) != warp) continue;
-                double* cp = sm + (8 * bj + 2 * tig) * TP + 8 * bi + grp;
-                double v0 = cp[0], v1 = cp[TP];
+        // (c) blocks (bi, bj), s < bj <= bi < 8: tile(bi, bj) -= X(bi) X(bj)^T. At most 28 blocks, four per warp: their loads are issued together and
+        // the mma chains interleave
+        {
+            const int rem = 7 - s;
+            int bis[4], bjs[4];
+            bool on[4];
 #pragma unroll
-                for (int kk = 0; kk < 8; kk += 4) {
-                    const double af = -sm[(c0 + kk + tig) * TP + 8 * bi + grp];
-                    const double bf = sm[(c0 + kk + tig) * TP + 8 * bj + grp];
-                    dmma(v0, v1, af, bf);
-                }
-                cp[0] = v0;
-                cp[TP] = v1;
+            for (int q = 0; q < 4; ++q) {
+                const int idx = warp + 8 * q;  // index into the row-major lower triangle of the rem x rem block grid
+                int bi = 0;
+                while ((bi + 1) * (bi + 2) / 2 <= idx) ++bi;
+                on[q] = idx < rem * (rem + 1) / 2;
+                bis[q] = s + 1 + bi;
+                bjs[q] = s + 1 + (idx - bi * (bi + 1) / 2);
             }
+            double v[4][2], af[4][2], bf[4][2];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (on[q]) {
+                    const double* cp = sm + (8 * bjs[q] + 2 * tig) * TP + 8 * bis[q] + grp;
+                    v[q][0] = cp[0];
+                    v[q][1] = cp[TP];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        af[q][h] = -sm[(c0 + 4 * h + tig) * TP + 8 * bis[q] + grp];
+                        bf[q][h] = sm[(c0 + 4 * h + tig) * TP + 8 * bjs[q] + grp];
+                    }
+                }
+#pragma unroll
+            for (int h = 0; h < 2; ++h)
+#pragma unroll
+                for (int q = 0; q < 4; ++q)
+                    if (on[q]) dmma(v[q][0], v[q][1], af[q][h], bf[q][h]);
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (on[q]) {
+                    double* cp = sm + (8 * bjs[q] + 2 * tig) * TP + 8 * bis[q] + grp;
+                    cp[0] = v[q][0];
+                    cp[TP] = v[q][1];
+                }
+        }
         __syncthreads();
     }
 }
@@ -253,17 +287,36 @@ __device__ void solve_tile(Ctx& c, const double* sl, double* sx) {
         }
         __syncthreads();
         if (s == 7) break;
-        // rows 8 warp .. 8 warp + 7: columns beyond the block take X(:, c0..c0+7) L(cols, c0..c0+7)^T
+        // rows 8 warp .. 8 warp + 7: columns beyond the block take X(:, c0..c0+7) L(cols, c0..c0+7)^T; the (up to seven) column blocks are independent
+        // mma chains: loads first, then the mmas back to back
         double af[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) af[h] = -sx[(c0 + 4 * h + tig) * TP + 8 * warp + grp];
-        for (int cb = s + 1; cb < 8; ++cb) {
-            double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
-            double v0 = cp[0], v1 = cp[TP];
+        double v[7][2], bf[7][2];
 #pragma unroll
-            for (int h = 0; h < 2; ++h) dmma(v0, v1, af[h], sl[(c0 + 4 * h + tig) * TP + 8 * cb + grp]);
-            cp[0] = v0;
-            cp[TP] = v1;
+        for (int q = 0; q < 7; ++q) {
+            const int cb = q + 1;
+            if (cb > s) {
+                const double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
+                v[q][0] = cp[0];
+                v[q][1] = cp[TP];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) bf[q][h] = sl[(c0 + 4 * h + tig) * TP + 8 * cb + grp];
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h)
+#pragma unroll
+            for (int q = 0; q < 7; ++q)
+                if (q + 1 > s) dmma(v[q][0], v[q][1], af[h], bf[q][h]);
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const int cb = q + 1;
+            if (cb > s) {
+                double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
+                cp[0] = v[q][0];
+                cp[TP] = v[q][1];
+            }
         }
         __syncthreads();
     }
@@ -288,6 +341,33 @@ __device__ __forceinline__ void tile_product(const double* sa, const double* sb,
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int j = 0; j < 2; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
+    }
+}
+
+// the 36 lower 8 x 8 blocks of sa sa^T (a symmetric update needs no more): block idx = warp + 8 q of the row-major lower triangle, q < 5
+__device__ __forceinline__ void tile_product_lower(const double* sa, double (&acc)[5][2], int (&bi)[5], int (&bj)[5]) {
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
+#pragma unroll
+    for (int q = 0; q < 5; ++q) {
+        const int idx = warp + 8 * q;
+        int b = 0;
+        while ((b + 1) * (b + 2) / 2 <= idx) ++b;
+        bi[q] = idx < 36 ? b : -1;
+        bj[q] = idx - b * (b + 1) / 2;
+        acc[q][0] = acc[q][1] = 0.0;
+    }
+#pragma unroll 2
+    for (int kk = 0; kk < TB_; kk += 4) {
+        double af[5], bf[5];
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+            if (bi[q] >= 0) {
+                af[q] = sa[(kk + tig) * TP + 8 * bi[q] + grp];
+                bf[q] = sa[(kk + tig) * TP + 8 * bj[q] + grp];
+            }
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+            if (bi[q] >= 0) dmma(acc[q][0], acc[q][1], af[q], bf[q]);
     }
 }
 
@@ -317,6 +397,7 @@ __device__ void run_critical(Ctx& c) {
         const int kb = rows_of(c, k);
         const bool has_next = k + 1 < T;
         const int nb = has_next ? rows_of(c, k + 1) : 0;
+        TRACE(k * 16 + 0);
         // the panel tile (k+1, k) must carry the updates of steps < k; if it does already, its copy runs under the potf2
         bool sub_issued = false;
         if (has_next) {
@@ -330,10 +411,13 @@ __device__ void run_critical(Ctx& c) {
         }
         if (diag_in_flight) { tile_wait(c, 0); diag_in_flight = false; }
         if (sh->abort) return;
+        TRACE(k * 16 + 1);
         c.info_base = k * TB_;
         potf2_tile(c, sh->A, kb);
+        TRACE(k * 16 + 2);
         tile_store(c, sh->A, k, k, kb, kb, true);
         publish(c, c.ver(k, k), k + 1);
+        TRACE(k * 16 + 3);
         if (!has_next) break;
         if (!sub_issued) {
             if (!wait_ge(c, c.ver(k + 1, k), k)) return;
@@ -348,44 +432,164 @@ __device__ void run_critical(Ctx& c) {
             tile_load(c, 2, sh->C, tile_ptr(c, k + 1, k + 1), pad2(nb), nb);
             next_issued = true;
         }
+        TRACE(k * 16 + 4);
         tile_wait(c, 1);
         if (sh->abort) return;
+        TRACE(k * 16 + 5);
         // invd of this tile is what potf2 left (1 / sqrt(pivot)): solve in place
         solve_tile(c, sh->A, sh->B);
+        TRACE(k * 16 + 6);
         tile_store(c, sh->B, k + 1, k, nb, TB_, false);
         publish(c, c.ver(k + 1, k), k + 1);
+        TRACE(k * 16 + 7);
         if (!next_issued) {
             if (!wait_ge(c, c.ver(k + 1, k + 1), k)) return;
             tile_load(c, 2, sh->C, tile_ptr(c, k + 1, k + 1), pad2(nb), nb);
         }
+        TRACE(k * 16 + 8);
         tile_wait(c, 2);
         if (sh->abort) return;
-        // next diagonal tile = C - X X^T, written over A (L(k, k) is no longer needed)
-        double acc[4][2][2];
-        tile_product(sh->B, sh->B, acc);
-        __syncthreads();
+        TRACE(k * 16 + 9);
+        // next diagonal tile = C - X X^T (lower blocks; potf2 reads nothing above the diagonal), written over A: L(k, k) is no longer needed
         {
-            const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
-            const int wm = warp & 1, wn = warp >> 1;
+            double acc[5][2];
+            int bi[5], bj[5];
+            tile_product_lower(sh->B, acc, bi, bj);
+            const int lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-#pragma unroll
-                for (int j = 0; j < 2; ++j)
+            for (int q = 0; q < 5; ++q)
+                if (bi[q] >= 0) {
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
-                        const int r = 32 * wm + 8 * i + grp, col = 16 * wn + 8 * j + 2 * tig + e;
-                        sh->A[col * TP + r] = sh->C[col * TP + r] - acc[i][j][e];
+                        const int r = 8 * bi[q] + grp, col = 8 * bj[q] + 2 * tig + e;
+                        sh->A[col * TP + r] = sh->C[col * TP + r] - acc[q][e];
                     }
+                }
         }
         __syncthreads();
+        TRACE(k * 16 + 10);
         // tile (k+1, k+1) now carries step k as well; nobody else reads it before its potf2 publishes version k + 2
     }
 }
 
-// ---- the other CTAs: tile tasks in list order ----
+// ---- the other CTAs: tile tasks ----
+// One task: S = solve of panel tile (i, k) against L(k, k); U = tile (i, j) -= L(i, k) L(j, k)^T. Returns false when the kernel is giving up.
+__device__ bool do_task(Ctx& c, uint32_t w, int tb) {
+    Shared* sh = c.sh;
+    const int type = (int)(w >> 30), i = (int)((w >> 20) & 1023u), j = (int)((w >> 10) & 1023u), k = (int)(w & 1023u);
+    const int ri = rows_of(c, i);
+    TRACE(tb + 0);
+    if (c.trace && threadIdx.x == 0) c.trace[tb + 7] = (long long)w;
+    if (type == (int)TASK_S) {  // tile (i, k): X L(k, k)^T = A(i, k)
+        if (!wait_ge(c, c.ver(k, k), k + 1)) return false;
+        tile_load(c, 0, sh->A, tile_ptr(c, k, k), TB_, TB_);
+        if (!wait_ge(c, c.ver(i, k), k)) return false;
+        tile_load(c, 1, sh->B, tile_ptr(c, i, k), pad2(ri), TB_);
+        TRACE(tb + 1);
+        tile_wait(c, 0);
+        __syncthreads();
+        load_invd(c, sh->A);
+        tile_wait(c, 1);
+        __syncthreads();
+        if (sh->abort) return false;
+        TRACE(tb + 2);
+        solve_tile(c, sh->A, sh->B);
+        TRACE(tb + 3);
+        tile_store(c, sh->B, i, k, ri, TB_, false);
+        TRACE(tb + 4);
+        publish(c, c.ver(i, k), k + 1);
+        TRACE(tb + 5);
+        return true;
+    }
+    const int rj = rows_of(c, j);
+    if (!wait_ge(c, c.ver(i, k), k + 1)) return false;
+    tile_load(c, 0, sh->A, tile_ptr(c, i, k), pad2(ri), TB_);
+    const int lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
+    double* g = const_cast<double*>(tile_ptr(c, i, j));
+    if (i == j) {  // symmetric update of a diagonal tile: the 36 lower blocks
+        if (!wait_ge(c, c.ver(i, j), k)) return false;
+        TRACE(tb + 1);
+        tile_wait(c, 0);
+        __syncthreads();
+        if (sh->abort) return false;
+        TRACE(tb + 2);
+        double acc[5][2];
+        int bi[5], bj[5];
+        tile_product_lower(sh->A, acc, bi, bj);
+        TRACE(tb + 3);
+#pragma unroll
+        for (int q = 0; q < 5; ++q)
+            if (bi[q] >= 0) {
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int r = 8 * bi[q] + grp, col = 8 * bj[q] + 2 * tig + e;
+                    if (r < ri && col < rj) {
+                        double* p = g + (size_t)col * c.ld + r;
+                        *p = __ldcg(p) - acc[q][e];
+                    }
+                }
+            }
+    } else {
+        if (!wait_ge(c, c.ver(j, k), k + 1)) return false;
+        tile_load(c, 1, sh->B, tile_ptr(c, j, k), pad2(rj), TB_);
+        if (!wait_ge(c, c.ver(i, j), k)) return false;
+        TRACE(tb + 1);
+        // the C tile goes through registers: loads issued before the product so their latency hides under it
+        const int warp = threadIdx.x >> 5, wm = warp & 1, wn = warp >> 1;
+        double cv[4][2][2];
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
+                    cv[a][b][e] = (r < ri && col < rj) ? __ldcg(g + (size_t)col * c.ld + r) : 0.0;
+                }
+        tile_wait(c, 0);
+        tile_wait(c, 1);
+        __syncthreads();
+        if (sh->abort) return false;
+        TRACE(tb + 2);
+        double acc[4][2][2];
+        tile_product(sh->A, sh->B, acc);
+        TRACE(tb + 3);
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 2; ++b)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
+                    if (r < ri && col < rj) g[(size_t)col * c.ld + r] = cv[a][b][e] - acc[a][b][e];
+                }
+    }
+    TRACE(tb + 4);
+    publish(c, c.ver(i, j), k + 1);
+    TRACE(tb + 5);
+    return true;
+}
+
+// Roles by order of arrival: 0 the critical path; 1 and 2 the two short chains the critical CTA's NEXT step waits for — S(k+2, k) then
+// U(k+2, k+2, k), and U(k+2, k+1, k) — which must not queue behind bulk work (measured: in the common list they arrived ~5 us late at every
+// step); >= 3 the bulk list through the ticket.
 __device__ void run_worker(Ctx& c, const uint32_t* tasks, int n_tasks) {
     Shared* sh = c.sh;
-    for (;;) {
+    const int role = sh->role;
+    if (role != 3) c.trace = nullptr;  // only the first bulk worker is traced
+    if (role == 1 || role == 2) {
+        for (int k = 0; k + 2 < c.T; ++k) {
+            if (role == 1) {
+                if (!do_task(c, pack_task(TASK_S, k + 2, k, k), 0)) return;
+                if (!do_task(c, pack_task(TASK_U, k + 2, k + 2, k), 0)) return;
+            } else {
+                if (!do_task(c, pack_task(TASK_U, k + 2, k + 1, k), 0)) return;
+            }
+        }
+        return;
+    }
+    for (int done = 0;; ++done) {
+        if (done >= 256) c.trace = nullptr;
         __syncthreads();
         if (threadIdx.x == 0) {
             const int t = atomicAdd(c.state + 0, 1);
@@ -394,73 +598,16 @@ __device__ void run_worker(Ctx& c, const uint32_t* tasks, int n_tasks) {
         __syncthreads();
         const uint32_t w = sh->task;
         if (w == 0u || sh->abort) return;
-        const int type = (int)(w >> 30), i = (int)((w >> 20) & 1023u), j = (int)((w >> 10) & 1023u), k = (int)(w & 1023u);
-        const int ri = rows_of(c, i);
-        if (type == (int)TASK_S) {  // tile (i, k): X L(k, k)^T = A(i, k)
-            if (!wait_ge(c, c.ver(k, k), k + 1)) return;
-            tile_load(c, 0, sh->A, tile_ptr(c, k, k), TB_, TB_);
-            if (!wait_ge(c, c.ver(i, k), k)) return;
-            tile_load(c, 1, sh->B, tile_ptr(c, i, k), pad2(ri), TB_);
-            tile_wait(c, 0);
-            __syncthreads();
-            load_invd(c, sh->A);
-            tile_wait(c, 1);
-            __syncthreads();
-            if (sh->abort) return;
-            solve_tile(c, sh->A, sh->B);
-            tile_store(c, sh->B, i, k, ri, TB_, false);
-            publish(c, c.ver(i, k), k + 1);
-        } else {  // tile (i, j) -= L(i, k) L(j, k)^T
-            const int rj = rows_of(c, j);
-            if (!wait_ge(c, c.ver(i, k), k + 1)) return;
-            tile_load(c, 0, sh->A, tile_ptr(c, i, k), pad2(ri), TB_);
-            const double* sb = sh->A;
-            if (j != i) {
-                if (!wait_ge(c, c.ver(j, k), k + 1)) return;
-                tile_load(c, 1, sh->B, tile_ptr(c, j, k), pad2(rj), TB_);
-                sb = sh->B;
-            }
-            if (!wait_ge(c, c.ver(i, j), k)) return;
-            // the C tile goes through registers: loads issued before the product so their latency hides under it
-            const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
-            const int wm = warp & 1, wn = warp >> 1;
-            double* g = const_cast<double*>(tile_ptr(c, i, j));
-            double cv[4][2][2];
-#pragma unroll
-            for (int a = 0; a < 4; ++a)
-#pragma unroll
-                for (int b = 0; b < 2; ++b)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
-                        cv[a][b][e] = (r < ri && col < rj) ? __ldcg(g + (size_t)col * c.ld + r) : 0.0;
-                    }
-            tile_wait(c, 0);
-            if (j != i) tile_wait(c, 1);
-            __syncthreads();
-            if (sh->abort) return;
-            double acc[4][2][2];
-            tile_product(sh->A, sb, acc);
-#pragma unroll
-            for (int a = 0; a < 4; ++a)
-#pragma unroll
-                for (int b = 0; b < 2; ++b)
-#pragma unroll
-                    for (int e = 0; e < 2; ++e) {
-                        const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
-                        if (r < ri && col < rj) g[(size_t)col * c.ld + r] = cv[a][b][e] - acc[a][b][e];
-                    }
-            publish(c, c.ver(i, j), k + 1);
-        }
+        if (!do_task(c, w, c.T * 16 + done * 8)) return;
     }
 }
 
 __global__ void __launch_bounds__(CP_THREADS, 1) k_chol_persistent(double* A, int ld, int n, int T, int* state, int* info, const uint32_t* tasks,
-                                                                   int n_tasks) {
+                                                                   int n_tasks, long long* trace) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Shared* sh = reinterpret_cast<Shared*>(smem_raw);
     Ctx c;
-    c.A = A; c.ld = ld; c.n = n; c.T = T; c.state = state; c.info = info; c.info_base = 0; c.sh = sh;
+    c.A = A; c.ld = ld; c.n = n; c.T = T; c.state = state; c.info = info; c.info_base = 0; c.sh = sh; c.trace = trace;
     c.par[0] = c.par[1] = c.par[2] = 0u;
     if (threadIdx.x == 0) {
         for (int b = 0; b < 3; ++b) mbar_init(&sh->mbar[b], 1);
@@ -490,18 +637,14 @@ size_t chol_plan_state_ints(int n) {
     return 4 + T * T;
 }
 
-// The worker list. Step k's segment: first the three tasks the critical CTA's step k + 1 waits for, then the panel solves, then the next
-// panel column, then the rest by columns. Every dependency of a task is the critical CTA's or sits earlier in the list.
+// The bulk list. Step k's segment: the panel solves, then the next panel column, then the rest by columns. Every dependency of a task is
+// produced by the critical CTA, by a priority CTA (whose own inputs come from the critical CTA and from earlier segments), or sits earlier in the list.
 std::vector<uint32_t> chol_plan_tasks(int n) {
     const int T = chol_plan_tiles(n);
     std::vector<uint32_t> t;
     for (int k = 0; k + 1 < T; ++k) {
         // tile (k+1, k) and (k+1, k+1) of step k belong to the critical CTA
-        if (k + 2 < T) {
-            t.push_back(pack_task(TASK_S, k + 2, k, k));
-            t.push_back(pack_task(TASK_U, k + 2, k + 1, k));
-            t.push_back(pack_task(TASK_U, k + 2, k + 2, k));
-        }
+        // S(k+2, k), U(k+2, k+1, k), U(k+2, k+2, k) belong to the two priority CTAs (run_worker)
         for (int i = k + 3; i < T; ++i) t.push_back(pack_task(TASK_S, i, k, k));
         for (int i = k + 3; i < T; ++i) t.push_back(pack_task(TASK_U, i, k + 1, k));
         for (int j = k + 2; j < T; ++j)
@@ -514,7 +657,7 @@ std::vector<uint32_t> chol_plan_tasks(int n) {
 }
 
 cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* state_dev, const uint32_t* tasks_dev, int n_tasks,
-                                  int max_ctas) {
+                                  int max_ctas, long long* trace_dev) {
     const int T = chol_plan_tiles(n);
     if (T > 1023) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(state_dev, 0, chol_plan_state_ints(n) * sizeof(int), st);
@@ -522,9 +665,13 @@ cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int
     const size_t smem = sizeof(Shared) + 128;
     e = cudaFuncSetAttribute(k_chol_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    int grid = 1 + (n_tasks < max_ctas - 1 ? n_tasks : max_ctas - 1);
-    if (grid < 1) grid = 1;
-    k_chol_persistent<<<grid, CP_THREADS, smem, st>>>(A, ld, n, T, state_dev, info_dev, tasks_dev, n_tasks);
+    int grid = 1;  // T <= 2: the critical CTA does everything
+    if (T >= 3) {
+        int bulk = n_tasks < max_ctas - 3 ? n_tasks : max_ctas - 3;
+        if (n_tasks > 0 && bulk < 1) bulk = 1;  // the bulk list needs at least one CTA of its own
+        grid = 3 + (bulk > 0 ? bulk : 0);
+    }
+    k_chol_persistent<<<grid, CP_THREADS, smem, st>>>(A, ld, n, T, state_dev, info_dev, tasks_dev, n_tasks, trace_dev);
     ++g_kernel_launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;

@@ -48,7 +48,7 @@ size_t chol_plan_state_ints(int n);
 std::vector<uint32_t> chol_plan_tasks(int n);
 // info_dev: 0, the failing leading minor (1-based), or -1 when the kernel gave up waiting (never on a healthy device)
 cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* state_dev, const uint32_t* tasks_dev, int n_tasks,
-                                  int max_ctas);
+                                  int max_ctas, long long* trace_dev = nullptr);
 // plan != nullptr and n below the two-level threshold: the persistent kernel; milestones are then all recorded at the end.
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr,
                                const CholAux* aux = nullptr, const CholPlan* plan = nullptr);

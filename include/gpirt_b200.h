@@ -219,6 +219,9 @@ int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const 
  * pipes the sweep's contractions run on, ~20 ms each on an otherwise idle device: mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) and scalar DFMA,
  * in TFLOP/s. No reference counterpart. */
 int gpirt_debug_fp64_peak(int device, double* dmma_tflops, double* dfma_tflops);
+/* Measurement hook: the persistent Cholesky (csrc/chol_persistent.cu) on the n x n matrix A (n < 4096) with `ctas` CTAs and clock64 stamps of its
+ * critical CTA (16 per panel step) and first worker (8 per task, 256 tasks): trace_out holds 16 ceil(n/64) + 2048 values. */
+int gpirt_debug_chol_trace(int device, const double* A, int64_t n, int ctas, long long* trace_out);
 
 /* ---- horizon > 1 (dynamic GPIRT), constant_IRF == 0 ----
  * A panel is `horizon` single-session samplers (given theta the sessions are independent: the reference loops h outside every per-item
