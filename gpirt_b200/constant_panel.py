@@ -125,7 +125,10 @@ class ConstantPanel:
             S.set_state(thresholds=thr)
 
     def total_ll(self):
-        return float(sum(S.ll_bar()[1] for S in self.S))  # src/gpirtMCMC.cpp:324-331
+        acc = 0.0  # one running sum in session order, src/gpirtMCMC.cpp:324-331 (not the builtin sum(): Python >= 3.12 compensates float sums,
+        for S in self.S:  # which is not the reference's left-to-right accumulation and differs from it in the last bit now and then)
+            acc += S.ll_bar()[1]
+        return acc
 
     def sweep(self):
         """One sweep (src/gpirtMCMC.cpp:267-331), Philox streams."""

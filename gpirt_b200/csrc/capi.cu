@@ -394,7 +394,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         for (const Piece& pc : pieces) { *pc.p = h->arena + off; off += pc.bytes; }
     }
     {
-        static const int chol_ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 64;
+        static const int chol_ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 48;
         if (!tasks_n.empty()) CU(cudaMemcpyAsync(h->chol_tasks_n, tasks_n.data(), tasks_n.size() * 4, cudaMemcpyHostToDevice, h->stream));
         if (!tasks_N.empty()) CU(cudaMemcpyAsync(h->chol_tasks_N, tasks_N.data(), tasks_N.size() * 4, cudaMemcpyHostToDevice, h->stream));
         CU(cudaStreamSynchronize(h->stream));  // the host vectors go out of scope
@@ -1352,7 +1352,7 @@ int gpirt_chol(int device, const double* A, int64_t n, double* L) {
         CU(tT.alloc(std::max<size_t>(tasks.size(), 1) * 4));
         CU(tS.alloc(chol_plan_state_ints((int)n) * 4));
         if (!tasks.empty()) CU(cudaMemcpy(tT.p, tasks.data(), tasks.size() * 4, cudaMemcpyHostToDevice));
-        plan.tasks = tT.as<uint32_t>(); plan.n_tasks = (int)tasks.size(); plan.state = tS.as<int>(); plan.max_ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 64;
+        plan.tasks = tT.as<uint32_t>(); plan.n_tasks = (int)tasks.size(); plan.state = tS.as<int>(); plan.max_ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 48;
     }
     CU(chol_lower_blocked(0, dA, ld, (int)n, info, info + 1, nullptr, nullptr, plan.state ? &plan : nullptr));
     CU(cudaMemcpy2D(L, n * 8, dA, (size_t)ld * 8, n * 8, n, cudaMemcpyDeviceToHost));

@@ -113,17 +113,19 @@ __device__ __forceinline__ void publish(Ctx& c, int* p, int v) {
 }
 
 // TMA: columns [0, cols) of the tile at g (leading dimension ld), rows_pad rows (even, within the zero-padded leading dimension) -> sm, column pitch TP.
-// Called by every thread of the CTA: each one fences its own generic-proxy accesses of the buffer against the async proxy, the barrier ends all
-// use of `sm`, then warp 0 issues one bulk copy per column, all completing on the buffer's mbarrier.
+// Called by every thread of the CTA: each one fences its own generic-proxy accesses of the buffer against the async proxy, thread 0 arms the
+// buffer's mbarrier with the byte count, the barrier ends all use of `sm`, then every warp issues 8 of the 64 column copies (one per lane): the
+// bulk-copy instruction runs on the warp's uniform datapath, and 64 of them from one warp measured ~4.5k cycles of issue per tile (clock64 trace,
+// profiles/r02_chol_persistent.txt) on the critical path.
 __device__ __forceinline__ void tile_load(Ctx& c, int which, double* sm, const double* g, int rows_pad, int cols) {
+    unsigned long long* bar = &c.sh->mbar[which];
     fence_proxy_async();
+    if (threadIdx.x == 0) mbar_expect_tx(bar, (uint32_t)(rows_pad * 8 * cols));
     __syncthreads();
-    if (threadIdx.x < 32) {
-        unsigned long long* bar = &c.sh->mbar[which];
-        fence_proxy_async();  // this lane's view (flags acquired before the barrier) is ordered before its bulk reads
-        if (threadIdx.x == 0) mbar_expect_tx(bar, (uint32_t)(rows_pad * 8 * cols));
-        __syncwarp();
-        for (int col = threadIdx.x; col < cols; col += 32) bulk_g2s(sm + col * TP, g + (size_t)col * c.ld, (uint32_t)(rows_pad * 8), bar);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane < 8) {
+        const int col = warp + 8 * lane;
+        if (col < cols) bulk_g2s(sm + col * TP, g + (size_t)col * c.ld, (uint32_t)(rows_pad * 8), bar);
     }
 }
 __device__ __forceinline__ bool tile_wait(Ctx& c, int which) {
@@ -166,38 +168,28 @@ __device__ void potf2_tile(Ctx& c, double* sm, int kb) {
     for (int s = 0; s < 8; ++s) {
         const int c0 = 8 * s;
         if (tid == 0) {
-            // The pivot chain, the only serial part of the factorisation: kept to reciprocal -> multiply -> fma per column by eliminating in
-            // the unnormalised (L D L^T) form, c(i, j) = a(i, j) - sum_k c(i, k) c(j, k) / d_k; the square roots that turn it into the Cholesky
-            // columns l(i, j) = c(i, j) / sqrt(d_j) are independent of each other and come after the chain.
-            double a[8][8], d[8];
+            double a[8][8];
 #pragma unroll
             for (int col = 0; col < 8; ++col)
 #pragma unroll
                 for (int r = col; r < 8; ++r) a[r][col] = sm[(c0 + col) * TP + c0 + r];
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
-                double dj = a[j][j];
-                if (!(dj > 0.0)) {  // arma::chol throws here: record the failing leading minor, keep the arithmetic finite
+                double d = a[j][j];
+                if (!(d > 0.0)) {  // arma::chol throws here: record the failing leading minor, keep the arithmetic finite
                     atomicCAS(c.info, 0, c.info_base + c0 + j + 1);
-                    dj = 1.0;
+                    d = 1.0;
                 }
-                d[j] = dj;
-                const double inv = __drcp_rn(dj);
-#pragma unroll
-                for (int jj = j + 1; jj < 8; ++jj) {
-                    const double t = a[jj][j] * inv;
-#pragma unroll
-                    for (int i = jj; i < 8; ++i) a[i][jj] = fma(-a[i][j], t, a[i][jj]);
-                }
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
                 double sq, rs;
-                sqrt_rsqrt2(d[j], sq, rs);
-                c.sh->invd[c0 + j] = rs;
+                sqrt_rsqrt2(d, sq, rs);
                 a[j][j] = sq;
+                c.sh->invd[c0 + j] = rs;
 #pragma unroll
                 for (int i = j + 1; i < 8; ++i) a[i][j] *= rs;
+#pragma unroll
+                for (int jj = j + 1; jj < 8; ++jj)
+#pragma unroll
+                    for (int i = jj; i < 8; ++i) a[i][jj] -= a[i][j] * a[jj][j];
             }
 #pragma unroll
             for (int col = 0; col < 8; ++col)
@@ -221,47 +213,22 @@ __device__ void potf2_tile(Ctx& c, double* sm, int kb) {
             for (int col = 0; col < 8; ++col) sm[(c0 + col) * TP + r] = x[col];
         }
         __syncthreads();
-        // (c) blocks (bi, bj), s < bj <= bi < 8: tile(bi, bj) -= X(bi) X(bj)^T. At most 28 blocks, four per warp: their loads are issued together and
-        // the mma chains interleave
-        {
-            const int rem = 7 - s;
-            int bis[4], bjs[4];
-            bool on[4];
+        // (c) blocks (bi, bj), s < bj <= bi < 8: tile(bi, bj) -= X(bi) X(bj)^T
+        int cnt = 0;
+        for (int bi = s + 1; bi < 8; ++bi)
+            for (int bj = s + 1; bj <= bi; ++bj, ++cnt) {
+                if ((cnt & 7) != warp) continue;
+                double* cp = sm + (8 * bj + 2 * tig) * TP + 8 * bi + grp;
+                double v0 = cp[0], v1 = cp[TP];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int idx = warp + 8 * q;  // index into the row-major lower triangle of the rem x rem block grid
-                int bi = 0;
-                while ((bi + 1) * (bi + 2) / 2 <= idx) ++bi;
-                on[q] = idx < rem * (rem + 1) / 2;
-                bis[q] = s + 1 + bi;
-                bjs[q] = s + 1 + (idx - bi * (bi + 1) / 2);
+                for (int kk = 0; kk < 8; kk += 4) {
+                    const double af = -sm[(c0 + kk + tig) * TP + 8 * bi + grp];
+                    const double bf = sm[(c0 + kk + tig) * TP + 8 * bj + grp];
+                    dmma(v0, v1, af, bf);
+                }
+                cp[0] = v0;
+                cp[TP] = v1;
             }
-            double v[4][2], af[4][2], bf[4][2];
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-                if (on[q]) {
-                    const double* cp = sm + (8 * bjs[q] + 2 * tig) * TP + 8 * bis[q] + grp;
-                    v[q][0] = cp[0];
-                    v[q][1] = cp[TP];
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        af[q][h] = -sm[(c0 + 4 * h + tig) * TP + 8 * bis[q] + grp];
-                        bf[q][h] = sm[(c0 + 4 * h + tig) * TP + 8 * bjs[q] + grp];
-                    }
-                }
-#pragma unroll
-            for (int h = 0; h < 2; ++h)
-#pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    if (on[q]) dmma(v[q][0], v[q][1], af[q][h], bf[q][h]);
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-                if (on[q]) {
-                    double* cp = sm + (8 * bjs[q] + 2 * tig) * TP + 8 * bis[q] + grp;
-                    cp[0] = v[q][0];
-                    cp[TP] = v[q][1];
-                }
-        }
         __syncthreads();
     }
 }
@@ -287,36 +254,17 @@ __device__ void solve_tile(Ctx& c, const double* sl, double* sx) {
         }
         __syncthreads();
         if (s == 7) break;
-        // rows 8 warp .. 8 warp + 7: columns beyond the block take X(:, c0..c0+7) L(cols, c0..c0+7)^T; the (up to seven) column blocks are independent
-        // mma chains: loads first, then the mmas back to back
+        // rows 8 warp .. 8 warp + 7: columns beyond the block take X(:, c0..c0+7) L(cols, c0..c0+7)^T
         double af[2];
 #pragma unroll
         for (int h = 0; h < 2; ++h) af[h] = -sx[(c0 + 4 * h + tig) * TP + 8 * warp + grp];
-        double v[7][2], bf[7][2];
+        for (int cb = s + 1; cb < 8; ++cb) {
+            double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
+            double v0 = cp[0], v1 = cp[TP];
 #pragma unroll
-        for (int q = 0; q < 7; ++q) {
-            const int cb = q + 1;
-            if (cb > s) {
-                const double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
-                v[q][0] = cp[0];
-                v[q][1] = cp[TP];
-#pragma unroll
-                for (int h = 0; h < 2; ++h) bf[q][h] = sl[(c0 + 4 * h + tig) * TP + 8 * cb + grp];
-            }
-        }
-#pragma unroll
-        for (int h = 0; h < 2; ++h)
-#pragma unroll
-            for (int q = 0; q < 7; ++q)
-                if (q + 1 > s) dmma(v[q][0], v[q][1], af[h], bf[q][h]);
-#pragma unroll
-        for (int q = 0; q < 7; ++q) {
-            const int cb = q + 1;
-            if (cb > s) {
-                double* cp = sx + (8 * cb + 2 * tig) * TP + 8 * warp + grp;
-                cp[0] = v[q][0];
-                cp[TP] = v[q][1];
-            }
+            for (int h = 0; h < 2; ++h) dmma(v0, v1, af[h], sl[(c0 + 4 * h + tig) * TP + 8 * cb + grp]);
+            cp[0] = v0;
+            cp[TP] = v1;
         }
         __syncthreads();
     }
@@ -341,33 +289,6 @@ __device__ __forceinline__ void tile_product(const double* sa, const double* sb,
         for (int i = 0; i < 4; ++i)
 #pragma unroll
             for (int j = 0; j < 2; ++j) dmma(acc[i][j][0], acc[i][j][1], af[i], bf[j]);
-    }
-}
-
-// the 36 lower 8 x 8 blocks of sa sa^T (a symmetric update needs no more): block idx = warp + 8 q of the row-major lower triangle, q < 5
-__device__ __forceinline__ void tile_product_lower(const double* sa, double (&acc)[5][2], int (&bi)[5], int (&bj)[5]) {
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
-#pragma unroll
-    for (int q = 0; q < 5; ++q) {
-        const int idx = warp + 8 * q;
-        int b = 0;
-        while ((b + 1) * (b + 2) / 2 <= idx) ++b;
-        bi[q] = idx < 36 ? b : -1;
-        bj[q] = idx - b * (b + 1) / 2;
-        acc[q][0] = acc[q][1] = 0.0;
-    }
-#pragma unroll 2
-    for (int kk = 0; kk < TB_; kk += 4) {
-        double af[5], bf[5];
-#pragma unroll
-        for (int q = 0; q < 5; ++q)
-            if (bi[q] >= 0) {
-                af[q] = sa[(kk + tig) * TP + 8 * bi[q] + grp];
-                bf[q] = sa[(kk + tig) * TP + 8 * bj[q] + grp];
-            }
-#pragma unroll
-        for (int q = 0; q < 5; ++q)
-            if (bi[q] >= 0) dmma(acc[q][0], acc[q][1], af[q], bf[q]);
     }
 }
 
@@ -450,21 +371,22 @@ __device__ void run_critical(Ctx& c) {
         tile_wait(c, 2);
         if (sh->abort) return;
         TRACE(k * 16 + 9);
-        // next diagonal tile = C - X X^T (lower blocks; potf2 reads nothing above the diagonal), written over A: L(k, k) is no longer needed
+        // next diagonal tile = C - X X^T, written over A (L(k, k) is no longer needed)
         {
-            double acc[5][2];
-            int bi[5], bj[5];
-            tile_product_lower(sh->B, acc, bi, bj);
-            const int lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
+            double acc[4][2][2];
+            tile_product(sh->B, sh->B, acc);
+            __syncthreads();
+            const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
+            const int wm = warp & 1, wn = warp >> 1;
 #pragma unroll
-            for (int q = 0; q < 5; ++q)
-                if (bi[q] >= 0) {
+            for (int i = 0; i < 4; ++i)
+#pragma unroll
+                for (int j = 0; j < 2; ++j)
 #pragma unroll
                     for (int e = 0; e < 2; ++e) {
-                        const int r = 8 * bi[q] + grp, col = 8 * bj[q] + 2 * tig + e;
-                        sh->A[col * TP + r] = sh->C[col * TP + r] - acc[q][e];
+                        const int r = 32 * wm + 8 * i + grp, col = 16 * wn + 8 * j + 2 * tig + e;
+                        sh->A[col * TP + r] = sh->C[col * TP + r] - acc[i][j][e];
                     }
-                }
         }
         __syncthreads();
         TRACE(k * 16 + 10);
@@ -506,64 +428,43 @@ __device__ bool do_task(Ctx& c, uint32_t w, int tb) {
     tile_load(c, 0, sh->A, tile_ptr(c, i, k), pad2(ri), TB_);
     const int lane = threadIdx.x & 31, grp = lane >> 2, tig = lane & 3;
     double* g = const_cast<double*>(tile_ptr(c, i, j));
-    if (i == j) {  // symmetric update of a diagonal tile: the 36 lower blocks
-        if (!wait_ge(c, c.ver(i, j), k)) return false;
-        TRACE(tb + 1);
-        tile_wait(c, 0);
-        __syncthreads();
-        if (sh->abort) return false;
-        TRACE(tb + 2);
-        double acc[5][2];
-        int bi[5], bj[5];
-        tile_product_lower(sh->A, acc, bi, bj);
-        TRACE(tb + 3);
-#pragma unroll
-        for (int q = 0; q < 5; ++q)
-            if (bi[q] >= 0) {
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int r = 8 * bi[q] + grp, col = 8 * bj[q] + 2 * tig + e;
-                    if (r < ri && col < rj) {
-                        double* p = g + (size_t)col * c.ld + r;
-                        *p = __ldcg(p) - acc[q][e];
-                    }
-                }
-            }
-    } else {
+    const double* sb = sh->A;
+    if (j != i) {
         if (!wait_ge(c, c.ver(j, k), k + 1)) return false;
         tile_load(c, 1, sh->B, tile_ptr(c, j, k), pad2(rj), TB_);
-        if (!wait_ge(c, c.ver(i, j), k)) return false;
-        TRACE(tb + 1);
-        // the C tile goes through registers: loads issued before the product so their latency hides under it
-        const int warp = threadIdx.x >> 5, wm = warp & 1, wn = warp >> 1;
-        double cv[4][2][2];
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
-                    cv[a][b][e] = (r < ri && col < rj) ? __ldcg(g + (size_t)col * c.ld + r) : 0.0;
-                }
-        tile_wait(c, 0);
-        tile_wait(c, 1);
-        __syncthreads();
-        if (sh->abort) return false;
-        TRACE(tb + 2);
-        double acc[4][2][2];
-        tile_product(sh->A, sh->B, acc);
-        TRACE(tb + 3);
-#pragma unroll
-        for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 2; ++b)
-#pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
-                    if (r < ri && col < rj) g[(size_t)col * c.ld + r] = cv[a][b][e] - acc[a][b][e];
-                }
+        sb = sh->B;
     }
+    if (!wait_ge(c, c.ver(i, j), k)) return false;
+    TRACE(tb + 1);
+    // the C tile goes through registers: loads issued before the product so their latency hides under it
+    const int warp = threadIdx.x >> 5, wm = warp & 1, wn = warp >> 1;
+    double cv[4][2][2];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
+                cv[a][b][e] = (r < ri && col < rj) ? __ldcg(g + (size_t)col * c.ld + r) : 0.0;
+            }
+    tile_wait(c, 0);
+    if (j != i) tile_wait(c, 1);
+    __syncthreads();
+    if (sh->abort) return false;
+    TRACE(tb + 2);
+    double acc[4][2][2];
+    tile_product(sh->A, sb, acc);
+    TRACE(tb + 3);
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 2; ++b)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int r = 32 * wm + 8 * a + grp, col = 16 * wn + 8 * b + 2 * tig + e;
+                if (r < ri && col < rj) g[(size_t)col * c.ld + r] = cv[a][b][e] - acc[a][b][e];
+            }
     TRACE(tb + 4);
     publish(c, c.ver(i, j), k + 1);
     TRACE(tb + 5);
