@@ -61,7 +61,7 @@ class RecoverArgs(C.Structure):
 # every symbol include/gpirt_b200.h declares (tests check the library exports each one)
 SYMBOLS = [
     "gpirt_last_error", "gpirt_device_count", "gpirt_K", "gpirt_K_time", "gpirt_delta_to_threshold",
-    "gpirt_threshold_to_delta", "gpirt_chol", "gpirt_double_solve", "gpirt_create", "gpirt_destroy", "gpirt_release_cached_memory", "gpirt_set_stream",
+    "gpirt_threshold_to_delta", "gpirt_chol", "gpirt_chol_device_noalloc", "gpirt_double_solve", "gpirt_create", "gpirt_destroy", "gpirt_release_cached_memory", "gpirt_set_stream",
     "gpirt_set_data_f64", "gpirt_set_data_i8", "gpirt_set_priors", "gpirt_set_state", "gpirt_get_state", "gpirt_get_L",
     "gpirt_store_open", "gpirt_store_push", "gpirt_store_count", "gpirt_store_flush", "gpirt_store_flush_slice", "gpirt_store_close", "gpirt_store_sample_bytes",
     "gpirt_set_iter", "gpirt_init_f_from_z", "gpirt_panel_create", "gpirt_panel_destroy", "gpirt_panel_session", "gpirt_panel_get_L_time",

@@ -583,3 +583,115 @@ cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int
 }
 
 }  // namespace gpirt
+
+// ------------------------------------------------------------------------------------------------------------------------------------------
+// gpirt_chol_device_noalloc (include/gpirt_b200.h): the persistent factorisation for callers that cannot allocate device memory — code under CUDA
+// graph capture, tight serving loops, harnesses that forbid cudaMalloc. No counterpart in the reference.
+// The kernel's scratch (tile version counters and the ordered task list, which the handle-based entry points keep in the sampler's
+// arena or in temporaries of the call) lives in ONE file-scope device array per GPU that has loaded the library, held until the process exits.
+// Every call on a device shares it: the state words are cleared and the task list is rewritten at the start of each call, and calls that overlap
+// on the same GPU (two streams, two host threads) race on it — issue them on one stream, or serialise them.
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
+
+#include "../../include/gpirt_b200.h"
+
+namespace gpirt { int fail_msg(int code, const char* msg); }  // capi.cu: sets gpirt_last_error()
+
+namespace gpirt {
+namespace {
+
+constexpr int NOALLOC_MAX_N = GPIRT_NOALLOC_CHOL_MAX_N;                    // 2048 -> 32 x 32 tiles
+constexpr int NOALLOC_MAX_T = (NOALLOC_MAX_N + TB_ - 1) / TB_;
+constexpr size_t NOALLOC_STATE_BYTES = (((size_t)(4 + NOALLOC_MAX_T * NOALLOC_MAX_T) * sizeof(int)) + 255) & ~(size_t)255;
+constexpr size_t NOALLOC_MAX_TASKS = 6144;                                  // the task list of n = 2048 has 5800 entries (checked at run time)
+constexpr size_t NOALLOC_SCRATCH_BYTES = NOALLOC_STATE_BYTES + NOALLOC_MAX_TASKS * sizeof(uint32_t);  // 28 928 bytes
+
+// In HOST code this name is a stand-in, not a device address: the address the kernels get comes from cudaGetSymbolAddress, once per device.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// number of bulk-list tasks of step k for T tiles per side (the order of chol_plan_tasks)
+__host__ __device__ inline int tasks_of_step(int T, int k) {
+    if (k + 1 >= T) return 0;
+    const int s = T - k - 3 > 0 ? T - k - 3 : 0;   // S(i, k, k) and U(i, k+1, k), i >= k + 3
+    const int r = T - k - 2;                        // columns j >= k + 2: r (r + 1) / 2 tiles, minus (k+2, k+2)
+    return 2 * s + (r > 0 ? r * (r + 1) / 2 - 1 : 0);
+}
+
+// the task list of chol_plan_tasks, written on the device: thread k writes the segment of step k
+__global__ void k_noalloc_plan(uint32_t* tasks, int T) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k + 1 >= T) return;
+    int off = 0;
+    for (int q = 0; q < k; ++q) off += tasks_of_step(T, q);
+    uint32_t* t = tasks + off;
+    for (int i = k + 3; i < T; ++i) *t++ = pack_task(TASK_S, i, k, k);
+    for (int i = k + 3; i < T; ++i) *t++ = pack_task(TASK_U, i, k + 1, k);
+    for (int j = k + 2; j < T; ++j)
+        for (int i = j; i < T; ++i) {
+            if (i == k + 2 && j == k + 2) continue;
+            *t++ = pack_task(TASK_U, i, j, k);
+        }
+}
+
+}  // namespace
+}  // namespace gpirt
+
+extern "C" int gpirt_chol_device_noalloc(int device, double* A_dev, int64_t ld, int64_t n, int32_t* info_dev, void* cuda_stream) {
+    using namespace gpirt;
+    char msg[256];
+    if (!A_dev || !info_dev) return fail_msg(GPIRT_ERR_INVALID, "chol_device_noalloc: NULL device pointer");
+    if (n < 1 || n > NOALLOC_MAX_N) {
+        snprintf(msg, sizeof(msg), "chol_device_noalloc: n = %lld outside 1..%d (the static scratch of this entry point is sized for %d; use gpirt_chol or a sampler handle beyond it)",
+                 (long long)n, NOALLOC_MAX_N, NOALLOC_MAX_N);
+        return fail_msg(GPIRT_ERR_SHAPE, msg);
+    }
+    if (ld < ((n + 1) & ~(int64_t)1) || (ld & 1) || ((uintptr_t)A_dev & 15)) {
+        snprintf(msg, sizeof(msg), "chol_device_noalloc: ld = %lld must be even and >= n rounded up to even (%lld), A 16-byte aligned (columns are moved by 16-byte bulk copies)",
+                 (long long)ld, (long long)((n + 1) & ~(int64_t)1));
+        return fail_msg(GPIRT_ERR_SHAPE, msg);
+    }
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) return fail_msg(GPIRT_ERR_NO_DEVICE, "no CUDA device; gpirt_b200 has no CPU path");
+    if (device < 0 || device >= count || device >= NOALLOC_MAX_DEVICES) return fail_msg(GPIRT_ERR_INVALID, "chol_device_noalloc: device out of range");
+    cudaError_t e = cudaSetDevice(device);
+    unsigned char* scratch = nullptr;
+    if (e == cudaSuccess) {  // set-up, once per device, with that device current: the device address behind the host-side stand-in
+        std::lock_guard<std::mutex> lk(g_noalloc_mu);
+        if (!g_noalloc_ptr[device]) {
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e == cudaSuccess) g_noalloc_ptr[device] = (unsigned char*)p;
+        }
+        scratch = g_noalloc_ptr[device];
+    }
+    if (e != cudaSuccess || !scratch) {
+        snprintf(msg, sizeof(msg), "chol_device_noalloc: cudaGetSymbolAddress / cudaSetDevice: %s", cudaGetErrorString(e));
+        return fail_msg(GPIRT_ERR_CUDA, msg);
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int T = chol_plan_tiles((int)n);
+    int n_tasks = 0;
+    for (int k = 0; k < T; ++k) n_tasks += tasks_of_step(T, k);
+    if ((size_t)n_tasks > NOALLOC_MAX_TASKS) return fail_msg(GPIRT_ERR_SHAPE, "chol_device_noalloc: task list exceeds the static scratch");
+    int* state = (int*)scratch;
+    uint32_t* tasks = (uint32_t*)(scratch + NOALLOC_STATE_BYTES);
+    // what must start at zero: the caller's info word here, the state words inside chol_lower_persistent; the task list is rewritten for this n
+    if ((e = cudaMemsetAsync(info_dev, 0, sizeof(int32_t), st)) == cudaSuccess && T > 1) {
+        k_noalloc_plan<<<1, 64, 0, st>>>(tasks, T);
+        ++g_kernel_launches;
+        e = cudaGetLastError();
+    }
+    static const int ctas = getenv("GPIRT_CHOL_CTAS") ? atoi(getenv("GPIRT_CHOL_CTAS")) : 48;
+    if (e == cudaSuccess) e = chol_lower_persistent(st, A_dev, (int)ld, (int)n, (int*)info_dev, state, tasks, n_tasks, ctas);
+    if (e != cudaSuccess) {
+        snprintf(msg, sizeof(msg), "chol_device_noalloc: %s", cudaGetErrorString(e));
+        return fail_msg(GPIRT_ERR_CUDA, msg);
+    }
+    return GPIRT_OK;
+}

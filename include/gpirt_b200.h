@@ -101,6 +101,17 @@ int gpirt_K_time(int device, const double* x1, int64_t n1, const double* x2, int
 int gpirt_delta_to_threshold(const double* deltas, int C, double* thresholds);   /* host-only bookkeeping, bit-exact */
 int gpirt_threshold_to_delta(const double* thresholds, int C, double* deltas);
 int gpirt_chol(int device, const double* A, int64_t n, double* L);               /* arma::chol(A,"lower") */
+/* NO COUNTERPART IN THE REFERENCE. gpirt_chol's factorisation for callers that cannot allocate
+ * device memory (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): it calls no cudaMalloc / cudaFree or any
+ * allocating routine. DEVICE in, DEVICE out: A_dev is the n x n matrix on `device`, column-major with leading dimension ld (even, >= n rounded up
+ * to even; A_dev 16-byte aligned), lower triangle read; on return of the work queued on `cuda_stream` (a cudaStream_t, NULL = default stream)
+ * the lower triangle holds L, the strict upper triangle zeros, and *info_dev (a device int the call clears first) 0, or the 1-based index of the
+ * failing leading minor, or -1 if the kernel gave up waiting. The call does not synchronise. Limit: n <= GPIRT_NOALLOC_CHOL_MAX_N; beyond it the
+ * call fails with GPIRT_ERR_SHAPE (use gpirt_chol or a sampler handle). The kernel's scratch (tile version counters + task list, 28 928 bytes)
+ * is a static device array that every GPU which loads the library holds until the process exits, and ALL calls on a device share it: it is
+ * cleared / rewritten at the start of each call, so calls that overlap on one GPU (two streams, two host threads) race - keep them on one stream. */
+#define GPIRT_NOALLOC_CHOL_MAX_N 2048
+int gpirt_chol_device_noalloc(int device, double* A_dev, int64_t ld, int64_t n, int32_t* info_dev, void* cuda_stream);
 /* arma::interp1(X, Y.col(j), XI, YI.col(j), "linear") for every column j of Y (src/draw-fstar.cpp:77-82, the inducing points of the constant-IRF
  * f* draw): X sorted, duplicated abscissae dropped keeping the lowest row index, NaN outside [min X, max X]. Y: nx x m, YI: nq x m, column-major. */
 int gpirt_interp1(int device, const double* X, int64_t nx, const double* Y, int64_t m, const double* XI, int64_t nq, double* YI);
