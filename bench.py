@@ -276,16 +276,20 @@ def ours(args):
     inner = S.S if hasattr(S, "S") else S
     ex = {b: inner.exact_evals(b) for b in ("f", "beta", "thr")}
     screened = {b: round(1.0 - float(np.maximum(ex[b][ev[b] > 0] - 1, 0).sum()) / max(1.0, float((ev[b][ev[b] > 0] - 1).sum())), 4) for b in ex}
-    ext = inner.exact_evals("theta")  # theta step: the current state is screened too; an undecided proposal costs two exact evaluations the first time
-    sel = ev["theta"] > 0
-    screened["theta"] = round(1.0 - float(np.maximum(ext[sel] - 1, 0).sum()) / max(1.0, float((ev["theta"][sel] - 1).sum())), 4)
+    items_mode = world > 1 and getattr(S, "theta_shard", "") == "items"
+    if items_mode:  # item-sharded theta step: fp64 partial sums of the local items, no fp32 screen
+        screened["theta"] = None
+    else:
+        ext = inner.exact_evals("theta")  # theta step: the current state is screened too; an undecided proposal costs two exact evaluations the first time
+        sel = ev["theta"] > 0
+        screened["theta"] = round(1.0 - float(np.maximum(ext[sel] - 1, 0).sum()) / max(1.0, float((ev["theta"][sel] - 1).sum())), 4)
     E = {b: float(np.mean(ev[b][ev[b] > 0])) if np.any(ev[b] > 0) else 0.0 for b in ev}
     m_loc, N = M_PER_GPU, 1001
     nm = n * m_loc
     algo = {  # algorithmic bytes (HBM-bound groups) or flops (FP64-tensor groups) per sweep, SURVEY.md 8(d)
-        "ess_f": ("hbm", 25.0 * nm), "ess_theta": ("hbm", E["theta"] * (n / world) * m * 9.0), "ess_beta": ("hbm", 9.0 * nm),
+        "ess_f": ("hbm", 25.0 * nm), "ess_theta": ("hbm", E["theta"] * (n * m_loc if items_mode else (n / world) * m) * 9.0), "ess_beta": ("hbm", 9.0 * nm),
         "ess_thr": ("hbm", 9.0 * nm), "item_ll": ("hbm", 9.0 * nm + 8.0 * (n + 3 * m_loc + (C + 1) * m_loc)), "gather_f": ("hbm", 16.0 * nm),
-        "gen_Z": ("hbm", 8.0 * (n + N) * m_loc), "theta_table": ("hbm", 8.0 * N * m * (C + 1)), "add_mustar": ("hbm", 16.0 * N * m_loc), "add_mustar_push": ("hbm", 8.0 * (world + 1) * N * m_loc), "K_build": ("hbm", 8.0 * (n * n + n * N + N * N)),
+        "gen_Z": ("hbm", 8.0 * (n + N) * m_loc), "theta_table": ("hbm", 8.0 * N * (m_loc if items_mode else m) * (C + 1)), "add_mustar": ("hbm", 16.0 * N * m_loc), "add_mustar_push": ("hbm", 8.0 * (world + 1) * N * m_loc), "K_build": ("hbm", 8.0 * (n * n + n * N + N * N)),
         "gemm_LZ": ("tensor", 1.0 * n * n * m_loc), "gemm_FtW": ("tensor", 2.0 * N * n * m_loc), "gemm_ZLpost": ("tensor", 1.0 * N * N * m_loc),
         "gemm_Kpost": ("tensor", 1.0 * n * N * N), "chol_K": ("tensor", n ** 3 / 3.0), "chol_Kpost": ("tensor", N ** 3 / 3.0),
         "trsm_kstar": ("tensor", 1.0 * n * n * N), "trsm_W": ("tensor", 1.0 * n * n * N),
@@ -336,7 +340,9 @@ def ours(args):
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"C3 synthetic ordinal n={n} x m={m} ({M_PER_GPU} items per GPU), C={C}, 5% missing", "n": n, "m": m, "C": C,
                        "l2": "working set per sweep (f, nu, Z, f*, L, W: >350 MB) exceeds the 126 MB L2; no explicit flush",
-                       "parallelism": f"items sharded over {world} GPU(s), theta step sharded over respondents"},
+                       "parallelism": f"items sharded over {world} GPU(s), theta step " + (
+                           f"sharded by items too: partial log-likelihoods of 16 proposals per unfinished respondent exchanged per round ({getattr(S, 'theta_rounds', 0)} "
+                           "NCCL all-gathers of n x 17 doubles in the last sweep), no f* exchange" if items_mode else "sharded over respondents (f* all-gather)")},
             "gpu_launches": int(launches), "ll_after": ll, "mean_evals": E, "proposals_decided_in_fp32": screened,
             "kernels_note": "per-group device times of a separate pass in the serial order (profiling level 1); the timed pass overlaps the "
                             "theta-only chain (K_build, chol_K, trtri, gemm_tmp, gemm_Kpost, chol_Kpost, gemm_W) with the item kernels on a second stream",

@@ -302,6 +302,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     h->ldn = pad_ld(h->n); h->ldN = pad_ld(NGRID); h->ldy = pad_ld(h->n);
     h->ld_chunk = pad_ld(h->m_chunk); h->ldz = std::max(h->ldn, h->ldN);
     h->ldm = pad_ld((long long)h->world * h->m_chunk);
+    h->ldml = pad_ld(h->m_chunk);
     // regime switch of src/draw-theta.cpp:112,171,206 at horizon 1: CST and RDM share L_i = sqrt(1 + sd^2)
     const double ls = cfg->theta_ls;
     h->theta_regime = (ls >= 3.0 || ls <= 0.1) ? 0 : 1;
@@ -354,6 +355,14 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     };
     want(&h->y_im, (size_t)h->ldy * std::max(h->m_local, 1));
     want(&h->y_rm, (size_t)h->ldm * std::max(h->n_local, 1));
+    if (h->world > 1) {
+        want(&h->y_rl, (size_t)h->ldml * h->n);
+        want(&h->theta_part, (size_t)h->world * h->n * (THETA_BATCH + 1));
+        want(&h->theta_ll0, (size_t)h->n);
+        want(&h->theta_knext, (size_t)h->n);
+        want(&h->theta_nact, 1);
+        want(&h->items_packed, (size_t)h->world * h->m_chunk * (h->C + 5));
+    }
     want(&h->theta, (size_t)h->world * h->n_chunk);
     want(&h->theta_x, (size_t)h->world * h->n_chunk);
     want(&h->beta, 3 * mt);
@@ -524,6 +533,10 @@ static int build_layouts(gpirt_sampler* h, const int8_t* d_full) {
     CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
     CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
     CU(launch_y_layouts(h->stream, d_full, h->n, h->m_total, h->item0, h->m_local, h->y_im, h->ldy, h->resp0, h->n_local, h->y_rm, h->ldm));
+    if (h->y_rl && h->m_local > 0) {  // all respondents' rows over the local items: the local columns as a matrix of their own, row layout only
+        CU(cudaMemsetAsync(h->y_rl, 0, (size_t)h->ldml * h->n, h->stream));
+        CU(launch_y_layouts(h->stream, d_full + (size_t)h->item0 * h->n, h->n, h->m_local, 0, 0, h->y_im, h->ldy, 0, h->n, h->y_rl, h->ldml));
+    }
     h->have_data = true;
     return GPIRT_OK;
 }
@@ -572,6 +585,7 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
     int rc = GPIRT_OK;
     CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
     CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
+    if (h->y_rl) CU(cudaMemsetAsync(h->y_rl, 0, (size_t)h->ldml * h->n, h->stream));
     for (size_t k = 0; k < blocks.size() && rc == GPIRT_OK; ++k) {
         const Block& b = blocks[k];
         if (b.nrows <= 0 || b.ncols <= 0) continue;
@@ -580,8 +594,8 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
         cudaError_t e;
         if (h->world == 1)
             e = launch_y_layouts(h->stream, d_i8, h->n, h->m_total, 0, h->m_total, h->y_im, h->ldy, 0, h->n, h->y_rm, h->ldm);
-        else if (k == 0)  // the block IS the local items: item-major layout only
-            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_local, 0, h->m_local, h->y_im, h->ldy, 0, 0, h->y_rm, h->ldm);
+        else if (k == 0)  // the block IS the local items: item-major layout, and all respondents' rows over these items (item-sharded theta step)
+            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_local, 0, h->m_local, h->y_im, h->ldy, 0, h->n, h->y_rl, h->ldml);
         else              // the block IS the local respondents: respondent-major layout only
             e = launch_y_layouts(h->stream, d_i8, h->n_local, h->m_total, 0, 0, h->y_im, h->ldy, 0, h->n_local, h->y_rm, h->ldm);
         if (e != cudaSuccess) rc = fail(GPIRT_ERR_CUDA, "y layouts: %s", cudaGetErrorString(e));
@@ -620,6 +634,7 @@ int gpirt_copy_data(gpirt_sampler* h, gpirt_sampler* src) {
     CU(cudaStreamSynchronize(src->stream));
     CU(cudaMemcpyAsync(h->y_im, src->y_im, (size_t)h->ldy * std::max(h->m_local, 1), cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaMemcpyAsync(h->y_rm, src->y_rm, (size_t)h->ldm * std::max(h->n_local, 1), cudaMemcpyDeviceToDevice, h->stream));
+    if (h->y_rl && src->y_rl) CU(cudaMemcpyAsync(h->y_rl, src->y_rl, (size_t)h->ldml * h->n, cudaMemcpyDeviceToDevice, h->stream));
     CU(cudaStreamSynchronize(h->stream));
     h->have_data = true;
     return GPIRT_OK;
@@ -1103,6 +1118,18 @@ static int do_draw_fstar(gpirt_sampler* h, const gpirt_streams* s, bool push_to_
     return GPIRT_OK;
 }
 
+static int need_theta_tab(gpirt_sampler* h, size_t bytes) {  // the table of the respondent-sharded and of the item-sharded theta step share one block
+    if (h->theta_tab && h->theta_tab_bytes >= bytes) return GPIRT_OK;
+    if (h->theta_tab) {
+        CU(cudaStreamSynchronize(h->stream));
+        CU(dev_free(h->theta_tab));
+        h->theta_tab = nullptr;
+    }
+    CU(dev_malloc((void**)&h->theta_tab, bytes));
+    h->theta_tab_bytes = bytes;
+    return GPIRT_OK;
+}
+
 // table_only != nullptr: only prepare the per-sweep term table (or decide against it) and report it — the joint step of a panel launches its own kernel
 static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double** table_only = nullptr) {
     ThetaView v{};
@@ -1123,7 +1150,7 @@ static int do_draw_theta(gpirt_sampler* h, const gpirt_streams* s, const double*
     v.table32 = nullptr;
     v.exact_evals = h->exact[GPIRT_BLOCK_THETA];
     if (direct_cost > table_cost && table_bytes <= ((size_t)12 << 30)) {
-        if (!h->theta_tab) CU(dev_malloc((void**)&h->theta_tab, table_bytes));
+        TRY(need_theta_tab(h, table_bytes));
         // The bounds add up over the items (~3e-6 per term): at m = 5000 0.8 % of the proposals stay undecided, at m = 40 000 (8 item shards of C3)
         // 4 %, and an undecided proposal costs two fp64 evaluations of all m items on ONE SM (75 us at m = 40 000) — measured at 8 GPUs the
         // screened step is then slower than the fp64 table (0.85 + 0.92 ms against 1.03 + 0.45 ms), so it is used up to 12 000 items.
@@ -1271,6 +1298,60 @@ int gpirt_peer_wait(gpirt_sampler* h) {
     return GPIRT_OK;
 }
 int gpirt_sweep_phase_theta(gpirt_sampler* h) { ENTER(h); return do_draw_theta(h, nullptr); }
+
+// ---- item-sharded theta step (samplers.cuh ThetaItemsView): begin, then rounds of { partials, exchange THETA_PART, decide } until nobody is active ----
+static ThetaItemsView theta_items_view(gpirt_sampler* h) {
+    ThetaItemsView v{};
+    v.n = h->n; v.m_local = h->m_local; v.C = h->C; v.world = h->world;
+    v.y_rl = h->y_rl; v.ldml = h->ldml; v.table = h->theta_tab; v.theta = h->theta; v.theta_new = h->theta_x;
+    v.theta_prior_sds = h->tps; v.regime = h->theta_regime; v.theta_os = h->cfg.theta_os;
+    v.z = h->theta_z_dev; v.z_stride = h->theta_z_stride; v.us = h->theta_us; v.key = h->key();
+    v.part_mine = h->theta_part + (size_t)h->rank * h->n * (THETA_BATCH + 1); v.part_all = h->theta_part;
+    v.k_next = h->theta_knext; v.ll0 = h->theta_ll0; v.n_active = h->theta_nact;
+    v.evals = h->evals[GPIRT_BLOCK_THETA]; v.margin = h->margin[GPIRT_BLOCK_THETA]; v.flags = h->flags;
+    return v;
+}
+int gpirt_theta_items_begin(gpirt_sampler* h, const gpirt_streams* s) {
+    ENTER(h);
+    if (h->world < 2 || !h->y_rl) return fail(GPIRT_ERR_INVALID, "theta_items: the item-sharded theta step belongs to an item shard (world > 1)");
+    TRY(stage_streams(h, s, h->n, 1, &h->theta_z_dev, &h->theta_z_stride, &h->theta_us));
+    // the term table of the LOCAL items only: f* chunk, beta and thresholds of this rank (every other rank builds its own)
+    const size_t table_bytes = (size_t)NGRID * std::max(h->m_local, 1) * h->C * 8;
+    TRY(need_theta_tab(h, std::max(table_bytes, (size_t)NGRID * h->m_chunk * h->C * 8)));
+    if (h->m_local > 0) {
+        ThetaView t{};
+        t.m_total = h->m_local; t.m_chunk = h->m_local; t.ld_chunk = h->ld_chunk; t.world = 1; t.C = h->C;
+        t.fstar_all = h->fstar + (size_t)h->rank * NGRID * h->ld_chunk; t.chunk_elems = (long long)NGRID * h->ld_chunk;
+        t.beta = h->beta + 3 * (size_t)h->item0;
+        t.thr = (h->thr_theta ? h->thr_theta : h->thr) + (size_t)(h->C + 1) * h->item0;
+        SEC(h, "theta_table", CU(launch_theta_table(h->stream, t, h->theta_tab)));
+    }
+    CU(cudaMemsetAsync(h->theta_knext, 0, (size_t)h->n * 4, h->stream));
+    return GPIRT_OK;
+}
+int gpirt_theta_items_partials(gpirt_sampler* h) {
+    ENTER(h);
+    if (h->world < 2 || !h->theta_tab) return fail(GPIRT_ERR_INVALID, "theta_items_partials: call gpirt_theta_items_begin first");
+    ThetaItemsView v = theta_items_view(h);
+    SEC(h, "ess_theta", CU(launch_theta_partials(h->stream, v)));
+    return GPIRT_OK;
+}
+int gpirt_theta_items_decide(gpirt_sampler* h, int32_t* n_active) {
+    ENTER(h);
+    if (h->world < 2 || !n_active) return fail(GPIRT_ERR_INVALID, "theta_items_decide: bad arguments");
+    ThetaItemsView v = theta_items_view(h);
+    CU(cudaMemsetAsync(h->theta_nact, 0, 4, h->stream));
+    SEC(h, "theta_decide", CU(launch_theta_decide(h->stream, v)));
+    CU(cudaMemcpyAsync(n_active, h->theta_nact, 4, cudaMemcpyDeviceToHost, h->stream));
+    CU(cudaStreamSynchronize(h->stream));  // the caller's loop ends on this count
+    return GPIRT_OK;
+}
+int gpirt_items_pack(gpirt_sampler* h, int unpack) {
+    ENTER(h);
+    if (h->world < 2) return GPIRT_OK;
+    CU(launch_pack_items(h->stream, h->beta, h->thr, h->item_ll, h->C + 1, h->m_chunk, h->rank, h->world, h->items_packed, unpack));
+    return GPIRT_OK;
+}
 int gpirt_sweep_phase_close(gpirt_sampler* h) {
     ENTER(h);
     TRY(commit_theta(h));
@@ -1304,6 +1385,8 @@ int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* 
         case GPIRT_XCHG_THR: *dev_ptr = h->thr; *chunk_bytes = (int64_t)(h->C + 1) * h->m_chunk * 8; break;
         case GPIRT_XCHG_THETA: *dev_ptr = h->theta_x; *chunk_bytes = (int64_t)h->n_chunk * 8; break;
         case GPIRT_XCHG_ITEM_LL: *dev_ptr = h->item_ll; *chunk_bytes = (int64_t)h->m_chunk * 8; break;
+        case GPIRT_XCHG_THETA_PART: *dev_ptr = h->theta_part; *chunk_bytes = (int64_t)h->n * (THETA_BATCH + 1) * 8; break;
+        case GPIRT_XCHG_ITEMS_PACKED: *dev_ptr = h->items_packed; *chunk_bytes = (int64_t)h->m_chunk * (h->C + 5) * 8; break;
         default: return fail(GPIRT_ERR_INVALID, "exchange_buffer: unknown buffer %d", which);
     }
     return GPIRT_OK;

@@ -56,6 +56,14 @@ struct gpirt_sampler {
     bool pending_L = false, pending_W = false, pending_shared = false;  // the main stream has not yet waited for ev_L / ev_W / ev_shared
 
     int8_t *y_im = nullptr, *y_rm = nullptr;
+    // item-sharded theta step (world > 1, samplers.cuh ThetaItemsView): all respondents' rows over the LOCAL items, the partial-sum exchange buffer,
+    // per-respondent round state, and the packed (beta, thresholds, item ll) exchange buffer
+    int8_t* y_rl = nullptr;
+    long long ldml = 0;
+    double *theta_part = nullptr, *theta_ll0 = nullptr, *items_packed = nullptr;
+    int32_t *theta_knext = nullptr, *theta_nact = nullptr;
+    const double* theta_z_dev = nullptr; long long theta_z_stride = 0;  // supplied streams of the current item-sharded theta step (staged at begin)
+    gpirt::UniformSrc theta_us{nullptr, 0};
     double *theta = nullptr, *theta_x = nullptr, *beta = nullptr, *thr = nullptr;
     double *f = nullptr, *nu = nullptr, *zbuf = nullptr, *fstar = nullptr;
     double *L = nullptr, *W = nullptr, *Kpost = nullptr, *tstar = nullptr;
@@ -63,6 +71,7 @@ struct gpirt_sampler {
     int solver = 1;  // 0: blocked substitution TRSM (backward stable), 1: explicit L^-1 by parallel block inversion + GEMMs
     double* mu_rows = nullptr;    // optional per-row means of the f / threshold blocks (gpirt_set_mean_rows), [ldn][m_local]
     double* theta_tab = nullptr;  // [NGRID][m_total][C] per-sweep table of theta-step terms (allocated on first use)
+    size_t theta_tab_bytes = 0;
     double *sds = nullptr, *tps = nullptr, *item_ll = nullptr, *total_ll = nullptr;
     int32_t* evals[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     int32_t* exact[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // per unit: evaluations that ran in fp64 (screening diagnostics)

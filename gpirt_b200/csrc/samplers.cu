@@ -943,3 +943,187 @@ cudaError_t launch_y_layouts(cudaStream_t st, const int8_t* y_full, int n, int m
 }
 
 }  // namespace gpirt
+
+namespace gpirt {
+
+// ------------------------------------------------------------------------------------------------
+// Item-sharded theta step (samplers.cuh, ThetaItemsView).
+// One ESS unit's proposal sequence under rejections: the arithmetic of k_ess_theta, operation for operation (src/draw-theta.cpp:38-62).
+struct ThetaWalk {
+    double th0, nu, log_u, eps, eps_min, eps_max;
+    uint32_t k;      // uniforms consumed
+    int overrun;
+    __device__ __forceinline__ void init(const ThetaItemsView& v, int i) {
+        double Li;
+        if (v.regime == 0) {
+            const double sd = v.theta_prior_sds[2 * (size_t)i];
+            Li = sqrt(__dadd_rn(1.0, __dmul_rn(sd, sd)));
+        } else {
+            Li = sqrt(__dadd_rn(__dmul_rn(v.theta_os, v.theta_os), 1e-6));
+        }
+        const double z = v.z ? v.z[(size_t)i * v.z_stride] : philox_normal(v.key, ST_THETA_Z, i, 0);
+        nu = __dmul_rn(Li, z);
+        th0 = v.theta[i];
+        overrun = 0;
+        k = 0;
+        log_u = log(v.us.get(v.key, ST_THETA_U, i, k++, &overrun));
+        eps_min = 0.0; eps_max = TWO_PI_R;
+        eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+        eps_min = __dsub_rn(eps, TWO_PI_R);
+    }
+    __device__ __forceinline__ double proposal() const {
+        const double raw = __dadd_rn(__dmul_rn(th0, cos(eps)), __dmul_rn(nu, sin(eps)));
+        return fmax(-5.0, fmin(5.0, raw));
+    }
+    __device__ __forceinline__ void reject(const ThetaItemsView& v, int i) {
+        if (eps < 0.0) eps_min = eps; else eps_max = eps;
+        eps = __dadd_rn(eps_min, __dmul_rn(__dsub_rn(eps_max, eps_min), v.us.get(v.key, ST_THETA_U, i, k++, &overrun)));
+    }
+};
+
+// One CTA per respondent: partial log-likelihoods over the local items of the current state and of the next THETA_BATCH proposals. The item loop is
+// the outer one, so a thread keeps THETA_BATCH + 1 independent table gathers in flight per item instead of one evaluation after the other.
+__global__ void __launch_bounds__(256) k_theta_partials(ThetaItemsView v) {
+    constexpr int S = THETA_BATCH + 1, T = 256;
+    __shared__ int s_idx[S];
+    __shared__ double s_red[S][T / 32];
+    extern __shared__ __align__(16) int8_t s_yl[];
+    const int i = blockIdx.x, tid = threadIdx.x;
+    const int k0 = v.k_next[i];
+    if (k0 < 0) return;  // finished in an earlier round
+    if (tid == 0) {
+        ThetaWalk w;
+        w.init(v, i);
+        for (int q = 0; q < k0; ++q) w.reject(v, i);
+        s_idx[0] = grid_index(w.th0);
+        for (int b = 1; b < S; ++b) {
+            s_idx[b] = grid_index(w.proposal());
+            w.reject(v, i);  // a supplied stream may run dry here for proposals no decision will ever reach: only k_theta_decide reports an overrun
+        }
+    }
+    const int m = v.m_local, C = v.C;
+    const int8_t* yrow = v.y_rl + (size_t)i * v.ldml;
+    const bool y_smem = (size_t)((m + 15) / 16 * 16) <= (size_t)24 << 10;
+    if (y_smem) {
+        const int4* src = reinterpret_cast<const int4*>(yrow);
+        int4* dst = reinterpret_cast<int4*>(s_yl);
+        for (int q = tid; q < (m + 15) / 16; q += T) dst[q] = src[q];
+        yrow = s_yl;
+    }
+    __syncthreads();
+    int idx[S];
+#pragma unroll
+    for (int b = 0; b < S; ++b) idx[b] = s_idx[b];
+    const int b_first = k0 == 0 ? 0 : 1;  // the current state is scored in the first round only
+    double acc[S];
+#pragma unroll
+    for (int b = 0; b < S; ++b) acc[b] = 0.0;
+    const size_t row = (size_t)m * C;
+    for (int J = tid; J < m; J += T) {
+        const int y = yrow[J];
+        if (y == 0) continue;
+        const double* base = v.table + (size_t)J * C + (y - 1);
+#pragma unroll
+        for (int b = 0; b < S; ++b)
+            if (b >= b_first) acc[b] += base[(size_t)idx[b] * row];
+    }
+    const int lane = tid & 31, warp = tid >> 5;
+#pragma unroll
+    for (int b = 0; b < S; ++b) {
+        const double w = warp_sum(acc[b]);
+        if (lane == 0) s_red[b][warp] = w;
+    }
+    __syncthreads();
+    if (tid < S) {
+        double t = 0.0;
+#pragma unroll
+        for (int w = 0; w < T / 32; ++w) t += s_red[tid][w];
+        v.part_mine[(size_t)i * S + tid] = t;
+    }
+}
+
+cudaError_t launch_theta_partials(cudaStream_t st, const ThetaItemsView& v) {
+    if (v.n <= 0) return cudaSuccess;
+    const size_t row_bytes = ((size_t)v.m_local + 15) / 16 * 16;
+    const size_t smem = row_bytes <= ((size_t)24 << 10) ? row_bytes : 0;
+    k_theta_partials<<<v.n, 256, smem, st>>>(v);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+// One thread per respondent, the same on every rank: partials added in rank order, then the reference's accept test proposal by proposal.
+__global__ void __launch_bounds__(128) k_theta_decide(ThetaItemsView v) {
+    constexpr int S = THETA_BATCH + 1;
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= v.n) return;
+    const int k0 = v.k_next[i];
+    if (k0 < 0) return;
+    auto total = [&](int slot) {
+        double t = 0.0;
+        for (int r = 0; r < v.world; ++r) t += v.part_all[((size_t)r * v.n + i) * S + slot];
+        return t;
+    };
+    ThetaWalk w;
+    w.init(v, i);
+    for (int q = 0; q < k0; ++q) w.reject(v, i);
+    if (k0 == 0) { v.ll0[i] = total(0); v.margin[i] = CUDART_INF; }
+    const double log_y = __dadd_rn(w.log_u, v.ll0[i]);
+    double margin = v.margin[i];
+    double raw = w.th0;
+    int done = 0, over = w.overrun;
+    int kk = k0;
+    for (int b = 1; b < S && !over; ++b) {
+        raw = w.proposal();
+        const double llp = total(b);
+        ++kk;
+        margin = fmin(margin, fabs(llp - log_y));
+        if (llp > log_y) { done = 1; break; }
+        if (kk >= ESS_MAX_PROPOSALS) { done = 2; break; }
+        w.reject(v, i);
+        over = w.overrun;
+    }
+    v.margin[i] = margin;
+    if (over) { atomicExch(&v.flags->overrun, 1); done = 3; }
+    if (done) {
+        v.theta_new[i] = grid_value(grid_index(raw));  // snapped to the grid, src/draw-theta.cpp:165-169 (on a stall: the last proposal, as k_ess_theta)
+        v.evals[i] = 1 + kk;
+        v.k_next[i] = -1;
+        if (done == 2) atomicExch(&v.flags->stalled, 1);
+    } else {
+        v.k_next[i] = kk;
+        atomicAdd(v.n_active, 1);
+    }
+}
+
+cudaError_t launch_theta_decide(cudaStream_t st, const ThetaItemsView& v) {
+    if (v.n <= 0) return cudaSuccess;
+    k_theta_decide<<<(v.n + 127) / 128, 128, 0, st>>>(v);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+// (beta 3 x m_chunk | thresholds (C+1) x m_chunk | item ll m_chunk) of every rank's chunk <-> packed[world][m_chunk * (C1 + 4)]; pack touches this
+// rank's chunk only, unpack every other rank's
+__global__ void k_pack_items(double* __restrict__ beta, double* __restrict__ thr, double* __restrict__ item_ll, int C1, int m_chunk, int rank, int world,
+                             double* __restrict__ packed, int unpack) {
+    const int per = m_chunk * (C1 + 4);
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long long)per * world) return;
+    const int r = (int)(e / per), q = (int)(e - (long long)r * per);
+    if (unpack ? r == rank : r != rank) return;
+    double* p;
+    if (q < 3 * m_chunk) p = beta + (size_t)r * 3 * m_chunk + q;
+    else if (q < (3 + C1) * m_chunk) p = thr + (size_t)r * C1 * m_chunk + (q - 3 * m_chunk);
+    else p = item_ll + (size_t)r * m_chunk + (q - (3 + C1) * m_chunk);
+    if (unpack) *p = packed[e]; else packed[e] = *p;
+}
+cudaError_t launch_pack_items(cudaStream_t st, const double* beta, const double* thr, const double* item_ll, int C1, int m_chunk, int rank, int world,
+                              double* packed, int unpack) {
+    const long long total = (long long)m_chunk * (C1 + 4) * world;
+    k_pack_items<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(const_cast<double*>(beta), const_cast<double*>(thr), const_cast<double*>(item_ll), C1, m_chunk,
+                                                                rank, world, packed, unpack);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+}  // namespace gpirt

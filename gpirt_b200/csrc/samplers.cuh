@@ -113,6 +113,41 @@ struct ThetaPanelView {
 };
 cudaError_t launch_ess_theta_panel(cudaStream_t st, const ThetaPanelView& v);
 
+// Item-sharded theta step (world > 1; draw_theta, src/draw-theta.cpp:26-84,112-170, with the per-respondent loop distributed over the ranks BY ITEMS):
+// every rank keeps all n respondents and scores them against its own items only. The shrink sequence of an ESS unit under rejections is a function
+// of its uniforms alone (the bracket shrinks to the rejected angle, no likelihood value enters), so a round evaluates the next THETA_BATCH
+// proposals of every unfinished respondent at once: k_theta_partials writes this rank's partial log-likelihoods (slot 0: the current state,
+// slots 1..THETA_BATCH: the proposals), the ranks exchange them (n x (THETA_BATCH + 1) doubles each), and k_theta_decide — the same arithmetic on
+// every rank — adds the partials in rank order and takes the reference's decisions `ll' > log_y` proposal by proposal. No f* exchange, no
+// replicated term table; the decisions are those of the single-GPU kernel unless a margin |ll' - log_y| is below fp64 summation noise (the
+// recorded minimum margin tells).
+constexpr int THETA_BATCH = 16;
+struct ThetaItemsView {
+    int n, m_local, C, world;
+    const int8_t* y_rl;       // respondent-major rows over the LOCAL items: y_rl[i*ldml + j]
+    long long ldml;
+    const double* table;      // [NGRID][m_local][C] cell terms of the local items (k_theta_table)
+    const double* theta;      // n (current)
+    double* theta_new;        // n
+    const double* theta_prior_sds;
+    int regime; double theta_os;
+    const double* z; long long z_stride;
+    UniformSrc us;
+    RngKey key;
+    double* part_mine;        // this rank's partials [n][THETA_BATCH + 1]                                (k_theta_partials writes)
+    const double* part_all;   // every rank's partials [world][n][THETA_BATCH + 1], chunk r = rank r      (k_theta_decide reads)
+    int32_t* k_next;          // per respondent: proposals already decided (all rejected); -1 = finished
+    double* ll0;              // per respondent: log-likelihood of the current state (sum over ranks, set in the first round)
+    int32_t* n_active;        // device counter: respondents still unfinished after this round
+    int32_t* evals; double* margin;
+    DevFlags* flags;
+};
+cudaError_t launch_theta_partials(cudaStream_t st, const ThetaItemsView& v);
+cudaError_t launch_theta_decide(cudaStream_t st, const ThetaItemsView& v);
+// packs / unpacks this rank's chunk of (beta, thresholds, per-item ll) into one exchange buffer: [world][m_chunk * (3 + C + 1 + 1)] doubles
+cudaError_t launch_pack_items(cudaStream_t st, const double* beta, const double* thr, const double* item_ll, int C1, int m_chunk, int rank, int world,
+                              double* packed, int unpack);
+
 enum ItemBlock { IB_F = 0, IB_BETA = 1, IB_THR = 2 };
 
 cudaError_t launch_gen_normals(cudaStream_t st, double* out, int ld, int rows, int cols, RngKey key, uint32_t stream, uint32_t unit0);

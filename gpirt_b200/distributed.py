@@ -4,16 +4,19 @@ for the exchanges, every kernel and buffer owned by the rank's gpirt_sampler han
 Given theta, the items are conditionally independent — the reference's `omp parallel for` over j
 (src/draw-f.cpp:68, src/draw-fstar.cpp:44, src/draw-beta.cpp:64, src/draw_threshold.cpp:210) — so rank r owns the
 contiguous item block [r*m_chunk, (r+1)*m_chunk). The theta step is independent over respondents but needs every
-item (src/draw-theta.cpp:123), so it is sharded by respondents and fed by one all-gather of the f* shards:
+item (src/draw-theta.cpp:123). Default ("items"): it stays sharded BY ITEMS too — every rank scores all respondents
+against its own items and the ranks exchange partial log-likelihoods, 16 proposals of every unfinished respondent per
+round (include/gpirt_b200.h, gpirt_theta_items_*):
 
     phase_items   draw_f, draw_fstar on the local items                     (no communication)
-    all_gather    f* chunks (8*1001*m bytes in total), beta, thresholds
-    phase_theta   theta ESS for the local respondents over the whole table
-    all_gather    theta (8*n bytes)
+    theta rounds  { partials over the local items ; all_gather n x 17 doubles per rank ; decide (same on every rank) }
     phase_close   f <- f* gather, draw_beta, K + Cholesky (replicated), draw_threshold, per-item ll
-    all_gather    beta, thresholds, per-item ll  (tiny)
+    all_gather    beta, thresholds, per-item ll packed into one buffer
 
-Random streams are keyed by GLOBAL item / respondent index, so a chain is bit-identical for any world size.
+GPIRT_THETA_SHARD=respondents selects the first scheme of round 1: the theta step sharded by respondents, fed by an all-gather of
+the f* shards (8*1001*m bytes per sweep) and a term table over ALL items on every rank.
+
+Random streams are keyed by GLOBAL item / respondent index, so a chain is the same for any world size.
 """
 import os
 
@@ -56,7 +59,7 @@ class _DevBuf:
 class ShardedSampler:
     """One rank's shard of a chain. Every rank passes the same full-size y / state arrays; the handle keeps its part."""
 
-    def __init__(self, n, m, Ccat, *, rank, world, device, group=None, **kw):
+    def __init__(self, n, m, Ccat, *, rank, world, device, group=None, theta_shard=None, **kw):
         import torch
 
         self.rank, self.world, self.group = rank, world, group
@@ -71,7 +74,16 @@ class ShardedSampler:
         # last kernel of the f* draw stores into all of them over NVLink (gpirt_ipc_*, include/gpirt_b200.h). Measured at 8 x B200 on C3 blocks
         # (profiles/r01_scaling.txt): the push costs 0.41 ms (280 MB per GPU at 680 GB/s, the NVLink egress floor) against ~0.45 ms for NCCL,
         # 6.80 vs 6.86 ms per sweep — but mapping 7 peers costs ~200 ms per handle, which a 20-sweep gpirtMCMC call never earns back, hence opt-in.
-        self.p2p = world > 1 and os.environ.get("GPIRT_FSTAR_EXCHANGE", "nccl") == "p2p"
+        self.theta_shard = os.environ.get("GPIRT_THETA_SHARD", "items") if theta_shard is None else theta_shard
+        if self.theta_shard not in ("items", "respondents"):
+            raise ValueError(f"theta_shard {self.theta_shard!r}: 'items' or 'respondents'")
+        if world == 1:
+            self.theta_shard = "respondents"  # one rank: the ordinary kernels
+        for name in (("theta_part", "items_packed") if world > 1 else ()):
+            ptr, chunk_bytes = self.S.exchange_buffer(name)
+            self._bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * world), device=f"cuda:{device}")
+        self.theta_rounds = 0  # exchange rounds of the last item-sharded theta step
+        self.p2p = world > 1 and self.theta_shard == "respondents" and os.environ.get("GPIRT_FSTAR_EXCHANGE", "nccl") == "p2p"
         if self.p2p:
             import torch.distributed as dist
 
@@ -85,19 +97,38 @@ class ShardedSampler:
     def _gather(self, name):
         all_gather_chunks(self._bufs[name], self.rank, self.world, self.group)
 
-    def sweep(self, k=1):
-        for _ in range(k):
-            self.S.phase_items()
+    def draw_theta(self, z=None, u=None):
+        """The theta step alone (parity tests): item-sharded rounds, or the respondent-sharded kernel + theta exchange."""
+        if self.theta_shard == "items":
+            self.S.theta_items_begin(z=z, u=u)
+            self.theta_rounds = 0
+            while True:
+                self.S.theta_items_partials()
+                self._gather("theta_part")
+                self.theta_rounds += 1
+                if self.S.theta_items_decide() == 0:
+                    break
+        else:
             if self.p2p:
                 self.S.peer_wait()
             else:
                 self._gather("fstar")
             self.S.phase_theta()
             self._gather("theta")
+
+    def sweep(self, k=1):
+        for _ in range(k):
+            self.S.phase_items()
+            self.draw_theta()
             self.S.phase_close()
-            self._gather("beta")
-            self._gather("thr")
-            self._gather("item_ll")
+            if self.theta_shard == "items":
+                self.S.items_pack()
+                self._gather("items_packed")
+                self.S.items_pack(unpack=True)
+            else:
+                self._gather("beta")
+                self._gather("thr")
+                self._gather("item_ll")
 
     def total_ll(self):
         return self.S.total_ll()
@@ -156,3 +187,117 @@ def gpirtMCMC_sharded(data, sample_iterations, burn_iterations, THIN=1, *, rank,
         S.close()
     return dict(theta=out["theta"], beta=[out["beta"][..., s] for s in range(n_samples)],
                 threshold=[out["threshold"][..., s] for s in range(n_samples)], ll=out["ll"], f=None, fstar=None)
+
+
+class LocalShards:
+    """The same item-sharded chain driven from ONE process: `len(devices)` shards, shard r on devices[r] (the same device may appear
+    several times), the exchanges done as device-to-device copies of chunk r from shard r into every other shard's buffer (peer copies
+    between different GPUs). What the torch.distributed driver does with NCCL, without a process group: for a host application that is one
+    process, and for testing the sharded logic on a single GPU. Same calls and same bits as ShardedSampler on `world` ranks."""
+
+    def __init__(self, n, m, Ccat, *, devices, theta_shard="items", **kw):
+        import torch
+
+        self.world = len(devices)
+        if self.world < 2:
+            raise ValueError("LocalShards needs at least two shards; use Sampler for one")
+        self.devices, self.theta_shard = list(devices), theta_shard
+        self.S, self._bufs = [], []
+        for r, dev in enumerate(self.devices):
+            S = Sampler(n, m, Ccat, rank=r, world=self.world, device=dev, **kw)
+            S.set_stream(torch.cuda.current_stream(dev).cuda_stream)
+            bufs = {}
+            for name in ("fstar", "beta", "thr", "theta", "item_ll", "theta_part", "items_packed"):
+                ptr, chunk_bytes = S.exchange_buffer(name)
+                bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * self.world), device=f"cuda:{dev}")
+            self.S.append(S)
+            self._bufs.append(bufs)
+        self.theta_rounds = 0
+
+    def _gather(self, name):
+        chunk = self._bufs[0][name].numel() // self.world
+        for r in range(self.world):  # chunk r is owned by shard r
+            src = self._bufs[r][name][r * chunk:(r + 1) * chunk]
+            for q in range(self.world):
+                if q != r:
+                    self._bufs[q][name][r * chunk:(r + 1) * chunk].copy_(src, non_blocking=True)
+
+    def _each(self, method, *a, **kw):
+        return [getattr(S, method)(*a, **kw) for S in self.S]
+
+    def draw_theta(self, z=None, u=None):
+        if self.theta_shard == "items":
+            self._each("theta_items_begin", z=z, u=u)
+            self.theta_rounds = 0
+            while True:
+                self._each("theta_items_partials")
+                self._gather("theta_part")
+                self.theta_rounds += 1
+                active = self._each("theta_items_decide")
+                assert len(set(active)) == 1, f"the shards disagree on the unfinished respondents: {active}"
+                if active[0] == 0:
+                    break
+        else:
+            self._gather("fstar")
+            self._each("phase_theta")
+            self._gather("theta")
+
+    def sweep(self, k=1):
+        for _ in range(k):
+            self._each("phase_items")
+            self.draw_theta()
+            self._each("phase_close")
+            if self.theta_shard == "items":
+                self._each("items_pack")
+                self._gather("items_packed")
+                self._each("items_pack", unpack=True)
+            else:
+                for name in ("beta", "thr", "item_ll"):
+                    self._gather(name)
+
+    # every shard takes the same full-size arrays and keeps its part
+    def set_data(self, y):
+        self._each("set_data", y)
+
+    def set_priors(self, *a, **kw):
+        self._each("set_priors", *a, **kw)
+
+    def set_state(self, **kw):
+        self._each("set_state", **kw)
+
+    def set_iter(self, it):
+        self._each("set_iter", it)
+
+    def init_draw(self, **kw):
+        self._each("init_draw", **kw)
+
+    def sync(self):
+        self._each("sync")
+
+    def get_state(self, **kw):
+        """theta / beta / thresholds are complete on every shard after a sweep (shard 0's are returned); f is assembled from the shards' columns."""
+        kw.setdefault("fstar", False)
+        st = self.S[0].get_state(**kw)
+        if kw.get("f", True):
+            import ctypes as C
+
+            from ._lib import check
+
+            for S in self.S[1:]:  # gpirt_get_state writes the local items' columns only
+                check(S._L.gpirt_get_state(S._h, None, None, st["f"].ctypes.data_as(C.c_void_p), None, None))
+        return st
+
+    def diag(self, block):
+        ev, mg = self.S[0].diag(block)
+        if block != "theta" or self.theta_shard != "items":  # per-unit diagnostics live on the shard that owns the unit
+            chunk = self.S[0].n_chunk if block == "theta" else self.S[0].m_chunk
+            for r, S in enumerate(self.S[1:], start=1):
+                e, g = S.diag(block)
+                ev[r * chunk:(r + 1) * chunk], mg[r * chunk:(r + 1) * chunk] = e[r * chunk:(r + 1) * chunk], g[r * chunk:(r + 1) * chunk]
+        return ev, mg
+
+    def total_ll(self):
+        return self.S[0].total_ll()
+
+    def close(self):
+        self._each("close")

@@ -299,6 +299,24 @@ class Sampler:
     def phase_close(self):
         check(self._L.gpirt_sweep_phase_close(self._h))
 
+    # ---- item-sharded theta step (include/gpirt_b200.h): begin, then rounds of partials / exchange / decide ----
+    def theta_items_begin(self, z=None, u=None):
+        s, keep = _streams(z, u)
+        check(self._L.gpirt_theta_items_begin(self._h, C.byref(s) if s is not None else None))
+        if keep:
+            self.sync()
+
+    def theta_items_partials(self):
+        check(self._L.gpirt_theta_items_partials(self._h))
+
+    def theta_items_decide(self):
+        n_active = C.c_int32()
+        check(self._L.gpirt_theta_items_decide(self._h, C.byref(n_active)))
+        return n_active.value
+
+    def items_pack(self, unpack=False):
+        check(self._L.gpirt_items_pack(self._h, int(unpack)))
+
     # ---- f* exchange through NVLink peer memory (item shards, one process per GPU) ----
     def ipc_export(self):
         buf, o1, o2 = (C.c_ubyte * 64)(), C.c_int64(), C.c_int64()

@@ -201,7 +201,25 @@ int gpirt_sweep(gpirt_sampler* h, int n_sweeps);             /* world == 1: whol
 int gpirt_sweep_phase_items(gpirt_sampler* h);               /* draw_f, draw_fstar on the local items */
 int gpirt_sweep_phase_theta(gpirt_sampler* h);               /* theta ESS for the local respondents */
 int gpirt_sweep_phase_close(gpirt_sampler* h);               /* gather, beta, mu, cholesky, thresholds, item ll */
-typedef enum { GPIRT_XCHG_FSTAR = 0, GPIRT_XCHG_BETA = 1, GPIRT_XCHG_THR = 2, GPIRT_XCHG_THETA = 3, GPIRT_XCHG_ITEM_LL = 4 } gpirt_xchg;
+typedef enum { GPIRT_XCHG_FSTAR = 0, GPIRT_XCHG_BETA = 1, GPIRT_XCHG_THR = 2, GPIRT_XCHG_THETA = 3, GPIRT_XCHG_ITEM_LL = 4,
+               GPIRT_XCHG_THETA_PART = 5, GPIRT_XCHG_ITEMS_PACKED = 6 } gpirt_xchg;
+/* Item-sharded theta step (the default of the sharded drivers): draw_theta's per-respondent loop (src/draw-theta.cpp:121-170) distributed over the
+ * ranks BY ITEMS instead of by respondents. Every rank keeps all n respondents and scores them against its own items (its own term table of
+ * NGRID x m_local x C cells); a round evaluates the next 16 proposals of every unfinished respondent at once - the shrink sequence of an ESS unit
+ * under rejections depends on its uniforms only (src/draw-theta.cpp:72-80) - and the ranks exchange n x 17 partial log-likelihoods per round
+ * (GPIRT_XCHG_THETA_PART, in-place all-gather) instead of the f* table. Sequence per sweep:
+ *     gpirt_theta_items_begin(h, streams or NULL);
+ *     do { gpirt_theta_items_partials(h); <all-gather GPIRT_XCHG_THETA_PART>; gpirt_theta_items_decide(h, &n_active); } while (n_active > 0);
+ *     gpirt_sweep_phase_close(h);   (the new theta is complete on every rank: no theta exchange)
+ * gpirt_theta_items_decide synchronises the stream (the loop ends on its count) and is the same computation on every rank: partials added in rank
+ * order, then the reference's strict `ll' > log_y` proposal by proposal. The decisions are the single-GPU kernel's unless a margin falls below fp64
+ * summation noise; gpirt_get_diag reports the minimum margin per respondent.
+ * gpirt_items_pack(h, 0) / <all-gather GPIRT_XCHG_ITEMS_PACKED> / gpirt_items_pack(h, 1): beta, thresholds and the per-item log-likelihood terms
+ * of all ranks in ONE exchange instead of three. */
+int gpirt_theta_items_begin(gpirt_sampler* h, const gpirt_streams* s);
+int gpirt_theta_items_partials(gpirt_sampler* h);
+int gpirt_theta_items_decide(gpirt_sampler* h, int32_t* n_active);
+int gpirt_items_pack(gpirt_sampler* h, int unpack);
 /* device pointer of the all-gather buffer `which`; it holds `world` equal chunks of chunk_bytes, chunk r owned by rank r */
 int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
 int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */

@@ -59,14 +59,17 @@ def _gpus():
     return _lib.lib().gpirt_device_count()
 
 
-@pytest.mark.parametrize("exchange", ["p2p", "nccl"])  # f* chunks pushed through NVLink peer memory by the producing kernel / NCCL all-gather
+# items: the theta step sharded by items, partial sums exchanged round by round (default); respondents-p2p / respondents-nccl: the theta step sharded
+# by respondents, f* chunks pushed through NVLink peer memory by the producing kernel / NCCL all-gather
+@pytest.mark.parametrize("exchange", ["items", "p2p", "nccl"])
 def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path, exchange):
     if _gpus() < 2:
         pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
     s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
-    env = dict(os.environ, GPIRT_ROOT=ROOT, GPIRT_FSTAR_EXCHANGE=exchange)
+    env = dict(os.environ, GPIRT_ROOT=ROOT, GPIRT_FSTAR_EXCHANGE=exchange if exchange != "items" else "nccl",
+               GPIRT_THETA_SHARD="items" if exchange == "items" else "respondents")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                         "--master-port", str(port), str(script)], env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
