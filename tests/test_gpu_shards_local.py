@@ -30,7 +30,9 @@ def test_item_sharded_theta_step_takes_the_oracles_decisions(n, m, C, world):
     O.set_state(theta=P["theta0"], beta=beta, f=f0, thr=P["thr0"], fstar=fstar)
     O.compute_mu()
     z = np.asfortranarray(rng.standard_normal((1, n)))
-    u = uniform_streams(rng, n, stride=96)
+    u = uniform_streams(rng, n, stride=256)
+    if m > 1000:
+        u[1:, :] = 0.9  # brackets that shrink by a tenth per rejection: up to 40 proposals per respondent, i.e. three exchange rounds
     G.draw_theta(z=z, u=u)
     O.draw_theta(orc.supplied(z=z, u=u))
     ev_o, mg_o, over = O.diag("theta")
