@@ -26,6 +26,18 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_RESP, M_PER_GPU, C_CAT = 2000, 5000, 5
+
+
+def workload(config, gpus):
+    """BASELINE.json configs[2] (c3: the configuration the metric is quoted on, weak-scaled by items: 5000 items per GPU) and configs[3]
+    (c4: n = 10 000 x m = 50 000, C = 7, one chain item-sharded over the GPUs: strong scaling)."""
+    if config == "c4":
+        n, m, C = 10000, 50000, 7
+        return dict(name="c4", n=n, m=m, m_loc=(m + gpus - 1) // gpus, C=C, seed=20261104 + 4, scaling="strong", blocks=1, metric="mcmc_sweeps_per_sec_c4",
+                    text=f"C4 synthetic ordinal n={n} x m={m}, C={C}, 5% missing, one chain item-sharded over {gpus} GPU(s) ({(m + gpus - 1) // gpus} items per GPU)")
+    n, m, C = N_RESP, M_PER_GPU * gpus, C_CAT
+    return dict(name="c3", n=n, m=m, m_loc=M_PER_GPU, C=C, seed=20261104 + 3, scaling="weak", blocks=gpus, metric="mcmc_sweeps_per_sec_c3_blocks",
+                text=f"C3 synthetic ordinal n={n} x m={m} ({M_PER_GPU} items per GPU), C={C}, 5% missing")
 FP64_DMMA_PEAK_FALLBACK = 37.1  # profiles/r01_microbench_fp64.txt; used only if the in-run microbenchmark (gpirt_debug_fp64_peak) fails
 
 
@@ -70,6 +82,19 @@ class ClockSampler:
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = sorted({names[k] for r in self.rows if len(r) >= 6 for k in range(4) if r[2 + k].lower().startswith("active")})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def host_responses(torch, y_i8, pinned=True):
+    """The responses as the reference holds them — n x m doubles, NaN = missing, column-major — in pinned (or, for the 4 GB of config 4, pageable)
+    host memory, filled in column slabs so that no second full-size temporary exists."""
+    n, m = y_i8.shape
+    buf = torch.empty((m, n), dtype=torch.float64, pin_memory=True).numpy() if pinned else np.empty((m, n))
+    y_host = buf.T
+    step = max(1, (1 << 25) // max(n, 1))
+    for j0 in range(0, m, step):
+        blk = y_i8[:, j0:j0 + step]
+        y_host[:, j0:j0 + step] = np.where(blk == 0, np.nan, blk.astype(np.float64))
+    return y_host
 
 
 def synth(n, m, C, seed):
@@ -132,7 +157,7 @@ def cpu_sweeps(n, m, C, seed, *, faithful, warm, max_timed, min_timed, budget_s,
     return dict(variant=name, value=1.0 / mean, ms_per_step=1e3 * mean, steps=len(times), warmup=warm, threads=O.num_threads(), cores=os.cpu_count(),
                 blas=os.path.basename(blas_path) if blas_path else None, sweep_s=[round(t, 3) for t in times], warm_s=round(t_warm, 3),
                 shared_s=round(fixed, 3), items_s=round(items, 3),
-                sample=f"{len(times)} whole sweep(s) over ALL {m} items x {n} respondents ({name}, {O.num_threads()} threads) after {warm} warm-up sweep(s) from {start}: "
+                sample=f"{len(times)} whole sweep(s) over all {m} items x {n} respondents of the problem given ({name}, {O.num_threads()} threads) after {warm} warm-up sweep(s) from {start}: "
                        f"{mean:.2f} s/sweep = {fixed:.2f} s shared by all items (chol(K), k* solves, chol(K_post)) + {items:.2f} s per-item / per-respondent work; measured, not extrapolated")
 
 
@@ -143,6 +168,8 @@ def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    if args.config == "c4":
+        return reference_arm_c4(args)
     m_full = M_PER_GPU * args.gpus
     main = cpu_sweeps(N_RESP, M_PER_GPU, C_CAT, 20261104 + 3, faithful=1, warm=1, max_timed=max(1, args.steps), min_timed=min(3, max(1, args.steps)),
                       budget_s=args.ref_budget, blas=True)
@@ -165,6 +192,32 @@ def reference_arm(args):
                              "Cholesky (same arithmetic) and is the denominator to use for a speed-up that is not inflated by a reference inefficiency",
             "e2e": {"value": value, "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
+
+
+def reference_arm_c4(args):
+    """Config 4 on the CPU: a whole sweep of 10 000 x 50 000 is out of reach (the faithful sweep copies 8 TB of tables per sweep), so
+    the first 64 items are swept with all 10 000 respondents; the oracle clocks the work shared by all items (chol(K) at n = 10 000, the k* solves,
+    chol(K_post)) apart from the per-item / per-respondent work, which is linear in m: value = 1 / (shared + items * 50000 / 64). EXTRAPOLATED."""
+    W = workload("c4", args.gpus)
+    m_sub = 64
+    out = {}
+    for faithful in (1, 0):
+        r = cpu_sweeps(W["n"], m_sub, W["C"], W["seed"], faithful=faithful, warm=1, max_timed=2, min_timed=1, budget_s=120.0, blas=True)
+        t_full = r["shared_s"] + r["items_s"] * W["m"] / m_sub
+        out[r["variant"]] = dict(value=1.0 / t_full, ms_per_step=1e3 * t_full, steps=r["steps"], warmup=r["warmup"], threads=r["threads"], blas=r["blas"],
+                                 sample_sweep_s=r["sweep_s"], shared_s=r["shared_s"], items_s_on_sample=r["items_s"], m_sample=m_sub)
+    names = list(out)
+    main = out[names[0]]
+    sample = (f"first {m_sub} of {W['m']} items, all n={W['n']} respondents, {main['steps']} timed sweep(s) of {names[0]} on {main['threads']} threads: "
+              f"{main['shared_s']:.2f} s shared by all items + {main['items_s_on_sample']:.2f} s per-item / per-respondent work on the sample, scaled by {W['m']}/{m_sub}; extrapolated")
+    line = {"impl": "reference", "metric": W["metric"], "value": main["value"], "unit": "sweeps/s", "n_gpus": args.gpus, "steps": main["steps"], "warmup": main["warmup"],
+            "steps_requested": args.steps, "warmup_requested": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": W["scaling"],
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "extrapolated": True, "sample_m": m_sub,
+            "config": {"workload": f"sub-sample of C4: n={W['n']} x the first {m_sub} of m={W['m']} items, C={W['C']}; per-item work scaled to m={W['m']} (extrapolated, not C4 itself)",
+                       "n": W["n"], "m": m_sub, "C": W["C"]},
+            "cpu_baseline": {"value": main["value"], "unit": "sweeps/s", "cores": main["threads"], "kind": "port", "sample": sample},
+            "variants": out, "e2e": {"value": main["value"], "unit": "sweeps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
@@ -217,8 +270,9 @@ def ours(args):
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
-    n, m, C = N_RESP, M_PER_GPU * world, C_CAT
-    P = synth(n, m, C, 20261104 + 3)
+    W = workload(args.config, world)
+    n, m, C = W["n"], W["m"], W["C"]
+    P = synth(n, m, C, W["seed"])
     common = dict(seed=20261104, chain=0)
     if world == 1:
         S = gpirt_b200.Sampler(n, m, C, device=local, **common)
@@ -261,7 +315,7 @@ def ours(args):
         ms = float(t.item())
     ll = S.total_ll()
     ms_per_step = ms / args.steps
-    value = world * 1e3 / ms_per_step  # C3-sized item blocks swept per second
+    value = W["blocks"] * 1e3 / ms_per_step  # c3: C3-sized item blocks swept per second (weak scaling); c4: sweeps of the whole problem per second
 
     # ---- per-kernel-group device times (CUDA events inside the library), separate pass ----
     S.profile(True)
@@ -284,7 +338,7 @@ def ours(args):
         sel = ev["theta"] > 0
         screened["theta"] = round(1.0 - float(np.maximum(ext[sel] - 1, 0).sum()) / max(1.0, float((ev["theta"][sel] - 1).sum())), 4)
     E = {b: float(np.mean(ev[b][ev[b] > 0])) if np.any(ev[b] > 0) else 0.0 for b in ev}
-    m_loc, N = M_PER_GPU, 1001
+    m_loc, N = W["m_loc"], 1001
     nm = n * m_loc
     algo = {  # algorithmic bytes (HBM-bound groups) or flops (FP64-tensor groups) per sweep, SURVEY.md 8(d)
         "ess_f": ("hbm", 25.0 * nm), "ess_theta": ("hbm", E["theta"] * (n * m_loc if items_mode else (n / world) * m) * 9.0), "ess_beta": ("hbm", 9.0 * nm),
@@ -336,9 +390,9 @@ def ours(args):
     ll_ms = per_sweep.get("item_ll", 0.0)
     loglik_gbs = algo["item_ll"][1] / (ll_ms * 1e-3) / 1e9 if ll_ms > 0 else None
 
-    line = {"metric": "mcmc_sweeps_per_sec_c3_blocks", "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"C3 synthetic ordinal n={n} x m={m} ({M_PER_GPU} items per GPU), C={C}, 5% missing", "n": n, "m": m, "C": C,
+    line = {"metric": W["metric"], "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": W["scaling"], "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": W["text"], "n": n, "m": m, "C": C,
                        "l2": "working set per sweep (f, nu, Z, f*, L, W: >350 MB) exceeds the 126 MB L2; no explicit flush",
                        "parallelism": f"items sharded over {world} GPU(s), theta step " + (
                            f"sharded by items too: partial log-likelihoods of 16 proposals per unfinished respondent exchanged per round ({getattr(S, 'theta_rounds', 0)} "
@@ -350,19 +404,18 @@ def ours(args):
             "loglik_gbs": loglik_gbs}
     if rank == 0:
         line["clocks"] = clk
-    gpu_state = S.get_state() if world == 1 and not args.no_cpu_baseline else None  # where the CPU baseline below starts from
+    big = W["name"] == "c4"  # 4 GB of fp64 responses: fewer end-to-end repetitions, pageable host memory, no CPU sweep beside it (--impl reference extrapolates)
+    gpu_state = S.get_state() if world == 1 and not args.no_cpu_baseline and not big else None  # where the CPU baseline below starts from
     if world > 1:
         line["sharded_equals_single"] = sharded_equals_single(rank, world, local)
 
     # ---- e2e: the reference-facing call with HOST buffers (gpirtMCMC -> gpirt_mcmc C-ABI), copies inside the timed region ----
     if world == 1:
         S.close()
-        y_pin = torch.empty((m, n), dtype=torch.float64, pin_memory=True)  # column-major n x m in pinned host memory
-        y_host = y_pin.numpy().T
-        y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
+        y_host = host_responses(torch, P["y"], pinned=not big)  # column-major n x m
         k = args.steps
         rates = []
-        for _ in range(9):  # wall clock on a shared host (set_data / create vary by several ms between calls): the median of nine calls is reported
+        for _ in range(2 if big else 9):  # wall clock on a shared host (set_data / create vary by several ms between calls): the median of nine calls is reported
             t0 = time.perf_counter()
             res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=1, beta_prior_sds=P["beta_prior_sds"],
                                        theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104,
@@ -372,18 +425,20 @@ def ours(args):
         h2d = (y_host.nbytes + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
-                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of 9 calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
+                       "host_memory": "pageable" if big else "pinned",
+                       "what": f"gpirtMCMC(sample_iterations={k}) wall clock (median of {2 if big else 9} calls) incl. handle creation, fp64 y upload from pinned memory, initial draws, the kept theta/beta/threshold/ll draws of every sweep copied to the host (buffered on the device, read back in bulk), handle destruction"}
         # ---- batched chains (BASELINE config 5's mode at the C3 shape): the same call with CHAIN = 4, chains side by side on the device ----
         nch = 4
         t0 = time.perf_counter()
-        res = gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=nch, beta_prior_sds=P["beta_prior_sds"],
+        res = [] if big else gpirt_b200.gpirtMCMC(y_host, sample_iterations=k, burn_iterations=0, THIN=1, CHAIN=nch, beta_prior_sds=P["beta_prior_sds"],
                                    theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=20261104, device=local)
-        line["batched_chains"] = {"chains": nch, "value": nch * k / (time.perf_counter() - t0), "unit": "chain-sweeps/s",
-                                  "what": f"gpirtMCMC(CHAIN={nch}, sample_iterations={k}) end to end with host buffers (one gpirt_mcmc_chains call: y uploaded "
-                                          "once, chains on their own streams, sweeps issued round-robin); each chain is bit-identical to the chain run alone"}
+        if not big:
+            line["batched_chains"] = {"chains": nch, "value": nch * k / (time.perf_counter() - t0), "unit": "chain-sweeps/s",
+                                      "what": f"gpirtMCMC(CHAIN={nch}, sample_iterations={k}) end to end with host buffers (one gpirt_mcmc_chains call: y uploaded "
+                                              "once, chains on their own streams, sweeps issued round-robin); each chain is bit-identical to the chain run alone"}
         assert all(np.all(np.isfinite(r["ll"])) for r in res)
         # ---- CPU baseline beside it (bounded sample, rank 0, N=1 only) ----
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and not big:
             # bounded sample: ONE whole faithful sweep of the full workload (tens of seconds) and two tidy ones, from the GPU chain's own state
             r = cpu_sweeps(n, m, C, 20261104 + 3, faithful=1, warm=0, max_timed=1, min_timed=1, budget_s=0.0, state=gpu_state, blas=True)
             t = cpu_sweeps(n, m, C, 20261104 + 3, faithful=0, warm=0, max_timed=2, min_timed=1, budget_s=30.0, state=gpu_state, blas=True)
@@ -396,12 +451,10 @@ def ours(args):
         from gpirt_b200.distributed import gpirtMCMC_sharded
 
         S.close()
-        y_pin = torch.empty((m, n), dtype=torch.float64, pin_memory=True)
-        y_host = y_pin.numpy().T
-        y_host[...] = np.where(P["y"] == 0, np.nan, P["y"].astype(np.float64))
+        y_host = host_responses(torch, P["y"], pinned=not big)
         k = args.steps
         rates = []
-        for _ in range(5):
+        for _ in range(2 if big else 5):
             barrier()
             t0 = time.perf_counter()
             res = gpirtMCMC_sharded(y_host, k, 0, THIN=1, rank=rank, world=world, device=local, beta_prior_sds=P["beta_prior_sds"],
@@ -409,15 +462,16 @@ def ours(args):
             barrier()
             t = torch.tensor([time.perf_counter() - t0], device="cuda", dtype=torch.float64)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            rates.append(world * k / float(t.item()))
+            rates.append(W["blocks"] * k / float(t.item()))
             assert np.all(np.isfinite(res["ll"]))
         # per rank: its items' columns and its respondents' rows of y (2/world of the matrix), the small state arrays; draws come back on every rank
         h2d = world * (2.0 * y_host.nbytes / world + 8 * (n + 3 * m + m * (C + 1) + 3 * m + 2 * n)) / k
         d2h = world * 8 * (n + 3 * m + m * (C + 1) + 1)
         line["e2e"] = {"value": float(np.median(rates)), "unit": "sweeps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "calls": [round(r, 2) for r in rates],
-                       "what": f"gpirtMCMC_sharded(sample_iterations={k}) on {world} ranks, wall clock between barriers (max over ranks, median of 5 calls) incl. handle "
+                       "host_memory": "pageable" if big else "pinned",
+                       "what": f"gpirtMCMC_sharded(sample_iterations={k}) on {world} ranks, wall clock between barriers (max over ranks, median of {2 if big else 5} calls) incl. handle "
                                "creation, each rank's partial fp64 y upload from pinned memory, initial draws, exchanges, kept draws read back on every rank; "
-                               f"value = {world} C3-sized item blocks x sweeps per second, as `value`"}
+                               + (f"value = {world} C3-sized item blocks x sweeps per second, as `value`" if not big else "value = sweeps of the whole problem per second")}
     if rank == 0:
         print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
@@ -436,6 +490,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c3", choices=["c3", "c4"], help="c3: BASELINE configs[2], the headline (weak scaling over items); c4: configs[3], n=10000 x m=50000, C=7 (strong scaling)")
     ap.add_argument("--ref-budget", type=float, default=210.0, help="--impl reference: wall-clock budget (s) of the faithful variant's warm-up + timed sweeps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
