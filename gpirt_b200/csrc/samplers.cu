@@ -638,7 +638,8 @@ cudaError_t launch_ess_theta(cudaStream_t st, const ThetaView& v) {
     const size_t row_bytes = ((size_t)v.m_total + 15) / 16 * 16;
     w.y_in_smem = row_bytes <= (wide ? (size_t)96 << 10 : (size_t)24 << 10) && row_bytes <= (size_t)v.ldm;  // keeps >= 2 wide / 8 narrow CTAs per SM
     const size_t smem = w.y_in_smem ? row_bytes : 0;
-    if (wide && smem > ((size_t)48 << 10)) {  // the opt-in is per device (one process may drive several): set where it is needed, it costs microseconds
+    if (wide && smem > ((size_t)32 << 10)) {  // static (~9 KB: virtual lanes, partials) + dynamic above the 48 KB default: the opt-in is per device (one
+                                              // process may drive several), so it is set where it is needed; it costs microseconds
         cudaError_t ea = cudaFuncSetAttribute(k_ess_theta<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 << 10);
         if (ea != cudaSuccess) return ea;
     }
