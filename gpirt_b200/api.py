@@ -25,9 +25,10 @@ def _as_cube(data):
 def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_codes=None, beta_prior_means=None,
               beta_prior_sds=None, theta_prior_means=None, theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern",
               theta_init=None, thresholds=None, SEED=1, constant_IRF=0, store_f=False, store_fstar=False, beta_init=None,
-              f_init=None, device=0, progress=None, f_init_z=None, first_chain=0):
+              f_init=None, device=0, progress=None, f_init_z=None, first_chain=0, devices=None):
     """Drop-in for gpirtMCMC() (R/gpirtMCMC.R:98-167). `vote_codes` must stay None: the reference's recoding
-    path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing."""
+    path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing.
+    `devices=[0, 1, ...]` (or the environment variable GPIRT_DEVICES="0,1,...") shards the items of every chain over several GPUs."""
     if vote_codes is not None:
         raise GpirtError(_lib.ERR_UNSUPPORTED, "vote_codes recoding is not part of the sampler path; pass codes 1..C")
     y = _as_cube(data)
@@ -56,6 +57,8 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
     outs, keep = [], []
     args = (McmcArgs * CHAIN)()
     cb = _lib.PROGRESS_FN(progress) if progress is not None else _lib.PROGRESS_FN()
+    # devices=[0, 1, ...]: every chain item-sharded over these GPUs from this one process (gpirt_mcmc_args.n_devices; no torch, no NCCL)
+    devs = None if devices is None else np.ascontiguousarray(np.asarray(devices, dtype=np.int32))
     for chain in range(CHAIN):
         rng = np.random.default_rng(SEED + first_chain + chain)  # stands in for set.seed(SEED+chain-1) (R/gpirtMCMC.R:114)
         if theta_init is None:
@@ -89,6 +92,8 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         a.f_draws = out["f"].ctypes.data if store_f else None
         a.fstar_draws = out["fstar"].ctypes.data if store_fstar else None
         a.progress = cb
+        if devs is not None and devs.size > 1:
+            a.n_devices, a.devices = int(devs.size), devs.ctypes.data
         outs.append(out)
     # all chains in one call: they share y on the device and run side by side (gpirt_mcmc_chains; CHAIN == 1 is gpirt_mcmc)
     check(_lib.lib().gpirt_mcmc_chains(args, CHAIN) if CHAIN > 1 else _lib.lib().gpirt_mcmc(C.byref(args[0])))

@@ -318,6 +318,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_W, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&h->ev_xchg, cudaEventDisableTiming));
         if (h->n >= 4096) {  // look-ahead of the two-level Cholesky (linalg.cuh, CholAux): the bulk of a trailing update runs beside the next panels
             CU(cudaStreamCreateWithPriority(&h->chol_aux.helper, cudaStreamNonBlocking, lo));  // below the side stream: the panels must not queue behind the bulk GEMM's pending tiles
             CU(cudaEventCreateWithFlags(&h->chol_aux.ev_panel, cudaEventDisableTiming));
@@ -429,6 +430,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->ev_L) cudaEventDestroy(h->ev_L);
     if (h->ev_shared) cudaEventDestroy(h->ev_shared);
     if (h->ev_W) cudaEventDestroy(h->ev_W);
+    if (h->ev_xchg) cudaEventDestroy(h->ev_xchg);
     for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
     for (int c = 0; c < h->Lpost_rows.count; ++c) cudaEventDestroy(h->Lpost_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
@@ -1389,6 +1391,30 @@ int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* 
         case GPIRT_XCHG_ITEMS_PACKED: *dev_ptr = h->items_packed; *chunk_bytes = (int64_t)h->m_chunk * (h->C + 5) * 8; break;
         default: return fail(GPIRT_ERR_INVALID, "exchange_buffer: unknown buffer %d", which);
     }
+    return GPIRT_OK;
+}
+
+// One process, several shards (handles of one chain, possibly on different GPUs): chunk `src->rank` of exchange buffer `which` goes from src's
+// buffer into dst's, on dst's stream, after everything queued on src's stream so far. A peer copy between two GPUs (direct over NVLink once
+// peer access is enabled, gpirt_mcmc does that), a device copy on one. The caller keeps src from rewriting its chunk before dst has pulled it
+// (gpirt_mcmc's loop: every round ends in gpirt_theta_items_decide, which synchronises each shard's stream).
+int gpirt_exchange_pull(gpirt_sampler* dst, gpirt_sampler* src, int which) {
+    CHECK_H(dst);
+    CHECK_H(src);
+    if (dst == src) return GPIRT_OK;
+    if (dst->world != src->world || dst->n != src->n || dst->m_total != src->m_total || dst->C != src->C)
+        return fail(GPIRT_ERR_SHAPE, "exchange_pull: the two handles are not shards of the same problem");
+    void *pd = nullptr, *ps = nullptr;
+    int64_t bd = 0, bs = 0;
+    TRY(gpirt_exchange_buffer(dst, which, &pd, &bd));
+    TRY(gpirt_exchange_buffer(src, which, &ps, &bs));
+    if (bd != bs || !pd || !ps) return fail(GPIRT_ERR_SHAPE, "exchange_pull: buffer %d differs between the shards", which);
+    const size_t off = (size_t)src->rank * (size_t)bs;
+    CU(cudaSetDevice(src->cfg.device));
+    CU(cudaEventRecord(src->ev_xchg, src->stream));
+    CU(cudaSetDevice(dst->cfg.device));
+    CU(cudaStreamWaitEvent(dst->stream, src->ev_xchg, 0));
+    CU(cudaMemcpyPeerAsync((char*)pd + off, dst->cfg.device, (char*)ps + off, src->cfg.device, (size_t)bs, dst->stream));
     return GPIRT_OK;
 }
 

@@ -4,6 +4,8 @@
 // Host side only: sample storage, thinning and the progress/interrupt poll; all arithmetic runs in the
 // kernels behind the subsystem calls.
 #include <cstdio>
+#include <cstdlib>
+#include <cuda_runtime.h>
 #include <algorithm>
 #include <cstring>
 #include <limits>
@@ -305,6 +307,115 @@ struct ChainRun {
 };
 }  // namespace
 
+// gpirtMCMC() on several GPUs from ONE process (gpirt_mcmc_args.n_devices / GPIRT_DEVICES): the item-sharded chain of gpirt_b200/distributed.py with
+// the exchanges as peer copies (gpirt_exchange_pull). Shard r = handle of rank r on devs[r]. Per sweep (src/gpirtMCMC.cpp:267-331):
+//   draw_f, draw_fstar on every shard's items | theta rounds { partials ; pull the other shards' partials ; decide } | f <- f*, draw_beta, K +
+//   Cholesky (replicated), draw_threshold, item ll on every shard | one packed exchange of beta / thresholds / item ll.
+// The kept draws (theta, beta, thresholds, ll: complete on every shard after the packed exchange) are stored on shard 0.
+static int mcmc_sharded(const gpirt_mcmc_args* a, const std::vector<int>& devs) {
+    const int W = (int)devs.size();
+    if (a->horizon != 1 || a->constant_IRF != 0) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "several devices: horizon 1 and constant_IRF 0 only");
+    if (a->f_draws || a->fstar_draws) return gpirt::fail_msg(GPIRT_ERR_UNSUPPORTED, "several devices: f / f* draws are not kept (every shard holds its own items only)");
+    if (W > a->m || W > a->n) return gpirt::fail_msg(GPIRT_ERR_SHAPE, "several devices: more shards than items or respondents");
+    for (int r = 0; r < W; ++r)  // direct NVLink copies between the shards' GPUs (already enabled / same device: fine)
+        for (int q = 0; q < W; ++q)
+            if (devs[r] != devs[q]) {
+                int can = 0;
+                if (cudaDeviceCanAccessPeer(&can, devs[r], devs[q]) == cudaSuccess && can && cudaSetDevice(devs[r]) == cudaSuccess) {
+                    cudaDeviceEnablePeerAccess(devs[q], 0);
+                    cudaGetLastError();
+                }
+            }
+    std::vector<Guard> g(W);
+    std::vector<gpirt_sampler*> h(W, nullptr);
+    for (int r = 0; r < W; ++r) {
+        gpirt_config cfg = config_of(a);
+        cfg.device = devs[r]; cfg.rank = r; cfg.world = W;
+        TRYC(gpirt_create(&cfg, &g[r].h));
+        h[r] = g[r].h;
+        TRYC(gpirt_set_data_f64(h[r], a->y));  // a shard uploads its items' columns and its respondents' rows
+        TRYC(gpirt_set_priors(h[r], a->beta_prior_sds, a->theta_prior_sds));
+        TRYC(gpirt_set_state(h[r], a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
+        TRYC(gpirt_set_iter(h[r], 0xFFFFFFFFu));
+        TRYC(gpirt_init_draw(h[r], a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
+        if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h[r], a->f_init_z));
+        TRYC(gpirt_set_iter(h[r], 0));
+    }
+    auto exchange = [&](int which) -> int {
+        for (int q = 0; q < W; ++q)
+            for (int r = 0; r < W; ++r)
+                if (r != q) TRYC(gpirt_exchange_pull(h[q], h[r], which));
+        return GPIRT_OK;
+    };
+    const int n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
+    int cap = 0, first = 0;
+    if (n_samples > 0) {
+        size_t free_b = 0, total_b = 0;
+        if (cudaSetDevice(devs[0]) != cudaSuccess || cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return GPIRT_ERR_CUDA;
+        const int64_t per = gpirt_store_sample_bytes(h[0], 0, 0);
+        cap = (int)std::max<int64_t>(1, std::min<int64_t>(n_samples, (int64_t)(free_b / 4) / per));
+        TRYC(gpirt_store_open(h[0], cap, 0, 0));
+    }
+    auto flush = [&]() -> int {
+        int cnt = 0;
+        TRYC(gpirt_store_count(h[0], &cnt, nullptr));
+        TRYC(gpirt_store_flush(h[0], n_samples, first, a->theta_draws, a->beta_draws, a->threshold_draws, a->ll_draws, nullptr, nullptr));
+        first += cnt;
+        return GPIRT_OK;
+    };
+    const int total = a->sample_iterations + a->burn_iterations;
+    std::vector<int32_t> active(W, 0);
+    for (int iter = 0; iter < total; ++iter) {
+        if (a->progress && a->progress(iter, total, a->user)) return GPIRT_ERR_INVALID;  // user interrupt
+        for (int r = 0; r < W; ++r) TRYC(gpirt_sweep_phase_items(h[r]));
+        for (int r = 0; r < W; ++r) TRYC(gpirt_theta_items_begin(h[r], nullptr));
+        for (;;) {
+            for (int r = 0; r < W; ++r) TRYC(gpirt_theta_items_partials(h[r]));
+            TRYC(exchange(GPIRT_XCHG_THETA_PART));
+            for (int r = 0; r < W; ++r) TRYC(gpirt_theta_items_decide(h[r], &active[r]));
+            for (int r = 1; r < W; ++r)
+                if (active[r] != active[0]) return gpirt::fail_msg(GPIRT_ERR_CUDA, "several devices: the shards disagree on the unfinished respondents");
+            if (active[0] == 0) break;
+        }
+        for (int r = 0; r < W; ++r) TRYC(gpirt_sweep_phase_close(h[r]));
+        for (int r = 0; r < W; ++r) TRYC(gpirt_items_pack(h[r], 0));
+        TRYC(exchange(GPIRT_XCHG_ITEMS_PACKED));
+        for (int r = 0; r < W; ++r) TRYC(gpirt_items_pack(h[r], 1));
+        if (iter >= a->burn_iterations && iter % a->THIN == 0) {  // src/gpirtMCMC.cpp:334-335
+            const int sidx = (iter - a->burn_iterations) / a->THIN;
+            if (sidx < n_samples) {
+                TRYC(gpirt_store_push(h[0]));
+                int cnt = 0;
+                TRYC(gpirt_store_count(h[0], &cnt, nullptr));
+                if (cnt == cap) TRYC(flush());
+            }
+        }
+    }
+    if (n_samples > 0) TRYC(flush());
+    for (int r = 0; r < W; ++r) TRYC(gpirt_sync(h[r]));
+    return GPIRT_OK;
+}
+
+// the devices of a call: args.devices, else GPIRT_DEVICES ("0,1,2,3"), else args.device alone
+static std::vector<int> devices_of(const gpirt_mcmc_args* a) {
+    std::vector<int> d;
+    if (a->n_devices > 1 && a->devices) {
+        d.assign(a->devices, a->devices + a->n_devices);
+    } else if (a->n_devices <= 0) {
+        if (const char* e = getenv("GPIRT_DEVICES")) {
+            for (const char* p = e; *p;) {
+                char* end = nullptr;
+                const long v = strtol(p, &end, 10);
+                if (end == p) break;
+                d.push_back((int)v);
+                p = (*end == ',') ? end + 1 : end;
+            }
+        }
+    }
+    if (d.size() < 2) d.assign(1, a->device);
+    return d;
+}
+
 extern "C" int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains) {
     if (!chains || n_chains < 1) return GPIRT_ERR_INVALID;
     const gpirt_mcmc_args* a0 = &chains[0];
@@ -314,6 +425,13 @@ extern "C" int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains
         if (a->n != a0->n || a->m != a0->m || a->horizon != a0->horizon || a->C != a0->C || a->device != a0->device ||
             a->sample_iterations != a0->sample_iterations || a->burn_iterations != a0->burn_iterations || a->THIN != a0->THIN)
             return GPIRT_ERR_SHAPE;
+    }
+    if (a0->horizon == 1 && !a0->constant_IRF) {  // several GPUs: every chain item-sharded over them, chains one after the other
+        const std::vector<int> devs = devices_of(a0);
+        if (devs.size() > 1) {
+            for (int c = 0; c < n_chains; ++c) TRYC(mcmc_sharded(&chains[c], devs));
+            return GPIRT_OK;
+        }
     }
     if (a0->constant_IRF) {  // one item response function for all sessions: the composed mode, chains one after the other
         for (int c = 0; c < n_chains; ++c) TRYC(mcmc_constant(&chains[c], config_of(&chains[c])));

@@ -46,6 +46,7 @@ struct gpirt_sampler {
     // ll, next draw_f): it is a long chain of small launches that cannot fill the GPU on its own.
     cudaStream_t side = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_W = nullptr, ev_shared = nullptr;
+    cudaEvent_t ev_xchg = nullptr;  // "this shard's chunk is written": what gpirt_exchange_pull makes the pulling shard's stream wait for
     gpirt::CholMilestones L_rows;  // leading row blocks of L signalled while chol(K) is still running on the side stream (nu = L Z starts under it)
     bool pending_rows = false;
     gpirt::CholAux chol_aux;       // helper stream + events of the two-level Cholesky's look-ahead (n >= 4096)

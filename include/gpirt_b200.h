@@ -220,6 +220,10 @@ int gpirt_theta_items_begin(gpirt_sampler* h, const gpirt_streams* s);
 int gpirt_theta_items_partials(gpirt_sampler* h);
 int gpirt_theta_items_decide(gpirt_sampler* h, int32_t* n_active);
 int gpirt_items_pack(gpirt_sampler* h, int unpack);
+/* One process driving several shards (handles with the same world, ranks 0..world-1, on the same or on different GPUs): copies chunk src->rank of
+ * exchange buffer `which` from src's buffer into dst's on dst's stream, ordered after the work queued on src's stream (an event) - the all-gathers
+ * above without a process group: a peer copy over NVLink between two GPUs. This is how gpirt_mcmc(n_devices > 1) exchanges; no torch, no NCCL. */
+int gpirt_exchange_pull(gpirt_sampler* dst, gpirt_sampler* src, int which);
 /* device pointer of the all-gather buffer `which`; it holds `world` equal chunks of chunk_bytes, chunk r owned by rank r */
 int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
 int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */
@@ -305,6 +309,12 @@ typedef struct {
      * an R shim that draws z with R::rnorm starts from the reference's own initial state without factorising K on the host.
      * Ignored when f_init is given. */
     const double* f_init_z;
+    /* Several GPUs behind the same call (the north star's "work is partitioned across the 8 x B200 box by items"): n_devices > 1 runs the chain
+     * item-sharded over devices[0..n_devices-1] from this one process - one shard per entry (an ordinal may repeat), peer copies for the exchanges,
+     * the item-sharded theta step - and returns the draws of the single-device chain (same Philox streams; decisions identical unless a margin is
+     * below fp64 summation noise). 0 or 1: `device` alone, unless the environment variable GPIRT_DEVICES ("0,1,2,3") names several - the way an
+     * unmodified caller (the R shim, src/RcppExports.cpp:16-39) reaches them. Needs horizon == 1, constant_IRF == 0, no f / f* draws kept. */
+    int32_t n_devices; const int32_t* devices;
 } gpirt_mcmc_args;
 /* constant_IRF == 1 (any horizon; with one session the reference's branch is the ordinary sampler with the inducing-point f* draw): composed from a panel, a stacked sampler over the n*horizon rows and a 100-respondent inducing-point sampler
  * (csrc/entry.cu mcmc_constant; src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96). beta_init / f_init / f_init_z are

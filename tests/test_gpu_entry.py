@@ -416,3 +416,29 @@ def test_a_NaN_state_stalls_the_ESS_loop_instead_of_scoring_finite_garbage(scree
         S.sync()
     assert e.value.code == _lib.ERR_ESS_STALLED
     S.close()
+
+
+@pytest.mark.parametrize("shards", [2, 3])
+def test_gpirtMCMC_item_sharded_from_one_process_returns_the_single_device_draws(shards, monkeypatch):
+    """gpirt_mcmc(n_devices > 1): the chain item-sharded over several shards from ONE process, exchanges as device / peer copies (csrc/entry.cu
+    mcmc_sharded; the north star's item partition behind the Rcpp entry point, src/RcppExports.cpp:16-39). Here every shard sits on device 0 —
+    the same code path as distinct GPUs, peer copies included — and must return the draws of the one-device call bit for bit; the
+    GPIRT_DEVICES environment variable reaches the same path for a caller that cannot change its arguments (the R shim)."""
+    import gpirt_b200
+
+    n, m, C = 180, 67, 4
+    P = make_problem(n, m, C, seed=17, missing=0.08)
+    kw = dict(beta_prior_sds=P["beta_prior_sds"], theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=31)
+    one = gpirt_b200.gpirtMCMC(P["y"], 6, 2, THIN=2, **kw)[0]
+    many = gpirt_b200.gpirtMCMC(P["y"], 6, 2, THIN=2, devices=[0] * shards, **kw)[0]
+    monkeypatch.setenv("GPIRT_DEVICES", ",".join(["0"] * shards))
+    env = gpirt_b200.gpirtMCMC(P["y"], 6, 2, THIN=2, **kw)[0]
+    monkeypatch.delenv("GPIRT_DEVICES")
+    for other in (many, env):
+        assert np.array_equal(one["theta"], other["theta"]) and np.array_equal(one["ll"], other["ll"])
+        assert len(other["beta"]) == 3
+        for a, b in zip(one["beta"] + one["threshold"], other["beta"] + other["threshold"]):
+            assert np.array_equal(a, b)
+    with pytest.raises(gpirt_b200.GpirtError) as e:  # f draws live on the shard that owns the item
+        gpirt_b200.gpirtMCMC(P["y"], 2, 0, devices=[0, 0], store_f=True, **kw)
+    assert e.value.code == 6

@@ -75,3 +75,19 @@ def test_two_gpu_chain_is_bit_identical_to_one_gpu(tmp_path, exchange):
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "WORLD2_EQUALS_WORLD1 True" in r.stdout, r.stdout[-2000:]
     assert "SHARDED_MCMC_EQUALS_SINGLE True" in r.stdout, r.stdout[-2000:]
+
+
+def test_gpirtMCMC_over_two_gpus_from_one_process_equals_one_gpu():
+    """gpirt_mcmc(n_devices = 2) with two real devices: peer copies over NVLink, no process group."""
+    if _gpus() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    import gpirt_b200
+    from tests.problems import make_problem
+
+    n, m, C = 203, 61, 4
+    P = make_problem(n, m, C, seed=5)
+    kw = dict(beta_prior_sds=P["beta_prior_sds"], theta_prior_sds=P["theta_prior_sds"], theta_init=P["theta0"], thresholds=P["thr0"], SEED=123, beta_init=P["beta0"])
+    a = gpirt_b200.gpirtMCMC(P["y"], 5, 1, THIN=2, devices=[0, 1], **kw)[0]
+    b = gpirt_b200.gpirtMCMC(P["y"], 5, 1, THIN=2, **kw)[0]
+    assert np.array_equal(a["theta"], b["theta"]) and np.array_equal(a["ll"], b["ll"])
+    assert all(np.array_equal(x, y) for x, y in zip(a["beta"] + a["threshold"], b["beta"] + b["threshold"]))

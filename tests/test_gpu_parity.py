@@ -537,7 +537,7 @@ def test_draw_theta_over_a_wide_item_row_matches_oracle(threads):
     (src/draw-theta.cpp:4-84,112-170)."""
     from gpirt_b200 import _lib
 
-    n, m, C = 48, 26500, 2
+    n, m, C = 48, 41000, 2  # 1024 threads: 41 008 bytes of dynamic + ~9 KB of static shared memory, i.e. above the 48 KB default (8 shards of C3 land here)
     P = make_problem(n, m, C, seed=35, on_grid=True)
     rng = P["rng"]
     try:
