@@ -52,6 +52,11 @@ class McmcArgs(C.Structure):
                 ("n_devices", C.c_int32), ("devices", C.c_void_p)]
 
 
+class MemEstimate(C.Structure):
+    _fields_ = [("n_samples", C.c_int32), ("theta_mb", C.c_double), ("beta_mb", C.c_double), ("f_mb", C.c_double), ("fstar_mb", C.c_double),
+                ("threshold_mb", C.c_double), ("total_mb", C.c_double), ("warn", C.c_int32)]
+
+
 class RecoverArgs(C.Structure):
     _fields_ = [("seed", C.c_int32), ("f", C.c_void_p), ("y", C.c_void_p), ("n", C.c_int32), ("m", C.c_int32),
                 ("horizon", C.c_int32), ("theta", C.c_void_p), ("beta", C.c_void_p), ("thresholds", C.c_void_p),
@@ -70,7 +75,7 @@ SYMBOLS = [
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_theta_items_begin", "gpirt_theta_items_partials",
     "gpirt_theta_items_decide", "gpirt_items_pack", "gpirt_exchange_pull", "gpirt_exchange_buffer",
-    "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_mcmc_chains", "gpirt_copy_data", "gpirt_set_mean_rows", "gpirt_interp1", "gpirt_ipc_export", "gpirt_ipc_attach", "gpirt_ipc_detach", "gpirt_peer_wait", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
+    "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_memory_estimate", "gpirt_mcmc_chains", "gpirt_copy_data", "gpirt_set_mean_rows", "gpirt_interp1", "gpirt_ipc_export", "gpirt_ipc_attach", "gpirt_ipc_detach", "gpirt_peer_wait", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
     "gpirt_profile_reset", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit", "gpirt_debug_cell32", "gpirt_debug_fp64_peak", "gpirt_debug_chol_trace",
 ]
 

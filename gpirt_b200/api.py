@@ -25,7 +25,7 @@ def _as_cube(data):
 def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_codes=None, beta_prior_means=None,
               beta_prior_sds=None, theta_prior_means=None, theta_prior_sds=None, theta_os=1, theta_ls=10, KERNEL="Matern",
               theta_init=None, thresholds=None, SEED=1, constant_IRF=0, store_f=False, store_fstar=False, beta_init=None,
-              f_init=None, device=0, progress=None, f_init_z=None, first_chain=0, devices=None):
+              f_init=None, device=0, progress=None, f_init_z=None, first_chain=0, devices=None, verbose=False):
     """Drop-in for gpirtMCMC() (R/gpirtMCMC.R:98-167). `vote_codes` must stay None: the reference's recoding
     path is broken for the ordinal sampler; pass integer codes 1..C with NaN for missing.
     `devices=[0, 1, ...]` (or the environment variable GPIRT_DEVICES="0,1,...") shards the items of every chain over several GPUs."""
@@ -95,6 +95,8 @@ def gpirtMCMC(data, sample_iterations, burn_iterations, THIN=1, CHAIN=1, vote_co
         if devs is not None and devs.size > 1:
             a.n_devices, a.devices = int(devs.size), devs.ctypes.data
         outs.append(out)
+    if verbose:  # the block the reference prints before the chain starts (src/gpirtMCMC.cpp:60-82)
+        print(memory_estimate(args[0])[1], end="")
     # all chains in one call: they share y on the device and run side by side (gpirt_mcmc_chains; CHAIN == 1 is gpirt_mcmc)
     check(_lib.lib().gpirt_mcmc_chains(args, CHAIN) if CHAIN > 1 else _lib.lib().gpirt_mcmc(C.byref(args[0])))
     result = []
@@ -277,3 +279,11 @@ def fp64_peak(device=0):
     a, b = C.c_double(), C.c_double()
     check(_lib.lib().gpirt_debug_fp64_peak(int(device), C.byref(a), C.byref(b)))
     return a.value, b.value
+
+
+def memory_estimate(args):
+    """(numbers, text) of gpirtMCMC()'s memory estimate (src/gpirtMCMC.cpp:47-82) for a filled McmcArgs; text is the reference's printed block."""
+    est = _lib.MemEstimate()
+    buf = C.create_string_buffer(2048)
+    check(_lib.lib().gpirt_memory_estimate(C.byref(args), C.byref(est), buf, C.c_int64(len(buf))))
+    return {k: getattr(est, k) for k, _ in est._fields_}, buf.value.decode()

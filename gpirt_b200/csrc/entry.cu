@@ -458,6 +458,36 @@ extern "C" int gpirt_mcmc_chains(const gpirt_mcmc_args* chains, int32_t n_chains
     return GPIRT_OK;
 }
 
+extern "C" int gpirt_memory_estimate(const gpirt_mcmc_args* a, gpirt_mem_estimate* out, char* text, int64_t text_cap) {
+    if (!a || !out || a->THIN < 1 || a->n < 1 || a->m < 1 || a->horizon < 1) return gpirt::fail_msg(GPIRT_ERR_INVALID, "memory_estimate: bad arguments");
+    // src/gpirtMCMC.cpp:48-58; its `C` is thresholds.n_cols, i.e. categories + 1
+    const double n = a->n, m = a->m, H = a->horizon, C1 = a->C + 1, mb = 1024.0 * 1024.0;
+    const int n_samples = a->sample_iterations / a->THIN;
+    gpirt_mem_estimate e;
+    e.n_samples = n_samples;
+    e.theta_mb = (n_samples * n * H * 8.0) / mb;
+    e.beta_mb = (n_samples * 3 * m * H * 8.0) / mb;
+    e.f_mb = (n_samples * n * m * H * 8.0) / mb;
+    e.fstar_mb = (n_samples * 1001 * m * H * 8.0) / mb;
+    e.threshold_mb = (n_samples * m * C1 * H * 8.0) / mb;
+    e.total_mb = e.theta_mb + e.beta_mb + e.threshold_mb;
+    if (a->store_f) e.total_mb += e.f_mb;
+    if (a->store_fstar) e.total_mb += e.fstar_mb;
+    e.warn = e.total_mb > 10000 ? 1 : 0;
+    *out = e;
+    if (text && text_cap > 0) {  // :60-82, number format of an ostream with default precision ("%g")
+        snprintf(text, (size_t)text_cap,
+                 "\n=== MEMORY ESTIMATE ===\nSamples to store: %d (thinned from %d)\nTheta samples:     %g MB\nBeta samples:      %g MB\n"
+                 "F samples:         %g MB (%s)\nFstar samples:     %g MB (%s)\nThreshold samples: %g MB\nTOTAL ESTIMATED:   %g MB (%g GB)\n%s"
+                 "========================\n\n",
+                 n_samples, a->sample_iterations, e.theta_mb, e.beta_mb, e.f_mb, a->store_f ? "ENABLED" : "DISABLED - will skip", e.fstar_mb,
+                 a->store_fstar ? "ENABLED" : "DISABLED - will skip", e.threshold_mb, e.total_mb, e.total_mb / 1024.0,
+                 e.warn ? "\nWARNING: Estimated memory usage exceeds 10 GB!\nConsider: (1) Increase THIN parameter, (2) Reduce sample_iterations\n"
+                          "          (3) Set store_f=FALSE, (4) Set store_fstar=FALSE\n\n" : "");
+    }
+    return GPIRT_OK;
+}
+
 extern "C" int gpirt_mcmc(const gpirt_mcmc_args* a) {
     if (!args_ok(a)) return GPIRT_ERR_INVALID;
     return gpirt_mcmc_chains(a, 1);

@@ -320,6 +320,12 @@ typedef struct {
  * (csrc/entry.cu mcmc_constant; src/draw-f.cpp:84-139, src/draw-fstar.cpp:58-125, src/draw_threshold.cpp:5-96). beta_init / f_init / f_init_z are
  * then read for session 0 only (the reference's constant branch draws nothing else, src/gpirtMCMC.cpp:176-188). */
 int gpirt_mcmc(const gpirt_mcmc_args* a);
+/* The memory estimate gpirtMCMC() prints before it allocates the kept draws (src/gpirtMCMC.cpp:47-82): MB of the theta / beta / f / f* / threshold
+ * draws for n_samples = sample_iterations / THIN, their total over what store_f / store_fstar keep, and the reference's warning when the total
+ * exceeds 10 000 MB. Host arithmetic only (no device needed). `text` (may be NULL) receives the block the reference writes to Rcpp::Rcout, same
+ * wording and number format; the R shim prints it there. warn != 0: the total exceeds 10 000 MB. */
+typedef struct { int32_t n_samples; double theta_mb, beta_mb, f_mb, fstar_mb, threshold_mb, total_mb; int32_t warn; } gpirt_mem_estimate;
+int gpirt_memory_estimate(const gpirt_mcmc_args* a, gpirt_mem_estimate* out, char* text, int64_t text_cap);
 /* The chain loop of the R wrapper (R/gpirtMCMC.R:111-158: `for(chain in 1:CHAIN)`, one .gpirtMCMC call per chain, run back to back) as ONE
  * call that runs the chains side by side on the device - BASELINE config 5 "independent chains batched per GPU". chains[c] is chain c's
  * argument block: same y (the first chain's is uploaded once and shared on the device), n, m, horizon == 1, C, iteration counts, THIN, KERNEL

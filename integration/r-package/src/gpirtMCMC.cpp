@@ -31,6 +31,14 @@ Rcpp::List gpirtMCMC(const arma::cube& y, arma::mat theta, const int sample_iter
                      arma::cube thresholds, const int constant_IRF, const bool store_f, const bool store_fstar) {
     const arma::uword n = y.n_rows, m = y.n_cols, horizon = y.n_slices, C1 = thresholds.n_cols;
     const int n_samples = int(sample_iterations / THIN);  // src/gpirtMCMC.cpp:48
+    {   // the memory estimate and the > 10 000 MB warning, printed before anything is allocated (src/gpirtMCMC.cpp:47-82)
+        gpirt_mcmc_args e{};
+        e.n = int(n); e.m = int(m); e.horizon = int(horizon); e.C = int(C1) - 1;
+        e.sample_iterations = sample_iterations; e.burn_iterations = burn_iterations; e.THIN = THIN; e.store_f = store_f; e.store_fstar = store_fstar;
+        gpirt_mem_estimate est;
+        char text[2048];
+        if (gpirt_memory_estimate(&e, &est, text, sizeof(text)) == GPIRT_OK) Rcpp::Rcout << text;
+    }
 
     // initial values with R's RNG, in the reference's order
     // constant_IRF == 1 draws beta for session 0 only and ONE f0 = L_0 z per item (src/gpirtMCMC.cpp:176-188): the library reads slice 0 then

@@ -107,3 +107,22 @@ def test_r_shim_builds_against_stand_in_rcpp_and_links_the_c_abi():
     L = C.CDLL(os.path.join(root, "tests", "rshim", "_build", "librshim_test.so"))
     for sym in ("shim_gpirtMCMC", "shim_recover_fstar", "shim_last_error", "shim_normals_used"):
         getattr(L, sym)
+
+
+def test_memory_estimate_reproduces_the_reference_arithmetic_and_warning():
+    """src/gpirtMCMC.cpp:47-82: MB of the kept draws, total over what is stored, warning above 10 000 MB. Host arithmetic: runs without a device."""
+    from gpirt_b200.api import memory_estimate
+
+    a = _lib.McmcArgs()
+    a.n, a.m, a.horizon, a.C = 2000, 5000, 1, 5
+    a.sample_iterations, a.burn_iterations, a.THIN, a.store_f, a.store_fstar = 1000, 500, 4, 0, 0
+    num, text = memory_estimate(a)
+    mb = 1024.0 * 1024.0
+    assert num["n_samples"] == 250
+    assert num["theta_mb"] == 250 * 2000 * 8.0 / mb and num["beta_mb"] == 250 * 3 * 5000 * 8.0 / mb
+    assert num["threshold_mb"] == 250 * 5000 * 6 * 8.0 / mb  # the reference's C is thresholds.n_cols = categories + 1
+    assert num["total_mb"] == num["theta_mb"] + num["beta_mb"] + num["threshold_mb"] and num["warn"] == 0
+    assert "=== MEMORY ESTIMATE ===" in text and "Samples to store: 250 (thinned from 1000)" in text and "DISABLED - will skip" in text and "WARNING" not in text
+    a.store_f = 1  # 250 draws of 2000 x 5000 doubles: 19 GB
+    num, text = memory_estimate(a)
+    assert num["warn"] == 1 and num["total_mb"] > 10000 and "WARNING: Estimated memory usage exceeds 10 GB!" in text and "F samples:         19073.5 MB (ENABLED)" in text
