@@ -18,4 +18,4 @@ S.sweep(w)
 S.sync()
 S.sweep(k)
 S.sync()
-print("ll", S.total_ll())
+print("ll", S.total_ll(), "mean evaluations per unit in the last sweep:", {b: round(float(S.diag(b)[0].mean()), 2) for b in ("f", "theta", "beta", "thr")})
