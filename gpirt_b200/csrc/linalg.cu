@@ -497,10 +497,14 @@ __global__ void k_zero_upper(double* __restrict__ A, int ld, int n) {
     if (i < n && j < n && i < j) A[(size_t)j * ld + i] = 0.0;
 }
 
+bool chol_is_persistent(int n, const CholPlan* plan) {
+    static const int persistent_env = getenv("GPIRT_CHOL_PERSISTENT") ? atoi(getenv("GPIRT_CHOL_PERSISTENT")) : 1;
+    return plan && plan->state && persistent_env && n < 4096;
+}
+
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks,
                                const CholAux* aux, const CholPlan* plan) {
-    static const int persistent_env = getenv("GPIRT_CHOL_PERSISTENT") ? atoi(getenv("GPIRT_CHOL_PERSISTENT")) : 1;
-    if (plan && plan->state && persistent_env && n < 4096) {
+    if (chol_is_persistent(n, plan)) {
         cudaError_t e = chol_lower_persistent(st, A, ld, n, info_dev, plan->state, plan->tasks, plan->n_tasks, plan->max_ctas);
         if (e != cudaSuccess) return e;
         for (int c = 0; marks && c < marks->count; ++c)

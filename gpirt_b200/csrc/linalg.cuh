@@ -43,6 +43,7 @@ struct CholPlan {
     int* state = nullptr;             // device: chol_plan_state_ints(n) ints
     int max_ctas = 0;
 };
+bool chol_is_persistent(int n, const CholPlan* plan);  // chol_lower_blocked(n, plan) runs the single persistent kernel: no row milestones before its end
 int chol_plan_tiles(int n);
 size_t chol_plan_state_ints(int n);
 std::vector<uint32_t> chol_plan_tasks(int n);
