@@ -71,7 +71,7 @@ SYMBOLS = [
     "gpirt_set_data_f64", "gpirt_set_data_i8", "gpirt_set_priors", "gpirt_set_state", "gpirt_get_state", "gpirt_get_L",
     "gpirt_store_open", "gpirt_store_push", "gpirt_store_count", "gpirt_store_flush", "gpirt_store_flush_slice", "gpirt_store_close", "gpirt_store_sample_bytes",
     "gpirt_set_iter", "gpirt_init_f_from_z", "gpirt_panel_create", "gpirt_panel_destroy", "gpirt_panel_session", "gpirt_panel_get_L_time",
-    "gpirt_panel_draw_theta", "gpirt_panel_sweep", "gpirt_panel_total_ll", "gpirt_panel_sync", "gpirt_set_solver", "gpirt_set_overlap", "gpirt_set_screen", "gpirt_debug_theta_threads", "gpirt_get_exact_evals", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
+    "gpirt_panel_draw_theta", "gpirt_panel_sweep", "gpirt_panel_total_ll", "gpirt_panel_sync", "gpirt_set_solver", "gpirt_set_overlap", "gpirt_set_chol_ctas", "gpirt_set_screen", "gpirt_debug_theta_threads", "gpirt_get_exact_evals", "gpirt_get_diag", "gpirt_sync", "gpirt_update_cholesky_cache", "gpirt_draw_f", "gpirt_draw_fstar",
     "gpirt_draw_theta", "gpirt_gather_f", "gpirt_draw_beta", "gpirt_draw_threshold", "gpirt_ll_bar", "gpirt_sweep",
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_theta_items_begin", "gpirt_theta_items_partials",
     "gpirt_theta_items_decide", "gpirt_items_pack", "gpirt_exchange_pull", "gpirt_exchange_buffer",

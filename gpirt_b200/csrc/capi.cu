@@ -464,6 +464,23 @@ int gpirt_set_solver(gpirt_sampler* h, int solver) {
     return GPIRT_OK;
 }
 
+// CTAs the persistent Cholesky kernels of this handle may hold (chol_persistent.cu); 0: the per-panel path of linalg.cu. Several chains side by side
+// (gpirt_mcmc_chains) share the SMs: every chain's persistent kernel parks spinning CTAs, so the budget is divided among them.
+int gpirt_set_chol_ctas(gpirt_sampler* h, int ctas) {
+    CHECK_H(h);
+    if (ctas < 0) return fail(GPIRT_ERR_INVALID, "set_chol_ctas: %d", ctas);
+    TRY(quiesce(h));
+    if (ctas == 0) {
+        h->plan_n.state = nullptr;
+        h->plan_N.state = nullptr;
+    } else {
+        if (h->n < 4096) h->plan_n.state = h->chol_state_n;
+        h->plan_N.state = h->chol_state_N;
+        h->plan_n.max_ctas = h->plan_N.max_ctas = ctas < 4 ? 4 : ctas;
+    }
+    return GPIRT_OK;
+}
+
 int gpirt_debug_theta_threads(int threads) {
     if (threads != 0 && threads != 256 && threads != 1024) return fail(GPIRT_ERR_INVALID, "theta threads %d: 0 (automatic), 256 or 1024", threads);
     g_theta_threads = threads;
@@ -1029,9 +1046,9 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     k_add_diag<<<(N + 255) / 256, 256, 0, st>>>(h->Kpost, h->ldN, N, 1e-6);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    const bool post_marks = st == h->side && h->Lpost_rows.count > 0 && !chol_is_persistent(N, &h->plan_N);
+    const bool post_marks = st == h->side && h->Lpost_rows.count > 0 && !chol_is_persistent(N, h->plan_N.state ? &h->plan_N : nullptr);
     SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws, post_marks ? &h->Lpost_rows : nullptr,
-                                                          nullptr, &h->plan_N)));
+                                                          nullptr, h->plan_N.state ? &h->plan_N : nullptr)));
     h->pending_post_rows = post_marks;
     if (h->solver != 1) {  // substitution overwrites tmp in place, so it comes after K_post
         SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));

@@ -270,7 +270,11 @@ struct ChainRun {
         if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h, a->f_init_z));
         TRYC(gpirt_set_iter(h, 0));
         n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
-        (void)n_chains;
+        if (n_chains > 1) {  // chains side by side share the SMs: the persistent Cholesky's CTA budget is divided among them. The factor does not depend
+            // on the CTA count (updates are applied in step order), so every chain stays bit-identical to the chain run alone; the per-panel path would not
+            static const int budget = getenv("GPIRT_CHAINS_CHOL_CTAS") ? atoi(getenv("GPIRT_CHAINS_CHOL_CTAS")) : 96;
+            TRYC(gpirt_set_chol_ctas(h, std::max(6, budget / n_chains)));
+        }
         return GPIRT_OK;
     }
     // The kept draws stay on the device and come back in bulk: no host synchronisation per sweep, so the next sweep's theta-only

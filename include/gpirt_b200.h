@@ -169,6 +169,10 @@ int gpirt_set_solver(gpirt_sampler* h, int solver);
  * src/draw-fstar.cpp:26-36) of the next sweep runs on a second CUDA stream under the item samplers; 0: every kernel in the
  * reference's order on one stream. Results are identical either way. */
 int gpirt_set_overlap(gpirt_sampler* h, int on);
+/* The Cholesky cache (src/cholesky-cache.cpp:20-24) and chol(K_post) (src/draw-fstar.cpp:36) run as one persistent kernel each (csrc/chol_persistent.cu)
+ * holding at most `ctas` CTAs (default 48, GPIRT_CHOL_CTAS); 0 selects the per-panel kernels of csrc/linalg.cu. Same factor up to rounding order;
+ * gpirt_mcmc_chains divides the budget among the chains it runs side by side. */
+int gpirt_set_chol_ctas(gpirt_sampler* h, int ctas);
 /* 1 (default): the ESS kernels (draw_f / draw_beta / draw_threshold: src/draw-f.cpp:23-41 and its three siblings) first evaluate a
  * proposal's log-likelihood in fp32 together with a rigorous bound on its distance to the fp64 value and only run the fp64 pass
  * when the accept test ll' > log_y is closer than that bound. Decisions, states and stream consumption are identical to 0 (every
