@@ -491,7 +491,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c3", choices=["c3", "c4"], help="c3: BASELINE configs[2], the headline (weak scaling over items); c4: configs[3], n=10000 x m=50000, C=7 (strong scaling)")
-    ap.add_argument("--ref-budget", type=float, default=210.0, help="--impl reference: wall-clock budget (s) of the faithful variant's warm-up + timed sweeps")
+    ap.add_argument("--ref-budget", type=float, default=150.0, help="--impl reference: wall-clock budget (s) of the faithful variant's warm-up + timed sweeps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -17,6 +17,7 @@
 //     ahead of use so the next tile lands while the current one is being factored.
 // Spins are bounded (2 s on %globaltimer): a stall raises `abort`, every CTA leaves, the host reports an error instead of hanging the GPU.
 #include <cstdint>
+#include <cstdlib>
 #include <vector>
 
 #include "linalg.cuh"
@@ -503,8 +504,12 @@ __device__ void run_worker(Ctx& c, const uint32_t* tasks, int n_tasks) {
     }
 }
 
-__global__ void __launch_bounds__(CP_THREADS, 1) k_chol_persistent(double* A, int ld, int n, int T, int* state, int* info, const uint32_t* tasks,
-                                                                   int n_tasks, long long* trace) {
+// The register budget is a template parameter: unbounded the kernel takes 174 registers (the 8 x 8 pivot block of one thread), and a CTA then leaves room
+// for ONE 256-thread, 64-register ESS CTA on its SM for as long as the factorisation runs beside the item kernels; MINB = 2 compiles to 126 registers
+// without spills (two ESS CTAs fit), MINB = 3 to 80 with 160 bytes of spills. GPIRT_CHOL_MINB selects (measured: profiles/r02_chol_persistent.txt).
+template <int MINB>
+__global__ void __launch_bounds__(CP_THREADS, MINB) k_chol_persistent(double* A, int ld, int n, int T, int* state, int* info, const uint32_t* tasks,
+                                                                      int n_tasks, long long* trace) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     Shared* sh = reinterpret_cast<Shared*>(smem_raw);
     Ctx c;
@@ -564,7 +569,9 @@ cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int
     cudaError_t e = cudaMemsetAsync(state_dev, 0, chol_plan_state_ints(n) * sizeof(int), st);
     if (e != cudaSuccess) return e;
     const size_t smem = sizeof(Shared) + 128;
-    e = cudaFuncSetAttribute(k_chol_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static const int minb = getenv("GPIRT_CHOL_MINB") ? atoi(getenv("GPIRT_CHOL_MINB")) : 1;
+    auto kern = minb <= 1 ? k_chol_persistent<1> : (minb == 2 ? k_chol_persistent<2> : k_chol_persistent<3>);
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int grid = 1;  // T <= 2: the critical CTA does everything
     if (T >= 3) {
@@ -572,7 +579,7 @@ cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int
         if (n_tasks > 0 && bulk < 1) bulk = 1;  // the bulk list needs at least one CTA of its own
         grid = 3 + (bulk > 0 ? bulk : 0);
     }
-    k_chol_persistent<<<grid, CP_THREADS, smem, st>>>(A, ld, n, T, state_dev, info_dev, tasks_dev, n_tasks, trace_dev);
+    kern<<<grid, CP_THREADS, smem, st>>>(A, ld, n, T, state_dev, info_dev, tasks_dev, n_tasks, trace_dev);
     ++g_kernel_launches;
     e = cudaGetLastError();
     if (e != cudaSuccess) return e;
