@@ -287,3 +287,11 @@ def memory_estimate(args):
     buf = C.create_string_buffer(2048)
     check(_lib.lib().gpirt_memory_estimate(C.byref(args), C.byref(est), buf, C.c_int64(len(buf))))
     return {k: getattr(est, k) for k, _ in est._fields_}, buf.value.decode()
+
+
+def debug_phi_tab(x, device=0):
+    """phi_tab(x) element-wise on the device: the table-based Phi of k_item_ll / k_theta_table"""
+    x = np.ascontiguousarray(np.asarray(x, dtype=np.float64))
+    out = np.empty_like(x)
+    check(_lib.lib().gpirt_debug_phi_tab(int(device), _p(x), int(x.size), _p(out)))
+    return out

@@ -1952,3 +1952,24 @@ extern "C" int gpirt_debug_chol_trace(int device, const double* A, int64_t n, in
     CU(cudaMemcpy(trace_out, tR.p, tl * 8, cudaMemcpyDeviceToHost));
     return GPIRT_OK;
 }
+
+// Test hook: phi_tab(), the table-based Phi of the log-likelihood pass (probit.cuh), evaluated element-wise from the device copy of its table.
+__global__ void k_debug_phi_tab(const double* x, int n, double* out) {
+    __shared__ PhiNode s_phi[PHI_TAB_N];
+    load_phi_table(s_phi);
+    __syncthreads();
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = phi_tab(x[i], s_phi);
+}
+extern "C" int gpirt_debug_phi_tab(int device, const double* x, int n, double* out) {
+    if (!x || !out || n < 1) return fail(GPIRT_ERR_INVALID, "debug_phi_tab: bad arguments");
+    TRY(select_device(device));
+    DevTemp t_d;
+    CU(t_d.alloc((size_t)2 * n * 8));
+    double* d = t_d.as<double>();
+    CU(cudaMemcpy(d, x, (size_t)n * 8, cudaMemcpyHostToDevice));
+    k_debug_phi_tab<<<(n + 255) / 256, 256>>>(d, n, d + n);
+    CU(cudaGetLastError());
+    CU(cudaMemcpy(out, d + n, (size_t)n * 8, cudaMemcpyDeviceToHost));
+    return GPIRT_OK;
+}

@@ -81,8 +81,51 @@ __host__ __device__ __forceinline__ double phi(double x) {
     return x < 0.0 ? q : 1.0 - q;
 }
 
-// log(x) for positive normal x (the likelihood's argument lies in [1e-6, 1 + 1e-6])
-__host__ __device__ __forceinline__ double log_pos(double x) {
+// ---- Phi from a table of grid values (round 2) --------------------------------------------------------------------------------
+// Phi at full double accuracy is what bounds the log-likelihood pass: phi() above costs ~52 fp64-pipe instructions (reciprocal, degree-18
+// polynomial, exp). phi_tab() takes a Taylor step of at most 1/256 from the nearest point a0 = k/128 of a table holding Q(a0) = Phi(-a0) and the density
+// phi(a0): Q(a0 + d) = Q(a0) - phi(a0) * d * (1 + d (c2 + d (c3 + d (c4 + d c5)))), c_k = (-1)^(k-1) He_(k-1)(a0) / k! with the Hermite polynomials formed
+// from a0 on the fly. ~27 instructions and ONE 16-byte table load; the remainder term is below 2e-18. Measured against mpmath at 50 digits over
+// [-9.5, 9.5] including every half-way point between grid values: absolute error <= 1.2e-16 (phi(): 4e-16; R::pnorm in the reference: ~1e-16).
+// Table: 1103 x 16 bytes (tools/gen_probit_coeffs.py -> phi_table.inc); kernels stage it in shared memory once per CTA.
+#include "phi_table.inc"
+struct PhiNode { double q, d; };
+constexpr int PHI_TAB_N = PHI_TAB_K + 1;
+GPIRT_TAB PhiNode g_phi_tab[PHI_TAB_N] = {PHI_TAB_ROWS};
+#ifndef __CUDA_ARCH__
+static const PhiNode h_phi_tab[PHI_TAB_N] = {PHI_TAB_ROWS};
+#endif
+
+__host__ __device__ __forceinline__ double phi_tab(double x, const PhiNode* __restrict__ tab) {
+    const double a = fabs(x);
+    if (a != a) return a;
+    double q = 0.0;  // beyond the table (a > 8.61) the tail is < 1e-17 and is returned as 0, as phi() does
+    const double t = a * PHI_TAB_H;
+    if (t <= (double)PHI_TAB_K + 0.5) {
+#ifdef __CUDA_ARCH__
+        const int k = __double2int_rn(t);
+#else
+        const int k = (int)nearbyint(t);
+#endif
+        const double a0 = (double)k * (1.0 / PHI_TAB_H);  // exact: a multiple of 2^-7
+        const double d = a - a0;                           // |d| <= 1/256
+        const PhiNode nd = tab[k];
+        const double a2 = a0 * a0;
+        const double c2 = -0.5 * a0;
+        const double c3 = fma(a2, 1.0 / 6.0, -1.0 / 6.0);
+        const double c4 = -a0 * fma(a2, 1.0 / 24.0, -0.125);
+        const double c5 = fma(a2 * (a2 - 6.0), 1.0 / 120.0, 0.025);
+        double sser = fma(d, c5, c4);
+        sser = fma(d, sser, c3);
+        sser = fma(d, sser, c2);
+        sser = fma(d, sser, 1.0);
+        q = fma(-nd.d, sser * d, nd.q);
+    }
+    return x < 0.0 ? q : 1.0 - q;
+}
+
+// log(x) for positive normal x (the likelihood's argument lies in [1e-6, 1 + 1e-6]); `tab`: the 128-node table (g_log_tab, or a shared-memory copy)
+__host__ __device__ __forceinline__ double log_pos_t(double x, const LogNode* __restrict__ tab) {
     // the exponent-bit arithmetic below reads NaN as ~ +-710: a NaN state must reach the ESS test as NaN (never accepted -> stall flag), as std::log
     // gives it in the reference (log(0) = -inf, log(negative) = NaN)
     if (!(x > 0.0)) return x == 0.0 ? -HUGE_VAL : x * HUGE_VAL * 0.0;
@@ -97,12 +140,11 @@ __host__ __device__ __forceinline__ double log_pos(double x) {
     const long long mb = (bits & 0x000FFFFFFFFFFFFFLL) | 0x3FF0000000000000LL;
 #ifdef __CUDA_ARCH__
     const double m = __longlong_as_double(mb);
-    const LogNode nd = g_log_tab[i];
 #else
     double m;
     memcpy(&m, &mb, 8);
-    const LogNode nd = h_log_tab[i];
 #endif
+    const LogNode nd = tab[i];
     const double r = fma(m, nd.inv, -1.0);
     double p = 1.0 / 7.0;
     p = fma(p, r, -1.0 / 6.0);
@@ -115,6 +157,14 @@ __host__ __device__ __forceinline__ double log_pos(double x) {
     const double lo = fma(ed, 4.7493250390316726e-07, p);    // ln2 lo
     const double hi = fma(ed, 0.6931467056274414, nd.logc);  // ln2 hi (low 32 bits zero: ed*hi is exact)
     return hi + lo;
+}
+
+__host__ __device__ __forceinline__ double log_pos(double x) {
+#ifdef __CUDA_ARCH__
+    return log_pos_t(x, g_log_tab);
+#else
+    return log_pos_t(x, h_log_tab);
+#endif
 }
 
 // log(Phi_hi - Phi_lo + 1e-6) with the reference's operation order (src/log-likelihood.cpp:62-63)
@@ -133,7 +183,30 @@ __host__ __device__ __forceinline__ double cell_ll(double g, double tau_lo, doub
     return cell_from_probs(p_lo, p_hi);
 }
 
+// the same cell term with Phi from the table (k_item_ll, k_theta_table)
+__host__ __device__ __forceinline__ double cell_ll_tab(double g, double tau_lo, double tau_hi, bool first, bool last, const PhiNode* __restrict__ tab) {
+    double p_hi = last ? 1.0 : phi_tab(tau_hi - g, tab);
+    double p_lo = first ? 0.0 : phi_tab(tau_lo - g, tab);
+    return cell_from_probs(p_lo, p_hi);
+}
+// Branch-free form for a uniform instruction stream: both tails are always evaluated. The open ends of an item's thresholds are -inf / +inf
+// (src/log-likelihood.cpp:68-70), for which phi_tab returns exactly 0 / 1 — the values the branches above substitute — so the result is the same bits.
+__host__ __device__ __forceinline__ double cell_ll_tab2(double g, double tau_lo, double tau_hi, const PhiNode* __restrict__ tab, const LogNode* __restrict__ ltab) {
+    const double p_hi = phi_tab(tau_hi - g, tab);
+    const double p_lo = phi_tab(tau_lo - g, tab);
+#ifdef __CUDA_ARCH__
+    return log_pos_t(__dadd_rn(__dsub_rn(p_hi, p_lo), 1e-6), ltab);
+#else
+    return log_pos_t((p_hi - p_lo) + 1e-6, ltab);
+#endif
+}
+
 #ifdef __CUDACC__
+// stage the Phi table in shared memory (every thread of the CTA calls this; a barrier follows at the caller)
+__device__ __forceinline__ void load_phi_table(PhiNode* s_tab) {
+    for (int q = threadIdx.x + blockDim.x * threadIdx.y; q < PHI_TAB_N; q += blockDim.x * blockDim.y) s_tab[q] = g_phi_tab[q];
+}
+
 // ---- fp32 screening of ESS proposals ---------------------------------------------------------------------------
 // An ESS proposal is accepted iff ll' > log_y. Most proposals miss log_y by far more than fp32 can blur, so the kernels first
 // evaluate ll' in fp32 TOGETHER WITH a rigorous bound E on |ll'_fp32 - ll'_fp64|, and only fall back to the fp64 evaluation when

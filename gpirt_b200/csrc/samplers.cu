@@ -356,41 +356,73 @@ cudaError_t launch_ess_items(cudaStream_t st, int block, const ItemView& v) {
     return cudaGetLastError();
 }
 
-// per-item ll_bar_sparse with the current state
+// per-item ll_bar_sparse with the current state. Grid-stride over the items: the Phi table (probit.cuh, phi_tab) is staged in shared memory once per CTA.
 template <int WARPS>
 __global__ void __launch_bounds__(WARPS * 32) k_item_ll(ItemView v) {
     constexpr int T = WARPS * 32;
+    __shared__ PhiNode s_phi[PHI_TAB_N];
+    __shared__ LogNode s_log[128];
     __shared__ double tau[MAX_C + 1];
     __shared__ double s_part[WARPS];
     const int tid = threadIdx.x;
-    const int j = blockIdx.x;
-    const int J = v.item0 + j;
-    for (int c = tid; c <= v.C; c += T) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
-    __syncthreads();
-    const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
-    const double* __restrict__ fj = v.f + (size_t)j * v.ldn;
-    const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
-    double acc = 0.0;
-    for (int i = tid; i < v.n; i += T) {
-        const int y = yj[i];
-        if (y == 0) continue;
-        const double g = __dadd_rn(fj[i], mu_of(v.theta[i], b0, b1, b2));
-        acc += cell_ll(g, tau[y - 1], tau[y], y == 1, y == v.C);
+    load_phi_table(s_phi);
+    for (int q = tid; q < 128; q += T) s_log[q] = g_log_tab[q];
+    constexpr int U = 4;  // cells in flight per thread: their loads are issued together (ncu on the one-cell loop: long_scoreboard 7.8 warps per issue)
+    for (int j = blockIdx.x; j < v.m_local; j += gridDim.x) {
+        const int J = v.item0 + j;
+        __syncthreads();  // tables staged; the previous item's tau / s_part are no longer read
+        for (int c = tid; c <= v.C; c += T) tau[c] = v.thr[(size_t)J * (v.C + 1) + c];
+        __syncthreads();
+        const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
+        const double* __restrict__ fj = v.f + (size_t)j * v.ldn;
+        const double* __restrict__ theta = v.theta;
+        const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = (v.p_beta == 3) ? v.beta[3 * (size_t)J + 2] : 0.0;
+        double acc = 0.0;  // cells tid, tid + T, tid + 2T, ... added in this order
+        for (int i0 = tid; i0 < v.n; i0 += U * T) {
+            int y[U];
+            double f[U], th[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int i = i0 + u * T;
+                const bool in = i < v.n;
+                y[u] = in ? (int)yj[i] : 0;
+                f[u] = in ? fj[i] : 0.0;
+                th[u] = in ? theta[i] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int c = y[u] > 0 ? y[u] : 1;  // a missing cell is evaluated as category 1 and not added
+                const double g = __dadd_rn(f[u], mu_of(th[u], b0, b1, b2));
+                const double t = cell_ll_tab2(g, tau[c - 1], tau[c], s_phi, s_log);
+                if (y[u] > 0) acc += t;
+            }
+        }
+        acc = block_sum<WARPS>(acc, s_part);
+        if (tid == 0) v.item_ll[J] = acc;
     }
-    acc = block_sum<WARPS>(acc, s_part);
-    if (tid == 0) v.item_ll[J] = acc;
+}
+
+template <int WARPS>
+static cudaError_t launch_item_ll_w(cudaStream_t st, const ItemView& v) {
+    // a grid-stride kernel: exactly the CTAs that are resident at once (more would run as a second wave behind CTAs that loop over all their items)
+    int per_sm = 0, dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_item_ll<WARPS>, WARPS * 32, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const int grid = std::min(v.m_local, sms * per_sm);
+    k_item_ll<WARPS><<<grid, WARPS * 32, 0, st>>>(v);
+    ++g_kernel_launches;
+    return cudaGetLastError();
 }
 
 cudaError_t launch_item_ll(cudaStream_t st, const ItemView& v) {
     if (v.m_local <= 0) return cudaSuccess;
     switch (item_warps(v.n)) {
-        case 1: k_item_ll<1><<<v.m_local, 32, 0, st>>>(v); break;
-        case 4: k_item_ll<4><<<v.m_local, 128, 0, st>>>(v); break;
-        case 8: k_item_ll<8><<<v.m_local, 256, 0, st>>>(v); break;
-        default: k_item_ll<16><<<v.m_local, 512, 0, st>>>(v); break;
+        case 1: return launch_item_ll_w<1>(st, v);
+        case 4: return launch_item_ll_w<4>(st, v);
+        case 8: return launch_item_ll_w<8>(st, v);
+        default: return launch_item_ll_w<16>(st, v);
     }
-    ++g_kernel_launches;
-    return cudaGetLastError();
 }
 
 }  // namespace gpirt
@@ -404,26 +436,32 @@ constexpr int THETA_THREADS = 256;
 int g_theta_threads = 0;  // 0: by the number of local respondents; 256 / 1024: forced (tests: both give the same bits)
 
 __global__ void __launch_bounds__(128) k_theta_table(ThetaView v, double* __restrict__ table) {
+    __shared__ PhiNode s_phi[PHI_TAB_N];
+    load_phi_table(s_phi);
+    __syncthreads();
     const int J = blockIdx.x * 128 + threadIdx.x;
-    const int idx = blockIdx.y;
     if (J >= v.m_total) return;
     const int C = v.C;
     const int r = J / v.m_chunk, jl = J - r * v.m_chunk;
-    const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
-    const double mu = mu_of(grid_value(idx), v.beta[3 * (size_t)J], v.beta[3 * (size_t)J + 1], v.beta[3 * (size_t)J + 2]);
-    const double g = __dadd_rn(fs, mu);
+    const double b0 = v.beta[3 * (size_t)J], b1 = v.beta[3 * (size_t)J + 1], b2 = v.beta[3 * (size_t)J + 2];
     const double* tau = v.thr + (size_t)J * (C + 1);
-    double* out = table + ((size_t)idx * v.m_total + J) * C;
-    double p_lo = 0.0;
-    for (int c = 1; c <= C; ++c) {
-        const double p_hi = (c == C) ? 1.0 : phi(tau[c] - g);
-        out[c - 1] = cell_from_probs(p_lo, p_hi);
-        p_lo = p_hi;
+    for (int idx = blockIdx.y; idx < NGRID; idx += gridDim.y) {  // the Phi table is staged once per CTA, then reused over the CTA's grid rows
+        const double fs = v.fstar_all[(size_t)r * v.chunk_elems + (size_t)idx * v.ld_chunk + jl];
+        const double g = __dadd_rn(fs, mu_of(grid_value(idx), b0, b1, b2));
+        double* out = table + ((size_t)idx * v.m_total + J) * C;
+        double p_lo = 0.0;
+        for (int c = 1; c <= C; ++c) {
+            const double p_hi = (c == C) ? 1.0 : phi_tab(tau[c] - g, s_phi);
+            out[c - 1] = cell_from_probs(p_lo, p_hi);
+            p_lo = p_hi;
+        }
     }
 }
 
 cudaError_t launch_theta_table(cudaStream_t st, const ThetaView& v, double* table) {
-    dim3 grid((v.m_total + 127) / 128, NGRID);
+    const int bx = (v.m_total + 127) / 128;
+    const int by = std::max(1, std::min((int)NGRID, (148 * 16 + bx - 1) / bx));  // ~16 CTAs of 128 threads per SM in one wave
+    dim3 grid(bx, by);
     k_theta_table<<<grid, 128, 0, st>>>(v, table);
     ++g_kernel_launches;
     return cudaGetLastError();

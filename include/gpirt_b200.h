@@ -251,6 +251,7 @@ int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int c
 int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out); /* device Phi(x), log(x) */
 int gpirt_debug_normals(gpirt_sampler* h, uint32_t stream, uint32_t unit0, int rows, int cols, double* out /* rows x cols */);
 /* fp32 screening term, its error bound and the fp64 cell term log(Phi(tau_hi-g) - Phi(tau_lo-g) + 1e-6), element-wise */
+int gpirt_debug_phi_tab(int device, const double* x, int n, double* out); /* device Phi(x) of the log-likelihood pass (table + Taylor step, csrc/probit.cuh) */
 int gpirt_debug_cell32(int device, const double* g, const double* tau_lo, const double* tau_hi, int n, double* t32, double* e32, double* t64);
 /* Measurement hook (bench.py's roofline denominator; MEASURED_PEAKS.json carries no fp64 figure): issue-rate microbenchmarks of the two fp64
  * pipes the sweep's contractions run on, ~20 ms each on an otherwise idle device: mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4) and scalar DFMA,

@@ -33,6 +33,22 @@ def test_device_phi_and_log_against_mpmath():
     assert max(abs(mp.mpf(float(l)) - mp.log(mp.mpf(float(zi)))) for zi, l in zip(z, lg)) < 4e-15
 
 
+def test_table_phi_of_the_likelihood_pass_against_mpmath():
+    """phi_tab (csrc/probit.cuh): Q and the density at 1103 grid points + a 5-term Taylor step with Hermite coefficients, used by k_item_ll and
+    k_theta_table. Absolute error against mpmath at 40 digits, including every half-way point between grid values and the ends of the table."""
+    import mpmath as mp
+    from gpirt_b200.api import debug_phi_tab
+    mp.mp.dps = 40
+    rng = np.random.default_rng(1)
+    half = (np.arange(0, 1103) + 0.5) / 128.0
+    x = np.concatenate([np.linspace(-9.5, 9.5, 2001), rng.normal(size=2000) * 2.5, half, -half * 0.99999, [0.0, -8.6, 8.6, 8.609375, 8.62, -8.62, np.inf, -np.inf]])
+    ph = debug_phi_tab(x)
+    assert ph[-2] == 1.0 and ph[-1] == 0.0
+    err = max(abs(mp.mpf(float(p)) - mp.ncdf(mp.mpf(float(xi)))) for xi, p in zip(x[:-2], ph[:-2]))
+    assert err < 2.5e-16  # measured 1.2e-16; R's pnorm (Cody) is ~1e-16
+    assert np.isnan(debug_phi_tab(np.array([np.nan]))[0])
+
+
 def test_K_matches_reference_formula():
     rng = np.random.default_rng(0)
     x1, x2 = rng.standard_normal(257) * 2, rng.standard_normal(130) * 2
