@@ -382,6 +382,7 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
     want(&h->total_ll, 1);
     want(&h->flags, 1);
     want(&h->flags_x, gpirt::MAX_PEERS + 1);
+    want(&h->flags_c, gpirt::MAX_PEERS + 1);
     want(&h->chol_ws, chol_ws_ints(std::max(h->n, (int)NGRID)));
     const std::vector<uint32_t> tasks_n = h->n < 4096 ? chol_plan_tasks(h->n) : std::vector<uint32_t>(), tasks_N = chol_plan_tasks(NGRID);
     want(&h->chol_tasks_n, tasks_n.size());
@@ -437,6 +438,8 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (h->chol_aux.helper) { cudaStreamSynchronize(h->chol_aux.helper); cudaStreamDestroy(h->chol_aux.helper); }
     if (h->chol_aux.ev_panel) cudaEventDestroy(h->chol_aux.ev_panel);
     if (h->chol_aux.ev_rest) cudaEventDestroy(h->chol_aux.ev_rest);
+    for (int p = 0; p <= gpirt::MAX_PEERS; ++p)
+        if (h->chain_peer[p] && h->chain_peer_ipc[p] && h->chain_peer[p] != h->peer_arena[p]) cudaIpcCloseMemHandle(h->chain_peer[p]);
     for (char*& pa : h->peer_arena)
         if (pa) { cudaIpcCloseMemHandle(pa); pa = nullptr; }
     for (void* p : {(void*)h->d_z, (void*)h->d_u, (void*)h->theta_tab, (void*)h->mu_rows, (void*)h->arena})
@@ -949,13 +952,65 @@ static int need_data(gpirt_sampler* h) {
     return GPIRT_OK;
 }
 
+// in-chain exchange helpers (side stream): every rank runs the same sequence of exchange points, so epochs advance in lockstep without a host handshake
+static double* chain_peer_ptr(gpirt_sampler* h, int p, int which, const double* mine, const double* my_base) {
+    return (double*)(h->chain_peer[p] + h->chain_off[p][which]) + (mine - my_base);
+}
+static int chain_signal(gpirt_sampler* h, cudaStream_t st, unsigned long long epoch) {  // publish `epoch` in this rank's word on every peer
+    PeerPush pp{};
+    for (int p = 0; p < h->world; ++p)
+        if (p != h->rank) pp.flag[pp.count++] = (unsigned long long*)(h->chain_peer[p] + h->chain_off[p][gpirt_sampler::OFF_CFLAGS]) + h->rank;
+    CU(launch_signal_peers(st, pp, epoch));
+    return GPIRT_OK;
+}
+static int chain_wait(gpirt_sampler* h, cudaStream_t st, unsigned long long epoch, int only) {
+    CU(launch_wait_peers(st, h->flags_c, h->world, h->rank, epoch, h->flags, only));
+    return GPIRT_OK;
+}
+static int chain_push(gpirt_sampler* h, cudaStream_t st, int which, const double* my_base, const double* block, int ld, int rows, int cols) {
+    PeerBlockPush pb{};
+    for (int p = 0; p < h->world; ++p)
+        if (p != h->rank) pb.dst[pb.count++] = chain_peer_ptr(h, p, which, block, my_base);
+    CU(launch_push_block(st, block, ld, rows, cols, pb));
+    return GPIRT_OK;
+}
+
+
+// The Cholesky's exchange points (linalg.cuh CholDist): block b of 256 columns belongs to rank b % world; its owner pushes the updated block to every peer.
+struct ChainCholCtx { gpirt_sampler* h; unsigned long long base; };
+static cudaError_t chain_chol_push(void* ctx, cudaStream_t st, int block_id, double* blk, int ld, int rows, int cols) {
+    ChainCholCtx* c = (ChainCholCtx*)ctx;
+    if (chain_push(c->h, st, gpirt_sampler::OFF_L, c->h->L, blk, ld, rows, cols) != GPIRT_OK) return cudaErrorUnknown;
+    return chain_signal(c->h, st, c->base + (unsigned long long)block_id) == GPIRT_OK ? cudaSuccess : cudaErrorUnknown;
+}
+static cudaError_t chain_chol_wait(void* ctx, cudaStream_t st, int block_id, int owner) {
+    ChainCholCtx* c = (ChainCholCtx*)ctx;
+    return chain_wait(c->h, st, c->base + (unsigned long long)block_id, owner) == GPIRT_OK ? cudaSuccess : cudaErrorUnknown;
+}
+
 static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
     // row milestones (nu = L Z in slices under the factorisation) only exist on the per-panel path: the persistent kernel finishes all rows at once, and
     // one launch of the product reads Z once instead of once per slice (ncu: 382 MB against 305 MB of DRAM traffic for the five slices)
     const bool marks = st == h->side && h->L_rows.count > 0 && !chol_is_persistent(h->n, h->plan_n.state ? &h->plan_n : nullptr);
+    // Distributed chain (every rank is at this point of the same sweep: launch_theta_chain): first everything this rank writes into the matrices its peers
+    // push into — raw K into L, k* into W — then a barrier, so that no pushed block can be overwritten by its receiver's own construction.
+    ChainCholCtx cctx{h, 0};
+    CholDist cd;
+    const bool distributed = h->dist_chain && st == h->side && h->world > 1;
+    if (distributed) {
+        SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->tstar, NGRID, h->sds0, h->W, h->ldn, 0.0)));
+        h->kstar_built = true;
+        const unsigned long long e = ++h->chain_epoch;
+        TRY(chain_signal(h, st, e));
+        TRY(chain_wait(h, st, e, -1));
+        cctx.base = h->chain_epoch;
+        h->chain_epoch += (unsigned long long)chol_dist_blocks(h->n);
+        cd.rank = h->rank; cd.world = h->world; cd.ctx = &cctx; cd.push = chain_chol_push; cd.wait = chain_chol_wait;
+    }
     SEC_ST(h, st, "chol_K", CU(chol_lower_blocked(st, h->L, h->ldn, h->n, &h->flags->chol_info, h->chol_ws, marks ? &h->L_rows : nullptr,
-                                                      h->chol_aux.helper ? &h->chol_aux : nullptr, h->plan_n.state ? &h->plan_n : nullptr)));
+                                                      h->chol_aux.helper ? &h->chol_aux : nullptr, h->plan_n.state ? &h->plan_n : nullptr,
+                                                      distributed ? &cd : nullptr)));
     h->pending_rows = marks;
     h->chol_valid = true;
     h->shared_valid = false;
@@ -1016,22 +1071,43 @@ static int do_draw_f(gpirt_sampler* h, const gpirt_streams* s) {
 // L_post = chol(K_post), and W = L^-T tmp = K^-1 k*. Depends on theta only, so a sweep runs it on the side stream.
 static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_after_W = nullptr) {
     const int n = h->n, N = NGRID;
-    SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
+    const bool distributed = h->dist_chain && st == h->side && h->world > 1 && h->kstar_built && h->solver == 1;
+    if (!h->kstar_built) SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
+    h->kstar_built = false;
     const double* tmp = h->W;  // L^-1 k*
     if (h->solver == 1) {
         // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
         SEC_ST(h, st, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
+        // distributed: the grid points' columns are split over the ranks in runs of whole 64-column tiles (same tiles, same k ranges as the one launch);
+        // every rank forms its columns of tmp = L^-1 k* and of W = L^-T tmp and pushes both to its peers
+        int c_lo = 0, c_hi = N;
+        if (distributed) {
+            const int tiles = (N + 63) / 64, per = (tiles + h->world - 1) / h->world;
+            c_lo = std::min(N, h->rank * per * 64);
+            c_hi = std::min(N, (h->rank + 1) * per * 64);
+        }
         GemmArgs g{};
-        g.M = n; g.N = N; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W; g.ldb = h->ldn; g.C = h->W2; g.ldc = h->ldn;
+        g.M = n; g.N = c_hi - c_lo; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W + (size_t)c_lo * h->ldn; g.ldb = h->ldn;
+        g.C = h->W2 + (size_t)c_lo * h->ldn; g.ldc = h->ldn;
         g.alpha = 1.0; g.beta = 0.0; g.a_lower = 1;
         SEC_ST(h, st, "gemm_tmp", CU(gemm_f64(st, false, false, g)));
         tmp = h->W2;
         // W = L^-T tmp = K^-1 k*: the per-item mean k*^T (L^-T L^-1 f_j) (:51-52) becomes one contraction F^T W. Formed BEFORE K_post and its
         // Cholesky: the consumer's first product (F^T W) then starts while the latency-bound chol(K_post) is still running.
         GemmArgs w{};  // W = (L^-1)^T * tmp; op(A) = Linv^T is upper triangular
-        w.M = n; w.N = N; w.K = n; w.A = h->Linv; w.lda = h->ldn; w.B = h->W2; w.ldb = h->ldn; w.C = h->W; w.ldc = h->ldn;
+        w.M = n; w.N = c_hi - c_lo; w.K = n; w.A = h->Linv; w.lda = h->ldn; w.B = h->W2 + (size_t)c_lo * h->ldn; w.ldb = h->ldn;
+        w.C = h->W + (size_t)c_lo * h->ldn; w.ldc = h->ldn;
         w.alpha = 1.0; w.beta = 0.0; w.a_upper = 1;
         SEC_ST(h, st, "gemm_W", CU(gemm_f64(st, true, false, w)));
+        if (distributed) {
+            if (c_hi > c_lo) {
+                TRY(chain_push(h, st, gpirt_sampler::OFF_W2, h->W2, h->W2 + (size_t)c_lo * h->ldn, h->ldn, n, c_hi - c_lo));
+                TRY(chain_push(h, st, gpirt_sampler::OFF_W, h->W, h->W + (size_t)c_lo * h->ldn, h->ldn, n, c_hi - c_lo));
+            }
+            const unsigned long long e = ++h->chain_epoch;
+            TRY(chain_signal(h, st, e));
+            TRY(chain_wait(h, st, e, -1));
+        }
         if (ev_after_W) CU(cudaEventRecord(ev_after_W, st));
     } else {
         SEC_ST(h, st, "trsm_kstar", CU(trsm_left_lower(st, h->L, h->ldn, n, h->W, h->ldn, N)));
@@ -1318,6 +1394,77 @@ int gpirt_peer_wait(gpirt_sampler* h) {
     CU(launch_wait_peers(h->stream, h->flags_x, h->world, h->rank, h->push_epoch, h->flags));
     return GPIRT_OK;
 }
+// ---- distributed theta-only chain: peers' chain buffers (one process per GPU: cudaIpc; one process, several GPUs: the pointers themselves) ----
+int gpirt_chain_export(gpirt_sampler* h, void* handle64, int64_t* offsets6) {
+    CHECK_H(h);
+    if (!handle64 || !offsets6) return fail(GPIRT_ERR_INVALID, "chain_export: NULL output");
+    CU(cudaSetDevice(h->cfg.device));
+    CU(cudaStreamSynchronize(h->stream));  // the arena's zero fill (flag words included) is complete before anyone maps it
+    offsets6[gpirt_sampler::OFF_L] = (int64_t)((char*)h->L - h->arena);
+    offsets6[gpirt_sampler::OFF_LINV] = (int64_t)((char*)h->Linv - h->arena);
+    offsets6[gpirt_sampler::OFF_W] = (int64_t)((char*)h->W - h->arena);
+    offsets6[gpirt_sampler::OFF_W2] = (int64_t)((char*)h->W2 - h->arena);
+    offsets6[gpirt_sampler::OFF_CFLAGS] = (int64_t)((char*)h->flags_c - h->arena);
+    offsets6[5] = (int64_t)(intptr_t)h->arena;  // meaningful inside the exporting process only
+    cudaIpcMemHandle_t mh;
+    CU(cudaIpcGetMemHandle(&mh, h->arena));
+    std::memcpy(handle64, &mh, 64);
+    return GPIRT_OK;
+}
+// handle64 != NULL: the peer lives in another process (IPC mapping); NULL: in this one (offsets6[5] is its arena; peer access between two GPUs is enabled
+// here). Once world - 1 peers are attached and n >= 4096 the theta-only chain of a sweep is distributed (capi.cu).
+int gpirt_chain_attach(gpirt_sampler* h, int peer_rank, const void* handle64, const int64_t* offsets6) {
+    CHECK_H(h);
+    if (!offsets6 || peer_rank < 0 || peer_rank >= h->world || peer_rank == h->rank || h->world > gpirt::MAX_PEERS + 1)
+        return fail(GPIRT_ERR_INVALID, "chain_attach: peer rank %d of a world of %d (at most %d ranks)", peer_rank, h->world, gpirt::MAX_PEERS + 1);
+    if (h->chain_peer[peer_rank]) return fail(GPIRT_ERR_INVALID, "chain_attach: rank %d is attached already", peer_rank);
+    CU(cudaSetDevice(h->cfg.device));
+    if (handle64) {
+        if (h->peer_arena[peer_rank]) h->chain_peer[peer_rank] = h->peer_arena[peer_rank];  // mapped already for the f* push
+        else {
+            cudaIpcMemHandle_t mh;
+            std::memcpy(&mh, handle64, 64);
+            void* base = nullptr;
+            CU(cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+            h->chain_peer[peer_rank] = (char*)base;
+            h->chain_peer_ipc[peer_rank] = true;
+        }
+    } else {
+        h->chain_peer[peer_rank] = (char*)(intptr_t)offsets6[5];
+        cudaPointerAttributes pa{};
+        CU(cudaPointerGetAttributes(&pa, h->chain_peer[peer_rank]));
+        if (pa.type != cudaMemoryTypeDevice) return fail(GPIRT_ERR_INVALID, "chain_attach: offsets6[5] is not a device address of this process");
+        if (pa.device != h->cfg.device) {  // this GPU's kernels store into the peer's arena over NVLink
+            int can = 0;
+            CU(cudaDeviceCanAccessPeer(&can, h->cfg.device, pa.device));
+            if (!can) return fail(GPIRT_ERR_INVALID, "chain_attach: device %d has no peer access to device %d", h->cfg.device, pa.device);
+            cudaError_t pe = cudaDeviceEnablePeerAccess(pa.device, 0);
+            if (pe == cudaErrorPeerAccessAlreadyEnabled) (void)cudaGetLastError();
+            else CU(pe);
+        }
+    }
+    for (int k = 0; k < gpirt_sampler::N_CHAIN_OFFS; ++k) h->chain_off[peer_rank][k] = (size_t)offsets6[k];
+    h->chain_attached += 1;
+    static const int enabled = getenv("GPIRT_DIST_CHAIN") ? atoi(getenv("GPIRT_DIST_CHAIN")) : 1;
+    static const int min_n = getenv("GPIRT_DIST_CHAIN_MIN_N") ? atoi(getenv("GPIRT_DIST_CHAIN_MIN_N")) : 4096;
+    h->dist_chain = enabled && h->chain_attached == h->world - 1 && h->n >= min_n;
+    return GPIRT_OK;
+}
+int gpirt_chain_detach(gpirt_sampler* h) {
+    CHECK_H(h);
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(quiesce(h));
+    CU(cudaStreamSynchronize(h->stream));
+    for (int p = 0; p <= gpirt::MAX_PEERS; ++p) {
+        if (h->chain_peer[p] && h->chain_peer_ipc[p] && h->chain_peer[p] != h->peer_arena[p]) CU(cudaIpcCloseMemHandle(h->chain_peer[p]));
+        h->chain_peer[p] = nullptr;
+        h->chain_peer_ipc[p] = false;
+    }
+    h->chain_attached = 0;
+    h->dist_chain = false;
+    return GPIRT_OK;
+}
+
 int gpirt_sweep_phase_theta(gpirt_sampler* h) { ENTER(h); return do_draw_theta(h, nullptr); }
 
 // ---- item-sharded theta step (samplers.cuh ThetaItemsView): begin, then rounds of { partials, exchange THETA_PART, decide } until nobody is active ----

@@ -345,6 +345,19 @@ static int mcmc_sharded(const gpirt_mcmc_args* a, const std::vector<int>& devs) 
         if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h[r], a->f_init_z));
         TRYC(gpirt_set_iter(h[r], 0));
     }
+    {   // config-4 sizes with every shard on a GPU of its own: the theta-only chain is distributed over the shards (gpirt_chain_*, same process: no IPC)
+        bool distinct = true;
+        for (int r = 0; r < W; ++r)
+            for (int q = 0; q < r; ++q) distinct = distinct && devs[r] != devs[q];
+        if (distinct && a->n >= 4096) {
+            std::vector<int64_t> offs((size_t)W * 6);
+            unsigned char dummy[64];
+            for (int r = 0; r < W; ++r) TRYC(gpirt_chain_export(h[r], dummy, &offs[(size_t)r * 6]));
+            for (int r = 0; r < W; ++r)
+                for (int q = 0; q < W; ++q)
+                    if (q != r) TRYC(gpirt_chain_attach(h[r], q, nullptr, &offs[(size_t)q * 6]));
+        }
+    }
     auto exchange = [&](int which) -> int {
         for (int q = 0; q < W; ++q)
             for (int r = 0; r < W; ++r)
@@ -397,6 +410,7 @@ static int mcmc_sharded(const gpirt_mcmc_args* a, const std::vector<int>& devs) 
     }
     if (n_samples > 0) TRYC(flush());
     for (int r = 0; r < W; ++r) TRYC(gpirt_sync(h[r]));
+    for (int r = 0; r < W; ++r) TRYC(gpirt_chain_detach(h[r]));  // before any shard's arena is freed
     return GPIRT_OK;
 }
 

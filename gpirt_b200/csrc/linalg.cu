@@ -503,7 +503,7 @@ bool chol_is_persistent(int n, const CholPlan* plan) {
 }
 
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks,
-                               const CholAux* aux, const CholPlan* plan) {
+                               const CholAux* aux, const CholPlan* plan, const CholDist* dist) {
     if (chol_is_persistent(n, plan)) {
         cudaError_t e = chol_lower_persistent(st, A, ld, n, info_dev, plan->state, plan->tasks, plan->n_tasks, plan->max_ctas);
         if (e != cudaSuccess) return e;
@@ -522,9 +522,17 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
     // DMMA GEMM runs near its peak. At n = 2000 the K = 64 updates are latency-bound launches either way (no gain, profiles/
     // r01_gemm_tiles.txt: OB = NB there); at n = 10 000 (config C4) the flops dominate and the K = 64 updates reach only ~16 TFLOP/s.
     static const int ob_env = getenv("GPIRT_CHOL_OB") ? atoi(getenv("GPIRT_CHOL_OB")) : 0;
-    const int OB = ob_env > 0 ? ob_env : (n >= 4096 ? 256 : NB);
+    const bool distributed = dist && dist->world > 1 && dist->push && dist->wait && n >= 4096;
+    const int OB = distributed ? 256 : (ob_env > 0 ? ob_env : (n >= 4096 ? 256 : NB));
     for (int o0 = 0; o0 < n; o0 += OB) {
         const int ob = (n - o0 < OB) ? n - o0 : OB;
+        if (distributed && o0 > 0) {  // columns [o0, o0 + ob), rows o0 .. n-1, as updated by their owner
+            const int b = o0 / OB, owner = b % dist->world;
+            if (owner != dist->rank) {
+                cudaError_t ew = dist->wait(dist->ctx, st, b, owner);
+                if (ew != cudaSuccess) return ew;
+            }
+        }
         for (int k0 = o0; k0 < o0 + ob; k0 += NB) {
             const int kb = (n - k0 < NB) ? n - k0 : NB;
             double* Akk = A + (size_t)k0 * ld + k0;
@@ -549,6 +557,23 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
             }
         }
         const int rows_t = n - o0 - ob;
+        if (distributed && rows_t > 0) {
+            double* P = A + (size_t)o0 * ld + (o0 + ob);  // rows below the outer block, its ob columns
+            for (int c0 = 0; c0 < rows_t; c0 += OB) {      // this rank's column blocks of the trailing matrix; c0 == 0 is the next outer block
+                const int b = (o0 + ob + c0) / OB;
+                if (b % dist->world != dist->rank) continue;
+                const int w = (rows_t - c0 < OB) ? rows_t - c0 : OB;
+                GemmArgs g{};
+                g.M = rows_t - c0; g.N = w; g.K = ob;
+                g.A = P + c0; g.lda = ld; g.B = P + c0; g.ldb = ld;
+                g.C = A + (size_t)(o0 + ob + c0) * ld + (o0 + ob + c0); g.ldc = ld;
+                g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
+                cudaError_t e = gemm_f64(st, false, true, g);
+                if (e != cudaSuccess) return e;
+                if (c0 == 0 && (e = dist->push(dist->ctx, st, b, g.C, ld, rows_t, w)) != cudaSuccess) return e;  // before this rank's other blocks: the peers' panels wait for it
+            }
+            continue;
+        }
         if (OB != NB && rows_t > 0) {
             double* P = A + (size_t)o0 * ld + (o0 + ob);  // rows below the outer block, its ob columns
             const bool split = aux && aux->helper && lookahead_env && rows_t > OB;

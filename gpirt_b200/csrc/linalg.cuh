@@ -50,9 +50,20 @@ std::vector<uint32_t> chol_plan_tasks(int n);
 // info_dev: 0, the failing leading minor (1-based), or -1 when the kernel gave up waiting (never on a healthy device)
 cudaError_t chol_lower_persistent(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* state_dev, const uint32_t* tasks_dev, int n_tasks,
                                   int max_ctas, long long* trace_dev = nullptr);
+// Two-level factorisation (n >= 4096) distributed over `world` ranks that each hold the whole matrix: outer block b (256 columns) belongs to rank
+// b % world. After the panels of an outer block every rank applies the K = 256 trailing update to ITS column blocks only (same tiles, same k order as
+// the single launch: the factor is the one-GPU factor), the owner of the next outer block updates that block first and `push`es it (rows from its
+// diagonal down) into every peer's matrix; the others `wait` for it before they factor its panels. Every rank ends with the whole L.
+struct CholDist {
+    int rank = 0, world = 1;
+    void* ctx = nullptr;
+    cudaError_t (*push)(void* ctx, cudaStream_t st, int block_id, double* block, int ld, int rows, int cols) = nullptr;
+    cudaError_t (*wait)(void* ctx, cudaStream_t st, int block_id, int owner) = nullptr;
+};
+inline int chol_dist_blocks(int n) { return (n + 255) / 256; }  // exchange points a distributed factorisation of n columns may use (block ids 1 .. blocks-1)
 // plan != nullptr and n below the two-level threshold: the persistent kernel; milestones are then all recorded at the end.
 cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* info_dev, int* readers_ws, const CholMilestones* marks = nullptr,
-                               const CholAux* aux = nullptr, const CholPlan* plan = nullptr);
+                               const CholAux* aux = nullptr, const CholPlan* plan = nullptr, const CholDist* dist = nullptr);
 // B <- L^-1 B and B <- L^-T B for an n x nrhs right-hand side, in place.
 cudaError_t trsm_left_lower(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);
 cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, double* B, int ldb, int nrhs);

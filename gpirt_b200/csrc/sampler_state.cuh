@@ -108,6 +108,16 @@ struct gpirt_sampler {
     size_t peer_fstar_off[gpirt::MAX_PEERS + 1] = {}, peer_flags_off[gpirt::MAX_PEERS + 1] = {};  // where the peer keeps its f* table / flag words
     int peers_attached = 0;
     unsigned long long push_epoch = 0;
+    // Distributed theta-only chain (item shards with n >= 4096, capi.cu "distributed chain"): the peers' L / L^-1 / W / W2 matrices and chain flag words.
+    enum { OFF_L = 0, OFF_LINV = 1, OFF_W = 2, OFF_W2 = 3, OFF_CFLAGS = 4, N_CHAIN_OFFS = 5 };
+    unsigned long long* flags_c = nullptr;             // [MAX_PEERS + 1] chain epochs, word p written by rank p (monotonic)
+    char* chain_peer[gpirt::MAX_PEERS + 1] = {};       // base of peer p's arena as this process / device can address it (IPC mapping or the pointer itself)
+    bool chain_peer_ipc[gpirt::MAX_PEERS + 1] = {};    // opened here with cudaIpcOpenMemHandle (closed at detach)
+    size_t chain_off[gpirt::MAX_PEERS + 1][N_CHAIN_OFFS] = {};
+    int chain_attached = 0;
+    unsigned long long chain_epoch = 0;                // advanced identically on every rank (the exchange points of the chain are a fixed program order)
+    bool dist_chain = false;
+    bool kstar_built = false;                          // k* is in W already (the distributed chain builds it before its start barrier)
     size_t d_z_cap = 0, d_u_cap = 0;
     // device-side store of the draws gpirtMCMC keeps (src/gpirtMCMC.cpp:230-255,334-356): appended on the stream, read back in bulk
     struct DrawStore {

@@ -859,9 +859,9 @@ cudaError_t launch_signal_peers(cudaStream_t st, const PeerPush& peers, unsigned
 
 // Holds the stream until every peer's flag word has reached `epoch` (their chunks of the f* table are then complete in this GPU's memory).
 // Bounded: after ~4 s without progress it reports peer_timeout instead of hanging the device.
-__global__ void k_wait_peers(const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags) {
+__global__ void k_wait_peers(const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags, int only) {
     const int p = threadIdx.x;
-    if (p < world && p != rank) {
+    if (p < world && p != rank && (only < 0 || p == only)) {
         const volatile unsigned long long* f = flags + p;
         unsigned long long t0 = 0;
         asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -877,8 +877,32 @@ __global__ void k_wait_peers(const unsigned long long* flags, int world, int ran
     }
     __threadfence_system();
 }
-cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags) {
-    k_wait_peers<<<1, 32, 0, st>>>(flags, world, rank, epoch, dev_flags);
+cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags, int only) {
+    k_wait_peers<<<1, 32, 0, st>>>(flags, world, rank, epoch, dev_flags, only);
+    ++g_kernel_launches;
+    return cudaGetLastError();
+}
+
+// one thread per pair of rows of one column; 16-byte loads and stores where the pair is whole
+__global__ void __launch_bounds__(128) k_push_block(const double* __restrict__ src, int ld, int rows, int cols, PeerBlockPush pb) {
+    const int r = 2 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int c = blockIdx.y;
+    if (r >= rows || c >= cols) return;
+    const size_t off = (size_t)c * ld + r;
+    if (r + 1 < rows) {
+        const double2 v = *reinterpret_cast<const double2*>(src + off);
+#pragma unroll 1
+        for (int p = 0; p < pb.count; ++p) *reinterpret_cast<double2*>(pb.dst[p] + off) = v;
+    } else {
+        const double v = src[off];
+#pragma unroll 1
+        for (int p = 0; p < pb.count; ++p) pb.dst[p][off] = v;
+    }
+}
+cudaError_t launch_push_block(cudaStream_t st, const double* src, int ld, int rows, int cols, const PeerBlockPush& pb) {
+    if (rows <= 0 || cols <= 0 || pb.count <= 0) return cudaSuccess;
+    dim3 grid(((rows + 1) / 2 + 127) / 128, cols);
+    k_push_block<<<grid, 128, 0, st>>>(src, ld, rows, cols, pb);
     ++g_kernel_launches;
     return cudaGetLastError();
 }

@@ -166,7 +166,12 @@ cudaError_t launch_add_mustar(cudaStream_t st, double* fstar_chunk, int ld_chunk
 cudaError_t launch_add_mustar_push(cudaStream_t st, double* fstar_chunk, int ld_chunk, int m_local, int item0, const double* beta, int p_beta,
                                    const PeerPush& peers);
 cudaError_t launch_signal_peers(cudaStream_t st, const PeerPush& peers, unsigned long long epoch);
-cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags);
+// only < 0: every peer's word must reach `epoch`; only >= 0: the word of that rank alone (a broadcast from one owner)
+cudaError_t launch_wait_peers(cudaStream_t st, const unsigned long long* flags, int world, int rank, unsigned long long epoch, DevFlags* dev_flags, int only = -1);
+// a rows x cols block (column-major, leading dimension ld, the same on every rank) copied to the same place of every peer's matrix: dst[p] points at
+// the block's first element in peer p's memory (NVLink peer mapping). Rows start at a multiple of 2 of a 16-byte aligned matrix.
+struct PeerBlockPush { int count; double* dst[MAX_PEERS]; };
+cudaError_t launch_push_block(cudaStream_t st, const double* src, int ld, int rows, int cols, const PeerBlockPush& pb);
 // sum of per-item values in index order (src/gpirtMCMC.cpp:325-331 accumulates item by item)
 cudaError_t launch_ordered_sum(cudaStream_t st, const double* x, int n, double* out);
 // layout converters between the reference's N x m column-major f* and the grid-row-major device table

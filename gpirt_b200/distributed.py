@@ -83,6 +83,18 @@ class ShardedSampler:
             ptr, chunk_bytes = self.S.exchange_buffer(name)
             self._bufs[name] = torch.as_tensor(_DevBuf(ptr, chunk_bytes * world), device=f"cuda:{device}")
         self.theta_rounds = 0  # exchange rounds of the last item-sharded theta step
+        # config-4 sizes: the theta-only chain (Cholesky of K, L^-1 k*, K^-1 k*) is distributed over the ranks through NVLink peer memory instead of being
+        # recomputed on every one of them (include/gpirt_b200.h gpirt_chain_*): every rank maps its peers' arenas
+        self.dist_chain = world > 1 and n >= int(os.environ.get("GPIRT_DIST_CHAIN_MIN_N", "4096")) and os.environ.get("GPIRT_DIST_CHAIN", "1") != "0"
+        if self.dist_chain:
+            import torch.distributed as dist
+
+            exports = [None] * world
+            dist.all_gather_object(exports, self.S.chain_export(), group=group)
+            for r, ex in enumerate(exports):
+                if r != rank:
+                    self.S.chain_attach(r, ex)
+            dist.barrier(group=group)
         self.p2p = world > 1 and self.theta_shard == "respondents" and os.environ.get("GPIRT_FSTAR_EXCHANGE", "nccl") == "p2p"
         if self.p2p:
             import torch.distributed as dist
@@ -134,6 +146,13 @@ class ShardedSampler:
         return self.S.total_ll()
 
     def close(self):
+        if self.dist_chain:  # no rank frees its arena while a peer still maps it
+            import torch.distributed as dist
+
+            self.S.sync()
+            self.S.chain_detach()
+            dist.barrier(group=self.group)
+            self.dist_chain = False
         if self.p2p:  # no rank frees its arena while a peer still maps it
             import torch.distributed as dist
 
@@ -213,6 +232,16 @@ class LocalShards:
             self.S.append(S)
             self._bufs.append(bufs)
         self.theta_rounds = 0
+        # the distributed theta-only chain (n >= 4096) needs every shard on a GPU of its own: its exchange points are spinning wait kernels, which on a shared
+        # device can be queued in front of the very kernels they wait for
+        distinct = len(set(self.devices)) == self.world or os.environ.get("GPIRT_DIST_CHAIN_SAME_DEVICE") == "1"  # the override: experiments only
+        self.dist_chain = distinct and n >= int(os.environ.get("GPIRT_DIST_CHAIN_MIN_N", "4096")) and os.environ.get("GPIRT_DIST_CHAIN", "1") != "0"
+        if self.dist_chain:
+            exports = [S.chain_export() for S in self.S]
+            for r, S in enumerate(self.S):
+                for q, ex in enumerate(exports):
+                    if q != r:
+                        S.chain_attach(q, ex, same_process=True)
 
     def _gather(self, name):
         chunk = self._bufs[0][name].numel() // self.world
@@ -300,4 +329,7 @@ class LocalShards:
         return self.S[0].total_ll()
 
     def close(self):
+        if self.dist_chain:
+            self._each("sync")
+            self._each("chain_detach")
         self._each("close")

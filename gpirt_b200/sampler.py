@@ -334,6 +334,21 @@ class Sampler:
     def peer_wait(self):
         check(self._L.gpirt_peer_wait(self._h))
 
+    # ---- distributed theta-only chain (n >= 4096 on item shards): the peers' chain buffers ----
+    def chain_export(self):
+        buf, offs = (C.c_ubyte * 64)(), (C.c_int64 * 6)()
+        check(self._L.gpirt_chain_export(self._h, buf, offs))
+        return bytes(buf), list(offs)
+
+    def chain_attach(self, peer_rank, exported, same_process=False):
+        handle, offs = exported
+        o = (C.c_int64 * 6)(*offs)
+        buf = None if same_process else (C.c_ubyte * 64).from_buffer_copy(handle)
+        check(self._L.gpirt_chain_attach(self._h, int(peer_rank), buf, o))
+
+    def chain_detach(self):
+        check(self._L.gpirt_chain_detach(self._h))
+
     def exchange_buffer(self, which):
         ptr, nbytes = C.c_void_p(), C.c_int64()
         check(self._L.gpirt_exchange_buffer(self._h, _lib.XCHG[which], C.byref(ptr), C.byref(nbytes)))
