@@ -529,7 +529,7 @@ static int check_flags(gpirt_sampler* h) {
     CU(cudaStreamSynchronize(h->stream));
     if (fl.chol_info || fl.chol_post_info || fl.overrun || fl.stalled || fl.bad_code || fl.peer_timeout) {
         CU(cudaMemsetAsync(h->flags, 0, sizeof(fl), h->stream));
-        if (fl.peer_timeout) return fail(GPIRT_ERR_CUDA, "f* exchange: the chunk of rank %d did not arrive within 4 s", fl.peer_timeout - 1);
+        if (fl.peer_timeout) return fail(GPIRT_ERR_CUDA, "peer exchange (f* chunks / the distributed theta-only chain): what rank %d publishes did not arrive within 4 s", fl.peer_timeout - 1);
         if (fl.bad_code) return fail(GPIRT_ERR_CATEGORIES, "response code outside 1..%d", h->C);
         if (fl.chol_info < 0 || fl.chol_post_info < 0) return fail(GPIRT_ERR_CUDA, "chol(): the persistent factorisation kernel gave up waiting for a tile (device stalled?)");
         if (fl.chol_info) return fail(GPIRT_ERR_NOT_PD, "chol(): decomposition failed: K(theta,theta) + 1e-6 I not positive definite at leading minor %d", fl.chol_info);
@@ -988,6 +988,17 @@ static cudaError_t chain_chol_wait(void* ctx, cudaStream_t st, int block_id, int
     return chain_wait(c->h, st, c->base + (unsigned long long)block_id, owner) == GPIRT_OK ? cudaSuccess : cudaErrorUnknown;
 }
 
+// trtri's exchange points (linalg.cuh TrtriDist)
+static cudaError_t chain_trtri_push(void* ctx, cudaStream_t st, double* blk, int ld, int rows, int cols) {
+    gpirt_sampler* h = (gpirt_sampler*)ctx;
+    return chain_push(h, st, gpirt_sampler::OFF_LINV, h->Linv, blk, ld, rows, cols) == GPIRT_OK ? cudaSuccess : cudaErrorUnknown;
+}
+static cudaError_t chain_trtri_sync(void* ctx, cudaStream_t st) {
+    gpirt_sampler* h = (gpirt_sampler*)ctx;
+    const unsigned long long e = ++h->chain_epoch;
+    return chain_signal(h, st, e) == GPIRT_OK && chain_wait(h, st, e, -1) == GPIRT_OK ? cudaSuccess : cudaErrorUnknown;
+}
+
 static int do_update_cholesky(gpirt_sampler* h, cudaStream_t st) {  // src/cholesky-cache.cpp:20-24
     SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, h->n, h->theta, h->n, h->sds0, h->L, h->ldn, 1e-6)));
     // row milestones (nu = L Z in slices under the factorisation) only exist on the per-panel path: the persistent kernel finishes all rows at once, and
@@ -1077,7 +1088,9 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     const double* tmp = h->W;  // L^-1 k*
     if (h->solver == 1) {
         // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
-        SEC_ST(h, st, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch)));
+        TrtriDist td;
+        td.rank = h->rank; td.world = h->world; td.ctx = h; td.push = chain_trtri_push; td.sync = chain_trtri_sync;
+        SEC_ST(h, st, "trtri", CU(trtri_lower(st, h->L, h->ldn, n, h->Linv, h->ldn, h->tri_scratch, distributed ? &td : nullptr)));
         // distributed: the grid points' columns are split over the ranks in runs of whole 64-column tiles (same tiles, same k ranges as the one launch);
         // every rank forms its columns of tmp = L^-1 k* and of W = L^-T tmp and pushes both to its peers
         int c_lo = 0, c_hi = N;

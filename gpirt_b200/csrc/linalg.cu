@@ -559,18 +559,40 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
         const int rows_t = n - o0 - ob;
         if (distributed && rows_t > 0) {
             double* P = A + (size_t)o0 * ld + (o0 + ob);  // rows below the outer block, its ob columns
-            for (int c0 = 0; c0 < rows_t; c0 += OB) {      // this rank's column blocks of the trailing matrix; c0 == 0 is the next outer block
-                const int b = (o0 + ob + c0) / OB;
-                if (b % dist->world != dist->rank) continue;
+            const bool ahead = aux && aux->helper && lookahead_env;
+            cudaError_t e;
+            auto update_block = [&](cudaStream_t s, int c0) {  // column block (o0 + ob + c0) / OB of the trailing matrix, from its diagonal down
                 const int w = (rows_t - c0 < OB) ? rows_t - c0 : OB;
                 GemmArgs g{};
                 g.M = rows_t - c0; g.N = w; g.K = ob;
                 g.A = P + c0; g.lda = ld; g.B = P + c0; g.ldb = ld;
                 g.C = A + (size_t)(o0 + ob + c0) * ld + (o0 + ob + c0); g.ldc = ld;
                 g.alpha = -1.0; g.beta = 1.0; g.lower_only = 1;
-                cudaError_t e = gemm_f64(st, false, true, g);
-                if (e != cudaSuccess) return e;
-                if (c0 == 0 && (e = dist->push(dist->ctx, st, b, g.C, ld, rows_t, w)) != cudaSuccess) return e;  // before this rank's other blocks: the peers' panels wait for it
+                return gemm_f64(s, false, true, g);
+            };
+            if (ahead && (e = cudaEventRecord(aux->ev_panel, st)) != cudaSuccess) return e;
+            const int b_next = (o0 + ob) / OB;
+            if (b_next % dist->world == dist->rank) {  // the next outer block is this rank's: updated first, on the panels' stream, and published
+                if (rest_pending) {  // its earlier updates ran on the helper stream
+                    if ((e = cudaStreamWaitEvent(st, aux->ev_rest, 0)) != cudaSuccess) return e;
+                    rest_pending = false;
+                }
+                if ((e = update_block(st, 0)) != cudaSuccess) return e;
+                const int w = rows_t < OB ? rows_t : OB;
+                if ((e = dist->push(dist->ctx, st, b_next, A + (size_t)(o0 + ob) * ld + (o0 + ob), ld, rows_t, w)) != cudaSuccess) return e;
+            }
+            // this rank's other column blocks: under the next outer block's panels (helper stream), which only need the block just published
+            cudaStream_t s2 = ahead ? aux->helper : st;
+            bool any = false;
+            for (int c0 = OB; c0 < rows_t; c0 += OB) {
+                if (((o0 + ob + c0) / OB) % dist->world != dist->rank) continue;
+                if (!any && ahead && (e = cudaStreamWaitEvent(s2, aux->ev_panel, 0)) != cudaSuccess) return e;
+                any = true;
+                if ((e = update_block(s2, c0)) != cudaSuccess) return e;
+            }
+            if (any && ahead) {
+                if ((e = cudaEventRecord(aux->ev_rest, s2)) != cudaSuccess) return e;
+                rest_pending = true;
             }
             continue;
         }
@@ -670,7 +692,7 @@ size_t trtri_scratch_elems(int n) {
 // merge levels: inv([A 0; C B]) = [A^-1 0; -B^-1 C A^-1  B^-1], each level two batched GEMMs over all pairs. No sequential chain
 // over the n/64 block rows, unlike a blocked TRSM: 1 + 2*levels launches in total. Linv's strict upper triangle must be zero on
 // entry (it is never written).
-cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch) {
+cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch, const TrtriDist* dist) {
     constexpr int NB = CHOL_NB;
     k_trtri_diag<<<(n + NB - 1) / NB, TILE_THREADS, 0, st>>>(L, ld, n, Linv, ldi);
     ++g_kernel_launches;
@@ -679,24 +701,45 @@ cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double*
         int pairs = 0, last_b2 = 0;
         for (int r0 = 0; r0 + b < n; r0 += 2 * b) { ++pairs; last_b2 = (n - r0 - b < b) ? n - r0 - b : b; }
         if (pairs == 0) break;
-        GemmArgs g{};  // T_z = C_z * A_z^-1   (C_z = L[r0+b.., r0..], A_z^-1 lower triangular)
-        g.M = b; g.N = b; g.K = b;
-        g.A = L + b; g.lda = ld; g.strideA = (long long)2 * b * ((long long)ld + 1);
-        g.B = Linv; g.ldb = ldi; g.strideB = (long long)2 * b * ((long long)ldi + 1); g.b_lower = 1;
-        g.C = scratch; g.ldc = b; g.strideC = (long long)b * b;
-        g.alpha = 1.0; g.beta = 0.0; g.batch = pairs > 1 ? pairs : 0; g.M_last = last_b2;
-        if (pairs == 1) g.M = last_b2;
-        cudaError_t e = gemm_f64(st, false, false, g);
-        if (e != cudaSuccess) return e;
-        GemmArgs h{};  // Linv[r0+b.., r0..] = -B_z^-1 * T_z   (B_z^-1 lower triangular)
-        h.M = b; h.N = b; h.K = b;
-        h.A = Linv + (size_t)b * ldi + b; h.lda = ldi; h.strideA = (long long)2 * b * ((long long)ldi + 1); h.a_lower = 1;
-        h.B = scratch; h.ldb = b; h.strideB = (long long)b * b;
-        h.C = Linv + b; h.ldc = ldi; h.strideC = (long long)2 * b * ((long long)ldi + 1);
-        h.alpha = -1.0; h.beta = 0.0; h.batch = pairs > 1 ? pairs : 0; h.M_last = last_b2; h.K_last = last_b2;
-        if (pairs == 1) { h.M = last_b2; h.K = last_b2; }
-        e = gemm_f64(st, false, false, h);
-        if (e != cudaSuccess) return e;
+        // this rank's columns [c_lo, c_hi) of every pair's b x b block. Work per column at relative position x: 2(1 - x) in the first product (A^-1 is
+        // lower triangular) + 1 in the second: the cumulative 3x - x^2 is cut into `world` equal parts.
+        const bool split = dist && dist->world > 1 && dist->push && dist->sync && b >= 512 && b / 64 >= dist->world;
+        int c_lo = 0, c_hi = b;
+        if (split) {
+            auto cut = [&](int r) {
+                if (r <= 0) return 0;
+                if (r >= dist->world) return b;
+                const double x = (3.0 - sqrt(9.0 - 8.0 * (double)r / dist->world)) * 0.5;
+                int c = (int)(x * (b / 64) + 0.5) * 64;
+                return c < 0 ? 0 : (c > b ? b : c);
+            };
+            c_lo = cut(dist->rank);
+            c_hi = cut(dist->rank + 1);
+        }
+        cudaError_t e;
+        if (c_hi > c_lo) {
+            GemmArgs g{};  // T_z = C_z * A_z^-1   (C_z = L[r0+b.., r0..], A_z^-1 lower triangular)
+            g.M = b; g.N = c_hi - c_lo; g.K = b; g.n_off = c_lo;
+            g.A = L + b; g.lda = ld; g.strideA = (long long)2 * b * ((long long)ld + 1);
+            g.B = Linv + (size_t)c_lo * ldi; g.ldb = ldi; g.strideB = (long long)2 * b * ((long long)ldi + 1); g.b_lower = 1;
+            g.C = scratch + (size_t)c_lo * b; g.ldc = b; g.strideC = (long long)b * b;
+            g.alpha = 1.0; g.beta = 0.0; g.batch = pairs > 1 ? pairs : 0; g.M_last = last_b2;
+            if (pairs == 1) g.M = last_b2;
+            if ((e = gemm_f64(st, false, false, g)) != cudaSuccess) return e;
+            GemmArgs h{};  // Linv[r0+b.., r0..] = -B_z^-1 * T_z   (B_z^-1 lower triangular)
+            h.M = b; h.N = c_hi - c_lo; h.K = b;
+            h.A = Linv + (size_t)b * ldi + b; h.lda = ldi; h.strideA = (long long)2 * b * ((long long)ldi + 1); h.a_lower = 1;
+            h.B = scratch + (size_t)c_lo * b; h.ldb = b; h.strideB = (long long)b * b;
+            h.C = Linv + b + (size_t)c_lo * ldi; h.ldc = ldi; h.strideC = (long long)2 * b * ((long long)ldi + 1);
+            h.alpha = -1.0; h.beta = 0.0; h.batch = pairs > 1 ? pairs : 0; h.M_last = last_b2; h.K_last = last_b2;
+            if (pairs == 1) { h.M = last_b2; h.K = last_b2; }
+            if ((e = gemm_f64(st, false, false, h)) != cudaSuccess) return e;
+            for (int z = 0; split && z < pairs; ++z) {
+                double* blk = Linv + b + (size_t)z * 2 * b * ((size_t)ldi + 1) + (size_t)c_lo * ldi;
+                if ((e = dist->push(dist->ctx, st, blk, ldi, z == pairs - 1 ? last_b2 : b, c_hi - c_lo)) != cudaSuccess) return e;
+            }
+        }
+        if (split && (e = dist->sync(dist->ctx, st)) != cudaSuccess) return e;
     }
     return cudaGetLastError();
 }

@@ -70,6 +70,15 @@ cudaError_t trsm_left_lower_t(cudaStream_t st, const double* L, int ldl, int n, 
 
 // Linv <- L^-1 (lower triangular, strict upper triangle of Linv must already be zero); scratch holds trtri_scratch_elems(n) doubles.
 size_t trtri_scratch_elems(int n);
-cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch);
+// dist: the merge levels with blocks of 512 columns or more (all but 1/8 of the flops at config-4 sizes) are split by COLUMNS of every pair's block over
+// the ranks — both products of a level are column-wise independent — at 64-column tile boundaries placed so that the two products' work together is even
+// (the first one is triangular in its columns); every rank `push`es its columns of the new blocks into its peers' Linv and all `sync` once per level.
+struct TrtriDist {
+    int rank = 0, world = 1;
+    void* ctx = nullptr;
+    cudaError_t (*push)(void* ctx, cudaStream_t st, double* block, int ld, int rows, int cols) = nullptr;
+    cudaError_t (*sync)(void* ctx, cudaStream_t st) = nullptr;
+};
+cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch, const TrtriDist* dist = nullptr);
 
 }  // namespace gpirt

@@ -20,7 +20,7 @@ struct DevFlags {
     int overrun;         // a supplied uniform stream ran dry
     int stalled;         // an ESS loop hit ESS_MAX_PROPOSALS
     int bad_code;        // a y code outside 0..C
-    int peer_timeout;    // a peer's f* chunk did not arrive within the wait limit (item-sharded sweeps over NVLink peer memory)
+    int peer_timeout;    // a peer's f* chunk or chain block did not arrive within the wait limit (item-sharded sweeps over NVLink peer memory)
 };
 
 // Item-sharded sweeps: the f* exchange that feeds the theta step (the all-gather of SURVEY.md 8e) is done by the producing kernel itself.

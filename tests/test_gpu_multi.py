@@ -35,7 +35,8 @@ def run(S):
     S.close()
     return st
 S = ShardedSampler(n, m, C, rank=rank, world=world, device=local, seed=77)
-print("DIST_CHAIN", S.dist_chain)
+if rank == 0:
+    print(f"DIST_CHAIN {S.dist_chain}", flush=True)
 sh = run(S)
 # gather the f columns of every rank on rank 0 (get_state writes only the local item block)
 f = torch.from_numpy(np.ascontiguousarray(sh["f"].T)).cuda()

@@ -34,8 +34,17 @@ def run(S, label):
     ms = (time.perf_counter() - t0) * 1e3 / sweeps
     st = S.get_state(fstar=False)
     st["ll"] = S.total_ll()
-    S.close()
     print(f"{label}: {ms:.2f} ms/sweep, ll {st['ll']:.6f}", flush=True)
+    # the overlapped schedule's own timeline (profiling level 2: section times include waiting for peers and sharing the SMs)
+    each = (lambda f, *a: [getattr(x, f)(*a) for x in S.S]) if hasattr(S, "S") and isinstance(S.S, list) else (lambda f, *a: [getattr(S, f)(*a)])
+    each("profile", 2)
+    each("profile_reset")
+    S.sweep(2)
+    S.sync()
+    sec = each("profile_read")[0]
+    each("profile", 0)
+    print("   shard 0 sections (ms/sweep): " + " ".join(f"{k}={v[0] / 2:.2f}" for k, v in sorted(sec.items(), key=lambda kv: -kv[1][0])[:12]), flush=True)
+    S.close()
     return st
 
 
