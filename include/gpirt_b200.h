@@ -231,8 +231,9 @@ int gpirt_exchange_pull(gpirt_sampler* dst, gpirt_sampler* src, int which);
 /* Distributed theta-only chain (config 4 sizes: n >= 4096, item shards). K, its Cholesky factor, L^-1 and K^-1 k* depend on theta alone and are the same on
  * every rank (src/cholesky-cache.cpp:20-24, src/draw-fstar.cpp:26-36); replicated they are 28 of 62 ms per sweep at n = 10 000 on 8 GPUs. With every peer's
  * arena attached, the trailing updates of the Cholesky are split over the ranks by 256-column blocks (the owner of the next block pushes it to its peers
- * over NVLink, every rank factors the panel), and the columns of L^-1 k* and K^-1 k* are computed by their owner and pushed; every tile is computed by
- * the same arithmetic as on one GPU, so the chain does not change. gpirt_chain_export: this handle's IPC handle and buffer offsets (offsets6[5]: the arena
+ * over NVLink, every rank factors the panel), the large merge levels of L^-1 by columns of their blocks, and the columns of L^-1 k* and K^-1 k* are
+ * computed by their owner and pushed; every tile is computed by the same arithmetic as on one GPU, so the chain does not change (45 instead of 59 ms).
+ * Every shard needs a GPU of its own (the exchange points are spinning wait kernels) and the same profiling level on all ranks. gpirt_chain_export: this handle's IPC handle and buffer offsets (offsets6[5]: the arena
  * address, for a peer in the SAME process); gpirt_chain_attach(h, peer_rank, handle64 or NULL for a same-process peer, offsets6). GPIRT_DIST_CHAIN=0
  * keeps the chain replicated. gpirt_chain_detach (then a barrier) precedes gpirt_destroy on every rank. */
 int gpirt_chain_export(gpirt_sampler* h, void* handle64, int64_t* offsets6);
