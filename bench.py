@@ -374,8 +374,8 @@ def ours(args):
     ach = gemm_flops / (gemm_ms * 1e-3) / 1e12 if gemm_ms > 0 else 0.0
     roofline = {"kernel": "gemm_f64_kernel<64,64,16,32,32,3> (mma.sync m8n8k4 f64 = SASS DMMA.8x8x4; tcgen05 has no fp64 kind)",
                 "bound": "tensor", "achieved": round(ach, 2), "peak": FP64_DMMA_PEAK_TFLOPS, "unit": "TFLOP/s", "frac": round(ach / FP64_DMMA_PEAK_TFLOPS, 4),
-                "traffic": 305.3e6,
-                "traffic_note": "dram read+write of the largest launch (L*Z: algorithmic 176 MB), ncu --set full, profiles/r01_ncu_gemm64.txt",
+                "traffic": 167.3e6,
+                "traffic_note": "dram read+write of the largest launch (L*Z: algorithmic 176 MB), ncu --set full, profiles/r02_ncu_gemm_band.txt (column tiles in two L2-sized bands; 305.3 MB with every column tile under every row tile, profiles/r01_ncu_gemm64.txt)",
                 "peak_source": fp64_src + "; MEASURED_PEAKS.json has no fp64 figure",
                 "groups": gemm_groups, "ms_per_sweep": round(gemm_ms, 4), "call_sites_per_sweep": gemm_launches,
                 "share_of_sweep": round(gemm_ms / sum(per_sweep.values()), 3),

@@ -37,6 +37,7 @@ struct GemmArgs {
     int batch;        // 0 or 1: a single product
     long long strideA, strideB, strideC;
     int M_last, N_last, K_last;  // extents of batch (batch-1) when > 0, else M / N / K
+    int band_n;       // column tiles per band of the tile order (0: chosen by gemm_f64 from K; only without b_upper / b_lower)
     int n_off;        // column index of C(0,0) inside the full product (column slices with b_upper / b_lower)
     int m_off;        // row index of C(0,0) inside the full product (a launch over a row slice keeps the triangular k ranges right)
 };
@@ -94,8 +95,15 @@ gemm_f64_kernel(GemmArgs g) {
     if (g.b_upper || g.b_lower) {  // work varies with the column tile: column tiles are the slow index
         nt = blockIdx.x / tiles_m; mt = blockIdx.x - nt * tiles_m;
         if (g.b_upper) nt = tiles_n - 1 - nt;
-    } else {                       // row tiles are the slow index
-        mt = blockIdx.x / tiles_n; nt = blockIdx.x - mt * tiles_n;
+    } else {
+        // Row tiles are the slow index INSIDE a band of `band_n` column tiles: a wave of CTAs then covers every row tile of one band, whose slice of op(B)
+        // (band_n * BN columns x K, sized for the L2 by gemm_f64) is read from DRAM once instead of once per wave (L*Z at C3 with all 79 column tiles under
+        // every row tile: 305 MB of DRAM traffic for 176 MB of operands, profiles/r01_ncu_gemm64.txt). op(A)'s row blocks are re-read per band from the L2.
+        const int bw = (g.band_n > 0 && g.band_n < tiles_n) ? g.band_n : tiles_n;
+        const int per_band = tiles_m * bw;
+        const int band = blockIdx.x / per_band, r = blockIdx.x - band * per_band;
+        const int w = min(bw, tiles_n - band * bw);  // the last band may be narrower
+        mt = r / w; nt = band * bw + (r - mt * w);
         if (g.a_lower) mt = tiles_m - 1 - mt;
     }
     const int m0 = mt * BM, n0 = nt * BN;

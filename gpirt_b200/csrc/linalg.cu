@@ -71,8 +71,16 @@ static cudaError_t gemm_pick(cudaStream_t st, const GemmArgs& g) {
     return launch_gemm<128, 128, 16, 64, 32, 3, TA, TB>(st, g);
 }
 
-cudaError_t gemm_f64(cudaStream_t st, bool ta, bool tb, const GemmArgs& g) {
-    if (g.M <= 0 || g.N <= 0) return cudaSuccess;
+cudaError_t gemm_f64(cudaStream_t st, bool ta, bool tb, const GemmArgs& g0) {
+    if (g0.M <= 0 || g0.N <= 0) return cudaSuccess;
+    GemmArgs g = g0;
+    if (g.band_n <= 0) {  // a band's slice of op(B), 64 columns x K doubles per column tile, should stay in the L2 next to op(A) and the output. 41 MB = two bands at C3 (narrower bands measured slower: profiles/r02_gemm_band.txt)
+        static const int band_mb = getenv("GPIRT_GEMM_BAND_MB") ? atoi(getenv("GPIRT_GEMM_BAND_MB")) : 41;
+        const long long per_tile = (long long)(g.K > 0 ? g.K : 1) * 64 * 8;
+        const long long bw = ((long long)band_mb << 20) / per_tile;
+        g.band_n = (int)(bw < 4 ? 4 : bw);  // band_mb = 0 in the environment: one band (the order before)
+        if (band_mb <= 0) g.band_n = 1 << 30;
+    }
     if (ta) return tb ? gemm_pick<true, true>(st, g) : gemm_pick<true, false>(st, g);
     return tb ? gemm_pick<false, true>(st, g) : gemm_pick<false, false>(st, g);
 }

@@ -260,6 +260,78 @@ __device__ __forceinline__ void cell_ll32(double g, double tau_lo, double tau_hi
     const float u = fminf(fabsf(a), 9.25f), v = fminf(fabsf(b), 9.25f);
     cell_ll32_core(a, b, u, v, q_tail32(u), q_tail32(v), t, e);
 }
+
+// ---- two cells per instruction stream: sm_100's packed fp32 pairs (FADD2 / FMUL2 / FFMA2: add / mul / fma .rn.f32x2) --------------------------
+// The ESS item kernels are bound by instruction issue (ncu: issue slots 77 % busy, every pipe below 40 %, profiles/r02_ncu_ess.txt), and almost all
+// of a cell's fp32 arithmetic is the same operation on its own two tails and on the next cell's. A pair holds lane 0 = cell 0, lane 1 = cell 1: the
+// lower tails of both cells form one pair, the upper tails another. Every lane operation is the IEEE round-to-nearest operation of the scalar code
+// above, in the same order, so (t, e) are the bits cell_ll32 gives (gpirt_debug_cell32 checks that) — one instruction for two cells instead of two.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 bc2(float c) { return pk2(c, c); }
+__device__ __forceinline__ float min_nan(float a, float b) { float r; asm("min.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b)); return r; }
+
+// Q of both lanes (arguments already clamped to [0, 9.25]); xx receives the squares (the error weights reuse them)
+__device__ __forceinline__ f32x2 q_tail32x2(f32x2 x, f32x2& xx) {
+    const f32x2 xm = add2(x, bc2(-4.0f)), xp = add2(x, bc2(4.0f));
+    float p0, p1;
+    upk2(xp, p0, p1);
+    const f32x2 s = mul2(xm, pk2(f_rcp(p0), f_rcp(p1)));
+    f32x2 p = bc2(0.000785236840738696f);
+    p = fma2(p, s, bc2(0.0005041266204986191f));
+    p = fma2(p, s, bc2(-0.008529436410853592f));
+    p = fma2(p, s, bc2(0.03085854142686483f));
+    p = fma2(p, s, bc2(-0.07170505823364434f));
+    p = fma2(p, s, bc2(0.12437966746436852f));
+    p = fma2(p, s, bc2(-0.1703977371436323f));
+    p = fma2(p, s, bc2(0.09441063861780297f));
+    xx = mul2(x, x);
+    float e0, e1;
+    upk2(mul2(xx, bc2(-0.72134752f)), e0, e1);
+    return mul2(p, pk2(f_ex2(e0), f_ex2(e1)));
+}
+
+// cells 0 and 1 at once; same results as two calls of cell_ll32
+__device__ __forceinline__ void cell_ll32x2(double g0, double lo0, double hi0, double g1, double lo1, double hi1, float& t0, float& e0, float& t1,
+                                            float& e1) {
+    const float a0 = (float)__dsub_rn(lo0, g0), b0 = (float)__dsub_rn(hi0, g0);
+    const float a1 = (float)__dsub_rn(lo1, g1), b1 = (float)__dsub_rn(hi1, g1);
+    // min.NaN keeps a NaN argument (fminf would clamp it to 9.25 and pass it as a deep-tail cell): it then runs through both tails into t and e of its
+    // cell — every form of d below uses both tails — so the cell needs no NaN test of its own: a NaN sum or bound fails both screening comparisons
+    const f32x2 U = pk2(min_nan(fabsf(a0), 9.25f), min_nan(fabsf(a1), 9.25f));  // the lower thresholds' tails of both cells
+    const f32x2 V = pk2(min_nan(fabsf(b0), 9.25f), min_nan(fabsf(b1), 9.25f));  // the upper thresholds'
+    f32x2 UU, VV;
+    const f32x2 QU = q_tail32x2(U, UU), QV = q_tail32x2(V, VV);
+    // the three forms of Phi(b) - Phi(a) (cell_ll32_core), then each cell picks its own
+    const f32x2 X1 = sub2(QU, QV);                    // both arguments in the upper tail:  qu - qv   (negated: both in the lower tail)
+    const f32x2 X3 = sub2(sub2(bc2(1.0f), QU), QV);   // the bin straddles zero:            (1 - qu) - qv
+    float x10, x11, x30, x31;
+    upk2(X1, x10, x11);
+    upk2(X3, x30, x31);
+    const bool sa0 = a0 >= 0.0f, sb0 = b0 <= 0.0f, sa1 = a1 >= 0.0f, sb1 = b1 <= 0.0f;
+    const float d0 = sa0 ? x10 : (sb0 ? -x10 : x30), d1 = sa1 ? x11 : (sb1 ? -x11 : x31);
+    const f32x2 S = pk2((sa0 || sb0) ? 0.0f : 1.0f, (sa1 || sb1) ? 0.0f : 1.0f);
+    const f32x2 P = add2(pk2(d0, d1), bc2(1e-6f));
+    float p0, p1;
+    upk2(P, p0, p1);
+    t0 = f_lg2(p0) * 0.6931472f;
+    t1 = f_lg2(p1) * 0.6931472f;
+    // dp = (4e-7 u^2 + 4e-6) qu + (4e-7 v^2 + 4e-6) qv + 2.4e-7 (p + straddle), with cell_ll32_core's association
+    const f32x2 RU = fma2(bc2(4e-7f), UU, bc2(4e-6f)), RV = fma2(bc2(4e-7f), VV, bc2(4e-6f));
+    const f32x2 DP = add2(fma2(RU, QU, mul2(RV, QV)), mul2(bc2(2.4e-7f), add2(P, S)));
+    const f32x2 DEN = sub2(P, DP);
+    float dp0, dp1, den0, den1;
+    upk2(DP, dp0, dp1);
+    upk2(DEN, den0, den1);
+    const float r0 = den0 > dp0 ? dp0 * f_rcp(den0) * 1.0001f : 14.0f, r1 = den1 > dp1 ? dp1 * f_rcp(den1) * 1.0001f : 14.0f;
+    e0 = r0 + fmaf(5e-7f, fabsf(t0), 2e-6f);  // t is NaN for a NaN argument, and so is e
+    e1 = r1 + fmaf(5e-7f, fabsf(t1), 2e-6f);
+}
 #endif
 
 // grid index of theta on theta* = -5:0.01:5 (src/draw-theta.cpp:10-11, src/gpirtMCMC.cpp:291-296):

@@ -147,9 +147,28 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
             l += (double)t;
             e += et;
         };
+        // cells i and i + T as one packed pair (probit.cuh cell_ll32x2: the same (t, e) per cell, one instruction for both). A missing cell is
+        // evaluated as category 1 and not added, so the pair's instruction stream has no branch.
+        auto two = [&](int i) {
+            const int y0 = yj[i], y1 = yj[i + T];
+            double f0 = fj[i], f1 = fj[i + T];
+            if (MODE == IB_F) {
+                f0 = __dadd_rn(__dmul_rn(f0, ce), __dmul_rn(nuj[i], se));
+                f1 = __dadd_rn(__dmul_rn(f1, ce), __dmul_rn(nuj[i + T], se));
+            }
+            const double g0 = __dadd_rn(f0, mur ? mur[i] : mu_of(theta[i], pb0, pb1, pb2));
+            const double g1 = __dadd_rn(f1, mur ? mur[i + T] : mu_of(theta[i + T], pb0, pb1, pb2));
+            const int c0 = y0 > 0 ? y0 : 1, c1 = y1 > 0 ? y1 : 1;
+            float t0, t1, et0, et1;
+            cell_ll32x2(g0, tau[c0 - 1], tau[c0], g1, tau[c1 - 1], tau[c1], t0, et0, t1, et1);
+            l0 += (double)(y0 > 0 ? t0 : 0.0f);  // adding +0 leaves the sums as they are
+            l1 += (double)(y1 > 0 ? t1 : 0.0f);
+            e0 += y0 > 0 ? et0 : 0.0f;
+            e1 += y1 > 0 ? et1 : 0.0f;
+        };
         const int i_end = min(n, c_end * T);
         int i = tid + c_begin * T;
-        for (; i + T < i_end; i += 2 * T) { one(i, l0, e0); one(i + T, l1, e1); }
+        for (; i + T < i_end; i += 2 * T) two(i);
         if (i < i_end) one(i, l0, e0);
         L = l0 + l1;
         E = (double)(e0 + e1);
