@@ -74,7 +74,7 @@ static cudaError_t gemm_pick(cudaStream_t st, const GemmArgs& g) {
 cudaError_t gemm_f64(cudaStream_t st, bool ta, bool tb, const GemmArgs& g0) {
     if (g0.M <= 0 || g0.N <= 0) return cudaSuccess;
     GemmArgs g = g0;
-    if (g.band_n <= 0) {  // a band's slice of op(B), 64 columns x K doubles per column tile, should stay in the L2 next to op(A) and the output. 41 MB = two bands at C3 (narrower bands measured slower: profiles/r02_gemm_band.txt)
+    if (g.band_n <= 0) {  // a band's slice of op(B), 64 columns x K doubles per column tile, should stay in the L2 next to op(A) and the output. 41 MB = two bands at C3 (narrower bands measured slower: profiles/r02_sweep_schedule_experiments.txt)
         static const int band_mb = getenv("GPIRT_GEMM_BAND_MB") ? atoi(getenv("GPIRT_GEMM_BAND_MB")) : 41;
         const long long per_tile = (long long)(g.K > 0 ? g.K : 1) * 64 * 8;
         const long long bw = ((long long)band_mb << 20) / per_tile;
