@@ -314,6 +314,8 @@ int gpirt_create(const gpirt_config* cfg, gpirt_sampler** out) {
         int lo = 0, hi = 0;
         CU(cudaDeviceGetStreamPriorityRange(&lo, &hi));
         CU(cudaStreamCreateWithPriority(&h->side, cudaStreamNonBlocking, hi));
+        CU(cudaStreamCreateWithPriority(&h->side2, cudaStreamNonBlocking, hi));
+        CU(cudaEventCreateWithFlags(&h->ev_tmp, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_L, cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&h->ev_shared, cudaEventDisableTiming));
@@ -426,6 +428,7 @@ int gpirt_destroy(gpirt_sampler* h) {
     if (!h) return GPIRT_OK;
     cudaSetDevice(h->cfg.device);
     if (h->side) cudaStreamSynchronize(h->side);
+    if (h->side2) cudaStreamSynchronize(h->side2);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->ev_fork) cudaEventDestroy(h->ev_fork);
     if (h->ev_L) cudaEventDestroy(h->ev_L);
@@ -435,6 +438,8 @@ int gpirt_destroy(gpirt_sampler* h) {
     for (int c = 0; c < h->L_rows.count; ++c) cudaEventDestroy(h->L_rows.ev[c]);
     for (int c = 0; c < h->Lpost_rows.count; ++c) cudaEventDestroy(h->Lpost_rows.ev[c]);
     if (h->side) cudaStreamDestroy(h->side);
+    if (h->side2) cudaStreamDestroy(h->side2);
+    if (h->ev_tmp) cudaEventDestroy(h->ev_tmp);
     if (h->chol_aux.helper) { cudaStreamSynchronize(h->chol_aux.helper); cudaStreamDestroy(h->chol_aux.helper); }
     if (h->chol_aux.ev_panel) cudaEventDestroy(h->chol_aux.ev_panel);
     if (h->chol_aux.ev_rest) cudaEventDestroy(h->chol_aux.ev_rest);
@@ -1086,6 +1091,8 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     if (!h->kstar_built) SEC_ST(h, st, "K_build", CU(build_K(st, h->theta, n, h->tstar, N, h->sds0, h->W, h->ldn, 0.0)));
     h->kstar_built = false;
     const double* tmp = h->W;  // L^-1 k*
+    bool forked_w = false;
+    cudaEvent_t w_done = nullptr;
     if (h->solver == 1) {
         // L^-1 explicitly: every diagonal block inverted in parallel, log2(n/64) batched merge levels, then the two solves are GEMMs
         TrtriDist td;
@@ -1111,7 +1118,22 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
         w.M = n; w.N = c_hi - c_lo; w.K = n; w.A = h->Linv; w.lda = h->ldn; w.B = h->W2 + (size_t)c_lo * h->ldn; w.ldb = h->ldn;
         w.C = h->W + (size_t)c_lo * h->ldn; w.ldc = h->ldn;
         w.alpha = 1.0; w.beta = 0.0; w.a_upper = 1;
-        SEC_ST(h, st, "gemm_W", CU(gemm_f64(st, true, false, w)));
+        // W and K_post both need tmp only: inside a sweep W goes to a second side stream and K_post with its latency-bound Cholesky starts at once,
+        // instead of after W (the f* noise term was waiting 0.2 ms for chol(K_post) at C3, tools/timeline_c3.py)
+        static const int fork_env = getenv("GPIRT_FORK_W") ? atoi(getenv("GPIRT_FORK_W")) : 1;
+        const bool fork_w = fork_env && !distributed && st == h->side && h->side2 && ev_after_W;
+        cudaStream_t sw = fork_w ? h->side2 : st;
+        if (fork_w) {
+            CU(cudaEventRecord(h->ev_tmp, st));
+            CU(cudaStreamWaitEvent(sw, h->ev_tmp, 0));
+        }
+        SEC_ST(h, sw, "gemm_W", CU(gemm_f64(sw, true, false, w)));
+        if (fork_w) {
+            CU(cudaEventRecord(ev_after_W, sw));
+            w_done = ev_after_W;
+            ev_after_W = nullptr;  // recorded; `st` joins it at the end, so that whatever follows on `st` (ev_shared) covers W as before
+            forked_w = true;
+        }
         if (distributed) {
             if (c_hi > c_lo) {
                 TRY(chain_push(h, st, gpirt_sampler::OFF_W2, h->W2, h->W2 + (size_t)c_lo * h->ldn, h->ldn, n, c_hi - c_lo));
@@ -1139,6 +1161,7 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
     SEC_ST(h, st, "chol_Kpost", CU(chol_lower_blocked(st, h->Kpost, h->ldN, N, &h->flags->chol_post_info, h->chol_ws, post_marks ? &h->Lpost_rows : nullptr,
                                                           nullptr, h->plan_N.state ? &h->plan_N : nullptr)));
     h->pending_post_rows = post_marks;
+    if (forked_w) CU(cudaStreamWaitEvent(st, w_done, 0));
     if (h->solver != 1) {  // substitution overwrites tmp in place, so it comes after K_post
         SEC_ST(h, st, "trsm_W", CU(trsm_left_lower_t(st, h->L, h->ldn, n, h->W, h->ldn, N)));
         if (ev_after_W) CU(cudaEventRecord(ev_after_W, st));
@@ -1933,11 +1956,19 @@ int gpirt_profile_enable(gpirt_sampler* h, int on) {
     h->profile_level = on;
     return GPIRT_OK;
 }
+// joins the side streams without recording the wait as a section (it would show up as a stall of the last sweep that the schedule itself does not have)
+static int quiesce_unrecorded(gpirt_sampler* h) {
+    const bool was = h->profiling;
+    h->profiling = false;
+    const int rc = quiesce(h);
+    h->profiling = was;
+    return rc;
+}
 // Collects finished sections; writes up to `cap` entries "name\0" (32 bytes each) with total ms and launch counts.
 int gpirt_profile_read(gpirt_sampler* h, char* names, double* ms, int64_t* launches, int cap, int* count) {
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
-    TRY(quiesce(h));  // sections of the overlapped schedule (profiling level 2) live on the side stream
+    TRY(quiesce_unrecorded(h));  // sections of the overlapped schedule (profiling level 2) live on the side stream
     CU(cudaStreamSynchronize(h->stream));
     for (auto& p : h->pending) {
         float t = 0.f;
@@ -1957,10 +1988,37 @@ int gpirt_profile_read(gpirt_sampler* h, char* names, double* ms, int64_t* launc
     *count = k;
     return GPIRT_OK;
 }
+// Every section recorded since the last read / reset, in the order it was issued, with its begin and end on the device clock relative to the begin of
+// the first one (events of different streams of one device share a clock): the overlapped schedule as it ran. Collects like gpirt_profile_read.
+int gpirt_profile_timeline(gpirt_sampler* h, char* names, double* begin_ms, double* end_ms, int cap, int* count) {
+    CHECK_H(h);
+    if (!names || !begin_ms || !end_ms || !count) return fail(GPIRT_ERR_INVALID, "profile_timeline: NULL output");
+    CU(cudaSetDevice(h->cfg.device));
+    TRY(quiesce_unrecorded(h));
+    CU(cudaStreamSynchronize(h->stream));
+    int k = 0;
+    for (auto& p : h->pending) {
+        float t = 0.f, b = 0.f, e = 0.f;
+        cudaEventElapsedTime(&t, p.a, p.b);
+        if (k < cap) {
+            cudaEventElapsedTime(&b, h->pending[0].a, p.a);
+            cudaEventElapsedTime(&e, h->pending[0].a, p.b);
+            std::snprintf(names + 32 * k, 32, "%s", p.name);
+            begin_ms[k] = b; end_ms[k] = e;
+            ++k;
+        }
+        auto& sct = h->sections[p.name];
+        sct.first += t; sct.second += 1;
+    }
+    for (auto& p : h->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
+    h->pending.clear();
+    *count = k;
+    return GPIRT_OK;
+}
 int gpirt_profile_reset(gpirt_sampler* h) {  // forgets the totals AND the sections recorded so far whose events have not been collected yet
     CHECK_H(h);
     CU(cudaSetDevice(h->cfg.device));
-    TRY(quiesce(h));
+    TRY(quiesce_unrecorded(h));
     CU(cudaStreamSynchronize(h->stream));
     for (auto& p : h->pending) { cudaEventDestroy(p.a); cudaEventDestroy(p.b); }
     h->pending.clear();

@@ -45,6 +45,8 @@ struct gpirt_sampler {
     // stream as soon as the new theta is committed, under the item kernels of the main stream (draw_beta, draw_threshold,
     // ll, next draw_f): it is a long chain of small launches that cannot fill the GPU on its own.
     cudaStream_t side = nullptr;
+    cudaStream_t side2 = nullptr;    // W = L^-T tmp runs here, beside K_post and its Cholesky on `side` (both need tmp only)
+    cudaEvent_t ev_tmp = nullptr;
     cudaEvent_t ev_fork = nullptr, ev_L = nullptr, ev_W = nullptr, ev_shared = nullptr;
     cudaEvent_t ev_xchg = nullptr;  // "this shard's chunk is written": what gpirt_exchange_pull makes the pulling shard's stream wait for
     gpirt::CholMilestones L_rows;  // leading row blocks of L signalled while chol(K) is still running on the side stream (nu = L Z starts under it)

@@ -221,7 +221,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
             pb2 = __dadd_rn(__dmul_rn(b2, ce_), __dmul_rn(nu_small[2], se_));
         }
         if (MODE == IB_THR) {
-            __syncthreads();
+            // no barrier in front: every evaluation ends in a block reduction, whose barrier all threads pass only after their last read of tau
             if (tid == 0) {  // delta_to_threshold(delta'), src/log-likelihood.cpp:66-76
                 tau[1] = __dadd_rn(__dmul_rn(delta[0], ce_), __dmul_rn(nu_small[0], se_));
                 for (int q = 1; q < C - 1; ++q)

@@ -371,6 +371,14 @@ class Sampler:
         check(self._L.gpirt_profile_read(self._h, names, ms, cnt, cap, C.byref(k)))
         return {names.raw[32 * i:32 * i + 32].split(b"\0")[0].decode(): (ms[i], cnt[i]) for i in range(k.value)}
 
+    def profile_timeline(self, cap=512):
+        """[(section, begin_ms, end_ms)] of everything recorded since the last read / reset, in issue order, on the device clock (profiling level 2)"""
+        names = C.create_string_buffer(32 * cap)
+        b, e = (C.c_double * cap)(), (C.c_double * cap)()
+        k = C.c_int()
+        check(self._L.gpirt_profile_timeline(self._h, names, b, e, cap, C.byref(k)))
+        return [(names.raw[32 * i:32 * i + 32].split(b"\0")[0].decode(), b[i], e[i]) for i in range(k.value)]
+
     def debug_uniforms(self, stream, unit, count):
         out = np.empty(count)
         check(self._L.gpirt_debug_uniforms(self._h, C.c_uint32(stream), C.c_uint32(unit), int(count), _p(out)))

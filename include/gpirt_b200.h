@@ -257,6 +257,8 @@ int gpirt_peer_wait(gpirt_sampler* h);
 int gpirt_profile_enable(gpirt_sampler* h, int on);          /* CUDA events around every kernel group of a sweep */
 int gpirt_profile_read(gpirt_sampler* h, char* names /* cap x 32 */, double* ms, int64_t* launches, int cap, int* count);
 int gpirt_profile_reset(gpirt_sampler* h);
+/* level 2 (the overlapped schedule): every recorded section in issue order with its begin / end in ms after the first one's begin (tools/timeline_c3.py) */
+int gpirt_profile_timeline(gpirt_sampler* h, char* names /* cap x 32 */, double* begin_ms, double* end_ms, int cap, int* count);
 long long gpirt_launch_count(void);                          /* kernels launched by this library so far */
 int gpirt_debug_uniforms(gpirt_sampler* h, uint32_t stream, uint32_t unit, int count, double* out);
 int gpirt_debug_probit(int device, const double* x, int n, double* phi_out, double* log_out); /* device Phi(x), log(x) */

@@ -29,3 +29,15 @@ for level in (2, 1):
     print(f"level {level}: main " + " ".join(f"{k}={sec[k][0] / 6:.3f}" for k in main if k in sec) + f" | sum {sum(sec[k][0] for k in main if k in sec) / 6:.3f}")
     print(f"         side " + " ".join(f"{k}={sec[k][0] / 6:.3f}" for k in side if k in sec) + f" | sum {sum(sec[k][0] for k in side if k in sec) / 6:.3f}")
     print("         other " + " ".join(f"{k}={v[0] / 6:.3f}" for k, v in sec.items() if k not in main and k not in side))
+
+# the schedule as it ran: two consecutive sweeps, every section with its begin / end on the device clock
+S.profile(2)
+S.sweep(1)
+S.profile_reset()
+S.sweep(2)
+tl = S.profile_timeline()
+S.profile(0)
+side_names = set(side)
+print("timeline of two sweeps (ms after the first section's begin; M = main stream, S = side streams):")
+for name, b, e in sorted(tl, key=lambda x: x[1]):
+    print(f"  {'S' if name in side_names else 'M'} {name:12s} {b:7.3f} -> {e:7.3f}  ({e - b:.3f})")
