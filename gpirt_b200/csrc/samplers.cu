@@ -330,8 +330,10 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
 
 // One CTA per item when the grid covers the items; with a smaller grid (launch_ess_mode: beta / threshold blocks, which share the SMs with the
 // theta-only chain on the side stream) every CTA walks the items with the grid's stride. An item's arithmetic does not depend on which CTA ran it.
+// 1024 resident threads per SM at least, i.e. at most 64 registers: the packed two-cell loop otherwise takes 76-80 in the beta / threshold kernels and
+// drops them from four 256-thread CTAs per SM to three
 template <int MODE, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32) k_ess_items(ItemView v) {
+__global__ void __launch_bounds__(WARPS * 32, 32 / WARPS) k_ess_items(ItemView v) {
     __shared__ double tau[MAX_C + 1];
     __shared__ double s_part[WARPS];
     __shared__ double s_part2[2][2][WARPS];

@@ -31,4 +31,4 @@ S.sweep(4)
 sec = S.profile_read()
 S.profile(False)
 print(f"band_mb={os.environ.get('GPIRT_GEMM_BAND_MB', 'default')}: {best:.3f} ms/sweep ({1e3 / best:.1f}/s)  " +
-      " ".join(f"{k}={sec[k][0] / 4:.4f}" for k in ("gemm_LZ", "gemm_FtW", "gemm_ZLpost", "gemm_tmp", "gemm_W", "gemm_Kpost", "trtri", "chol_K")))
+      " ".join(f"{k}={sec[k][0] / 4:.4f}" for k in ("ess_f", "ess_beta", "ess_thr", "ess_theta", "gemm_LZ", "gemm_FtW", "gemm_ZLpost", "gemm_tmp", "gemm_W", "gemm_Kpost", "trtri", "chol_K")))
