@@ -578,13 +578,13 @@ int gpirt_sync(gpirt_sampler* h) {
 
 // Rows [row0, row0 + nrows) x columns [col0, col0 + ncols) of the host matrix y (n x m_total doubles, NaN = missing) as int8 codes on the
 // device (nrows x ncols, column-major), staged in column slabs so the fp64 copy never needs more than 256 MB of device memory.
-static int upload_block_i8(gpirt_sampler* h, const double* y, long long row0, long long nrows, long long col0, long long ncols, int8_t* d_out,
-                           double* d_stage, long long slab_cols) {
+static int upload_block_i8(gpirt_sampler* h, cudaStream_t st, const double* y, long long row0, long long nrows, long long col0, long long ncols,
+                           int8_t* d_out, double* d_stage, long long slab_cols) {
     for (long long c0 = 0; c0 < ncols; c0 += slab_cols) {
         const long long cols = std::min<long long>(slab_cols, ncols - c0);
         CU(cudaMemcpy2DAsync(d_stage, (size_t)nrows * 8, y + (col0 + c0) * h->n + row0, (size_t)h->n * 8, (size_t)nrows * 8, (size_t)cols,
-                             cudaMemcpyHostToDevice, h->stream));
-        CU(launch_y_to_i8(h->stream, d_stage, cols * nrows, h->C, d_out + c0 * nrows, h->flags));
+                             cudaMemcpyHostToDevice, st));
+        CU(launch_y_to_i8(st, d_stage, cols * nrows, h->C, d_out + c0 * nrows, h->flags));
     }
     return GPIRT_OK;
 }
@@ -610,24 +610,29 @@ int gpirt_set_data_f64(gpirt_sampler* h, const double* y) {
     double* d_y = t_y.as<double>();
     int8_t* d_i8 = t_i8.as<int8_t>();
     int rc = GPIRT_OK;
-    CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), h->stream));
-    CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), h->stream));
-    if (h->y_rl) CU(cudaMemsetAsync(h->y_rl, 0, (size_t)h->ldml * h->n, h->stream));
+    // The first upload of a handle runs on the side stream: nothing queued on the main stream can be reading the responses yet, so the initial draws
+    // (K, its Cholesky, f0 = L z: gpirt_mcmc issues them first) run under the 8 n m bytes coming over PCIe. Replacing data joins everything first.
+    cudaStream_t st = h->stream;
+    if (!h->have_data && h->side && !h->pending_L && !h->pending_shared) st = h->side;
+    else { TRY(quiesce(h)); CU(cudaStreamSynchronize(h->stream)); }
+    CU(cudaMemsetAsync(h->y_im, 0, (size_t)h->ldy * std::max(h->m_local, 1), st));
+    CU(cudaMemsetAsync(h->y_rm, 0, (size_t)h->ldm * std::max(h->n_local, 1), st));
+    if (h->y_rl) CU(cudaMemsetAsync(h->y_rl, 0, (size_t)h->ldml * h->n, st));
     for (size_t k = 0; k < blocks.size() && rc == GPIRT_OK; ++k) {
         const Block& b = blocks[k];
         if (b.nrows <= 0 || b.ncols <= 0) continue;
-        rc = upload_block_i8(h, y, b.row0, b.nrows, b.col0, b.ncols, d_i8, d_y, slab_cols);
+        rc = upload_block_i8(h, st, y, b.row0, b.nrows, b.col0, b.ncols, d_i8, d_y, slab_cols);
         if (rc != GPIRT_OK) break;
         cudaError_t e;
         if (h->world == 1)
-            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_total, 0, h->m_total, h->y_im, h->ldy, 0, h->n, h->y_rm, h->ldm);
+            e = launch_y_layouts(st, d_i8, h->n, h->m_total, 0, h->m_total, h->y_im, h->ldy, 0, h->n, h->y_rm, h->ldm);
         else if (k == 0)  // the block IS the local items: item-major layout, and all respondents' rows over these items (item-sharded theta step)
-            e = launch_y_layouts(h->stream, d_i8, h->n, h->m_local, 0, h->m_local, h->y_im, h->ldy, 0, h->n, h->y_rl, h->ldml);
+            e = launch_y_layouts(st, d_i8, h->n, h->m_local, 0, h->m_local, h->y_im, h->ldy, 0, h->n, h->y_rl, h->ldml);
         else              // the block IS the local respondents: respondent-major layout only
-            e = launch_y_layouts(h->stream, d_i8, h->n_local, h->m_total, 0, 0, h->y_im, h->ldy, 0, h->n_local, h->y_rm, h->ldm);
+            e = launch_y_layouts(st, d_i8, h->n_local, h->m_total, 0, 0, h->y_im, h->ldy, 0, h->n_local, h->y_rm, h->ldm);
         if (e != cudaSuccess) rc = fail(GPIRT_ERR_CUDA, "y layouts: %s", cudaGetErrorString(e));
     }
-    cudaStreamSynchronize(h->stream);
+    cudaStreamSynchronize(st);  // the staging blocks go back to the cache below, and whatever the caller launches next comes after the layouts
     if (rc != GPIRT_OK) return rc;
     h->have_data = true;
     return check_flags(h);

@@ -261,14 +261,16 @@ struct ChainRun {
         gpirt_config cfg = config_of(a);
         TRYC(gpirt_create(&cfg, &g.h));
         gpirt_sampler* h = g.h;
-        if (data_from) TRYC(gpirt_copy_data(h, data_from));
-        else TRYC(gpirt_set_data_f64(h, a->y));
         TRYC(gpirt_set_priors(h, a->beta_prior_sds, a->theta_prior_sds));
         TRYC(gpirt_set_state(h, a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
         TRYC(gpirt_set_iter(h, 0xFFFFFFFFu));  // initial draws use a sweep id no sweep reaches
         TRYC(gpirt_init_draw(h, a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
         if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h, a->f_init_z));
         TRYC(gpirt_set_iter(h, 0));
+        // the responses last: the initial draws (K, its Cholesky, f0 = L z) do not read them and are already running when their 8 n m bytes start
+        // over PCIe on the handle's side stream (gpirt_set_data_f64)
+        if (data_from) TRYC(gpirt_copy_data(h, data_from));
+        else TRYC(gpirt_set_data_f64(h, a->y));
         n_samples = a->sample_iterations / a->THIN;  // src/gpirtMCMC.cpp:48
         if (n_chains > 1) {  // chains side by side share the SMs: the persistent Cholesky's CTA budget is divided among them. The factor does not depend
             // on the CTA count (updates are applied in step order), so every chain stays bit-identical to the chain run alone; the per-panel path would not
@@ -337,13 +339,13 @@ static int mcmc_sharded(const gpirt_mcmc_args* a, const std::vector<int>& devs) 
         cfg.device = devs[r]; cfg.rank = r; cfg.world = W;
         TRYC(gpirt_create(&cfg, &g[r].h));
         h[r] = g[r].h;
-        TRYC(gpirt_set_data_f64(h[r], a->y));  // a shard uploads its items' columns and its respondents' rows
         TRYC(gpirt_set_priors(h[r], a->beta_prior_sds, a->theta_prior_sds));
         TRYC(gpirt_set_state(h[r], a->theta, a->beta_init, a->f_init, a->thresholds, nullptr));
         TRYC(gpirt_set_iter(h[r], 0xFFFFFFFFu));
         TRYC(gpirt_init_draw(h[r], a->beta_prior_means, a->beta_init == nullptr, a->f_init == nullptr && a->f_init_z == nullptr));
         if (!a->f_init && a->f_init_z) TRYC(gpirt_init_f_from_z(h[r], a->f_init_z));
         TRYC(gpirt_set_iter(h[r], 0));
+        TRYC(gpirt_set_data_f64(h[r], a->y));  // a shard uploads its items' columns and its respondents' rows, under its initial draws
     }
     {   // config-4 sizes with every shard on a GPU of its own: the theta-only chain is distributed over the shards (gpirt_chain_*, same process: no IPC)
         bool distinct = true;
