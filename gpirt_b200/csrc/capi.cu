@@ -242,11 +242,31 @@ __global__ void k_init_beta(double* beta, const double* means, const double* sds
 }
 
 // thresholds item-major (C+1) x m -> the reference's m x (C+1) column-major slice of threshold_draws
-__global__ void k_store_thr(const double* __restrict__ thr, int C1, int m, double* __restrict__ out) {
-    int e = blockIdx.x * blockDim.x + threadIdx.x;  // e = c * m + J
+// One kept sample in one launch: theta, beta, the thresholds (m x (C+1) out of the (C+1) x m state) and the total log-likelihood — the last CTA adds the
+// per-item terms as k_ordered_sum does (256 strided partial sums combined in index order by one thread: the same bits).
+__global__ void __launch_bounds__(256) k_store_sample(const double* __restrict__ theta, int n, const double* __restrict__ beta, int m,
+                                                      const double* __restrict__ thr, int C1, const double* __restrict__ item_ll,
+                                                      double* __restrict__ o_theta, double* __restrict__ o_beta, double* __restrict__ o_thr,
+                                                      double* __restrict__ o_ll) {
+    if (blockIdx.x == gridDim.x - 1) {
+        __shared__ double part[256];
+        double acc = 0.0;
+        for (int i = threadIdx.x; i < m; i += 256) acc += item_ll[i];
+        part[threadIdx.x] = acc;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            double t = 0.0;
+            for (int k = 0; k < 256; ++k) t += part[k];
+            *o_ll = t;
+        }
+        return;
+    }
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < n) o_theta[e] = theta[e];
+    if (e < 3 * m) o_beta[e] = beta[e];
     if (e < C1 * m) {
-        const int c = e / m, J = e - c * m;
-        out[e] = thr[(size_t)J * C1 + c];
+        const int c = e / m, J = e - c * m;  // e = c * m + J
+        o_thr[e] = thr[(size_t)J * C1 + c];
     }
 }
 
@@ -837,12 +857,12 @@ int gpirt_store_push(gpirt_sampler* h) {
     const size_t k = (size_t)s.count, m = (size_t)h->m_total;
     const int C1 = h->C + 1;
     // theta, beta, thresholds, f and f* are written by main-stream kernels only (the side stream owns L, L^-1, W, K_post)
-    CU(cudaMemcpyAsync(s.theta + k * h->n, h->theta, (size_t)h->n * 8, cudaMemcpyDeviceToDevice, st));
-    CU(cudaMemcpyAsync(s.beta + k * 3 * m, h->beta, 3 * m * 8, cudaMemcpyDeviceToDevice, st));
-    k_store_thr<<<(C1 * h->m_total + 255) / 256, 256, 0, st>>>(h->thr, C1, h->m_total, s.thr + k * C1 * m);
+    const int elems = std::max(h->n, std::max(3, C1) * h->m_total);
+    // the total log-likelihood: the per-item terms of the sweep's last step (src/gpirtMCMC.cpp:324-331)
+    k_store_sample<<<(elems + 255) / 256 + 1, 256, 0, st>>>(h->theta, h->n, h->beta, h->m_total, h->thr, C1, h->item_ll, s.theta + k * h->n,
+                                                            s.beta + k * 3 * m, s.thr + k * C1 * m, s.ll + k);
     ++g_kernel_launches;
     CU(cudaGetLastError());
-    CU(launch_ordered_sum(st, h->item_ll, h->m_total, s.ll + k));  // the per-item terms of the sweep's last step (src/gpirtMCMC.cpp:324-331)
     if (s.f)
         CU(cudaMemcpy2DAsync(s.f + k * h->n * m, (size_t)h->n * 8, h->f, (size_t)h->ldn * 8, (size_t)h->n * 8, h->m_total, cudaMemcpyDeviceToDevice, st));
     if (s.fstar)  // the table is m x NGRID (ld_chunk) column-major in (item, grid point): back to NGRID x m
