@@ -341,6 +341,49 @@ def test_overlapped_sweeps_equal_serial_sweeps_bit_for_bit():
     assert states[0]["ll"] == states[1]["ll"]
 
 
+def test_profiled_sweeps_leave_the_chain_alone_and_the_timeline_is_ordered():
+    """gpirt_profile_*: the serial order (level 1) and the overlapped schedule with events around every group (level 2) give the chain of unprofiled
+    sweeps; a reset forgets the sections recorded so far (collected or not); the timeline lists each group of each recorded sweep with begin <= end."""
+    n, m, C = 300, 40, 5
+    P = make_problem(n, m, C, seed=81)
+    states = []
+    for level in (0, 1, 2):
+        S = gpirt_b200.Sampler(n, m, C, seed=99)
+        S.set_data(P["y"])
+        S.set_priors(P["beta_prior_sds"], P["theta_prior_sds"])
+        S.set_state(theta=P["theta0"], beta=P["beta0"], thresholds=P["thr0"])
+        S.init_draw(draw_beta=False, draw_f=True)
+        S.profile(level)
+        S.sweep(2)
+        S.profile_reset()
+        S.sweep(3)
+        if level == 1:
+            sec = S.profile_read()
+            # every group once per recorded sweep: the two sweeps before the reset are gone, and the shared f* terms are formed in each recorded sweep
+            for name in ("gemm_LZ", "ess_f", "gemm_FtW", "ess_theta", "ess_beta", "ess_thr", "item_ll", "chol_K", "trtri", "gemm_tmp", "gemm_W", "chol_Kpost"):
+                assert sec[name][1] == 3, (name, sec[name])
+                assert sec[name][0] > 0.0
+            assert not any(k.startswith("wait_") for k in sec)
+        if level == 2:
+            tl = S.profile_timeline()
+            names = [t[0] for t in tl]
+            assert names.count("gemm_LZ") == 3 and names.count("chol_K") == 3 and names.count("chol_Kpost") == 3
+            assert all(0.0 <= b <= e for _, b, e in tl)
+            lz = [b for name, b, _ in tl if name == "gemm_LZ"]
+            assert lz == sorted(lz)
+            assert S.profile_timeline() == []  # collected
+        S.profile(0)
+        S.sync()
+        st = S.get_state(fstar=True)
+        st["ll"] = S.total_ll()
+        states.append(st)
+        S.close()
+    for st in states[1:]:
+        for k in ("theta", "beta", "f", "thresholds", "fstar"):
+            assert np.array_equal(states[0][k], st[k]), k
+        assert states[0]["ll"] == st["ll"]
+
+
 def test_fp32_screening_term_stays_inside_its_error_bound():
     """cell_ll32 (csrc/probit.cuh): |t32 - t64| <= e32 over random and adversarial cells (tails, narrow bins, edge categories)."""
     from gpirt_b200.api import debug_cell32
