@@ -86,12 +86,21 @@ __device__ __forceinline__ void block_sum2(double& a, double& b, double (*s_part
 }
 
 template <int MODE, int WARPS>
-__device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, double* tau, double* s_part, double (*s_part2)[2][WARPS], int& red_parity) {
+__device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, double* tau, double2* tau2, double* s_part, double (*s_part2)[2][WARPS],
+                                             int& red_parity) {
     constexpr int T = WARPS * 32;
     const int tid = threadIdx.x;
     const int J = v.item0 + j;
     const int C = v.C;
     for (int c = tid; c <= C; c += T) tau[c] = v.thr[(size_t)J * (C + 1) + c];
+    __syncthreads();
+    // tau2[y] = (tau[y-1], tau[y]): the two thresholds of a cell in one 16-byte shared-memory load indexed by the response itself; entry 0 (a missing
+    // response, evaluated and not added in the packed loop) repeats category 1. Rewritten by whoever rewrites tau, in front of the same barrier.
+    auto fill_tau2 = [&]() {
+        for (int c = 1; c <= C; ++c) tau2[c] = make_double2(tau[c - 1], tau[c]);
+        tau2[0] = tau2[1];
+    };
+    if (tid == 0) fill_tau2();
     __syncthreads();
 
     const int8_t* __restrict__ yj = v.y_im + (size_t)j * v.ldy;
@@ -158,9 +167,9 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
             }
             const double g0 = __dadd_rn(f0, mur ? mur[i] : mu_of(theta[i], pb0, pb1, pb2));
             const double g1 = __dadd_rn(f1, mur ? mur[i + T] : mu_of(theta[i + T], pb0, pb1, pb2));
-            const int c0 = y0 > 0 ? y0 : 1, c1 = y1 > 0 ? y1 : 1;
+            const double2 th0 = tau2[y0], th1 = tau2[y1];
             float t0, t1, et0, et1;
-            cell_ll32x2(g0, tau[c0 - 1], tau[c0], g1, tau[c1 - 1], tau[c1], t0, et0, t1, et1);
+            cell_ll32x2(g0, th0.x, th0.y, g1, th1.x, th1.y, t0, et0, t1, et1);
             l0 += (double)(y0 > 0 ? t0 : 0.0f);  // adding +0 leaves the sums as they are
             l1 += (double)(y1 > 0 ? t1 : 0.0f);
             e0 += y0 > 0 ? et0 : 0.0f;
@@ -204,6 +213,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
         if (tid == 0) {
             tau[1] = delta[0];
             for (int q = 1; q < C - 1; ++q) tau[q + 1] = __dadd_rn(tau[q], exp(delta[q]));
+            fill_tau2();
         }
         __syncthreads();
     }
@@ -226,6 +236,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
                 tau[1] = __dadd_rn(__dmul_rn(delta[0], ce_), __dmul_rn(nu_small[0], se_));
                 for (int q = 1; q < C - 1; ++q)
                     tau[q + 1] = __dadd_rn(tau[q], exp(__dadd_rn(__dmul_rn(delta[q], ce_), __dmul_rn(nu_small[q], se_))));
+                fill_tau2();
             }
             __syncthreads();
         }
@@ -287,6 +298,7 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
                     if (tid == 0) {
                         tau[1] = delta[0];
                         for (int q = 1; q < C - 1; ++q) tau[q + 1] = __dadd_rn(tau[q], exp(delta[q]));
+                        fill_tau2();
                     }
                     __syncthreads();
                 }
@@ -335,11 +347,12 @@ __device__ __forceinline__ void ess_one_item(const ItemView& v, const int j, dou
 template <int MODE, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 32 / WARPS) k_ess_items(ItemView v) {
     __shared__ double tau[MAX_C + 1];
+    __shared__ double2 tau2[MAX_C + 1];
     __shared__ double s_part[WARPS];
     __shared__ double s_part2[2][2][WARPS];
     int red_parity = 0;
     for (int j = blockIdx.x; j < v.m_local; j += gridDim.x) {
-        ess_one_item<MODE, WARPS>(v, j, tau, s_part, s_part2, red_parity);
+        ess_one_item<MODE, WARPS>(v, j, tau, tau2, s_part, s_part2, red_parity);
         __syncthreads();  // tau / s_part are reused by the next item
     }
 }
