@@ -76,7 +76,7 @@ SYMBOLS = [
     "gpirt_sweep_phase_items", "gpirt_sweep_phase_theta", "gpirt_sweep_phase_close", "gpirt_theta_items_begin", "gpirt_theta_items_partials",
     "gpirt_theta_items_decide", "gpirt_items_pack", "gpirt_exchange_pull", "gpirt_chain_export", "gpirt_chain_attach", "gpirt_chain_detach", "gpirt_exchange_buffer",
     "gpirt_total_ll", "gpirt_init_draw", "gpirt_mcmc", "gpirt_memory_estimate", "gpirt_mcmc_chains", "gpirt_copy_data", "gpirt_set_mean_rows", "gpirt_interp1", "gpirt_ipc_export", "gpirt_ipc_attach", "gpirt_ipc_detach", "gpirt_peer_wait", "gpirt_recover_fstar", "gpirt_profile_enable", "gpirt_profile_read",
-    "gpirt_profile_reset", "gpirt_profile_timeline", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit", "gpirt_debug_phi_tab", "gpirt_debug_cell32", "gpirt_debug_fp64_peak", "gpirt_debug_chol_trace",
+    "gpirt_profile_reset", "gpirt_profile_timeline", "gpirt_debug_dist_plan", "gpirt_debug_uniforms", "gpirt_debug_normals", "gpirt_launch_count", "gpirt_debug_probit", "gpirt_debug_phi_tab", "gpirt_debug_cell32", "gpirt_debug_fp64_peak", "gpirt_debug_chol_trace",
 ]
 
 _lib = None

@@ -1126,11 +1126,7 @@ static int prep_fstar_shared(gpirt_sampler* h, cudaStream_t st, cudaEvent_t ev_a
         // distributed: the grid points' columns are split over the ranks in runs of whole 64-column tiles (same tiles, same k ranges as the one launch);
         // every rank forms its columns of tmp = L^-1 k* and of W = L^-T tmp and pushes both to its peers
         int c_lo = 0, c_hi = N;
-        if (distributed) {
-            const int tiles = (N + 63) / 64, per = (tiles + h->world - 1) / h->world;
-            c_lo = std::min(N, h->rank * per * 64);
-            c_hi = std::min(N, (h->rank + 1) * per * 64);
-        }
+        if (distributed) kstar_dist_cols(N, h->world, h->rank, &c_lo, &c_hi);
         GemmArgs g{};
         g.M = n; g.N = c_hi - c_lo; g.K = n; g.A = h->Linv; g.lda = h->ldn; g.B = h->W + (size_t)c_lo * h->ldn; g.ldb = h->ldn;
         g.C = h->W2 + (size_t)c_lo * h->ldn; g.ldc = h->ldn;
@@ -1512,6 +1508,27 @@ int gpirt_chain_attach(gpirt_sampler* h, int peer_rank, const void* handle64, co
     static const int min_n = getenv("GPIRT_DIST_CHAIN_MIN_N") ? atoi(getenv("GPIRT_DIST_CHAIN_MIN_N")) : 4096;
     h->dist_chain = enabled && h->chain_attached == h->world - 1 && h->n >= min_n;
     return GPIRT_OK;
+}
+// Test hook (no device needed): rank `rank`'s share of the distributed theta-only chain for n respondents on `world` ranks — out[0..1] its columns of the
+// grid points (L^-1 k*, K^-1 k*), out[2] the number of 256-column Cholesky blocks it owns, out[3] the number of split inversion levels, then for each
+// split level (block widths ascending) its block width and its column range: out[4 + 3 l .. 6 + 3 l]. Returns the number of ints written.
+int gpirt_debug_dist_plan(int n, int world, int rank, int32_t* out, int cap) {
+    if (!out || n < 1 || world < 1 || rank < 0 || rank >= world || cap < 4) return fail(GPIRT_ERR_INVALID, "debug_dist_plan: bad arguments");
+    int lo = 0, hi = 0;
+    kstar_dist_cols((int)NGRID, world, rank, &lo, &hi);
+    out[0] = lo; out[1] = hi;
+    int owned = 0;
+    for (int b = 0; b < chol_dist_blocks(n); ++b) owned += chol_dist_owner(b, world) == rank;
+    out[2] = owned;
+    int k = 4, levels = 0;
+    for (int b = CHOL_NB; b < n; b *= 2) {
+        if (!trtri_dist_level(b, world)) continue;
+        if (k + 3 > cap) return fail(GPIRT_ERR_INVALID, "debug_dist_plan: cap too small");
+        out[k++] = b; out[k++] = trtri_dist_cut(b, world, rank); out[k++] = trtri_dist_cut(b, world, rank + 1);
+        ++levels;
+    }
+    out[3] = levels;
+    return k;
 }
 int gpirt_chain_detach(gpirt_sampler* h) {
     CHECK_H(h);

@@ -535,7 +535,7 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
     for (int o0 = 0; o0 < n; o0 += OB) {
         const int ob = (n - o0 < OB) ? n - o0 : OB;
         if (distributed && o0 > 0) {  // columns [o0, o0 + ob), rows o0 .. n-1, as updated by their owner
-            const int b = o0 / OB, owner = b % dist->world;
+            const int b = o0 / OB, owner = chol_dist_owner(b, dist->world);
             if (owner != dist->rank) {
                 cudaError_t ew = dist->wait(dist->ctx, st, b, owner);
                 if (ew != cudaSuccess) return ew;
@@ -580,7 +580,7 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
             };
             if (ahead && (e = cudaEventRecord(aux->ev_panel, st)) != cudaSuccess) return e;
             const int b_next = (o0 + ob) / OB;
-            if (b_next % dist->world == dist->rank) {  // the next outer block is this rank's: updated first, on the panels' stream, and published
+            if (chol_dist_owner(b_next, dist->world) == dist->rank) {  // the next outer block is this rank's: updated first, on the panels' stream, and published
                 if (rest_pending) {  // its earlier updates ran on the helper stream
                     if ((e = cudaStreamWaitEvent(st, aux->ev_rest, 0)) != cudaSuccess) return e;
                     rest_pending = false;
@@ -593,7 +593,7 @@ cudaError_t chol_lower_blocked(cudaStream_t st, double* A, int ld, int n, int* i
             cudaStream_t s2 = ahead ? aux->helper : st;
             bool any = false;
             for (int c0 = OB; c0 < rows_t; c0 += OB) {
-                if (((o0 + ob + c0) / OB) % dist->world != dist->rank) continue;
+                if (chol_dist_owner((o0 + ob + c0) / OB, dist->world) != dist->rank) continue;
                 if (!any && ahead && (e = cudaStreamWaitEvent(s2, aux->ev_panel, 0)) != cudaSuccess) return e;
                 any = true;
                 if ((e = update_block(s2, c0)) != cudaSuccess) return e;
@@ -711,18 +711,11 @@ cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double*
         if (pairs == 0) break;
         // this rank's columns [c_lo, c_hi) of every pair's b x b block. Work per column at relative position x: 2(1 - x) in the first product (A^-1 is
         // lower triangular) + 1 in the second: the cumulative 3x - x^2 is cut into `world` equal parts.
-        const bool split = dist && dist->world > 1 && dist->push && dist->sync && b >= 512 && b / 64 >= dist->world;
+        const bool split = dist && dist->push && dist->sync && trtri_dist_level(b, dist->world);
         int c_lo = 0, c_hi = b;
         if (split) {
-            auto cut = [&](int r) {
-                if (r <= 0) return 0;
-                if (r >= dist->world) return b;
-                const double x = (3.0 - sqrt(9.0 - 8.0 * (double)r / dist->world)) * 0.5;
-                int c = (int)(x * (b / 64) + 0.5) * 64;
-                return c < 0 ? 0 : (c > b ? b : c);
-            };
-            c_lo = cut(dist->rank);
-            c_hi = cut(dist->rank + 1);
+            c_lo = trtri_dist_cut(b, dist->world, dist->rank);
+            c_hi = trtri_dist_cut(b, dist->world, dist->rank + 1);
         }
         cudaError_t e;
         if (c_hi > c_lo) {

@@ -1,5 +1,6 @@
 // Declarations of the dense fp64 building blocks (see linalg.cu).
 #pragma once
+#include <cmath>
 #include <cuda_runtime.h>
 
 #include <cstdint>
@@ -80,5 +81,24 @@ struct TrtriDist {
     cudaError_t (*sync)(void* ctx, cudaStream_t st) = nullptr;
 };
 cudaError_t trtri_lower(cudaStream_t st, const double* L, int ld, int n, double* Linv, int ldi, double* scratch, const TrtriDist* dist = nullptr);
+
+// ---- who computes what in the distributed theta-only chain: pure functions of (sizes, world, rank), the same on every rank (tests/test_dist_plan.py) ----
+inline int chol_dist_owner(int block, int world) { return block % world; }  // 256-column outer block `block` of the two-level Cholesky
+inline bool trtri_dist_level(int b, int world) { return world > 1 && b >= 512 && b / 64 >= world; }  // is the merge level with b-column blocks split?
+// first column of rank r's share of a b-column block of a split level (r = world: b). Work per column at relative position x: 2(1 - x) in the first
+// product (A^-1 is lower triangular) + 1 in the second; the cumulative 3x - x^2 is cut into `world` equal parts, at whole 64-column tiles.
+inline int trtri_dist_cut(int b, int world, int r) {
+    if (r <= 0) return 0;
+    if (r >= world) return b;
+    const double x = (3.0 - sqrt(9.0 - 8.0 * (double)r / world)) * 0.5;
+    const int c = (int)(x * (b / 64) + 0.5) * 64;
+    return c < 0 ? 0 : (c > b ? b : c);
+}
+// columns [lo, hi) of the N grid points whose L^-1 k* and K^-1 k* rank r forms: runs of whole 64-column tiles
+inline void kstar_dist_cols(int N, int world, int r, int* lo, int* hi) {
+    const int tiles = (N + 63) / 64, per = (tiles + world - 1) / world;
+    *lo = r * per * 64 < N ? r * per * 64 : N;
+    *hi = (r + 1) * per * 64 < N ? (r + 1) * per * 64 : N;
+}
 
 }  // namespace gpirt

@@ -239,6 +239,8 @@ int gpirt_exchange_pull(gpirt_sampler* dst, gpirt_sampler* src, int which);
 int gpirt_chain_export(gpirt_sampler* h, void* handle64, int64_t* offsets6);
 int gpirt_chain_attach(gpirt_sampler* h, int peer_rank, const void* handle64, const int64_t* offsets6);
 int gpirt_chain_detach(gpirt_sampler* h);
+/* test hook, no device needed: what rank `rank` of `world` computes in the distributed chain at n respondents (layout of `out`: csrc/capi.cu); returns the count (>= 4) or GPIRT_ERR_INVALID */
+int gpirt_debug_dist_plan(int n, int world, int rank, int32_t* out, int cap);
 /* device pointer of the all-gather buffer `which`; it holds `world` equal chunks of chunk_bytes, chunk r owned by rank r */
 int gpirt_exchange_buffer(gpirt_sampler* h, int which, void** dev_ptr, int64_t* chunk_bytes);
 int gpirt_total_ll(gpirt_sampler* h, double* total);         /* after the ITEM_LL exchange (or world == 1) */
